@@ -1,0 +1,119 @@
+/* libdv3b200 -- C ABI of the B200 (sm_100a) kernels behind the DreamerV3 training step.
+ *
+ * The reference (hanshuo-shuo/sheeprl_prey, SheepRL 0.4.4) is 100 % Python and has no FFI for this path; its
+ * boundary is the Python-level `train()` / `build_models()` / replay-buffer API.  This
+ * header is the C-ABI a maintainer binds from Python with ctypes (INTEGRATION.md shows the stub); each entry
+ * point cites the reference lines whose arithmetic it replaces (paths relative to the reference root).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative DV3_ERR_* code for bad arguments, or a positive
+ *     cudaError_t if the launch failed; nothing throws, nothing allocates, nothing synchronises;
+ *   - all pointers are DEVICE pointers owned by the caller (float = fp32, int = int32, long long = int64);
+ *   - matrices are row-major; `ld*` is the row stride in elements (the last dimension is contiguous);
+ *   - `stream` is a cudaStream_t passed as void*; kernels are enqueued on it and the call returns immediately;
+ *   - functions taking `scratch` use it as device workspace (size from the matching *_scratch_bytes());
+ *   - no hidden global state: calls on different streams with different buffers are independent.
+ */
+#ifndef DV3_B200_H
+#define DV3_B200_H
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DV3_OK 0
+#define DV3_ERR_ARG (-1)
+#define DV3_ERR_UNSUPPORTED (-2)
+#define DV3_ERR_SCRATCH (-3)
+
+#define DV3_GEMM_NT 0 /* C[M,N] = A[M,K] * B[N,K]^T   (nn.Linear forward)            */
+#define DV3_GEMM_NN 1 /* C[M,N] = A[M,K] * B[K,N]     (input gradient dX = dY * W)    */
+#define DV3_GEMM_TN 2 /* C[M,N] = A[K,M]^T * B[K,N]   (weight gradient dW = dY^T * X) */
+
+int dv3_version(void);
+
+/* ---- replay (sheeprl/data/buffers.py) ------------------------------------------------------------------- */
+/* ReplayBuffer.add, buffers.py:99-151: rows l=0..L-1 of `src` ([L][row_bytes]) go to ring[env][(pos+l) % size]. */
+int dv3_buffer_add(const void* src, void* ring, int env, long long pos, int L, int size, long long row_bytes, void* stream);
+/* SequentialReplayBuffer.sample/_get_samples buffers.py:238-339 + AsyncReplayBuffer.sample :646-690 (the byte
+ * movement; index selection stays on the host with the reference's RNG call order).  For every key k:
+ * dst[k][samp[j]][t][col[j]][:] = src[k][env_id[j]][(start[j]+t) % size][:], j < B*n_samples, t < T. Bit-exact. */
+int dv3_seq_gather(int n_keys, const void* const* src, void* const* dst, const long long* row_bytes, int size, int T, int B,
+                   int n_samples, const int* env_id, const long long* start, const int* col, const int* samp, void* stream);
+
+/* ---- dense contractions: every torch addmm/mm of the step (models.py:115-118, :389 and their backward) ---- */
+int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                 const float* bias, int accumulate, void* stream);
+
+/* ---- LayerNorm(+SiLU) blocks: miniblock order Linear -> LayerNorm -> SiLU, utils/model.py:71-87 ---------- */
+int dv3_ln_act_fwd(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
+                   float* y, int ldy, float* mean, float* rstd, void* stream);
+int dv3_ln_act_bwd(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
+                   const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* stream);
+/* out_a[u] = sum_m d[m,u]*xhat[m,u] (LN weight grad; skipped when x == NULL), out_b[u] = sum_m d[m,u] (LN bias /
+ * Linear bias grad).  Two-stage reduction through `scratch`. */
+size_t dv3_col_reduce_scratch_bytes(int M, int U);
+int dv3_col_reduce(int M, int U, const float* d, int ldd, const float* x, int ldx, const float* mean, const float* rstd,
+                   float* out_a, float* out_b, float* scratch, size_t scratch_bytes, void* stream);
+
+/* ---- LayerNormGRUCell gates, models.py:388-395 ------------------------------------------------------------ */
+int dv3_gru_gate_fwd(int R, int D, const float* gates_pre, int ldg, const float* lnw, const float* lnb, const float* h_in,
+                     int ldhi, float* h_out, int ldho, float* mean, float* rstd, void* stream);
+int dv3_gru_gate_bwd(int R, int D, const float* dh_out, int lddho, const float* gates_pre, int ldg, const float* lnw,
+                     const float* lnb, const float* mean, const float* rstd, const float* h_in, int ldhi, float* dgates_pre,
+                     int lddg, float* dln, int lddln, float* dh_in, int lddhi, void* stream);
+
+/* ---- RSSM.dynamic plumbing, agent.py:379-384 and dreamer_v3.py:108 ---------------------------------------- */
+int dv3_scan_prep(int B, int D, int S, const float* first, const float* h_prev, int ldhp, const float* z_prev, int ldzp,
+                  const float* zreset, float* h_in, int ldhi, float* z_in, int ldzi, void* stream);
+int dv3_scan_carry(int B, int D, int S, const float* first, const float* dz_prev, int lddz, const float* dh_a, int lda,
+                   const float* dh_b, int ldb, float* dz_dst, int ldzd, float* dh_dst, int ldhd, void* stream);
+int dv3_mask_shift_actions(int T, int B, int A, const float* actions, const float* first, float* out, int ldo, void* stream);
+
+/* ---- categorical: unimix agent.py:390-402/:741-747; ST one-hot sample distribution.py:355-360,:390-393 ---- */
+int dv3_unimix_fwd(int R, int groups, int K, float mix, const float* raw, int ldr, float* logits, int ldo, void* stream);
+int dv3_sample_onehot(int R, int groups, int K, const float* logits, int ldl, const float* u, int ldu, const int* forced,
+                      int ldf, int mode, int* idx, int ldi, float* onehot, int ldo, void* stream);
+int dv3_unimix_bwd(int R, int groups, int K, float mix, const float* raw, int ldr, const float* dlogits, int lddl,
+                   const float* dz, int lddz, float* draw, int lddr, void* stream);
+
+/* ---- world-model losses, loss.py:65-110 with distribution.py:177-193 (symlog MSE), :253-270 (two-hot) ---- */
+int dv3_kl_balance(int R, int groups, int K, const float* post, const float* prior, float free_nats, float w_dyn, float w_rep,
+                   float scale, float* rows_out, float* dpost, float* dprior, void* stream);
+int dv3_twohot_loss(int M, int K, const float* logits, int ldl, const float* x, const float* w, float scale, float* loss_rows,
+                    float* dlogits, int ldd, int accumulate, void* stream);
+int dv3_twohot_mean(int M, int K, const float* logits, int ldl, float* out, void* stream); /* distribution.py:245-247 */
+int dv3_symlog(size_t n, const float* x, float* y, void* stream);                           /* utils/utils.py:120-121 */
+int dv3_symlog_mse(int M, int D, const float* mode, int ldm, const float* target, int ldt, float scale, float* loss_rows,
+                   float* dmode, int ldd, void* stream);
+int dv3_bernoulli_loss(int M, const float* logit, const float* dones, float scale, float* loss_rows, float* dlogit, void* stream);
+int dv3_reduce_mean(int M, const float* x, int ldx, int col, float* out, int slot, float scale, int accumulate, void* stream);
+
+/* ---- behaviour learning --------------------------------------------------------------------------------- */
+/* compute_lambda_values algos/dreamer_v3/utils.py:44-55 + continues/discount dreamer_v3.py:262-280 */
+int dv3_lambda_returns(int H, int N, const float* values, const float* rewards, const float* cont_logit, const float* dones,
+                       float gamma, float lmbda, float* lam, float* discount, void* stream);
+/* Moments.forward algos/dreamer_v3/utils.py:34-41 (exact torch.quantile 'linear' by radix select) */
+int dv3_moments(int n, const float* x, float* state, float* out, float decay, float max_, float plow, float phigh, void* stream);
+/* actor objective dreamer_v3.py:292-317 (discrete): value per row + gradient wrt the raw head logits */
+int dv3_actor_loss(int M, int n_heads, const int* head_dims_host, const float* raw, int ldr, const int* act_idx, int lda,
+                   const float* lam, const float* values, const float* discount, const float* mom, float mix, float ent_coef,
+                   float scale, float* loss_rows, float* draw, int ldd, void* stream);
+
+/* ---- optimizer: clip_grad_norm_ + torch.optim.Adam.step, dreamer_v3.py:179-187,:318-323,:339-344 ---------- */
+size_t dv3_adam_clip_scratch_bytes(void);
+int dv3_adam_clip(size_t n, float* p, const float* g, float* m, float* v, float* step, float lr, float beta1, float beta2,
+                  float eps, float max_norm, float* norm_out, int slot, float* scratch, size_t scratch_bytes, void* stream);
+int dv3_ema(size_t n, float* target, const float* src, float tau, void* stream); /* dreamer_v3.py:713-716 */
+
+/* ---- utilities ------------------------------------------------------------------------------------------- */
+int dv3_copy2d(int R, int C, const float* s, int lds, float* d, int ldd, void* stream);
+int dv3_transpose(int R, int C, const float* s, int lds, float* d, int ldd, void* stream);
+int dv3_fill(size_t n, float* p, float v, void* stream);
+int dv3_uniform_fill(size_t n, float* out, unsigned long long seed, long long* counter, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DV3_B200_H */

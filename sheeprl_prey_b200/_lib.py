@@ -1,0 +1,331 @@
+"""ctypes binding of libdv3b200.so (the C-ABI declared in include/dv3_b200.h) and `CudaOps`, the object the
+step engine calls.  There is no fallback: if the library is missing or a call fails, this raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Sequence
+
+import torch
+
+Tensor = torch.Tensor
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdv3b200.so")
+_lib = None
+
+c_fp = C.c_void_p
+_i, _f, _sz, _ll, _ull = C.c_int, C.c_float, C.c_size_t, C.c_longlong, C.c_ulonglong
+
+# name -> argtypes (restype is int unless listed in _RESTYPE)
+SIGNATURES = {
+    "dv3_version": [],
+    "dv3_buffer_add": [c_fp, c_fp, _i, _ll, _i, _i, _ll, c_fp],
+    "dv3_seq_gather": [_i, c_fp, c_fp, c_fp, _i, _i, _i, _i, c_fp, c_fp, c_fp, c_fp, c_fp],
+    "dv3_gemm_f32": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_ln_act_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp],
+    "dv3_ln_act_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_col_reduce_scratch_bytes": [_i, _i],
+    "dv3_col_reduce": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
+    "dv3_gru_gate_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp],
+    "dv3_gru_gate_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_scan_prep": [_i, _i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_scan_carry": [_i, _i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_mask_shift_actions": [_i, _i, _i, c_fp, c_fp, c_fp, _i, c_fp],
+    "dv3_unimix_fwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_sample_onehot": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_unimix_bwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_kl_balance": [_i, _i, _i, c_fp, c_fp, _f, _f, _f, _f, c_fp, c_fp, c_fp, c_fp],
+    "dv3_twohot_loss": [_i, _i, c_fp, _i, c_fp, c_fp, _f, c_fp, c_fp, _i, _i, c_fp],
+    "dv3_twohot_mean": [_i, _i, c_fp, _i, c_fp, c_fp],
+    "dv3_symlog": [_sz, c_fp, c_fp, c_fp],
+    "dv3_symlog_mse": [_i, _i, c_fp, _i, c_fp, _i, _f, c_fp, c_fp, _i, c_fp],
+    "dv3_bernoulli_loss": [_i, c_fp, c_fp, _f, c_fp, c_fp, c_fp],
+    "dv3_reduce_mean": [_i, c_fp, _i, _i, c_fp, _i, _f, _i, c_fp],
+    "dv3_lambda_returns": [_i, _i, c_fp, c_fp, c_fp, c_fp, _f, _f, c_fp, c_fp, c_fp],
+    "dv3_moments": [_i, c_fp, c_fp, c_fp, _f, _f, _f, _f, c_fp],
+    "dv3_actor_loss": [_i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _f, _f, _f, c_fp, c_fp, _i, c_fp],
+    "dv3_adam_clip_scratch_bytes": [],
+    "dv3_adam_clip": [_sz, c_fp, c_fp, c_fp, c_fp, c_fp, _f, _f, _f, _f, _f, c_fp, _i, c_fp, _sz, c_fp],
+    "dv3_ema": [_sz, c_fp, c_fp, _f, c_fp],
+    "dv3_copy2d": [_i, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_transpose": [_i, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_fill": [_sz, c_fp, _f, c_fp],
+    "dv3_uniform_fill": [_sz, c_fp, _ull, c_fp, c_fp],
+}
+_RESTYPE = {"dv3_col_reduce_scratch_bytes": _sz, "dv3_adam_clip_scratch_bytes": _sz}
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen the in-tree library and declare every prototype.  Raises if it is absent (no fallback)."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise RuntimeError(
+            f"{p} not found: build it with `python -m sheeprl_prey_b200.build` (nvcc, sm_100a). "
+            "sheeprl_prey_b200 has no CPU or PyTorch fallback for its kernels.")
+    lib = C.CDLL(p)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = _RESTYPE.get(name, _i)
+    if path is None:
+        _lib = lib
+    return lib
+
+
+class Dv3Error(RuntimeError):
+    pass
+
+
+def _chk(rc: int, what: str) -> None:
+    if rc != 0:
+        kind = {-1: "bad argument", -2: "unsupported size", -3: "scratch too small"}.get(rc, f"cudaError {rc}")
+        raise Dv3Error(f"{what} failed: {kind}")
+
+
+def _p(t: Optional[Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _mat(t: Tensor):
+    """(ptr, rows, cols, ld) of a 2-D view with contiguous last dim."""
+    assert t.dim() == 2 and (t.stride(1) == 1 or t.shape[1] == 1), (t.shape, t.stride())
+    return t.data_ptr(), t.shape[0], t.shape[1], (t.stride(0) if t.shape[0] > 1 else max(t.stride(0), t.shape[1]))
+
+
+_MODE = {"NT": 0, "NN": 1, "TN": 2}
+
+
+class CudaOps:
+    """The primitive ops of the step, each one C-ABI call enqueued on torch's current CUDA stream.
+    Method semantics are stated (in torch) by oracle/torch_ops.py, which the GPU tests compare against."""
+
+    name = "cuda"
+
+    def __init__(self, device, scratch_bytes: int = 32 << 20):
+        self.lib = load_library()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("CudaOps needs a CUDA device; sheeprl_prey_b200 has no CPU path")
+        self.scratch = torch.empty(scratch_bytes // 4, dtype=torch.float32, device=self.device)
+        self.launches = 0   # kernels of ours enqueued so far
+        self.gemm_log = None   # when a list: (start_event, end_event, flops, M, N, K, mode) per gemm call (bench / profiling)
+
+    def _s(self):
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    # ---------------------------------------------------------------- contractions
+    def gemm(self, mode, A, B, Cm, bias=None, accumulate=False):
+        pa, ra, ca, lda = _mat(A)
+        pb, rb, cb, ldb = _mat(B)
+        pc, M, N, ldc = _mat(Cm)
+        if mode == "NT":
+            K = ca
+            assert ra == M and rb == N and cb == K, (mode, A.shape, B.shape, Cm.shape)
+        elif mode == "NN":
+            K = ca
+            assert ra == M and rb == K and cb == N, (mode, A.shape, B.shape, Cm.shape)
+        else:
+            K = ra
+            assert ca == M and rb == K and cb == N, (mode, A.shape, B.shape, Cm.shape)
+        self.launches += 1
+        if self.gemm_log is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(torch.cuda.current_stream(self.device))
+        _chk(self.lib.dv3_gemm_f32(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()), "dv3_gemm_f32")
+        if self.gemm_log is not None:
+            e1.record(torch.cuda.current_stream(self.device))
+            self.gemm_log.append((e0, e1, 2.0 * M * N * K, M, N, K, mode))
+
+    def transpose(self, src, dst):
+        ps, R, Cc, lds = _mat(src)
+        pd, _, _, ldd = _mat(dst)
+        self.launches += 1
+        _chk(self.lib.dv3_transpose(R, Cc, ps, lds, pd, ldd, self._s()), "dv3_transpose")
+
+    def copy2d(self, src, dst):
+        ps, R, Cc, lds = _mat(src)
+        pd, R2, C2, ldd = _mat(dst)
+        assert (R, Cc) == (R2, C2)
+        self.launches += 1
+        _chk(self.lib.dv3_copy2d(R, Cc, ps, lds, pd, ldd, self._s()), "dv3_copy2d")
+
+    # ---------------------------------------------------------------- LayerNorm
+    def ln_act_fwd(self, x, gamma, beta, eps, act, y, mean, rstd):
+        px, M, U, ldx = _mat(x)
+        py, _, _, ldy = _mat(y)
+        self.launches += 1
+        _chk(self.lib.dv3_ln_act_fwd(M, U, px, ldx, _p(gamma), _p(beta), eps, act, py, ldy, _p(mean), _p(rstd), self._s()), "dv3_ln_act_fwd")
+
+    def ln_act_bwd(self, dy, x, gamma, beta, mean, rstd, act, dx, dln):
+        pdy, M, U, lddy = _mat(dy)
+        px, _, _, ldx = _mat(x)
+        pdx, _, _, lddx = _mat(dx)
+        pdl, lddl = (None, 0) if dln is None else (_mat(dln)[0], _mat(dln)[3])
+        self.launches += 1
+        _chk(self.lib.dv3_ln_act_bwd(M, U, pdy, lddy, px, ldx, _p(gamma), _p(beta), _p(mean), _p(rstd), act, pdx, lddx, pdl, lddl,
+                                     self._s()), "dv3_ln_act_bwd")
+
+    def ln_param_grad(self, dln, x, mean, rstd, dgamma, dbeta):
+        pd, M, U, ldd = _mat(dln)
+        px, _, _, ldx = _mat(x)
+        self.launches += 2
+        _chk(self.lib.dv3_col_reduce(M, U, pd, ldd, px, ldx, _p(mean), _p(rstd), _p(dgamma), _p(dbeta), self.scratch.data_ptr(),
+                                     self.scratch.numel() * 4, self._s()), "dv3_col_reduce")
+
+    def colsum(self, dy, db):
+        pd, M, U, ldd = _mat(dy)
+        self.launches += 2
+        _chk(self.lib.dv3_col_reduce(M, U, pd, ldd, None, 0, None, None, None, _p(db), self.scratch.data_ptr(),
+                                     self.scratch.numel() * 4, self._s()), "dv3_col_reduce")
+
+    def symlog(self, x, y):
+        self.launches += 1
+        _chk(self.lib.dv3_symlog(x.numel(), _p(x), _p(y), self._s()), "dv3_symlog")
+
+    # ---------------------------------------------------------------- GRU
+    def gru_gate_fwd(self, gates_pre, lnw, lnb, h_in, h_out, mean, rstd):
+        pg, R, D3, ldg = _mat(gates_pre)
+        phi, _, _, ldhi = _mat(h_in)
+        pho, _, _, ldho = _mat(h_out)
+        self.launches += 1
+        _chk(self.lib.dv3_gru_gate_fwd(R, D3 // 3, pg, ldg, _p(lnw), _p(lnb), phi, ldhi, pho, ldho, _p(mean), _p(rstd), self._s()),
+             "dv3_gru_gate_fwd")
+
+    def gru_gate_bwd(self, dh_out, gates_pre, lnw, lnb, mean, rstd, h_in, dgates_pre, dln, dh_in):
+        pdo, R, D, lddo = _mat(dh_out)
+        pg, _, _, ldg = _mat(gates_pre)
+        phi, _, _, ldhi = _mat(h_in)
+        pdg, _, _, lddg = _mat(dgates_pre)
+        pdl, _, _, lddl = _mat(dln)
+        pdi, _, _, lddi = _mat(dh_in)
+        self.launches += 1
+        _chk(self.lib.dv3_gru_gate_bwd(R, D, pdo, lddo, pg, ldg, _p(lnw), _p(lnb), _p(mean), _p(rstd), phi, ldhi, pdg, lddg, pdl, lddl,
+                                       pdi, lddi, self._s()), "dv3_gru_gate_bwd")
+
+    # ---------------------------------------------------------------- categorical
+    def unimix_fwd(self, raw, groups, K, unimix, logits):
+        pr, R, _, ldr = _mat(raw)
+        po, _, _, ldo = _mat(logits)
+        self.launches += 1
+        _chk(self.lib.dv3_unimix_fwd(R, groups, K, unimix, pr, ldr, po, ldo, self._s()), "dv3_unimix_fwd")
+
+    def sample_onehot(self, logits, groups, K, u, forced, mode, idx, onehot):
+        pl, R, _, ldl = _mat(logits)
+        pu, ldu = (None, 0) if u is None else (_mat(u)[0], _mat(u)[3])
+        pf, ldf = (None, 0) if forced is None else (_mat(forced)[0], _mat(forced)[3])
+        if forced is not None:
+            assert forced.dtype == torch.int32
+        pi, _, _, ldi = _mat(idx)
+        po, _, _, ldo = _mat(onehot)
+        self.launches += 1
+        _chk(self.lib.dv3_sample_onehot(R, groups, K, pl, ldl, pu, ldu, pf, ldf, mode, pi, ldi, po, ldo, self._s()), "dv3_sample_onehot")
+
+    def unimix_bwd(self, raw, groups, K, unimix, dlogits, dz, draw):
+        pr, R, _, ldr = _mat(raw)
+        pdl, lddl = (None, 0) if dlogits is None else (_mat(dlogits)[0], _mat(dlogits)[3])
+        pdz, lddz = (None, 0) if dz is None else (_mat(dz)[0], _mat(dz)[3])
+        pdr, _, _, lddr = _mat(draw)
+        self.launches += 1
+        _chk(self.lib.dv3_unimix_bwd(R, groups, K, unimix, pr, ldr, pdl, lddl, pdz, lddz, pdr, lddr, self._s()), "dv3_unimix_bwd")
+
+    # ---------------------------------------------------------------- losses
+    def kl_balance(self, post, prior, groups, K, free_nats, w_dyn, w_rep, scale, rows_out, dpost, dprior):
+        for t in (post, prior, dpost, dprior, rows_out):
+            assert t.is_contiguous()
+        self.launches += 1
+        _chk(self.lib.dv3_kl_balance(post.shape[0], groups, K, _p(post), _p(prior), free_nats, w_dyn, w_rep, scale, _p(rows_out),
+                                     _p(dpost), _p(dprior), self._s()), "dv3_kl_balance")
+
+    def twohot_loss(self, logits, x, w, scale, loss_rows, dlogits, accumulate):
+        pl, M, K, ldl = _mat(logits)
+        pd, _, _, ldd = _mat(dlogits)
+        self.launches += 1
+        _chk(self.lib.dv3_twohot_loss(M, K, pl, ldl, _p(x), _p(w), scale, _p(loss_rows), pd, ldd, int(accumulate), self._s()),
+             "dv3_twohot_loss")
+
+    def twohot_mean(self, logits, out):
+        pl, M, K, ldl = _mat(logits)
+        self.launches += 1
+        _chk(self.lib.dv3_twohot_mean(M, K, pl, ldl, _p(out), self._s()), "dv3_twohot_mean")
+
+    def symlog_mse(self, mode, target, scale, loss_rows, dmode):
+        pm, M, Dd, ldm = _mat(mode)
+        pt, _, _, ldt = _mat(target)
+        pd, _, _, ldd = _mat(dmode)
+        self.launches += 1
+        _chk(self.lib.dv3_symlog_mse(M, Dd, pm, ldm, pt, ldt, scale, _p(loss_rows), pd, ldd, self._s()), "dv3_symlog_mse")
+
+    def bernoulli_loss(self, logit, dones, scale, loss_rows, dlogit):
+        self.launches += 1
+        _chk(self.lib.dv3_bernoulli_loss(logit.numel(), _p(logit), _p(dones), scale, _p(loss_rows), _p(dlogit), self._s()),
+             "dv3_bernoulli_loss")
+
+    def reduce_mean(self, x, col, out, slot, scale, accumulate):
+        px, M, _, ldx = _mat(x)
+        self.launches += 1
+        _chk(self.lib.dv3_reduce_mean(M, px, ldx, col, _p(out), slot, scale, int(accumulate), self._s()), "dv3_reduce_mean")
+
+    # ---------------------------------------------------------------- behaviour
+    def lambda_returns(self, values, rewards, cont_logit, dones, H, N, gamma, lmbda, lam, discount):
+        self.launches += 1
+        _chk(self.lib.dv3_lambda_returns(H, N, _p(values), _p(rewards), _p(cont_logit), _p(dones), gamma, lmbda, _p(lam), _p(discount),
+                                         self._s()), "dv3_lambda_returns")
+
+    def moments(self, x, state, out, decay, max_, plow, phigh):
+        self.launches += 1
+        _chk(self.lib.dv3_moments(x.numel(), _p(x), _p(state), _p(out), decay, max_, plow, phigh, self._s()), "dv3_moments")
+
+    def actor_loss(self, raw, head_dims: Sequence[int], act_idx, lam, values, discount, mom, unimix, ent_coef, scale, loss_rows, draw):
+        pr, M, _, ldr = _mat(raw)
+        pa, _, _, lda = _mat(act_idx)
+        pd, _, _, ldd = _mat(draw)
+        hd = (C.c_int * len(head_dims))(*head_dims)
+        self.launches += 1
+        _chk(self.lib.dv3_actor_loss(M, len(head_dims), C.cast(hd, C.c_void_p), pr, ldr, pa, lda, _p(lam), _p(values), _p(discount),
+                                     _p(mom), unimix, ent_coef, scale, _p(loss_rows), pd, ldd, self._s()), "dv3_actor_loss")
+
+    # ---------------------------------------------------------------- optimizer
+    def adam_clip(self, p, g, m, v, step, lr, beta1, beta2, eps, max_norm, norm_out, slot):
+        self.launches += 3
+        _chk(self.lib.dv3_adam_clip(p.numel(), _p(p), _p(g), _p(m), _p(v), _p(step), lr, beta1, beta2, eps, max_norm, _p(norm_out), slot,
+                                    self.scratch.data_ptr(), self.scratch.numel() * 4, self._s()), "dv3_adam_clip")
+
+    def ema(self, target, src, tau):
+        self.launches += 1
+        _chk(self.lib.dv3_ema(target.numel(), _p(target), _p(src), tau, self._s()), "dv3_ema")
+
+    # ---------------------------------------------------------------- scan plumbing
+    def scan_prep(self, first, h_prev, z_prev, zreset, h_in, z_in):
+        phi, B, D, ldhi = _mat(h_in)
+        pzi, _, S, ldzi = _mat(z_in)
+        php, ldhp = (None, 0) if h_prev is None else (_mat(h_prev)[0], _mat(h_prev)[3])
+        pzp, ldzp = (None, 0) if z_prev is None else (_mat(z_prev)[0], _mat(z_prev)[3])
+        self.launches += 1
+        _chk(self.lib.dv3_scan_prep(B, D, S, _p(first), php, ldhp, pzp, ldzp, _p(zreset), phi, ldhi, pzi, ldzi, self._s()), "dv3_scan_prep")
+
+    def scan_carry(self, first, dz_prev, dh_a, dh_b, dz_dst, dh_dst):
+        pz, B, S, ldz = _mat(dz_prev)
+        pa, _, D, lda = _mat(dh_a)
+        pb, _, _, ldb = _mat(dh_b)
+        pzd, _, _, ldzd = _mat(dz_dst)
+        phd, _, _, ldhd = _mat(dh_dst)
+        self.launches += 1
+        _chk(self.lib.dv3_scan_carry(B, D, S, _p(first), pz, ldz, pa, lda, pb, ldb, pzd, ldzd, phd, ldhd, self._s()), "dv3_scan_carry")
+
+    def mask_shift_actions(self, actions, first, out):
+        T, B, A = actions.shape
+        assert actions.is_contiguous() and first.is_contiguous() and out.stride(2) == 1 and out.stride(0) == B * out.stride(1)
+        self.launches += 1
+        _chk(self.lib.dv3_mask_shift_actions(T, B, A, _p(actions), _p(first), out.data_ptr(), out.stride(1), self._s()),
+             "dv3_mask_shift_actions")
+
+    def uniform_fill(self, out, seed, counter):
+        self.launches += 2
+        _chk(self.lib.dv3_uniform_fill(out.numel(), _p(out), int(seed) & (2 ** 64 - 1), _p(counter), self._s()), "dv3_uniform_fill")
+
+    def fill(self, t, v):
+        self.launches += 1
+        _chk(self.lib.dv3_fill(t.numel(), _p(t), float(v), self._s()), "dv3_fill")

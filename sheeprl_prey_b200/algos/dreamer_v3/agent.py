@@ -1,0 +1,290 @@
+"""Module tree of the DreamerV3 agent with the reference's names and `build_models` signature
+(sheeprl/algos/dreamer_v3/agent.py:831-1068), so that state_dict keys, checkpoints and the caller-side code that
+reaches into the modules (PlayerDV3 agent.py:494-501, target-critic EMA dreamer_v3.py:713-716) keep working.
+
+The modules are parameter containers: every nn.Parameter is a view into one of three flat fp32 arenas
+(world model / actor / critic, plus a fourth for the target critic) that the CUDA step engine reads and updates
+in place.  `train()` never calls these modules' forward; their plain-torch `forward` exists only for the
+caller-side player / evaluation code, which is outside the accelerated path.
+"""
+from __future__ import annotations
+
+import math
+from collections import OrderedDict
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn as nn
+from torch import Tensor
+
+from ...engine import Arena, DV3Engine
+
+
+# ----------------------------------------------------------------------------- init (algos/dreamer_v3/utils.py:116-159)
+def init_weights(m: nn.Module) -> None:
+    if isinstance(m, nn.Linear):
+        denom = (m.in_features + m.out_features) / 2.0
+        std = math.sqrt(1.0 / denom) / 0.87962566103423978
+        nn.init.trunc_normal_(m.weight.data, mean=0.0, std=std, a=-2.0 * std, b=2.0 * std)
+        if m.bias is not None:
+            m.bias.data.fill_(0.0)
+    elif isinstance(m, nn.LayerNorm):
+        m.weight.data.fill_(1.0)
+        m.bias.data.fill_(0.0)
+
+
+def uniform_init_weights(given_scale: float):
+    def f(m: nn.Module) -> None:
+        if isinstance(m, nn.Linear):
+            denom = (m.in_features + m.out_features) / 2.0
+            limit = math.sqrt(3 * given_scale / denom)
+            nn.init.uniform_(m.weight.data, a=-limit, b=limit)
+            if m.bias is not None:
+                m.bias.data.fill_(0.0)
+        elif isinstance(m, nn.LayerNorm):
+            m.weight.data.fill_(1.0)
+            m.bias.data.fill_(0.0)
+
+    return f
+
+
+# ----------------------------------------------------------------------------- blocks (sheeprl/models/models.py)
+class MLP(nn.Module):
+    """hidden x [Linear, LayerNorm, SiLU] (+ final Linear): models.py:15-118 with the DV3 arguments."""
+
+    def __init__(self, input_dims: int, output_dim: Optional[int], hidden_sizes: Sequence[int], bias: bool, eps: float):
+        super().__init__()
+        dims = [input_dims] + list(hidden_sizes)
+        layers: List[nn.Module] = []
+        for i, o in zip(dims[:-1], dims[1:]):
+            layers += [nn.Linear(i, o, bias=bias), nn.LayerNorm(o, eps=eps), nn.SiLU()]
+        if output_dim is not None:
+            layers.append(nn.Linear(dims[-1], output_dim))
+        self._model = nn.Sequential(*layers)
+        self._output_dim = output_dim or dims[-1]
+
+    @property
+    def model(self) -> nn.Module:
+        return self._model
+
+    @property
+    def output_dim(self) -> int:
+        return self._output_dim
+
+    def forward(self, x: Tensor) -> Tensor:
+        return self._model(x)
+
+
+class LayerNormGRUCell(nn.Module):
+    """models.py:330-402"""
+
+    def __init__(self, input_size: int, hidden_size: int):
+        super().__init__()
+        self.input_size, self.hidden_size = input_size, hidden_size
+        self.linear = nn.Linear(input_size + hidden_size, 3 * hidden_size, bias=False)
+        self.layer_norm = nn.LayerNorm(3 * hidden_size)
+
+    def forward(self, input: Tensor, hx: Tensor) -> Tensor:
+        three_d = input.dim() == 3
+        if three_d:
+            input, hx = input.squeeze(0), hx.squeeze(0)
+        x = self.layer_norm(self.linear(torch.cat((hx, input), -1)))
+        r, c, u = torch.chunk(x, 3, -1)
+        r = torch.sigmoid(r)
+        c = torch.tanh(r * c)
+        u = torch.sigmoid(u - 1)
+        hx = u * c + (1 - u) * hx
+        return hx.unsqueeze(0) if three_d else hx
+
+
+class MLPEncoder(nn.Module):
+    """agent.py:83-133"""
+
+    def __init__(self, keys: Sequence[str], input_dims: Sequence[int], mlp_layers: int, dense_units: int):
+        super().__init__()
+        self.keys = list(keys)
+        self.input_dim = sum(input_dims)
+        self.model = MLP(self.input_dim, None, [dense_units] * mlp_layers, bias=False, eps=1e-3)
+        self.output_dim = dense_units
+
+    def forward(self, obs: Dict[str, Tensor]) -> Tensor:
+        x = torch.cat([torch.sign(obs[k]) * torch.log(1 + torch.abs(obs[k])) for k in self.keys], -1)
+        return self.model(x)
+
+
+class MLPDecoder(nn.Module):
+    """agent.py:209-257"""
+
+    def __init__(self, keys: Sequence[str], output_dims: Sequence[int], latent_state_size: int, mlp_layers: int, dense_units: int):
+        super().__init__()
+        self.keys, self.output_dims = list(keys), list(output_dims)
+        self.model = MLP(latent_state_size, None, [dense_units] * mlp_layers, bias=False, eps=1e-3)
+        self.heads = nn.ModuleList([nn.Linear(dense_units, d) for d in self.output_dims])
+
+    def forward(self, latent: Tensor) -> Dict[str, Tensor]:
+        x = self.model(latent)
+        return {k: h(x) for k, h in zip(self.keys, self.heads)}
+
+
+class MultiEncoder(nn.Module):
+    """models.py:405-460 (vector branch)"""
+
+    def __init__(self, cnn_encoder, mlp_encoder):
+        super().__init__()
+        self.cnn_encoder, self.mlp_encoder = cnn_encoder, mlp_encoder
+        self.cnn_output_dim = 0
+        self.mlp_output_dim = mlp_encoder.output_dim if mlp_encoder is not None else 0
+        self.output_dim = self.cnn_output_dim + self.mlp_output_dim
+
+    def forward(self, obs):
+        return self.mlp_encoder(obs)
+
+
+class MultiDecoder(nn.Module):
+    """models.py:463-489 (vector branch)"""
+
+    def __init__(self, cnn_decoder, mlp_decoder):
+        super().__init__()
+        self.cnn_decoder, self.mlp_decoder = cnn_decoder, mlp_decoder
+
+    def forward(self, x):
+        return self.mlp_decoder(x)
+
+
+class RecurrentModel(nn.Module):
+    """agent.py:260-309"""
+
+    def __init__(self, input_size: int, recurrent_state_size: int, dense_units: int):
+        super().__init__()
+        self.mlp = MLP(input_size, None, [dense_units], bias=False, eps=1e-3)
+        self.rnn = LayerNormGRUCell(dense_units, recurrent_state_size)
+
+    def forward(self, input: Tensor, recurrent_state: Tensor) -> Tensor:
+        return self.rnn(self.mlp(input), recurrent_state)
+
+
+class RSSM(nn.Module):
+    """agent.py:312-455 (container; the training-time scan runs in the CUDA engine)"""
+
+    def __init__(self, recurrent_model, representation_model, transition_model, distribution_cfg, discrete=32, unimix=0.01):
+        super().__init__()
+        self.recurrent_model, self.representation_model, self.transition_model = recurrent_model, representation_model, transition_model
+        self.discrete, self.unimix, self.distribution_cfg = discrete, unimix, distribution_cfg
+
+
+class WorldModel(nn.Module):
+    """sheeprl/algos/dreamer_v2/agent.py:630-655"""
+
+    def __init__(self, encoder, rssm, observation_model, reward_model, continue_model):
+        super().__init__()
+        self.encoder, self.rssm, self.observation_model = encoder, rssm, observation_model
+        self.reward_model, self.continue_model = reward_model, continue_model
+
+
+class Actor(nn.Module):
+    """agent.py:602-747 (discrete heads)"""
+
+    def __init__(self, latent_state_size: int, actions_dim: Sequence[int], is_continuous: bool, dense_units: int, mlp_layers: int,
+                 unimix: float = 0.01):
+        super().__init__()
+        if is_continuous:
+            raise NotImplementedError("continuous actions are SURVEY.md section 8(f) item 1 (not built yet)")
+        self.model = MLP(latent_state_size, None, [dense_units] * mlp_layers, bias=False, eps=1e-3)
+        self.mlp_heads = nn.ModuleList([nn.Linear(dense_units, a) for a in actions_dim])
+        self.actions_dim, self.is_continuous, self._unimix = list(actions_dim), is_continuous, unimix
+
+
+def _arena_from(module: nn.Module, device) -> Arena:
+    shapes = OrderedDict((k, tuple(p.shape)) for k, p in module.named_parameters())
+    arena = Arena(shapes, device)
+    for k, p in module.named_parameters():
+        arena.p[k].copy_(p.data)
+        p.data = arena.p[k]          # the nn.Parameter now aliases the arena
+    return arena
+
+
+def build_models(
+    fabric: Any,
+    actions_dim: Sequence[int],
+    is_continuous: bool,
+    cfg: Dict[str, Any],
+    obs_space: Dict[str, Any],
+    world_model_state: Optional[Dict[str, Tensor]] = None,
+    actor_state: Optional[Dict[str, Tensor]] = None,
+    critic_state: Optional[Dict[str, Tensor]] = None,
+    target_critic_state: Optional[Dict[str, Tensor]] = None,
+    ops=None,
+) -> Tuple[WorldModel, nn.Module, nn.Module, nn.Module]:
+    """Same positional contract as the reference's build_models.  `ops` is a test seam (the CPU statement of the
+    kernels for host-logic tests); by default the CUDA library is required."""
+    w, a = cfg.algo.world_model, cfg.algo
+    device = torch.device(fabric.device)
+    if len(cfg.cnn_keys.encoder) > 0:
+        raise NotImplementedError("pixel observations (cnn_keys) are not built yet; see DESIGN.md scope table")
+    keys = list(cfg.mlp_keys.encoder)
+    obs_dims = {k: int(obs_space[k].shape[0]) for k in keys}
+    S = w.stochastic_size * w.discrete_size
+    D = w.recurrent_model.recurrent_state_size
+    lat = S + D
+    enc = MultiEncoder(None, MLPEncoder(keys, [obs_dims[k] for k in keys], w.encoder.mlp_layers, w.encoder.dense_units))
+    rec = RecurrentModel(int(sum(actions_dim) + S), D, w.recurrent_model.dense_units)
+    rep = MLP(D + enc.output_dim, S, [w.representation_model.hidden_size], bias=True, eps=1e-5)
+    tra = MLP(D, S, [w.transition_model.hidden_size], bias=True, eps=1e-5)
+    rssm = RSSM(rec.apply(init_weights), rep.apply(init_weights), tra.apply(init_weights), cfg.distribution, w.discrete_size, a.unimix)
+    dec = MultiDecoder(None, MLPDecoder(list(cfg.mlp_keys.decoder), [obs_dims[k] for k in cfg.mlp_keys.decoder], lat,
+                                        w.observation_model.mlp_layers, w.observation_model.dense_units))
+    rew = MLP(lat, w.reward_model.bins, [w.reward_model.dense_units] * w.reward_model.mlp_layers, bias=True, eps=1e-5)
+    con = MLP(lat, 1, [w.discount_model.dense_units] * w.discount_model.mlp_layers, bias=True, eps=1e-5)
+    world_model = WorldModel(enc.apply(init_weights), rssm, dec.apply(init_weights), rew.apply(init_weights), con.apply(init_weights))
+    actor = Actor(lat, actions_dim, is_continuous, a.actor.dense_units, a.actor.mlp_layers, a.unimix)
+    critic = MLP(lat, a.critic.bins, [a.critic.dense_units] * a.critic.mlp_layers, bias=True, eps=1e-5)
+    actor.apply(init_weights)
+    critic.apply(init_weights)
+    if a.hafner_initialization:   # agent.py:1033-1043
+        actor.mlp_heads.apply(uniform_init_weights(1.0))
+        critic.model[-1].apply(uniform_init_weights(0.0))
+        tra.model[-1].apply(uniform_init_weights(1.0))
+        rep.model[-1].apply(uniform_init_weights(1.0))
+        rew.model[-1].apply(uniform_init_weights(0.0))
+        con.model[-1].apply(uniform_init_weights(1.0))
+        dec.mlp_decoder.heads.apply(uniform_init_weights(1.0))
+    if world_model_state:
+        world_model.load_state_dict(world_model_state)
+    if actor_state:
+        actor.load_state_dict(actor_state)
+    if critic_state:
+        critic.load_state_dict(critic_state)
+    import copy
+
+    target_critic = copy.deepcopy(critic)
+    if target_critic_state:
+        target_critic.load_state_dict(target_critic_state)
+
+    # move everything into flat arenas on the device; parameters become views
+    for m in (world_model, actor, critic, target_critic):
+        m.to(device)
+    arenas = [_arena_from(m, device) for m in (world_model, actor, critic, target_critic)]
+    if ops is None:
+        from ..._lib import CudaOps
+
+        ops = CudaOps(device)
+    dist = None
+    if getattr(fabric, "world_size", 1) > 1:
+        from ...parallel import TorchDist
+
+        dist = TorchDist(fabric.world_size)
+    engine = DV3Engine(cfg, obs_dims, list(actions_dim), *arenas, ops, device, dist=dist, seed=int(getattr(fabric, "global_rank", 0)))
+    object.__setattr__(world_model, "_dv3_engine", engine)   # not a submodule / not in state_dict
+
+    # Fabric wrapping, same call sites as agent.py:1054-1063 (DDP hooks are inert: the engine all-reduces its own grads)
+    wm = world_model
+    wm.encoder = fabric.setup_module(wm.encoder)
+    wm.observation_model = fabric.setup_module(wm.observation_model)
+    wm.reward_model = fabric.setup_module(wm.reward_model)
+    wm.rssm.recurrent_model = fabric.setup_module(wm.rssm.recurrent_model)
+    wm.rssm.representation_model = fabric.setup_module(wm.rssm.representation_model)
+    wm.rssm.transition_model = fabric.setup_module(wm.rssm.transition_model)
+    wm.continue_model = fabric.setup_module(wm.continue_model)
+    actor = fabric.setup_module(actor)
+    critic = fabric.setup_module(critic)
+    return world_model, actor, critic, target_critic

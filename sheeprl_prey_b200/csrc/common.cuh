@@ -1,0 +1,69 @@
+// Shared device helpers for libdv3b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+#define DV3_OK 0
+#define DV3_ERR_ARG (-1)
+#define DV3_ERR_UNSUPPORTED (-2)
+#define DV3_ERR_SCRATCH (-3)
+
+#define DV3_LAUNCH_CHECK()                                    \
+  do {                                                        \
+    cudaError_t e__ = cudaGetLastError();                     \
+    if (e__ != cudaSuccess) return (int)e__;                  \
+  } while (0)
+
+static __device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+static __device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+static __device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Block-wide sum of one float; `red` is >= 32 floats of shared memory. All threads get the result.
+static __device__ __forceinline__ float block_sum(float v, float* red) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();  // protect `red` from a previous use
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  float r = (lane < nw) ? red[lane] : 0.f;
+  r = warp_sum(r);
+  return r;
+}
+// Two sums at once.
+static __device__ __forceinline__ void block_sum2(float& a, float& b, float* red) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+  a = warp_sum(a);
+  b = warp_sum(b);
+  __syncthreads();
+  if (lane == 0) { red[w] = a; red[32 + w] = b; }
+  __syncthreads();
+  float ra = (lane < nw) ? red[lane] : 0.f;
+  float rb = (lane < nw) ? red[32 + lane] : 0.f;
+  a = warp_sum(ra);
+  b = warp_sum(rb);
+}
+
+static __device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+static __device__ __forceinline__ float siluf_(float x) { return x * sigmoidf_(x); }
+static __device__ __forceinline__ float symlogf_(float x) {
+  float s = (x > 0.f) ? 1.f : ((x < 0.f) ? -1.f : 0.f);
+  return s * logf(1.f + fabsf(x));
+}
+static __device__ __forceinline__ float symexpf_(float x) {
+  float s = (x > 0.f) ? 1.f : ((x < 0.f) ? -1.f : 0.f);
+  return s * (expf(fabsf(x)) - 1.f);
+}
+#define DV3_EPS32 1.1920928955078125e-07f

@@ -1,0 +1,191 @@
+// fp32 CUDA-core contractions for the strict-parity ("fp32") mode of libdv3b200.
+//   * dv3_gemm_f32 tiled kernel: 128x128x16 tiles, 8x8 register micro-tile, register-prefetched global loads.
+//     Handles NT / NN / TN operand layouts with arbitrary leading dimensions and ragged edges.
+//   * skinny NT kernel (M <= 32): the per-step contractions of the RSSM observe scan, where the batch is the
+//     M dimension (B = 16) and the problem is streaming the weight matrix once.
+// Replaces, for the reference, every torch `addmm/mm` on the DreamerV3 train path
+// (sheeprl/models/models.py:115-118 MLP.forward, :389 LayerNormGRUCell linear, and their autograd backward).
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 16, TM = 8, TN_ = 8, NT_THREADS = 256;
+
+enum { MODE_NT = 0, MODE_NN = 1, MODE_TN = 2 };
+
+template <int MODE>
+__global__ void __launch_bounds__(NT_THREADS)
+gemm_tiled_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
+                  float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+  __shared__ float As[BK][BM + 4];
+  __shared__ float Bs[BK][BN + 4];
+  const int tid = threadIdx.x;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads
+
+  // element mappings for the global->shared staging (8 A + 8 B elements per thread per k-tile)
+  constexpr bool A_KCONTIG = (MODE != MODE_TN);  // A(m,k) contiguous in k for NT/NN
+  constexpr bool B_KCONTIG = (MODE == MODE_NT);  // B(k,n) contiguous in k for NT
+  float ra[8], rb[8];
+
+  auto load_tiles = [&](int k0) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int lin = tid + e * NT_THREADS;
+      int m, k;
+      if (A_KCONTIG) { m = lin / BK; k = lin % BK; } else { k = lin / BM; m = lin % BM; }
+      const int gm = m0 + m, gk = k0 + k;
+      float v = 0.f;
+      if (gm < M && gk < K) v = A_KCONTIG ? __ldg(A + (size_t)gm * lda + gk) : __ldg(A + (size_t)gk * lda + gm);
+      ra[e] = v;
+      int n, kb;
+      if (B_KCONTIG) { n = lin / BK; kb = lin % BK; } else { kb = lin / BN; n = lin % BN; }
+      const int gn = n0 + n, gkb = k0 + kb;
+      float w = 0.f;
+      if (gn < N && gkb < K) w = B_KCONTIG ? __ldg(B + (size_t)gn * ldb + gkb) : __ldg(B + (size_t)gkb * ldb + gn);
+      rb[e] = w;
+    }
+  };
+  auto store_tiles = [&]() {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int lin = tid + e * NT_THREADS;
+      int m, k;
+      if (A_KCONTIG) { m = lin / BK; k = lin % BK; } else { k = lin / BM; m = lin % BM; }
+      As[k][m] = ra[e];
+      int n, kb;
+      if (B_KCONTIG) { n = lin / BK; kb = lin % BK; } else { kb = lin / BN; n = lin % BN; }
+      Bs[kb][n] = rb[e];
+    }
+  };
+
+  float acc[TM][TN_];
+#pragma unroll
+  for (int i = 0; i < TM; ++i)
+#pragma unroll
+    for (int j = 0; j < TN_; ++j) acc[i][j] = 0.f;
+
+  load_tiles(0);
+  for (int k0 = 0; k0 < K; k0 += BK) {
+    store_tiles();
+    __syncthreads();
+    if (k0 + BK < K) load_tiles(k0 + BK);
+#pragma unroll
+    for (int k = 0; k < BK; ++k) {
+      float a[TM], b[TN_];
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[k][ty * 4 + 64]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[k][tx * 4 + 64]);
+      a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+      b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+#pragma unroll
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN_; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+#pragma unroll
+  for (int i = 0; i < TM; ++i) {
+    const int gm = m0 + ty * 4 + (i & 3) + (i >> 2) * 64;
+    if (gm >= M) continue;
+#pragma unroll
+    for (int j = 0; j < TN_; ++j) {
+      const int gn = n0 + tx * 4 + (j & 3) + (j >> 2) * 64;
+      if (gn >= N) continue;
+      float v = acc[i][j];
+      if (bias) v += __ldg(bias + gn);
+      float* c = C + (size_t)gm * ldc + gn;
+      if (accumulate) v += *c;
+      *c = v;
+    }
+  }
+}
+
+// ---- skinny NT: C[M<=32, N] = A[M,K] * B[N,K]^T ------------------------------------------------------
+constexpr int SK_WARPS = 8, SK_NPW = 2, SK_KT = 256;
+
+template <int MT>
+__global__ void __launch_bounds__(SK_WARPS * 32)
+gemm_skinny_nt_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
+                      float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+  __shared__ float As[MT][SK_KT];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nbase = (blockIdx.x * SK_WARPS + warp) * SK_NPW;
+  float acc[SK_NPW][MT];
+#pragma unroll
+  for (int c = 0; c < SK_NPW; ++c)
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[c][m] = 0.f;
+
+  for (int k0 = 0; k0 < K; k0 += SK_KT) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < MT * SK_KT; i += blockDim.x) {
+      const int m = i / SK_KT, kk = i % SK_KT;
+      float v = 0.f;
+      if (m < M && k0 + kk < K) v = A[(size_t)m * lda + k0 + kk];
+      As[m][kk] = v;
+    }
+    __syncthreads();
+    const int kmax = min(SK_KT, K - k0);
+    for (int kk = lane; kk < kmax; kk += 32) {
+      float bv[SK_NPW];
+#pragma unroll
+      for (int c = 0; c < SK_NPW; ++c) {
+        const int n = nbase + c;
+        bv[c] = (n < N) ? __ldg(B + (size_t)n * ldb + k0 + kk) : 0.f;
+      }
+#pragma unroll
+      for (int m = 0; m < MT; ++m) {
+        const float a = As[m][kk];
+#pragma unroll
+        for (int c = 0; c < SK_NPW; ++c) acc[c][m] = fmaf(a, bv[c], acc[c][m]);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < SK_NPW; ++c) {
+    const int n = nbase + c;
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      float v = warp_sum(acc[c][m]);
+      if (lane == 0 && n < N && m < M) {
+        if (bias) v += bias[n];
+        float* cp = C + (size_t)m * ldc + n;
+        if (accumulate) v += *cp;
+        *cp = v;
+      }
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C,
+                            int ldc, const float* bias, int accumulate, void* stream_) {
+  if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return DV3_ERR_ARG;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (mode == MODE_NT && M <= 32) {
+    dim3 grid((N + SK_WARPS * SK_NPW - 1) / (SK_WARPS * SK_NPW));
+    if (M <= 8)
+      gemm_skinny_nt_kernel<8><<<grid, SK_WARPS * 32, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+    else if (M <= 16)
+      gemm_skinny_nt_kernel<16><<<grid, SK_WARPS * 32, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+    else
+      gemm_skinny_nt_kernel<32><<<grid, SK_WARPS * 32, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+    DV3_LAUNCH_CHECK();
+    return DV3_OK;
+  }
+  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
+  if (grid.y > 65535) return DV3_ERR_UNSUPPORTED;
+  switch (mode) {
+    case MODE_NT: gemm_tiled_kernel<MODE_NT><<<grid, NT_THREADS, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate); break;
+    case MODE_NN: gemm_tiled_kernel<MODE_NN><<<grid, NT_THREADS, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate); break;
+    case MODE_TN: gemm_tiled_kernel<MODE_TN><<<grid, NT_THREADS, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate); break;
+    default: return DV3_ERR_ARG;
+  }
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}

@@ -1,0 +1,626 @@
+// Categorical / loss kernels of the DreamerV3 step (forward value and hand-written gradient in one pass).
+//   unimix + straight-through one-hot sampling : sheeprl/algos/dreamer_v3/agent.py:390-402, :741-747;
+//                                                sheeprl/utils/distribution.py:355-360, :390-393
+//   KL balance with free nats                  : sheeprl/algos/dreamer_v3/loss.py:69-98 (+ torch _kl_categorical_categorical)
+//   two-hot symlog log-prob / mean             : sheeprl/utils/distribution.py:245-270
+//   symlog MSE                                 : sheeprl/utils/distribution.py:177-193
+//   Bernoulli continue loss                    : sheeprl/algos/dreamer_v3/dreamer_v3.py:150-155, loss.py:100-101
+//   lambda-returns + discount                  : sheeprl/algos/dreamer_v3/utils.py:44-55, dreamer_v3.py:262-280
+//   Moments (percentile EMA)                   : sheeprl/algos/dreamer_v3/utils.py:34-41
+//   REINFORCE + entropy actor objective        : sheeprl/algos/dreamer_v3/dreamer_v3.py:292-317
+// One warp owns one categorical group / one row; reductions are warp shuffles.
+#include "common.cuh"
+
+namespace {
+
+constexpr int KR = 8;            // classes per lane kept in registers -> K <= 256
+constexpr int WARPS_PER_BLOCK = 4;
+
+template <int KRT>
+struct Group {  // per-lane slice of one K-class group (K <= 32*KRT)
+  float v[KRT];
+};
+
+template <int KRT, typename F>
+static __device__ __forceinline__ void for_k(int K, int lane, F f) {
+#pragma unroll
+  for (int j = 0; j < KRT; ++j) {
+    const int k = lane + 32 * j;
+    if (k < K) f(j, k);
+  }
+}
+template <int KRT>
+static __device__ __forceinline__ float group_max(const Group<KRT>& g, int K, int lane) {
+  float m = -INFINITY;
+  for_k<KRT>(K, lane, [&](int j, int) { m = fmaxf(m, g.v[j]); });
+  return warp_max(m);
+}
+template <int KRT>
+static __device__ __forceinline__ float group_sum(const Group<KRT>& g, int K, int lane) {
+  float s = 0.f;
+  for_k<KRT>(K, lane, [&](int j, int) { s += g.v[j]; });
+  return warp_sum(s);
+}
+// ps = softmax(raw)
+template <int KRT>
+static __device__ __forceinline__ void softmax_group(const Group<KRT>& raw, Group<KRT>& ps, int K, int lane) {
+  const float m = group_max(raw, K, lane);
+  for_k<KRT>(K, lane, [&](int j, int) { ps.v[j] = expf(raw.v[j] - m); });
+  const float s = group_sum(ps, K, lane);
+  for_k<KRT>(K, lane, [&](int j, int) { ps.v[j] = ps.v[j] / s; });
+}
+// unimix: pm = (1-mix) ps + mix/K ; lu = log(clamp(pm, eps, 1-eps)); inside = clamp inactive
+template <int KRT>
+static __device__ __forceinline__ void unimix_group(const Group<KRT>& ps, Group<KRT>& pm, Group<KRT>& lu, float mix, int K, int lane) {
+  for_k<KRT>(K, lane, [&](int j, int) {
+    const float p = (1.f - mix) * ps.v[j] + mix / (float)K;
+    pm.v[j] = p;
+    lu.v[j] = logf(fminf(fmaxf(p, DV3_EPS32), 1.f - DV3_EPS32));
+  });
+}
+// ln = l - logsumexp(l) ; p = softmax(ln)   (torch Categorical(logits=l))
+template <int KRT>
+static __device__ __forceinline__ void normalise_group(const Group<KRT>& l, Group<KRT>& ln, Group<KRT>& p, int K, int lane) {
+  const float m = group_max(l, K, lane);
+  Group<KRT> e;
+  for_k<KRT>(K, lane, [&](int j, int) { e.v[j] = expf(l.v[j] - m); });
+  const float lse = m + logf(group_sum(e, K, lane));
+  for_k<KRT>(K, lane, [&](int j, int) { ln.v[j] = l.v[j] - lse; });
+  const float m2 = group_max(ln, K, lane);
+  for_k<KRT>(K, lane, [&](int j, int) { p.v[j] = expf(ln.v[j] - m2); });
+  const float s2 = group_sum(p, K, lane);
+  for_k<KRT>(K, lane, [&](int j, int) { p.v[j] = p.v[j] / s2; });
+}
+template <int KRT>
+static __device__ __forceinline__ void load_group(Group<KRT>& g, const float* p, int K, int lane) {
+  for_k<KRT>(K, lane, [&](int j, int k) { g.v[j] = p[k]; });
+}
+
+// ---------------------------------------------------------------- unimix forward
+template <int KRT>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+unimix_fwd_kernel(int R, int groups, int K, float mix, const float* __restrict__ raw, int ldr, float* __restrict__ out, int ldo) {
+  const int lane = threadIdx.x & 31;
+  const int gid = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (gid >= R * groups) return;
+  const int row = gid / groups, g = gid % groups;
+  Group<KRT> r, ps, pm, lu;
+  load_group(r, raw + (size_t)row * ldr + g * K, K, lane);
+  softmax_group(r, ps, K, lane);
+  if (mix > 0.f) unimix_group(ps, pm, lu, mix, K, lane);
+  else lu = r;
+  float* o = out + (size_t)row * ldo + g * K;
+  for_k<KRT>(K, lane, [&](int j, int k) { o[k] = lu.v[j]; });
+}
+
+// ---------------------------------------------------------------- sampling (inverse CDF on injected uniforms)
+template <int KRT>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+sample_onehot_kernel(int R, int groups, int K, const float* __restrict__ logits, int ldl, const float* __restrict__ u, int ldu,
+                     const int* __restrict__ forced, int ldf, int mode, int* __restrict__ idx, int ldi,
+                     float* __restrict__ onehot, int ldo) {
+  __shared__ float sp[WARPS_PER_BLOCK][KR * 32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int gid = blockIdx.x * WARPS_PER_BLOCK + w;
+  if (gid >= R * groups) return;
+  const int row = gid / groups, g = gid % groups;
+  int choice;
+  if (forced) {
+    choice = forced[(size_t)row * ldf + g];
+  } else {
+    Group<KRT> l, ln, p;
+    load_group(l, logits + (size_t)row * ldl + g * K, K, lane);
+    normalise_group(l, ln, p, K, lane);
+    for_k<KRT>(K, lane, [&](int j, int k) { sp[w][k] = p.v[j]; });
+    __syncwarp();
+    choice = 0;
+    if (lane == 0) {
+      if (mode) {  // argmax, first maximal index
+        float best = sp[w][0];
+        for (int k = 1; k < K; ++k) if (sp[w][k] > best) { best = sp[w][k]; choice = k; }
+      } else {     // idx = #{k : c_k <= u}, c = sequential fp32 cumsum
+        const float uu = u[(size_t)row * ldu + g];
+        float c = 0.f;
+        for (int k = 0; k < K; ++k) { c += sp[w][k]; choice += (c <= uu) ? 1 : 0; }
+        if (choice > K - 1) choice = K - 1;
+      }
+    }
+    choice = __shfl_sync(0xffffffffu, choice, 0);
+  }
+  if (lane == 0) idx[(size_t)row * ldi + g] = choice;
+  float* o = onehot + (size_t)row * ldo + g * K;
+  for_k<KRT>(K, lane, [&](int, int k) { o[k] = (k == choice) ? 1.f : 0.f; });
+}
+
+// ---------------------------------------------------------------- unimix backward (+ straight-through)
+template <int KRT>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+unimix_bwd_kernel(int R, int groups, int K, float mix, const float* __restrict__ raw, int ldr,
+                  const float* __restrict__ dlogits, int lddl, const float* __restrict__ dz, int lddz,
+                  float* __restrict__ draw, int lddr) {
+  const int lane = threadIdx.x & 31;
+  const int gid = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (gid >= R * groups) return;
+  const int row = gid / groups, g = gid % groups;
+  Group<KRT> r, ps, pm, lu, gl;
+  load_group(r, raw + (size_t)row * ldr + g * K, K, lane);
+  softmax_group(r, ps, K, lane);
+  if (mix > 0.f) unimix_group(ps, pm, lu, mix, K, lane);
+  else { lu = r; pm = ps; }
+  for_k<KRT>(K, lane, [&](int j, int k) { gl.v[j] = dlogits ? dlogits[(size_t)row * lddl + g * K + k] : 0.f; });
+  if (dz) {
+    Group<KRT> ln, p, d;
+    normalise_group(lu, ln, p, K, lane);
+    load_group(d, dz + (size_t)row * lddz + g * K, K, lane);
+    float dot = 0.f;
+    for_k<KRT>(K, lane, [&](int j, int) { dot = fmaf(p.v[j], d.v[j], dot); });
+    dot = warp_sum(dot);
+    for_k<KRT>(K, lane, [&](int j, int) { gl.v[j] += p.v[j] * (d.v[j] - dot); });
+  }
+  float* o = draw + (size_t)row * lddr + g * K;
+  if (mix > 0.f) {
+    Group<KRT> gps;
+    float dot = 0.f;
+    for_k<KRT>(K, lane, [&](int j, int) {
+      const bool inside = (pm.v[j] >= DV3_EPS32) && (pm.v[j] <= 1.f - DV3_EPS32);
+      gps.v[j] = inside ? (1.f - mix) * (gl.v[j] / pm.v[j]) : 0.f;
+      dot = fmaf(ps.v[j], gps.v[j], dot);
+    });
+    dot = warp_sum(dot);
+    for_k<KRT>(K, lane, [&](int j, int k) { o[k] = ps.v[j] * (gps.v[j] - dot); });
+  } else {
+    for_k<KRT>(K, lane, [&](int j, int k) { o[k] = gl.v[j]; });
+  }
+}
+
+// ---------------------------------------------------------------- KL balance (block = one row, warp = one group)
+template <int KRT>
+__global__ void __launch_bounds__(1024)
+kl_balance_kernel(int groups, int K, const float* __restrict__ post, const float* __restrict__ prior, float free_nats,
+                  float w_dyn, float w_rep, float scale, float* __restrict__ rows_out, float* __restrict__ dpost,
+                  float* __restrict__ dprior) {
+  __shared__ float s_kl[32], s_ep[32], s_eq[32];
+  const int lane = threadIdx.x & 31, g = threadIdx.x >> 5, row = blockIdx.x;
+  const size_t off = ((size_t)row * groups + g) * K;
+  Group<KRT> lp, lq, p, q, lpn, lqn;
+  load_group(lp, post + off, K, lane);
+  load_group(lq, prior + off, K, lane);
+  normalise_group(lp, lpn, p, K, lane);
+  normalise_group(lq, lqn, q, K, lane);
+  float t = 0.f, ep = 0.f, eq = 0.f;
+  for_k<KRT>(K, lane, [&](int j, int) {
+    float tt = p.v[j] * (lpn.v[j] - lqn.v[j]);
+    if (q.v[j] == 0.f) tt = INFINITY;
+    if (p.v[j] == 0.f) tt = 0.f;
+    t += tt;
+    ep -= fmaxf(lpn.v[j], -3.4028234663852886e38f) * p.v[j];
+    eq -= fmaxf(lqn.v[j], -3.4028234663852886e38f) * q.v[j];
+  });
+  const float klg = warp_sum(t);
+  ep = warp_sum(ep);
+  eq = warp_sum(eq);
+  if (lane == 0) { s_kl[g] = klg; s_ep[g] = ep; s_eq[g] = eq; }
+  __syncthreads();
+  float kl = 0.f, sep = 0.f, seq = 0.f;
+  for (int i = 0; i < groups; ++i) { kl += s_kl[i]; sep += s_ep[i]; seq += s_eq[i]; }  // fixed order, every thread
+  if (threadIdx.x == 0) {
+    rows_out[(size_t)row * 4 + 0] = kl;
+    rows_out[(size_t)row * 4 + 1] = (w_dyn + w_rep) * fmaxf(kl, free_nats);
+    rows_out[(size_t)row * 4 + 2] = sep;
+    rows_out[(size_t)row * 4 + 3] = seq;
+  }
+  const float active = (kl > free_nats) ? 1.f : ((kl == free_nats) ? 0.5f : 0.f);
+  for_k<KRT>(K, lane, [&](int j, int k) {
+    dprior[off + k] = scale * w_dyn * active * (q.v[j] - p.v[j]);
+    dpost[off + k] = scale * w_rep * active * p.v[j] * ((lpn.v[j] - lqn.v[j]) - klg);
+  });
+}
+
+// ---------------------------------------------------------------- two-hot
+static __device__ __forceinline__ float bin_value(int i, int K) {
+  // torch.linspace(-20, 20, K): start + i*step below the midpoint, end - (K-1-i)*step above it
+  const float step = 40.f / (float)(K - 1);
+  return (i < K / 2) ? (-20.f + step * (float)i) : (20.f - step * (float)(K - 1 - i));
+}
+// two-hot target of symlog(x): indices (below, above) and weights
+static __device__ __forceinline__ void twohot_target(float x, int K, int lane, int& below, int& above, float& wb, float& wa) {
+  const float y = symlogf_(x);
+  int le = 0, gt = 0;
+  for (int k = lane; k < K; k += 32) {
+    const float b = bin_value(k, K);
+    le += (b <= y) ? 1 : 0;
+    gt += (b > y) ? 1 : 0;
+  }
+  le = warp_sum_i(le);
+  gt = warp_sum_i(gt);
+  below = min(max(le - 1, 0), K - 1);
+  above = min(max(K - gt, 0), K - 1);
+  float db, da;
+  if (below == above) { db = 1.f; da = 1.f; }
+  else { db = fabsf(bin_value(below, K) - y); da = fabsf(bin_value(above, K) - y); }
+  const float tot = db + da;
+  wb = da / tot;
+  wa = db / tot;
+}
+
+template <int KRT>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+twohot_loss_kernel(int M, int K, const float* __restrict__ logits, int ldl, const float* __restrict__ x,
+                   const float* __restrict__ w, float scale, float* __restrict__ loss_rows, float* __restrict__ dlogits,
+                   int ldd, int accumulate) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (row >= M) return;
+  Group<KRT> l, e;
+  load_group(l, logits + (size_t)row * ldl, K, lane);
+  const float m = group_max(l, K, lane);
+  for_k<KRT>(K, lane, [&](int j, int) { e.v[j] = expf(l.v[j] - m); });
+  const float s = group_sum(e, K, lane);
+  const float lse = m + logf(s);
+  int below, above;
+  float wb, wa;
+  twohot_target(x[row], K, lane, below, above, wb, wa);
+  float part = 0.f;
+  for_k<KRT>(K, lane, [&](int j, int k) {
+    float tgt = 0.f;
+    if (k == below) tgt += wb;
+    if (k == above) tgt += wa;
+    part += tgt * (l.v[j] - lse);
+  });
+  const float nll = -warp_sum(part);
+  const float ww = w ? w[row] : 1.f;
+  if (lane == 0) loss_rows[row] = (accumulate ? loss_rows[row] : 0.f) + ww * nll;
+  float* d = dlogits + (size_t)row * ldd;
+  for_k<KRT>(K, lane, [&](int j, int k) {
+    float tgt = 0.f;
+    if (k == below) tgt += wb;
+    if (k == above) tgt += wa;
+    const float gval = scale * ww * (expf(l.v[j] - lse) * (wb + wa) - tgt);
+    d[k] = (accumulate ? d[k] : 0.f) + gval;
+  });
+}
+
+template <int KRT>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+twohot_mean_kernel(int M, int K, const float* __restrict__ logits, int ldl, float* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (row >= M) return;
+  Group<KRT> l, ps;
+  load_group(l, logits + (size_t)row * ldl, K, lane);
+  softmax_group(l, ps, K, lane);
+  float part = 0.f;
+  for_k<KRT>(K, lane, [&](int j, int k) { part = fmaf(ps.v[j], bin_value(k, K), part); });
+  const float v = warp_sum(part);
+  if (lane == 0) out[row] = symexpf_(v);
+}
+
+// ---------------------------------------------------------------- symlog-MSE / Bernoulli
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+symlog_mse_kernel(int M, int Dd, const float* __restrict__ mode, int ldm, const float* __restrict__ target, int ldt,
+                  float scale, float* __restrict__ loss_rows, float* __restrict__ dmode, int ldd) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (row >= M) return;
+  float s = 0.f;
+  for (int i = lane; i < Dd; i += 32) {
+    const float diff = mode[(size_t)row * ldm + i] - target[(size_t)row * ldt + i];
+    const float d = diff * diff;
+    const bool keep = d >= 1e-8f;
+    s += keep ? d : 0.f;
+    dmode[(size_t)row * ldd + i] = keep ? scale * 2.f * diff : 0.f;
+  }
+  s = warp_sum(s);
+  if (lane == 0) loss_rows[row] = s;
+}
+__global__ void bernoulli_loss_kernel(int M, const float* __restrict__ logit, const float* __restrict__ dones, float scale,
+                                      float* __restrict__ loss_rows, float* __restrict__ dlogit) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= M) return;
+  const float l = logit[i], t = 1.f - dones[i];
+  loss_rows[i] = fmaxf(l, 0.f) - l * t + log1pf(expf(-fabsf(l)));
+  dlogit[i] = scale * (sigmoidf_(l) - t);
+}
+
+// out[slot] (+)= scale * sum_m x[m*ldx + col]   (single block; deterministic order)
+__global__ void __launch_bounds__(1024)
+reduce_mean_kernel(int M, const float* __restrict__ x, int ldx, int col, float* __restrict__ out, int slot, float scale,
+                   int accumulate) {
+  __shared__ float red[64];
+  float s = 0.f;
+  for (int m = threadIdx.x; m < M; m += blockDim.x) s += x[(size_t)m * ldx + col];
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) out[slot] = (accumulate ? out[slot] : 0.f) + scale * s;
+}
+
+// ---------------------------------------------------------------- lambda-returns
+__global__ void lambda_returns_kernel(int H, int N, const float* __restrict__ values, const float* __restrict__ rewards,
+                                      const float* __restrict__ cont_logit, const float* __restrict__ dones, float gamma,
+                                      float lmbda, float* __restrict__ lam, float* __restrict__ discount) {
+  const int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  auto cont = [&](int t) -> float {
+    if (t == 0) return 1.f - dones[n];
+    const float p = sigmoidf_(cont_logit[(size_t)t * N + n]);
+    return (p == 0.5f) ? NAN : ((p > 0.5f) ? 1.f : 0.f);   // Bernoulli.mode
+  };
+  float nxt = values[(size_t)H * N + n];
+  for (int t = H - 1; t >= 0; --t) {  // output index t <-> imagined step t+1
+    const float cg = cont(t + 1) * gamma;
+    const float interm = rewards[(size_t)(t + 1) * N + n] + cg * values[(size_t)(t + 1) * N + n] * (1.f - lmbda);
+    nxt = interm + cg * lmbda * nxt;
+    lam[(size_t)t * N + n] = nxt;
+  }
+  float prod = 1.f;
+  for (int t = 0; t <= H; ++t) {
+    prod *= cont(t) * gamma;
+    discount[(size_t)t * N + n] = prod / gamma;
+  }
+}
+
+// ---------------------------------------------------------------- Moments: exact quantiles by radix select (one block)
+static __device__ __forceinline__ unsigned f2key(float f) {
+  const unsigned u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+static __device__ __forceinline__ float key2f(unsigned k) {
+  const unsigned u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+  return __uint_as_float(u);
+}
+// k-th smallest (0-based) of x[0..n): MSB-first 8-bit radix select; all threads of the block participate.
+static __device__ float select_kth(const float* __restrict__ x, int n, int kth, unsigned* hist, unsigned* bcast) {
+  unsigned prefix = 0, mask = 0;
+  int rank = kth;
+  for (int shift = 24; shift >= 0; shift -= 8) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const unsigned key = f2key(x[i]);
+      if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned acc = 0;
+      int b = 0;
+      for (; b < 256; ++b) {
+        if (acc + hist[b] > (unsigned)rank) break;
+        acc += hist[b];
+      }
+      bcast[0] = (unsigned)b;
+      bcast[1] = acc;
+    }
+    __syncthreads();
+    prefix |= bcast[0] << shift;
+    mask |= 255u << shift;
+    rank -= (int)bcast[1];
+    __syncthreads();
+  }
+  return key2f(prefix);
+}
+static __device__ float quantile_linear(const float* x, int n, float q, unsigned* hist, unsigned* bcast) {
+  const float rank = q * (float)(n - 1);       // fp32, like torch.quantile
+  const float fl = floorf(rank), ce = ceilf(rank);
+  const float w = rank - fl;
+  const float a = select_kth(x, n, (int)fl, hist, bcast);
+  const float b = ((int)ce == (int)fl) ? a : select_kth(x, n, (int)ce, hist, bcast);
+  return (w < 0.5f) ? (a + w * (b - a)) : (b - (b - a) * (1.f - w));  // at::lerp
+}
+__global__ void __launch_bounds__(1024)
+moments_kernel(int n, const float* __restrict__ x, float* __restrict__ state, float* __restrict__ out, float decay,
+               float max_, float plow, float phigh) {
+  __shared__ unsigned hist[256];
+  __shared__ unsigned bcast[2];
+  const float lo = quantile_linear(x, n, plow, hist, bcast);
+  const float hi = quantile_linear(x, n, phigh, hist, bcast);
+  if (threadIdx.x == 0) {
+    const float nl = decay * state[0] + (1.f - decay) * lo;
+    const float nh = decay * state[1] + (1.f - decay) * hi;
+    state[0] = nl;
+    state[1] = nh;
+    out[0] = nl;
+    out[1] = fmaxf(1.f / max_, nh - nl);
+  }
+}
+
+// ---------------------------------------------------------------- actor objective (warp = one imagined state)
+struct HeadDims { int n; int k[8]; };
+
+template <int KRT>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+actor_loss_kernel(int M, HeadDims hd, const float* __restrict__ raw, int ldr, const int* __restrict__ act_idx, int lda,
+                  const float* __restrict__ lam, const float* __restrict__ values, const float* __restrict__ discount,
+                  const float* __restrict__ mom, float mix, float ent_coef, float scale, float* __restrict__ loss_rows,
+                  float* __restrict__ draw, int ldd) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const float off = mom[0], inv = mom[1];
+  const float adv = (lam[row] - off) / inv - (values[row] - off) / inv;
+  const float disc = discount[row];
+  float total = 0.f;
+  int col = 0;
+  for (int h = 0; h < hd.n; ++h) {
+    const int K = hd.k[h];
+    Group<KRT> r, ps, pm, lu, ln, p;
+    load_group(r, raw + (size_t)row * ldr + col, K, lane);
+    softmax_group(r, ps, K, lane);
+    if (mix > 0.f) unimix_group(ps, pm, lu, mix, K, lane);
+    else { lu = r; pm = ps; }
+    normalise_group(lu, ln, p, K, lane);
+    const int a = act_idx[(size_t)row * lda + h];
+    float lp = 0.f, en = 0.f;
+    for_k<KRT>(K, lane, [&](int j, int k) {
+      if (k == a) lp = ln.v[j];
+      en -= ln.v[j] * p.v[j];
+    });
+    lp = warp_sum(lp);
+    en = warp_sum(en);
+    total += lp * adv + ent_coef * en;
+    Group<KRT> glu;
+    for_k<KRT>(K, lane, [&](int j, int k) {
+      const float oh = (k == a) ? 1.f : 0.f;
+      glu.v[j] = -(scale * disc) * (adv * (oh - p.v[j]) + ent_coef * (-p.v[j] * (ln.v[j] + en)));
+    });
+    float* o = draw + (size_t)row * ldd + col;
+    if (mix > 0.f) {
+      Group<KRT> gps;
+      float dot = 0.f;
+      for_k<KRT>(K, lane, [&](int j, int) {
+        const bool inside = (pm.v[j] >= DV3_EPS32) && (pm.v[j] <= 1.f - DV3_EPS32);
+        gps.v[j] = inside ? (1.f - mix) * (glu.v[j] / pm.v[j]) : 0.f;
+        dot = fmaf(ps.v[j], gps.v[j], dot);
+      });
+      dot = warp_sum(dot);
+      for_k<KRT>(K, lane, [&](int j, int k) { o[k] = ps.v[j] * (gps.v[j] - dot); });
+    } else {
+      for_k<KRT>(K, lane, [&](int j, int k) { o[k] = glu.v[j]; });
+    }
+    col += K;
+  }
+  if (lane == 0) loss_rows[row] = -disc * total;
+}
+
+// ---------------------------------------------------------------- counter-based uniforms
+static __device__ __forceinline__ unsigned long long splitmix64(unsigned long long z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+__global__ void uniform_fill_kernel(size_t n, float* __restrict__ out, unsigned long long seed,
+                                    const long long* __restrict__ counter) {
+  const unsigned long long base = splitmix64(seed ^ splitmix64((unsigned long long)counter[0]));
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const unsigned long long r = splitmix64(base + i);
+    out[i] = (float)(r >> 40) * (1.0f / 16777216.0f);   // 24 random bits -> [0,1)
+  }
+}
+__global__ void bump_counter_kernel(long long* counter) { counter[0] += 1; }
+
+}  // namespace
+
+#define DV3_DISPATCH_KR(K, ...)                      \
+  do {                                               \
+    if ((K) <= 32) { constexpr int KRT = 1; __VA_ARGS__; }        \
+    else if ((K) <= 128) { constexpr int KRT = 4; __VA_ARGS__; }  \
+    else { constexpr int KRT = 8; __VA_ARGS__; }                  \
+  } while (0)
+
+extern "C" {
+
+static inline int groups_grid(long long n) { return (int)((n + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK); }
+
+int dv3_unimix_fwd(int R, int groups, int K, float mix, const float* raw, int ldr, float* logits, int ldo, void* stream) {
+  if (R <= 0 || groups <= 0 || K <= 0) return DV3_ERR_ARG;
+  if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
+  DV3_DISPATCH_KR(K, unimix_fwd_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(R, groups, K, mix, raw, ldr, logits, ldo));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_sample_onehot(int R, int groups, int K, const float* logits, int ldl, const float* u, int ldu, const int* forced,
+                      int ldf, int mode, int* idx, int ldi, float* onehot, int ldo, void* stream) {
+  if (R <= 0 || groups <= 0 || K <= 0) return DV3_ERR_ARG;
+  if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
+  if (!forced && !mode && !u) return DV3_ERR_ARG;
+  DV3_DISPATCH_KR(K, sample_onehot_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+      R, groups, K, logits, ldl, u, ldu, forced, ldf, mode, idx, ldi, onehot, ldo));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_unimix_bwd(int R, int groups, int K, float mix, const float* raw, int ldr, const float* dlogits, int lddl,
+                   const float* dz, int lddz, float* draw, int lddr, void* stream) {
+  if (R <= 0 || groups <= 0 || K <= 0) return DV3_ERR_ARG;
+  if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
+  DV3_DISPATCH_KR(K, unimix_bwd_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+      R, groups, K, mix, raw, ldr, dlogits, lddl, dz, lddz, draw, lddr));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_kl_balance(int R, int groups, int K, const float* post, const float* prior, float free_nats, float w_dyn,
+                   float w_rep, float scale, float* rows_out, float* dpost, float* dprior, void* stream) {
+  if (R <= 0 || groups <= 0 || groups > 32 || K <= 0) return DV3_ERR_ARG;
+  if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
+  DV3_DISPATCH_KR(K, kl_balance_kernel<KRT><<<R, groups * 32, 0, (cudaStream_t)stream>>>(groups, K, post, prior, free_nats, w_dyn, w_rep, scale,
+                                                                rows_out, dpost, dprior));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_twohot_loss(int M, int K, const float* logits, int ldl, const float* x, const float* w, float scale,
+                    float* loss_rows, float* dlogits, int ldd, int accumulate, void* stream) {
+  if (M <= 0 || K <= 1) return DV3_ERR_ARG;
+  if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
+  DV3_DISPATCH_KR(K, twohot_loss_kernel<KRT><<<groups_grid(M), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(M, K, logits, ldl, x, w, scale,
+                                                                                       loss_rows, dlogits, ldd, accumulate));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_twohot_mean(int M, int K, const float* logits, int ldl, float* out, void* stream) {
+  if (M <= 0 || K <= 1) return DV3_ERR_ARG;
+  if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
+  DV3_DISPATCH_KR(K, twohot_mean_kernel<KRT><<<groups_grid(M), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(M, K, logits, ldl, out));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_symlog_mse(int M, int Dd, const float* mode, int ldm, const float* target, int ldt, float scale, float* loss_rows,
+                   float* dmode, int ldd, void* stream) {
+  if (M <= 0 || Dd <= 0) return DV3_ERR_ARG;
+  symlog_mse_kernel<<<groups_grid(M), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(M, Dd, mode, ldm, target, ldt, scale,
+                                                                                      loss_rows, dmode, ldd);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_bernoulli_loss(int M, const float* logit, const float* dones, float scale, float* loss_rows, float* dlogit, void* stream) {
+  if (M <= 0) return DV3_ERR_ARG;
+  bernoulli_loss_kernel<<<(M + 255) / 256, 256, 0, (cudaStream_t)stream>>>(M, logit, dones, scale, loss_rows, dlogit);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_reduce_mean(int M, const float* x, int ldx, int col, float* out, int slot, float scale, int accumulate, void* stream) {
+  if (M <= 0) return DV3_ERR_ARG;
+  reduce_mean_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(M, x, ldx, col, out, slot, scale, accumulate);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_lambda_returns(int H, int N, const float* values, const float* rewards, const float* cont_logit, const float* dones,
+                       float gamma, float lmbda, float* lam, float* discount, void* stream) {
+  if (H <= 0 || N <= 0) return DV3_ERR_ARG;
+  lambda_returns_kernel<<<(N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(H, N, values, rewards, cont_logit, dones, gamma,
+                                                                          lmbda, lam, discount);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_moments(int n, const float* x, float* state, float* out, float decay, float max_, float plow, float phigh, void* stream) {
+  if (n <= 0) return DV3_ERR_ARG;
+  moments_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n, x, state, out, decay, max_, plow, phigh);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_actor_loss(int M, int n_heads, const int* head_dims, const float* raw, int ldr, const int* act_idx, int lda,
+                   const float* lam, const float* values, const float* discount, const float* mom, float mix, float ent_coef,
+                   float scale, float* loss_rows, float* draw, int ldd, void* stream) {
+  if (M <= 0 || n_heads <= 0 || n_heads > 8) return DV3_ERR_ARG;
+  HeadDims hd;
+  hd.n = n_heads;
+  int kmax = 0;
+  for (int i = 0; i < n_heads; ++i) {
+    if (head_dims[i] > KR * 32 || head_dims[i] <= 0) return DV3_ERR_UNSUPPORTED;
+    hd.k[i] = head_dims[i];
+    if (head_dims[i] > kmax) kmax = head_dims[i];
+  }
+  DV3_DISPATCH_KR(kmax, actor_loss_kernel<KRT><<<groups_grid(M), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+      M, hd, raw, ldr, act_idx, lda, lam, values, discount, mom, mix, ent_coef, scale, loss_rows, draw, ldd));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_uniform_fill(size_t n, float* out, unsigned long long seed, long long* counter, void* stream) {
+  if (n == 0) return DV3_OK;
+  size_t g = (n + 255) / 256;
+  if (g > 1184) g = 1184;
+  uniform_fill_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(n, out, seed, counter);
+  DV3_LAUNCH_CHECK();
+  bump_counter_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(counter);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+
+}  // extern "C"

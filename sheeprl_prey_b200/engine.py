@@ -198,6 +198,11 @@ class DV3Engine:
         self.lat = self.S + self.D
         self.bins = w.reward_model.bins
         self.seed = seed
+        self.opt_hparams = {
+            "world": dict(lr=w.optimizer.lr, eps=w.optimizer.eps, beta1=0.9, beta2=0.999),
+            "actor": dict(lr=a.actor.optimizer.lr, eps=a.actor.optimizer.eps, beta1=0.9, beta2=0.999),
+            "critic": dict(lr=a.critic.optimizer.lr, eps=a.critic.optimizer.eps, beta1=0.9, beta2=0.999),
+        }
         T, B, N, S, D, U, Hh, E, A, lat, H, M1, M0 = (self.T, self.B, self.N, self.S, self.D, self.U, self.Hh, self.E,
                                                        self.A, self.lat, self.H, self.M1, self.M0)
         f32 = dict(dtype=torch.float32, device=device)
@@ -418,10 +423,12 @@ class DV3Engine:
         ops.gemm("NN", self.dhidr_pre, self.Wr0[:, D:], self.de)
         self.enc.backward(self.obs_sym, N, self.de)
 
-    def _optimize(self, arena: Arena, opt_cfg, max_norm: float, slot: str) -> None:
+    def _optimize(self, arena: Arena, tag: str, max_norm: float, slot: str) -> None:
+        """a7 / a15: gradient all-reduce (data parallel), global-norm clip, Adam."""
         if self.dist is not None:
             self.dist.all_reduce_mean(arena.grad)
-        self.ops.adam_clip(arena.flat, arena.grad, arena.m, arena.v, arena.step, opt_cfg.lr, 0.9, 0.999, opt_cfg.eps,
+        hp = self.opt_hparams[tag]
+        self.ops.adam_clip(arena.flat, arena.grad, arena.m, arena.v, arena.step, hp["lr"], hp["beta1"], hp["beta2"], hp["eps"],
                            max_norm, self.metrics, _SLOT[slot])
 
     # ------------------------------------------------------------------ behaviour learning
@@ -483,7 +490,7 @@ class DV3Engine:
                        self.mom_out, a.unimix, a.actor.ent_coef, 1.0 / M0, self.pl_rows.view(M0), self.d_actor_raw)
         ops.reduce_mean(self.pl_rows, 0, self.metrics, _SLOT["Loss/policy_loss"], 1.0 / M0, False)
         self.act_stack.backward(self.traj, M0, self.d_actor_raw)
-        self._optimize(self.actor, a.actor.optimizer, a.actor.clip_gradients, "Grads/actor")
+        self._optimize(self.actor, "actor", a.actor.clip_gradients, "Grads/actor")
         # a13: critic loss (activations of the value pass above; target critic forward)
         self.tcrit_stack.forward(self.traj[:M0])
         ops.twohot_mean(self.tcrit_stack.out, self.tvalues)
@@ -491,7 +498,7 @@ class DV3Engine:
         ops.twohot_loss(self.crit_stack.out[:M0], self.tvalues, self.discount[:M0], 1.0 / M0, self.vl_rows.view(M0), self.d_crit, True)
         ops.reduce_mean(self.vl_rows, 0, self.metrics, _SLOT["Loss/value_loss"], 1.0 / M0, False)
         self.crit_stack.backward(self.traj, M0, self.d_crit)
-        self._optimize(self.critic, a.critic.optimizer, a.critic.clip_gradients, "Grads/critic")
+        self._optimize(self.critic, "critic", a.critic.clip_gradients, "Grads/critic")
 
     # ------------------------------------------------------------------ whole step
     def step(self, forced: Optional[dict] = None) -> None:
@@ -501,7 +508,7 @@ class DV3Engine:
         self.world_forward(None if forced is None else forced.get("post_idx"))
         self.world_losses()
         self.world_backward()
-        self._optimize(self.wm, w.optimizer, w.clip_gradients, "Grads/world_model")
+        self._optimize(self.wm, "world", w.clip_gradients, "Grads/world_model")
         self.imagine(None if forced is None else forced.get("imagine"))
         self.behaviour()
 

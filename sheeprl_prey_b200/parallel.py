@@ -1,0 +1,25 @@
+"""Data-parallel exchange steps of the training step over torch.distributed (NCCL on GPUs, gloo in CPU tests).
+Reference: the DDP gradient all-reduce implicit in fabric.backward (sheeprl/algos/dreamer_v3/agent.py:1054-1063,
+dreamer_v3.py:179,:318,:339) and fabric.all_gather inside Moments (algos/dreamer_v3/utils.py:35).  The engine reduces one
+flat gradient arena per optimizer group instead of the reference's nine DDP reducers."""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+class TorchDist:
+    def __init__(self, world_size: int):
+        if not dist.is_initialized():
+            raise RuntimeError("torch.distributed is not initialised")
+        self.world_size = world_size
+
+    def all_reduce_mean(self, t: torch.Tensor) -> None:
+        if dist.get_backend() == "nccl":
+            dist.all_reduce(t, op=dist.ReduceOp.AVG)
+        else:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            t.div_(self.world_size)
+
+    def all_gather(self, src: torch.Tensor, dst: torch.Tensor) -> None:
+        dist.all_gather_into_tensor(dst, src)

@@ -1,0 +1,114 @@
+"""Replay buffers: host logic on CPU (index selection with the reference's RNG order, ring semantics) against golden
+sessions recorded from the reference AsyncReplayBuffer, property tests in the style of the reference's
+tests/test_data/test_sequential_buffer.py, and (-m gpu) the bit-exact gather / ring-write kernels."""
+import pytest
+import torch
+
+from sheeprl_prey_b200.data.buffers import AsyncReplayBuffer, SequentialReplayBuffer, plan_sequential_starts
+from util import load_golden
+
+
+def _replay_session(sess, device, ops):
+    torch.manual_seed(sess["seed"])
+    rb = AsyncReplayBuffer(sess["size"], sess["n_envs"], device=device, sequential=True, ops=ops)
+    it = iter(sess["samples"])
+    for ev in sess["script"]:
+        if ev[0] == "add":
+            rb.add(ev[1], ev[2])
+        else:
+            s = rb.sample(ev[1], sequence_length=sess["T"], n_samples=ev[2])
+            ref = next(it)
+            for k, v in ref.items():
+                assert s[k].dtype == v.dtype and tuple(s[k].shape) == tuple(v.shape), k
+                assert torch.equal(s[k].cpu(), v), k          # bit-exact, uint8 and fp32 alike
+    assert [b._pos for b in rb.buffer] == sess["pos"] and [b.full for b in rb.buffer] == sess["full"]
+
+
+def test_golden_sessions_host_logic():
+    for sess in load_golden("buffers.pt"):
+        _replay_session(sess, "cpu", "cpu")
+
+
+@pytest.mark.gpu
+def test_golden_sessions_gpu():
+    for sess in load_golden("buffers.pt"):
+        _replay_session(sess, "cuda:0", None)
+
+
+def test_constructor_guards_and_errors():
+    with pytest.raises(ValueError):
+        AsyncReplayBuffer(-1, ops="cpu")
+    with pytest.raises(ValueError):
+        AsyncReplayBuffer(1, -1, ops="cpu")
+    rb = SequentialReplayBuffer(10, 1, device="cpu", ops="cpu")
+    with pytest.raises(RuntimeError):
+        rb.sample(2, sequence_length=2)
+    rb.add({"t": torch.rand(5, 1, 1)})
+    with pytest.raises(ValueError):
+        rb.sample(0, sequence_length=2)
+    with pytest.raises(ValueError):
+        rb.sample(2, sequence_length=8)      # too long for a not-full buffer
+    assert rb.sample(3, sequence_length=5, n_samples=2)["t"].shape == (2, 5, 3, 1)
+
+
+def test_sequences_never_straddle_the_write_head():
+    size, T = 20, 6
+    rb = SequentialReplayBuffer(size, 1, device="cpu", ops="cpu")
+    rb.add({"t": torch.arange(27, dtype=torch.float32).view(27, 1, 1)})   # full, pos = 7
+    assert rb.full == (True,) and rb._pos[0] == 7
+    s = rb.sample(256, sequence_length=T)["t"][0, :, :, 0]                 # [T, 256]
+    assert bool((s[1:] - s[:-1] == 1).all())                               # consecutive in time => never crosses pos
+    # not full: stays below pos
+    rb2 = SequentialReplayBuffer(size, 1, device="cpu", ops="cpu")
+    rb2.add({"t": torch.arange(9, dtype=torch.float32).view(9, 1, 1)})
+    s2 = rb2.sample(128, sequence_length=4)["t"]
+    assert float(s2.max()) <= 8
+
+
+def test_start_distribution_matches_reference_list_semantics():
+    # the analytic index map must equal indexing the reference's explicit list (buffers.py:292-297)
+    for size, pos, T in ((23, 7, 5), (23, 2, 5), (23, 0, 5), (23, 22, 5), (8, 3, 8)):
+        first_end = pos - T + 1
+        second_end = size if first_end >= 0 else size + first_end
+        valid = list(range(0, first_end)) + list(range(pos, second_end))
+        torch.manual_seed(4)
+        mine = plan_sequential_starts(pos, True, size, 64, T)
+        torch.manual_seed(4)
+        ref = torch.tensor(valid)[torch.randint(0, len(valid), size=(64,))]
+        assert torch.equal(mine, ref)
+
+
+def test_env_view_pokes_storage():
+    rb = AsyncReplayBuffer(6, 2, device="cpu", sequential=True, ops="cpu")
+    rb.add({"dones": torch.zeros(3, 2, 1)})
+    rb.buffer[1]["dones"][(rb.buffer[1]._pos - 1) % rb.buffer_size] = 1.0     # dreamer_v3.py:636-640
+    assert float(rb._store["dones"][1, 2, 0]) == 1.0 and float(rb._store["dones"][0].sum()) == 0.0
+
+
+@pytest.mark.gpu
+def test_gather_large_bit_exact():
+    dev = "cuda:0"
+    size, n_envs, T, B = 4096, 4, 64, 16
+    rb = AsyncReplayBuffer(size, n_envs, device=dev, sequential=True)
+    g = torch.Generator().manual_seed(0)
+    chunk = {"rgb": torch.randint(0, 256, (size + 100, n_envs, 3, 64, 64), generator=g, dtype=torch.uint8),
+             "state": torch.randn(size + 100, n_envs, 14, generator=g), "rewards": torch.randn(size + 100, n_envs, 1, generator=g)}
+    for i in range(0, size + 100, 512):
+        rb.add({k: v[i:i + 512] for k, v in chunk.items()})
+    torch.manual_seed(9)
+    env_id, start, col, samp = rb.plan(B, T, 2)
+    out = rb.gather(env_id, start, col, samp, B, T, 2)
+    torch.cuda.synchronize()
+    t = torch.arange(T)
+    for j in range(env_id.numel()):
+        rows = (int(start[j]) + t) % size
+        # ring content: element at ring position r is the last row written there
+        for k in chunk:
+            src = rb._store[k][int(env_id[j])].cpu()[rows]
+            assert torch.equal(out[k][int(samp[j]), :, int(col[j])].cpu(), src), k
+    # ring content itself equals the reference semantics: last `size` rows, wrapped
+    L = size + 100
+    expect = torch.empty(size, 14)
+    idx = torch.arange(L - size, L)
+    expect[idx % size] = chunk["state"][idx, 2]
+    assert torch.equal(rb._store["state"][2].cpu(), expect)

@@ -1,0 +1,301 @@
+"""-m gpu: every C-ABI kernel against its plain-PyTorch fp32 statement (oracle/torch_ops.py) on the same inputs.
+Tolerances: 1e-5 relative (to the output's max magnitude) for fp32 arithmetic; exact for indices / byte copies."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+TOL = 1e-5
+
+
+def rel(a, b):
+    return float((a - b).abs().max() / (b.abs().max() + 1e-20))
+
+
+def rnd(*shape, scale=1.0, seed=None):
+    g = torch.Generator(device="cpu")
+    g.manual_seed(hash(shape) % 100000 if seed is None else seed)
+    return (torch.randn(*shape, generator=g) * scale).to(DEV)
+
+
+@pytest.mark.parametrize("mode", ["NT", "NN", "TN"])
+@pytest.mark.parametrize("M,N,K", [(16, 512, 1124), (1, 1024, 256), (8, 100, 40), (32, 1536, 1024), (33, 77, 19),
+                                   (1024, 512, 1536), (1024, 255, 512), (1024, 1, 512), (257, 130, 14), (128, 128, 16)])
+def test_gemm(cuda_ops, torch_ops, mode, M, N, K):
+    A = rnd(M, K) if mode != "TN" else rnd(K, M)
+    B = rnd(N, K) if mode == "NT" else rnd(K, N)
+    bias = rnd(N)
+    for acc in (False, True):
+        C0 = rnd(M, N, seed=7)
+        C1 = C0.clone()
+        C0_d = C0.double()
+        torch_ops.gemm(mode, A.double(), B.double(), C0_d, bias.double(), acc)
+        cuda_ops.gemm(mode, A, B, C1, bias, acc)
+        assert rel(C1.double(), C0_d) < TOL, (mode, M, N, K, acc)
+
+
+def test_gemm_strided(cuda_ops, torch_ops):
+    big_a, big_b, big_c = rnd(64, 300), rnd(200, 300), rnd(64, 400)
+    A, B = big_a[:, 20:120], big_b[10:90, 50:150]
+    C0 = big_c.clone()
+    C1 = big_c.clone()
+    torch_ops.gemm("NT", A, B, C0[:, 100:180])
+    cuda_ops.gemm("NT", A, B, C1[:, 100:180])
+    assert rel(C1, C0) < TOL
+    assert torch.equal(C1[:, :100], big_c[:, :100]) and torch.equal(C1[:, 180:], big_c[:, 180:])
+
+
+def test_transpose_copy(cuda_ops):
+    s = rnd(100, 70)
+    d = torch.zeros(50, 100, device=DEV)
+    cuda_ops.transpose(s[:, 10:60], d)
+    assert torch.equal(d, s[:, 10:60].t())
+    d2 = torch.zeros(100, 90, device=DEV)
+    cuda_ops.copy2d(s[:, 5:65], d2[:, 20:80])
+    assert torch.equal(d2[:, 20:80], s[:, 5:65]) and float(d2[:, :20].abs().sum()) == 0
+
+
+@pytest.mark.parametrize("M,U,act,eps", [(16, 512, 1, 1e-3), (1024, 640, 1, 1e-5), (3, 40, 0, 1e-5), (16, 1536, 1, 1e-3)])
+def test_ln_act(cuda_ops, torch_ops, M, U, act, eps):
+    x, g, b = rnd(M, U, scale=2.0) + 0.3, rnd(U) * 0.2 + 1, rnd(U) * 0.1
+    outs = []
+    for ops in (torch_ops, cuda_ops):
+        y, mean, rstd = torch.zeros(M, U + 8, device=DEV), torch.zeros(M, device=DEV), torch.zeros(M, device=DEV)
+        ops.ln_act_fwd(x, g, b, eps, act, y[:, 4:4 + U], mean, rstd)
+        outs.append((y, mean, rstd))
+    for a, r in zip(outs[1], outs[0]):
+        assert rel(a, r) < TOL
+    y, mean, rstd = outs[0]
+    dy = rnd(M, U, seed=3)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        dx, dln = torch.zeros(M, U, device=DEV), torch.zeros(M, U, device=DEV)
+        ops.ln_act_bwd(dy, x, g, b, mean, rstd, act, dx, dln)
+        dg, db, db2 = torch.zeros(U, device=DEV), torch.zeros(U, device=DEV), torch.zeros(U, device=DEV)
+        ops.ln_param_grad(dln, x, mean, rstd, dg, db)
+        ops.colsum(dln, db2)
+        res.append((dx, dln, dg, db, db2))
+    for a, r in zip(res[1], res[0]):
+        assert rel(a, r) < 2e-5
+    # against autograd
+    xx = x.clone().requires_grad_(True)
+    gg, bb = g.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ln = torch.nn.functional.layer_norm(xx, (U,), gg, bb, eps)
+    out = torch.nn.functional.silu(ln) if act else ln
+    out.backward(dy)
+    assert rel(res[1][0], xx.grad) < 5e-5 and rel(res[1][2], gg.grad) < 5e-5 and rel(res[1][3], bb.grad) < 5e-5
+
+
+@pytest.mark.parametrize("R,D", [(16, 512), (1024, 256), (5, 24)])
+def test_gru_gate(cuda_ops, torch_ops, R, D):
+    gp, lnw, lnb, h = rnd(R, 3 * D, scale=1.5), rnd(3 * D) * 0.2 + 1, rnd(3 * D) * 0.1, rnd(R, D)
+    fw = []
+    for ops in (torch_ops, cuda_ops):
+        ho, mean, rstd = torch.zeros(R, D, device=DEV), torch.zeros(R, device=DEV), torch.zeros(R, device=DEV)
+        ops.gru_gate_fwd(gp, lnw, lnb, h, ho, mean, rstd)
+        fw.append((ho, mean, rstd))
+    for a, r in zip(fw[1], fw[0]):
+        assert rel(a, r) < TOL
+    dho = rnd(R, D, seed=5)
+    bw = []
+    for ops in (torch_ops, cuda_ops):
+        dgp, dln, dhi = torch.zeros(R, 3 * D, device=DEV), torch.zeros(R, 3 * D, device=DEV), torch.zeros(R, D, device=DEV)
+        ops.gru_gate_bwd(dho, gp, lnw, lnb, fw[0][1], fw[0][2], h, dgp, dln, dhi)
+        bw.append((dgp, dln, dhi))
+    for a, r in zip(bw[1], bw[0]):
+        assert rel(a, r) < 2e-5
+
+
+@pytest.mark.parametrize("R,groups,K", [(16, 32, 32), (1024, 1, 100), (7, 1, 2), (64, 4, 18), (9, 1, 200)])
+def test_unimix_sample(cuda_ops, torch_ops, R, groups, K):
+    raw = rnd(R, groups * K, scale=3.0)
+    lo = []
+    for ops in (torch_ops, cuda_ops):
+        l = torch.zeros(R, groups * K, device=DEV)
+        ops.unimix_fwd(raw, groups, K, 0.01, l)
+        lo.append(l)
+    assert rel(lo[1], lo[0]) < TOL
+    u = torch.rand(R, groups, device=DEV)
+    out = []
+    for ops in (torch_ops, cuda_ops):
+        idx = torch.zeros(R, groups, dtype=torch.int32, device=DEV)
+        oh = torch.zeros(R, groups * K, device=DEV)
+        ops.sample_onehot(lo[0], groups, K, u, None, 0, idx, oh)
+        idx_m = torch.zeros(R, groups, dtype=torch.int32, device=DEV)
+        oh_m = torch.zeros(R, groups * K, device=DEV)
+        ops.sample_onehot(lo[0], groups, K, None, None, 1, idx_m, oh_m)
+        out.append((idx, oh, idx_m, oh_m))
+    flips = float((out[0][0] != out[1][0]).float().mean())
+    assert flips <= 2e-3, flips          # boundary draws may flip on 1-ulp prob differences
+    assert torch.equal(out[0][2], out[1][2])
+    assert torch.equal(out[1][1].reshape(R, groups, K).argmax(-1).int(), out[1][0])
+    assert float(out[1][1].sum()) == R * groups
+    # forced indices
+    idx_f = torch.zeros(R, groups, dtype=torch.int32, device=DEV)
+    oh_f = torch.zeros(R, groups * K, device=DEV)
+    cuda_ops.sample_onehot(lo[0], groups, K, None, out[0][0], 0, idx_f, oh_f)
+    assert torch.equal(idx_f, out[0][0]) and torch.equal(oh_f, out[0][1])
+    # backward
+    dl, dz = rnd(R, groups * K, seed=11), rnd(R, groups * K, seed=12)
+    for a_dl, a_dz in ((dl, dz), (dl, None), (None, dz)):
+        r = []
+        for ops in (torch_ops, cuda_ops):
+            d = torch.zeros(R, groups * K, device=DEV)
+            ops.unimix_bwd(raw, groups, K, 0.01, a_dl, a_dz, d)
+            r.append(d)
+        assert rel(r[1], r[0]) < 2e-5
+
+
+def test_kl_balance(cuda_ops, torch_ops):
+    R, G, K = 64, 32, 32
+    post, prior = rnd(R, G * K, scale=0.2), rnd(R, G * K, scale=0.2, seed=9)
+    post[:32] *= 20   # rows well above the free-nats threshold
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        rows, dp, dq = torch.zeros(R, 4, device=DEV), torch.zeros(R, G * K, device=DEV), torch.zeros(R, G * K, device=DEV)
+        ops.kl_balance(post, prior, G, K, 1.0, 0.5, 0.1, 1.0 / R, rows, dp, dq)
+        res.append((rows, dp, dq))
+    assert float(res[0][0][:, 0].max()) > 1.0 > float(res[0][0][:, 0].min())
+    for a, r in zip(res[1], res[0]):
+        assert rel(a, r) < 2e-5
+
+
+@pytest.mark.parametrize("M,K", [(1024, 255), (37, 255), (16, 41)])
+def test_twohot(cuda_ops, torch_ops, M, K):
+    logits = rnd(M, K, scale=2.0)
+    x = rnd(M, scale=30.0)
+    x[0], x[1], x[2], x[3] = 0.0, 1e9, -1e9, math.expm1(20.0 / (K - 1) * 2)  # exact-bin / clipped edge cases
+    w = torch.rand(M, device=DEV)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        lr, dl, mean = torch.zeros(M, device=DEV), torch.zeros(M, K, device=DEV), torch.zeros(M, device=DEV)
+        ops.twohot_loss(logits, x, None, 0.5, lr, dl, False)
+        ops.twohot_loss(logits, -x, w, 0.25, lr, dl, True)
+        ops.twohot_mean(logits, mean)
+        res.append((lr, dl, mean))
+    for a, r in zip(res[1], res[0]):
+        assert rel(a, r) < 2e-5
+
+
+def test_small_losses(cuda_ops, torch_ops):
+    M, Dd = 1024, 14
+    mode, tgt = rnd(M, Dd), rnd(M, Dd, seed=2)
+    mode[0, :3] = tgt[0, :3] + 5e-5     # below the 1e-8 squared-distance tolerance
+    logit, dones = rnd(M, scale=3.0), (torch.rand(M, device=DEV) < 0.2).float()
+    x = torch.zeros(M, device=DEV)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        lr, dm = torch.zeros(M, device=DEV), torch.zeros(M, Dd, device=DEV)
+        ops.symlog_mse(mode, tgt, 1.0 / M, lr, dm)
+        lb, dlb = torch.zeros(M, device=DEV), torch.zeros(M, 1, device=DEV)
+        ops.bernoulli_loss(logit.view(M, 1), dones, 1.0 / M, lb, dlb)
+        sy = torch.zeros(M, Dd, device=DEV)
+        ops.symlog(mode * 10, sy)
+        met = torch.zeros(4, device=DEV)
+        ops.reduce_mean(dm, 3, met, 1, 0.5, False)
+        ops.reduce_mean(dm, 4, met, 1, 0.5, True)
+        res.append((lr, dm, lb, dlb, sy, met))
+    for a, r in zip(res[1], res[0]):
+        assert rel(a, r) < 2e-5
+
+
+def test_lambda_moments(cuda_ops, torch_ops):
+    H, N = 15, 1024
+    v, r, c = rnd((H + 1) * N, scale=3.0), rnd((H + 1) * N, seed=4), rnd((H + 1) * N, scale=2.0, seed=5)
+    dones = (torch.rand(N, device=DEV) < 0.1).float()
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        lam, disc = torch.zeros(H * N, device=DEV), torch.zeros((H + 1) * N, device=DEV)
+        ops.lambda_returns(v, r, c, dones, H, N, 0.997, 0.95, lam, disc)
+        st, out = torch.tensor([0.1, 0.7], device=DEV), torch.zeros(2, device=DEV)
+        ops.moments(lam, st, out, 0.99, 1.0, 0.05, 0.95)
+        ops.moments(lam * 3 + 1, st, out, 0.99, 1.0, 0.05, 0.95)
+        res.append((lam, disc, st, out))
+    assert rel(res[1][0], res[0][0]) < TOL and rel(res[1][1], res[0][1]) < TOL
+    assert rel(res[1][2], res[0][2]) < 1e-6 and rel(res[1][3], res[0][3]) < 1e-6
+    # exact order statistics
+    x = rnd(15360, scale=5.0)
+    for q in (0.05, 0.95, 0.5):
+        st, out = torch.zeros(2, device=DEV), torch.zeros(2, device=DEV)
+        cuda_ops.moments(x, st, out, 0.0, 1e8, q, q)
+        assert float(st[0]) == float(torch.quantile(x, q)), q
+
+
+@pytest.mark.parametrize("heads", [[100], [3, 5], [18], [200, 2]])
+def test_actor_loss(cuda_ops, torch_ops, heads):
+    M, A = 2048, sum(heads)
+    raw = rnd(M, A, scale=2.0)
+    idx = torch.stack([torch.randint(0, k, (M,)) for k in heads], -1).int().to(DEV)
+    lam, val, disc = rnd(M, seed=1), rnd(M, seed=2), torch.rand(M, device=DEV)
+    mom = torch.tensor([0.05, 1.3], device=DEV)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        lr, dr = torch.zeros(M, device=DEV), torch.zeros(M, A, device=DEV)
+        ops.actor_loss(raw, heads, idx, lam, val, disc, mom, 0.01, 3e-4, 1.0 / M, lr, dr)
+        res.append((lr, dr))
+    for a, r in zip(res[1], res[0]):
+        assert rel(a, r) < 2e-5
+
+
+def test_adam_clip_ema(cuda_ops, torch_ops):
+    n = 1_000_003 + 61
+    n = (n // 64) * 64
+    p0, g0 = rnd(n), rnd(n, scale=0.01, seed=3)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        p, g, m, v = p0.clone(), g0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+        step, norm = torch.zeros(1, device=DEV), torch.zeros(4, device=DEV)
+        for it in range(3):
+            ops.adam_clip(p, g * (it + 1), m, v, step, 1e-4, 0.9, 0.999, 1e-8, 5.0 if it < 2 else 1e9, norm, 2)
+        tgt = p0.clone()
+        ops.ema(tgt, p, 0.02)
+        res.append((p, m, v, step, norm, tgt))
+    # reference: torch.optim.Adam + clip_grad_norm_
+    pr = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([pr], lr=1e-4, eps=1e-8)
+    for it in range(3):
+        pr.grad = g0 * (it + 1)
+        torch.nn.utils.clip_grad_norm_([pr], 5.0 if it < 2 else 1e9)
+        opt.step()
+    assert rel(res[1][0], pr.detach()) < 1e-6
+    for a, r in zip(res[1], res[0]):
+        assert rel(a, r) < 1e-5
+
+
+def test_scan_plumbing(cuda_ops, torch_ops):
+    B, D, S, A, T = 16, 64, 96, 7, 5
+    first = (torch.rand(T, B, device=DEV) < 0.3).float()
+    hp, zp, zr = rnd(B, D + 8), rnd(B, S + 4), rnd(1, S)
+    for t_first in (True, False):
+        res = []
+        for ops in (torch_ops, cuda_ops):
+            hi, zi = torch.zeros(B, D + 3, device=DEV), torch.zeros(B, S + 5, device=DEV)
+            ops.scan_prep(first[1], None if t_first else hp[:, :D], None if t_first else zp[:, :S], zr, hi[:, :D], zi[:, :S])
+            res.append((hi, zi))
+        assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        dzd, dhd = rnd(B, S + 2, seed=1), rnd(B, D + 2, seed=2)
+        ops.scan_carry(first[2], zp[:, :S], hp[:, :D], hp[:, 8:], dzd[:, :S], dhd[:, :D])
+        res.append((dzd, dhd))
+    assert rel(res[1][0], res[0][0]) < 1e-6 and rel(res[1][1], res[0][1]) < 1e-6
+    acts = rnd(T, B, A)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        out = torch.zeros(T, B, S + A, device=DEV)
+        ops.mask_shift_actions(acts, first, out[:, :, S:])
+        res.append(out)
+    assert torch.equal(res[0], res[1])
+
+
+def test_uniform_fill(cuda_ops):
+    out = torch.zeros(1 << 20, device=DEV)
+    ctr = torch.zeros(1, dtype=torch.int64, device=DEV)
+    cuda_ops.uniform_fill(out, 7, ctr)
+    a = out.clone()
+    cuda_ops.uniform_fill(out, 7, ctr)
+    assert int(ctr) == 2 and not torch.equal(a, out)
+    assert 0.0 <= float(out.min()) and float(out.max()) < 1.0
+    assert abs(float(out.mean()) - 0.5) < 2e-3 and abs(float(out.var()) - 1 / 12) < 2e-3

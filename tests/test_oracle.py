@@ -1,0 +1,112 @@
+"""Pins the oracle (oracle/dv3_oracle.py, our CPU restatement) against the reference:
+  * everywhere: against tests/golden/dv3_step.pt, produced by the UNMODIFIED reference train() (oracle/make_golden.py);
+  * in the build container (where /root/reference exists): against the reference run live on fresh random inputs;
+  * closed-form known answers the reference's own tests do not hold."""
+import math
+
+import pytest
+import torch
+
+from oracle import dv3_oracle as O
+from oracle import ref_shim
+from sheeprl_prey_b200.configs import make_cfg
+from util import load_golden, rel
+
+KEYS = ["Loss/world_model_loss", "Loss/observation_loss", "Loss/reward_loss", "Loss/state_loss", "Loss/continue_loss", "State/kl",
+        "State/post_entropy", "State/prior_entropy", "Grads/world_model", "Loss/policy_loss", "Grads/actor", "Loss/value_loss",
+        "Grads/critic"]
+
+
+def test_oracle_matches_reference_golden():
+    g = load_golden("dv3_step.pt")
+    cfg = make_cfg(**g["cfg"])
+    tr = O.OracleTrainer(cfg, g["obs"], g["actions_dim"], g["params0"]["wm"], g["params0"]["actor"], g["params0"]["critic"],
+                         g["params0"]["target"])
+    for it in range(2):
+        out = tr.step({k: v.clone() for k, v in g["data"].items()}, g["noise"])
+        ref = g["steps"][it]
+        for k in KEYS:
+            assert abs(float(out[k]) - ref["metrics"][k]) <= 2e-5 * max(1.0, abs(ref["metrics"][k])), (it, k)
+        assert torch.equal(out["post_idx"].int(), ref["post_idx"])
+        assert torch.equal(out["z_idx"].int(), ref["z_idx"])
+        assert torch.equal(out["act_idx"].int(), ref["act_idx"])
+        assert abs(float(tr.low) - ref["moments_low"]) < 1e-7 and abs(float(tr.high) - ref["moments_high"]) < 1e-7
+    for name, mine in (("wm", tr.wm), ("actor", tr.actor), ("critic", tr.critic)):
+        for k, v in g["params2"][name].items():
+            assert rel(mine[k], v) < 2e-5, (name, k)
+
+
+@pytest.mark.skipif(not ref_shim.reference_available(), reason="reference tree only exists in the build container")
+def test_oracle_matches_reference_live():
+    from oracle import harness
+    from sheeprl_prey_b200.configs import ObsSpace
+
+    dv3, agent, loss, utils, buffers, dist = ref_shim.ref_modules()
+    from sheeprl.utils.utils import dotdict as ref_dotdict
+
+    torch.manual_seed(3)
+    kw = dict(size="XS", batch_size=4, sequence_length=7, horizon=3, deter=24, hidden=16, units=32, layers=1)
+    cfg = ref_dotdict(make_cfg(**kw))
+    adims, od = [4], {"state": 5}
+    fab = ref_shim.FakeFabric()
+    wm, actor, critic, tcritic = agent.build_models(fab, adims, False, cfg, ObsSpace({"state": (5,)}))
+    with torch.no_grad():
+        for p in list(critic.parameters()) + list(wm.reward_model.parameters()):
+            p.add_(0.05 * torch.randn_like(p))
+    S = harness.strip_wrapper_keys
+    tr = O.OracleTrainer(make_cfg(**kw), od, adims, S(wm.state_dict()), S(actor.state_dict()), S(critic.state_dict()), S(tcritic.state_dict()))
+    T, B, H = 7, 4, 3
+    data = harness.synthetic_batch(T, B, od, adims, done_p=0.2, seed=5)
+    noise = harness.synthetic_noise(T, B, H, 32, 1, seed=6)
+    a = cfg.algo
+    opts = [torch.optim.Adam(m.parameters(), lr=o.lr, eps=o.eps) for m, o in
+            ((wm, a.world_model.optimizer), (actor, a.actor.optimizer), (critic, a.critic.optimizer))]
+    mom = utils.Moments(fab, 0.99, 1.0, 0.05, 0.95)
+    agg = ref_shim.Aggregator()
+    tape = ref_shim.NoiseTape(harness.noise_tape_order(noise, T, H, 1, T * B))
+    tape.install(dist)
+    try:
+        dv3.train(fab, wm, actor, critic, tcritic, *opts, {k: v.clone() for k, v in data.items()}, agg, cfg, False, adims, mom)
+    finally:
+        tape.uninstall()
+    out = tr.step(data, noise)
+    for k in KEYS:
+        assert abs(float(out[k]) - agg.values[k]) <= 2e-5 * max(1.0, abs(agg.values[k])), k
+    for mine, ref in ((tr.wm, wm), (tr.actor, actor), (tr.critic, critic)):
+        rsd = S(ref.state_dict())
+        for k, v in mine.items():
+            assert rel(v, rsd[k]) < 2e-5, k
+
+
+# ---------------------------------------------------------------- closed-form known answers
+def test_symlog_symexp_roundtrip():
+    x = torch.linspace(-50, 50, 101)
+    assert rel(O.symexp(O.symlog(x)), x) < 1e-5
+
+
+def test_twohot_known_answers():
+    K = 255
+    bins = torch.linspace(-20, 20, K)
+    # zero-init head: -log_prob = ln K for any target
+    lp = O.twohot_log_prob(torch.zeros(4, K), torch.tensor([[0.0], [1.0], [-3.0], [1e6]]))
+    assert torch.allclose(-lp, torch.full((4,), math.log(K)), atol=1e-5)
+    # a target exactly on a bin is one-hot: log_prob = log_softmax at that bin
+    logits = torch.randn(1, K)
+    x = O.symexp(bins[100]).reshape(1, 1)
+    assert abs(float(O.twohot_log_prob(logits, x)) - float(torch.log_softmax(logits, -1)[0, 100])) < 1e-4
+    assert abs(float(O.twohot_mean(torch.zeros(1, K)))) < 1e-5
+
+
+def test_unimix_of_uniform_is_uniform_and_kl_floor():
+    l = O.unimix_logits(torch.zeros(2, 32, 32), 0.01)
+    assert torch.allclose(l.exp(), torch.full_like(l, 1 / 32), atol=1e-7)
+    assert float(O.kl_categorical(l, l).abs().max()) < 1e-6
+    # KL below the free-nats threshold -> state loss is exactly 0.5*1 + 0.1*1
+    assert abs(0.5 * max(0.0, 1.0) + 0.1 * max(0.0, 1.0) - 0.6) < 1e-12
+
+
+def test_lambda_values_limits():
+    H, N = 5, 3
+    r, v, c = torch.randn(H, N, 1), torch.randn(H, N, 1), torch.rand(H, N, 1)
+    assert torch.allclose(O.lambda_values(r, v, c, 0.0), r + c * v, atol=1e-6)
+    assert torch.allclose(O.lambda_values(r, v, torch.zeros_like(c), 0.95), r, atol=1e-6)

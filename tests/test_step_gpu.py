@@ -1,0 +1,141 @@
+"""-m gpu: the whole DreamerV3 gradient step on the CUDA library against (a) the reference's own train() outputs
+(golden) and (b) the CPU oracle at the BASELINE.json config-2 size (S, B16 x T64, H15, obs 14, 100 actions).
+Tolerances (north_star): 1e-5 relative for fp32 states / losses / lambda-returns; indices exact when teacher-forced."""
+import json
+import os
+
+import pytest
+import torch
+
+from oracle import dv3_oracle as O
+from oracle import harness
+from sheeprl_prey_b200.configs import make_cfg
+from sheeprl_prey_b200.engine import METRIC_KEYS
+from util import engine_from_params, load_golden, random_params_like, rel
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+REPORT = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+
+
+def _to(d, dev):
+    return {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in d.items()}
+
+
+def _dev_params(p):
+    return {n: {k: v.to(DEV) for k, v in d.items()} for n, d in p.items()}
+
+
+def test_step_reproduces_reference_golden(cuda_ops):
+    g = load_golden("dv3_step.pt")
+    cfg = make_cfg(**g["cfg"])
+    eng = engine_from_params(cfg, g["obs"], g["actions_dim"], _dev_params(g["params0"]), cuda_ops, DEV)
+    T, B = cfg.per_rank_sequence_length, cfg.per_rank_batch_size
+    for it in range(2):
+        eng.load_batch(_to(g["data"], DEV))
+        eng.load_noise(_to(g["noise"], DEV))
+        ref = g["steps"][it]
+        forced = dict(post_idx=ref["post_idx"].reshape(T * B, -1).to(DEV),
+                      imagine=dict(z_idx=ref["z_idx"].to(DEV), act_idx=ref["act_idx"].to(DEV)))
+        eng.step(forced if it == 1 else None)
+        torch.cuda.synchronize()
+        md = eng.metrics_dict()
+        if it == 0:   # free-running draws from the injected uniforms must give the reference's indices
+            assert torch.equal(eng.post_idx.cpu().reshape(T, B, -1), ref["post_idx"])
+            assert torch.equal(eng.z_idx.cpu(), ref["z_idx"])
+            assert torch.equal(eng.act_idx.cpu().reshape(ref["act_idx"].shape), ref["act_idx"])
+        for k in METRIC_KEYS:
+            assert abs(md[k] - ref["metrics"][k]) <= 3e-5 * max(1.0, abs(ref["metrics"][k])), (it, k, md[k], ref["metrics"][k])
+        assert abs(float(eng.mom_state[0]) - ref["moments_low"]) < 1e-6 and abs(float(eng.mom_state[1]) - ref["moments_high"]) < 1e-6
+    for name, arena in (("wm", eng.wm), ("actor", eng.actor), ("critic", eng.critic)):
+        for k, v in g["params2"][name].items():
+            assert rel(arena.p[k], v) < 5e-5, (name, k)
+
+
+@pytest.mark.parametrize("size,B,T,H,obs,acts", [("XS", 16, 64, 15, 4, [2]), ("S", 16, 64, 15, 14, [100])])
+def test_step_matches_oracle_at_baseline_sizes(cuda_ops, size, B, T, H, obs, acts):
+    cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=H)
+    od = {"state": obs}
+    params = random_params_like(cfg, od, acts, seed=11)
+    tr = O.OracleTrainer(cfg, od, acts, params["wm"], params["actor"], params["critic"], params["target"])
+    data = harness.synthetic_batch(T, B, od, acts, seed=1234, done_p=1 / 50)
+    noise = harness.synthetic_noise(T, B, H, 32, len(acts), seed=99)
+    out = tr.step({k: v.clone() for k, v in data.items()}, noise)
+    eng = engine_from_params(cfg, od, acts, _dev_params(params), cuda_ops, DEV)
+    eng.load_batch(_to(data, DEV))
+    eng.load_noise(_to(noise, DEV))
+    # (i) free-running: flip rate of the categorical draws (1-ulp prob differences may flip boundary draws)
+    eng.world_forward()
+    torch.cuda.synchronize()
+    flips = float((eng.post_idx.cpu().reshape(T, B, -1) != out["post_idx"]).float().mean())
+    # (ii) teacher-forced: continuous tensors to tolerance
+    forced = dict(post_idx=out["post_idx"].reshape(T * B, -1).int().to(DEV),
+                  imagine=dict(z_idx=out["z_idx"].int().to(DEV), act_idx=out["act_idx"].int().to(DEV)))
+    eng.step(forced)
+    torch.cuda.synchronize()
+    md = eng.metrics_dict()
+    N = T * B
+    rep = {"config": size, "flip_rate_free_running": flips}
+    rep["recurrent_states"] = rel(eng.latent[:, eng.S:].reshape(T, B, -1), out["recurrent_states"])
+    rep["post_logits"] = rel(eng.post_logits.reshape(out["post_logits"].shape), out["post_logits"])
+    rep["prior_logits"] = rel(eng.prior_logits.reshape(out["prior_logits"].shape), out["prior_logits"])
+    rep["traj"] = rel(eng.traj.reshape(out["traj"].shape), out["traj"])
+    rep["values"] = rel(eng.values.reshape(out["values"].shape), out["values"])
+    rep["lambda_values"] = rel(eng.lam.reshape(out["lambda_values"].shape), out["lambda_values"])
+    rep["discount"] = rel(eng.discount.reshape(out["discount"].shape), out["discount"])
+    for k in METRIC_KEYS:
+        rep[k] = abs(md[k] - float(out[k])) / max(1.0, abs(float(out[k])))
+    for nm, arena, gk, mx in (("world_model", eng.wm, "world_grads", 1000.0), ("actor", eng.actor, "actor_grads", 100.0),
+                              ("critic", eng.critic, "critic_grads", 100.0)):
+        coef = min(1.0, mx / (float(out[f"Grads/{nm}"]) + 1e-6))
+        rep[f"grad_{nm}"] = max(rel(arena.g[k] * coef, out[gk][k]) for k in arena.g)
+    for nm, arena, ref in (("wm", eng.wm, tr.wm), ("actor", eng.actor, tr.actor), ("critic", eng.critic, tr.critic)):
+        rep[f"param_{nm}"] = max(rel(arena.p[k], ref[k]) for k in arena.p)
+    os.makedirs(REPORT, exist_ok=True)
+    with open(os.path.join(REPORT, f"parity_{size}.json"), "w") as f:
+        json.dump(rep, f, indent=1)
+    assert flips < 2e-3, rep
+    assert torch.equal(eng.post_idx.cpu().reshape(T, B, -1), out["post_idx"].int())
+    for k in ("recurrent_states", "post_logits", "prior_logits", "traj", "values", "lambda_values", "discount"):
+        assert rep[k] < 1e-5, (k, rep)
+    for k in METRIC_KEYS:
+        assert rep[k] < 2e-5, (k, rep)
+    for k in ("grad_world_model", "grad_actor", "grad_critic"):
+        assert rep[k] < 1e-4, (k, rep)
+    for k in ("param_wm", "param_actor", "param_critic"):
+        assert rep[k] < 1e-4, (k, rep)
+
+
+def test_train_api_on_gpu():
+    """build_models() + train() through the reference-facing API: side effects of dreamer_v3.py:51-351."""
+    from sheeprl_prey_b200.algos.dreamer_v3 import build_models, train
+    from sheeprl_prey_b200.algos.dreamer_v3.dreamer_v3 import Moments
+    from sheeprl_prey_b200.configs import ObsSpace
+    from util import Aggregator, FakeFabric
+
+    cfg = make_cfg("XS", batch_size=8, sequence_length=16, horizon=5)
+    acts, od = [6], {"state": 9}
+    fab = FakeFabric(DEV)
+    torch.manual_seed(0)
+    wm, actor, critic, target = build_models(fab, acts, False, cfg, ObsSpace({"state": (9,)}))
+    a = cfg.algo
+    wo = torch.optim.Adam(wm.parameters(), lr=a.world_model.optimizer.lr, eps=a.world_model.optimizer.eps)
+    ao = torch.optim.Adam(actor.parameters(), lr=a.actor.optimizer.lr, eps=a.actor.optimizer.eps)
+    co = torch.optim.Adam(critic.parameters(), lr=a.critic.optimizer.lr, eps=a.critic.optimizer.eps)
+    mom = Moments(fab, 0.99, 1.0, 0.05, 0.95).to(DEV)
+    data = _to(harness.synthetic_batch(16, 8, od, acts, seed=3), DEV)
+    before = {k: v.clone() for k, v in wm.state_dict().items()}
+    losses = []
+    for it in range(3):
+        agg = Aggregator()
+        train(fab, wm, actor, critic, target, wo, ao, co, data, agg, cfg, False, acts, mom)
+        assert set(agg.values) == set(METRIC_KEYS)
+        assert all(v == v and abs(v) < 1e6 for v in agg.values.values()), agg.values
+        losses.append(agg.values["Loss/world_model_loss"])
+    assert float(data["is_first"][0].min()) == 1.0
+    after = wm.state_dict()
+    assert any(not torch.equal(before[k], after[k]) for k in before)
+    st = wo.state_dict()["state"]
+    assert len(st) > 0 and float(st[0]["step"]) == 3.0 and float(st[0]["exp_avg"].abs().sum()) > 0
+    assert losses[2] < losses[0]
+    assert float(mom.low) != 0.0 or float(mom.high) != 0.0

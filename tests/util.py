@@ -1,0 +1,73 @@
+"""Shared helpers for the test-suite (test infrastructure)."""
+import os
+from collections import OrderedDict
+
+import torch
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load_golden(name):
+    return torch.load(os.path.join(GOLDEN, name), weights_only=False)
+
+
+def rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-20))
+
+
+def make_arena(Arena, d, device, opt=True):
+    a = Arena(OrderedDict((k, tuple(v.shape)) for k, v in d.items()), device, with_opt=opt)
+    a.load(d)
+    return a
+
+
+def engine_from_params(cfg, obs_dims, actions_dim, params, ops, device):
+    from sheeprl_prey_b200.engine import Arena, DV3Engine
+
+    return DV3Engine(cfg, obs_dims, actions_dim, make_arena(Arena, params["wm"], device), make_arena(Arena, params["actor"], device),
+                     make_arena(Arena, params["critic"], device), make_arena(Arena, params["target"], device, False), ops, device)
+
+
+class FakeFabric:
+    """Single-process stand-in for lightning.Fabric (only what build_models / train touch)."""
+
+    world_size = 1
+    global_rank = 0
+
+    def __init__(self, device="cpu"):
+        self.device = torch.device(device)
+
+    def setup_module(self, m):
+        return m
+
+
+class Aggregator:
+    def __init__(self):
+        self.values = {}
+
+    def update(self, k, v):
+        self.values[k] = float(v)
+
+
+def random_params_like(cfg, obs_dims, actions_dim, seed=0):
+    """Random, non-degenerate parameters with the reference's state_dict names, made by the product's build_models on CPU
+    with the torch statement of the kernels (no reference needed -> usable on the GPU box)."""
+    from oracle.torch_ops import TorchOps
+    from sheeprl_prey_b200.algos.dreamer_v3.agent import build_models
+    from sheeprl_prey_b200.configs import ObsSpace
+
+    torch.manual_seed(seed)
+    wm, actor, critic, target = build_models(FakeFabric("cpu"), actions_dim, False, cfg, ObsSpace({k: (d,) for k, d in obs_dims.items()}),
+                                             ops=TorchOps())
+    g = torch.Generator().manual_seed(seed + 1)
+    with torch.no_grad():
+        for m in (wm, actor, critic, target):
+            for n, p in m.named_parameters():
+                if p.dim() == 1:
+                    p.add_(0.1 * torch.randn(p.shape, generator=g))
+        for m in (critic, target, wm.reward_model):
+            for p in m.parameters():
+                p.add_(0.05 * torch.randn(p.shape, generator=g))
+    sd = lambda m: {k: v.detach().clone() for k, v in m.state_dict().items()}  # noqa: E731
+    return dict(wm=sd(wm), actor=sd(actor), critic=sd(critic), target=sd(target))
