@@ -103,6 +103,8 @@ class CudaOps:
     Method semantics are stated (in torch) by oracle/torch_ops.py, which the GPU tests compare against."""
 
     name = "cuda"
+    dtype_name = "f32"                      # arithmetic type of the contractions in this mode
+    gemm_kernel_name = "gemm_tiled_kernel (fp32 CUDA-core, 128x128x16)"
 
     def __init__(self, device, scratch_bytes: int = 32 << 20):
         self.lib = load_library()

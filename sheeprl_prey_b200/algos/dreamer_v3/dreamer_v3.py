@@ -2,6 +2,7 @@
 executed by the CUDA step engine.  Callable from the reference's `main` loop unchanged (dreamer_v3.py:717-732)."""
 from __future__ import annotations
 
+import os
 from typing import Any, Dict, Optional, Sequence
 
 import torch
@@ -15,6 +16,37 @@ def get_engine(world_model) -> DV3Engine:
         raise RuntimeError("world_model was not created by sheeprl_prey_b200.algos.dreamer_v3.build_models: "
                            "there is no PyTorch fallback for the training step")
     return eng
+
+
+def _graphs_enabled(eng: DV3Engine) -> bool:
+    """CUDA-graph replay of the step (the step has no host syncs, static buffers and device-side scalars).
+    DV3_CUDA_GRAPH=0 disables it; with data parallelism it is opt-in (DV3_CUDA_GRAPH=1) because the NCCL calls are
+    captured too."""
+    flag = os.environ.get("DV3_CUDA_GRAPH")
+    if flag is not None:
+        return flag == "1"
+    return eng.dist is None and eng.ops.name == "cuda"
+
+
+def _graphed_step(eng: DV3Engine) -> None:
+    """First call runs eagerly (warm-up: lazy module loading, NCCL setup), the second captures noise generation +
+    the whole step into one CUDA graph, later calls replay it."""
+    calls = getattr(eng, "_graph_calls", 0)
+    eng._graph_calls = calls + 1
+    if calls == 0:
+        eng.load_noise(None)
+        eng.step()
+        return
+    if getattr(eng, "_graph", None) is None:
+        torch.cuda.synchronize(eng.device)
+        l0 = eng.ops.launches
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            eng.load_noise(None)
+            eng.step()
+        eng._graph_launches = eng.ops.launches - l0     # kernels of ours inside one replay
+        eng._graph = g
+    eng._graph.replay()
 
 
 def _adopt_optimizer(eng: DV3Engine, arena, optimizer, tag: str) -> None:
@@ -77,8 +109,11 @@ def train(
         eng.mom_state[1:2].copy_(moments.high.reshape(1))
         moments._dv3_bound = True
     eng.load_batch(data)
-    eng.load_noise(noise)
-    eng.step()
+    if noise is not None or not _graphs_enabled(eng):
+        eng.load_noise(noise)
+        eng.step()
+    else:
+        _graphed_step(eng)
     if moments is not None:
         moments.low = eng.mom_state[0].clone()
         moments.high = eng.mom_state[1].clone()

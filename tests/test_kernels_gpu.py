@@ -150,8 +150,8 @@ def test_unimix_sample(cuda_ops, torch_ops, R, groups, K):
 
 def test_kl_balance(cuda_ops, torch_ops):
     R, G, K = 64, 32, 32
-    post, prior = rnd(R, G * K, scale=0.2), rnd(R, G * K, scale=0.2, seed=9)
-    post[:32] *= 20   # rows well above the free-nats threshold
+    post, prior = rnd(R, G * K, scale=0.1), rnd(R, G * K, scale=0.1, seed=9)
+    post[:32] *= 40   # rows well above the free-nats threshold; the rest below it
     res = []
     for ops in (torch_ops, cuda_ops):
         rows, dp, dq = torch.zeros(R, 4, device=DEV), torch.zeros(R, G * K, device=DEV), torch.zeros(R, G * K, device=DEV)
@@ -260,8 +260,10 @@ def test_adam_clip_ema(cuda_ops, torch_ops):
         torch.nn.utils.clip_grad_norm_([pr], 5.0 if it < 2 else 1e9)
         opt.step()
     assert rel(res[1][0], pr.detach()) < 1e-6
+    st = opt.state[pr]
+    assert rel(res[1][1], st["exp_avg"]) < 1e-6 and rel(res[1][2], st["exp_avg_sq"]) < 1e-6   # kernel follows torch's lerp form
     for a, r in zip(res[1], res[0]):
-        assert rel(a, r) < 1e-5
+        assert rel(a, r) < 5e-5
 
 
 def test_scan_plumbing(cuda_ops, torch_ops):
