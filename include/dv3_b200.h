@@ -46,6 +46,11 @@ int dv3_seq_gather(int n_keys, const void* const* src, void* const* dst, const l
 int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                  const float* bias, int accumulate, void* stream);
 
+/* Same contract on the tcgen05 tensor cores: operands are rounded to bf16 while being staged into shared memory,
+ * products accumulate in fp32 in TMEM (north_star: "2e-2 for bf16 tensor-core GEMMs"). */
+int dv3_gemm_bf16_tc(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                     const float* bias, int accumulate, void* stream);
+
 /* ---- LayerNorm(+SiLU) blocks: miniblock order Linear -> LayerNorm -> SiLU, utils/model.py:71-87 ---------- */
 int dv3_ln_act_fwd(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
                    float* y, int ldy, float* mean, float* rstd, void* stream);
@@ -103,8 +108,8 @@ int dv3_actor_loss(int M, int n_heads, const int* head_dims_host, const float* r
 
 /* ---- optimizer: clip_grad_norm_ + torch.optim.Adam.step, dreamer_v3.py:179-187,:318-323,:339-344 ---------- */
 size_t dv3_adam_clip_scratch_bytes(void);
-int dv3_adam_clip(size_t n, float* p, const float* g, float* m, float* v, float* step, float lr, float beta1, float beta2,
-                  float eps, float max_norm, float* norm_out, int slot, float* scratch, size_t scratch_bytes, void* stream);
+int dv3_adam_clip(size_t n, float* p, const float* g, float* m, float* v, float* step, double lr, double beta1, double beta2,
+                  double eps, double max_norm, float* norm_out, int slot, float* scratch, size_t scratch_bytes, void* stream);
 int dv3_ema(size_t n, float* target, const float* src, float tau, void* stream); /* dreamer_v3.py:713-716 */
 
 /* ---- utilities ------------------------------------------------------------------------------------------- */

@@ -22,6 +22,7 @@ SIGNATURES = {
     "dv3_buffer_add": [c_fp, c_fp, _i, _ll, _i, _i, _ll, c_fp],
     "dv3_seq_gather": [_i, c_fp, c_fp, c_fp, _i, _i, _i, _i, c_fp, c_fp, c_fp, c_fp, c_fp],
     "dv3_gemm_f32": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_gemm_bf16_tc": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_ln_act_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp],
     "dv3_ln_act_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_col_reduce_scratch_bytes": [_i, _i],
@@ -45,7 +46,8 @@ SIGNATURES = {
     "dv3_moments": [_i, c_fp, c_fp, c_fp, _f, _f, _f, _f, c_fp],
     "dv3_actor_loss": [_i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _f, _f, _f, c_fp, c_fp, _i, c_fp],
     "dv3_adam_clip_scratch_bytes": [],
-    "dv3_adam_clip": [_sz, c_fp, c_fp, c_fp, c_fp, c_fp, _f, _f, _f, _f, _f, c_fp, _i, c_fp, _sz, c_fp],
+    "dv3_adam_clip": [_sz, c_fp, c_fp, c_fp, c_fp, c_fp, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, c_fp, _i, c_fp,
+                      _sz, c_fp],
     "dv3_ema": [_sz, c_fp, c_fp, _f, c_fp],
     "dv3_copy2d": [_i, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_transpose": [_i, _i, c_fp, _i, c_fp, _i, c_fp],
@@ -103,10 +105,16 @@ class CudaOps:
     Method semantics are stated (in torch) by oracle/torch_ops.py, which the GPU tests compare against."""
 
     name = "cuda"
-    dtype_name = "f32"                      # arithmetic type of the contractions in this mode
-    gemm_kernel_name = "gemm_tiled_kernel (fp32 CUDA-core, 128x128x16)"
 
-    def __init__(self, device, scratch_bytes: int = 32 << 20):
+    def __init__(self, device, scratch_bytes: int = 32 << 20, precision: Optional[str] = None):
+        """precision: "fp32" (CUDA-core contractions, strict 1e-5 parity mode) or "bf16" (tcgen05 tensor-core contractions for
+        the large-M GEMMs, 2e-2 parity mode); default from $DV3_PRECISION, else "fp32"."""
+        self.precision = precision or os.environ.get("DV3_PRECISION", "fp32")
+        if self.precision not in ("fp32", "bf16"):
+            raise ValueError(self.precision)
+        self.dtype_name = "f32" if self.precision == "fp32" else "bf16"
+        self.gemm_kernel_name = ("gemm_tiled_kernel (fp32 CUDA-core, 128x128x16)" if self.precision == "fp32"
+                                 else "gemm_tc_kernel (tcgen05 bf16, 128x128x64, fp32 TMEM accumulate)")
         self.lib = load_library()
         self.device = torch.device(device)
         if self.device.type != "cuda":
@@ -136,7 +144,11 @@ class CudaOps:
         if self.gemm_log is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(torch.cuda.current_stream(self.device))
-        _chk(self.lib.dv3_gemm_f32(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()), "dv3_gemm_f32")
+        if self.precision == "bf16" and M >= 128 and N >= 32 and K >= 32:
+            _chk(self.lib.dv3_gemm_bf16_tc(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()),
+                 "dv3_gemm_bf16_tc")
+        else:
+            _chk(self.lib.dv3_gemm_f32(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()), "dv3_gemm_f32")
         if self.gemm_log is not None:
             e1.record(torch.cuda.current_stream(self.device))
             self.gemm_log.append((e0, e1, 2.0 * M * N * K, M, N, K, mode))

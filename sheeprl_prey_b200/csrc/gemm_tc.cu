@@ -1,0 +1,284 @@
+// bf16 tensor-core contraction on the 5th-generation tensor cores (tcgen05) with fp32 accumulation in TMEM.
+//
+//   C[M,N] (+)= op(A) * op(B) (+ bias)      NT / NN / TN, fp32 operands in HBM, arbitrary leading dimensions, ragged edges.
+//
+// Design (sm_100a only):
+//   * one CTA per 128 x 128 output tile, 256 threads, warp-specialised:
+//       warps 0-3  producers : read the fp32 operand tiles from global memory (coalesced for either majorness), round to
+//                              bf16 in registers and write them into shared memory directly in the canonical K-major
+//                              SWIZZLE_128B UMMA layout (so the fp32->bf16 conversion and any transposition are fused
+//                              into the load path: no staging copies of activations / weights / gradients in HBM);
+//       warp  4    issuer    : allocates TMEM, one elected lane issues tcgen05.mma (M128 x N128 x K16, kind::f16) per
+//                              16-wide k slice, and tcgen05.commit's the stage's "empty" mbarrier;
+//       warps 4-7  epilogue  : tcgen05.ld the 128x128 fp32 accumulator (one TMEM lane = one output row), add bias /
+//                              accumulate, store to global.
+//   * 4-stage shared-memory ring (32 KB / stage) with full / empty mbarriers; generic-proxy writes are made visible to
+//     the tensor core's async proxy with fence.proxy.async before the "full" arrive.
+// Replaces torch addmm/mm (cuBLAS) on the large-M contractions of the step (a3, a5, a8, a9, a12, a13 and
+// the batched weight-gradient contractions of a7).  Numerics: bf16 operands, fp32 accumulate -> the north-star's
+// "2e-2 for bf16 tensor-core GEMMs" mode.
+#include "common.cuh"
+#include <cuda_bf16.h>
+
+namespace {
+
+constexpr int TBM = 128, TBN = 128, TBK = 64, STAGES = 4;
+constexpr int NUM_PRODUCERS = 128, NUM_THREADS = 256;
+constexpr int STAGE_A_BYTES = TBM * TBK * 2, STAGE_B_BYTES = TBN * TBK * 2;
+constexpr int TMEM_COLS = 128;
+enum { MODE_NT = 0, MODE_NN = 1, MODE_TN = 2 };
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+
+// K-major SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): 8-row groups 1024 B apart.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);   // start address, 16 B units
+  d |= (uint64_t)1 << 16;                        // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset: next 8-row group
+  d |= (uint64_t)1 << 46;                        // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
+  return d;
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): D=F32, A=B=BF16, both K-major, N>>3 at [17,23), M>>4 at [24,29)
+__device__ __forceinline__ uint32_t make_instr_desc(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// Loads one [128 rows][64 k] operand tile (fp32, either majorness) and stores it as bf16 in the UMMA layout.
+//   kcontig: element (r, k) at src[(r0 + r) * ld + k0 + k]     else: src[(k0 + k) * ld + r0 + r]
+template <bool KCONTIG>
+__device__ __forceinline__ void load_tile(const float* __restrict__ src, int ld, int r0, int k0, int R, int K, bool vec_ok,
+                                          uint8_t* smem_tile, int p) {
+  float v[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int item = p + NUM_PRODUCERS * i;
+    if (KCONTIG) {
+      const int row = item >> 3, chunk = item & 7;
+      const int gr = r0 + row, gk = k0 + chunk * 8;
+      const float* ptr = src + (size_t)gr * ld + gk;
+      if (gr < R && vec_ok && gk + 8 <= K) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(ptr));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(ptr) + 1);
+        v[i][0] = a.x; v[i][1] = a.y; v[i][2] = a.z; v[i][3] = a.w;
+        v[i][4] = b.x; v[i][5] = b.y; v[i][6] = b.z; v[i][7] = b.w;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] = (gr < R && gk + j < K) ? __ldg(ptr + j) : 0.f;
+      }
+    } else {
+      const int row = item & 127, chunk = item >> 7;
+      const int gr = r0 + row, gk = k0 + chunk * 8;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[i][j] = (gr < R && gk + j < K) ? __ldg(src + (size_t)(gk + j) * ld + gr) : 0.f;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int item = p + NUM_PRODUCERS * i;
+    const int row = KCONTIG ? (item >> 3) : (item & 127);
+    const int chunk = KCONTIG ? (item & 7) : (item >> 7);
+    const uint32_t off = (uint32_t)(row >> 3) * 1024u + (uint32_t)(row & 7) * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
+    uint4 q;
+    q.x = pack_bf16(v[i][0], v[i][1]);
+    q.y = pack_bf16(v[i][2], v[i][3]);
+    q.z = pack_bf16(v[i][4], v[i][5]);
+    q.w = pack_bf16(v[i][6], v[i][7]);
+    *reinterpret_cast<uint4*>(smem_tile + off) = q;
+  }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
+               float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B: 1024 B alignment
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * STAGE_A_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (STAGE_A_BYTES + STAGE_B_BYTES));
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * TBN;
+  const int num_kb = (K + TBK - 1) / TBK;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], NUM_PRODUCERS); mbar_init(&empty_bar[s], 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 4) {   // TMEM allocation is warp-collective; the same warp frees it at the end
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp < 4) {
+    // ===================== producers =====================
+    const int p = threadIdx.x;
+    constexpr bool A_KCONTIG = (MODE != MODE_TN);
+    constexpr bool B_KCONTIG = (MODE == MODE_NT);
+    const bool a_vec = A_KCONTIG && ((lda & 3) == 0) && ((((uintptr_t)A) & 15) == 0);
+    const bool b_vec = B_KCONTIG && ((ldb & 3) == 0) && ((((uintptr_t)B) & 15) == 0);
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % STAGES;
+      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      mbar_wait(&empty_bar[s], ph ^ 1u);
+      load_tile<A_KCONTIG>(A, lda, m0, kb * TBK, M, K, a_vec, smem_a + s * STAGE_A_BYTES, p);
+      load_tile<B_KCONTIG>(B, ldb, n0, kb * TBK, N, K, b_vec, smem_b + s * STAGE_B_BYTES, p);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the async (UMMA) proxy
+      mbar_arrive(&full_bar[s]);
+    }
+  } else {
+    if (warp == 4) {
+      // ===================== MMA issuer =====================
+      const uint32_t idesc = make_instr_desc(TBM, TBN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+        mbar_wait(&full_bar[s], ph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (lane == 0) {
+          const uint32_t a_addr = smem_u32(smem_a + s * STAGE_A_BYTES);
+          const uint32_t b_addr = smem_u32(smem_b + s * STAGE_B_BYTES);
+#pragma unroll
+          for (int k = 0; k < TBK / 16; ++k) {
+            const uint64_t adesc = make_smem_desc(a_addr + k * 32);   // 16 bf16 = 32 B along K inside the swizzle atom
+            const uint64_t bdesc = make_smem_desc(b_addr + k * 32);
+            const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+            asm volatile(
+                "{\n"
+                ".reg .pred p;\n"
+                "setp.ne.b32 p, %4, 0;\n"
+                "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+                "}\n" ::"r"(tmem_base),
+                "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+                : "memory");
+          }
+          // frees the smem stage once the MMAs above have read it (implies tcgen05.fence::before_thread_sync)
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[s])) : "memory");
+          if (kb == num_kb - 1)
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(tmem_full_bar)) : "memory");
+        }
+        __syncwarp();
+      }
+    }
+    // ===================== epilogue (warps 4-7; TMEM lanes 32*(warp%4) ..) =====================
+    mbar_wait(tmem_full_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const int ew = warp & 3;
+    const int gm = m0 + ew * 32 + lane;
+    const bool vec_store = ((ldc & 3) == 0) && ((((uintptr_t)C) & 15) == 0);
+#pragma unroll 1
+    for (int c0 = 0; c0 < TBN; c0 += 32) {
+      uint32_t r[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)c0;
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+            "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+            "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+            "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+          : "r"(taddr));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (gm < M) {
+        float* crow = C + (size_t)gm * ldc;
+        const int gn0 = n0 + c0;
+        if (vec_store && gn0 + 32 <= N) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 o;
+            o.x = __uint_as_float(r[j]); o.y = __uint_as_float(r[j + 1]); o.z = __uint_as_float(r[j + 2]); o.w = __uint_as_float(r[j + 3]);
+            if (bias) { o.x += __ldg(bias + gn0 + j); o.y += __ldg(bias + gn0 + j + 1); o.z += __ldg(bias + gn0 + j + 2); o.w += __ldg(bias + gn0 + j + 3); }
+            float4* dst = reinterpret_cast<float4*>(crow + gn0 + j);
+            if (accumulate) { const float4 old = *dst; o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w; }
+            *dst = o;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int gn = gn0 + j;
+            if (gn < N) {
+              float o = __uint_as_float(r[j]);
+              if (bias) o += __ldg(bias + gn);
+              if (accumulate) o += crow[gn];
+              crow[gn] = o;
+            }
+          }
+        }
+      }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 4) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+  }
+}
+
+constexpr int SMEM_BYTES = STAGES * (STAGE_A_BYTES + STAGE_B_BYTES) + (2 * STAGES + 1) * 8 + 16 + 1024;
+
+template <int MODE>
+int launch_tc(int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc, const float* bias,
+              int accumulate, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  dim3 grid((N + TBN - 1) / TBN, (M + TBM - 1) / TBM);
+  if (grid.y > 65535) return DV3_ERR_UNSUPPORTED;
+  gemm_tc_kernel<MODE><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+
+}  // namespace
+
+extern "C" int dv3_gemm_bf16_tc(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C,
+                                int ldc, const float* bias, int accumulate, void* stream_) {
+  if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return DV3_ERR_ARG;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  switch (mode) {
+    case MODE_NT: return launch_tc<MODE_NT>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    case MODE_NN: return launch_tc<MODE_NN>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    case MODE_TN: return launch_tc<MODE_TN>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    default: return DV3_ERR_ARG;
+  }
+}
