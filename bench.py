@@ -322,10 +322,13 @@ def main():
     ap.add_argument("--size", default="S", choices=sorted(WORKLOADS))
     ap.add_argument("--buffer", type=int, default=100000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
+                    help="bf16: tcgen05 tensor-core contractions (north-star 2e-2 mode); fp32: CUDA-core strict-parity mode")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    os.environ["DV3_PRECISION"] = args.precision
     if args.impl == "reference":
         run_reference(args, rank)
     else:

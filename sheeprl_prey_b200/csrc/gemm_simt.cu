@@ -161,12 +161,108 @@ gemm_skinny_nt_kernel(int M, int N, int K, const float* __restrict__ A, int lda,
   }
 }
 
+
+// ---- skinny NT, streaming version: no shared memory, no barriers --------------------------------------
+// One warp owns SKV_NPW output columns; each lane streams V-wide vectors of the weight rows (coalesced, several loads in
+// flight) and reads the <= 16 activation rows through L1 (they are shared by every warp of the SM).  The per-step
+// contractions of the RSSM scan have M = B = 16: the problem is to read the weight matrix once at L2/HBM speed.
+constexpr int SKV_WARPS = 8, SKV_NPW = 2;
+
+template <int V> struct VecT;
+template <> struct VecT<4> { using T = float4; };
+template <> struct VecT<2> { using T = float2; };
+template <> struct VecT<1> { using T = float; };
+template <int V> __device__ __forceinline__ void vec_load(const float* p, float (&o)[V]) {
+  typename VecT<V>::T v = __ldg(reinterpret_cast<const typename VecT<V>::T*>(p));
+  const float* f = reinterpret_cast<const float*>(&v);
+#pragma unroll
+  for (int i = 0; i < V; ++i) o[i] = f[i];
+}
+
+template <int MT, int V>
+__global__ void __launch_bounds__(SKV_WARPS * 32)
+gemm_skinny_stream_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
+                          float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nbase = (blockIdx.x * SKV_WARPS + warp) * SKV_NPW;
+  if (nbase >= N) return;
+  float acc[SKV_NPW][MT];
+#pragma unroll
+  for (int c = 0; c < SKV_NPW; ++c)
+#pragma unroll
+    for (int m = 0; m < MT; ++m) acc[c][m] = 0.f;
+  const int KV = (K / V) * V;
+  const float* brow[SKV_NPW];
+#pragma unroll
+  for (int c = 0; c < SKV_NPW; ++c) brow[c] = B + (size_t)min(nbase + c, N - 1) * ldb;
+#pragma unroll 2
+  for (int k = lane * V; k < KV; k += 32 * V) {
+    float w[SKV_NPW][V];
+#pragma unroll
+    for (int c = 0; c < SKV_NPW; ++c) vec_load<V>(brow[c] + k, w[c]);
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      float a[V];
+      if (m < M) vec_load<V>(A + (size_t)m * lda + k, a);
+      else {
+#pragma unroll
+        for (int i = 0; i < V; ++i) a[i] = 0.f;
+      }
+#pragma unroll
+      for (int c = 0; c < SKV_NPW; ++c)
+#pragma unroll
+        for (int i = 0; i < V; ++i) acc[c][m] = fmaf(a[i], w[c][i], acc[c][m]);
+    }
+  }
+  for (int k = KV + lane; k < K; k += 32) {   // scalar tail
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      const float a = (m < M) ? __ldg(A + (size_t)m * lda + k) : 0.f;
+#pragma unroll
+      for (int c = 0; c < SKV_NPW; ++c) acc[c][m] = fmaf(a, __ldg(brow[c] + k), acc[c][m]);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < SKV_NPW; ++c) {
+    const int n = nbase + c;
+#pragma unroll
+    for (int m = 0; m < MT; ++m) {
+      float v = warp_sum(acc[c][m]);
+      if (lane == 0 && n < N && m < M) {
+        if (bias) v += bias[n];
+        float* cp = C + (size_t)m * ldc + n;
+        if (accumulate) v += *cp;
+        *cp = v;
+      }
+    }
+  }
+}
+
+template <int MT>
+static int launch_skinny_stream(int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                                const float* bias, int accumulate, cudaStream_t stream) {
+  dim3 grid((N + SKV_WARPS * SKV_NPW - 1) / (SKV_WARPS * SKV_NPW));
+  const uintptr_t al = (uintptr_t)A | (uintptr_t)B | ((uintptr_t)lda * 4) | ((uintptr_t)ldb * 4);
+  if ((al & 15) == 0)
+    gemm_skinny_stream_kernel<MT, 4><<<grid, SKV_WARPS * 32, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+  else if ((al & 7) == 0)
+    gemm_skinny_stream_kernel<MT, 2><<<grid, SKV_WARPS * 32, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+  else
+    gemm_skinny_stream_kernel<MT, 1><<<grid, SKV_WARPS * 32, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+  cudaError_t e = cudaGetLastError();
+  return e == cudaSuccess ? DV3_OK : (int)e;
+}
+
 }  // namespace
 
 extern "C" int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C,
                             int ldc, const float* bias, int accumulate, void* stream_) {
   if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return DV3_ERR_ARG;
   cudaStream_t stream = (cudaStream_t)stream_;
+  if (mode == MODE_NT && M <= 16) {
+    if (M <= 8) return launch_skinny_stream<8>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    return launch_skinny_stream<16>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+  }
   if (mode == MODE_NT && M <= 32) {
     dim3 grid((N + SK_WARPS * SK_NPW - 1) / (SK_WARPS * SK_NPW));
     if (M <= 8)

@@ -180,6 +180,9 @@ def test_step_bf16_tensor_core_mode_within_2e2():
     cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=H)
     od = {"state": obs}
     params = random_params_like(cfg, od, acts, seed=11)
+    # Bernoulli.mode thresholds the continue logit at 0 (dreamer_v3.py:262-266): with a random-init head the logits sit at the
+    # discontinuity and any rounding flips them.  A trained model predicts "continue" confidently; emulate that with the bias.
+    params["wm"][f"continue_model._model.{3 * cfg.algo.world_model.discount_model.mlp_layers}.bias"] += 4.0
     tr = O.OracleTrainer(cfg, od, acts, params["wm"], params["actor"], params["critic"], params["target"])
     data = harness.synthetic_batch(T, B, od, acts, seed=1234, done_p=1 / 50)
     noise = harness.synthetic_noise(T, B, H, 32, len(acts), seed=99)
@@ -199,6 +202,7 @@ def test_step_bf16_tensor_core_mode_within_2e2():
     rep["traj"] = rel(eng.traj.reshape(out["traj"].shape), out["traj"])
     rep["values"] = rel(eng.values.reshape(out["values"].shape), out["values"])
     rep["lambda_values"] = rel(eng.lam.reshape(out["lambda_values"].shape), out["lambda_values"])
+    rep["continue_flag_flips"] = float((eng.discount.reshape(out["discount"].shape).cpu() != out["discount"]).float().mean())
     for k in METRIC_KEYS:
         rep[k] = abs(md[k] - float(out[k])) / max(1.0, abs(float(out[k])))
     for nm, arena, gk, mx in (("world_model", eng.wm, "world_grads", 1000.0), ("actor", eng.actor, "actor_grads", 100.0),
