@@ -281,6 +281,17 @@ def run_ours(args, rank, world, local_rank):
             os.environ.pop("DV3_CUDA_GRAPH", None)
         else:
             os.environ["DV3_CUDA_GRAPH"] = saved
+        table = {}
+        for (s_, e_, f, M, N, Kk, mode) in log:
+            t = table.setdefault(f"{mode} M{M} N{N} K{Kk}", [0, 0.0, f])
+            t[0] += 1
+            t[1] += s_.elapsed_time(e_)
+        rows = sorted(((k, c, ms_ / c, f / (ms_ / c * 1e-3) / 1e12) for k, (c, ms_, f) in table.items()), key=lambda r: -r[1] * r[2])
+        if os.path.isdir(os.path.join(ROOT, "gpurun_out")):
+            with open(os.path.join(ROOT, "gpurun_out", f"gemm_table_{args.size}_{args.precision}.txt"), "w") as fh:
+                fh.write("shape | launches (2 steps) | avg ms | TFLOP/s\n")
+                for k, c, ms_, tf in rows:
+                    fh.write(f"{k} | {c} | {ms_:.4f} | {tf:.1f}\n")
         big = [(s.elapsed_time(e), f) for (s, e, f, M, N, Kk, mode) in log if M > 32]
         tot_ms, tot_fl = sum(x[0] for x in big), sum(x[1] for x in big)
         all_ms = sum(s.elapsed_time(e) for (s, e, *_r) in log)
