@@ -26,6 +26,7 @@ extern "C" {
 #define DV3_ERR_ARG (-1)
 #define DV3_ERR_UNSUPPORTED (-2)
 #define DV3_ERR_SCRATCH (-3)
+#define DV3_ERR_TOO_LARGE (-4)
 
 #define DV3_GEMM_NT 0 /* C[M,N] = A[M,K] * B[N,K]^T   (nn.Linear forward)            */
 #define DV3_GEMM_NN 1 /* C[M,N] = A[M,K] * B[K,N]     (input gradient dX = dY * W)    */
@@ -61,6 +62,15 @@ int dv3_ln_act_bwd(int M, int U, const float* dy, int lddy, const float* x, int 
 size_t dv3_col_reduce_scratch_bytes(int M, int U);
 int dv3_col_reduce(int M, int U, const float* d, int ldd, const float* x, int ldx, const float* mean, const float* rstd,
                    float* out_a, float* out_b, float* scratch, size_t scratch_bytes, void* stream);
+
+/* No counterpart in the reference.  Same reduction as dv3_col_reduce for hosts that cannot give it a workspace (a plugin
+ * handed only inputs and outputs, a loop that cannot afford cudaMalloc's device-wide synchronisation, a runtime that owns
+ * all device memory): the partial sums live in a fixed 2 MiB __device__ array inside the library, so nothing is allocated.
+ * Limit: U <= 4096 columns (any M); larger U returns DV3_ERR_TOO_LARGE.  The first call on a device resolves the array's
+ * address -- issue it before any stream capture.  All calls on a device share the array: calls that can overlap on the
+ * GPU race, serialise them. */
+int dv3_col_reduce_noalloc(int M, int U, const float* d, int ldd, const float* x, int ldx, const float* mean, const float* rstd,
+                           float* out_a, float* out_b, void* stream);
 
 /* ---- LayerNormGRUCell gates, models.py:388-395 ------------------------------------------------------------ */
 int dv3_gru_gate_fwd(int R, int D, const float* gates_pre, int ldg, const float* lnw, const float* lnb, const float* h_in,

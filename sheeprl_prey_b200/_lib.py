@@ -27,6 +27,7 @@ SIGNATURES = {
     "dv3_ln_act_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_col_reduce_scratch_bytes": [_i, _i],
     "dv3_col_reduce": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
+    "dv3_col_reduce_noalloc": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp],
     "dv3_gru_gate_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp],
     "dv3_gru_gate_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_scan_prep": [_i, _i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, _i, c_fp, _i, c_fp],
@@ -83,7 +84,7 @@ class Dv3Error(RuntimeError):
 
 def _chk(rc: int, what: str) -> None:
     if rc != 0:
-        kind = {-1: "bad argument", -2: "unsupported size", -3: "scratch too small"}.get(rc, f"cudaError {rc}")
+        kind = {-1: "bad argument", -2: "unsupported size", -3: "scratch too small", -4: "problem larger than the built-in workspace"}.get(rc, f"cudaError {rc}")
         raise Dv3Error(f"{what} failed: {kind}")
 
 

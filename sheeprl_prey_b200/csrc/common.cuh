@@ -8,6 +8,7 @@
 #define DV3_ERR_ARG (-1)
 #define DV3_ERR_UNSUPPORTED (-2)
 #define DV3_ERR_SCRATCH (-3)
+#define DV3_ERR_TOO_LARGE (-4)
 
 #define DV3_LAUNCH_CHECK()                                    \
   do {                                                        \

@@ -296,6 +296,52 @@ int dv3_col_reduce(int M, int U, const float* d, int ldd, const float* x, int ld
   return DV3_OK;
 }
 
+// ---- dv3_col_reduce for callers that must not allocate ------------------------------------------------------------
+// Some hosts of this library cannot hand us a workspace: a plugin that is only given its input and output buffers, a
+// real-time loop in which cudaMalloc's implicit device-wide synchronisation is not acceptable, or an embedding runtime that
+// owns every byte of device memory through its own pool and forbids side allocations.  For them the two-stage reduction
+// keeps its partial sums in the fixed array below instead of a caller-provided scratch buffer.
+//   * the array lives in every GPU that loads this library until the process exits (2 MiB per device);
+//   * it bounds the problem: U (columns) <= DV3_COL_REDUCE_NOALLOC_MAX_U, any M; larger U is refused with DV3_ERR_TOO_LARGE;
+//   * nothing in it has to start at zero: stage 1 overwrites every partial that stage 2 reads, so leftovers of the previous
+//     call are harmless -- but all calls on a device share the one array, so two calls whose kernels can overlap on the GPU
+//     (different streams without an ordering between them) race and must be serialised by the caller;
+//   * the first call on each device looks the array's device address up (cudaGetSymbolAddress, with that device current) and
+//     caches it; make that first call before starting any stream capture.
+// No cudaMalloc / cudaFree / allocating library routine is reached from this entry point.
+#define DV3_COL_REDUCE_NOALLOC_MAX_U 4096
+#define DV3_COL_REDUCE_MAX_CHUNKS 64
+static __device__ __align__(256) float g_col_reduce_partials[DV3_COL_REDUCE_MAX_CHUNKS * 2 * DV3_COL_REDUCE_NOALLOC_MAX_U];
+static float* g_col_reduce_partials_addr[64] = {nullptr};   // per device ordinal: DEVICE address of the array above
+
+int dv3_col_reduce_noalloc(int M, int U, const float* d, int ldd, const float* x, int ldx, const float* mean,
+                           const float* rstd, float* out_a, float* out_b, void* stream) {
+  if (M <= 0 || U <= 0 || !d) return DV3_ERR_ARG;
+  if (U > DV3_COL_REDUCE_NOALLOC_MAX_U) return DV3_ERR_TOO_LARGE;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return DV3_ERR_UNSUPPORTED;
+  float* partials = g_col_reduce_partials_addr[dev];
+  if (partials == nullptr) {
+    // In host code `g_col_reduce_partials` is only a handle for the symbol, not an address a kernel may dereference.
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_col_reduce_partials);
+    if (e != cudaSuccess) return (int)e;
+    partials = static_cast<float*>(p);
+    g_col_reduce_partials_addr[dev] = partials;
+  }
+  int nchunks = (M + 63) / 64;
+  if (nchunks > DV3_COL_REDUCE_MAX_CHUNKS) nchunks = DV3_COL_REDUCE_MAX_CHUNKS;
+  const int rows_per_chunk = (M + nchunks - 1) / nchunks;
+  dim3 g1((U + CR_COLS - 1) / CR_COLS, nchunks);
+  col_reduce_stage1<<<g1, CR_COLS * CR_ROWLANES, 0, (cudaStream_t)stream>>>(M, U, d, ldd, x, ldx, mean, rstd, rows_per_chunk, partials);
+  DV3_LAUNCH_CHECK();
+  col_reduce_stage2<<<(U + 127) / 128, 128, 0, (cudaStream_t)stream>>>(U, nchunks, partials, out_a, out_b);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+
 int dv3_gru_gate_fwd(int R, int D, const float* gates_pre, int ldg, const float* lnw, const float* lnb,
                      const float* h_in, int ldhi, float* h_out, int ldho, float* mean, float* rstd, void* stream) {
   if (R <= 0 || D <= 0) return DV3_ERR_ARG;
