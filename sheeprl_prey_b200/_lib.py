@@ -145,7 +145,7 @@ class CudaOps:
         if self.gemm_log is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(torch.cuda.current_stream(self.device))
-        if self.precision == "bf16" and M >= 128 and N >= 32 and K >= 32:
+        if self.precision == "bf16" and N >= 32 and K >= 32 and (M >= 128 or (mode == "TN" and M >= 16 and K >= 2048)):
             _chk(self.lib.dv3_gemm_bf16_tc(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()),
                  "dv3_gemm_bf16_tc")
         else:

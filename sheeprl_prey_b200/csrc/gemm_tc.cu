@@ -19,11 +19,12 @@
 // "2e-2 for bf16 tensor-core GEMMs" mode.
 #include "common.cuh"
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 namespace {
 
 constexpr int TBM = 128, TBN = 128, TBK = 64, STAGES = 4;
-constexpr int NUM_PRODUCERS = 128, NUM_THREADS = 256;
+constexpr int NUM_PRODUCERS = 256, NUM_THREADS = 384;
 constexpr int STAGE_A_BYTES = TBM * TBK * 2, STAGE_B_BYTES = TBN * TBK * 2;
 constexpr int TMEM_COLS = 128;
 enum { MODE_NT = 0, MODE_NN = 1, MODE_TN = 2 };
@@ -60,9 +61,22 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
   return d;
 }
+// MN-major SWIZZLE_128B descriptor: the tile is stored as [64-element MN groups][8-deep k groups][8 k rows x 128 B];
+// LBO = byte stride between 64-element MN groups, SBO = byte stride between 8-deep k groups (cute canonical layout
+// ((T,8,m),(8,k)) : ((1,T,LBO),(8T,SBO)) for Major-MN, T = 8 bf16).
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
 // Instruction descriptor (cute::UMMA::InstrDescriptor): D=F32, A=B=BF16, both K-major, N>>3 at [17,23), M>>4 at [24,29)
-__device__ __forceinline__ uint32_t make_instr_desc(int m, int n) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+__device__ __forceinline__ uint32_t make_instr_desc(int m, int n, bool a_mn_major, bool b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
+         ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
@@ -75,9 +89,10 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 template <bool KCONTIG>
 __device__ __forceinline__ void load_tile(const float* __restrict__ src, int ld, int r0, int k0, int R, int K, bool vec_ok,
                                           uint8_t* smem_tile, int p) {
-  float v[8][8];
+  constexpr int PER = (TBM * TBK / 8) / NUM_PRODUCERS;
+  float v[PER][8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
+  for (int i = 0; i < PER; ++i) {
     const int item = p + NUM_PRODUCERS * i;
     if (KCONTIG) {
       const int row = item >> 3, chunk = item & 7;
@@ -100,7 +115,7 @@ __device__ __forceinline__ void load_tile(const float* __restrict__ src, int ld,
     }
   }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
+  for (int i = 0; i < PER; ++i) {
     const int item = p + NUM_PRODUCERS * i;
     const int row = KCONTIG ? (item >> 3) : (item & 127);
     const int chunk = KCONTIG ? (item & 7) : (item >> 7);
@@ -114,10 +129,54 @@ __device__ __forceinline__ void load_tile(const float* __restrict__ src, int ld,
   }
 }
 
-template <int MODE>
+// MN-contiguous source kept MN-major in shared memory (no transposition): element (r, k) at src[(k0 + k) * ld + r0 + r].
+// Each item is 8 consecutive r (two float4 loads) at one k -> one 16 B store.  Tile = 2 MN groups x 8 k groups of 1 KB atoms.
+__device__ __forceinline__ void load_tile_mn(const float* __restrict__ src, int ld, int r0, int k0, int R, int K, bool vec_ok,
+                                             uint8_t* smem_tile, int p) {
+  constexpr int ITEMS = (TBM / 8) * TBK;              // 16 chunks x 64 k = 1024
+  constexpr int PER = ITEMS / NUM_PRODUCERS;
+  float v[PER][8];
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int item = p + NUM_PRODUCERS * i;
+    const int chunk = item & 15, k = item >> 4;       // 16 consecutive threads cover 128 contiguous r
+    const int gr = r0 + chunk * 8, gk = k0 + k;
+    const float* ptr = src + (size_t)gk * ld + gr;
+    if (gk < K && vec_ok && gr + 8 <= R) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(ptr));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(ptr) + 1);
+      v[i][0] = a.x; v[i][1] = a.y; v[i][2] = a.z; v[i][3] = a.w;
+      v[i][4] = b.x; v[i][5] = b.y; v[i][6] = b.z; v[i][7] = b.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[i][j] = (gk < K && gr + j < R) ? __ldg(ptr + j) : 0.f;
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < PER; ++i) {
+    const int item = p + NUM_PRODUCERS * i;
+    const int chunk = item & 15, k = item >> 4;
+    const uint32_t off = (uint32_t)(chunk >> 3) * 8192u + (uint32_t)(k >> 3) * 1024u + (uint32_t)(k & 7) * 128u +
+                         (uint32_t)(((chunk & 7) ^ (k & 7)) << 4);
+    uint4 q;
+    q.x = pack_bf16(v[i][0], v[i][1]);
+    q.y = pack_bf16(v[i][2], v[i][3]);
+    q.z = pack_bf16(v[i][4], v[i][5]);
+    q.w = pack_bf16(v[i][6], v[i][7]);
+    *reinterpret_cast<uint4*>(smem_tile + off) = q;
+  }
+}
+
+__global__ void zero2d_kernel(int M, int N, float* __restrict__ C, int ldc) {
+  const size_t n = (size_t)M * N;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    C[(i / N) * ldc + (i % N)] = 0.f;
+}
+
+template <int MODE, bool MNMAJ>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
-               float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+               float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int kb_per_split) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B: 1024 B alignment
   uint8_t* smem_a = smem;
@@ -129,14 +188,17 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * TBN;
-  const int num_kb = (K + TBK - 1) / TBK;
+  const int total_kb = (K + TBK - 1) / TBK;
+  const int kb_begin = blockIdx.z * kb_per_split;                 // split-K: this CTA owns k-blocks [kb_begin, kb_begin + num_kb)
+  const int num_kb = min(kb_per_split, total_kb - kb_begin);
+  const bool split = gridDim.z > 1;                                // partial tiles are combined with red.global.add
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], NUM_PRODUCERS); mbar_init(&empty_bar[s], 1); }
     mbar_init(tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 4) {   // TMEM allocation is warp-collective; the same warp frees it at the end
+  if (warp == NUM_PRODUCERS / 32) {   // TMEM allocation is warp-collective; the same warp frees it at the end
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(TMEM_COLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
@@ -145,26 +207,31 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  if (warp < 4) {
+  constexpr bool A_KCONTIG = (MODE != MODE_TN);
+  constexpr bool B_KCONTIG = (MODE == MODE_NT);
+  constexpr bool A_MN = MNMAJ && !A_KCONTIG;      // operand stays MN-major in shared memory
+  constexpr bool B_MN = MNMAJ && !B_KCONTIG;
+  if (warp < NUM_PRODUCERS / 32) {
     // ===================== producers =====================
     const int p = threadIdx.x;
-    constexpr bool A_KCONTIG = (MODE != MODE_TN);
-    constexpr bool B_KCONTIG = (MODE == MODE_NT);
-    const bool a_vec = A_KCONTIG && ((lda & 3) == 0) && ((((uintptr_t)A) & 15) == 0);
-    const bool b_vec = B_KCONTIG && ((ldb & 3) == 0) && ((((uintptr_t)B) & 15) == 0);
+    const bool a_vec = ((lda & 3) == 0) && ((((uintptr_t)A) & 15) == 0);
+    const bool b_vec = ((ldb & 3) == 0) && ((((uintptr_t)B) & 15) == 0);
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % STAGES;
       const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
       mbar_wait(&empty_bar[s], ph ^ 1u);
-      load_tile<A_KCONTIG>(A, lda, m0, kb * TBK, M, K, a_vec, smem_a + s * STAGE_A_BYTES, p);
-      load_tile<B_KCONTIG>(B, ldb, n0, kb * TBK, N, K, b_vec, smem_b + s * STAGE_B_BYTES, p);
+      const int k0 = (kb_begin + kb) * TBK;
+      if (A_MN) load_tile_mn(A, lda, m0, k0, M, K, a_vec, smem_a + s * STAGE_A_BYTES, p);
+      else load_tile<A_KCONTIG>(A, lda, m0, k0, M, K, a_vec && A_KCONTIG, smem_a + s * STAGE_A_BYTES, p);
+      if (B_MN) load_tile_mn(B, ldb, n0, k0, N, K, b_vec, smem_b + s * STAGE_B_BYTES, p);
+      else load_tile<B_KCONTIG>(B, ldb, n0, k0, N, K, b_vec && B_KCONTIG, smem_b + s * STAGE_B_BYTES, p);
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the async (UMMA) proxy
       mbar_arrive(&full_bar[s]);
     }
   } else {
-    if (warp == 4) {
+    if (warp == NUM_PRODUCERS / 32) {
       // ===================== MMA issuer =====================
-      const uint32_t idesc = make_instr_desc(TBM, TBN);
+      const uint32_t idesc = make_instr_desc(TBM, TBN, A_MN, B_MN);
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % STAGES;
         const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
@@ -175,8 +242,9 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
           const uint32_t b_addr = smem_u32(smem_b + s * STAGE_B_BYTES);
 #pragma unroll
           for (int k = 0; k < TBK / 16; ++k) {
-            const uint64_t adesc = make_smem_desc(a_addr + k * 32);   // 16 bf16 = 32 B along K inside the swizzle atom
-            const uint64_t bdesc = make_smem_desc(b_addr + k * 32);
+            // K-major: 16 bf16 = 32 B along K inside the swizzle atom.  MN-major: 16 k = two 1 KB k-groups.
+            const uint64_t adesc = A_MN ? make_smem_desc_mn(a_addr + k * 2048, 8192, 1024) : make_smem_desc(a_addr + k * 32);
+            const uint64_t bdesc = B_MN ? make_smem_desc_mn(b_addr + k * 2048, 8192, 1024) : make_smem_desc(b_addr + k * 32);
             const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
             asm volatile(
                 "{\n"
@@ -218,7 +286,17 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
       if (gm < M) {
         float* crow = C + (size_t)gm * ldc;
         const int gn0 = n0 + c0;
-        if (vec_store && gn0 + 32 <= N) {
+        if (split) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int gn = gn0 + j;
+            if (gn < N) {
+              float o = __uint_as_float(r[j]);
+              if (bias && blockIdx.z == 0) o += __ldg(bias + gn);
+              atomicAdd(crow + gn, o);
+            }
+          }
+        } else if (vec_store && gn0 + 32 <= N) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
             float4 o;
@@ -245,7 +323,7 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
   __syncthreads();
-  if (warp == 4) {
+  if (warp == NUM_PRODUCERS / 32) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
   }
@@ -253,32 +331,62 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
 
 constexpr int SMEM_BYTES = STAGES * (STAGE_A_BYTES + STAGE_B_BYTES) + (2 * STAGES + 1) * 8 + 16 + 1024;
 
-template <int MODE>
+template <int MODE, bool MNMAJ>
 int launch_tc(int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc, const float* bias,
               int accumulate, cudaStream_t stream) {
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MODE, MNMAJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
-  dim3 grid((N + TBN - 1) / TBN, (M + TBM - 1) / TBM);
+  dim3 grid((N + TBN - 1) / TBN, (M + TBM - 1) / TBM, 1);
   if (grid.y > 65535) return DV3_ERR_UNSUPPORTED;
-  gemm_tc_kernel<MODE><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+  // split-K when the output has too few tiles to fill the 148 SMs (weight-gradient contractions: K = T*B*H tokens)
+  const int total_kb = (K + TBK - 1) / TBK;
+  const int tiles = (int)(grid.x * grid.y);
+  int splits = 1;
+  if (tiles < 120 && total_kb >= 8) {
+    splits = (296 + tiles - 1) / tiles;
+    if (splits > total_kb / 4) splits = total_kb / 4;
+    if (splits > 64) splits = 64;
+    if (splits < 1) splits = 1;
+  }
+  int kb_per_split = (total_kb + splits - 1) / splits;
+  splits = (total_kb + kb_per_split - 1) / kb_per_split;
+  grid.z = splits;
+  if (splits > 1 && !accumulate) {
+    size_t n = (size_t)M * N;
+    int zb = (int)((n + 255) / 256);
+    if (zb > 1184) zb = 1184;
+    zero2d_kernel<<<zb, 256, 0, stream>>>(M, N, C, ldc);
+    DV3_LAUNCH_CHECK();
+  }
+  gemm_tc_kernel<MODE, MNMAJ><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, kb_per_split);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }
 
 }  // namespace
 
+static int g_tc_mn_major = -1;   // operands whose contiguous dimension is M/N: keep them MN-major in smem (1) or transpose (0)
+
 extern "C" int dv3_gemm_bf16_tc(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C,
                                 int ldc, const float* bias, int accumulate, void* stream_) {
   if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return DV3_ERR_ARG;
   cudaStream_t stream = (cudaStream_t)stream_;
+  if (g_tc_mn_major < 0) {
+    const char* e = getenv("DV3_TC_MNMAJOR");
+    g_tc_mn_major = (e && e[0] == '0') ? 0 : 1;
+  }
   switch (mode) {
-    case MODE_NT: return launch_tc<MODE_NT>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
-    case MODE_NN: return launch_tc<MODE_NN>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
-    case MODE_TN: return launch_tc<MODE_TN>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    case MODE_NT: return launch_tc<MODE_NT, false>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    case MODE_NN:
+      return g_tc_mn_major ? launch_tc<MODE_NN, true>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream)
+                           : launch_tc<MODE_NN, false>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    case MODE_TN:
+      return g_tc_mn_major ? launch_tc<MODE_TN, true>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream)
+                           : launch_tc<MODE_TN, false>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
     default: return DV3_ERR_ARG;
   }
 }

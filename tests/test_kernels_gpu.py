@@ -305,7 +305,8 @@ def test_uniform_fill(cuda_ops):
 
 @pytest.mark.parametrize("mode", ["NT", "NN", "TN"])
 @pytest.mark.parametrize("M,N,K", [(128, 128, 64), (256, 128, 128), (1024, 512, 1536), (16384, 512, 512), (1024, 255, 512),
-                                   (300, 100, 70), (512, 1536, 1024), (15360, 512, 1536)])
+                                   (300, 100, 70), (512, 1536, 1024), (15360, 512, 1536), (512, 1536, 15360), (100, 512, 15360),
+                                   (255, 512, 4100), (136, 72, 1000)])
 def test_gemm_bf16_tensor_core(mode, M, N, K):
     """tcgen05 path: inputs are rounded to bf16 exactly once, products accumulate in fp32 -> must match a float64 product of
     the bf16-rounded inputs to fp32 accumulation accuracy, and the fp32 product to the north-star's 2e-2."""
