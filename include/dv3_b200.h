@@ -86,6 +86,34 @@ int dv3_scan_carry(int B, int D, int S, const float* first, const float* dz_prev
                    const float* dh_b, int ldb, float* dz_dst, int ldzd, float* dh_dst, int ldhd, void* stream);
 int dv3_mask_shift_actions(int T, int B, int A, const float* actions, const float* first, float* out, int ldo, void* stream);
 
+/* ---- persistent RSSM observe scan: the whole loop dreamer_v3.py:122-129 over RSSM.dynamic (agent.py:350-388) in one
+ * cooperative kernel (posterior path; the prior head is batched outside).  B <= 16.  Returns DV3_ERR_UNSUPPORTED when the
+ * shape does not fit the kernel's plan (caller then uses the per-step entry points above). */
+typedef struct Dv3ScanFwdArgs {
+  int T, B, G, Kc, D, U, Hh, A, E;
+  float unimix;
+  const float* Wmlp; int ld_wmlp; const float* g_mlp; const float* b_mlp;     /* RecurrentModel.mlp: [U, G*Kc+A] + LN(1e-3) */
+  const float* Wgru; int ld_wgru; const float* g_gru; const float* b_gru;     /* LayerNormGRUCell: [3D, D+U] + LN(1e-5)     */
+  const float* Wr0; int ld_wr0; const float* g_r; const float* b_r;           /* representation layer 0: [Hh, D+E] + LN      */
+  const float* Wr1; int ld_wr1; const float* br1;                             /* representation head: [G*Kc, Hh] + bias      */
+  const float* eW;            /* [T*B, Hh] = e_t . Wr0[:, D:]^T + b_r0 (hoisted out of the scan)                            */
+  const float* first;         /* [T*B] is_first, row 0 forced to 1                                                           */
+  const float* u_post;        /* [T*B, G] uniforms of the posterior draws                                                    */
+  const int* forced_idx;      /* [T*B, G] teacher-forced draws, or NULL                                                      */
+  const int* zreset_idx;      /* [G] mode(unimix(transition(0)))                                                             */
+  float* x_mlp; int ld_xmlp;  /* [T*B, G*Kc+A]: one-hot z_in written, masked previous action read                           */
+  float* feat_pre; float* feat_mean; float* feat_rstd;
+  float* x_gru; int ld_xgru;  /* [T*B, D+U] = [h_in, feat]                                                                   */
+  float* gates_pre; float* gru_mean; float* gru_rstd;
+  float* x_rep; int ld_xrep;  /* [T*B, D+E]: h_t written to the first D columns                                              */
+  float* hidr_pre; float* hidr; float* hidr_mean; float* hidr_rstd;
+  float* post_raw; float* post_logits; int* post_idx;
+  float* latent; int ld_lat;  /* [T*B, G*Kc+D]: one-hot z_t written to the first G*Kc columns                                */
+  float* scratch; size_t scratch_bytes;
+} Dv3ScanFwdArgs;
+size_t dv3_rssm_observe_fwd_scratch_bytes(void);
+int dv3_rssm_observe_fwd(const Dv3ScanFwdArgs* args, void* stream);
+
 /* ---- categorical: unimix agent.py:390-402/:741-747; ST one-hot sample distribution.py:355-360,:390-393 ---- */
 int dv3_unimix_fwd(int R, int groups, int K, float mix, const float* raw, int ldr, float* logits, int ldo, void* stream);
 int dv3_sample_onehot(int R, int groups, int K, const float* logits, int ldl, const float* u, int ldu, const int* forced,

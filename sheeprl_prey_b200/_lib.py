@@ -33,6 +33,8 @@ SIGNATURES = {
     "dv3_scan_prep": [_i, _i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, _i, c_fp, _i, c_fp],
     "dv3_scan_carry": [_i, _i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_mask_shift_actions": [_i, _i, _i, c_fp, c_fp, c_fp, _i, c_fp],
+    "dv3_rssm_observe_fwd_scratch_bytes": [],
+    "dv3_rssm_observe_fwd": [c_fp, c_fp],
     "dv3_unimix_fwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp],
     "dv3_sample_onehot": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_unimix_bwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
@@ -55,7 +57,28 @@ SIGNATURES = {
     "dv3_fill": [_sz, c_fp, _f, c_fp],
     "dv3_uniform_fill": [_sz, c_fp, _ull, c_fp, c_fp],
 }
-_RESTYPE = {"dv3_col_reduce_scratch_bytes": _sz, "dv3_adam_clip_scratch_bytes": _sz}
+_RESTYPE = {"dv3_col_reduce_scratch_bytes": _sz, "dv3_adam_clip_scratch_bytes": _sz, "dv3_rssm_observe_fwd_scratch_bytes": _sz}
+
+
+class ScanFwdArgs(C.Structure):
+    """Mirror of `Dv3ScanFwdArgs` (include/dv3_b200.h)."""
+    _fields_ = [
+        ("T", _i), ("B", _i), ("G", _i), ("Kc", _i), ("D", _i), ("U", _i), ("Hh", _i), ("A", _i), ("E", _i), ("unimix", _f),
+        ("Wmlp", c_fp), ("ld_wmlp", _i), ("g_mlp", c_fp), ("b_mlp", c_fp),
+        ("Wgru", c_fp), ("ld_wgru", _i), ("g_gru", c_fp), ("b_gru", c_fp),
+        ("Wr0", c_fp), ("ld_wr0", _i), ("g_r", c_fp), ("b_r", c_fp),
+        ("Wr1", c_fp), ("ld_wr1", _i), ("br1", c_fp),
+        ("eW", c_fp), ("first", c_fp), ("u_post", c_fp), ("forced_idx", c_fp), ("zreset_idx", c_fp),
+        ("x_mlp", c_fp), ("ld_xmlp", _i),
+        ("feat_pre", c_fp), ("feat_mean", c_fp), ("feat_rstd", c_fp),
+        ("x_gru", c_fp), ("ld_xgru", _i),
+        ("gates_pre", c_fp), ("gru_mean", c_fp), ("gru_rstd", c_fp),
+        ("x_rep", c_fp), ("ld_xrep", _i),
+        ("hidr_pre", c_fp), ("hidr", c_fp), ("hidr_mean", c_fp), ("hidr_rstd", c_fp),
+        ("post_raw", c_fp), ("post_logits", c_fp), ("post_idx", c_fp),
+        ("latent", c_fp), ("ld_lat", _i),
+        ("scratch", c_fp), ("scratch_bytes", _sz),
+    ]
 
 
 def load_library(path: Optional[str] = None):
@@ -311,6 +334,37 @@ class CudaOps:
     def ema(self, target, src, tau):
         self.launches += 1
         _chk(self.lib.dv3_ema(target.numel(), _p(target), _p(src), tau, self._s()), "dv3_ema")
+
+    # ---------------------------------------------------------------- persistent scan
+    def rssm_observe_fwd(self, eng, forced_post_idx) -> bool:
+        """Whole observe scan in one cooperative launch.  Returns False if the shape is outside the kernel's plan
+        (the engine then runs the per-step composition)."""
+        a = ScanFwdArgs()
+        a.T, a.B, a.G, a.Kc, a.D, a.U, a.Hh, a.A, a.E = eng.T, eng.B, eng.G, eng.K, eng.D, eng.U, eng.Hh, eng.A, eng.E
+        a.unimix = float(eng.cfg.algo.unimix)
+        a.Wmlp, a.ld_wmlp, a.g_mlp, a.b_mlp = _p(eng.Wmlp), eng.Wmlp.stride(0), _p(eng.g_mlp), _p(eng.b_mlp)
+        a.Wgru, a.ld_wgru, a.g_gru, a.b_gru = _p(eng.Wgru), eng.Wgru.stride(0), _p(eng.g_gru), _p(eng.b_gru)
+        a.Wr0, a.ld_wr0, a.g_r, a.b_r = _p(eng.Wr0), eng.Wr0.stride(0), _p(eng.g_r), _p(eng.b_r)
+        a.Wr1, a.ld_wr1, a.br1 = _p(eng.Wr1), eng.Wr1.stride(0), _p(eng.br1)
+        a.eW, a.first, a.u_post = _p(eng.eW), _p(eng.first), _p(eng.u_post)
+        if forced_post_idx is not None:
+            assert forced_post_idx.dtype == torch.int32 and forced_post_idx.is_contiguous()
+        a.forced_idx, a.zreset_idx = _p(forced_post_idx), _p(eng.zreset_idx)
+        a.x_mlp, a.ld_xmlp = _p(eng.x_mlp), eng.x_mlp.stride(0)
+        a.feat_pre, a.feat_mean, a.feat_rstd = _p(eng.feat_pre), _p(eng.feat_mean), _p(eng.feat_rstd)
+        a.x_gru, a.ld_xgru = _p(eng.x_gru), eng.x_gru.stride(0)
+        a.gates_pre, a.gru_mean, a.gru_rstd = _p(eng.gates_pre), _p(eng.gru_mean), _p(eng.gru_rstd)
+        a.x_rep, a.ld_xrep = _p(eng.x_rep), eng.x_rep.stride(0)
+        a.hidr_pre, a.hidr, a.hidr_mean, a.hidr_rstd = _p(eng.hidr_pre), _p(eng.hidr), _p(eng.hidr_mean), _p(eng.hidr_rstd)
+        a.post_raw, a.post_logits, a.post_idx = _p(eng.post_raw), _p(eng.post_logits), _p(eng.post_idx)
+        a.latent, a.ld_lat = _p(eng.latent), eng.latent.stride(0)
+        a.scratch, a.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel() * 4
+        rc = self.lib.dv3_rssm_observe_fwd(C.addressof(a), self._s())
+        if rc == -2:
+            return False
+        _chk(rc, "dv3_rssm_observe_fwd")
+        self.launches += 1
+        return True
 
     # ---------------------------------------------------------------- scan plumbing
     def scan_prep(self, first, h_prev, z_prev, zreset, h_in, z_in):

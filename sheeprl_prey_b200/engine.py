@@ -22,6 +22,7 @@ Restructurings relative to the reference (each keeps results within fp32 round-o
 """
 from __future__ import annotations
 
+import os
 from collections import OrderedDict
 from typing import Dict, List, Optional, Sequence
 
@@ -228,6 +229,8 @@ class DV3Engine:
         self.dgates_pre, self.dln_gru, self.dh_direct, self.dx_gru = z(N, 3 * D), z(N, 3 * D), z(B, D), z(B, D + U)
         self.dfeat_pre, self.dln_feat, self.dz_prev, self.de = z(N, U), z(N, U), z(B, S), z(N, E)
         self.W_r1T, self.W_r0hT, self.W_gruT, self.W_mlpzT = z(Hh, S), z(D, Hh), z(D + U, 3 * D), z(S, U)
+        self.eW = z(N, Hh)                       # e_t . Wr0[:, D:]^T + b_r0 for all t (hoisted out of the scan)
+        self.use_fused_scan = hasattr(ops, "rssm_observe_fwd") and os.environ.get("DV3_FUSED_SCAN", "1") != "0"
         self.metrics = z(16)
         self.u_post = z(T, B, self.G)
         nh = len(self.actions_dim)
@@ -325,8 +328,14 @@ class DV3Engine:
         ops.transpose(self.Wr0[:, :D], self.W_r0hT)
         ops.transpose(self.Wgru, self.W_gruT)
         ops.transpose(self.Wmlp[:, :S], self.W_mlpzT)
-        # a4: observe scan
-        for t in range(T):
+        # a4: observe scan -- one persistent cooperative kernel when the shape fits, else the per-step composition
+        fused = False
+        if self.use_fused_scan:
+            ops.gemm("NT", self.x_rep[:, D:], self.Wr0[:, D:], self.eW, bias=self.br0)
+            fused = ops.rssm_observe_fwd(self, forced_post_idx)
+            if not fused:
+                self.use_fused_scan = False
+        for t in range(0 if not fused else T, T):
             r = slice(t * B, (t + 1) * B)
             rp = slice((t - 1) * B, t * B)
             ops.scan_prep(self.first[t], None if t == 0 else self.x_rep[rp, :D], None if t == 0 else self.latent[rp, :S],

@@ -324,9 +324,13 @@ def test_gemm_bf16_tensor_core(mode, M, N, K):
         exact = ref(Ab, Bb) + bias.double() + (C0.double() if acc else 0)
         ops.gemm(mode, A, B, C1, bias, acc)
         torch.cuda.synchronize()
-        assert rel(C1.double(), exact) < 2e-5, (mode, M, N, K, acc, rel(C1.double(), exact))
         full = ref(A.double(), B.double()) + bias.double() + (C0.double() if acc else 0)
-        assert rel(C1.double(), full) < 2e-2
+        on_tc = N >= 32 and K >= 32 and (M >= 128 or (mode == "TN" and M >= 16 and K >= 2048))   # CudaOps.gemm dispatch
+        if on_tc:
+            assert rel(C1.double(), exact) < 2e-5, (mode, M, N, K, acc, rel(C1.double(), exact))
+            assert rel(C1.double(), full) < 2e-2
+        else:       # small problems stay on the fp32 CUDA-core kernel
+            assert rel(C1.double(), full) < 1e-5
 
 
 def test_gemm_bf16_strided_views():

@@ -218,3 +218,30 @@ def test_step_bf16_tensor_core_mode_within_2e2():
         assert rep[k] < 2e-2, (k, rep)
     for k in ("grad_world_model", "grad_actor", "grad_critic"):
         assert rep[k] < 5e-2, (k, rep)
+
+
+@pytest.mark.parametrize("size,B,T,obs,acts", [("XS", 16, 64, 4, [2]), ("S", 16, 64, 14, [100]), ("S", 5, 9, 14, [7, 3]), ("M", 16, 20, 20, [18])])
+def test_persistent_scan_matches_per_step_composition(cuda_ops, size, B, T, obs, acts):
+    """dv3_rssm_observe_fwd (one cooperative kernel for the whole observe loop) against the per-step kernels: every tensor the
+    backward consumes must agree to fp32 round-off, the sampled indices exactly."""
+    cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=3)
+    od = {"state": obs}
+    params = random_params_like(cfg, od, acts, seed=5)
+    data = _to(harness.synthetic_batch(T, B, od, acts, seed=77, done_p=0.1), DEV)
+    noise = _to(harness.synthetic_noise(T, B, 3, 32, len(acts), seed=78), DEV)
+    engs = []
+    for fused in (False, True):
+        eng = engine_from_params(cfg, od, acts, _dev_params(params), cuda_ops, DEV)
+        eng.use_fused_scan = fused
+        eng.load_batch(data)
+        eng.load_noise(noise)
+        eng.world_forward()
+        torch.cuda.synchronize()
+        assert eng.use_fused_scan == fused, "the persistent kernel refused this shape"
+        engs.append(eng)
+    a, b = engs
+    assert torch.equal(a.post_idx, b.post_idx)
+    assert torch.equal(a.latent[:, :a.S], b.latent[:, :a.S]) and torch.equal(a.x_mlp, b.x_mlp)
+    for name in ("feat_pre", "feat_mean", "feat_rstd", "x_gru", "gates_pre", "gru_mean", "gru_rstd", "x_rep", "hidr_pre", "hidr",
+                 "hidr_mean", "hidr_rstd", "post_raw", "post_logits", "latent", "prior_logits"):
+        assert rel(getattr(b, name), getattr(a, name)) < 3e-6, (name, rel(getattr(b, name), getattr(a, name)))
