@@ -292,6 +292,10 @@ def run_ours(args, rank, world, local_rank):
                 fh.write("shape | launches (2 steps) | avg ms | TFLOP/s\n")
                 for k, c, ms_, tf in rows:
                     fh.write(f"{k} | {c} | {ms_:.4f} | {tf:.1f}\n")
+        phases = eng.timed_step()
+        if os.path.isdir(os.path.join(ROOT, "gpurun_out")):
+            with open(os.path.join(ROOT, "gpurun_out", f"phases_{args.size}_{args.precision}.json"), "w") as fh:
+                json.dump(phases, fh, indent=1)
         big = [(s.elapsed_time(e), f) for (s, e, f, M, N, Kk, mode) in log if M > 32]
         tot_ms, tot_fl = sum(x[0] for x in big), sum(x[1] for x in big)
         all_ms = sum(s.elapsed_time(e) for (s, e, *_r) in log)

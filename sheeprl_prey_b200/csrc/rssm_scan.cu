@@ -21,6 +21,8 @@
 // same buffers the per-op path fills.
 #include "common.cuh"
 #include <cooperative_groups.h>
+#include <stdlib.h>
+#include <stdio.h>
 namespace cg = cooperative_groups;
 
 namespace {
@@ -57,70 +59,120 @@ struct ScanFwdArgs {
   float* post_raw; float* post_logits; int* post_idx;         // [T*B, S], [T*B, S], [T*B, G]
   float* latent; int ld_lat;           // [T*B, S+D]: one-hot z written to the first S columns
   float* lnpart;                       // [gridDim.x][MB][2] scratch (per-CTA mean, M2 of the own gate values)
+  long long* dbg;                      // optional: clock64 stamps of CTA 0 during step t == 1
   // shared-memory plan (floats): which weight slices are resident
   int smem_wmlp, smem_wgru, smem_wr0, smem_wr1;
 };
 
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 
-// acc[r][m] += sum_k w_r[k] * act[m][k] over this lane's k (k = 4*lane + 128*j); w rows are 16 B aligned, K % 4 == 0.
-template <int RB>
-__device__ __forceinline__ void lane_dot(const float* const (&w)[RB], int K, const float* act, int ldact, int lane,
-                                         float (&acc)[RB][MB]) {
-  for (int k = lane * 4; k < K; k += 128) {
-    float4 wv[RB];
+// v[i] (i < 32) per lane -> lane l returns the warp-wide sum of v[l]  (31 shuffles instead of 32 x 5)
+__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {
 #pragma unroll
-    for (int r = 0; r < RB; ++r) wv[r] = ld4(w[r] + k);
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
 #pragma unroll
-    for (int m = 0; m < MB; ++m) {
-      const float4 a = ld4(act + m * ldact + k);
-#pragma unroll
-      for (int r = 0; r < RB; ++r) {
-        acc[r][m] = fmaf(a.x, wv[r].x, acc[r][m]);
-        acc[r][m] = fmaf(a.y, wv[r].y, acc[r][m]);
-        acc[r][m] = fmaf(a.z, wv[r].z, acc[r][m]);
-        acc[r][m] = fmaf(a.w, wv[r].w, acc[r][m]);
-      }
+    for (int j = 0; j < s; ++j) {
+      const float send = up ? v[j] : v[j + s];
+      const float keep = up ? v[j + s] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, s);
     }
   }
+  return v[0];
 }
 
-// rows [0, R) of a weight slice (row stride ldw) times act[MB][K] -> out(r, m) via callback, warp per row pair.
+// rows [0, R) of a weight slice (row stride ldw, 16 B aligned rows, K % 4 == 0) times act[MB][K] (shared memory):
+// one warp per pair of rows, lanes over k (float4), 32 accumulators per lane, transposed reduction; out(r, m, value).
 template <typename F>
 __device__ __forceinline__ void cta_gemv(const float* W, int ldw, int R, int K, const float* act, int ldact, F out) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int r0 = warp * 2; r0 < R; r0 += NW * 2) {
     const bool two = (r0 + 1 < R);
-    float acc[2][MB];
+    const float* w0 = W + (size_t)r0 * ldw;
+    const float* w1 = W + (size_t)(two ? r0 + 1 : r0) * ldw;
+    float acc[32];
 #pragma unroll
-    for (int m = 0; m < MB; ++m) { acc[0][m] = 0.f; acc[1][m] = 0.f; }
-    const float* const w[2] = {W + (size_t)r0 * ldw, W + (size_t)(two ? r0 + 1 : r0) * ldw};
-    lane_dot<2>(w, K, act, ldact, lane, acc);
+    for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+#pragma unroll 2
+    for (int k = lane * 4; k < K; k += 128) {
+      const float4 wa = ld4(w0 + k), wb = ld4(w1 + k);
 #pragma unroll
-    for (int m = 0; m < MB; ++m) {
-      const float v0 = warp_sum(acc[0][m]);
-      const float v1 = warp_sum(acc[1][m]);
-      if (lane == 0) { out(r0, m, v0); if (two) out(r0 + 1, m, v1); }
+      for (int m = 0; m < MB; ++m) {
+        const float4 x = ld4(act + m * ldact + k);
+        acc[m] = fmaf(x.x, wa.x, acc[m]); acc[m] = fmaf(x.y, wa.y, acc[m]);
+        acc[m] = fmaf(x.z, wa.z, acc[m]); acc[m] = fmaf(x.w, wa.w, acc[m]);
+        acc[MB + m] = fmaf(x.x, wb.x, acc[MB + m]); acc[MB + m] = fmaf(x.y, wb.y, acc[MB + m]);
+        acc[MB + m] = fmaf(x.z, wb.z, acc[MB + m]); acc[MB + m] = fmaf(x.w, wb.w, acc[MB + m]);
+      }
+    }
+    const float v = warp_transpose_reduce32(acc, lane);
+    const int r = r0 + (lane >> 4);
+    if (r < R) out(r, lane & 15, v);
+  }
+}
+
+// smem dst[m][0..cols) (row stride ldd) <- global src[m][0..cols) (row stride lds) for m < rows, zero rows up to MB.
+// cols % 4 == 0 and 16 B aligned rows; every thread keeps 8 independent 16 B L2 loads in flight (ld.global.cg: the data
+// was written by other CTAs during this kernel, L1 must be bypassed).
+__device__ __forceinline__ void load_rows_cg(float* dst, int ldd, const float* src, int lds, int rows, int cols) {
+  const int c4 = cols >> 2, n4 = MB * c4;
+  for (int base = 0; base < n4; base += ST * 8) {
+    float4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int i = base + threadIdx.x + j * ST;
+      v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < n4) {
+        const int m = i / c4, k = (i - m * c4) << 2;
+        if (m < rows) v[j] = __ldcg(reinterpret_cast<const float4*>(src + (size_t)m * lds + k));
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int i = base + threadIdx.x + j * ST;
+      if (i < n4) {
+        const int m = i / c4, k = (i - m * c4) << 2;
+        *reinterpret_cast<float4*>(dst + m * ldd + k) = v[j];
+      }
     }
   }
 }
 
-// Row-wise LayerNorm (+SiLU) of buf[MB][U] in shared memory, in place; optional global outputs (written by CTA `writer`).
-__device__ __forceinline__ void smem_ln_silu(float* buf, int ld, int U, int B, const float* __restrict__ gamma,
+// Row-wise LayerNorm + SiLU of buf[MB][U] in shared memory, in place: 16 threads per row, 4-way unrolled passes.
+__device__ __forceinline__ void smem_ln_silu(float* buf, int ld, int U, const float* __restrict__ gamma,
                                              const float* __restrict__ beta, float eps, float* s_mean, float* s_rstd) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int m = warp; m < MB; m += NW) {
-    float* row = buf + m * ld;
-    float s = 0.f;
-    for (int i = lane; i < U; i += 32) s += row[i];
-    const float mu = warp_sum(s) / (float)U;
-    float v = 0.f;
-    for (int i = lane; i < U; i += 32) { const float d = row[i] - mu; v = fmaf(d, d, v); }
-    const float rs = rsqrtf(warp_sum(v) / (float)U + eps);
-    for (int i = lane; i < U; i += 32) row[i] = siluf_((row[i] - mu) * rs * __ldg(gamma + i) + __ldg(beta + i));
-    if (lane == 0) { s_mean[m] = mu; s_rstd[m] = rs; }
+  const int m = threadIdx.x >> 4, sub = threadIdx.x & 15;
+  float* row = buf + m * ld;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  int i = sub;
+  for (; i + 48 < U; i += 64) { s0 += row[i]; s1 += row[i + 16]; s2 += row[i + 32]; s3 += row[i + 48]; }
+  for (; i < U; i += 16) s0 += row[i];
+  float s = (s0 + s1) + (s2 + s3);
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mu = s / (float)U;
+  s0 = s1 = s2 = s3 = 0.f;
+  i = sub;
+  for (; i + 48 < U; i += 64) {
+    const float a0 = row[i] - mu, a1 = row[i + 16] - mu, a2 = row[i + 32] - mu, a3 = row[i + 48] - mu;
+    s0 = fmaf(a0, a0, s0); s1 = fmaf(a1, a1, s1); s2 = fmaf(a2, a2, s2); s3 = fmaf(a3, a3, s3);
   }
+  for (; i < U; i += 16) { const float a0 = row[i] - mu; s0 = fmaf(a0, a0, s0); }
+  float v = (s0 + s1) + (s2 + s3);
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const float rs = rsqrtf(v / (float)U + eps);
+  // SiLU through ex2.approx / rcp.approx: this loop runs redundantly in every CTA on all MB x U values, so it is
+  // instruction-issue bound; the approximations are ~1e-7 absolute, far inside the fp32-mode parity tolerance.
+#pragma unroll 4
+  for (i = sub; i < U; i += 16) {
+    const float x = (row[i] - mu) * rs * __ldg(gamma + i) + __ldg(beta + i);
+    row[i] = __fdividef(x, 1.f + __expf(-x));
+  }
+  if (sub == 0) { s_mean[m] = mu; s_rstd[m] = rs; }
 }
+
+#define DBG(p) do { if (a.dbg && c == 0 && tid == 0 && t == 1) a.dbg[p] = clock64(); } while (0)
 
 __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) {
   cg::grid_group grid = cg::this_grid();
@@ -129,28 +181,30 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
   const int c = blockIdx.x, NC = gridDim.x;
   const int B = a.B, G = a.G, Kc = a.Kc, D = a.D, U = a.U, Hh = a.Hh, A = a.A;
   const int S = G * Kc, KA = S + A, KG = D + U;
-  const int KAp = (KA + 3) & ~3;
+  const int KAp = (KA + 3) & ~3, Ap = A + 4;
 
-  // ---- static partition of the output rows
-  const int ua = (U + NC - 1) / NC, ua0 = min(c * ua, U), ua1 = min(ua0 + ua, U);          // feat rows
-  const int dd = (D + NC - 1) / NC, d0 = min(c * dd, D), d1 = min(d0 + dd, D);             // recurrent units (3 gate rows each)
-  const int hr = (Hh + NC - 1) / NC, hr0 = min(c * hr, Hh), hr1 = min(hr0 + hr, Hh);       // posterior hidden rows
-  const int nA = ua1 - ua0, nD = d1 - d0, nH = hr1 - hr0;
-  const bool owner = c < G;                                                                 // owns categorical c
+  // ---- static partition of the output rows of every in-loop contraction
+  const int ua = (U + NC - 1) / NC, ua0 = min(c * ua, U), nA = min(ua0 + ua, U) - ua0;      // feat rows
+  const int dd = (D + NC - 1) / NC, d0 = min(c * dd, D), nD = min(d0 + dd, D) - d0;         // recurrent units (3 gate rows each)
+  const int hr = (Hh + NC - 1) / NC, hr0 = min(c * hr, Hh), nH = min(hr0 + hr, Hh) - hr0;   // posterior hidden rows
+  const int sr = (S + NC - 1) / NC, sr0 = min(c * sr, S), nS = min(sr0 + sr, S) - sr0;      // posterior logit rows
+  const bool owner = c < G;                                                                  // samples categorical c
 
   // ---- shared memory carve-up (floats; every region 16 B aligned)
   float* sp = smem;
   auto take = [&](int n) { float* p = sp; sp += (n + 3) & ~3; return p; };
   float* act = take(MB * KG);              // [MB][D+U]: h (first D) and feat / hid (from D on)
-  float* acta = take(MB * (A + 4));        // [MB][A] masked previous action
+  float* acta = take(MB * Ap);             // [MB][A] masked previous action
   float* gown = take(3 * max(dd, 1) * MB); // own gate pre-activations [3*nD][MB]
   float* s_stat = take(4 * MB);            // mean / rstd scratch
-  float* s_log = take(MB * Kc);            // owner: raw logits [MB][Kc]
+  float* s_log = take(MB * Kc);            // owner: logits / probs [MB][Kc]
   int* s_idx = reinterpret_cast<int*>(take(MB * G));   // z indices of the previous step [MB][G]
+  int* s_reset = reinterpret_cast<int*>(take(MB));
+  float* lnp = take(NC * MB * 2);          // staging of every CTA's LN partials
   float* w_mlp_s = a.smem_wmlp ? take(max(ua, 1) * KAp) : nullptr;
   float* w_gru_s = a.smem_wgru ? take(3 * max(dd, 1) * KG) : nullptr;
   float* w_r0_s = a.smem_wr0 ? take(max(hr, 1) * D) : nullptr;
-  float* w_r1_s = a.smem_wr1 ? take(Kc * Hh) : nullptr;
+  float* w_r1_s = a.smem_wr1 ? take(max(sr, 1) * Hh) : nullptr;
 
   // ---- preload the resident weight slices
   if (w_mlp_s)
@@ -162,61 +216,92 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
     }
   if (w_r0_s)
     for (int i = tid; i < nH * D; i += ST) { const int r = i / D, k = i % D; w_r0_s[i] = __ldg(a.Wr0 + (size_t)(hr0 + r) * a.ld_wr0 + k); }
-  if (w_r1_s && owner)
-    for (int i = tid; i < Kc * Hh; i += ST) { const int r = i / Hh, k = i % Hh; w_r1_s[i] = __ldg(a.Wr1 + (size_t)(c * Kc + r) * a.ld_wr1 + k); }
+  if (w_r1_s)
+    for (int i = tid; i < nS * Hh; i += ST) { const int r = i / Hh, k = i % Hh; w_r1_s[i] = __ldg(a.Wr1 + (size_t)(sr0 + r) * a.ld_wr1 + k); }
   for (int i = tid; i < MB * KG; i += ST) act[i] = 0.f;
-  for (int i = tid; i < MB * (A + 4); i += ST) acta[i] = 0.f;
+  for (int i = tid; i < MB * Ap; i += ST) acta[i] = 0.f;
   __syncthreads();
 
   for (int t = 0; t < a.T; ++t) {
     const int row0 = t * B;
+    DBG(0);
     // ================= P0: reset masking, previous z indices, previous action =================
-    for (int i = tid; i < MB * G; i += ST) {
-      const int m = i / G, g = i % G;
-      int v = 0;
-      if (m < B) {
-        const bool reset = (t == 0) || (__ldg(a.first + row0 + m) != 0.f);
-        v = reset ? __ldg(a.zreset_idx + g) : __ldcg(a.post_idx + (size_t)(row0 - B + m) * G + g);
+    {
+      int pv[2] = {0, 0};
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {            // G * MB <= 2 * ST is checked by the host wrapper
+        const int i = tid + j * ST;
+        if (i < MB * G && t > 0) { const int m = i / G, g = i - m * G; if (m < B) pv[j] = __ldcg(a.post_idx + (size_t)(row0 - B + m) * G + g); }
       }
-      s_idx[i] = v;
+      float av[8];
+      const int nact = B * A;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i = tid + j * ST;
+        av[j] = 0.f;
+        if (i < nact) { const int m = i / A, k = i - m * A; av[j] = __ldg(a.x_mlp + (size_t)(row0 + m) * a.ld_xmlp + S + k); }
+      }
+      if (tid < MB) s_reset[tid] = (tid >= B || t == 0 || __ldg(a.first + row0 + tid) != 0.f) ? 1 : 0;
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int i = tid + j * ST;
+        if (i < MB * G) { const int m = i / G, g = i - m * G; s_idx[i] = s_reset[m] ? __ldg(a.zreset_idx + g) : pv[j]; }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const int i = tid + j * ST; if (i < nact) { const int m = i / A, k = i - m * A; acta[m * Ap + k] = av[j]; } }
+      for (int i = tid + 8 * ST; i < nact; i += ST) { const int m = i / A, k = i - m * A; acta[m * Ap + k] = __ldg(a.x_mlp + (size_t)(row0 + m) * a.ld_xmlp + S + k); }
+      for (int m = 0; m < MB; ++m)
+        if (s_reset[m]) for (int k = tid; k < D; k += ST) act[m * KG + k] = 0.f;   // else act[:, :D] holds h'_{t-1} (loaded in P4)
     }
-    for (int i = tid; i < MB * D; i += ST) {
-      const int m = i / D, k = i % D;
-      const bool reset = (m >= B) || (t == 0) || (__ldg(a.first + row0 + m) != 0.f);
-      if (reset) act[m * KG + k] = 0.f;        // else act[:, :D] already holds h'_{t-1} (loaded in P4 of the previous step)
-    }
-    for (int i = tid; i < B * A; i += ST) { const int m = i / A, k = i % A; acta[m * (A + 4) + k] = __ldg(a.x_mlp + (size_t)(row0 + m) * a.ld_xmlp + S + k); }
     __syncthreads();
+    DBG(11);
     // saved inputs of the step: dense one-hot z_in and h_in (column ranges spread over the CTAs)
     for (int i = c * ST + tid; i < B * S; i += NC * ST) {
-      const int m = i / S, s = i % S;
-      a.x_mlp[(size_t)(row0 + m) * a.ld_xmlp + s] = (s_idx[m * G + s / Kc] == (s % Kc)) ? 1.f : 0.f;
+      const int m = i / S, s = i - m * S, g = s / Kc;
+      a.x_mlp[(size_t)(row0 + m) * a.ld_xmlp + s] = (s_idx[m * G + g] == (s - g * Kc)) ? 1.f : 0.f;
     }
-    for (int i = c * ST + tid; i < B * D; i += NC * ST) { const int m = i / D, k = i % D; a.x_gru[(size_t)(row0 + m) * a.ld_xgru + k] = act[m * KG + k]; }
+    for (int i = c * ST + tid; i < B * D; i += NC * ST) { const int m = i / D, k = i - m * D; a.x_gru[(size_t)(row0 + m) * a.ld_xgru + k] = act[m * KG + k]; }
+    DBG(12);
 
-    // ================= P1: feat_pre slice (one-hot gather + action part) =================
-    for (int task = warp; task < nA * MB; task += NW) {
-      const int r = task / MB, m = task % MB;
-      if (m >= B) continue;
-      const float* wrow = w_mlp_s ? (w_mlp_s + r * KAp) : (a.Wmlp + (size_t)(ua0 + r) * a.ld_wmlp);
-      float s = 0.f;
-      for (int g = lane; g < G; g += 32) s += wrow[g * Kc + s_idx[m * G + g]];
-      for (int k = lane; k < A; k += 32) s = fmaf(wrow[S + k], acta[m * (A + 4) + k], s);
-      s = warp_sum(s);
-      if (lane == 0) a.feat_pre[(size_t)(row0 + m) * U + ua0 + r] = s;
+    // ================= P1: feat_pre slice (one-hot gather + action part), one warp per pair of rows ================
+    for (int r0 = warp * 2; r0 < nA; r0 += NW * 2) {
+      const bool two = r0 + 1 < nA;
+      const float* wr0 = w_mlp_s ? (w_mlp_s + r0 * KAp) : (a.Wmlp + (size_t)(ua0 + r0) * a.ld_wmlp);
+      const float* wr1 = two ? (w_mlp_s ? (w_mlp_s + (r0 + 1) * KAp) : (a.Wmlp + (size_t)(ua0 + r0 + 1) * a.ld_wmlp)) : wr0;
+      float acc[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+      for (int g = lane; g < G; g += 32) {
+#pragma unroll
+        for (int m = 0; m < MB; ++m) {
+          const int col = g * Kc + s_idx[m * G + g];
+          acc[m] += wr0[col];
+          acc[MB + m] += wr1[col];
+        }
+      }
+      for (int k = lane; k < A; k += 32) {
+        const float wa = wr0[S + k], wb = wr1[S + k];
+#pragma unroll
+        for (int m = 0; m < MB; ++m) { const float x = acta[m * Ap + k]; acc[m] = fmaf(wa, x, acc[m]); acc[MB + m] = fmaf(wb, x, acc[MB + m]); }
+      }
+      const float v = warp_transpose_reduce32(acc, lane);
+      const int r = r0 + (lane >> 4), m = lane & 15;
+      if (r < nA && m < B) a.feat_pre[(size_t)(row0 + m) * U + ua0 + r] = v;
     }
+    DBG(1);
     grid.sync();
 
     // ================= P2: feat = SiLU(LN(feat_pre)); own GRU gate rows =================
-    for (int i = tid; i < MB * U; i += ST) {
-      const int m = i / U, k = i % U;
-      act[m * KG + D + k] = (m < B) ? __ldcg(a.feat_pre + (size_t)(row0 + m) * U + k) : 0.f;
-    }
+    load_rows_cg(act + D, KG, a.feat_pre + (size_t)row0 * U, U, B, U);
     __syncthreads();
-    smem_ln_silu(act + D, KG, U, B, a.g_mlp, a.b_mlp, 1e-3f, s_stat, s_stat + MB);
+    DBG(2);
+    smem_ln_silu(act + D, KG, U, a.g_mlp, a.b_mlp, 1e-3f, s_stat, s_stat + MB);
     __syncthreads();
+    DBG(13);
     if (c == 0 && tid < B) { a.feat_mean[row0 + tid] = s_stat[tid]; a.feat_rstd[row0 + tid] = s_stat[MB + tid]; }
-    for (int i = c * ST + tid; i < B * U; i += NC * ST) { const int m = i / U, k = i % U; a.x_gru[(size_t)(row0 + m) * a.ld_xgru + D + k] = act[m * KG + D + k]; }
+    for (int i = c * ST + tid; i < B * U; i += NC * ST) { const int m = i / U, k = i - m * U; a.x_gru[(size_t)(row0 + m) * a.ld_xgru + D + k] = act[m * KG + D + k]; }
+    DBG(14);
     if (w_gru_s) {
       cta_gemv(w_gru_s, KG, 3 * nD, KG, act, KG, [&](int rl, int m, float v) { gown[rl * MB + m] = v; });
     } else {
@@ -225,11 +310,12 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
                  [&](int dl, int m, float v) { gown[(gate * nD + dl) * MB + m] = v; });
     }
     __syncthreads();
+    DBG(15);
     for (int i = tid; i < 3 * nD * B; i += ST) {
-      const int rl = i / B, m = i % B, gate = rl / nD, dl = rl % nD;
+      const int rl = i / B, m = i - rl * B, gate = rl / nD, dl = rl - gate * nD;
       a.gates_pre[(size_t)(row0 + m) * 3 * D + gate * D + d0 + dl] = gown[rl * MB + m];
     }
-    if (tid < MB) {   // Chan partials of the own 3*nD values of row m
+    if (tid < MB) {   // Chan partials (mean, M2) of the own 3*nD values of row m
       const int n = 3 * nD;
       float mu = 0.f, m2 = 0.f;
       if (n > 0) {
@@ -240,29 +326,46 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
       a.lnpart[((size_t)c * MB + tid) * 2 + 0] = mu;
       a.lnpart[((size_t)c * MB + tid) * 2 + 1] = m2;
     }
+    DBG(3);
     grid.sync();
 
     // ================= P3: LN statistics of the gate vector, gates, h'[own d] =================
-    for (int m = warp; m < MB; m += NW) {
+    {   // all partials (NC x MB x 2 floats) into shared memory with every load in flight at once
+      const int n4 = NC * MB * 2 / 4;
+      for (int base = 0; base < n4; base += ST * 8) {
+        float4 v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const int i = base + tid + j * ST; if (i < n4) v[j] = __ldcg(reinterpret_cast<const float4*>(a.lnpart) + i); }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const int i = base + tid + j * ST; if (i < n4) reinterpret_cast<float4*>(lnp)[i] = v[j]; }
+      }
+    }
+    __syncthreads();
+    DBG(4);
+    {   // 16 threads per row: mean = sum n_c mean_c / 3D ; M2 = sum (M2_c + n_c (mean_c - mean)^2)
+      const int m = tid >> 4, sub = tid & 15;
       float sw = 0.f;
-      for (int cc = lane; cc < NC; cc += 32) {
-        const int n = 3 * (min(min(cc * dd, D) + dd, D) - min(cc * dd, D));
-        sw += (float)n * __ldcg(a.lnpart + ((size_t)cc * MB + m) * 2);
+      for (int cc = sub; cc < NC; cc += 16) {
+        const int lo = min(cc * dd, D);
+        sw += (float)(3 * (min(lo + dd, D) - lo)) * lnp[(cc * MB + m) * 2];
       }
-      const float mean = warp_sum(sw) / (float)(3 * D);
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) sw += __shfl_xor_sync(0xffffffffu, sw, o);
+      const float mean = sw / (float)(3 * D);
       float sm2 = 0.f;
-      for (int cc = lane; cc < NC; cc += 32) {
-        const int n = 3 * (min(min(cc * dd, D) + dd, D) - min(cc * dd, D));
-        const float dm = __ldcg(a.lnpart + ((size_t)cc * MB + m) * 2) - mean;
-        sm2 += __ldcg(a.lnpart + ((size_t)cc * MB + m) * 2 + 1) + (float)n * dm * dm;
+      for (int cc = sub; cc < NC; cc += 16) {
+        const int lo = min(cc * dd, D);
+        const float dm = lnp[(cc * MB + m) * 2] - mean;
+        sm2 += lnp[(cc * MB + m) * 2 + 1] + (float)(3 * (min(lo + dd, D) - lo)) * dm * dm;
       }
-      const float var = warp_sum(sm2) / (float)(3 * D);
-      if (lane == 0) { s_stat[m] = mean; s_stat[MB + m] = rsqrtf(var + 1e-5f); }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) sm2 += __shfl_xor_sync(0xffffffffu, sm2, o);
+      if (sub == 0) { s_stat[m] = mean; s_stat[MB + m] = rsqrtf(sm2 / (float)(3 * D) + 1e-5f); }
     }
     __syncthreads();
     if (c == 0 && tid < B) { a.gru_mean[row0 + tid] = s_stat[tid]; a.gru_rstd[row0 + tid] = s_stat[MB + tid]; }
     for (int i = tid; i < nD * B; i += ST) {
-      const int dl = i / B, m = i % B, d = d0 + dl;
+      const int dl = i / B, m = i - dl * B, d = d0 + dl;
       const float mu = s_stat[m], rs = s_stat[MB + m];
       const float r = sigmoidf_((gown[(0 * nD + dl) * MB + m] - mu) * rs * __ldg(a.g_gru + d) + __ldg(a.b_gru + d));
       const float cp = (gown[(1 * nD + dl) * MB + m] - mu) * rs * __ldg(a.g_gru + D + d) + __ldg(a.b_gru + D + d);
@@ -271,14 +374,13 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
       const float h = act[m * KG + d];
       a.x_rep[(size_t)(row0 + m) * a.ld_xrep + d] = u * cd + (1.f - u) * h;
     }
+    DBG(5);
     grid.sync();
 
     // ================= P4: h' (all rows) -> own posterior-hidden rows =================
-    for (int i = tid; i < MB * D; i += ST) {
-      const int m = i / D, k = i % D;
-      act[m * KG + k] = (m < B) ? __ldcg(a.x_rep + (size_t)(row0 + m) * a.ld_xrep + k) : 0.f;
-    }
+    load_rows_cg(act, KG, a.x_rep + (size_t)row0 * a.ld_xrep, a.ld_xrep, B, D);
     __syncthreads();
+    DBG(6);
     {
       const float* W = w_r0_s ? w_r0_s : (a.Wr0 + (size_t)hr0 * a.ld_wr0);
       const int ldw = w_r0_s ? D : a.ld_wr0;
@@ -286,27 +388,33 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
         if (m < B) a.hidr_pre[(size_t)(row0 + m) * Hh + hr0 + r] = v + __ldg(a.eW + (size_t)(row0 + m) * Hh + hr0 + r);
       });
     }
+    DBG(7);
+    grid.sync();
+    DBG(8);
+
+    // ================= P5a: hid = SiLU(LN(hidr_pre)) (every CTA); own posterior logit rows =================
+    {
+      float* hid = act + D;   // feat is no longer needed in this step
+      load_rows_cg(hid, KG, a.hidr_pre + (size_t)row0 * Hh, Hh, B, Hh);
+      __syncthreads();
+      DBG(16);
+      smem_ln_silu(hid, KG, Hh, a.g_r, a.b_r, 1e-5f, s_stat + 2 * MB, s_stat + 3 * MB);
+      __syncthreads();
+      DBG(17);
+      if (c == 0 && tid < B) { a.hidr_mean[row0 + tid] = s_stat[2 * MB + tid]; a.hidr_rstd[row0 + tid] = s_stat[3 * MB + tid]; }
+      for (int i = c * ST + tid; i < B * Hh; i += NC * ST) { const int m = i / Hh, k = i - m * Hh; a.hidr[(size_t)(row0 + m) * Hh + k] = hid[m * KG + k]; }
+      const float* W = w_r1_s ? w_r1_s : (a.Wr1 + (size_t)sr0 * a.ld_wr1);
+      const int ldw = w_r1_s ? Hh : a.ld_wr1;
+      cta_gemv(W, ldw, nS, Hh, hid, KG, [&](int r, int m, float v) {
+        if (m < B) a.post_raw[(size_t)(row0 + m) * S + sr0 + r] = v + __ldg(a.br1 + sr0 + r);
+      });
+    }
+    DBG(18);
     grid.sync();
 
-    // ================= P5: categorical c: hid, logits, unimix, sample =================
+    // ================= P5b: CTA c < G samples categorical c of every batch row =================
     if (owner) {
-      float* hid = act + D;   // feat is no longer needed in this step
-      for (int i = tid; i < MB * Hh; i += ST) {
-        const int m = i / Hh, k = i % Hh;
-        hid[m * KG + k] = (m < B) ? __ldcg(a.hidr_pre + (size_t)(row0 + m) * Hh + k) : 0.f;
-      }
-      __syncthreads();
-      smem_ln_silu(hid, KG, Hh, B, a.g_r, a.b_r, 1e-5f, s_stat + 2 * MB, s_stat + 3 * MB);
-      __syncthreads();
-      if (c == 0) {
-        if (tid < B) { a.hidr_mean[row0 + tid] = s_stat[2 * MB + tid]; a.hidr_rstd[row0 + tid] = s_stat[3 * MB + tid]; }
-        for (int i = tid; i < B * Hh; i += ST) { const int m = i / Hh, k = i % Hh; a.hidr[(size_t)(row0 + m) * Hh + k] = hid[m * KG + k]; }
-      }
-      {
-        const float* W = w_r1_s ? w_r1_s : (a.Wr1 + (size_t)(c * Kc) * a.ld_wr1);
-        const int ldw = w_r1_s ? Hh : a.ld_wr1;
-        cta_gemv(W, ldw, Kc, Hh, hid, KG, [&](int r, int m, float v) { s_log[m * Kc + r] = v + __ldg(a.br1 + c * Kc + r); });
-      }
+      for (int i = tid; i < B * Kc; i += ST) { const int m = i / Kc, k = i - m * Kc; s_log[m * Kc + k] = __ldcg(a.post_raw + (size_t)(row0 + m) * S + c * Kc + k); }
       __syncthreads();
       // one warp per batch row: softmax -> unimix -> log -> normalise -> inverse CDF
       for (int m = warp; m < B; m += NW) {
@@ -320,7 +428,6 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
         float mx2 = -INFINITY;
         for (int k = lane; k < Kc; k += 32) {
           const float raw = s_log[m * Kc + k];
-          a.post_raw[orow * S + c * Kc + k] = raw;
           float lu = raw;
           if (a.unimix > 0.f) {
             const float p = (1.f - a.unimix) * (expf(raw - mx) / se) + a.unimix / (float)Kc;
@@ -351,6 +458,7 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
         } else if (lane == 0) {
           const float uu = __ldg(a.u_post + orow * G + c);
           float cs = 0.f;
+#pragma unroll 8
           for (int k = 0; k < Kc; ++k) { cs += s_log[m * Kc + k]; choice += (cs <= uu) ? 1 : 0; }
           if (choice > Kc - 1) choice = Kc - 1;
         }
@@ -359,7 +467,9 @@ __global__ void __launch_bounds__(ST, 1) rssm_observe_fwd_kernel(ScanFwdArgs a) 
         for (int k = lane; k < Kc; k += 32) a.latent[orow * a.ld_lat + c * Kc + k] = (k == choice) ? 1.f : 0.f;
       }
     }
+    DBG(9);
     grid.sync();
+    DBG(10);
   }
 }
 
@@ -402,7 +512,7 @@ int dv3_rssm_observe_fwd(const Dv3ScanFwdArgs* h, void* stream_) {
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   int NC = sms;
-  if (NC < h->G) return DV3_ERR_UNSUPPORTED;       // one CTA per categorical in P5
+  if (NC < h->G || h->G * MB > 2 * ST || ((NC * MB * 2) & 3)) return DV3_ERR_UNSUPPORTED;   // one CTA per categorical in P5b
   if (NC > 1024) NC = 1024;
   if (h->scratch_bytes < (size_t)NC * MB * 2 * sizeof(float)) return DV3_ERR_SCRATCH;
 
@@ -423,18 +533,21 @@ int dv3_rssm_observe_fwd(const Dv3ScanFwdArgs* h, void* stream_) {
   a.post_raw = h->post_raw; a.post_logits = h->post_logits; a.post_idx = h->post_idx;
   a.latent = h->latent; a.ld_lat = h->ld_lat;
   a.lnpart = h->scratch;
+  a.dbg = (h->scratch_bytes >= (size_t)(NC * MB * 2 + 64) * sizeof(float) && getenv("DV3_SCAN_DEBUG"))
+              ? reinterpret_cast<long long*>(h->scratch + NC * MB * 2 + ((NC * MB * 2) & 1)) : nullptr;
 
   // shared-memory plan: fixed buffers first, then the weight slices in order of benefit while they fit
   auto r4 = [](long long n) { return (n + 3) & ~3LL; };
   const int KA = S + h->A, KAp = (KA + 3) & ~3;
   const int ua = (h->U + NC - 1) / NC, dd = (h->D + NC - 1) / NC, hr = (h->Hh + NC - 1) / NC;
   long long used = r4((long long)MB * KG) + r4((long long)MB * (h->A + 4)) + r4(3LL * (dd > 1 ? dd : 1) * MB) + r4(4 * MB) +
-                   r4((long long)MB * h->Kc) + r4((long long)MB * h->G);
+                   r4((long long)MB * h->Kc) + r4((long long)MB * h->G) + r4(MB) + r4((long long)NC * MB * 2);
   const long long budget = (long long)max_smem / 4 - 64;
   const long long n_gru = r4(3LL * (dd > 1 ? dd : 1) * KG), n_mlp = r4((long long)(ua > 1 ? ua : 1) * KAp),
-                  n_r0 = r4((long long)(hr > 1 ? hr : 1) * h->D), n_r1 = r4((long long)h->Kc * h->Hh);
+                  n_r0 = r4((long long)(hr > 1 ? hr : 1) * h->D), n_r1 = r4((long long)(((S + NC - 1) / NC) > 1 ? ((S + NC - 1) / NC) : 1) * h->Hh);
   a.smem_wgru = a.smem_wmlp = a.smem_wr0 = a.smem_wr1 = 0;
   if (used > budget) return DV3_ERR_UNSUPPORTED;
+  const long long fixed_used = used;
   if (used + n_gru <= budget) { a.smem_wgru = 1; used += n_gru; }
   if (used + n_mlp <= budget) { a.smem_wmlp = 1; used += n_mlp; }
   if (used + n_r0 <= budget) { a.smem_wr0 = 1; used += n_r0; }
@@ -443,6 +556,9 @@ int dv3_rssm_observe_fwd(const Dv3ScanFwdArgs* h, void* stream_) {
     // gather path reads scalars, so unaligned rows are fine; nothing to check
   }
   const size_t smem_bytes = (size_t)used * 4 + 64;
+  if (getenv("DV3_SCAN_DEBUG"))
+    fprintf(stderr, "[dv3 scan] NC=%d fixed=%lld KB budget=%lld KB resident: gru=%d mlp=%d r0=%d r1=%d total=%zu KB\n", NC,
+            fixed_used * 4 / 1024, budget * 4 / 1024, a.smem_wgru, a.smem_wmlp, a.smem_wr0, a.smem_wr1, smem_bytes / 1024);
   e = cudaFuncSetAttribute(rssm_observe_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return (int)e;
   int occ = 0;

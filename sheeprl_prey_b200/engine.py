@@ -521,6 +521,32 @@ class DV3Engine:
         self.imagine(None if forced is None else forced.get("imagine"))
         self.behaviour()
 
+    def timed_step(self) -> Dict[str, float]:
+        """One eager step with CUDA events between the phases (diagnostics for bench.py / DESIGN.md; milliseconds)."""
+        w = self.cfg.algo.world_model
+        marks = []
+
+        def mark(name):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(torch.cuda.current_stream(self.device))
+            marks.append((name, e))
+
+        mark("start")
+        self.world_forward()
+        mark("world_forward (encoder, observe scan, prior head, decoder/reward/continue heads)")
+        self.world_losses()
+        mark("world_losses")
+        self.world_backward()
+        mark("world_backward (heads, prior head, reverse scan, weight grads, encoder)")
+        self._optimize(self.wm, "world", w.clip_gradients, "Grads/world_model")
+        mark("world clip+Adam")
+        self.imagine()
+        mark("imagination rollout (H steps x [GRU, prior, sample, actor])")
+        self.behaviour()
+        mark("behaviour (value/reward/continue heads, lambda, moments, actor+critic loss/backward/Adam)")
+        torch.cuda.synchronize(self.device)
+        return {marks[i][0]: marks[i - 1][1].elapsed_time(marks[i][1]) for i in range(1, len(marks))}
+
     def update_target(self, tau: float) -> None:
         self.ops.ema(self.target.flat, self.critic.flat, tau)
 

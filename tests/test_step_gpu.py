@@ -244,4 +244,4 @@ def test_persistent_scan_matches_per_step_composition(cuda_ops, size, B, T, obs,
     assert torch.equal(a.latent[:, :a.S], b.latent[:, :a.S]) and torch.equal(a.x_mlp, b.x_mlp)
     for name in ("feat_pre", "feat_mean", "feat_rstd", "x_gru", "gates_pre", "gru_mean", "gru_rstd", "x_rep", "hidr_pre", "hidr",
                  "hidr_mean", "hidr_rstd", "post_raw", "post_logits", "latent", "prior_logits"):
-        assert rel(getattr(b, name), getattr(a, name)) < 3e-6, (name, rel(getattr(b, name), getattr(a, name)))
+        assert rel(getattr(b, name), getattr(a, name)) < 1e-5, (name, rel(getattr(b, name), getattr(a, name)))
