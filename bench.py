@@ -32,7 +32,16 @@ WORKLOADS = {
     # BASELINE.json configs[0]: DreamerV3 XS, CartPole-v1 (Box(4,), Discrete(2)) -- the reference's CPU-runnable case
     "XS": dict(size="XS", obs={"state": 4}, actions=[2], desc="DreamerV3-XS CartPole-v1 vector obs 4 / Discrete(2)"),
 }
-GFLOP_PER_STEP = {"S": 542.0, "XS": 174.9}   # SURVEY.md section 8(d), reference op count (discrete actions)
+WORKLOADS["M"] = dict(size="M", obs={"rgb": (3, 64, 64)}, actions=[18], desc="DreamerV3-M synthetic 64x64x3 pixel obs (Atari-shaped) / Discrete(18)")
+GFLOP_PER_STEP = {"S": 542.0, "XS": 174.9, "M": 1913.4}   # SURVEY.md section 8(d), reference op count (discrete actions)
+
+
+def cfg_for(wl, B, T, H):
+    from sheeprl_prey_b200.configs import make_cfg
+
+    cnn = tuple(k for k, d in wl["obs"].items() if not isinstance(d, int))
+    mlp = tuple(k for k, d in wl["obs"].items() if isinstance(d, int))
+    return make_cfg(wl["size"], batch_size=B, sequence_length=T, horizon=H, cnn_keys=cnn, mlp_keys=mlp)
 
 
 class Fab:
@@ -118,7 +127,7 @@ def cpu_reference(workload: str, steps: int, warmup: int):
     wl = WORKLOADS[workload]
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    cfg = make_cfg(wl["size"], batch_size=16, sequence_length=64, horizon=15)
+    cfg = cfg_for(wl, 16, 64, 15)
     params = random_params_like(cfg, wl["obs"], wl["actions"], seed=0)
     tr = O.OracleTrainer(cfg, wl["obs"], wl["actions"], params["wm"], params["actor"], params["critic"], params["target"])
     data = harness.synthetic_batch(64, 16, wl["obs"], wl["actions"], seed=1234)
@@ -153,7 +162,12 @@ def synthetic_steps(L, n_envs, obs, actions, seed):
     import torch
 
     g = torch.Generator().manual_seed(seed)
-    d = {k: torch.randn(L, n_envs, n, generator=g).clamp_(-5, 5) for k, n in obs.items()}
+    d = {}
+    for k, n in obs.items():
+        if isinstance(n, int):
+            d[k] = torch.randn(L, n_envs, n, generator=g).clamp_(-5, 5)
+        else:
+            d[k] = torch.randint(0, 256, (L, n_envs, *n), generator=g, dtype=torch.uint8)
     d["actions"] = torch.cat([torch.nn.functional.one_hot(torch.randint(0, a, (L, n_envs), generator=g), a).float() for a in actions], -1)
     d["rewards"] = torch.randn(L, n_envs, 1, generator=g)
     dones = (torch.rand(L, n_envs, 1, generator=g) < 1 / 200).float()
@@ -177,10 +191,10 @@ def run_ours(args, rank, world, local_rank):
         dist.init_process_group("nccl", device_id=dev)
     wl = WORKLOADS[args.size]
     B, T, H = 16, 64, 15
-    cfg = make_cfg(wl["size"], batch_size=B, sequence_length=T, horizon=H)
+    cfg = cfg_for(wl, B, T, H)
     fab = Fab(dev, world, rank)
     torch.manual_seed(0)                                    # identical initial weights on every rank
-    wm, actor, critic, target = build_models(fab, wl["actions"], False, cfg, ObsSpace({k: (d,) for k, d in wl["obs"].items()}))
+    wm, actor, critic, target = build_models(fab, wl["actions"], False, cfg, ObsSpace({k: ((d,) if isinstance(d, int) else d) for k, d in wl["obs"].items()}))
     a = cfg.algo
     wo = torch.optim.Adam(wm.parameters(), lr=a.world_model.optimizer.lr, eps=a.world_model.optimizer.eps)
     ao = torch.optim.Adam(actor.parameters(), lr=a.actor.optimizer.lr, eps=a.actor.optimizer.eps)
@@ -190,9 +204,11 @@ def run_ours(args, rank, world, local_rank):
 
     # per-rank replay shard, device resident, ring full with the write head mid-ring
     n_envs, size = 4, args.buffer
+    if any(not isinstance(d, int) for d in wl["obs"].values()):
+        size = min(size, 16384)          # pixel rows are 12 KB: keep the synthetic fill quick (ring is still > L2 and full)
     rb = AsyncReplayBuffer(size, n_envs, device=dev, sequential=True)
     torch.manual_seed(1234 + rank)
-    chunk = 8192
+    chunk = 8192 if size > 16384 else 2048
     filled = 0
     while filled < size + size // 2:
         L = min(chunk, size + size // 2 - filled)

@@ -72,6 +72,21 @@ int dv3_col_reduce(int M, int U, const float* d, int ldd, const float* x, int ld
 int dv3_col_reduce_noalloc(int M, int U, const float* d, int ldd, const float* x, int ldx, const float* mean, const float* rstd,
                            float* out_a, float* out_b, void* stream);
 
+/* ---- pixel encoder / decoder: CNNEncoder agent.py:28-80, CNNDecoder agent.py:136-206, LayerNormChannelLast
+ * utils/model.py:225-235.  Activations are channel-last; k = tap*C + c with tap = kh*4 + kw; the contractions run on
+ * dv3_gemm_*: Conv2d(k4,s2,p1) = im2col + GEMM, ConvTranspose2d(k4,s2,p1) = GEMM + col2im (and vice versa backward). */
+int dv3_im2col_k4s2p1(int N, int H, int W, int C, const float* x, float* col, void* stream);
+int dv3_col2im_k4s2p1(int N, int Hi, int Wi, int C, const float* col, const float* bias, float add, float* y, void* stream);
+int dv3_permute_last2(int A, int B, int C, const float* src, long long lds, float* dst, long long ldd, void* stream);
+int dv3_u8_nchw_to_nhwc(int N, int C, int HW, const unsigned char* src, float scale, float* dst, int Ctot, int c_off, void* stream);
+/* warp-per-row variants of dv3_ln_act_fwd / _bwd for narrow rows (channel LayerNorm over N*H*W pixel rows) */
+int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
+                        float* y, int ldy, float* mean, float* rstd, void* stream);
+int dv3_ln_act_bwd_rows(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
+                        const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* stream);
+/* MSEDistribution.log_prob, utils/distribution.py:212-221: loss[m] = sum_d (mode-x)^2, dmode = scale*2*(mode-x) */
+int dv3_mse_rows(int M, int D, const float* mode, const float* target, float scale, float* loss_rows, float* dmode, void* stream);
+
 /* ---- LayerNormGRUCell gates, models.py:388-395 ------------------------------------------------------------ */
 int dv3_gru_gate_fwd(int R, int D, const float* gates_pre, int ldg, const float* lnw, const float* lnb, const float* h_in,
                      int ldhi, float* h_out, int ldho, float* mean, float* rstd, void* stream);

@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE ONLY -- the checker, never the product.
 
 CPU restatement (plain eager PyTorch fp32, autograd, torch.optim.Adam) of the reference's
-DreamerV3 training step, vector-observation ("mlp_keys") configs, discrete actions.
+DreamerV3 training step: vector ("mlp_keys") and 64x64 pixel ("cnn_keys") observations, discrete actions.
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference leg may
 import this file.  The product package (sheeprl_prey_b200/) never does; it raises if its CUDA
@@ -169,6 +169,7 @@ class DV3Oracle:
         a = cfg.algo
         w = a.world_model
         self.keys = list(cfg.mlp_keys.encoder)
+        self.cnn_keys = list(cfg.cnn_keys.encoder)
         self.obs_dims = obs_dims
         self.actions_dim = list(actions_dim)
         self.A = sum(actions_dim)
@@ -185,10 +186,44 @@ class DV3Oracle:
         self.wm, self.actor, self.critic, self.target_critic = wm, actor, critic, target_critic
 
     # ---- world model pieces -------------------------------------------------------------
+    @staticmethod
+    def _ln_channel_last(x: Tensor, w: Tensor, b: Tensor) -> Tensor:
+        """LayerNormChannelLast, sheeprl/utils/model.py:225-235 (eps 1e-3 at agent.py:67, :194)."""
+        return F.layer_norm(x.permute(0, 2, 3, 1), (x.shape[1],), w, b, 1e-3).permute(0, 3, 1, 2)
+
+    def cnn_encoder(self, obs: Dict[str, Tensor]) -> Tensor:
+        """sheeprl/algos/dreamer_v3/agent.py:61-80: 4 x [Conv2d k4 s2 p1 no bias, LN channel-last, SiLU], Flatten(C,H,W)."""
+        x = torch.cat([obs[k] for k in self.cnn_keys], -3)
+        lead = x.shape[:-3]
+        x = x.reshape(-1, *x.shape[-3:])
+        p = "encoder.cnn_encoder.model.0._model."
+        for i in range(4):
+            x = F.conv2d(x, self.wm[f"{p}{3 * i}.weight"], None, stride=2, padding=1)
+            x = F.silu(self._ln_channel_last(x, self.wm[f"{p}{3 * i + 1}.weight"], self.wm[f"{p}{3 * i + 1}.bias"]))
+        return x.flatten(-3).reshape(*lead, -1)
+
+    def cnn_decoder(self, latent: Tensor) -> Tensor:
+        """sheeprl/algos/dreamer_v3/agent.py:178-206: Linear -> Unflatten(C,4,4) -> 3 x [ConvT k4 s2 p1, LN-CL, SiLU] -> ConvT(+bias) -> +0.5."""
+        p = "observation_model.cnn_decoder.model."
+        lead = latent.shape[:-1]
+        x = F.linear(latent.reshape(-1, latent.shape[-1]), self.wm[p + "0.weight"], self.wm[p + "0.bias"])
+        x = x.reshape(x.shape[0], -1, 4, 4)
+        for i in range(3):
+            x = F.conv_transpose2d(x, self.wm[f"{p}2._model.{3 * i}.weight"], None, stride=2, padding=1)
+            x = F.silu(self._ln_channel_last(x, self.wm[f"{p}2._model.{3 * i + 1}.weight"], self.wm[f"{p}2._model.{3 * i + 1}.bias"]))
+        x = F.conv_transpose2d(x, self.wm[p + "2._model.9.weight"], self.wm[p + "2._model.9.bias"], stride=2, padding=1)
+        return x.reshape(*lead, *x.shape[1:]) + 0.5
+
     def encoder(self, obs: Dict[str, Tensor]) -> Tensor:
-        """sheeprl/algos/dreamer_v3/agent.py:131-133 (symlog, concat, MLP no-bias, LN eps 1e-3)."""
-        x = torch.cat([symlog(obs[k]) for k in self.keys], -1)
-        return dense_stack(x, self.wm, "encoder.mlp_encoder.model._model.", self.L_enc, 1e-3)
+        """MultiEncoder sheeprl/models/models.py:452-460: cat(cnn features, mlp features).
+        MLP part: agent.py:131-133 (symlog, concat, MLP no-bias, LN eps 1e-3)."""
+        outs = []
+        if self.cnn_keys:
+            outs.append(self.cnn_encoder(obs))
+        if self.keys:
+            x = torch.cat([symlog(obs[k]) for k in self.keys], -1)
+            outs.append(dense_stack(x, self.wm, "encoder.mlp_encoder.model._model.", self.L_enc, 1e-3))
+        return torch.cat(outs, -1)
 
     def recurrent(self, z: Tensor, a: Tensor, h: Tensor) -> Tensor:
         """sheeprl/algos/dreamer_v3/agent.py:296-309 + LayerNormGRUCell sheeprl/models/models.py:388-395."""
@@ -246,11 +281,17 @@ class DV3Oracle:
         return (torch.stack(hs), torch.stack(zs), torch.stack(idxs), torch.stack(post_l), torch.stack(prior_l))
 
     def decoder(self, latent: Tensor) -> Dict[str, Tensor]:
-        """sheeprl/algos/dreamer_v3/agent.py:255-257"""
-        x = dense_stack(latent, self.wm, "observation_model.mlp_decoder.model._model.", self.L_dec, 1e-3)
-        return {k: F.linear(x, self.wm[f"observation_model.mlp_decoder.heads.{i}.weight"],
-                            self.wm[f"observation_model.mlp_decoder.heads.{i}.bias"])
-                for i, k in enumerate(self.keys)}
+        """MultiDecoder models.py:483-489; MLPDecoder sheeprl/algos/dreamer_v3/agent.py:255-257; CNNDecoder :204-206"""
+        out: Dict[str, Tensor] = {}
+        if self.cnn_keys:
+            rec = self.cnn_decoder(latent)
+            chans = [self.obs_dims[k][0] for k in self.cnn_keys]
+            out.update({k: v for k, v in zip(self.cnn_keys, torch.split(rec, chans, -3))})
+        if self.keys:
+            x = dense_stack(latent, self.wm, "observation_model.mlp_decoder.model._model.", self.L_dec, 1e-3)
+            out.update({k: F.linear(x, self.wm[f"observation_model.mlp_decoder.heads.{i}.weight"],
+                                    self.wm[f"observation_model.mlp_decoder.heads.{i}.bias"]) for i, k in enumerate(self.keys)})
+        return out
 
     def reward_logits(self, latent: Tensor) -> Tensor:
         return mlp_with_head(latent, self.wm, "reward_model._model.", self.L_rew, 1e-5)
@@ -272,6 +313,7 @@ class DV3Oracle:
         """dreamer_v3.py:102-178 + loss.py:65-110.  Returns dict with the scalar loss and intermediates."""
         w = self.cfg.algo.world_model
         obs = {k: data[k] for k in self.keys}
+        obs.update({k: data[k].float() / 255.0 for k in self.cnn_keys})        # dreamer_v3.py:102
         is_first = data["is_first"].clone()
         is_first[0] = 1.0
         embed = self.encoder(obs)
@@ -280,6 +322,8 @@ class DV3Oracle:
         rec = self.decoder(latent)
         # SymlogDistribution.log_prob: sheeprl/utils/distribution.py:177-193
         obs_loss = 0
+        for k in self.cnn_keys:                 # MSEDistribution(dims=3).log_prob: sheeprl/utils/distribution.py:212-221
+            obs_loss = obs_loss + ((rec[k] - obs[k]) ** 2).sum((-3, -2, -1))
         for k in self.keys:
             d = (rec[k] - symlog(obs[k])) ** 2
             d = torch.where(d < 1e-8, torch.zeros_like(d), d)

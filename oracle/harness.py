@@ -13,7 +13,12 @@ def synthetic_batch(T: int, B: int, obs_dims: Dict[str, int], actions_dim: Seque
     """vectors ~ N(0,1) clipped to +-5; actions one-hot uniform; rewards ~ N(0,1);
     dones ~ Bernoulli(done_p); is_first[t] = dones[t-1]."""
     g = torch.Generator().manual_seed(seed)
-    data = {k: torch.randn(T, B, d, generator=g).clamp_(-5, 5) for k, d in obs_dims.items()}
+    data = {}
+    for k, d in obs_dims.items():
+        if isinstance(d, int):
+            data[k] = torch.randn(T, B, d, generator=g).clamp_(-5, 5)
+        else:       # image key: uint8 ~ U{0..255}, shape (C, H, W)
+            data[k] = torch.randint(0, 256, (T, B, *d), generator=g, dtype=torch.uint8)
     acts = [torch.nn.functional.one_hot(torch.randint(0, a, (T, B), generator=g), a).float() for a in actions_dim]
     data["actions"] = torch.cat(acts, -1)
     data["rewards"] = torch.randn(T, B, 1, generator=g)

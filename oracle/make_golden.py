@@ -26,7 +26,13 @@ STEP_OBS = {"state": 6}
 STEP_ACTIONS = [3, 5]
 
 
-def make_step_golden():
+PIX_CFG = dict(size="XS", batch_size=3, sequence_length=4, horizon=3, deter=24, hidden=16, units=24, layers=1, stochastic_size=4,
+               discrete_size=8, cnn_keys=("rgb",), mlp_keys=("state",), cnn_mult=2)
+PIX_OBS = {"rgb": (3, 64, 64), "state": 5}
+PIX_ACTIONS = [4]
+
+
+def make_step_golden(STEP_CFG=STEP_CFG, STEP_OBS=STEP_OBS, STEP_ACTIONS=STEP_ACTIONS, fname="dv3_step.pt"):
     dv3, agent, loss, utils, buffers, dist = ref_shim.ref_modules()
     from sheeprl.utils.utils import dotdict as ref_dotdict
 
@@ -35,7 +41,8 @@ def make_step_golden():
     T, B, H = cfg.per_rank_sequence_length, cfg.per_rank_batch_size, cfg.algo.horizon
     G = cfg.algo.world_model.stochastic_size
     fab = ref_shim.FakeFabric()
-    wm, actor, critic, tcritic = agent.build_models(fab, STEP_ACTIONS, False, cfg, ObsSpace({k: (d,) for k, d in STEP_OBS.items()}))
+    wm, actor, critic, tcritic = agent.build_models(fab, STEP_ACTIONS, False, cfg,
+                                                    ObsSpace({k: ((d,) if isinstance(d, int) else d) for k, d in STEP_OBS.items()}))
     with torch.no_grad():
         for p in list(critic.parameters()) + list(wm.reward_model.parameters()):
             p.add_(0.05 * torch.randn_like(p))
@@ -80,7 +87,7 @@ def make_step_golden():
                           act_idx=torch.stack(act_idx).int(), moments_low=float(mom.low), moments_high=float(mom.high)))
     params2 = dict(wm=S(wm.state_dict()), actor=S(actor.state_dict()), critic=S(critic.state_dict()))
     torch.save(dict(cfg=STEP_CFG, obs=STEP_OBS, actions_dim=STEP_ACTIONS, params0=params0, data=data, noise=noise, steps=steps,
-                    params2=params2, torch_version=torch.__version__), os.path.join(GOLDEN_DIR, "dv3_step.pt"))
+                    params2=params2, torch_version=torch.__version__), os.path.join(GOLDEN_DIR, fname))
 
 
 def make_buffer_golden():
@@ -137,6 +144,7 @@ def make_buffer_golden():
 if __name__ == "__main__":
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     make_step_golden()
+    make_step_golden(PIX_CFG, PIX_OBS, PIX_ACTIONS, "dv3_step_pixels.pt")
     make_buffer_golden()
     for f in sorted(os.listdir(GOLDEN_DIR)):
         print(f, os.path.getsize(os.path.join(GOLDEN_DIR, f)))

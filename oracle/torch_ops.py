@@ -105,6 +105,40 @@ class TorchOps:
     def symlog(self, x: Tensor, y: Tensor) -> None:
         y.copy_(torch.sign(x) * torch.log(1 + torch.abs(x)))
 
+    # ------------------------------------------------------------------ pixel path (channel-last, k = tap*C + c)
+    def im2col(self, x: Tensor, N: int, H: int, W: int, C: int, col: Tensor) -> None:
+        """col[(n,oh,ow)][(kh*4+kw)*C + c] = x[n][2oh-1+kh][2ow-1+kw][c] (zero padded); x NHWC."""
+        xp = F.pad(x.reshape(N, H, W, C), (0, 0, 1, 1, 1, 1))
+        Ho, Wo = H // 2, W // 2
+        taps = [xp[:, kh:kh + 2 * Ho:2, kw:kw + 2 * Wo:2, :] for kh in range(4) for kw in range(4)]
+        col.copy_(torch.stack(taps, 3).reshape(N * Ho * Wo, 16 * C))
+
+    def col2im(self, col: Tensor, N: int, Hi: int, Wi: int, C: int, bias: Optional[Tensor], add: float, y: Tensor) -> None:
+        """y[n][2ih-1+kh][2iw-1+kw][c] += col[(n,ih,iw)][(kh*4+kw)*C + c]  (+ bias + add); y NHWC [N,2Hi,2Wi,C]."""
+        c = col.reshape(N, Hi, Wi, 4, 4, C)
+        out = torch.zeros(N, 2 * Hi + 2, 2 * Wi + 2, C, dtype=col.dtype, device=col.device)
+        for kh in range(4):
+            for kw in range(4):
+                out[:, kh:kh + 2 * Hi:2, kw:kw + 2 * Wi:2, :] += c[:, :, :, kh, kw, :]
+        out = out[:, 1:-1, 1:-1, :] + add
+        if bias is not None:
+            out = out + bias
+        y.copy_(out.reshape(y.shape))
+
+    def permute_last2(self, src: Tensor, A: int, Bn: int, Cn: int, dst: Tensor, lds=None, ldd=None) -> None:
+        lds, ldd = lds or Bn * Cn, ldd or Bn * Cn
+        s = torch.as_strided(src, (A, Bn, Cn), (lds, Cn, 1), src.storage_offset())
+        d = torch.as_strided(dst, (A, Cn, Bn), (ldd, Bn, 1), dst.storage_offset())
+        d.copy_(s.transpose(1, 2))
+
+    def u8_to_nhwc(self, src: Tensor, N: int, C: int, HW: int, scale: float, dst: Tensor, Ctot: int, c_off: int) -> None:
+        dst.view(N, HW, Ctot)[:, :, c_off:c_off + C] = src.reshape(N, C, HW).permute(0, 2, 1).float() * scale
+
+    def mse_rows(self, mode: Tensor, target: Tensor, scale: float, loss_rows: Tensor, dmode: Tensor) -> None:
+        diff = mode - target
+        loss_rows.copy_((diff * diff).sum(-1))
+        dmode.copy_(scale * 2 * diff)
+
     # ------------------------------------------------------------------ GRU gates
     def gru_gate_fwd(self, gates_pre: Tensor, lnw: Tensor, lnb: Tensor, h_in: Tensor, h_out: Tensor, mean: Tensor,
                      rstd: Tensor) -> None:

@@ -28,6 +28,13 @@ SIGNATURES = {
     "dv3_col_reduce_scratch_bytes": [_i, _i],
     "dv3_col_reduce": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
     "dv3_col_reduce_noalloc": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp],
+    "dv3_im2col_k4s2p1": [_i, _i, _i, _i, c_fp, c_fp, c_fp],
+    "dv3_col2im_k4s2p1": [_i, _i, _i, _i, c_fp, c_fp, _f, c_fp, c_fp],
+    "dv3_permute_last2": [_i, _i, _i, c_fp, _ll, c_fp, _ll, c_fp],
+    "dv3_u8_nchw_to_nhwc": [_i, _i, _i, c_fp, _f, c_fp, _i, _i, c_fp],
+    "dv3_ln_act_fwd_rows": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp],
+    "dv3_ln_act_bwd_rows": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_mse_rows": [_i, _i, c_fp, c_fp, _f, c_fp, c_fp, c_fp],
     "dv3_gru_gate_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp],
     "dv3_gru_gate_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_scan_prep": [_i, _i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, _i, c_fp, _i, c_fp],
@@ -195,7 +202,8 @@ class CudaOps:
         px, M, U, ldx = _mat(x)
         py, _, _, ldy = _mat(y)
         self.launches += 1
-        _chk(self.lib.dv3_ln_act_fwd(M, U, px, ldx, _p(gamma), _p(beta), eps, act, py, ldy, _p(mean), _p(rstd), self._s()), "dv3_ln_act_fwd")
+        fn = self.lib.dv3_ln_act_fwd_rows if (U <= 1024 and M >= 256) else self.lib.dv3_ln_act_fwd
+        _chk(fn(M, U, px, ldx, _p(gamma), _p(beta), eps, act, py, ldy, _p(mean), _p(rstd), self._s()), "dv3_ln_act_fwd")
 
     def ln_act_bwd(self, dy, x, gamma, beta, mean, rstd, act, dx, dln):
         pdy, M, U, lddy = _mat(dy)
@@ -203,8 +211,8 @@ class CudaOps:
         pdx, _, _, lddx = _mat(dx)
         pdl, lddl = (None, 0) if dln is None else (_mat(dln)[0], _mat(dln)[3])
         self.launches += 1
-        _chk(self.lib.dv3_ln_act_bwd(M, U, pdy, lddy, px, ldx, _p(gamma), _p(beta), _p(mean), _p(rstd), act, pdx, lddx, pdl, lddl,
-                                     self._s()), "dv3_ln_act_bwd")
+        fn = self.lib.dv3_ln_act_bwd_rows if (U <= 1024 and M >= 256) else self.lib.dv3_ln_act_bwd
+        _chk(fn(M, U, pdy, lddy, px, ldx, _p(gamma), _p(beta), _p(mean), _p(rstd), act, pdx, lddx, pdl, lddl, self._s()), "dv3_ln_act_bwd")
 
     def ln_param_grad(self, dln, x, mean, rstd, dgamma, dbeta):
         pd, M, U, ldd = _mat(dln)
@@ -222,6 +230,33 @@ class CudaOps:
     def symlog(self, x, y):
         self.launches += 1
         _chk(self.lib.dv3_symlog(x.numel(), _p(x), _p(y), self._s()), "dv3_symlog")
+
+    # ---------------------------------------------------------------- pixel path
+    def im2col(self, x, N, H, W, Cc, col):
+        assert x.is_contiguous() and col.is_contiguous() and col.numel() == N * (H // 2) * (W // 2) * 16 * Cc
+        self.launches += 1
+        _chk(self.lib.dv3_im2col_k4s2p1(N, H, W, Cc, _p(x), _p(col), self._s()), "dv3_im2col_k4s2p1")
+
+    def col2im(self, col, N, Hi, Wi, Cc, bias, add, y):
+        assert col.is_contiguous() and y.is_contiguous() and y.numel() == N * Hi * Wi * 4 * Cc
+        self.launches += 1
+        _chk(self.lib.dv3_col2im_k4s2p1(N, Hi, Wi, Cc, _p(col), _p(bias), float(add), _p(y), self._s()), "dv3_col2im_k4s2p1")
+
+    def permute_last2(self, src, A, Bn, Cn, dst, lds=None, ldd=None):
+        """dst[a][c][b] = src[a][b][c]; lds / ldd = element stride between consecutive a (default B*C)."""
+        self.launches += 1
+        _chk(self.lib.dv3_permute_last2(A, Bn, Cn, _p(src), lds or Bn * Cn, _p(dst), ldd or Bn * Cn, self._s()), "dv3_permute_last2")
+
+    def u8_to_nhwc(self, src, N, Cc, HW, scale, dst, Ctot, c_off):
+        assert src.dtype == torch.uint8 and src.is_contiguous()
+        self.launches += 1
+        _chk(self.lib.dv3_u8_nchw_to_nhwc(N, Cc, HW, _p(src), float(scale), _p(dst), Ctot, c_off, self._s()), "dv3_u8_nchw_to_nhwc")
+
+    def mse_rows(self, mode, target, scale, loss_rows, dmode):
+        M, Dd = mode.shape
+        assert mode.is_contiguous() and target.is_contiguous() and dmode.is_contiguous()
+        self.launches += 1
+        _chk(self.lib.dv3_mse_rows(M, Dd, _p(mode), _p(target), float(scale), _p(loss_rows), _p(dmode), self._s()), "dv3_mse_rows")
 
     # ---------------------------------------------------------------- GRU
     def gru_gate_fwd(self, gates_pre, lnw, lnb, h_in, h_out, mean, rstd):

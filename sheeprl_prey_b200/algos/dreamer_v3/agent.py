@@ -22,7 +22,14 @@ from ...engine import Arena, DV3Engine
 
 # ----------------------------------------------------------------------------- init (algos/dreamer_v3/utils.py:116-159)
 def init_weights(m: nn.Module) -> None:
-    if isinstance(m, nn.Linear):
+    if isinstance(m, (nn.Conv2d, nn.ConvTranspose2d)):
+        space = m.kernel_size[0] * m.kernel_size[1]
+        denom = (space * m.in_channels + space * m.out_channels) / 2.0
+        std = math.sqrt(1.0 / denom) / 0.87962566103423978
+        nn.init.trunc_normal_(m.weight.data, mean=0.0, std=std, a=-2.0, b=2.0)
+        if m.bias is not None:
+            m.bias.data.fill_(0.0)
+    elif isinstance(m, nn.Linear):
         denom = (m.in_features + m.out_features) / 2.0
         std = math.sqrt(1.0 / denom) / 0.87962566103423978
         nn.init.trunc_normal_(m.weight.data, mean=0.0, std=std, a=-2.0 * std, b=2.0 * std)
@@ -97,6 +104,65 @@ class LayerNormGRUCell(nn.Module):
         return hx.unsqueeze(0) if three_d else hx
 
 
+class LayerNormChannelLast(nn.LayerNorm):
+    """sheeprl/utils/model.py:225-235"""
+
+    def forward(self, x: Tensor) -> Tensor:
+        return super().forward(x.permute(0, 2, 3, 1)).permute(0, 3, 1, 2)
+
+
+class _ConvSeq(nn.Module):
+    """Container with the `_model` Sequential of sheeprl.models.models.CNN / DeCNN (models.py:121-284)."""
+
+    def __init__(self, layers: List[nn.Module]):
+        super().__init__()
+        self._model = nn.Sequential(*layers)
+
+    def forward(self, x: Tensor) -> Tensor:
+        return self._model(x)
+
+
+class CNNEncoder(nn.Module):
+    """agent.py:28-80: stages x [Conv2d(k4,s2,p1,no bias), LayerNormChannelLast(eps 1e-3), SiLU], Flatten."""
+
+    def __init__(self, keys: Sequence[str], input_channels: Sequence[int], image_size, channels_multiplier: int, stages: int = 4):
+        super().__init__()
+        self.keys = list(keys)
+        self.input_dim = (sum(input_channels), *image_size)
+        chans = [sum(input_channels)] + [(2 ** i) * channels_multiplier for i in range(stages)]
+        layers: List[nn.Module] = []
+        for i, o in zip(chans[:-1], chans[1:]):
+            layers += [nn.Conv2d(i, o, kernel_size=4, stride=2, padding=1, bias=False), LayerNormChannelLast(o, eps=1e-3), nn.SiLU()]
+        self.model = nn.Sequential(_ConvSeq(layers), nn.Flatten(-3, -1))
+        self.output_dim = chans[-1] * (image_size[0] // 2 ** stages) * (image_size[1] // 2 ** stages)
+
+    def forward(self, obs: Dict[str, Tensor]) -> Tensor:
+        x = torch.cat([obs[k] for k in self.keys], -3)
+        lead = x.shape[:-3]
+        return self.model(x.reshape(-1, *x.shape[-3:])).reshape(*lead, -1)
+
+
+class CNNDecoder(nn.Module):
+    """agent.py:136-206"""
+
+    def __init__(self, keys: Sequence[str], output_channels: Sequence[int], channels_multiplier: int, latent_state_size: int,
+                 cnn_encoder_output_dim: int, image_size, stages: int = 4):
+        super().__init__()
+        self.keys, self.output_channels = list(keys), list(output_channels)
+        self.output_dim = (sum(output_channels), *image_size)
+        chans = [(2 ** (stages - 1)) * channels_multiplier] + [(2 ** i) * channels_multiplier for i in reversed(range(stages - 1))]
+        layers: List[nn.Module] = []
+        for i, o in zip(chans[:-1], chans[1:]):
+            layers += [nn.ConvTranspose2d(i, o, kernel_size=4, stride=2, padding=1, bias=False), LayerNormChannelLast(o, eps=1e-3), nn.SiLU()]
+        layers.append(nn.ConvTranspose2d(chans[-1], self.output_dim[0], kernel_size=4, stride=2, padding=1))
+        self.model = nn.Sequential(nn.Linear(latent_state_size, cnn_encoder_output_dim), nn.Unflatten(1, (-1, 4, 4)), _ConvSeq(layers))
+
+    def forward(self, latent: Tensor) -> Dict[str, Tensor]:
+        lead = latent.shape[:-1]
+        out = self.model(latent.reshape(-1, latent.shape[-1])).reshape(*lead, *self.output_dim) + 0.5
+        return {k: v for k, v in zip(self.keys, torch.split(out, self.output_channels, -3))}
+
+
 class MLPEncoder(nn.Module):
     """agent.py:83-133"""
 
@@ -131,13 +197,16 @@ class MultiEncoder(nn.Module):
 
     def __init__(self, cnn_encoder, mlp_encoder):
         super().__init__()
+        if cnn_encoder is None and mlp_encoder is None:
+            raise ValueError("There must be at least one encoder, both cnn and mlp encoders are None")
         self.cnn_encoder, self.mlp_encoder = cnn_encoder, mlp_encoder
-        self.cnn_output_dim = 0
+        self.cnn_output_dim = cnn_encoder.output_dim if cnn_encoder is not None else 0
         self.mlp_output_dim = mlp_encoder.output_dim if mlp_encoder is not None else 0
         self.output_dim = self.cnn_output_dim + self.mlp_output_dim
 
     def forward(self, obs):
-        return self.mlp_encoder(obs)
+        outs = [e(obs) for e in (self.cnn_encoder, self.mlp_encoder) if e is not None]
+        return torch.cat(outs, -1)
 
 
 class MultiDecoder(nn.Module):
@@ -148,7 +217,12 @@ class MultiDecoder(nn.Module):
         self.cnn_decoder, self.mlp_decoder = cnn_decoder, mlp_decoder
 
     def forward(self, x):
-        return self.mlp_decoder(x)
+        out = {}
+        if self.cnn_decoder is not None:
+            out.update(self.cnn_decoder(x))
+        if self.mlp_decoder is not None:
+            out.update(self.mlp_decoder(x))
+        return out
 
 
 class RecurrentModel(nn.Module):
@@ -219,20 +293,28 @@ def build_models(
     kernels for host-logic tests); by default the CUDA library is required."""
     w, a = cfg.algo.world_model, cfg.algo
     device = torch.device(fabric.device)
-    if len(cfg.cnn_keys.encoder) > 0:
-        raise NotImplementedError("pixel observations (cnn_keys) are not built yet; see DESIGN.md scope table")
-    keys = list(cfg.mlp_keys.encoder)
+    keys = list(cfg.mlp_keys.encoder or [])
+    ckeys = list(cfg.cnn_keys.encoder or [])
     obs_dims = {k: int(obs_space[k].shape[0]) for k in keys}
+    obs_shapes = dict(obs_dims)
+    obs_shapes.update({k: tuple(int(x) for x in obs_space[k].shape[-3:]) for k in ckeys})
     S = w.stochastic_size * w.discrete_size
     D = w.recurrent_model.recurrent_state_size
     lat = S + D
-    enc = MultiEncoder(None, MLPEncoder(keys, [obs_dims[k] for k in keys], w.encoder.mlp_layers, w.encoder.dense_units))
+    cnn_enc = (CNNEncoder(ckeys, [obs_shapes[k][0] for k in ckeys], obs_shapes[ckeys[0]][-2:], w.encoder.cnn_channels_multiplier)
+               if ckeys else None)
+    mlp_enc = MLPEncoder(keys, [obs_dims[k] for k in keys], w.encoder.mlp_layers, w.encoder.dense_units) if keys else None
+    enc = MultiEncoder(cnn_enc, mlp_enc)
     rec = RecurrentModel(int(sum(actions_dim) + S), D, w.recurrent_model.dense_units)
     rep = MLP(D + enc.output_dim, S, [w.representation_model.hidden_size], bias=True, eps=1e-5)
     tra = MLP(D, S, [w.transition_model.hidden_size], bias=True, eps=1e-5)
     rssm = RSSM(rec.apply(init_weights), rep.apply(init_weights), tra.apply(init_weights), cfg.distribution, w.discrete_size, a.unimix)
-    dec = MultiDecoder(None, MLPDecoder(list(cfg.mlp_keys.decoder), [obs_dims[k] for k in cfg.mlp_keys.decoder], lat,
-                                        w.observation_model.mlp_layers, w.observation_model.dense_units))
+    cnn_dec = (CNNDecoder(list(cfg.cnn_keys.decoder), [obs_shapes[k][0] for k in cfg.cnn_keys.decoder],
+                          w.observation_model.cnn_channels_multiplier, lat, cnn_enc.output_dim, obs_shapes[ckeys[0]][-2:])
+               if ckeys else None)
+    mlp_dec = (MLPDecoder(list(cfg.mlp_keys.decoder), [obs_dims[k] for k in cfg.mlp_keys.decoder], lat,
+                          w.observation_model.mlp_layers, w.observation_model.dense_units) if keys else None)
+    dec = MultiDecoder(cnn_dec, mlp_dec)
     rew = MLP(lat, w.reward_model.bins, [w.reward_model.dense_units] * w.reward_model.mlp_layers, bias=True, eps=1e-5)
     con = MLP(lat, 1, [w.discount_model.dense_units] * w.discount_model.mlp_layers, bias=True, eps=1e-5)
     world_model = WorldModel(enc.apply(init_weights), rssm, dec.apply(init_weights), rew.apply(init_weights), con.apply(init_weights))
@@ -247,7 +329,8 @@ def build_models(
         rep.model[-1].apply(uniform_init_weights(1.0))
         rew.model[-1].apply(uniform_init_weights(0.0))
         con.model[-1].apply(uniform_init_weights(1.0))
-        dec.mlp_decoder.heads.apply(uniform_init_weights(1.0))
+        if mlp_dec is not None:
+            mlp_dec.heads.apply(uniform_init_weights(1.0))
     if world_model_state:
         world_model.load_state_dict(world_model_state)
     if actor_state:
@@ -273,7 +356,7 @@ def build_models(
         from ...parallel import TorchDist
 
         dist = TorchDist(fabric.world_size)
-    engine = DV3Engine(cfg, obs_dims, list(actions_dim), *arenas, ops, device, dist=dist, seed=int(getattr(fabric, "global_rank", 0)))
+    engine = DV3Engine(cfg, obs_shapes, list(actions_dim), *arenas, ops, device, dist=dist, seed=int(getattr(fabric, "global_rank", 0)))
     object.__setattr__(world_model, "_dv3_engine", engine)   # not a submodule / not in state_dict
 
     # Fabric wrapping, same call sites as agent.py:1054-1063 (DDP hooks are inert: the engine all-reduces its own grads)

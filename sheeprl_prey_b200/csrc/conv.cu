@@ -1,0 +1,232 @@
+// Data-movement kernels that turn the k4-s2-p1 convolutions / transposed convolutions of the DreamerV3 pixel encoder and
+// decoder into dense contractions (which then run on dv3_gemm_*):
+//   Conv2d(k4,s2,p1)          forward = im2col -> GEMM(NT, W[Cout][16*Cin])      backward-data = GEMM(NN) -> col2im
+//   ConvTranspose2d(k4,s2,p1) forward = GEMM(NN, W[Cin][16*Cout]) -> col2im       backward-data = im2col -> GEMM(NT)
+// Reference: CNNEncoder sheeprl/algos/dreamer_v3/agent.py:28-80 (Conv2d k4 s2 p1, no bias, LayerNormChannelLast eps 1e-3,
+// SiLU), CNNDecoder agent.py:136-206 (Linear -> Unflatten(C,4,4) -> 3x[ConvTranspose2d, LN-CL, SiLU] -> ConvTranspose2d(+bias)
+// -> +0.5), cnn_forward / LayerNormChannelLast sheeprl/utils/model.py:164-235.
+// Activations are kept channel-last (NHWC) so that the channel LayerNorm is a row LayerNorm and every gather below moves
+// contiguous channel runs; the 16 kernel taps are the slow index of the contraction dimension (k = tap*C + c), and the
+// torch-layout weights ([Cout][Cin][4][4] / [Cin][Cout][4][4]) are re-ordered once per step with dv3_permute_last2.
+#include "common.cuh"
+
+namespace {
+
+// col[(n*Ho + oh)*Wo + ow][tap*C + c] = x[n][2*oh-1+kh][2*ow-1+kw][c]  (0 outside), tap = kh*4 + kw, Ho = H/2, Wo = W/2
+__global__ void __launch_bounds__(256) im2col_k4s2p1_kernel(int N, int H, int W, int C, const float* __restrict__ x,
+                                                           float* __restrict__ col) {
+  const int Ho = H >> 1, Wo = W >> 1;
+  const size_t total = (size_t)N * Ho * Wo * 16 * C;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    size_t r = i / C;
+    const int tap = (int)(r % 16);
+    r /= 16;
+    const int ow = (int)(r % Wo);
+    r /= Wo;
+    const int oh = (int)(r % Ho);
+    const int n = (int)(r / Ho);
+    const int ih = 2 * oh - 1 + (tap >> 2), iw = 2 * ow - 1 + (tap & 3);
+    float v = 0.f;
+    if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (((size_t)n * H + ih) * W + iw) * C + c);
+    col[i] = v;
+  }
+}
+
+// y[n][oh][ow][c] = sum over the (<= 4) taps that reach it of col[(n*Hi + ih)*Wi + iw][tap*C + c]  (+ bias[c] + add)
+// oh = 2*ih - 1 + kh  =>  kh = oh + 1 - 2*ih, two valid ih per oh (same for w).  Output is [N][2Hi][2Wi][C].
+__global__ void __launch_bounds__(256) col2im_k4s2p1_kernel(int N, int Hi, int Wi, int C, const float* __restrict__ col,
+                                                           const float* __restrict__ bias, float add, float* __restrict__ y) {
+  const int Ho = Hi * 2, Wo = Wi * 2;
+  const size_t total = (size_t)N * Ho * Wo * C;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    size_t r = i / C;
+    const int ow = (int)(r % Wo);
+    r /= Wo;
+    const int oh = (int)(r % Ho);
+    const int n = (int)(r / Ho);
+    float s = add + (bias ? __ldg(bias + c) : 0.f);
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      const int ih = ((oh + 1) >> 1) - a, kh = oh + 1 - 2 * ih;     // kh in {0..3} by construction when ih is valid
+      if (ih < 0 || ih >= Hi || kh < 0 || kh > 3) continue;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int iw = ((ow + 1) >> 1) - b, kw = ow + 1 - 2 * iw;
+        if (iw < 0 || iw >= Wi || kw < 0 || kw > 3) continue;
+        s += __ldg(col + (((size_t)n * Hi + ih) * Wi + iw) * (16 * (size_t)C) + (kh * 4 + kw) * C + c);
+      }
+    }
+    y[i] = s;
+  }
+}
+
+// dst[a][c][b] = src[a][b][c]   (weights [Cout][Cin][16] <-> [Cout][16][Cin]; features [N][C][16] <-> [N][16][C])
+__global__ void __launch_bounds__(256) permute_last2_kernel(int A, int B, int Cc, const float* __restrict__ src, size_t lds,
+                                                           float* __restrict__ dst, size_t ldd) {
+  const size_t total = (size_t)A * B * Cc;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(i % B);
+    size_t r = i / B;
+    const int c = (int)(r % Cc);
+    const int a = (int)(r / Cc);
+    dst[(size_t)a * ldd + (size_t)c * B + b] = __ldg(src + (size_t)a * lds + (size_t)b * Cc + c);
+  }
+}
+
+// uint8 NCHW [N][C][HW] -> float NHWC [N][HW][C] scaled by `scale` (the /255 of dreamer_v3.py:102)
+// (several image keys are concatenated on channels: this key's C channels land at channel offset c_off of Ctot)
+__global__ void __launch_bounds__(256) u8_nchw_to_nhwc_kernel(int N, int C, int HW, const unsigned char* __restrict__ src,
+                                                             float scale, float* __restrict__ dst, int Ctot, int c_off) {
+  const size_t total = (size_t)N * HW * C;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    size_t r = i / C;
+    const int p = (int)(r % HW);
+    const int n = (int)(r / HW);
+    dst[((size_t)n * HW + p) * Ctot + c_off + c] = (float)src[((size_t)n * C + c) * HW + p] * scale;
+  }
+}
+
+// ---- warp-per-row LayerNorm (+SiLU) for narrow rows (channel-last LN over C = 24..1024 on N*H*W pixel rows) -------
+constexpr int LW_WARPS = 8;
+__global__ void __launch_bounds__(LW_WARPS * 32)
+ln_act_fwd_warp_kernel(int M, int U, const float* __restrict__ x, int ldx, const float* __restrict__ gamma,
+                       const float* __restrict__ beta, float eps, int act, float* __restrict__ y, int ldy,
+                       float* __restrict__ mean, float* __restrict__ rstd) {
+  const int lane = threadIdx.x & 31;
+  const size_t row = (size_t)blockIdx.x * LW_WARPS + (threadIdx.x >> 5);
+  if (row >= (size_t)M) return;
+  const float* xr = x + row * ldx;
+  float s = 0.f;
+  for (int i = lane; i < U; i += 32) s += xr[i];
+  const float mu = warp_sum(s) / (float)U;
+  float v = 0.f;
+  for (int i = lane; i < U; i += 32) { const float d = xr[i] - mu; v = fmaf(d, d, v); }
+  const float rs = rsqrtf(warp_sum(v) / (float)U + eps);
+  float* yr = y + row * ldy;
+  for (int i = lane; i < U; i += 32) {
+    const float ln = (xr[i] - mu) * rs * __ldg(gamma + i) + __ldg(beta + i);
+    yr[i] = act ? siluf_(ln) : ln;
+  }
+  if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+}
+
+__global__ void __launch_bounds__(LW_WARPS * 32)
+ln_act_bwd_warp_kernel(int M, int U, const float* __restrict__ dy, int lddy, const float* __restrict__ x, int ldx,
+                       const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
+                       const float* __restrict__ rstd, int act, float* __restrict__ dx, int lddx, float* __restrict__ dln,
+                       int lddln) {
+  const int lane = threadIdx.x & 31;
+  const size_t row = (size_t)blockIdx.x * LW_WARPS + (threadIdx.x >> 5);
+  if (row >= (size_t)M) return;
+  const float* xr = x + row * ldx;
+  const float* dyr = dy + row * lddy;
+  const float mu = mean[row], rs = rstd[row];
+  float s1 = 0.f, s2 = 0.f;
+  for (int i = lane; i < U; i += 32) {
+    const float xh = (xr[i] - mu) * rs;
+    float g = dyr[i];
+    if (act) {
+      const float ln = xh * __ldg(gamma + i) + __ldg(beta + i);
+      const float sg = sigmoidf_(ln);
+      g *= sg * (1.f + ln * (1.f - sg));
+    }
+    if (dln) dln[row * lddln + i] = g;
+    const float gg = g * __ldg(gamma + i);
+    s1 += gg;
+    s2 = fmaf(gg, xh, s2);
+  }
+  s1 = warp_sum(s1) / (float)U;
+  s2 = warp_sum(s2) / (float)U;
+  for (int i = lane; i < U; i += 32) {
+    const float xh = (xr[i] - mu) * rs;
+    float g = dyr[i];
+    if (act) {
+      const float ln = xh * __ldg(gamma + i) + __ldg(beta + i);
+      const float sg = sigmoidf_(ln);
+      g *= sg * (1.f + ln * (1.f - sg));
+    }
+    dx[row * lddx + i] = rs * (g * __ldg(gamma + i) - s1 - xh * s2);
+  }
+}
+
+// MSEDistribution.log_prob (sheeprl/utils/distribution.py:212-221): loss[m] = sum_d (mode - x)^2, dmode = scale*2*(mode-x)
+__global__ void __launch_bounds__(256) mse_rows_kernel(int M, int Dd, const float* __restrict__ mode, const float* __restrict__ target,
+                                                      float scale, float* __restrict__ loss_rows, float* __restrict__ dmode) {
+  __shared__ float red[64];
+  const int row = blockIdx.x;
+  const float* a = mode + (size_t)row * Dd;
+  const float* b = target + (size_t)row * Dd;
+  float* d = dmode + (size_t)row * Dd;
+  float s = 0.f;
+  for (int i = threadIdx.x; i < Dd; i += blockDim.x) {
+    const float diff = a[i] - b[i];
+    s = fmaf(diff, diff, s);
+    d[i] = scale * 2.f * diff;
+  }
+  s = block_sum(s, red);
+  if (threadIdx.x == 0) loss_rows[row] = s;
+}
+
+static inline int grid_for(size_t n) {
+  size_t g = (n + 255) / 256;
+  if (g > 148 * 32) g = 148 * 32;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dv3_im2col_k4s2p1(int N, int H, int W, int C, const float* x, float* col, void* stream) {
+  if (N <= 0 || H < 2 || W < 2 || (H & 1) || (W & 1) || C <= 0) return DV3_ERR_ARG;
+  im2col_k4s2p1_kernel<<<grid_for((size_t)N * (H / 2) * (W / 2) * 16 * C), 256, 0, (cudaStream_t)stream>>>(N, H, W, C, x, col);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_col2im_k4s2p1(int N, int Hi, int Wi, int C, const float* col, const float* bias, float add, float* y, void* stream) {
+  if (N <= 0 || Hi <= 0 || Wi <= 0 || C <= 0) return DV3_ERR_ARG;
+  col2im_k4s2p1_kernel<<<grid_for((size_t)N * Hi * Wi * 4 * C), 256, 0, (cudaStream_t)stream>>>(N, Hi, Wi, C, col, bias, add, y);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_permute_last2(int A, int B, int C, const float* src, long long lds, float* dst, long long ldd, void* stream) {
+  if (A <= 0 || B <= 0 || C <= 0) return DV3_ERR_ARG;
+  permute_last2_kernel<<<grid_for((size_t)A * B * C), 256, 0, (cudaStream_t)stream>>>(A, B, C, src, (size_t)lds, dst, (size_t)ldd);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_u8_nchw_to_nhwc(int N, int C, int HW, const unsigned char* src, float scale, float* dst, int Ctot, int c_off, void* stream) {
+  if (N <= 0 || C <= 0 || HW <= 0 || c_off < 0 || c_off + C > Ctot) return DV3_ERR_ARG;
+  u8_nchw_to_nhwc_kernel<<<grid_for((size_t)N * C * HW), 256, 0, (cudaStream_t)stream>>>(N, C, HW, src, scale, dst, Ctot, c_off);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
+                        float* y, int ldy, float* mean, float* rstd, void* stream) {
+  if (M <= 0 || U <= 0) return DV3_ERR_ARG;
+  ln_act_fwd_warp_kernel<<<(M + LW_WARPS - 1) / LW_WARPS, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(M, U, x, ldx, gamma, beta, eps, act,
+                                                                                                  y, ldy, mean, rstd);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_ln_act_bwd_rows(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
+                        const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* stream) {
+  if (M <= 0 || U <= 0) return DV3_ERR_ARG;
+  if ((const void*)dx == (const void*)dy) return DV3_ERR_ARG;
+  ln_act_bwd_warp_kernel<<<(M + LW_WARPS - 1) / LW_WARPS, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(
+      M, U, dy, lddy, x, ldx, gamma, beta, mean, rstd, act, dx, lddx, dln, lddln);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_mse_rows(int M, int D, const float* mode, const float* target, float scale, float* loss_rows, float* dmode, void* stream) {
+  if (M <= 0 || D <= 0) return DV3_ERR_ARG;
+  mse_rows_kernel<<<M, 256, 0, (cudaStream_t)stream>>>(M, D, mode, target, scale, loss_rows, dmode);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+
+}  // extern "C"

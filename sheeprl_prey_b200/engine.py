@@ -180,10 +180,16 @@ class DV3Engine:
         self.cfg, self.ops, self.device, self.dist = cfg, ops, device, dist
         self.wm, self.actor, self.critic, self.target = wm, actor, critic, target
         self.keys = list(cfg.mlp_keys.encoder)
-        if len(cfg.cnn_keys.encoder) > 0:
-            raise NotImplementedError("pixel (cnn_keys) observations: SURVEY.md section 8 rows a3/a5 pixel path is not built yet")
-        self.obs_dims = [obs_dims[k] for k in self.keys]
+        self.cnn_keys = list(cfg.cnn_keys.encoder)
+        if list(cfg.cnn_keys.decoder) != self.cnn_keys or list(cfg.mlp_keys.decoder) != self.keys:
+            raise NotImplementedError("decoder keys must equal encoder keys")
+        shp = {k: ((v,) if isinstance(v, int) else tuple(v)) for k, v in obs_dims.items()}
+        self.obs_dims = [shp[k][0] for k in self.keys]
         self.Od = sum(self.obs_dims)
+        self.img_channels = [shp[k][0] for k in self.cnn_keys]
+        self.img_hw = shp[self.cnn_keys[0]][-1] if self.cnn_keys else 0
+        if self.cnn_keys and any(shp[k][-1] != 64 or shp[k][-2] != 64 for k in self.cnn_keys):
+            raise NotImplementedError("pixel observations must be 64x64 (4 conv stages), as in every DreamerV3 config of the reference")
         self.actions_dim = list(actions_dim)
         self.A = sum(actions_dim)
         self.T, self.B = cfg.per_rank_sequence_length, cfg.per_rank_batch_size
@@ -195,7 +201,8 @@ class DV3Engine:
         self.D = w.recurrent_model.recurrent_state_size
         self.U = w.recurrent_model.dense_units
         self.Hh = w.representation_model.hidden_size
-        self.E = w.encoder.dense_units
+        self.cnn_out = 8 * w.encoder.cnn_channels_multiplier * 16 if self.cnn_keys else 0
+        self.E = self.cnn_out + (w.encoder.dense_units if self.keys else 0)
         self.lat = self.S + self.D
         self.bins = w.reward_model.bins
         self.seed = seed
@@ -212,7 +219,7 @@ class DV3Engine:
         P, Gd = wm.p, wm.g
 
         # ---------------- world-model buffers
-        self.obs_cat, self.obs_sym = z(N, self.Od), z(N, self.Od)
+        self.obs_cat, self.obs_sym = z(N, max(self.Od, 1)), z(N, max(self.Od, 1))
         self.actions, self.rewards, self.dones, self.first = z(T, B, A), z(N), z(N), z(T, B)
         self.x_rep, self.x_gru, self.x_mlp, self.latent = z(N, D + E), z(N, D + U), z(N, S + A), z(N, lat)
         self.feat_pre, self.feat_mean, self.feat_rstd = z(N, U), z(N), z(N)
@@ -223,7 +230,7 @@ class DV3Engine:
         self.zreset, self.zreset_logits, self.zreset_idx = z(1, S), z(1, S), torch.zeros(1, self.G, **i32)
         self.zero_h = z(1, D)
         self.kl_rows, self.obs_rows, self.rew_rows, self.cont_rows = z(N, 4), z(N, 1), z(N, 1), z(N, 1)
-        self.d_rec, self.d_rew, self.d_cont = z(N, self.Od), z(N, self.bins), z(N, 1)
+        self.d_rec, self.d_rew, self.d_cont = z(N, max(self.Od, 1)), z(N, self.bins), z(N, 1)
         self.dpost_logits, self.dprior_logits, self.dlatent = z(N, S), z(N, S), z(N, lat)
         self.dpost_raw, self.dhidr_act, self.dhidr_pre, self.dln_r = z(N, S), z(B, Hh), z(N, Hh), z(N, Hh)
         self.dgates_pre, self.dln_gru, self.dh_direct, self.dx_gru = z(N, 3 * D), z(N, 3 * D), z(B, D), z(B, D + U)
@@ -238,15 +245,35 @@ class DV3Engine:
         self.rng_counter = torch.zeros(1, dtype=torch.int64, device=device)
 
         # ---------------- world-model stacks
-        enc_l, _ = _stack_spec(P, Gd, "encoder.mlp_encoder.model._model.", w.encoder.mlp_layers, 1e-3, [])
-        self.enc = DenseStack(ops, device, N, self.Od, enc_l, [], last_act_out=self.x_rep[:, D:])
+        self.enc = self.dec = self.cnn_enc = self.cnn_dec = None
+        if self.keys:
+            enc_l, _ = _stack_spec(P, Gd, "encoder.mlp_encoder.model._model.", w.encoder.mlp_layers, 1e-3, [])
+            self.enc = DenseStack(ops, device, N, self.Od, enc_l, [], last_act_out=self.x_rep[:, D + self.cnn_out:])
+        if self.cnn_keys:
+            from .conv_stack import ConvDecoder, ConvEncoder
+
+            ep, dp = "encoder.cnn_encoder.model.0._model.", "observation_model.cnn_decoder.model."
+            el = [dict(w=P[f"{ep}{3 * i}.weight"], g=P[f"{ep}{3 * i + 1}.weight"], beta=P[f"{ep}{3 * i + 1}.bias"],
+                       dw=Gd[f"{ep}{3 * i}.weight"], dg=Gd[f"{ep}{3 * i + 1}.weight"], dbeta=Gd[f"{ep}{3 * i + 1}.bias"]) for i in range(4)]
+            self.cnn_enc = ConvEncoder(ops, device, N, self.img_channels, self.img_hw, el, self.x_rep[:, D:D + self.cnn_out], D + E)
+            dl = []
+            for i in range(4):
+                wk = f"{dp}2._model.{3 * i}"
+                Ld = dict(w=P[wk + ".weight"], dw=Gd[wk + ".weight"], b=P.get(wk + ".bias"), db=Gd.get(wk + ".bias"))
+                if i < 3:
+                    Ld.update(g=P[f"{dp}2._model.{3 * i + 1}.weight"], beta=P[f"{dp}2._model.{3 * i + 1}.bias"],
+                              dg=Gd[f"{dp}2._model.{3 * i + 1}.weight"], dbeta=Gd[f"{dp}2._model.{3 * i + 1}.bias"])
+                dl.append(Ld)
+            lin = dict(w=P[dp + "0.weight"], b=P[dp + "0.bias"], dw=Gd[dp + "0.weight"], db=Gd[dp + "0.bias"])
+            self.cnn_dec = ConvDecoder(ops, device, N, lat, self.img_channels, lin, dl)
         tr_l, tr_h = _stack_spec(P, Gd, "rssm.transition_model._model.", 1, 1e-5, ["rssm.transition_model._model.3"])
         self.trans = DenseStack(ops, device, N, D, tr_l, tr_h)
         tr0_l, tr0_h = _stack_spec(P, None, "rssm.transition_model._model.", 1, 1e-5, ["rssm.transition_model._model.3"])
         self.trans0 = DenseStack(ops, device, 1, D, tr0_l, tr0_h, need_bwd=False)
-        dec_l, dec_h = _stack_spec(P, Gd, "observation_model.mlp_decoder.model._model.", w.observation_model.mlp_layers, 1e-3,
-                                   [f"observation_model.mlp_decoder.heads.{i}" for i in range(len(self.keys))])
-        self.dec = DenseStack(ops, device, N, lat, dec_l, dec_h)
+        if self.keys:
+            dec_l, dec_h = _stack_spec(P, Gd, "observation_model.mlp_decoder.model._model.", w.observation_model.mlp_layers, 1e-3,
+                                       [f"observation_model.mlp_decoder.heads.{i}" for i in range(len(self.keys))])
+            self.dec = DenseStack(ops, device, N, lat, dec_l, dec_h)
         Lr, Lc = w.reward_model.mlp_layers, w.discount_model.mlp_layers
         rw_l, rw_h = _stack_spec(P, Gd, "reward_model._model.", Lr, 1e-5, [f"reward_model._model.{3 * Lr}"])
         self.rew = DenseStack(ops, device, N, lat, rw_l, rw_h)
@@ -294,6 +321,8 @@ class DV3Engine:
         for k, d in zip(self.keys, self.obs_dims):
             self.ops.copy2d(data[k].reshape(N, d), self.obs_cat[:, col:col + d])
             col += d
+        if self.cnn_enc is not None:
+            self.cnn_enc.load_images([data[k] for k in self.cnn_keys])
         self.ops.copy2d(data["actions"].reshape(N, self.A), self.actions.view(N, self.A))
         self.ops.copy2d(data["rewards"].reshape(N, 1), self.rewards.view(N, 1))
         self.ops.copy2d(data["dones"].reshape(N, 1), self.dones.view(N, 1))
@@ -316,8 +345,11 @@ class DV3Engine:
         T, B, N, S, D, U, E, A, lat = self.T, self.B, self.N, self.S, self.D, self.U, self.E, self.A, self.lat
         G, K, mix = self.G, self.K, self.cfg.algo.unimix
         # a2/a3: symlog + encoder (embedding lands in x_rep[:, D:])
-        ops.symlog(self.obs_cat, self.obs_sym)
-        self.enc.forward(self.obs_sym)
+        if self.cnn_enc is not None:
+            self.cnn_enc.forward()
+        if self.enc is not None:
+            ops.symlog(self.obs_cat, self.obs_sym)
+            self.enc.forward(self.obs_sym)
         ops.mask_shift_actions(self.actions, self.first, self.x_mlp.view(T, B, S + A)[:, :, S:])
         # z_reset = mode(unimix(transition(0)))
         self.trans0.forward(self.zero_h)
@@ -357,7 +389,10 @@ class DV3Engine:
         self.trans.forward(self.x_rep[:, :D])
         ops.unimix_fwd(self.trans.out, G, K, mix, self.prior_logits)
         # a5: decoder / reward / continue heads
-        self.dec.forward(self.latent)
+        if self.dec is not None:
+            self.dec.forward(self.latent)
+        if self.cnn_dec is not None:
+            self.cnn_dec.forward(self.latent)
         self.rew.forward(self.latent)
         self.cont.forward(self.latent)
 
@@ -365,13 +400,21 @@ class DV3Engine:
         """a6: per-row losses and their gradients (scale 1/(T*B) = the .mean() of loss.py:102)."""
         ops, w, N = self.ops, self.cfg.algo.world_model, self.N
         sc = 1.0 / N
-        ops.symlog_mse(self.dec.out, self.obs_sym, sc, self.obs_rows.view(N), self.d_rec)
+        if self.dec is not None:
+            ops.symlog_mse(self.dec.out, self.obs_sym, sc, self.obs_rows.view(N), self.d_rec)
+        if self.cnn_dec is not None:
+            self.cnn_dec.loss(self.cnn_enc.x0, sc)
         ops.twohot_loss(self.rew.out, self.rewards, None, sc, self.rew_rows.view(N), self.d_rew, False)
         ops.bernoulli_loss(self.cont.out, self.dones, sc * w.continue_scale_factor, self.cont_rows.view(N), self.d_cont)
         ops.kl_balance(self.post_logits, self.prior_logits, self.G, self.K, w.kl_free_nats, w.kl_dynamic, w.kl_representation,
                        sc * w.kl_regularizer, self.kl_rows, self.dpost_logits, self.dprior_logits)
         m = self.metrics
-        ops.reduce_mean(self.obs_rows, 0, m, _SLOT["Loss/observation_loss"], sc, False)
+        first_obs = True
+        if self.dec is not None:
+            ops.reduce_mean(self.obs_rows, 0, m, _SLOT["Loss/observation_loss"], sc, False)
+            first_obs = False
+        if self.cnn_dec is not None:
+            ops.reduce_mean(self.cnn_dec.loss_rows.view(N, 1), 0, m, _SLOT["Loss/observation_loss"], sc, not first_obs)
         ops.reduce_mean(self.rew_rows, 0, m, _SLOT["Loss/reward_loss"], sc, False)
         ops.reduce_mean(self.cont_rows, 0, m, _SLOT["Loss/continue_loss"], sc * w.continue_scale_factor, False)
         ops.reduce_mean(self.kl_rows, 0, m, _SLOT["State/kl"], sc, False)
@@ -381,7 +424,10 @@ class DV3Engine:
         # rec_loss = mean(kl_regularizer*kl_loss + obs + reward + continue)  (loss.py:102); the mean is linear
         tot = _SLOT["Loss/world_model_loss"]
         ops.reduce_mean(self.kl_rows, 1, m, tot, sc * w.kl_regularizer, False)
-        ops.reduce_mean(self.obs_rows, 0, m, tot, sc, True)
+        if self.dec is not None:
+            ops.reduce_mean(self.obs_rows, 0, m, tot, sc, True)
+        if self.cnn_dec is not None:
+            ops.reduce_mean(self.cnn_dec.loss_rows.view(N, 1), 0, m, tot, sc, True)
         ops.reduce_mean(self.rew_rows, 0, m, tot, sc, True)
         ops.reduce_mean(self.cont_rows, 0, m, tot, sc * w.continue_scale_factor, True)
 
@@ -391,7 +437,12 @@ class DV3Engine:
         G, K, mix = self.G, self.K, self.cfg.algo.unimix
         Gd = self.wm.g
         # heads -> dlatent
-        self.dec.backward(self.latent, N, self.d_rec, dx=self.dlatent, dx_accumulate=False)
+        acc = False
+        if self.dec is not None:
+            self.dec.backward(self.latent, N, self.d_rec, dx=self.dlatent, dx_accumulate=False)
+            acc = True
+        if self.cnn_dec is not None:
+            self.cnn_dec.backward(self.latent, self.dlatent, acc)
         self.rew.backward(self.latent, N, self.d_rew, dx=self.dlatent, dx_accumulate=True)
         self.cont.backward(self.latent, N, self.d_cont, dx=self.dlatent, dx_accumulate=True)
         # prior head (batched): d prior_logits -> d raw -> transition stack -> dh
@@ -430,7 +481,10 @@ class DV3Engine:
                           Gd["rssm.recurrent_model.mlp._model.1.weight"], Gd["rssm.recurrent_model.mlp._model.1.bias"])
         # encoder
         ops.gemm("NN", self.dhidr_pre, self.Wr0[:, D:], self.de)
-        self.enc.backward(self.obs_sym, N, self.de)
+        if self.cnn_enc is not None:
+            self.cnn_enc.backward(self.de[:, :self.cnn_out], E)
+        if self.enc is not None:
+            self.enc.backward(self.obs_sym, N, self.de[:, self.cnn_out:])
 
     def _optimize(self, arena: Arena, tag: str, max_norm: float, slot: str) -> None:
         """a7 / a15: gradient all-reduce (data parallel), global-norm clip, Adam."""

@@ -1,5 +1,6 @@
 """Host-logic test (no GPU): the step engine's hand-written backward / scan orchestration, run with the plain-PyTorch
 statement of the kernels (oracle/torch_ops.py), must reproduce the reference's train() (golden) and the oracle's autograd."""
+import pytest
 import torch
 
 from oracle import dv3_oracle as O
@@ -9,8 +10,9 @@ from sheeprl_prey_b200.engine import METRIC_KEYS
 from util import engine_from_params, load_golden, rel
 
 
-def test_engine_reproduces_reference_golden():
-    g = load_golden("dv3_step.pt")
+@pytest.mark.parametrize("fixture", ["dv3_step.pt", "dv3_step_pixels.pt"])
+def test_engine_reproduces_reference_golden(fixture):
+    g = load_golden(fixture)
     cfg = make_cfg(**g["cfg"])
     eng = engine_from_params(cfg, g["obs"], g["actions_dim"], g["params0"], TorchOps(), "cpu")
     T, B = cfg.per_rank_sequence_length, cfg.per_rank_batch_size
@@ -34,8 +36,9 @@ def test_engine_reproduces_reference_golden():
             assert rel(arena.p[k], v) < 5e-5, (name, k)
 
 
-def test_engine_gradients_match_oracle_autograd():
-    g = load_golden("dv3_step.pt")
+@pytest.mark.parametrize("fixture", ["dv3_step.pt", "dv3_step_pixels.pt"])
+def test_engine_gradients_match_oracle_autograd(fixture):
+    g = load_golden(fixture)
     cfg = make_cfg(**g["cfg"])
     eng = engine_from_params(cfg, g["obs"], g["actions_dim"], g["params0"], TorchOps(), "cpu")
     tr = O.OracleTrainer(cfg, g["obs"], g["actions_dim"], g["params0"]["wm"], g["params0"]["actor"], g["params0"]["critic"],

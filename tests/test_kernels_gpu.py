@@ -344,3 +344,65 @@ def test_gemm_bf16_strided_views():
     exact = A.bfloat16().double() @ B.bfloat16().double().t()
     assert rel(C1[:, 101:357].double(), exact) < 2e-5
     assert torch.equal(C1[:, :101], big_c[:, :101]) and torch.equal(C1[:, 357:], big_c[:, 357:])
+
+
+@pytest.mark.parametrize("N,H,C", [(3, 64, 3), (5, 16, 24), (2, 8, 96), (7, 4, 40)])
+def test_conv_data_movement(cuda_ops, torch_ops, N, H, C):
+    x = rnd(N * H * H, C)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        col = torch.zeros(N * (H // 2) ** 2, 16 * C, device=DEV)
+        ops.im2col(x, N, H, H, C, col)
+        y = torch.zeros(N * 4 * H * H, C, device=DEV)
+        bias = rnd(C, seed=3)
+        colT = rnd(N * H * H, 16 * C, seed=4)
+        ops.col2im(colT, N, H, H, C, bias, 0.5, y)
+        y2 = torch.zeros(N * 4 * H * H, C, device=DEV)
+        ops.col2im(colT, N, H, H, C, None, 0.0, y2)
+        res.append((col, y, y2))
+    assert torch.equal(res[0][0], res[1][0])
+    assert rel(res[1][1], res[0][1]) < 1e-6 and rel(res[1][2], res[0][2]) < 1e-6
+
+
+def test_conv_equals_torch_conv(cuda_ops):
+    """im2col + GEMM == F.conv2d(k4,s2,p1);  GEMM + col2im == F.conv_transpose2d(k4,s2,p1)  (fp32 mode)."""
+    N, H, Cin, Cout = 4, 16, 12, 20
+    x_nchw = rnd(N, Cin, H, H)
+    w = rnd(Cout, Cin, 4, 4, seed=2) * 0.1
+    x = x_nchw.permute(0, 2, 3, 1).contiguous().view(N * H * H, Cin)
+    wt = torch.zeros(Cout, 16 * Cin, device=DEV)
+    cuda_ops.permute_last2(w, Cout, Cin, 16, wt)
+    col = torch.zeros(N * (H // 2) ** 2, 16 * Cin, device=DEV)
+    cuda_ops.im2col(x, N, H, H, Cin, col)
+    y = torch.zeros(N * (H // 2) ** 2, Cout, device=DEV)
+    cuda_ops.gemm("NT", col, wt, y)
+    ref = torch.nn.functional.conv2d(x_nchw, w, None, stride=2, padding=1).permute(0, 2, 3, 1).reshape(-1, Cout)
+    assert rel(y, ref) < 1e-5
+    wT = rnd(Cin, Cout, 4, 4, seed=5) * 0.1
+    wr = torch.zeros(Cin, 16 * Cout, device=DEV)
+    cuda_ops.permute_last2(wT, Cin, Cout, 16, wr)
+    colT = torch.zeros(N * H * H, 16 * Cout, device=DEV)
+    cuda_ops.gemm("NN", x, wr, colT)
+    b = rnd(Cout, seed=6)
+    out = torch.zeros(N * 4 * H * H, Cout, device=DEV)
+    cuda_ops.col2im(colT, N, H, H, Cout, b, 0.5, out)
+    refT = torch.nn.functional.conv_transpose2d(x_nchw, wT, b, stride=2, padding=1) + 0.5
+    assert rel(out, refT.permute(0, 2, 3, 1).reshape(-1, Cout)) < 1e-5
+
+
+def test_pixel_small_kernels(cuda_ops, torch_ops):
+    N, C, HW = 6, 3, 64 * 64
+    img = torch.randint(0, 256, (N, C, HW), dtype=torch.uint8).to(DEV)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        dst = torch.zeros(N * HW, 5, device=DEV)
+        ops.u8_to_nhwc(img, N, C, HW, 1 / 255.0, dst, 5, 2)
+        a, b = rnd(N, 777), rnd(N, 777, seed=8)
+        lr, dm = torch.zeros(N, device=DEV), torch.zeros(N, 777, device=DEV)
+        ops.mse_rows(a, b, 0.25, lr, dm)
+        src = rnd(4, 6 * 10 + 3)
+        d2 = torch.zeros(4, 6 * 10 + 5, device=DEV)
+        ops.permute_last2(src, 4, 6, 10, d2, lds=63, ldd=65)
+        res.append((dst, lr, dm, d2))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][3], res[1][3])
+    assert rel(res[1][1], res[0][1]) < 1e-5 and rel(res[1][2], res[0][2]) < 1e-6

@@ -17,8 +17,9 @@ KEYS = ["Loss/world_model_loss", "Loss/observation_loss", "Loss/reward_loss", "L
         "Grads/critic"]
 
 
-def test_oracle_matches_reference_golden():
-    g = load_golden("dv3_step.pt")
+@pytest.mark.parametrize("fixture", ["dv3_step.pt", "dv3_step_pixels.pt"])
+def test_oracle_matches_reference_golden(fixture):
+    g = load_golden(fixture)
     cfg = make_cfg(**g["cfg"])
     tr = O.OracleTrainer(cfg, g["obs"], g["actions_dim"], g["params0"]["wm"], g["params0"]["actor"], g["params0"]["critic"],
                          g["params0"]["target"])

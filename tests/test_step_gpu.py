@@ -26,8 +26,9 @@ def _dev_params(p):
     return {n: {k: v.to(DEV) for k, v in d.items()} for n, d in p.items()}
 
 
-def test_step_reproduces_reference_golden(cuda_ops):
-    g = load_golden("dv3_step.pt")
+@pytest.mark.parametrize("fixture", ["dv3_step.pt", "dv3_step_pixels.pt"])
+def test_step_reproduces_reference_golden(cuda_ops, fixture):
+    g = load_golden(fixture)
     cfg = make_cfg(**g["cfg"])
     eng = engine_from_params(cfg, g["obs"], g["actions_dim"], _dev_params(g["params0"]), cuda_ops, DEV)
     T, B = cfg.per_rank_sequence_length, cfg.per_rank_batch_size
@@ -245,3 +246,30 @@ def test_persistent_scan_matches_per_step_composition(cuda_ops, size, B, T, obs,
     for name in ("feat_pre", "feat_mean", "feat_rstd", "x_gru", "gates_pre", "gru_mean", "gru_rstd", "x_rep", "hidr_pre", "hidr",
                  "hidr_mean", "hidr_rstd", "post_raw", "post_logits", "latent", "prior_logits"):
         assert rel(getattr(b, name), getattr(a, name)) < 1e-5, (name, rel(getattr(b, name), getattr(a, name)))
+
+
+def test_pixel_step_matches_oracle(cuda_ops):
+    """Pixel + vector observations (multi-encoder / multi-decoder, BASELINE config-4 structure at a small size) vs the oracle."""
+    B, T, H = 4, 8, 3
+    cfg = make_cfg("XS", batch_size=B, sequence_length=T, horizon=H, deter=64, hidden=48, units=64, layers=2, cnn_mult=8,
+                   cnn_keys=("rgb",), mlp_keys=("state",))
+    od, acts = {"rgb": (3, 64, 64), "state": 9}, [6]
+    params = random_params_like(cfg, od, acts, seed=3)
+    tr = O.OracleTrainer(cfg, od, acts, params["wm"], params["actor"], params["critic"], params["target"])
+    data = harness.synthetic_batch(T, B, od, acts, seed=21, done_p=0.1)
+    noise = harness.synthetic_noise(T, B, H, 32, len(acts), seed=22)
+    out = tr.step({k: v.clone() for k, v in data.items()}, noise)
+    eng = engine_from_params(cfg, od, acts, _dev_params(params), cuda_ops, DEV)
+    eng.load_batch(_to(data, DEV))
+    eng.load_noise(_to(noise, DEV))
+    forced = dict(post_idx=out["post_idx"].reshape(T * B, -1).int().to(DEV),
+                  imagine=dict(z_idx=out["z_idx"].int().to(DEV), act_idx=out["act_idx"].int().to(DEV)))
+    eng.step(forced)
+    torch.cuda.synchronize()
+    md = eng.metrics_dict()
+    for k in METRIC_KEYS:
+        assert abs(md[k] - float(out[k])) <= (1e-4 if k.startswith("Grads/") else 2e-5) * max(1.0, abs(float(out[k]))), (k, md[k], float(out[k]))
+    assert rel(eng.latent[:, eng.S:].reshape(T, B, -1), out["recurrent_states"]) < 1e-5
+    coef = min(1.0, 1000.0 / (float(out["Grads/world_model"]) + 1e-6))
+    worst = max((rel(eng.wm.g[k] * coef, out["world_grads"][k]), k) for k in eng.wm.g)
+    assert worst[0] < 5e-5, worst

@@ -58,7 +58,7 @@ def random_params_like(cfg, obs_dims, actions_dim, seed=0):
     from sheeprl_prey_b200.configs import ObsSpace
 
     torch.manual_seed(seed)
-    wm, actor, critic, target = build_models(FakeFabric("cpu"), actions_dim, False, cfg, ObsSpace({k: (d,) for k, d in obs_dims.items()}),
+    wm, actor, critic, target = build_models(FakeFabric("cpu"), actions_dim, False, cfg, ObsSpace({k: ((d,) if isinstance(d, int) else tuple(d)) for k, d in obs_dims.items()}),
                                              ops=TorchOps())
     g = torch.Generator().manual_seed(seed + 1)
     with torch.no_grad():
