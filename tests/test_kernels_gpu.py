@@ -376,8 +376,9 @@ def test_conv_equals_torch_conv(cuda_ops):
     cuda_ops.im2col(x, N, H, H, Cin, col)
     y = torch.zeros(N * (H // 2) ** 2, Cout, device=DEV)
     cuda_ops.gemm("NT", col, wt, y)
-    ref = torch.nn.functional.conv2d(x_nchw, w, None, stride=2, padding=1).permute(0, 2, 3, 1).reshape(-1, Cout)
-    assert rel(y, ref) < 1e-5
+    # float64 reference: torch's fp32 GPU convolutions run on TF32 tensor cores by default
+    ref = torch.nn.functional.conv2d(x_nchw.double(), w.double(), None, stride=2, padding=1).permute(0, 2, 3, 1).reshape(-1, Cout)
+    assert rel(y.double(), ref) < 1e-5
     wT = rnd(Cin, Cout, 4, 4, seed=5) * 0.1
     wr = torch.zeros(Cin, 16 * Cout, device=DEV)
     cuda_ops.permute_last2(wT, Cin, Cout, 16, wr)
@@ -386,8 +387,8 @@ def test_conv_equals_torch_conv(cuda_ops):
     b = rnd(Cout, seed=6)
     out = torch.zeros(N * 4 * H * H, Cout, device=DEV)
     cuda_ops.col2im(colT, N, H, H, Cout, b, 0.5, out)
-    refT = torch.nn.functional.conv_transpose2d(x_nchw, wT, b, stride=2, padding=1) + 0.5
-    assert rel(out, refT.permute(0, 2, 3, 1).reshape(-1, Cout)) < 1e-5
+    refT = torch.nn.functional.conv_transpose2d(x_nchw.double(), wT.double(), b.double(), stride=2, padding=1) + 0.5
+    assert rel(out.double(), refT.permute(0, 2, 3, 1).reshape(-1, Cout)) < 1e-5
 
 
 def test_pixel_small_kernels(cuda_ops, torch_ops):
