@@ -284,7 +284,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- roofline of the dominant kernel (the dense contraction), timed live with CUDA events on its stream
     roof = None
-    if rank == 0:
+    if True:   # every rank runs the diagnostic steps (they contain the gradient all-reduces); only rank 0 reports
         pk = peaks()
         saved = os.environ.get("DV3_CUDA_GRAPH")
         os.environ["DV3_CUDA_GRAPH"] = "0"
@@ -303,13 +303,13 @@ def run_ours(args, rank, world, local_rank):
             t[0] += 1
             t[1] += s_.elapsed_time(e_)
         rows = sorted(((k, c, ms_ / c, f / (ms_ / c * 1e-3) / 1e12) for k, (c, ms_, f) in table.items()), key=lambda r: -r[1] * r[2])
-        if os.path.isdir(os.path.join(ROOT, "gpurun_out")):
+        if rank == 0 and os.path.isdir(os.path.join(ROOT, "gpurun_out")):
             with open(os.path.join(ROOT, "gpurun_out", f"gemm_table_{args.size}_{args.precision}.txt"), "w") as fh:
                 fh.write("shape | launches (2 steps) | avg ms | TFLOP/s\n")
                 for k, c, ms_, tf in rows:
                     fh.write(f"{k} | {c} | {ms_:.4f} | {tf:.1f}\n")
         phases = eng.timed_step()
-        if os.path.isdir(os.path.join(ROOT, "gpurun_out")):
+        if rank == 0 and os.path.isdir(os.path.join(ROOT, "gpurun_out")):
             with open(os.path.join(ROOT, "gpurun_out", f"phases_{args.size}_{args.precision}.json"), "w") as fh:
                 json.dump(phases, fh, indent=1)
         big = [(s.elapsed_time(e), f) for (s, e, f, M, N, Kk, mode) in log if M > 32]
