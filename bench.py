@@ -341,7 +341,12 @@ def run_ours(args, rank, world, local_rank):
                 "metrics_last_step": {k: float(v) for k, v in agg.v.items()}}
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # the captured CUDA graph holds NCCL work: tearing the communicator down underneath it can block, so leave through a
+        # barrier and a hard exit once the result line is flushed
+        sys.stdout.flush()
+        dist.barrier()
+        torch.cuda.synchronize()
+        os._exit(0)
 
 
 def main():

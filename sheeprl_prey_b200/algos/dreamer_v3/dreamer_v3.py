@@ -20,12 +20,12 @@ def get_engine(world_model) -> DV3Engine:
 
 def _graphs_enabled(eng: DV3Engine) -> bool:
     """CUDA-graph replay of the step (the step has no host syncs, static buffers and device-side scalars).
-    DV3_CUDA_GRAPH=0 disables it; with data parallelism it is opt-in (DV3_CUDA_GRAPH=1) because the NCCL calls are
-    captured too."""
+    DV3_CUDA_GRAPH=0 disables it.  With data parallelism the NCCL all-reduces / all-gather are captured in the graph too
+    (measured on 2 B200: 17.8 ms/step graphed vs 20.1 ms eager)."""
     flag = os.environ.get("DV3_CUDA_GRAPH")
     if flag is not None:
         return flag == "1"
-    return eng.dist is None and eng.ops.name == "cuda"
+    return eng.ops.name == "cuda"
 
 
 def _graphed_step(eng: DV3Engine) -> None:
