@@ -238,6 +238,87 @@ gemm_skinny_stream_kernel(int M, int N, int K, const float* __restrict__ A, int 
   }
 }
 
+
+// ---- skinny NT, split-K inside the block: maximum memory-level parallelism -------------------------------------------
+// Block = 8 warps = 8 output columns; warp w streams the k-slice [w*K/8, (w+1)*K/8) of all 8 weight rows, so every lane has
+// 8 independent 16-byte loads in flight per 128-wide chunk and the whole 8 x K weight panel is fetched in about one memory
+// round trip.  Per-lane partial sums (8 columns x 16 rows) are reduced with four 31-shuffle transposed reductions, then across
+// the 8 warps through shared memory (fixed order -> deterministic).
+constexpr int SK3_COLS = 8, SK3_WARPS = 8;
+
+__device__ __forceinline__ float sk3_transpose_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int s = 16; s >= 1; s >>= 1) {
+    const bool up = (lane & s) != 0;
+#pragma unroll
+    for (int j = 0; j < s; ++j) {
+      const float send = up ? v[j] : v[j + s];
+      const float keep = up ? v[j + s] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, s);
+    }
+  }
+  return v[0];
+}
+
+__global__ void __launch_bounds__(SK3_WARPS * 32)
+gemm_skinny_splitk_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
+                          float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+  __shared__ float part[SK3_WARPS][SK3_COLS * 16];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n0 = blockIdx.x * SK3_COLS;
+  // k-slice of this warp, in units of 128-element chunks
+  const int chunks = (K + 127) / 128;
+  const int cpw = (chunks + SK3_WARPS - 1) / SK3_WARPS;
+  const int kbeg = warp * cpw * 128, kend = min(K, kbeg + cpw * 128);
+  float acc[SK3_COLS][16];
+#pragma unroll
+  for (int c = 0; c < SK3_COLS; ++c)
+#pragma unroll
+    for (int m = 0; m < 16; ++m) acc[c][m] = 0.f;
+  for (int k = kbeg + lane * 4; k < kend; k += 128) {      // K % 4 == 0 and 16 B aligned rows (checked by the launcher)
+    float4 w[SK3_COLS];
+#pragma unroll
+    for (int c = 0; c < SK3_COLS; ++c) {
+      const int n = min(n0 + c, N - 1);
+      w[c] = __ldg(reinterpret_cast<const float4*>(B + (size_t)n * ldb + k));
+    }
+#pragma unroll
+    for (int m = 0; m < 16; ++m) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (m < M) a = __ldg(reinterpret_cast<const float4*>(A + (size_t)m * lda + k));
+#pragma unroll
+      for (int c = 0; c < SK3_COLS; ++c) {
+        acc[c][m] = fmaf(a.x, w[c].x, acc[c][m]);
+        acc[c][m] = fmaf(a.y, w[c].y, acc[c][m]);
+        acc[c][m] = fmaf(a.z, w[c].z, acc[c][m]);
+        acc[c][m] = fmaf(a.w, w[c].w, acc[c][m]);
+      }
+    }
+  }
+  // lane-reduce: 4 groups of (2 columns x 16 rows) = 32 values each
+#pragma unroll
+  for (int g = 0; g < SK3_COLS / 2; ++g) {
+    float v[32];
+#pragma unroll
+    for (int m = 0; m < 16; ++m) { v[m] = acc[2 * g][m]; v[16 + m] = acc[2 * g + 1][m]; }
+    const float r = sk3_transpose_reduce32(v, lane);          // lane l: column 2g + (l>>4), row l&15
+    part[warp][(2 * g + (lane >> 4)) * 16 + (lane & 15)] = r;
+  }
+  __syncthreads();
+  if (threadIdx.x < SK3_COLS * 16) {
+    const int c = threadIdx.x >> 4, m = threadIdx.x & 15, n = n0 + c;
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < SK3_WARPS; ++w) s += part[w][threadIdx.x];
+    if (n < N && m < M) {
+      if (bias) s += bias[n];
+      float* cp = C + (size_t)m * ldc + n;
+      if (accumulate) s += *cp;
+      *cp = s;
+    }
+  }
+}
+
 template <int MT>
 static int launch_skinny_stream(int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                                 const float* bias, int accumulate, cudaStream_t stream) {
@@ -259,6 +340,12 @@ extern "C" int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int l
                             int ldc, const float* bias, int accumulate, void* stream_) {
   if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return DV3_ERR_ARG;
   cudaStream_t stream = (cudaStream_t)stream_;
+  if (mode == MODE_NT && M <= 16 && K >= 256 && (K & 3) == 0 && (lda & 3) == 0 && (ldb & 3) == 0 &&
+      (((uintptr_t)A | (uintptr_t)B) & 15) == 0) {
+    gemm_skinny_splitk_kernel<<<(N + SK3_COLS - 1) / SK3_COLS, SK3_WARPS * 32, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+    DV3_LAUNCH_CHECK();
+    return DV3_OK;
+  }
   if (mode == MODE_NT && M <= 16) {
     if (M <= 8) return launch_skinny_stream<8>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
     return launch_skinny_stream<16>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
