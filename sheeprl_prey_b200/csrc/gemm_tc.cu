@@ -86,14 +86,16 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 
 // Loads one [128 rows][64 k] operand tile (fp32, either majorness) and stores it as bf16 in the UMMA layout.
 //   kcontig: element (r, k) at src[(r0 + r) * ld + k0 + k]     else: src[(k0 + k) * ld + r0 + r]
+constexpr int TILE_THREADS = 128;   // producer threads per operand tile (A and B tiles are staged concurrently)
+
 template <bool KCONTIG>
 __device__ __forceinline__ void load_tile(const float* __restrict__ src, int ld, int r0, int k0, int R, int K, bool vec_ok,
                                           uint8_t* smem_tile, int p) {
-  constexpr int PER = (TBM * TBK / 8) / NUM_PRODUCERS;
+  constexpr int PER = (TBM * TBK / 8) / TILE_THREADS;
   float v[PER][8];
 #pragma unroll
   for (int i = 0; i < PER; ++i) {
-    const int item = p + NUM_PRODUCERS * i;
+    const int item = p + TILE_THREADS * i;
     if (KCONTIG) {
       const int row = item >> 3, chunk = item & 7;
       const int gr = r0 + row, gk = k0 + chunk * 8;
@@ -116,7 +118,7 @@ __device__ __forceinline__ void load_tile(const float* __restrict__ src, int ld,
   }
 #pragma unroll
   for (int i = 0; i < PER; ++i) {
-    const int item = p + NUM_PRODUCERS * i;
+    const int item = p + TILE_THREADS * i;
     const int row = KCONTIG ? (item >> 3) : (item & 127);
     const int chunk = KCONTIG ? (item & 7) : (item >> 7);
     const uint32_t off = (uint32_t)(row >> 3) * 1024u + (uint32_t)(row & 7) * 128u + (uint32_t)((chunk ^ (row & 7)) << 4);
@@ -134,11 +136,11 @@ __device__ __forceinline__ void load_tile(const float* __restrict__ src, int ld,
 __device__ __forceinline__ void load_tile_mn(const float* __restrict__ src, int ld, int r0, int k0, int R, int K, bool vec_ok,
                                              uint8_t* smem_tile, int p) {
   constexpr int ITEMS = (TBM / 8) * TBK;              // 16 chunks x 64 k = 1024
-  constexpr int PER = ITEMS / NUM_PRODUCERS;
+  constexpr int PER = ITEMS / TILE_THREADS;
   float v[PER][8];
 #pragma unroll
   for (int i = 0; i < PER; ++i) {
-    const int item = p + NUM_PRODUCERS * i;
+    const int item = p + TILE_THREADS * i;
     const int chunk = item & 15, k = item >> 4;       // 16 consecutive threads cover 128 contiguous r
     const int gr = r0 + chunk * 8, gk = k0 + k;
     const float* ptr = src + (size_t)gk * ld + gr;
@@ -154,7 +156,7 @@ __device__ __forceinline__ void load_tile_mn(const float* __restrict__ src, int 
   }
 #pragma unroll
   for (int i = 0; i < PER; ++i) {
-    const int item = p + NUM_PRODUCERS * i;
+    const int item = p + TILE_THREADS * i;
     const int chunk = item & 15, k = item >> 4;
     const uint32_t off = (uint32_t)(chunk >> 3) * 8192u + (uint32_t)(k >> 3) * 1024u + (uint32_t)(k & 7) * 128u +
                          (uint32_t)(((chunk & 7) ^ (k & 7)) << 4);
@@ -213,7 +215,8 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
   constexpr bool B_MN = MNMAJ && !B_KCONTIG;
   if (warp < NUM_PRODUCERS / 32) {
     // ===================== producers =====================
-    const int p = threadIdx.x;
+    const int p = threadIdx.x & (TILE_THREADS - 1);
+    const bool is_b = threadIdx.x >= TILE_THREADS;    // warps 0-3 stage the A tile, warps 4-7 the B tile, concurrently
     const bool a_vec = ((lda & 3) == 0) && ((((uintptr_t)A) & 15) == 0);
     const bool b_vec = ((ldb & 3) == 0) && ((((uintptr_t)B) & 15) == 0);
     for (int kb = 0; kb < num_kb; ++kb) {
@@ -221,10 +224,13 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
       const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
       mbar_wait(&empty_bar[s], ph ^ 1u);
       const int k0 = (kb_begin + kb) * TBK;
-      if (A_MN) load_tile_mn(A, lda, m0, k0, M, K, a_vec, smem_a + s * STAGE_A_BYTES, p);
-      else load_tile<A_KCONTIG>(A, lda, m0, k0, M, K, a_vec && A_KCONTIG, smem_a + s * STAGE_A_BYTES, p);
-      if (B_MN) load_tile_mn(B, ldb, n0, k0, N, K, b_vec, smem_b + s * STAGE_B_BYTES, p);
-      else load_tile<B_KCONTIG>(B, ldb, n0, k0, N, K, b_vec && B_KCONTIG, smem_b + s * STAGE_B_BYTES, p);
+      if (!is_b) {
+        if (A_MN) load_tile_mn(A, lda, m0, k0, M, K, a_vec, smem_a + s * STAGE_A_BYTES, p);
+        else load_tile<A_KCONTIG>(A, lda, m0, k0, M, K, a_vec && A_KCONTIG, smem_a + s * STAGE_A_BYTES, p);
+      } else {
+        if (B_MN) load_tile_mn(B, ldb, n0, k0, N, K, b_vec, smem_b + s * STAGE_B_BYTES, p);
+        else load_tile<B_KCONTIG>(B, ldb, n0, k0, N, K, b_vec && B_KCONTIG, smem_b + s * STAGE_B_BYTES, p);
+      }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the async (UMMA) proxy
       mbar_arrive(&full_bar[s]);
     }
@@ -263,14 +269,17 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
         __syncwarp();
       }
     }
-    // ===================== epilogue (warps 4-7; TMEM lanes 32*(warp%4) ..) =====================
+    // ===================== epilogue (4 warps; warp e reads TMEM lanes [32e, 32e+32) = output rows) =====================
+    // The accumulator arrives as one row per thread.  Each 32x32 chunk is transposed through shared memory (the operand ring
+    // is idle once the last MMA has committed) so that global stores / read-modify-writes / split-K reductions are issued with
+    // the 32 lanes of a warp on 32 consecutive columns of one row: full 128-byte transactions instead of 32 scattered sectors.
     mbar_wait(tmem_full_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const int ew = warp & 3;
-    const int gm = m0 + ew * 32 + lane;
-    const bool vec_store = ((ldc & 3) == 0) && ((((uintptr_t)C) & 15) == 0);
+    float* stg = reinterpret_cast<float*>(smem) + ew * (32 * 33);
 #pragma unroll 1
     for (int c0 = 0; c0 < TBN; c0 += 32) {
+      if (n0 + c0 >= N) break;
       uint32_t r[32];
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)c0;
       asm volatile(
@@ -283,42 +292,23 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
             "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
           : "r"(taddr));
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-      if (gm < M) {
-        float* crow = C + (size_t)gm * ldc;
-        const int gn0 = n0 + c0;
-        if (split) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int gn = gn0 + j;
-            if (gn < N) {
-              float o = __uint_as_float(r[j]);
-              if (bias && blockIdx.z == 0) o += __ldg(bias + gn);
-              atomicAdd(crow + gn, o);
-            }
-          }
-        } else if (vec_store && gn0 + 32 <= N) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            float4 o;
-            o.x = __uint_as_float(r[j]); o.y = __uint_as_float(r[j + 1]); o.z = __uint_as_float(r[j + 2]); o.w = __uint_as_float(r[j + 3]);
-            if (bias) { o.x += __ldg(bias + gn0 + j); o.y += __ldg(bias + gn0 + j + 1); o.z += __ldg(bias + gn0 + j + 2); o.w += __ldg(bias + gn0 + j + 3); }
-            float4* dst = reinterpret_cast<float4*>(crow + gn0 + j);
-            if (accumulate) { const float4 old = *dst; o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w; }
-            *dst = o;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int gn = gn0 + j;
-            if (gn < N) {
-              float o = __uint_as_float(r[j]);
-              if (bias) o += __ldg(bias + gn);
-              if (accumulate) o += crow[gn];
-              crow[gn] = o;
-            }
-          }
+      for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = __uint_as_float(r[j]);      // bank (lane + j) % 32: conflict-free
+      __syncwarp();
+      const int gn = n0 + c0 + lane;
+      const bool col_ok = gn < N;
+      const float bv = (bias && col_ok && (!split || blockIdx.z == 0)) ? __ldg(bias + gn) : 0.f;
+      const int rows_here = min(32, M - (m0 + ew * 32));
+#pragma unroll 4
+      for (int rr = 0; rr < rows_here; ++rr) {
+        if (col_ok) {
+          float* dst = C + (size_t)(m0 + ew * 32 + rr) * ldc + gn;
+          const float o = stg[rr * 33 + lane] + bv;
+          if (split) atomicAdd(dst, o);
+          else *dst = accumulate ? (*dst + o) : o;
         }
       }
+      __syncwarp();
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
