@@ -245,6 +245,27 @@ class RSSM(nn.Module):
         self.recurrent_model, self.representation_model, self.transition_model = recurrent_model, representation_model, transition_model
         self.discrete, self.unimix, self.distribution_cfg = discrete, unimix, distribution_cfg
 
+    # Caller-side (player / evaluation) single-step methods in plain torch, agent.py:390-437.  Not used by train().
+    def _uniform_mix(self, logits: Tensor) -> Tensor:
+        logits = logits.view(*logits.shape[:-1], -1, self.discrete)
+        if self.unimix > 0.0:
+            probs = (1 - self.unimix) * logits.softmax(-1) + self.unimix / self.discrete
+            logits = torch.distributions.utils.probs_to_logits(probs)
+        return logits.view(*logits.shape[:-2], -1)
+
+    def _stoch(self, logits: Tensor, sample: bool) -> Tensor:
+        l = logits.view(*logits.shape[:-1], -1, self.discrete)
+        d = torch.distributions.OneHotCategoricalStraightThrough(logits=l)
+        return d.rsample() if sample else torch.nn.functional.one_hot(d.probs.argmax(-1), self.discrete).to(l)
+
+    def _representation(self, recurrent_state: Tensor, embedded_obs: Tensor) -> Tuple[Tensor, Tensor]:
+        logits = self._uniform_mix(self.representation_model(torch.cat((recurrent_state, embedded_obs), -1)))
+        return logits, self._stoch(logits, True)
+
+    def _transition(self, recurrent_out: Tensor, sample_state: bool = True) -> Tuple[Tensor, Tensor]:
+        logits = self._uniform_mix(self.transition_model(recurrent_out))
+        return logits, self._stoch(logits, sample_state)
+
 
 class WorldModel(nn.Module):
     """sheeprl/algos/dreamer_v2/agent.py:630-655"""
@@ -259,13 +280,70 @@ class Actor(nn.Module):
     """agent.py:602-747 (discrete heads)"""
 
     def __init__(self, latent_state_size: int, actions_dim: Sequence[int], is_continuous: bool, dense_units: int, mlp_layers: int,
-                 unimix: float = 0.01):
+                 unimix: float = 0.01, distribution_cfg=None):
         super().__init__()
         if is_continuous:
             raise NotImplementedError("continuous actions are SURVEY.md section 8(f) item 1 (not built yet)")
         self.model = MLP(latent_state_size, None, [dense_units] * mlp_layers, bias=False, eps=1e-3)
         self.mlp_heads = nn.ModuleList([nn.Linear(dense_units, a) for a in actions_dim])
         self.actions_dim, self.is_continuous, self._unimix = list(actions_dim), is_continuous, unimix
+        self.distribution_cfg = distribution_cfg if distribution_cfg is not None else {"validate_args": False}
+
+    def forward(self, state: Tensor, is_training: bool = True, mask=None):
+        """Caller-side policy evaluation in plain torch (agent.py:682-739, discrete branch).  Not used by train()."""
+        out = self.model(state)
+        actions, dists = [], []
+        for head in self.mlp_heads:
+            logits = head(out)
+            if self._unimix > 0.0:
+                probs = (1 - self._unimix) * logits.softmax(-1) + self._unimix / logits.shape[-1]
+                logits = torch.distributions.utils.probs_to_logits(probs)
+            d = torch.distributions.OneHotCategoricalStraightThrough(logits=logits)
+            dists.append(d)
+            actions.append(d.rsample() if is_training else torch.nn.functional.one_hot(d.probs.argmax(-1), logits.shape[-1]).to(logits))
+        return tuple(actions), tuple(dists)
+
+
+class PlayerDV3(nn.Module):
+    """Environment-interaction side of the agent (agent.py:458-599): shares the trained modules' weights and steps
+    encoder -> GRU -> posterior -> actor once per env step, in plain torch.  It is the caller of the hot path, not part of it
+    (SURVEY.md section 8f-2); provided so that `main()` runs against these modules without the reference's class."""
+
+    def __init__(self, encoder, rssm: RSSM, actor, actions_dim: Sequence[int], num_envs: int, stochastic_size: int,
+                 recurrent_state_size: int, device="cpu", discrete_size: int = 32):
+        super().__init__()
+        unwrap = lambda m: getattr(m, "module", m)  # noqa: E731
+        self.encoder, self.actor = unwrap(encoder), unwrap(actor)
+        self.rssm = RSSM(unwrap(rssm.recurrent_model), unwrap(rssm.representation_model), unwrap(rssm.transition_model),
+                         rssm.distribution_cfg, rssm.discrete, rssm.unimix)
+        self.actions_dim, self.num_envs = list(actions_dim), num_envs
+        self.stochastic_size, self.discrete_size, self.recurrent_state_size = stochastic_size, discrete_size, recurrent_state_size
+        self.device = torch.device(device)
+
+    @torch.no_grad()
+    def init_states(self, reset_envs: Optional[Sequence[int]] = None) -> None:
+        if reset_envs is None or len(reset_envs) == 0:
+            self.actions = torch.zeros(1, self.num_envs, sum(self.actions_dim), device=self.device)
+            self.recurrent_state = torch.zeros(1, self.num_envs, self.recurrent_state_size, device=self.device)
+            self.stochastic_state = self.rssm._transition(self.recurrent_state, sample_state=False)[1].reshape(1, self.num_envs, -1)
+        else:
+            self.actions[:, reset_envs] = 0
+            self.recurrent_state[:, reset_envs] = 0
+            self.stochastic_state[:, reset_envs] = self.rssm._transition(
+                self.recurrent_state[:, reset_envs], sample_state=False)[1].reshape(1, len(reset_envs), -1)
+
+    @torch.no_grad()
+    def get_greedy_action(self, obs: Dict[str, Tensor], is_training: bool = True, mask=None) -> Sequence[Tensor]:
+        embedded = self.encoder(obs)
+        self.recurrent_state = self.rssm.recurrent_model(torch.cat((self.stochastic_state, self.actions), -1), self.recurrent_state)
+        _, stoch = self.rssm._representation(self.recurrent_state, embedded)
+        self.stochastic_state = stoch.view(*stoch.shape[:-2], self.stochastic_size * self.discrete_size)
+        actions, _ = self.actor(torch.cat((self.stochastic_state, self.recurrent_state), -1), is_training, mask)
+        self.actions = torch.cat(actions, -1)
+        return actions
+
+    def get_exploration_action(self, obs: Dict[str, Tensor], mask=None) -> Sequence[Tensor]:
+        return self.get_greedy_action(obs, True, mask)      # expl_amount is 0 in every DreamerV3 config (algo/dreamer_v3.yaml:141-146)
 
 
 def _arena_from(module: nn.Module, device) -> Arena:
@@ -318,7 +396,7 @@ def build_models(
     rew = MLP(lat, w.reward_model.bins, [w.reward_model.dense_units] * w.reward_model.mlp_layers, bias=True, eps=1e-5)
     con = MLP(lat, 1, [w.discount_model.dense_units] * w.discount_model.mlp_layers, bias=True, eps=1e-5)
     world_model = WorldModel(enc.apply(init_weights), rssm, dec.apply(init_weights), rew.apply(init_weights), con.apply(init_weights))
-    actor = Actor(lat, actions_dim, is_continuous, a.actor.dense_units, a.actor.mlp_layers, a.unimix)
+    actor = Actor(lat, actions_dim, is_continuous, a.actor.dense_units, a.actor.mlp_layers, a.unimix, cfg.distribution)
     critic = MLP(lat, a.critic.bins, [a.critic.dense_units] * a.critic.mlp_layers, bias=True, eps=1e-5)
     actor.apply(init_weights)
     critic.apply(init_weights)

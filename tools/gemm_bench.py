@@ -1,0 +1,40 @@
+#!/usr/bin/env python
+"""Per-shape timing of the contraction kernels: 20 launches captured in a CUDA graph (no CPU launch gaps), warm L2."""
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from sheeprl_prey_b200._lib import CudaOps  # noqa: E402
+
+dev = "cuda:0"
+shapes = [("NT", 1024, 512, 512), ("NT", 1024, 512, 1536), ("NT", 1024, 1536, 1024), ("NT", 16384, 512, 512), ("NT", 16384, 512, 1536),
+          ("NN", 15360, 512, 512), ("TN", 512, 1536, 15360), ("TN", 512, 512, 15360), ("NT", 16, 1536, 1024), ("NT", 16, 512, 1024),
+          ("NT", 16, 1024, 512), ("NT", 1024, 640, 6144), ("NT", 262144, 96, 768), ("NT", 8192, 8192, 8192)]
+print("precision | shape | us / launch | TFLOP/s")
+for prec in ("bf16", "fp32"):
+    ops = CudaOps(dev, precision=prec)
+    for mode, M, N, K in shapes:
+        if prec == "fp32" and M * N * K > 2e11:
+            continue
+        A = torch.randn((M, K) if mode != "TN" else (K, M), device=dev)
+        B = torch.randn((N, K) if mode == "NT" else (K, N), device=dev)
+        C = torch.zeros(M, N, device=dev)
+        ops.gemm(mode, A, B, C)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        reps = 20
+        with torch.cuda.graph(g):
+            for _ in range(reps):
+                ops.gemm(mode, A, B, C)
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / reps
+        print(f"{prec} | {mode} M{M} N{N} K{K} | {us:.1f} | {2.0 * M * N * K / us / 1e6:.1f}")
