@@ -175,12 +175,18 @@ __global__ void zero2d_kernel(int M, int N, float* __restrict__ C, int ldc) {
     C[(i / N) * ldc + (i % N)] = 0.f;
 }
 
+__device__ unsigned long long g_tc_stamps[16];     // diagnostics: %globaltimer stamps of CTA (0,0,0) (tools/gemm_bench.py)
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define TCSTAMP(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 31) == 0) g_tc_stamps[i] = gtimer(); } while (0)
+
 template <int MODE, bool MNMAJ>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
                float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int kb_per_split) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);   // SWIZZLE_128B: 1024 B alignment
+  // SWIZZLE_128B needs 1024 B alignment.  Plain pointer arithmetic on the __shared__ array (no integer round trip) keeps the
+  // address space visible to the compiler, so the staging stores / epilogue loads compile to STS / LDS instead of generic ST / LD.
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * STAGE_A_BYTES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (STAGE_A_BYTES + STAGE_B_BYTES));
@@ -190,6 +196,7 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * TBN;
+  if (threadIdx.x == 0) TCSTAMP(0);
   const int total_kb = (K + TBK - 1) / TBK;
   const int kb_begin = blockIdx.z * kb_per_split;                 // split-K: this CTA owns k-blocks [kb_begin, kb_begin + num_kb)
   const int num_kb = min(kb_per_split, total_kb - kb_begin);
@@ -208,6 +215,7 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (threadIdx.x == 0) TCSTAMP(1);
 
   constexpr bool A_KCONTIG = (MODE != MODE_TN);
   constexpr bool B_KCONTIG = (MODE == MODE_NT);
@@ -233,6 +241,8 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the async (UMMA) proxy
       mbar_arrive(&full_bar[s]);
+      if (threadIdx.x == 0 && kb == 0) TCSTAMP(2);
+      if (threadIdx.x == 0 && kb == num_kb - 1) TCSTAMP(3);
     }
   } else {
     if (warp == NUM_PRODUCERS / 32) {
@@ -276,6 +286,7 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
     mbar_wait(tmem_full_bar, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const int ew = warp & 3;
+    if (ew == 0) TCSTAMP(4);
     float* stg = reinterpret_cast<float*>(smem) + ew * (32 * 33);
 #pragma unroll 1
     for (int c0 = 0; c0 < TBN; c0 += 32) {
@@ -292,27 +303,52 @@ gemm_tc_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const 
             "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
           : "r"(taddr));
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (ew == 0 && c0 == 0) TCSTAMP(7);
 #pragma unroll
       for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = __uint_as_float(r[j]);      // bank (lane + j) % 32: conflict-free
       __syncwarp();
+      if (ew == 0 && c0 == 0) TCSTAMP(8);
       const int gn = n0 + c0 + lane;
       const bool col_ok = gn < N;
       const float bv = (bias && col_ok && (!split || blockIdx.z == 0)) ? __ldg(bias + gn) : 0.f;
-      const int rows_here = min(32, M - (m0 + ew * 32));
-#pragma unroll 4
-      for (int rr = 0; rr < rows_here; ++rr) {
-        if (col_ok) {
-          float* dst = C + (size_t)(m0 + ew * 32 + rr) * ldc + gn;
-          const float o = stg[rr * 33 + lane] + bv;
-          if (split) atomicAdd(dst, o);
-          else *dst = accumulate ? (*dst + o) : o;
+      const int rows_here = col_ok ? min(32, M - (m0 + ew * 32)) : 0;
+      float* dst0 = C + (size_t)(m0 + ew * 32) * ldc + gn;
+      float o[32];
+#pragma unroll
+      for (int rr = 0; rr < 32; ++rr) o[rr] = stg[rr * 33 + lane] + bv;            // all 32 reads in flight, conflict-free
+      // Full 32 x 32 chunk (the common case): branch-free unrolled stores.  Ragged edges take the predicated path.
+      const bool full = __all_sync(0xffffffffu, rows_here == 32);
+      const size_t ld = (size_t)ldc;
+      if (full) {
+        if (split) {
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) atomicAdd(dst0 + rr * ld, o[rr]);
+        } else if (accumulate) {
+          float old[32];
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) old[rr] = dst0[rr * ld];             // independent loads first
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) dst0[rr * ld] = old[rr] + o[rr];
+        } else {
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) dst0[rr * ld] = o[rr];
+        }
+      } else {
+#pragma unroll 1
+        for (int rr = 0; rr < rows_here; ++rr) {
+          float* d = dst0 + rr * ld;
+          if (split) atomicAdd(d, o[rr]);
+          else *d = accumulate ? (*d + o[rr]) : o[rr];
         }
       }
       __syncwarp();
+      if (ew == 0 && c0 == 0) TCSTAMP(9);
     }
+    if (ew == 0) TCSTAMP(5);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
   __syncthreads();
+  if (threadIdx.x == 0) TCSTAMP(6);
   if (warp == NUM_PRODUCERS / 32) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
@@ -336,7 +372,7 @@ int launch_tc(int M, int N, int K, const float* A, int lda, const float* B, int 
   const int total_kb = (K + TBK - 1) / TBK;
   const int tiles = (int)(grid.x * grid.y);
   int splits = 1;
-  if (tiles < 120 && total_kb >= 8) {
+  if (tiles < 120 && total_kb >= 32) {   // only long-K problems: a split needs a zero-fill launch and atomic epilogues
     splits = (296 + tiles - 1) / tiles;
     if (splits > total_kb / 4) splits = total_kb / 4;
     if (splits > 64) splits = 64;
@@ -358,6 +394,10 @@ int launch_tc(int M, int N, int K, const float* A, int lda, const float* B, int 
 }
 
 }  // namespace
+
+extern "C" int dv3_gemm_tc_debug_stamps(unsigned long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_tc_stamps, sizeof(unsigned long long) * 16);
+}
 
 static int g_tc_mn_major = -1;   // operands whose contiguous dimension is M/N: keep them MN-major in smem (1) or transpose (0)
 
