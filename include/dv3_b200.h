@@ -52,6 +52,12 @@ int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int lda, const f
 int dv3_gemm_bf16_tc(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                      const float* bias, int accumulate, void* stream);
 
+/* bf16-resident variant: A [M,K] and B [N,K] are bf16 in HBM (K contiguous, leading dimensions multiples of 8, 16 B aligned);
+ * operand tiles are fetched by TMA (cp.async.bulk.tensor, SWIZZLE_128B) into the UMMA layout, C is fp32. */
+int dv3_gemm_bf16_tma(int M, int N, int K, const void* A_bf16, int lda, const void* B_bf16, int ldb, float* C, int ldc,
+                      const float* bias, int accumulate, void* stream);
+int dv3_f32_to_bf16(int R, int C, const float* src, int lds, void* dst_bf16, int ldd, void* stream);
+
 /* ---- LayerNorm(+SiLU) blocks: miniblock order Linear -> LayerNorm -> SiLU, utils/model.py:71-87 ---------- */
 int dv3_ln_act_fwd(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
                    float* y, int ldy, float* mean, float* rstd, void* stream);

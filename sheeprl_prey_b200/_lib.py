@@ -23,6 +23,8 @@ SIGNATURES = {
     "dv3_seq_gather": [_i, c_fp, c_fp, c_fp, _i, _i, _i, _i, c_fp, c_fp, c_fp, c_fp, c_fp],
     "dv3_gemm_f32": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_gemm_bf16_tc": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_gemm_bf16_tma": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_f32_to_bf16": [_i, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_ln_act_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp],
     "dv3_ln_act_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_col_reduce_scratch_bytes": [_i, _i],

@@ -1,0 +1,268 @@
+// bf16-resident tensor-core contraction: TMA-fed tcgen05 GEMM.
+//
+//   C[M,N] (+)= A[M,K] * B[N,K]^T (+ bias)      A, B bf16 in HBM (K contiguous), C fp32.
+//
+// Used by the forward passes whose operands already live in bf16 (activations written in bf16 by the LayerNorm / GRU / sampling
+// kernels, bf16 weight shadows refreshed after every Adam step): the imagination rollout, the value / reward / continue heads on
+// the imagined states and the world-model heads.  Compared with gemm_tc.cu (fp32 operands converted by 8 producer warps) the
+// operand tiles are fetched by the TMA engine (cp.async.bulk.tensor, SWIZZLE_128B boxes of 128 rows x 64 k) straight into the
+// UMMA shared-memory layout: one elected thread keeps a 6-stage ring full, so the L2 latency is hidden instead of paid per
+// k-block, and half as many bytes cross the L2.
+//   warp 0 : TMA producer (one lane)        warp 1 : TMEM allocator + tcgen05.mma issuer (one lane)
+//   warps 2-5 : epilogue (tcgen05.ld -> shared-memory transpose -> coalesced global stores / accumulate)
+// Out-of-range rows / columns / k are zero-filled by the TMA unit, so ragged M, N, K need no special cases in the main loop.
+#include "common.cuh"
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+namespace {
+
+constexpr int TBM = 128, TBN = 128, TBK = 64, STAGES = 6;
+constexpr int NUM_THREADS = 192;
+constexpr int STAGE_A_BYTES = TBM * TBK * 2, STAGE_B_BYTES = TBN * TBK * 2;
+constexpr int TMEM_COLS = 128;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+// Bounded wait: a TMA fault must surface as a trapped kernel (an error code), never as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  for (uint32_t it = 0; it < (1u << 26); ++it) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, P1;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (ok) return;
+  }
+  __trap();
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c_inner, int c_outer) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer)
+      : "memory");
+}
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {   // K-major SWIZZLE_128B (see gemm_tc.cu)
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
+                     float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * STAGE_A_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (STAGE_A_BYTES + STAGE_B_BYTES));
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * TBN;
+  const int num_kb = (K + TBK - 1) / TBK;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+        mbar_wait(&empty_bar[s], ph ^ 1u);
+        mbar_expect_tx(&full_bar[s], STAGE_A_BYTES + STAGE_B_BYTES);
+        tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], kb * TBK, m0);
+        tma_load_2d(smem_b + s * STAGE_B_BYTES, &tmB, &full_bar[s], kb * TBK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % STAGES;
+      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      mbar_wait(&full_bar[s], ph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (lane == 0) {
+        const uint32_t a_addr = smem_u32(smem_a + s * STAGE_A_BYTES);
+        const uint32_t b_addr = smem_u32(smem_b + s * STAGE_B_BYTES);
+#pragma unroll
+        for (int k = 0; k < TBK / 16; ++k) {
+          const uint64_t adesc = make_smem_desc(a_addr + k * 32);
+          const uint64_t bdesc = make_smem_desc(b_addr + k * 32);
+          const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+          asm volatile(
+              "{\n"
+              ".reg .pred p;\n"
+              "setp.ne.b32 p, %4, 0;\n"
+              "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+              "}\n" ::"r"(tmem_base),
+              "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+              : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[s])) : "memory");
+        if (kb == num_kb - 1)
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(tmem_full_bar)) : "memory");
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===================== epilogue (warps 2-5; warp w owns TMEM lanes [32*(w&3), +32)) =====================
+    mbar_wait(tmem_full_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const int ew = warp & 3;
+    float* stg = reinterpret_cast<float*>(smem) + ew * (32 * 33);
+#pragma unroll 1
+    for (int c0 = 0; c0 < TBN; c0 += 32) {
+      if (n0 + c0 >= N) break;
+      uint32_t r[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)c0;
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+            "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+            "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+            "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+          : "r"(taddr));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = __uint_as_float(r[j]);
+      __syncwarp();
+      const int gn = n0 + c0 + lane;
+      const bool col_ok = gn < N;
+      const float bv = (bias && col_ok) ? __ldg(bias + gn) : 0.f;
+      const int rows_here = col_ok ? min(32, M - (m0 + ew * 32)) : 0;
+      float* dst0 = C + (size_t)(m0 + ew * 32) * ldc + gn;
+      float o[32];
+#pragma unroll
+      for (int rr = 0; rr < 32; ++rr) o[rr] = stg[rr * 33 + lane] + bv;
+      const bool full = __all_sync(0xffffffffu, rows_here == 32);
+      const size_t ld = (size_t)ldc;
+      if (full) {
+        if (accumulate) {
+          float old[32];
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) old[rr] = dst0[rr * ld];
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) dst0[rr * ld] = old[rr] + o[rr];
+        } else {
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) dst0[rr * ld] = o[rr];
+        }
+      } else {
+#pragma unroll 1
+        for (int rr = 0; rr < rows_here; ++rr) {
+          float* d = dst0 + rr * ld;
+          *d = accumulate ? (*d + o[rr]) : o[rr];
+        }
+      }
+      __syncwarp();
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+  }
+}
+
+constexpr int SMEM_BYTES = STAGES * (STAGE_A_BYTES + STAGE_B_BYTES) + (2 * STAGES + 1) * 8 + 16 + 1024;
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode = nullptr;
+
+// [rows, K] bf16, K contiguous, row stride ld elements -> 2-D tensor map with a 64 (k) x 128 (rows) SWIZZLE_128B box
+int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld) {
+  const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  const cuuint32_t box[2] = {TBK, TBM};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : 1000 + (int)r;
+}
+
+}  // namespace
+
+extern "C" int dv3_gemm_bf16_tma(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc,
+                                 const float* bias, int accumulate, void* stream_) {
+  if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return DV3_ERR_ARG;
+  // TMA: 16 B aligned base addresses and row strides
+  if (((uintptr_t)A & 15) || ((uintptr_t)B & 15) || (lda & 7) || (ldb & 7)) return DV3_ERR_UNSUPPORTED;
+  if (!g_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return DV3_ERR_UNSUPPORTED;
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    e = cudaFuncSetAttribute(gemm_bf16_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+  }
+  CUtensorMap tmA, tmB;
+  int rc = make_map(&tmA, A, M, K, lda);
+  if (rc) return rc;
+  rc = make_map(&tmB, B, N, K, ldb);
+  if (rc) return rc;
+  dim3 grid((N + TBN - 1) / TBN, (M + TBM - 1) / TBM, 1);
+  if (grid.y > 65535) return DV3_ERR_UNSUPPORTED;
+  gemm_bf16_tma_kernel<<<grid, NUM_THREADS, SMEM_BYTES, (cudaStream_t)stream_>>>(tmA, tmB, M, N, K, C, ldc, bias, accumulate);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+
+// fp32 -> bf16 (round to nearest even), 2-D with leading dimensions: weight shadows and operand staging
+namespace {
+__global__ void f32_to_bf16_kernel(int R, int Cc, const float* __restrict__ s, int lds, __nv_bfloat16* __restrict__ d, int ldd) {
+  const size_t n = (size_t)R * Cc;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / Cc), c = (int)(i % Cc);
+    d[(size_t)r * ldd + c] = __float2bfloat16_rn(s[(size_t)r * lds + c]);
+  }
+}
+}  // namespace
+
+extern "C" int dv3_f32_to_bf16(int R, int Cc, const float* src, int lds, void* dst, int ldd, void* stream) {
+  if (R <= 0 || Cc <= 0) return DV3_ERR_ARG;
+  size_t g = ((size_t)R * Cc + 255) / 256;
+  if (g > 148 * 16) g = 148 * 16;
+  f32_to_bf16_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(R, Cc, src, lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}

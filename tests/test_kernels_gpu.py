@@ -407,3 +407,27 @@ def test_pixel_small_kernels(cuda_ops, torch_ops):
         res.append((dst, lr, dm, d2))
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][3], res[1][3])
     assert rel(res[1][1], res[0][1]) < 1e-5 and rel(res[1][2], res[0][2]) < 1e-6
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1024, 512, 512), (1024, 512, 1536), (16384, 512, 1536), (1000, 255, 520), (130, 40, 72)])
+def test_gemm_bf16_tma(M, N, K):
+    """TMA-fed tcgen05 GEMM on bf16-resident operands (ragged sizes are zero-filled by the TMA unit)."""
+    from sheeprl_prey_b200._lib import load_library
+
+    lib = load_library()
+    A, B, bias = rnd(M, K), rnd(N, K), rnd(N)
+    Ab, Bb = A.bfloat16().contiguous(), B.bfloat16().contiguous()
+    st = torch.cuda.current_stream().cuda_stream
+    for acc in (0, 1):
+        C0 = rnd(M, N, seed=7)
+        C1 = C0.clone()
+        rc = lib.dv3_gemm_bf16_tma(M, N, K, Ab.data_ptr(), K, Bb.data_ptr(), K, C1.data_ptr(), N, bias.data_ptr(), acc, st)
+        assert rc == 0, rc
+        torch.cuda.synchronize()
+        exact = Ab.double() @ Bb.double().t() + bias.double() + (C0.double() if acc else 0)
+        assert rel(C1.double(), exact) < 2e-5, (M, N, K, acc)
+    # conversion kernel == round-to-nearest-even
+    dst = torch.zeros(M, K + 8, dtype=torch.bfloat16, device=DEV)
+    assert lib.dv3_f32_to_bf16(M, K, A.data_ptr(), K, dst.data_ptr(), K + 8, st) == 0
+    torch.cuda.synchronize()
+    assert torch.equal(dst[:, :K], Ab)

@@ -51,3 +51,30 @@ for prec in ("bf16", "fp32"):
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) * 1e3 / reps
         print(f"{prec} | {mode} M{M} N{N} K{K} | {us:.1f} | {2.0 * M * N * K / us / 1e6:.1f}" + (("   [" + stamps(ops) + "]") if prec == "bf16" and M >= 128 else ""))
+
+
+# TMA-fed bf16-resident variant (NT only)
+lib = CudaOps(dev).lib
+print("tma bf16 | shape | us / launch | TFLOP/s")
+for mode, M, N, K in shapes:
+    if mode != "NT" or M < 128 or K % 8:
+        continue
+    A = torch.randn(M, K, device=dev).bfloat16()
+    B = torch.randn(N, K, device=dev).bfloat16()
+    C = torch.zeros(M, N, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.dv3_gemm_bf16_tma(M, N, K, A.data_ptr(), K, B.data_ptr(), K, C.data_ptr(), N, None, 0, st) == 0
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(20):
+            lib.dv3_gemm_bf16_tma(M, N, K, A.data_ptr(), K, B.data_ptr(), K, C.data_ptr(), N, None, 0, torch.cuda.current_stream().cuda_stream)
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / 20
+    print(f"tma | NT M{M} N{N} K{K} | {us:.1f} | {2.0 * M * N * K / us / 1e6:.1f}")
