@@ -298,8 +298,8 @@ def run_ours(args, rank, world, local_rank):
         else:
             os.environ["DV3_CUDA_GRAPH"] = saved
         table = {}
-        for (s_, e_, f, M, N, Kk, mode) in log:
-            t = table.setdefault(f"{mode} M{M} N{N} K{Kk}", [0, 0.0, f])
+        for (s_, e_, f, M, N, Kk, mode, kern) in log:
+            t = table.setdefault(f"{mode} M{M} N{N} K{Kk} [{kern}]", [0, 0.0, f])
             t[0] += 1
             t[1] += s_.elapsed_time(e_)
         rows = sorted(((k, c, ms_ / c, f / (ms_ / c * 1e-3) / 1e12) for k, (c, ms_, f) in table.items()), key=lambda r: -r[1] * r[2])
@@ -312,7 +312,7 @@ def run_ours(args, rank, world, local_rank):
         if rank == 0 and os.path.isdir(os.path.join(ROOT, "gpurun_out")):
             with open(os.path.join(ROOT, "gpurun_out", f"phases_{args.size}_{args.precision}.json"), "w") as fh:
                 json.dump(phases, fh, indent=1)
-        big = [(s.elapsed_time(e), f) for (s, e, f, M, N, Kk, mode) in log if M > 32]
+        big = [(s.elapsed_time(e), f) for (s, e, f, M, N, Kk, mode, kern) in log if kern in ("tma", "tc") or (kern == "simt" and M > 32)]
         tot_ms, tot_fl = sum(x[0] for x in big), sum(x[1] for x in big)
         all_ms = sum(s.elapsed_time(e) for (s, e, *_r) in log)
         ach = tot_fl / (tot_ms * 1e-3) / 1e12 if tot_ms > 0 else 0.0

@@ -52,17 +52,21 @@ int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int lda, const f
 int dv3_gemm_bf16_tc(int mode, int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                      const float* bias, int accumulate, void* stream);
 
-/* bf16-resident variant: A [M,K] and B [N,K] are bf16 in HBM (K contiguous, leading dimensions multiples of 8, 16 B aligned);
- * operand tiles are fetched by TMA (cp.async.bulk.tensor, SWIZZLE_128B) into the UMMA layout, C is fp32. */
-int dv3_gemm_bf16_tma(int M, int N, int K, const void* A_bf16, int lda, const void* B_bf16, int ldb, float* C, int ldc,
+/* bf16-resident variant (same modes): A and B are bf16 in HBM (leading dimensions multiples of 8, 16 B aligned bases, else
+ * DV3_ERR_UNSUPPORTED); operand tiles are fetched by TMA (cp.async.bulk.tensor, SWIZZLE_128B) straight into the UMMA layout
+ * (K-major or MN-major, no transposition), C is fp32; split-K with fp32 atomics when the output has few tiles.
+ * Producers below take an optional `*_bf16` pointer: a bf16 mirror of their fp32 output with the SAME leading dimension,
+ * written in the same pass, so the next contraction reads half the bytes (NULL = no mirror). */
+int dv3_gemm_bf16_tma(int mode, int M, int N, int K, const void* A_bf16, int lda, const void* B_bf16, int ldb, float* C, int ldc,
                       const float* bias, int accumulate, void* stream);
 int dv3_f32_to_bf16(int R, int C, const float* src, int lds, void* dst_bf16, int ldd, void* stream);
 
 /* ---- LayerNorm(+SiLU) blocks: miniblock order Linear -> LayerNorm -> SiLU, utils/model.py:71-87 ---------- */
 int dv3_ln_act_fwd(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
-                   float* y, int ldy, float* mean, float* rstd, void* stream);
+                   float* y, int ldy, float* mean, float* rstd, void* y_bf16, void* stream);
 int dv3_ln_act_bwd(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
-                   const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* stream);
+                   const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* dx_bf16,
+                   void* stream);
 /* out_a[u] = sum_m d[m,u]*xhat[m,u] (LN weight grad; skipped when x == NULL), out_b[u] = sum_m d[m,u] (LN bias /
  * Linear bias grad).  Two-stage reduction through `scratch`. */
 size_t dv3_col_reduce_scratch_bytes(int M, int U);
@@ -87,15 +91,16 @@ int dv3_permute_last2(int A, int B, int C, const float* src, long long lds, floa
 int dv3_u8_nchw_to_nhwc(int N, int C, int HW, const unsigned char* src, float scale, float* dst, int Ctot, int c_off, void* stream);
 /* warp-per-row variants of dv3_ln_act_fwd / _bwd for narrow rows (channel LayerNorm over N*H*W pixel rows) */
 int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
-                        float* y, int ldy, float* mean, float* rstd, void* stream);
+                        float* y, int ldy, float* mean, float* rstd, void* y_bf16, void* stream);
 int dv3_ln_act_bwd_rows(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
-                        const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* stream);
+                        const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* dx_bf16,
+                        void* stream);
 /* MSEDistribution.log_prob, utils/distribution.py:212-221: loss[m] = sum_d (mode-x)^2, dmode = scale*2*(mode-x) */
 int dv3_mse_rows(int M, int D, const float* mode, const float* target, float scale, float* loss_rows, float* dmode, void* stream);
 
 /* ---- LayerNormGRUCell gates, models.py:388-395 ------------------------------------------------------------ */
 int dv3_gru_gate_fwd(int R, int D, const float* gates_pre, int ldg, const float* lnw, const float* lnb, const float* h_in,
-                     int ldhi, float* h_out, int ldho, float* mean, float* rstd, void* stream);
+                     int ldhi, float* h_out, int ldho, float* mean, float* rstd, void* h_out_bf16, void* stream);
 int dv3_gru_gate_bwd(int R, int D, const float* dh_out, int lddho, const float* gates_pre, int ldg, const float* lnw,
                      const float* lnb, const float* mean, const float* rstd, const float* h_in, int ldhi, float* dgates_pre,
                      int lddg, float* dln, int lddln, float* dh_in, int lddhi, void* stream);
@@ -138,7 +143,7 @@ int dv3_rssm_observe_fwd(const Dv3ScanFwdArgs* args, void* stream);
 /* ---- categorical: unimix agent.py:390-402/:741-747; ST one-hot sample distribution.py:355-360,:390-393 ---- */
 int dv3_unimix_fwd(int R, int groups, int K, float mix, const float* raw, int ldr, float* logits, int ldo, void* stream);
 int dv3_sample_onehot(int R, int groups, int K, const float* logits, int ldl, const float* u, int ldu, const int* forced,
-                      int ldf, int mode, int* idx, int ldi, float* onehot, int ldo, void* stream);
+                      int ldf, int mode, int* idx, int ldi, float* onehot, int ldo, void* onehot_bf16, void* stream);
 int dv3_unimix_bwd(int R, int groups, int K, float mix, const float* raw, int ldr, const float* dlogits, int lddl,
                    const float* dz, int lddz, float* draw, int lddr, void* stream);
 

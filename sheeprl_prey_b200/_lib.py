@@ -2,9 +2,10 @@
 step engine calls.  There is no fallback: if the library is missing or a call fails, this raises."""
 from __future__ import annotations
 
+import bisect
 import ctypes as C
 import os
-from typing import Optional, Sequence
+from typing import List, Optional, Sequence
 
 import torch
 
@@ -23,10 +24,10 @@ SIGNATURES = {
     "dv3_seq_gather": [_i, c_fp, c_fp, c_fp, _i, _i, _i, _i, c_fp, c_fp, c_fp, c_fp, c_fp],
     "dv3_gemm_f32": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_gemm_bf16_tc": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
-    "dv3_gemm_bf16_tma": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_gemm_bf16_tma": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_f32_to_bf16": [_i, _i, c_fp, _i, c_fp, _i, c_fp],
-    "dv3_ln_act_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp],
-    "dv3_ln_act_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_ln_act_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
+    "dv3_ln_act_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
     "dv3_col_reduce_scratch_bytes": [_i, _i],
     "dv3_col_reduce": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
     "dv3_col_reduce_noalloc": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp],
@@ -34,10 +35,10 @@ SIGNATURES = {
     "dv3_col2im_k4s2p1": [_i, _i, _i, _i, c_fp, c_fp, _f, c_fp, c_fp],
     "dv3_permute_last2": [_i, _i, _i, c_fp, _ll, c_fp, _ll, c_fp],
     "dv3_u8_nchw_to_nhwc": [_i, _i, _i, c_fp, _f, c_fp, _i, _i, c_fp],
-    "dv3_ln_act_fwd_rows": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp],
-    "dv3_ln_act_bwd_rows": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_ln_act_fwd_rows": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
+    "dv3_ln_act_bwd_rows": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
     "dv3_mse_rows": [_i, _i, c_fp, c_fp, _f, c_fp, c_fp, c_fp],
-    "dv3_gru_gate_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp],
+    "dv3_gru_gate_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_gru_gate_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_scan_prep": [_i, _i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, _i, c_fp, _i, c_fp],
     "dv3_scan_carry": [_i, _i, _i, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
@@ -45,7 +46,7 @@ SIGNATURES = {
     "dv3_rssm_observe_fwd_scratch_bytes": [],
     "dv3_rssm_observe_fwd": [c_fp, c_fp],
     "dv3_unimix_fwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp],
-    "dv3_sample_onehot": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_sample_onehot": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
     "dv3_unimix_bwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_kl_balance": [_i, _i, _i, c_fp, c_fp, _f, _f, _f, _f, c_fp, c_fp, c_fp, c_fp],
     "dv3_twohot_loss": [_i, _i, c_fp, _i, c_fp, c_fp, _f, c_fp, c_fp, _i, _i, c_fp],
@@ -154,10 +155,70 @@ class CudaOps:
             raise RuntimeError("CudaOps needs a CUDA device; sheeprl_prey_b200 has no CPU path")
         self.scratch = torch.empty(scratch_bytes // 4, dtype=torch.float32, device=self.device)
         self.launches = 0   # kernels of ours enqueued so far
-        self.gemm_log = None   # when a list: (start_event, end_event, flops, M, N, K, mode) per gemm call (bench / profiling)
+        self.gemm_log = None   # when a list: (start_event, end_event, flops, M, N, K, mode, kernel) per gemm call (bench / profiling)
+        # bf16 mirrors (bf16 precision only): for a registered fp32 buffer, a bf16 buffer with the same element layout.  Producer
+        # kernels write both in one pass; contractions whose two operands are mirrored run the TMA-fed kernel on the mirrors.
+        self.use_mirrors = self.precision == "bf16" and os.environ.get("DV3_BF16_RESIDENT", "1") != "0"
+        self.mirror_check = os.environ.get("DV3_MIRROR_CHECK", "0") == "1"
+        self._mir_start: List[int] = []
+        self._mir: List[tuple] = []
+        if self.use_mirrors:
+            self.gemm_kernel_name = ("gemm_bf16_tma_kernel (TMA-fed tcgen05 bf16, 128x128x64, fp32 TMEM accumulate) + "
+                                     "gemm_tc_kernel for operands without a bf16 mirror")
 
     def _s(self):
         return torch.cuda.current_stream(self.device).cuda_stream
+
+    # ---------------------------------------------------------------- bf16 mirrors
+    def mirror(self, base: Tensor) -> None:
+        """Registers a bf16 mirror for the contiguous fp32 buffer `base` (no-op in fp32 precision).  Keeping the mirror equal to
+        bf16(base) is the caller's contract: kernels with a `*_bf16` side output maintain it for free, any other writer is followed
+        by `refresh`.  $DV3_MIRROR_CHECK=1 verifies the contract at every contraction (eager runs)."""
+        if not self.use_mirrors:
+            return
+        assert base.is_contiguous() and base.dtype == torch.float32 and base.data_ptr() % 16 == 0
+        start = base.data_ptr()
+        i = bisect.bisect_right(self._mir_start, start)
+        if i > 0 and start < self._mir[i - 1][1]:
+            return                                      # already covered
+        m = torch.zeros(base.numel(), dtype=torch.bfloat16, device=self.device)
+        self._mir_start.insert(i, start)
+        self._mir.insert(i, (start, start + base.numel() * 4, m))
+
+    def _m16(self, ptr: Optional[int]) -> Optional[int]:
+        """Address of the bf16 mirror element that shadows the fp32 element at `ptr` (None when there is no mirror)."""
+        if not self._mir or ptr is None:
+            return None
+        i = bisect.bisect_right(self._mir_start, ptr) - 1
+        if i < 0:
+            return None
+        start, end, m = self._mir[i]
+        return m.data_ptr() + (ptr - start) // 2 if ptr < end else None
+
+    def _m16_view(self, t: Tensor) -> Optional[Tensor]:
+        i = bisect.bisect_right(self._mir_start, t.data_ptr()) - 1
+        if i < 0 or t.data_ptr() >= self._mir[i][1]:
+            return None
+        start, _, m = self._mir[i]
+        return m.as_strided(t.shape, t.stride(), (t.data_ptr() - start) // 4)
+
+    def refresh(self, t: Tensor) -> None:
+        """mirror(t) <- bf16(t) for a 1-D contiguous or 2-D view of a mirrored buffer (no-op when t has no mirror)."""
+        m = self._m16(t.data_ptr())
+        if m is None:
+            return
+        if t.dim() == 1:
+            R, Cc, ld = 1, t.numel(), t.numel()
+        else:
+            _, R, Cc, ld = _mat(t)
+        self.launches += 1
+        _chk(self.lib.dv3_f32_to_bf16(R, Cc, t.data_ptr(), ld, m, ld, self._s()), "dv3_f32_to_bf16")
+
+    def _check_mirror(self, t: Tensor, what: str) -> None:
+        mv = self._m16_view(t)
+        if not torch.equal(mv, t.bfloat16()):
+            bad = (mv.float() - t.bfloat16().float()).abs().max().item()
+            raise Dv3Error(f"stale bf16 mirror for {what} {tuple(t.shape)} (max |diff| {bad})")
 
     # ---------------------------------------------------------------- contractions
     def gemm(self, mode, A, B, Cm, bias=None, accumulate=False):
@@ -177,14 +238,29 @@ class CudaOps:
         if self.gemm_log is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(torch.cuda.current_stream(self.device))
-        if self.precision == "bf16" and N >= 32 and K >= 32 and (M >= 128 or (mode == "TN" and M >= 16 and K >= 2048)):
-            _chk(self.lib.dv3_gemm_bf16_tc(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()),
-                 "dv3_gemm_bf16_tc")
+        kern = "simt"
+        ma = mb = None
+        if self.use_mirrors and N >= 32 and K >= 32 and (M >= 128 or (mode == "TN" and K >= 2048)):
+            ma, mb = self._m16(pa), self._m16(pb)
+            if ma is None or mb is None or ((lda | ldb) & 7) or ((ma | mb) & 15):
+                ma = mb = None
+        if self.precision == "bf16" and N >= 32 and K >= 32 and (ma is not None or M >= 128 or (mode == "TN" and M >= 16 and K >= 2048)):
+            if ma is not None:
+                if self.mirror_check:
+                    self._check_mirror(A, f"A of {mode} M{M} N{N} K{K}")
+                    self._check_mirror(B, f"B of {mode} M{M} N{N} K{K}")
+                kern = "tma"
+                _chk(self.lib.dv3_gemm_bf16_tma(_MODE[mode], M, N, K, ma, lda, mb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()),
+                     "dv3_gemm_bf16_tma")
+            else:
+                kern = "tc"
+                _chk(self.lib.dv3_gemm_bf16_tc(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()),
+                     "dv3_gemm_bf16_tc")
         else:
             _chk(self.lib.dv3_gemm_f32(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()), "dv3_gemm_f32")
         if self.gemm_log is not None:
             e1.record(torch.cuda.current_stream(self.device))
-            self.gemm_log.append((e0, e1, 2.0 * M * N * K, M, N, K, mode))
+            self.gemm_log.append((e0, e1, 2.0 * M * N * K, M, N, K, mode, kern))
 
     def transpose(self, src, dst):
         ps, R, Cc, lds = _mat(src)
@@ -198,6 +274,7 @@ class CudaOps:
         assert (R, Cc) == (R2, C2)
         self.launches += 1
         _chk(self.lib.dv3_copy2d(R, Cc, ps, lds, pd, ldd, self._s()), "dv3_copy2d")
+        self.refresh(dst)
 
     # ---------------------------------------------------------------- LayerNorm
     def ln_act_fwd(self, x, gamma, beta, eps, act, y, mean, rstd):
@@ -205,7 +282,7 @@ class CudaOps:
         py, _, _, ldy = _mat(y)
         self.launches += 1
         fn = self.lib.dv3_ln_act_fwd_rows if (U <= 1024 and M >= 256) else self.lib.dv3_ln_act_fwd
-        _chk(fn(M, U, px, ldx, _p(gamma), _p(beta), eps, act, py, ldy, _p(mean), _p(rstd), self._s()), "dv3_ln_act_fwd")
+        _chk(fn(M, U, px, ldx, _p(gamma), _p(beta), eps, act, py, ldy, _p(mean), _p(rstd), self._m16(py), self._s()), "dv3_ln_act_fwd")
 
     def ln_act_bwd(self, dy, x, gamma, beta, mean, rstd, act, dx, dln):
         pdy, M, U, lddy = _mat(dy)
@@ -214,7 +291,8 @@ class CudaOps:
         pdl, lddl = (None, 0) if dln is None else (_mat(dln)[0], _mat(dln)[3])
         self.launches += 1
         fn = self.lib.dv3_ln_act_bwd_rows if (U <= 1024 and M >= 256) else self.lib.dv3_ln_act_bwd
-        _chk(fn(M, U, pdy, lddy, px, ldx, _p(gamma), _p(beta), _p(mean), _p(rstd), act, pdx, lddx, pdl, lddl, self._s()), "dv3_ln_act_bwd")
+        _chk(fn(M, U, pdy, lddy, px, ldx, _p(gamma), _p(beta), _p(mean), _p(rstd), act, pdx, lddx, pdl, lddl, self._m16(pdx), self._s()),
+             "dv3_ln_act_bwd")
 
     def ln_param_grad(self, dln, x, mean, rstd, dgamma, dbeta):
         pd, M, U, ldd = _mat(dln)
@@ -266,8 +344,8 @@ class CudaOps:
         phi, _, _, ldhi = _mat(h_in)
         pho, _, _, ldho = _mat(h_out)
         self.launches += 1
-        _chk(self.lib.dv3_gru_gate_fwd(R, D3 // 3, pg, ldg, _p(lnw), _p(lnb), phi, ldhi, pho, ldho, _p(mean), _p(rstd), self._s()),
-             "dv3_gru_gate_fwd")
+        _chk(self.lib.dv3_gru_gate_fwd(R, D3 // 3, pg, ldg, _p(lnw), _p(lnb), phi, ldhi, pho, ldho, _p(mean), _p(rstd),
+                                       self._m16(pho), self._s()), "dv3_gru_gate_fwd")
 
     def gru_gate_bwd(self, dh_out, gates_pre, lnw, lnb, mean, rstd, h_in, dgates_pre, dln, dh_in):
         pdo, R, D, lddo = _mat(dh_out)
@@ -296,7 +374,8 @@ class CudaOps:
         pi, _, _, ldi = _mat(idx)
         po, _, _, ldo = _mat(onehot)
         self.launches += 1
-        _chk(self.lib.dv3_sample_onehot(R, groups, K, pl, ldl, pu, ldu, pf, ldf, mode, pi, ldi, po, ldo, self._s()), "dv3_sample_onehot")
+        _chk(self.lib.dv3_sample_onehot(R, groups, K, pl, ldl, pu, ldu, pf, ldf, mode, pi, ldi, po, ldo, self._m16(po), self._s()),
+             "dv3_sample_onehot")
 
     def unimix_bwd(self, raw, groups, K, unimix, dlogits, dz, draw):
         pr, R, _, ldr = _mat(raw)

@@ -9,6 +9,7 @@
 // contiguous channel runs; the 16 kernel taps are the slow index of the contraction dimension (k = tap*C + c), and the
 // torch-layout weights ([Cout][Cin][4][4] / [Cin][Cout][4][4]) are re-ordered once per step with dv3_permute_last2.
 #include "common.cuh"
+#include <cuda_bf16.h>
 
 namespace {
 
@@ -94,7 +95,7 @@ constexpr int LW_WARPS = 8;
 __global__ void __launch_bounds__(LW_WARPS * 32)
 ln_act_fwd_warp_kernel(int M, int U, const float* __restrict__ x, int ldx, const float* __restrict__ gamma,
                        const float* __restrict__ beta, float eps, int act, float* __restrict__ y, int ldy,
-                       float* __restrict__ mean, float* __restrict__ rstd) {
+                       float* __restrict__ mean, float* __restrict__ rstd, __nv_bfloat16* __restrict__ y16) {
   const int lane = threadIdx.x & 31;
   const size_t row = (size_t)blockIdx.x * LW_WARPS + (threadIdx.x >> 5);
   if (row >= (size_t)M) return;
@@ -108,7 +109,9 @@ ln_act_fwd_warp_kernel(int M, int U, const float* __restrict__ x, int ldx, const
   float* yr = y + row * ldy;
   for (int i = lane; i < U; i += 32) {
     const float ln = (xr[i] - mu) * rs * __ldg(gamma + i) + __ldg(beta + i);
-    yr[i] = act ? siluf_(ln) : ln;
+    const float o = act ? siluf_(ln) : ln;
+    yr[i] = o;
+    if (y16) y16[row * ldy + i] = __float2bfloat16_rn(o);
   }
   if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
 }
@@ -117,7 +120,7 @@ __global__ void __launch_bounds__(LW_WARPS * 32)
 ln_act_bwd_warp_kernel(int M, int U, const float* __restrict__ dy, int lddy, const float* __restrict__ x, int ldx,
                        const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
                        const float* __restrict__ rstd, int act, float* __restrict__ dx, int lddx, float* __restrict__ dln,
-                       int lddln) {
+                       int lddln, __nv_bfloat16* __restrict__ dx16) {
   const int lane = threadIdx.x & 31;
   const size_t row = (size_t)blockIdx.x * LW_WARPS + (threadIdx.x >> 5);
   if (row >= (size_t)M) return;
@@ -148,7 +151,9 @@ ln_act_bwd_warp_kernel(int M, int U, const float* __restrict__ dy, int lddy, con
       const float sg = sigmoidf_(ln);
       g *= sg * (1.f + ln * (1.f - sg));
     }
-    dx[row * lddx + i] = rs * (g * __ldg(gamma + i) - s1 - xh * s2);
+    const float o = rs * (g * __ldg(gamma + i) - s1 - xh * s2);
+    dx[row * lddx + i] = o;
+    if (dx16) dx16[row * lddx + i] = __float2bfloat16_rn(o);
   }
 }
 
@@ -206,19 +211,20 @@ int dv3_u8_nchw_to_nhwc(int N, int C, int HW, const unsigned char* src, float sc
   return DV3_OK;
 }
 int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
-                        float* y, int ldy, float* mean, float* rstd, void* stream) {
+                        float* y, int ldy, float* mean, float* rstd, void* y_bf16, void* stream) {
   if (M <= 0 || U <= 0) return DV3_ERR_ARG;
-  ln_act_fwd_warp_kernel<<<(M + LW_WARPS - 1) / LW_WARPS, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(M, U, x, ldx, gamma, beta, eps, act,
-                                                                                                  y, ldy, mean, rstd);
+  ln_act_fwd_warp_kernel<<<(M + LW_WARPS - 1) / LW_WARPS, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(
+      M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }
 int dv3_ln_act_bwd_rows(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
-                        const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* stream) {
+                        const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* dx_bf16,
+                        void* stream) {
   if (M <= 0 || U <= 0) return DV3_ERR_ARG;
   if ((const void*)dx == (const void*)dy) return DV3_ERR_ARG;
   ln_act_bwd_warp_kernel<<<(M + LW_WARPS - 1) / LW_WARPS, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(
-      M, U, dy, lddy, x, ldx, gamma, beta, mean, rstd, act, dx, lddx, dln, lddln);
+      M, U, dy, lddy, x, ldx, gamma, beta, mean, rstd, act, dx, lddx, dln, lddln, reinterpret_cast<__nv_bfloat16*>(dx_bf16));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

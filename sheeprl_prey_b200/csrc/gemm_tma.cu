@@ -1,6 +1,9 @@
 // bf16-resident tensor-core contraction: TMA-fed tcgen05 GEMM.
 //
-//   C[M,N] (+)= A[M,K] * B[N,K]^T (+ bias)      A, B bf16 in HBM (K contiguous), C fp32.
+//   NT: C[M,N] (+)= A[M,K] * B[N,K]^T (+ bias)     forward      (both operands K-contiguous)
+//   NN: C[M,N] (+)= A[M,K] * B[K,N]                input grad   (B is N-contiguous: MN-major UMMA operand)
+//   TN: C[M,N] (+)= A[K,M]^T * B[K,N]              weight grad  (both MN-major; K = rows of the batch, split over CTAs)
+// A, B bf16 in HBM, C fp32.
 //
 // Used by the forward passes whose operands already live in bf16 (activations written in bf16 by the LayerNorm / GRU / sampling
 // kernels, bf16 weight shadows refreshed after every Adam step): the imagination rollout, the value / reward / continue heads on
@@ -11,6 +14,9 @@
 //   warp 0 : TMA producer (one lane)        warp 1 : TMEM allocator + tcgen05.mma issuer (one lane)
 //   warps 2-5 : epilogue (tcgen05.ld -> shared-memory transpose -> coalesced global stores / accumulate)
 // Out-of-range rows / columns / k are zero-filled by the TMA unit, so ragged M, N, K need no special cases in the main loop.
+// An MN-major operand tile is two boxes of 64 (mn) x 64 (k): 128-byte rows indexed by k, which is exactly the canonical
+// SWIZZLE_128B MN-major layout (LBO 8 KB between the 64-wide mn halves, SBO 1 KB between 8-deep k groups).
+// Split-K (grid.z) for contractions with few output tiles: partial sums are reduced with fp32 atomics into a zeroed C.
 #include "common.cuh"
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -61,10 +67,26 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {   // K-
   d |= (uint64_t)2 << 61;
   return d;
 }
+__device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t smem_addr) {   // MN-major SWIZZLE_128B: LBO 8192, SBO 1024
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)(8192 >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
 
+__global__ void zero2d_tma_kernel(int M, int N, float* __restrict__ C, int ldc) {
+  const size_t n = (size_t)M * N;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    C[(i / N) * ldc + (i % N)] = 0.f;
+}
+
+template <bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
-                     float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+                     float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int kb_per_split) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_a = smem;
@@ -76,7 +98,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * TBN;
-  const int num_kb = (K + TBK - 1) / TBK;
+  const int total_kb = (K + TBK - 1) / TBK;
+  const int kb0 = blockIdx.z * kb_per_split;
+  const int num_kb = min(kb_per_split, total_kb - kb0);
+  const bool split = gridDim.z > 1;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
@@ -102,13 +127,25 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
         mbar_wait(&empty_bar[s], ph ^ 1u);
         mbar_expect_tx(&full_bar[s], STAGE_A_BYTES + STAGE_B_BYTES);
-        tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], kb * TBK, m0);
-        tma_load_2d(smem_b + s * STAGE_B_BYTES, &tmB, &full_bar[s], kb * TBK, n0);
+        const int k0 = (kb0 + kb) * TBK;
+        if (A_MN) {
+          tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], m0, k0);
+          tma_load_2d(smem_a + s * STAGE_A_BYTES + 8192, &tmA, &full_bar[s], m0 + 64, k0);
+        } else {
+          tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], k0, m0);
+        }
+        if (B_MN) {
+          tma_load_2d(smem_b + s * STAGE_B_BYTES, &tmB, &full_bar[s], n0, k0);
+          tma_load_2d(smem_b + s * STAGE_B_BYTES + 8192, &tmB, &full_bar[s], n0 + 64, k0);
+        } else {
+          tma_load_2d(smem_b + s * STAGE_B_BYTES, &tmB, &full_bar[s], k0, n0);
+        }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                           ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % STAGES;
       const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
@@ -119,8 +156,9 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const uint32_t b_addr = smem_u32(smem_b + s * STAGE_B_BYTES);
 #pragma unroll
         for (int k = 0; k < TBK / 16; ++k) {
-          const uint64_t adesc = make_smem_desc(a_addr + k * 32);
-          const uint64_t bdesc = make_smem_desc(b_addr + k * 32);
+          // K-major: 16 bf16 = 32 B along K inside the swizzle atom.  MN-major: 16 k = two 1 KB k-groups.
+          const uint64_t adesc = A_MN ? make_smem_desc_mn(a_addr + k * 2048) : make_smem_desc(a_addr + k * 32);
+          const uint64_t bdesc = B_MN ? make_smem_desc_mn(b_addr + k * 2048) : make_smem_desc(b_addr + k * 32);
           const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
           asm volatile(
               "{\n"
@@ -163,7 +201,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       __syncwarp();
       const int gn = n0 + c0 + lane;
       const bool col_ok = gn < N;
-      const float bv = (bias && col_ok) ? __ldg(bias + gn) : 0.f;
+      const float bv = (bias && col_ok && (!split || blockIdx.z == 0)) ? __ldg(bias + gn) : 0.f;
       const int rows_here = col_ok ? min(32, M - (m0 + ew * 32)) : 0;
       float* dst0 = C + (size_t)(m0 + ew * 32) * ldc + gn;
       float o[32];
@@ -172,7 +210,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       const bool full = __all_sync(0xffffffffu, rows_here == 32);
       const size_t ld = (size_t)ldc;
       if (full) {
-        if (accumulate) {
+        if (split) {
+#pragma unroll
+          for (int rr = 0; rr < 32; ++rr) atomicAdd(dst0 + rr * ld, o[rr]);
+        } else if (accumulate) {
           float old[32];
 #pragma unroll
           for (int rr = 0; rr < 32; ++rr) old[rr] = dst0[rr * ld];
@@ -186,7 +227,8 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 #pragma unroll 1
         for (int rr = 0; rr < rows_here; ++rr) {
           float* d = dst0 + rr * ld;
-          *d = accumulate ? (*d + o[rr]) : o[rr];
+          if (split) atomicAdd(d, o[rr]);
+          else *d = accumulate ? (*d + o[rr]) : o[rr];
         }
       }
       __syncwarp();
@@ -207,11 +249,12 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
 
-// [rows, K] bf16, K contiguous, row stride ld elements -> 2-D tensor map with a 64 (k) x 128 (rows) SWIZZLE_128B box
-int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld) {
-  const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+// K-major operand: [rows, K] bf16, K contiguous, row stride ld -> box 64 (k) x 128 (rows).
+// MN-major operand: [K, rows] bf16, rows contiguous, row stride ld -> box 64 (rows) x 64 (k); two boxes per tile.
+int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld, bool mn_major) {
+  const cuuint64_t dims[2] = {(cuuint64_t)(mn_major ? rows : K), (cuuint64_t)(mn_major ? K : rows)};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  const cuuint32_t box[2] = {TBK, TBM};
+  const cuuint32_t box[2] = {64, (cuuint32_t)(mn_major ? TBK : TBM)};
   const cuuint32_t estr[2] = {1, 1};
   CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -219,9 +262,50 @@ int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld) {
   return r == CUDA_SUCCESS ? 0 : 1000 + (int)r;
 }
 
+template <bool A_MN, bool B_MN>
+int launch_tma(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc, const float* bias,
+               int accumulate, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  CUtensorMap tmA, tmB;
+  int rc = make_map(&tmA, A, M, K, lda, A_MN);
+  if (rc) return rc;
+  rc = make_map(&tmB, B, N, K, ldb, B_MN);
+  if (rc) return rc;
+  dim3 grid((N + TBN - 1) / TBN, (M + TBM - 1) / TBM, 1);
+  if (grid.y > 65535) return DV3_ERR_UNSUPPORTED;
+  // split-K when the output has too few tiles to fill the 148 SMs (weight gradients: K = T*B*H rows; small-batch forwards)
+  const int total_kb = (K + TBK - 1) / TBK;
+  const int tiles = (int)(grid.x * grid.y);
+  int splits = 1;
+  if (tiles < 120 && total_kb >= 32) {
+    splits = (296 + tiles - 1) / tiles;
+    if (splits > total_kb / 4) splits = total_kb / 4;
+    if (splits > 64) splits = 64;
+    if (splits < 1) splits = 1;
+  }
+  int kb_per_split = (total_kb + splits - 1) / splits;
+  splits = (total_kb + kb_per_split - 1) / kb_per_split;
+  grid.z = splits;
+  if (splits > 1 && !accumulate) {
+    size_t n = (size_t)M * N;
+    int zb = (int)((n + 255) / 256);
+    if (zb > 1184) zb = 1184;
+    zero2d_tma_kernel<<<zb, 256, 0, stream>>>(M, N, C, ldc);
+    DV3_LAUNCH_CHECK();
+  }
+  gemm_bf16_tma_kernel<A_MN, B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tmA, tmB, M, N, K, C, ldc, bias, accumulate, kb_per_split);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+
 }  // namespace
 
-extern "C" int dv3_gemm_bf16_tma(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc,
+extern "C" int dv3_gemm_bf16_tma(int mode, int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc,
                                  const float* bias, int accumulate, void* stream_) {
   if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !C) return DV3_ERR_ARG;
   // TMA: 16 B aligned base addresses and row strides
@@ -232,37 +316,67 @@ extern "C" int dv3_gemm_bf16_tma(int M, int N, int K, const void* A, int lda, co
     cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
     if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return DV3_ERR_UNSUPPORTED;
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
-    e = cudaFuncSetAttribute(gemm_bf16_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
   }
-  CUtensorMap tmA, tmB;
-  int rc = make_map(&tmA, A, M, K, lda);
-  if (rc) return rc;
-  rc = make_map(&tmB, B, N, K, ldb);
-  if (rc) return rc;
-  dim3 grid((N + TBN - 1) / TBN, (M + TBM - 1) / TBM, 1);
-  if (grid.y > 65535) return DV3_ERR_UNSUPPORTED;
-  gemm_bf16_tma_kernel<<<grid, NUM_THREADS, SMEM_BYTES, (cudaStream_t)stream_>>>(tmA, tmB, M, N, K, C, ldc, bias, accumulate);
-  DV3_LAUNCH_CHECK();
-  return DV3_OK;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  switch (mode) {
+    case 0: return launch_tma<false, false>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    case 1: return launch_tma<false, true>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    case 2: return launch_tma<true, true>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+    default: return DV3_ERR_ARG;
+  }
 }
 
-// fp32 -> bf16 (round to nearest even), 2-D with leading dimensions: weight shadows and operand staging
+// fp32 -> bf16 (round to nearest even), 2-D with leading dimensions: refresh of a bf16 mirror after a writer without a
+// fused bf16 side output (weight arenas after Adam, scan products, strided copies).
 namespace {
-__global__ void f32_to_bf16_kernel(int R, int Cc, const float* __restrict__ s, int lds, __nv_bfloat16* __restrict__ d, int ldd) {
-  const size_t n = (size_t)R * Cc;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-    const int r = (int)(i / Cc), c = (int)(i % Cc);
-    d[(size_t)r * ldd + c] = __float2bfloat16_rn(s[(size_t)r * lds + c]);
+__global__ void __launch_bounds__(256) f32_to_bf16_vec_kernel(size_t n4, const float4* __restrict__ s, uint2* __restrict__ d) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 v = __ldg(s + i);
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo);
+    o.y = *reinterpret_cast<uint32_t*>(&hi);
+    d[i] = o;
+  }
+}
+// one row per blockIdx.y step, columns vectorised by 4 when the row starts stay 16 B (source) / 8 B (destination) aligned
+__global__ void __launch_bounds__(256) f32_to_bf16_rows_kernel(int R, int Cc, const float* __restrict__ s, int lds,
+                                                               __nv_bfloat16* __restrict__ d, int ldd, int vec) {
+  for (int r = blockIdx.y; r < R; r += gridDim.y) {
+    const float* sr = s + (size_t)r * lds;
+    __nv_bfloat16* dr = d + (size_t)r * ldd;
+    if (vec) {
+      for (int c = (blockIdx.x * blockDim.x + threadIdx.x) * 4; c < Cc; c += gridDim.x * blockDim.x * 4) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(sr + c));
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 o;
+        o.x = *reinterpret_cast<uint32_t*>(&lo);
+        o.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(dr + c) = o;
+      }
+    } else {
+      for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < Cc; c += gridDim.x * blockDim.x) dr[c] = __float2bfloat16_rn(sr[c]);
+    }
   }
 }
 }  // namespace
 
 extern "C" int dv3_f32_to_bf16(int R, int Cc, const float* src, int lds, void* dst, int ldd, void* stream) {
-  if (R <= 0 || Cc <= 0) return DV3_ERR_ARG;
-  size_t g = ((size_t)R * Cc + 255) / 256;
-  if (g > 148 * 16) g = 148 * 16;
-  f32_to_bf16_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(R, Cc, src, lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd);
+  if (R <= 0 || Cc <= 0 || !src || !dst) return DV3_ERR_ARG;
+  const bool aligned = (((uintptr_t)src & 15) == 0) && (((uintptr_t)dst & 7) == 0);
+  if ((R == 1 || (lds == Cc && ldd == Cc)) && aligned && (((size_t)R * Cc) & 3) == 0) {
+    const size_t n4 = (size_t)R * Cc / 4;
+    size_t g = (n4 + 255) / 256;
+    if (g > 148 * 8) g = 148 * 8;
+    f32_to_bf16_vec_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(n4, reinterpret_cast<const float4*>(src),
+                                                                      reinterpret_cast<uint2*>(dst));
+  } else {
+    const int vec = aligned && (Cc & 3) == 0 && (lds & 3) == 0 && (ldd & 3) == 0;
+    const int per_row = vec ? Cc / 4 : Cc;
+    dim3 grid((per_row + 255) / 256, R > 4096 ? 4096 : R);
+    if (grid.x > 64) grid.x = 64;
+    f32_to_bf16_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(R, Cc, src, lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd, vec);
+  }
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -10,6 +10,7 @@
 //   REINFORCE + entropy actor objective        : sheeprl/algos/dreamer_v3/dreamer_v3.py:292-317
 // One warp owns one categorical group / one row; reductions are warp shuffles.
 #include "common.cuh"
+#include <cuda_bf16.h>
 
 namespace {
 
@@ -98,7 +99,7 @@ template <int KRT>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
 sample_onehot_kernel(int R, int groups, int K, const float* __restrict__ logits, int ldl, const float* __restrict__ u, int ldu,
                      const int* __restrict__ forced, int ldf, int mode, int* __restrict__ idx, int ldi,
-                     float* __restrict__ onehot, int ldo) {
+                     float* __restrict__ onehot, int ldo, __nv_bfloat16* __restrict__ onehot16) {
   __shared__ float sp[WARPS_PER_BLOCK][KR * 32];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int gid = blockIdx.x * WARPS_PER_BLOCK + w;
@@ -130,6 +131,10 @@ sample_onehot_kernel(int R, int groups, int K, const float* __restrict__ logits,
   if (lane == 0) idx[(size_t)row * ldi + g] = choice;
   float* o = onehot + (size_t)row * ldo + g * K;
   for_k<KRT>(K, lane, [&](int, int k) { o[k] = (k == choice) ? 1.f : 0.f; });
+  if (onehot16) {
+    __nv_bfloat16* o16 = onehot16 + (size_t)row * ldo + g * K;
+    for_k<KRT>(K, lane, [&](int, int k) { o16[k] = __float2bfloat16_rn((k == choice) ? 1.f : 0.f); });
+  }
 }
 
 // ---------------------------------------------------------------- unimix backward (+ straight-through)
@@ -518,12 +523,12 @@ int dv3_unimix_fwd(int R, int groups, int K, float mix, const float* raw, int ld
   return DV3_OK;
 }
 int dv3_sample_onehot(int R, int groups, int K, const float* logits, int ldl, const float* u, int ldu, const int* forced,
-                      int ldf, int mode, int* idx, int ldi, float* onehot, int ldo, void* stream) {
+                      int ldf, int mode, int* idx, int ldi, float* onehot, int ldo, void* onehot_bf16, void* stream) {
   if (R <= 0 || groups <= 0 || K <= 0) return DV3_ERR_ARG;
   if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
   if (!forced && !mode && !u) return DV3_ERR_ARG;
   DV3_DISPATCH_KR(K, sample_onehot_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
-      R, groups, K, logits, ldl, u, ldu, forced, ldf, mode, idx, ldi, onehot, ldo));
+      R, groups, K, logits, ldl, u, ldu, forced, ldf, mode, idx, ldi, onehot, ldo, reinterpret_cast<__nv_bfloat16*>(onehot_bf16)));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -4,6 +4,7 @@
 // sheeprl/utils/model.py:71-87); LayerNormGRUCell sheeprl/models/models.py:388-395; symlog
 // sheeprl/utils/utils.py:120-121; reset masking sheeprl/algos/dreamer_v3/agent.py:379-384.
 #include "common.cuh"
+#include <cuda_bf16.h>
 
 namespace {
 
@@ -13,7 +14,7 @@ constexpr int ROW_THREADS = 256;
 __global__ void __launch_bounds__(ROW_THREADS)
 ln_act_fwd_kernel(int U, const float* __restrict__ x, int ldx, const float* __restrict__ gamma,
                   const float* __restrict__ beta, float eps, int act, float* __restrict__ y, int ldy,
-                  float* __restrict__ mean, float* __restrict__ rstd) {
+                  float* __restrict__ mean, float* __restrict__ rstd, __nv_bfloat16* __restrict__ y16) {
   __shared__ float red[64];
   const int row = blockIdx.x;
   const float* xr = x + (size_t)row * ldx;
@@ -27,7 +28,9 @@ ln_act_fwd_kernel(int U, const float* __restrict__ x, int ldx, const float* __re
   float* yr = y + (size_t)row * ldy;
   for (int i = threadIdx.x; i < U; i += blockDim.x) {
     float ln = (xr[i] - mu) * rs * gamma[i] + beta[i];
-    yr[i] = act ? siluf_(ln) : ln;
+    const float o = act ? siluf_(ln) : ln;
+    yr[i] = o;
+    if (y16) y16[(size_t)row * ldy + i] = __float2bfloat16_rn(o);      // bf16 mirror for the next contraction
   }
   if (threadIdx.x == 0) { mean[row] = mu; rstd[row] = rs; }
 }
@@ -37,7 +40,7 @@ __global__ void __launch_bounds__(ROW_THREADS)
 ln_act_bwd_kernel(int U, const float* __restrict__ dy, int lddy, const float* __restrict__ x, int ldx,
                   const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
                   const float* __restrict__ rstd, int act, float* __restrict__ dx, int lddx,
-                  float* __restrict__ dln, int lddln) {
+                  float* __restrict__ dln, int lddln, __nv_bfloat16* __restrict__ dx16) {
   __shared__ float red[64];
   const int row = blockIdx.x;
   const float* xr = x + (size_t)row * ldx;
@@ -69,7 +72,9 @@ ln_act_bwd_kernel(int U, const float* __restrict__ dy, int lddy, const float* __
       g *= sg * (1.f + ln * (1.f - sg));
     }
     const float gg = g * gamma[i];
-    dx[(size_t)row * lddx + i] = rs * (gg - m1 - xh * m2);
+    const float o = rs * (gg - m1 - xh * m2);
+    dx[(size_t)row * lddx + i] = o;
+    if (dx16) dx16[(size_t)row * lddx + i] = __float2bfloat16_rn(o);
   }
 }
 
@@ -118,7 +123,7 @@ __global__ void col_reduce_stage2(int U, int nchunks, const float* __restrict__ 
 __global__ void __launch_bounds__(ROW_THREADS)
 gru_gate_fwd_kernel(int D, const float* __restrict__ gp, int ldg, const float* __restrict__ lnw,
                     const float* __restrict__ lnb, const float* __restrict__ h_in, int ldhi, float* __restrict__ h_out,
-                    int ldho, float* __restrict__ mean, float* __restrict__ rstd) {
+                    int ldho, float* __restrict__ mean, float* __restrict__ rstd, __nv_bfloat16* __restrict__ h16) {
   __shared__ float red[64];
   const int row = blockIdx.x, U3 = 3 * D;
   const float* g = gp + (size_t)row * ldg;
@@ -134,7 +139,9 @@ gru_gate_fwd_kernel(int D, const float* __restrict__ gp, int ldg, const float* _
     const float c = tanhf(r * cp);
     const float u = sigmoidf_((g[2 * D + d] - mu) * rs * lnw[2 * D + d] + lnb[2 * D + d] - 1.f);
     const float h = h_in[(size_t)row * ldhi + d];
-    h_out[(size_t)row * ldho + d] = u * c + (1.f - u) * h;
+    const float o = u * c + (1.f - u) * h;
+    h_out[(size_t)row * ldho + d] = o;
+    if (h16) h16[(size_t)row * ldho + d] = __float2bfloat16_rn(o);
   }
   if (threadIdx.x == 0) { mean[row] = mu; rstd[row] = rs; }
 }
@@ -255,20 +262,21 @@ static inline int grid_for(size_t n, int threads) {
 extern "C" {
 
 int dv3_ln_act_fwd(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
-                   float* y, int ldy, float* mean, float* rstd, void* stream) {
+                   float* y, int ldy, float* mean, float* rstd, void* y_bf16, void* stream) {
   if (M <= 0 || U <= 0) return DV3_ERR_ARG;
-  ln_act_fwd_kernel<<<M, ROW_THREADS, 0, (cudaStream_t)stream>>>(U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd);
+  ln_act_fwd_kernel<<<M, ROW_THREADS, 0, (cudaStream_t)stream>>>(U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd,
+                                                                reinterpret_cast<__nv_bfloat16*>(y_bf16));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }
 
 int dv3_ln_act_bwd(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma,
                    const float* beta, const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln,
-                   int lddln, void* stream) {
+                   int lddln, void* dx_bf16, void* stream) {
   if (M <= 0 || U <= 0) return DV3_ERR_ARG;
   if ((const void*)dx == (const void*)dy) return DV3_ERR_ARG;  // two passes read dy after dx is written
   ln_act_bwd_kernel<<<M, ROW_THREADS, 0, (cudaStream_t)stream>>>(U, dy, lddy, x, ldx, gamma, beta, mean, rstd, act, dx,
-                                                                lddx, dln, lddln);
+                                                                lddx, dln, lddln, reinterpret_cast<__nv_bfloat16*>(dx_bf16));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }
@@ -343,10 +351,11 @@ int dv3_col_reduce_noalloc(int M, int U, const float* d, int ldd, const float* x
 }
 
 int dv3_gru_gate_fwd(int R, int D, const float* gates_pre, int ldg, const float* lnw, const float* lnb,
-                     const float* h_in, int ldhi, float* h_out, int ldho, float* mean, float* rstd, void* stream) {
+                     const float* h_in, int ldhi, float* h_out, int ldho, float* mean, float* rstd, void* h_out_bf16,
+                     void* stream) {
   if (R <= 0 || D <= 0) return DV3_ERR_ARG;
   gru_gate_fwd_kernel<<<R, ROW_THREADS, 0, (cudaStream_t)stream>>>(D, gates_pre, ldg, lnw, lnb, h_in, ldhi, h_out, ldho,
-                                                                  mean, rstd);
+                                                                  mean, rstd, reinterpret_cast<__nv_bfloat16*>(h_out_bf16));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -42,6 +42,23 @@ def _round_up(n: int, m: int) -> int:
     return (n + m - 1) // m * m
 
 
+def _mirror(ops, *tensors: Tensor) -> None:
+    """Asks the ops object for a bf16 mirror of each buffer (CudaOps in bf16 precision; see CudaOps.mirror).  Contractions whose
+    operands are both mirrored read bf16 through TMA; every writer of a mirrored buffer either has a fused bf16 side output or
+    is followed by `_refresh`."""
+    fn = getattr(ops, "mirror", None)
+    if fn is not None:
+        for t in tensors:
+            fn(t)
+
+
+def _refresh(ops, *views: Tensor) -> None:
+    fn = getattr(ops, "refresh", None)
+    if fn is not None:
+        for v in views:
+            fn(v)
+
+
 class Arena:
     """One flat fp32 buffer holding every parameter of an optimizer group (+ grad, Adam m / v, step).
     Each named parameter is a view at a 256-byte-aligned offset."""
@@ -96,10 +113,12 @@ class DenseStack:
             self.rstd.append(torch.empty(rows, **f32))
         self.out_dim = sum(h["w"].shape[0] for h in heads)
         self.out = torch.empty(rows, self.out_dim, **f32) if heads else None
+        _mirror(ops, *[a for a in self.act if a is not last_act_out])
         if need_bwd:
             self._dact = torch.empty(rows * umax, **f32)
             self._dpre = torch.empty(rows * umax, **f32)
             self._dln = torch.empty(rows * umax, **f32)
+            _mirror(ops, self._dpre)
 
     def forward(self, x: Tensor, r0: int = 0, r1: Optional[int] = None) -> None:
         """Rows [r0, r1) of the stack's buffers <- stack(x); x is [r1-r0, in_dim]."""
@@ -216,7 +235,9 @@ class DV3Engine:
         f32 = dict(dtype=torch.float32, device=device)
         i32 = dict(dtype=torch.int32, device=device)
         z = lambda *s: torch.zeros(*s, **f32)  # noqa: E731
+        zp = lambda r, c: torch.zeros(r, _round_up(c, 8), **f32)[:, :c]  # noqa: E731  (row stride padded to 8: TMA-loadable mirror)
         P, Gd = wm.p, wm.g
+        _mirror(ops, wm.flat, actor.flat, critic.flat, target.flat)
 
         # ---------------- world-model buffers
         self.obs_cat, self.obs_sym = z(N, max(self.Od, 1)), z(N, max(self.Od, 1))
@@ -230,13 +251,16 @@ class DV3Engine:
         self.zreset, self.zreset_logits, self.zreset_idx = z(1, S), z(1, S), torch.zeros(1, self.G, **i32)
         self.zero_h = z(1, D)
         self.kl_rows, self.obs_rows, self.rew_rows, self.cont_rows = z(N, 4), z(N, 1), z(N, 1), z(N, 1)
-        self.d_rec, self.d_rew, self.d_cont = z(N, max(self.Od, 1)), z(N, self.bins), z(N, 1)
+        self.d_rec, self.d_rew, self.d_cont = zp(N, max(self.Od, 1)), zp(N, self.bins), z(N, 1)
         self.dpost_logits, self.dprior_logits, self.dlatent = z(N, S), z(N, S), z(N, lat)
         self.dpost_raw, self.dhidr_act, self.dhidr_pre, self.dln_r = z(N, S), z(B, Hh), z(N, Hh), z(N, Hh)
         self.dgates_pre, self.dln_gru, self.dh_direct, self.dx_gru = z(N, 3 * D), z(N, 3 * D), z(B, D), z(B, D + U)
         self.dfeat_pre, self.dln_feat, self.dz_prev, self.de = z(N, U), z(N, U), z(B, S), z(N, E)
         self.W_r1T, self.W_r0hT, self.W_gruT, self.W_mlpzT = z(Hh, S), z(D, Hh), z(D + U, 3 * D), z(S, U)
         self.eW = z(N, Hh)                       # e_t . Wr0[:, D:]^T + b_r0 for all t (hoisted out of the scan)
+        self.Wmlp_z = z(U, S)                    # compact copy of Wmlp[:, :S] for the rollout (row stride S+A is not TMA-loadable)
+        _mirror(ops, self.x_rep, self.x_gru, self.x_mlp, self.latent, self.hidr, self.Wmlp_z, self.dpost_raw, self.dhidr_pre,
+                self.dgates_pre, self.dfeat_pre, self.dprior_logits, self.d_rec._base, self.d_rew._base)
         self.use_fused_scan = hasattr(ops, "rssm_observe_fwd") and os.environ.get("DV3_FUSED_SCAN", "1") != "0"
         self.metrics = z(16)
         self.u_post = z(T, B, self.G)
@@ -302,6 +326,7 @@ class DV3Engine:
         self.tcrit_stack = DenseStack(ops, device, M0, lat, tc_l, tc_h, need_bwd=False)
         self.traj, self.acts = z(M1, lat), z(M1, A)
         self.img_feat_pre, self.img_feat, self.img_gates = z(N, U), z(N, U), z(N, 3 * D)
+        _mirror(ops, self.traj, self.img_feat)
         self.img_mean, self.img_rstd = z(N), z(N)
         self.img_logits, self.act_logits = z(N, S), z(N, A)
         self.z_idx = torch.zeros(H, N, self.G, **i32)
@@ -310,8 +335,9 @@ class DV3Engine:
         self.lam, self.discount = z(M0), z(M1)
         self.mom_state, self.mom_out = z(2), z(2)
         self.lam_all = z(M0 * (dist.world_size if dist is not None else 1))
-        self.pl_rows, self.d_actor_raw = z(M0, 1), z(M0, A)
-        self.vl_rows, self.d_crit = z(M0, 1), z(M0, self.bins)
+        self.pl_rows, self.d_actor_raw = z(M0, 1), zp(M0, A)
+        self.vl_rows, self.d_crit = z(M0, 1), zp(M0, self.bins)
+        _mirror(ops, self.d_actor_raw._base, self.d_crit._base)
 
     # ------------------------------------------------------------------ inputs
     def load_batch(self, data: Dict[str, Tensor]) -> None:
@@ -344,9 +370,11 @@ class DV3Engine:
         ops = self.ops
         T, B, N, S, D, U, E, A, lat = self.T, self.B, self.N, self.S, self.D, self.U, self.E, self.A, self.lat
         G, K, mix = self.G, self.K, self.cfg.algo.unimix
+        _refresh(ops, self.wm.flat)
         # a2/a3: symlog + encoder (embedding lands in x_rep[:, D:])
         if self.cnn_enc is not None:
             self.cnn_enc.forward()
+            _refresh(ops, self.x_rep[:, D:D + self.cnn_out])
         if self.enc is not None:
             ops.symlog(self.obs_cat, self.obs_sym)
             self.enc.forward(self.obs_sym)
@@ -384,6 +412,7 @@ class DV3Engine:
             ops.sample_onehot(self.post_logits[r], G, K, self.u_post[t].reshape(B, G),
                               None if forced_post_idx is None else forced_post_idx[r], 0,
                               self.post_idx[r], self.latent[r, :S])
+        _refresh(ops, self.x_rep[:, :D], self.x_gru, self.x_mlp, self.hidr, self.latent[:, :S])   # scan products
         ops.copy2d(self.x_rep[:, :D], self.latent[:, S:])
         # prior head, batched over all T*B rows
         self.trans.forward(self.x_rep[:, :D])
@@ -408,6 +437,7 @@ class DV3Engine:
         ops.bernoulli_loss(self.cont.out, self.dones, sc * w.continue_scale_factor, self.cont_rows.view(N), self.d_cont)
         ops.kl_balance(self.post_logits, self.prior_logits, self.G, self.K, w.kl_free_nats, w.kl_dynamic, w.kl_representation,
                        sc * w.kl_regularizer, self.kl_rows, self.dpost_logits, self.dprior_logits)
+        _refresh(ops, self.d_rec, self.d_rew)
         m = self.metrics
         first_obs = True
         if self.dec is not None:
@@ -447,6 +477,7 @@ class DV3Engine:
         self.cont.backward(self.latent, N, self.d_cont, dx=self.dlatent, dx_accumulate=True)
         # prior head (batched): d prior_logits -> d raw -> transition stack -> dh
         ops.unimix_bwd(self.trans.out, G, K, mix, self.dprior_logits, None, self.dprior_logits)
+        _refresh(ops, self.dprior_logits)
         self.trans.backward(self.x_rep[:, :D], N, self.dprior_logits, dx=self.dlatent[:, S:], dx_accumulate=True)
         # reverse scan: only dh / dz propagate sequentially
         for t in range(T - 1, -1, -1):
@@ -467,6 +498,7 @@ class DV3Engine:
                 ops.scan_carry(self.first[t], self.dz_prev, self.dx_gru[:, :D], self.dh_direct,
                                self.dlatent[rp, :S], self.dlatent[rp, S:])
         # parameter gradients of the scan, one K = T*B contraction each
+        _refresh(ops, self.dpost_raw, self.dgates_pre)          # (dhidr_pre / dfeat_pre mirrors are written by ln_act_bwd)
         rpfx = "rssm.representation_model._model."
         ops.gemm("TN", self.dpost_raw, self.hidr, Gd[rpfx + "3.weight"])
         ops.colsum(self.dpost_raw, Gd[rpfx + "3.bias"])
@@ -500,6 +532,8 @@ class DV3Engine:
         ops = self.ops
         N, S, D, U, A, lat, H = self.N, self.S, self.D, self.U, self.A, self.lat, self.H
         G, K, mix = self.G, self.K, self.cfg.algo.unimix
+        _refresh(ops, self.wm.flat, self.actor.flat)               # the world model was just updated (dreamer_v3.py:187)
+        ops.copy2d(self.Wmlp[:, :S], self.Wmlp_z)
         ops.copy2d(self.latent, self.traj[:N])
 
         def policy(i, u, fidx):
@@ -516,7 +550,7 @@ class DV3Engine:
         policy(0, self.u_act0, fa)
         for i in range(1, H + 1):
             r, rp = slice(i * N, (i + 1) * N), slice((i - 1) * N, i * N)
-            ops.gemm("NT", self.traj[rp, :S], self.Wmlp[:, :S], self.img_feat_pre)
+            ops.gemm("NT", self.traj[rp, :S], self.Wmlp_z, self.img_feat_pre)
             ops.gemm("NT", self.acts[rp], self.Wmlp[:, S:], self.img_feat_pre, accumulate=True)
             ops.ln_act_fwd(self.img_feat_pre, self.g_mlp, self.b_mlp, 1e-3, 1, self.img_feat, self.img_mean, self.img_rstd)
             ops.gemm("NT", self.traj[rp, S:], self.Wgru[:, :D], self.img_gates)
@@ -531,6 +565,7 @@ class DV3Engine:
     def behaviour(self) -> None:
         ops, a = self.ops, self.cfg.algo
         N, H, M0, M1 = self.N, self.H, self.M0, self.M1
+        _refresh(ops, self.critic.flat, self.target.flat)
         # a9: values / rewards / continues on the imagined states
         self.crit_stack.forward(self.traj)
         self.rew_img.forward(self.traj)
@@ -552,6 +587,7 @@ class DV3Engine:
         ops.actor_loss(self.act_stack.out[:M0], self.actions_dim, self.act_idx[:M0], self.lam, self.values[:M0], self.discount[:M0],
                        self.mom_out, a.unimix, a.actor.ent_coef, 1.0 / M0, self.pl_rows.view(M0), self.d_actor_raw)
         ops.reduce_mean(self.pl_rows, 0, self.metrics, _SLOT["Loss/policy_loss"], 1.0 / M0, False)
+        _refresh(ops, self.d_actor_raw)
         self.act_stack.backward(self.traj, M0, self.d_actor_raw)
         self._optimize(self.actor, "actor", a.actor.clip_gradients, "Grads/actor")
         # a13: critic loss (activations of the value pass above; target critic forward)
@@ -560,6 +596,7 @@ class DV3Engine:
         ops.twohot_loss(self.crit_stack.out[:M0], self.lam, self.discount[:M0], 1.0 / M0, self.vl_rows.view(M0), self.d_crit, False)
         ops.twohot_loss(self.crit_stack.out[:M0], self.tvalues, self.discount[:M0], 1.0 / M0, self.vl_rows.view(M0), self.d_crit, True)
         ops.reduce_mean(self.vl_rows, 0, self.metrics, _SLOT["Loss/value_loss"], 1.0 / M0, False)
+        _refresh(ops, self.d_crit)
         self.crit_stack.backward(self.traj, M0, self.d_crit)
         self._optimize(self.critic, "critic", a.critic.clip_gradients, "Grads/critic")
 

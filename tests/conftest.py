@@ -28,3 +28,15 @@ def torch_ops():
     from oracle.torch_ops import TorchOps
 
     return TorchOps()
+
+
+@pytest.fixture()
+def cuda_ops_bf16():
+    """A fresh bf16-precision CudaOps (own mirror registry, so tests cannot leak mirrors of freed tensors)."""
+    import torch
+
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from sheeprl_prey_b200._lib import CudaOps
+
+    return CudaOps("cuda:0", scratch_bytes=4 << 20, precision="bf16")

@@ -409,25 +409,93 @@ def test_pixel_small_kernels(cuda_ops, torch_ops):
     assert rel(res[1][1], res[0][1]) < 1e-5 and rel(res[1][2], res[0][2]) < 1e-6
 
 
-@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1024, 512, 512), (1024, 512, 1536), (16384, 512, 1536), (1000, 255, 520), (130, 40, 72)])
-def test_gemm_bf16_tma(M, N, K):
-    """TMA-fed tcgen05 GEMM on bf16-resident operands (ragged sizes are zero-filled by the TMA unit)."""
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["NT", "NN", "TN"])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1024, 512, 512), (1024, 512, 1536), (16384, 512, 1536), (1000, 255, 520),
+                                   (130, 40, 72), (512, 1536, 16384), (4, 512, 15360), (255, 512, 4096)])
+def test_gemm_bf16_tma(mode, M, N, K):
+    """TMA-fed tcgen05 GEMM on bf16-resident operands: K-major and MN-major operands, ragged sizes (zero-filled by the TMA
+    unit), split-K (long K with few output tiles) and accumulate."""
     from sheeprl_prey_b200._lib import load_library
 
     lib = load_library()
-    A, B, bias = rnd(M, K), rnd(N, K), rnd(N)
-    Ab, Bb = A.bfloat16().contiguous(), B.bfloat16().contiguous()
+    pad = lambda n: (n + 7) // 8 * 8  # noqa: E731
+    if mode == "NT":
+        a_shape, b_shape = (M, K), (N, K)
+    elif mode == "NN":
+        a_shape, b_shape = (M, K), (K, N)
+    else:
+        a_shape, b_shape = (K, M), (K, N)
+    A, B, bias = rnd(*a_shape), rnd(*b_shape, seed=3), rnd(N, seed=5)
+    # bf16 operands with the row stride padded to a multiple of 8 elements (the TMA constraint)
+    Ab = torch.zeros(a_shape[0], pad(a_shape[1]), dtype=torch.bfloat16, device=DEV)[:, :a_shape[1]]
+    Bb = torch.zeros(b_shape[0], pad(b_shape[1]), dtype=torch.bfloat16, device=DEV)[:, :b_shape[1]]
+    Ab.copy_(A)
+    Bb.copy_(B)
     st = torch.cuda.current_stream().cuda_stream
+    Ad, Bd = Ab.double(), Bb.double()
+    prod = Ad @ Bd.t() if mode == "NT" else (Ad @ Bd if mode == "NN" else Ad.t() @ Bd)
     for acc in (0, 1):
         C0 = rnd(M, N, seed=7)
         C1 = C0.clone()
-        rc = lib.dv3_gemm_bf16_tma(M, N, K, Ab.data_ptr(), K, Bb.data_ptr(), K, C1.data_ptr(), N, bias.data_ptr(), acc, st)
+        rc = lib.dv3_gemm_bf16_tma({"NT": 0, "NN": 1, "TN": 2}[mode], M, N, K, Ab.data_ptr(), Ab.stride(0), Bb.data_ptr(), Bb.stride(0),
+                                   C1.data_ptr(), N, bias.data_ptr(), acc, st)
         assert rc == 0, rc
         torch.cuda.synchronize()
-        exact = Ab.double() @ Bb.double().t() + bias.double() + (C0.double() if acc else 0)
-        assert rel(C1.double(), exact) < 2e-5, (M, N, K, acc)
-    # conversion kernel == round-to-nearest-even
-    dst = torch.zeros(M, K + 8, dtype=torch.bfloat16, device=DEV)
-    assert lib.dv3_f32_to_bf16(M, K, A.data_ptr(), K, dst.data_ptr(), K + 8, st) == 0
+        exact = prod + bias.double() + (C0.double() if acc else 0)
+        assert rel(C1.double(), exact) < 2e-5, (mode, M, N, K, acc)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("R,C,lds,ldd", [(1, 4096 * 33, 4096 * 33, 4096 * 33), (1, 1001, 1001, 1001), (300, 512, 512, 512),
+                                         (300, 512, 1536, 1536), (77, 255, 256, 256), (16, 31, 40, 33)])
+def test_f32_to_bf16(R, C, lds, ldd):
+    """Mirror refresh kernel == round-to-nearest-even on every (vectorised / strided / ragged) path."""
+    from sheeprl_prey_b200._lib import load_library
+
+    lib = load_library()
+    src = rnd(R, lds)
+    dst = torch.zeros(R, ldd, dtype=torch.bfloat16, device=DEV)
+    assert lib.dv3_f32_to_bf16(R, C, src.data_ptr(), lds, dst.data_ptr(), ldd, torch.cuda.current_stream().cuda_stream) == 0
     torch.cuda.synchronize()
-    assert torch.equal(dst[:, :K], Ab)
+    assert torch.equal(dst[:, :C], src[:, :C].bfloat16())
+    assert not dst[:, C:].any()
+
+
+@pytest.mark.gpu
+def test_bf16_side_outputs(cuda_ops_bf16):
+    """Producer kernels with a `*_bf16` pointer write bf16(output) into the mirror in the same pass."""
+    ops = cuda_ops_bf16
+    M, U, D, G, K = 300, 512, 256, 8, 32
+    x, g, b = rnd(M, U), rnd(U, seed=2), rnd(U, seed=3)
+    y, dx, dln = torch.zeros(M, U, device=DEV), torch.zeros(M, U, device=DEV), torch.zeros(M, U, device=DEV)
+    h_out, onehot = torch.zeros(M, D, device=DEV), torch.zeros(M, G * K, device=DEV)
+    for t in (y, dx, h_out, onehot):
+        ops.mirror(t)
+    mean, rstd = torch.zeros(M, device=DEV), torch.zeros(M, device=DEV)
+    for rows in (M, 16):       # warp-per-row and block-per-row variants
+        ops.ln_act_fwd(x[:rows], g, b, 1e-3, 1, y[:rows], mean[:rows], rstd[:rows])
+        ops.ln_act_bwd(rnd(rows, U, seed=9), x[:rows], g, b, mean[:rows], rstd[:rows], 1, dx[:rows], dln[:rows])
+        torch.cuda.synchronize()
+        assert torch.equal(ops._m16_view(y[:rows]), y[:rows].bfloat16())
+        assert torch.equal(ops._m16_view(dx[:rows]), dx[:rows].bfloat16())
+    ops.gru_gate_fwd(rnd(M, 3 * D, seed=4), rnd(3 * D, seed=5), rnd(3 * D, seed=6), rnd(M, D, seed=7), h_out, mean, rstd)
+    idx = torch.zeros(M, G, dtype=torch.int32, device=DEV)
+    ops.sample_onehot(rnd(M, G * K, seed=8), G, K, torch.rand(M, G, device=DEV), None, 0, idx, onehot)
+    src = rnd(M, D, seed=11)
+    ops.copy2d(src, h_out[:, :D])
+    torch.cuda.synchronize()
+    assert torch.equal(ops._m16_view(onehot), onehot.bfloat16()) and onehot.sum() == M * G
+    assert torch.equal(ops._m16_view(h_out), src.bfloat16())
+    # a contraction on two mirrored operands takes the TMA kernel and equals the exact product of the bf16 values
+    W = rnd(U, U, seed=12)
+    ops.mirror(W)
+    ops.refresh(W)
+    out = torch.zeros(M, U, device=DEV)
+    ops.gemm_log = []
+    ops.gemm("NT", y, W, out)
+    torch.cuda.synchronize()
+    assert ops.gemm_log[0][-1] == "tma"
+    ops.gemm_log = None
+    assert rel(out.double(), y.bfloat16().double() @ W.bfloat16().double().t()) < 2e-5

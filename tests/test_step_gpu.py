@@ -172,10 +172,17 @@ def test_train_api_on_gpu():
     assert float(mom.low) != 0.0 or float(mom.high) != 0.0
 
 
-def test_step_bf16_tensor_core_mode_within_2e2():
+@pytest.mark.parametrize("resident", [False, True])
+def test_step_bf16_tensor_core_mode_within_2e2(resident):
     """The same step with the large-M contractions on the tcgen05 tensor cores (bf16 operands, fp32 accumulate):
-    north-star tolerance 2e-2 relative on states, losses and lambda-returns (teacher-forced draws)."""
+    north-star tolerance 2e-2 relative on states, losses and lambda-returns (teacher-forced draws).
+    resident=False: fp32 operands rounded while staged (gemm_tc.cu).  resident=True: bf16 mirrors written by the producer
+    kernels and read through TMA (gemm_tma.cu); every contraction first checks that its mirrors equal bf16(fp32 operand)."""
     from sheeprl_prey_b200._lib import CudaOps
+
+    ops = CudaOps(DEV, precision="bf16")
+    ops.use_mirrors = resident
+    ops.mirror_check = resident
 
     size, B, T, H, obs, acts = "S", 16, 64, 15, 14, [100]
     cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=H)
@@ -188,15 +195,23 @@ def test_step_bf16_tensor_core_mode_within_2e2():
     data = harness.synthetic_batch(T, B, od, acts, seed=1234, done_p=1 / 50)
     noise = harness.synthetic_noise(T, B, H, 32, len(acts), seed=99)
     out = tr.step({k: v.clone() for k, v in data.items()}, noise)
-    eng = engine_from_params(cfg, od, acts, _dev_params(params), CudaOps(DEV, precision="bf16"), DEV)
+    eng = engine_from_params(cfg, od, acts, _dev_params(params), ops, DEV)
     eng.load_batch(_to(data, DEV))
     eng.load_noise(_to(noise, DEV))
     forced = dict(post_idx=out["post_idx"].reshape(T * B, -1).int().to(DEV),
                   imagine=dict(z_idx=out["z_idx"].int().to(DEV), act_idx=out["act_idx"].int().to(DEV)))
+    ops.gemm_log = []
     eng.step(forced)
     torch.cuda.synchronize()
+    kernels = [g[-1] for g in ops.gemm_log]
+    ops.gemm_log = None
+    if resident:
+        assert kernels.count("tma") > 10 * kernels.count("tc"), (kernels.count("tma"), kernels.count("tc"))
+    else:
+        assert kernels.count("tma") == 0
     md = eng.metrics_dict()
-    rep = {"config": size, "mode": "bf16-tc"}
+    rep = {"config": size, "mode": "bf16-tma-resident" if resident else "bf16-tc"}
+    rep["gemm_kernels"] = {k: kernels.count(k) for k in ("tma", "tc", "simt")}
     rep["recurrent_states"] = rel(eng.latent[:, eng.S:].reshape(T, B, -1), out["recurrent_states"])
     rep["post_logits"] = rel(eng.post_logits.reshape(out["post_logits"].shape), out["post_logits"])
     rep["prior_logits"] = rel(eng.prior_logits.reshape(out["prior_logits"].shape), out["prior_logits"])
@@ -211,7 +226,7 @@ def test_step_bf16_tensor_core_mode_within_2e2():
         coef = min(1.0, mx / (float(out[f"Grads/{nm}"]) + 1e-6))
         rep[f"grad_{nm}"] = max(rel(arena.g[k] * coef, out[gk][k]) for k in arena.g)
     os.makedirs(REPORT, exist_ok=True)
-    with open(os.path.join(REPORT, "parity_S_bf16.json"), "w") as f:
+    with open(os.path.join(REPORT, "parity_S_bf16_resident.json" if resident else "parity_S_bf16.json"), "w") as f:
         json.dump(rep, f, indent=1)
     for k in ("recurrent_states", "post_logits", "prior_logits", "traj", "values", "lambda_values"):
         assert rep[k] < 2e-2, (k, rep)

@@ -63,12 +63,12 @@ for mode, M, N, K in shapes:
     B = torch.randn(N, K, device=dev).bfloat16()
     C = torch.zeros(M, N, device=dev)
     st = torch.cuda.current_stream().cuda_stream
-    assert lib.dv3_gemm_bf16_tma(M, N, K, A.data_ptr(), K, B.data_ptr(), K, C.data_ptr(), N, None, 0, st) == 0
+    assert lib.dv3_gemm_bf16_tma(0, M, N, K, A.data_ptr(), K, B.data_ptr(), K, C.data_ptr(), N, None, 0, st) == 0
     torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
         for _ in range(20):
-            lib.dv3_gemm_bf16_tma(M, N, K, A.data_ptr(), K, B.data_ptr(), K, C.data_ptr(), N, None, 0, torch.cuda.current_stream().cuda_stream)
+            lib.dv3_gemm_bf16_tma(0, M, N, K, A.data_ptr(), K, B.data_ptr(), K, C.data_ptr(), N, None, 0, torch.cuda.current_stream().cuda_stream)
     g.replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
