@@ -319,6 +319,96 @@ gemm_skinny_splitk_kernel(int M, int N, int K, const float* __restrict__ A, int 
   }
 }
 
+
+// ---- narrow outputs ---------------------------------------------------------------------------------------------------
+// NT with N <= 16 (scalar / few-column heads: continue logit, low-dimensional observation decoder): one warp per row of A,
+// memory-bound on A (read once, coalesced 16 B per lane); the N weight rows stay in L1.
+constexpr int NARROW = 16;
+__global__ void __launch_bounds__(256)
+gemm_nt_narrow_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
+                      float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int vec) {
+  const int lane = threadIdx.x & 31;
+  const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= (size_t)M) return;
+  const float* a = A + row * lda;
+  float acc[NARROW];
+#pragma unroll
+  for (int n = 0; n < NARROW; ++n) acc[n] = 0.f;
+  if (vec) {
+    for (int k = lane * 4; k < K; k += 128) {
+      const float4 av = __ldg(reinterpret_cast<const float4*>(a + k));
+#pragma unroll
+      for (int n = 0; n < NARROW; ++n) {
+        if (n < N) {
+          const float4 w = __ldg(reinterpret_cast<const float4*>(B + (size_t)n * ldb + k));
+          acc[n] = fmaf(av.x, w.x, fmaf(av.y, w.y, fmaf(av.z, w.z, fmaf(av.w, w.w, acc[n]))));
+        }
+      }
+    }
+  } else {
+    for (int k = lane; k < K; k += 32) {
+      const float av = __ldg(a + k);
+#pragma unroll
+      for (int n = 0; n < NARROW; ++n)
+        if (n < N) acc[n] = fmaf(av, __ldg(B + (size_t)n * ldb + k), acc[n]);
+    }
+  }
+#pragma unroll
+  for (int n = 0; n < NARROW; ++n) {
+    if (n < N) {
+      float v = warp_sum(acc[n]);
+      if (lane == 0) {
+        if (bias) v += bias[n];
+        float* cp = C + row * ldc + n;
+        *cp = accumulate ? (*cp + v) : v;
+      }
+    }
+  }
+}
+
+// TN with one narrow side (<= 16): C = sum_k P[k, :]^T Q[k, :] with P [K, p <= 16] and Q [K, q] (bias / few-column weight
+// gradients over K = T*B(*H) rows).  Threads own q columns (coalesced reads of Q), the P rows of a 64-deep chunk are staged in
+// shared memory and broadcast; K is split over blockIdx.y and reduced with fp32 atomics into a zeroed (or accumulated) C.
+__global__ void __launch_bounds__(128)
+gemm_tn_narrow_kernel(int P, int Q, int K, const float* __restrict__ Pm, int ldp, const float* __restrict__ Qm, int ldq,
+                      float* __restrict__ C, int ldc, int transposed_out, int k_per_block) {
+  __shared__ float sp[64][NARROW];
+  const int q = blockIdx.x * 128 + threadIdx.x;
+  const int k0 = blockIdx.y * k_per_block, k1 = min(K, k0 + k_per_block);
+  float acc[NARROW];
+#pragma unroll
+  for (int p = 0; p < NARROW; ++p) acc[p] = 0.f;
+  for (int kc = k0; kc < k1; kc += 64) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 64 * NARROW; i += 128) {
+      const int kk = i >> 4, p = i & 15;
+      sp[kk][p] = (kc + kk < k1 && p < P) ? __ldg(Pm + (size_t)(kc + kk) * ldp + p) : 0.f;
+    }
+    __syncthreads();
+    if (q < Q) {
+      const int kn = min(64, k1 - kc);
+#pragma unroll 8
+      for (int kk = 0; kk < kn; ++kk) {
+        const float b = __ldg(Qm + (size_t)(kc + kk) * ldq + q);
+#pragma unroll
+        for (int p = 0; p < NARROW; ++p) acc[p] = fmaf(sp[kk][p], b, acc[p]);
+      }
+    }
+  }
+  if (q < Q) {
+    for (int p = 0; p < P; ++p) atomicAdd(transposed_out ? (C + (size_t)q * ldc + p) : (C + (size_t)p * ldc + q), acc[p]);
+  }
+}
+
+// C = (accumulate ? C : 0) + bias: the atomics of gemm_tn_narrow_kernel then add the product
+__global__ void init2d_simt_kernel(int M, int N, float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate) {
+  const size_t n = (size_t)M * N;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    float* cp = C + (i / N) * ldc + (i % N);
+    *cp = (accumulate ? *cp : 0.f) + (bias ? bias[i % N] : 0.f);
+  }
+}
+
 template <int MT>
 static int launch_skinny_stream(int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                                 const float* bias, int accumulate, cudaStream_t stream) {
@@ -343,6 +433,30 @@ extern "C" int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int l
   if (mode == MODE_NT && M <= 16 && K >= 256 && (K & 3) == 0 && (lda & 3) == 0 && (ldb & 3) == 0 &&
       (((uintptr_t)A | (uintptr_t)B) & 15) == 0) {
     gemm_skinny_splitk_kernel<<<(N + SK3_COLS - 1) / SK3_COLS, SK3_WARPS * 32, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate);
+    DV3_LAUNCH_CHECK();
+    return DV3_OK;
+  }
+  if (mode == MODE_NT && N <= NARROW && M > 32) {
+    const int vec = (K & 3) == 0 && (lda & 3) == 0 && (ldb & 3) == 0 && (((uintptr_t)A | (uintptr_t)B) & 15) == 0;
+    gemm_nt_narrow_kernel<<<(M + 7) / 8, 256, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, vec);
+    DV3_LAUNCH_CHECK();
+    return DV3_OK;
+  }
+  if (mode == MODE_TN && (M <= NARROW || N <= NARROW) && K >= 64) {
+    if (!accumulate || bias) {
+      size_t n = (size_t)M * N;
+      init2d_simt_kernel<<<(int)((n + 255) / 256 > 1184 ? 1184 : (n + 255) / 256), 256, 0, stream>>>(M, N, C, ldc, bias, accumulate);
+      DV3_LAUNCH_CHECK();
+    }
+    const bool a_narrow = M <= N;                       // the narrow operand is staged, the wide one is streamed
+    const int P = a_narrow ? M : N, Q = a_narrow ? N : M;
+    const int qb = (Q + 127) / 128;
+    int ks = (296 + qb - 1) / qb;                       // ~2 blocks per SM
+    int kpb = (K + ks - 1) / ks;
+    kpb = (kpb + 63) / 64 * 64;
+    ks = (K + kpb - 1) / kpb;
+    gemm_tn_narrow_kernel<<<dim3(qb, ks), 128, 0, stream>>>(P, Q, K, a_narrow ? A : B, a_narrow ? lda : ldb, a_narrow ? B : A,
+                                                            a_narrow ? ldb : lda, C, ldc, a_narrow ? 0 : 1, kpb);
     DV3_LAUNCH_CHECK();
     return DV3_OK;
   }
