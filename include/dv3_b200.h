@@ -139,6 +139,18 @@ typedef struct Dv3ScanFwdArgs {
 } Dv3ScanFwdArgs;
 size_t dv3_rssm_observe_fwd_scratch_bytes(void);
 int dv3_rssm_observe_fwd(const Dv3ScanFwdArgs* args, void* stream);
+/* Same scan on ONE thread-block cluster (16 CTAs, else 8): bf16 weight rows streamed from L2 into mma.sync fragments, activations
+ * and LayerNorm partials exchanged through distributed shared memory, hardware cluster barriers instead of grid-wide ones.
+ * Needs bf16 copies of the three in-loop weight matrices, Wmlp[:, :G*Kc]^T in fp32 (one-hot z = row gather) and the hoisted
+ * action projection aW[t] = a_t . Wmlp[:, G*Kc:]^T.  DV3_ERR_UNSUPPORTED when the shape / device cannot run it. */
+typedef struct Dv3ScanClusterExtra {
+  const void* Wgru_bf16; int ld_wgru;   /* [3D, D+U] bf16 */
+  const void* Wr0_bf16; int ld_wr0;     /* [Hh, D+E] bf16 (first D columns used) */
+  const void* Wr1_bf16; int ld_wr1;     /* [G*Kc, Hh] bf16 */
+  const float* WmlpzT;                  /* [G*Kc, U] fp32 */
+  const float* aW;                      /* [T*B, U] fp32 */
+} Dv3ScanClusterExtra;
+int dv3_rssm_observe_fwd_cluster(const Dv3ScanFwdArgs* args, const Dv3ScanClusterExtra* extra, void* stream);
 
 /* ---- categorical: unimix agent.py:390-402/:741-747; ST one-hot sample distribution.py:355-360,:390-393 ---- */
 int dv3_unimix_fwd(int R, int groups, int K, float mix, const float* raw, int ldr, float* logits, int ldo, void* stream);

@@ -45,6 +45,7 @@ SIGNATURES = {
     "dv3_mask_shift_actions": [_i, _i, _i, c_fp, c_fp, c_fp, _i, c_fp],
     "dv3_rssm_observe_fwd_scratch_bytes": [],
     "dv3_rssm_observe_fwd": [c_fp, c_fp],
+    "dv3_rssm_observe_fwd_cluster": [c_fp, c_fp, c_fp],
     "dv3_unimix_fwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp],
     "dv3_sample_onehot": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
     "dv3_unimix_bwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
@@ -89,6 +90,12 @@ class ScanFwdArgs(C.Structure):
         ("latent", c_fp), ("ld_lat", _i),
         ("scratch", c_fp), ("scratch_bytes", _sz),
     ]
+
+
+class ScanClusterExtra(C.Structure):
+    """Mirror of `Dv3ScanClusterExtra` (include/dv3_b200.h)."""
+    _fields_ = [("Wgru_bf16", c_fp), ("ld_wgru", _i), ("Wr0_bf16", c_fp), ("ld_wr0", _i), ("Wr1_bf16", c_fp), ("ld_wr1", _i),
+                ("WmlpzT", c_fp), ("aW", c_fp)]
 
 
 def load_library(path: Optional[str] = None):
@@ -160,6 +167,8 @@ class CudaOps:
         # kernels write both in one pass; contractions whose two operands are mirrored run the TMA-fed kernel on the mirrors.
         self.use_mirrors = self.precision == "bf16" and os.environ.get("DV3_BF16_RESIDENT", "1") != "0"
         self.mirror_check = os.environ.get("DV3_MIRROR_CHECK", "0") == "1"
+        self.use_cluster_scan = os.environ.get("DV3_CLUSTER_SCAN", "1") != "0"
+        self.scan_kernel = None
         self._mir_start: List[int] = []
         self._mir: List[tuple] = []
         if self.use_mirrors:
@@ -475,6 +484,23 @@ class CudaOps:
         a.post_raw, a.post_logits, a.post_idx = _p(eng.post_raw), _p(eng.post_logits), _p(eng.post_idx)
         a.latent, a.ld_lat = _p(eng.latent), eng.latent.stride(0)
         a.scratch, a.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel() * 4
+        if self.use_mirrors and self.use_cluster_scan and getattr(eng, "aW", None) is not None:
+            # one thread-block cluster, bf16 weights streamed into mma.sync fragments, DSMEM exchange (rssm_scan_cluster.cu)
+            x = ScanClusterExtra()
+            x.Wgru_bf16, x.ld_wgru = self._m16(_p(eng.Wgru)), eng.Wgru.stride(0)
+            x.Wr0_bf16, x.ld_wr0 = self._m16(_p(eng.Wr0)), eng.Wr0.stride(0)
+            x.Wr1_bf16, x.ld_wr1 = self._m16(_p(eng.Wr1)), eng.Wr1.stride(0)
+            x.WmlpzT, x.aW = _p(eng.W_mlpzT), _p(eng.aW)
+            if x.Wgru_bf16 and x.Wr0_bf16 and x.Wr1_bf16:
+                rc = self.lib.dv3_rssm_observe_fwd_cluster(C.addressof(a), C.addressof(x), self._s())
+                if rc == 0:
+                    self.launches += 1
+                    self.scan_kernel = "cluster"
+                    return True
+                if rc != -2:
+                    _chk(rc, "dv3_rssm_observe_fwd_cluster")
+                self.use_cluster_scan = False
+        self.scan_kernel = "cooperative"
         rc = self.lib.dv3_rssm_observe_fwd(C.addressof(a), self._s())
         if rc == -2:
             return False

@@ -258,6 +258,7 @@ class DV3Engine:
         self.dfeat_pre, self.dln_feat, self.dz_prev, self.de = z(N, U), z(N, U), z(B, S), z(N, E)
         self.W_r1T, self.W_r0hT, self.W_gruT, self.W_mlpzT = z(Hh, S), z(D, Hh), z(D + U, 3 * D), z(S, U)
         self.eW = z(N, Hh)                       # e_t . Wr0[:, D:]^T + b_r0 for all t (hoisted out of the scan)
+        self.aW = z(N, U)                        # a_t . Wmlp[:, S:]^T for all t (hoisted out of the scan; cluster kernel)
         self.Wmlp_z = z(U, S)                    # compact copy of Wmlp[:, :S] for the rollout (row stride S+A is not TMA-loadable)
         _mirror(ops, self.x_rep, self.x_gru, self.x_mlp, self.latent, self.hidr, self.Wmlp_z, self.dpost_raw, self.dhidr_pre,
                 self.dgates_pre, self.dfeat_pre, self.dprior_logits, self.d_rec._base, self.d_rew._base)
@@ -392,6 +393,7 @@ class DV3Engine:
         fused = False
         if self.use_fused_scan:
             ops.gemm("NT", self.x_rep[:, D:], self.Wr0[:, D:], self.eW, bias=self.br0)
+            ops.gemm("NT", self.x_mlp[:, S:], self.Wmlp[:, S:], self.aW)
             fused = ops.rssm_observe_fwd(self, forced_post_idx)
             if not fused:
                 self.use_fused_scan = False

@@ -263,6 +263,45 @@ def test_persistent_scan_matches_per_step_composition(cuda_ops, size, B, T, obs,
         assert rel(getattr(b, name), getattr(a, name)) < 1e-5, (name, rel(getattr(b, name), getattr(a, name)))
 
 
+@pytest.mark.parametrize("size,B,T,obs,acts", [("S", 16, 64, 14, [100]), ("XS", 16, 20, 4, [2]), ("S", 5, 9, 14, [7, 3]), ("M", 16, 12, 20, [18])])
+def test_cluster_scan_matches_cooperative_scan(cuda_ops, size, B, T, obs, acts):
+    """dv3_rssm_observe_fwd_cluster (one 16-CTA cluster, bf16 weights in mma.sync fragments, DSMEM exchange) against the fp32
+    cooperative scan kernel.  The contractions round their operands to bf16, so tensors agree to the bf16-mode tolerance (2e-2 of
+    the tensor's max) under teacher-forced draws; free-running draws flip only where a uniform lands next to a CDF step."""
+    from sheeprl_prey_b200._lib import CudaOps
+
+    cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=3)
+    od = {"state": obs}
+    params = random_params_like(cfg, od, acts, seed=5)
+    data = _to(harness.synthetic_batch(T, B, od, acts, seed=77, done_p=0.1), DEV)
+    noise = _to(harness.synthetic_noise(T, B, 3, 32, len(acts), seed=78), DEV)
+    ref = engine_from_params(cfg, od, acts, _dev_params(params), cuda_ops, DEV)
+    ref.load_batch(data)
+    ref.load_noise(noise)
+    ref.world_forward()
+    torch.cuda.synchronize()
+    assert ref.use_fused_scan
+    ops = CudaOps(DEV, precision="bf16")
+    eng = engine_from_params(cfg, od, acts, _dev_params(params), ops, DEV)
+    eng.load_batch(data)
+    eng.load_noise(noise)
+    eng.world_forward()
+    torch.cuda.synchronize()
+    assert ops.scan_kernel == "cluster", ops.scan_kernel
+    flips = float((eng.post_idx != ref.post_idx).float().mean())
+    assert flips < 0.05, flips
+    eng.world_forward(ref.post_idx)                      # teacher-forced: identical stochastic states
+    torch.cuda.synchronize()
+    assert torch.equal(eng.post_idx, ref.post_idx)
+    assert torch.equal(eng.latent[:, :eng.S], ref.latent[:, :eng.S]) and torch.equal(eng.x_mlp, ref.x_mlp)
+    worst = {}
+    for name in ("feat_pre", "feat_mean", "feat_rstd", "x_gru", "gates_pre", "gru_mean", "gru_rstd", "x_rep", "hidr_pre", "hidr",
+                 "hidr_mean", "hidr_rstd", "post_raw", "post_logits", "latent", "prior_logits"):
+        worst[name] = rel(getattr(eng, name), getattr(ref, name))
+    assert max(worst.values()) < 2e-2, worst
+    assert worst["feat_pre"] < 1e-5, worst                # fp32 gather of fp32 weights: only the summation order differs
+
+
 def test_pixel_step_matches_oracle(cuda_ops):
     """Pixel + vector observations (multi-encoder / multi-decoder, BASELINE config-4 structure at a small size) vs the oracle."""
     B, T, H = 4, 8, 3

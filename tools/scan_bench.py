@@ -52,3 +52,26 @@ names = ["P0 start", "P1 done", "sync1+load feat", "P2 done (LN, gates gemv)", "
 for i in range(1, 11):
     print(f"{names[i]:28s} {stamps[i] - stamps[i - 1]:8d} clk")
 print("step total", stamps[10] - stamps[0], "clk")
+
+
+# ---- cluster kernel (bf16 precision)
+ops16 = CudaOps(dev, precision="bf16")
+eng16 = engine_from_params(cfg, od, acts, {n: {k: v.to(dev) for k, v in d.items()} for n, d in params.items()}, ops16, dev)
+eng16.load_batch({k: v.to(dev) for k, v in harness.synthetic_batch(64, 16, od, acts, seed=1).items()})
+eng16.load_noise(None)
+eng16.world_forward()
+torch.cuda.synchronize()
+print("scan kernel in bf16 mode:", ops16.scan_kernel)
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(5):
+    ops16.rssm_observe_fwd(eng16, None)
+e1.record()
+torch.cuda.synchronize()
+print("cluster scan kernel", e0.elapsed_time(e1) / 5, "ms")
+st = ops16.scratch[:32].view(torch.int64)[:11].cpu().tolist()
+nm = ["P0 masks/saves", "P1 gather+partials", "sync1+LN+allgather", "sync2+gates contraction", "gates partials..sync3..h'..allgather",
+      "sync4+hidr contraction+partials", "sync5+LN+allgather", "sync6+logits contraction", "sampling", "sync7"]
+for i in range(10):
+    print(f"  {nm[i]:40s} {st[i + 1] - st[i]:8d} clk")
+print("  step total", st[10] - st[0], "clk")
