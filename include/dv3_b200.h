@@ -152,6 +152,36 @@ typedef struct Dv3ScanClusterExtra {
 } Dv3ScanClusterExtra;
 int dv3_rssm_observe_fwd_cluster(const Dv3ScanFwdArgs* args, const Dv3ScanClusterExtra* extra, void* stream);
 
+/* Reverse scan (backward through time of the same loop) on one thread-block cluster: what autograd does for RSSM.dynamic inside
+ * rec_loss.backward() (dreamer_v3.py:177).  Inputs: the tensors saved by the forward scan, dL/d post_logits (KL) and dL/d latent
+ * (heads) for all T*B rows, the softmax quantities of dv3_unimix_bwd_prep, bf16 TRANSPOSED weights.  Outputs: the pre-activation
+ * gradients from which the caller forms every parameter gradient with K = T*B contractions (and, optionally, their bf16 mirrors).
+ * DV3_ERR_UNSUPPORTED when the shape / device cannot run it (the caller then uses the per-step entry points). */
+typedef struct Dv3ScanBwdArgs {
+  int T, B, G, Kc, D, U, Hh;
+  float unimix;
+  const float* first;                                   /* [T*B] */
+  const float* ps; const float* coef; const float* pn;  /* [T*B, G*Kc] from dv3_unimix_bwd_prep */
+  const float* dpost_logits;                            /* [T*B, G*Kc] */
+  const float* dlatent; int ld_dlat;                    /* [T*B, G*Kc + D]: head gradients wrt (z_t, h_t) */
+  const float* hidr_pre; const float* hidr_mean; const float* hidr_rstd;
+  const float* gates_pre; const float* gru_mean; const float* gru_rstd;
+  const float* x_gru; int ld_xgru;                      /* [T*B, D+U]: h_in in the first D columns */
+  const float* feat_pre; const float* feat_mean; const float* feat_rstd;
+  const float* g_r; const float* b_r; const float* g_gru; const float* b_gru; const float* g_mlp; const float* b_mlp;
+  const void* Wr1T_bf16; int ld_wr1t;                   /* [Hh, G*Kc]  = Wr1^T            */
+  const void* Wr0hT_bf16; int ld_wr0ht;                 /* [D, Hh]     = Wr0[:, :D]^T     */
+  const void* WgruT_bf16; int ld_wgrut;                 /* [D+U, 3D]   = Wgru^T           */
+  const void* WmlpzT_bf16; int ld_wmlpzt;               /* [G*Kc, U]   = Wmlp[:, :G*Kc]^T */
+  float* dpost_raw; float* dhidr_pre; float* dln_r; float* dgates_pre; float* dln_gru; float* dfeat_pre; float* dln_feat;
+  void* dpost_raw_bf16; void* dhidr_pre_bf16; void* dgates_pre_bf16; void* dfeat_pre_bf16;   /* optional mirrors (NULL = none) */
+  long long* dbg;                                       /* optional: 16 clock64 stamps of CTA 0 at step T-2 */
+} Dv3ScanBwdArgs;
+int dv3_rssm_observe_bwd_cluster(const Dv3ScanBwdArgs* args, void* stream);
+/* ps = softmax(raw), pn = Categorical(logits = unimix(raw)).probs, coef = (1-mix)/pm inside the clamp else 0 (mix = 0: ps = pn,
+ * coef = 1): the step-independent factors of the unimix + straight-through Jacobian (see dv3_unimix_bwd). */
+int dv3_unimix_bwd_prep(int R, int groups, int K, float mix, const float* raw, int ldr, float* ps, float* coef, float* pn, void* stream);
+
 /* ---- categorical: unimix agent.py:390-402/:741-747; ST one-hot sample distribution.py:355-360,:390-393 ---- */
 int dv3_unimix_fwd(int R, int groups, int K, float mix, const float* raw, int ldr, float* logits, int ldo, void* stream);
 int dv3_sample_onehot(int R, int groups, int K, const float* logits, int ldl, const float* u, int ldu, const int* forced,

@@ -46,6 +46,8 @@ SIGNATURES = {
     "dv3_rssm_observe_fwd_scratch_bytes": [],
     "dv3_rssm_observe_fwd": [c_fp, c_fp],
     "dv3_rssm_observe_fwd_cluster": [c_fp, c_fp, c_fp],
+    "dv3_rssm_observe_bwd_cluster": [c_fp, c_fp],
+    "dv3_unimix_bwd_prep": [_i, _i, _i, _f, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_unimix_fwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp],
     "dv3_sample_onehot": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
     "dv3_unimix_bwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
@@ -96,6 +98,23 @@ class ScanClusterExtra(C.Structure):
     """Mirror of `Dv3ScanClusterExtra` (include/dv3_b200.h)."""
     _fields_ = [("Wgru_bf16", c_fp), ("ld_wgru", _i), ("Wr0_bf16", c_fp), ("ld_wr0", _i), ("Wr1_bf16", c_fp), ("ld_wr1", _i),
                 ("WmlpzT", c_fp), ("aW", c_fp)]
+
+
+class ScanBwdArgs(C.Structure):
+    """Mirror of `Dv3ScanBwdArgs` (include/dv3_b200.h)."""
+    _fields_ = [
+        ("T", _i), ("B", _i), ("G", _i), ("Kc", _i), ("D", _i), ("U", _i), ("Hh", _i), ("unimix", _f),
+        ("first", c_fp), ("ps", c_fp), ("coef", c_fp), ("pn", c_fp), ("dpost_logits", c_fp), ("dlatent", c_fp), ("ld_dlat", _i),
+        ("hidr_pre", c_fp), ("hidr_mean", c_fp), ("hidr_rstd", c_fp), ("gates_pre", c_fp), ("gru_mean", c_fp), ("gru_rstd", c_fp),
+        ("x_gru", c_fp), ("ld_xgru", _i), ("feat_pre", c_fp), ("feat_mean", c_fp), ("feat_rstd", c_fp),
+        ("g_r", c_fp), ("b_r", c_fp), ("g_gru", c_fp), ("b_gru", c_fp), ("g_mlp", c_fp), ("b_mlp", c_fp),
+        ("Wr1T_bf16", c_fp), ("ld_wr1t", _i), ("Wr0hT_bf16", c_fp), ("ld_wr0ht", _i), ("WgruT_bf16", c_fp), ("ld_wgrut", _i),
+        ("WmlpzT_bf16", c_fp), ("ld_wmlpzt", _i),
+        ("dpost_raw", c_fp), ("dhidr_pre", c_fp), ("dln_r", c_fp), ("dgates_pre", c_fp), ("dln_gru", c_fp), ("dfeat_pre", c_fp),
+        ("dln_feat", c_fp),
+        ("dpost_raw_bf16", c_fp), ("dhidr_pre_bf16", c_fp), ("dgates_pre_bf16", c_fp), ("dfeat_pre_bf16", c_fp),
+        ("dbg", c_fp),
+    ]
 
 
 def load_library(path: Optional[str] = None):
@@ -169,6 +188,7 @@ class CudaOps:
         self.mirror_check = os.environ.get("DV3_MIRROR_CHECK", "0") == "1"
         self.use_cluster_scan = os.environ.get("DV3_CLUSTER_SCAN", "1") != "0"
         self.scan_kernel = None
+        self.bwd_scan_kernel = None
         self._mir_start: List[int] = []
         self._mir: List[tuple] = []
         if self.use_mirrors:
@@ -276,6 +296,7 @@ class CudaOps:
         pd, _, _, ldd = _mat(dst)
         self.launches += 1
         _chk(self.lib.dv3_transpose(R, Cc, ps, lds, pd, ldd, self._s()), "dv3_transpose")
+        self.refresh(dst)
 
     def copy2d(self, src, dst):
         ps, R, Cc, lds = _mat(src)
@@ -506,6 +527,49 @@ class CudaOps:
             return False
         _chk(rc, "dv3_rssm_observe_fwd")
         self.launches += 1
+        return True
+
+    def unimix_bwd_prep(self, raw, groups, K, unimix, ps, coef, pn):
+        pr, R, _, ldr = _mat(raw)
+        assert ps.is_contiguous() and coef.is_contiguous() and pn.is_contiguous()
+        self.launches += 1
+        _chk(self.lib.dv3_unimix_bwd_prep(R, groups, K, unimix, pr, ldr, _p(ps), _p(coef), _p(pn), self._s()), "dv3_unimix_bwd_prep")
+
+    def rssm_observe_bwd(self, eng) -> bool:
+        """Whole reverse scan in one cluster launch (rssm_scan_bwd_cluster.cu; bf16 precision with mirrors only).  Returns False when
+        the shape / device is outside the kernel's plan (the engine then runs the per-step composition)."""
+        if not (self.use_mirrors and self.use_cluster_scan):
+            return False
+        w16 = [self._m16(_p(t)) for t in (eng.W_r1T, eng.W_r0hT, eng.W_gruT, eng.W_mlpzT)]
+        if any(w is None for w in w16):
+            return False
+        eng.ops.unimix_bwd_prep(eng.post_raw, eng.G, eng.K, float(eng.cfg.algo.unimix), eng.ub_ps, eng.ub_coef, eng.ub_pn)
+        a = ScanBwdArgs()
+        a.T, a.B, a.G, a.Kc, a.D, a.U, a.Hh = eng.T, eng.B, eng.G, eng.K, eng.D, eng.U, eng.Hh
+        a.unimix = float(eng.cfg.algo.unimix)
+        a.first, a.ps, a.coef, a.pn = _p(eng.first), _p(eng.ub_ps), _p(eng.ub_coef), _p(eng.ub_pn)
+        a.dpost_logits, a.dlatent, a.ld_dlat = _p(eng.dpost_logits), _p(eng.dlatent), eng.dlatent.stride(0)
+        a.hidr_pre, a.hidr_mean, a.hidr_rstd = _p(eng.hidr_pre), _p(eng.hidr_mean), _p(eng.hidr_rstd)
+        a.gates_pre, a.gru_mean, a.gru_rstd = _p(eng.gates_pre), _p(eng.gru_mean), _p(eng.gru_rstd)
+        a.x_gru, a.ld_xgru = _p(eng.x_gru), eng.x_gru.stride(0)
+        a.feat_pre, a.feat_mean, a.feat_rstd = _p(eng.feat_pre), _p(eng.feat_mean), _p(eng.feat_rstd)
+        a.g_r, a.b_r, a.g_gru, a.b_gru, a.g_mlp, a.b_mlp = _p(eng.g_r), _p(eng.b_r), _p(eng.g_gru), _p(eng.b_gru), _p(eng.g_mlp), _p(eng.b_mlp)
+        a.Wr1T_bf16, a.ld_wr1t = w16[0], eng.W_r1T.stride(0)
+        a.Wr0hT_bf16, a.ld_wr0ht = w16[1], eng.W_r0hT.stride(0)
+        a.WgruT_bf16, a.ld_wgrut = w16[2], eng.W_gruT.stride(0)
+        a.WmlpzT_bf16, a.ld_wmlpzt = w16[3], eng.W_mlpzT.stride(0)
+        a.dpost_raw, a.dhidr_pre, a.dln_r = _p(eng.dpost_raw), _p(eng.dhidr_pre), _p(eng.dln_r)
+        a.dgates_pre, a.dln_gru, a.dfeat_pre, a.dln_feat = _p(eng.dgates_pre), _p(eng.dln_gru), _p(eng.dfeat_pre), _p(eng.dln_feat)
+        a.dpost_raw_bf16, a.dhidr_pre_bf16 = self._m16(_p(eng.dpost_raw)), self._m16(_p(eng.dhidr_pre))
+        a.dgates_pre_bf16, a.dfeat_pre_bf16 = self._m16(_p(eng.dgates_pre)), self._m16(_p(eng.dfeat_pre))
+        a.dbg = self.scratch.data_ptr() if os.environ.get("DV3_SCAN_DEBUG") else None
+        rc = self.lib.dv3_rssm_observe_bwd_cluster(C.addressof(a), self._s())
+        if rc == -2:
+            self.use_cluster_bwd_ok = False
+            return False
+        _chk(rc, "dv3_rssm_observe_bwd_cluster")
+        self.launches += 1
+        self.bwd_scan_kernel = "cluster"
         return True
 
     # ---------------------------------------------------------------- scan plumbing

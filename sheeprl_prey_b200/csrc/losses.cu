@@ -178,6 +178,30 @@ unimix_bwd_kernel(int R, int groups, int K, float mix, const float* __restrict__
   }
 }
 
+// step-independent factors of unimix_bwd for every (row, group): ps = softmax(raw), pn = probs of the unimix logits, coef
+template <int KRT>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+unimix_bwd_prep_kernel(int R, int groups, int K, float mix, const float* __restrict__ raw, int ldr, float* __restrict__ ps_o,
+                       float* __restrict__ coef_o, float* __restrict__ pn_o) {
+  const int lane = threadIdx.x & 31;
+  const int gid = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (gid >= R * groups) return;
+  const int row = gid / groups, g = gid % groups;
+  Group<KRT> r, ps, pm, lu, ln, p;
+  load_group(r, raw + (size_t)row * ldr + g * K, K, lane);
+  softmax_group(r, ps, K, lane);
+  if (mix > 0.f) unimix_group(ps, pm, lu, mix, K, lane);
+  else { lu = r; pm = ps; }
+  normalise_group(lu, ln, p, K, lane);
+  const size_t o = (size_t)row * groups * K + g * K;
+  for_k<KRT>(K, lane, [&](int j, int k) {
+    const bool inside = (pm.v[j] >= DV3_EPS32) && (pm.v[j] <= 1.f - DV3_EPS32);
+    ps_o[o + k] = ps.v[j];
+    pn_o[o + k] = p.v[j];
+    coef_o[o + k] = (mix > 0.f) ? (inside ? (1.f - mix) / pm.v[j] : 0.f) : 1.f;
+  });
+}
+
 // ---------------------------------------------------------------- KL balance (block = one row, warp = one group)
 template <int KRT>
 __global__ void __launch_bounds__(1024)
@@ -538,6 +562,14 @@ int dv3_unimix_bwd(int R, int groups, int K, float mix, const float* raw, int ld
   if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
   DV3_DISPATCH_KR(K, unimix_bwd_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
       R, groups, K, mix, raw, ldr, dlogits, lddl, dz, lddz, draw, lddr));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_unimix_bwd_prep(int R, int groups, int K, float mix, const float* raw, int ldr, float* ps, float* coef, float* pn, void* stream) {
+  if (R <= 0 || groups <= 0 || K <= 0) return DV3_ERR_ARG;
+  if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
+  DV3_DISPATCH_KR(K, unimix_bwd_prep_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+      R, groups, K, mix, raw, ldr, ps, coef, pn));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -242,7 +242,7 @@ class DV3Engine:
         # ---------------- world-model buffers
         self.obs_cat, self.obs_sym = z(N, max(self.Od, 1)), z(N, max(self.Od, 1))
         self.actions, self.rewards, self.dones, self.first = z(T, B, A), z(N), z(N), z(T, B)
-        self.x_rep, self.x_gru, self.x_mlp, self.latent = z(N, D + E), z(N, D + U), z(N, S + A), z(N, lat)
+        self.x_rep, self.x_gru, self.x_mlp, self.latent = z(N, D + E), z(N, D + U), zp(N, S + A), z(N, lat)
         self.feat_pre, self.feat_mean, self.feat_rstd = z(N, U), z(N), z(N)
         self.gates_pre, self.gru_mean, self.gru_rstd = z(N, 3 * D), z(N), z(N)
         self.hidr_pre, self.hidr, self.hidr_mean, self.hidr_rstd = z(N, Hh), z(N, Hh), z(N), z(N)
@@ -258,9 +258,12 @@ class DV3Engine:
         self.dfeat_pre, self.dln_feat, self.dz_prev, self.de = z(N, U), z(N, U), z(B, S), z(N, E)
         self.W_r1T, self.W_r0hT, self.W_gruT, self.W_mlpzT = z(Hh, S), z(D, Hh), z(D + U, 3 * D), z(S, U)
         self.eW = z(N, Hh)                       # e_t . Wr0[:, D:]^T + b_r0 for all t (hoisted out of the scan)
+        self.ub_ps, self.ub_coef, self.ub_pn = z(N, S), z(N, S), z(N, S)   # unimix Jacobian factors (cluster reverse scan)
+        self.use_fused_bwd = os.environ.get("DV3_FUSED_BWD_SCAN", "1") != "0"
+        _mirror(ops, self.W_r1T, self.W_r0hT, self.W_gruT, self.W_mlpzT)
         self.aW = z(N, U)                        # a_t . Wmlp[:, S:]^T for all t (hoisted out of the scan; cluster kernel)
         self.Wmlp_z = z(U, S)                    # compact copy of Wmlp[:, :S] for the rollout (row stride S+A is not TMA-loadable)
-        _mirror(ops, self.x_rep, self.x_gru, self.x_mlp, self.latent, self.hidr, self.Wmlp_z, self.dpost_raw, self.dhidr_pre,
+        _mirror(ops, self.x_rep, self.x_gru, self.x_mlp._base, self.latent, self.hidr, self.Wmlp_z, self.dpost_raw, self.dhidr_pre,
                 self.dgates_pre, self.dfeat_pre, self.dprior_logits, self.d_rec._base, self.d_rew._base)
         self.use_fused_scan = hasattr(ops, "rssm_observe_fwd") and os.environ.get("DV3_FUSED_SCAN", "1") != "0"
         self.metrics = z(16)
@@ -379,7 +382,7 @@ class DV3Engine:
         if self.enc is not None:
             ops.symlog(self.obs_cat, self.obs_sym)
             self.enc.forward(self.obs_sym)
-        ops.mask_shift_actions(self.actions, self.first, self.x_mlp.view(T, B, S + A)[:, :, S:])
+        ops.mask_shift_actions(self.actions, self.first, self.x_mlp.unflatten(0, (T, B))[:, :, S:])
         # z_reset = mode(unimix(transition(0)))
         self.trans0.forward(self.zero_h)
         ops.unimix_fwd(self.trans0.out, G, K, mix, self.zreset_logits)
@@ -481,8 +484,13 @@ class DV3Engine:
         ops.unimix_bwd(self.trans.out, G, K, mix, self.dprior_logits, None, self.dprior_logits)
         _refresh(ops, self.dprior_logits)
         self.trans.backward(self.x_rep[:, :D], N, self.dprior_logits, dx=self.dlatent[:, S:], dx_accumulate=True)
-        # reverse scan: only dh / dz propagate sequentially
-        for t in range(T - 1, -1, -1):
+        # reverse scan: only dh / dz propagate sequentially -- one cluster kernel when available, else the per-step composition
+        fused_bwd = False
+        if self.use_fused_bwd and hasattr(ops, "rssm_observe_bwd"):
+            fused_bwd = ops.rssm_observe_bwd(self)
+            if not fused_bwd:
+                self.use_fused_bwd = False
+        for t in range(T - 1, -1, -1) if not fused_bwd else ():
             r = slice(t * B, (t + 1) * B)
             rp = slice((t - 1) * B, t * B)
             ops.unimix_bwd(self.post_raw[r], G, K, mix, self.dpost_logits[r], self.dlatent[r, :S], self.dpost_raw[r])
@@ -500,7 +508,8 @@ class DV3Engine:
                 ops.scan_carry(self.first[t], self.dz_prev, self.dx_gru[:, :D], self.dh_direct,
                                self.dlatent[rp, :S], self.dlatent[rp, S:])
         # parameter gradients of the scan, one K = T*B contraction each
-        _refresh(ops, self.dpost_raw, self.dgates_pre)          # (dhidr_pre / dfeat_pre mirrors are written by ln_act_bwd)
+        if not fused_bwd:
+            _refresh(ops, self.dpost_raw, self.dgates_pre)      # (dhidr_pre / dfeat_pre mirrors are written by ln_act_bwd)
         rpfx = "rssm.representation_model._model."
         ops.gemm("TN", self.dpost_raw, self.hidr, Gd[rpfx + "3.weight"])
         ops.colsum(self.dpost_raw, Gd[rpfx + "3.bias"])

@@ -287,9 +287,15 @@ def test_cluster_scan_matches_cooperative_scan(cuda_ops, size, B, T, obs, acts):
     eng.load_noise(noise)
     eng.world_forward()
     torch.cuda.synchronize()
+    if size == "M":       # 640 / 16 columns per CTA is not a power of two: outside the cluster kernel's plan, cooperative kernel runs
+        assert ops.scan_kernel == "cooperative", ops.scan_kernel
+        return
     assert ops.scan_kernel == "cluster", ops.scan_kernel
-    flips = float((eng.post_idx != ref.post_idx).float().mean())
-    assert flips < 0.05, flips
+    # free-running draws: a flip (uniform next to a CDF step) changes the state and everything after it, so only the first step
+    # measures the flip rate itself
+    flips0 = float((eng.post_idx[:B] != ref.post_idx[:B]).float().mean())
+    assert flips0 < 0.02, flips0
+    assert float((eng.post_idx != ref.post_idx).float().mean()) < 0.5
     eng.world_forward(ref.post_idx)                      # teacher-forced: identical stochastic states
     torch.cuda.synchronize()
     assert torch.equal(eng.post_idx, ref.post_idx)
@@ -299,7 +305,43 @@ def test_cluster_scan_matches_cooperative_scan(cuda_ops, size, B, T, obs, acts):
                  "hidr_mean", "hidr_rstd", "post_raw", "post_logits", "latent", "prior_logits"):
         worst[name] = rel(getattr(eng, name), getattr(ref, name))
     assert max(worst.values()) < 2e-2, worst
-    assert worst["feat_pre"] < 1e-5, worst                # fp32 gather of fp32 weights: only the summation order differs
+    assert worst["feat_pre"] < 2e-3, worst                # fp32 row gather; only the hoisted action projection is a bf16 contraction
+
+
+@pytest.mark.parametrize("size,B,T,obs,acts", [("S", 16, 64, 14, [100]), ("XS", 16, 20, 4, [2]), ("S", 5, 9, 14, [7, 3])])
+def test_cluster_reverse_scan_matches_per_step_composition(size, B, T, obs, acts):
+    """dv3_rssm_observe_bwd_cluster (the whole reverse scan on one cluster, bf16 transposed weights in mma.sync fragments) against
+    the per-step kernels (fp32 contractions for the B-row steps) on the same forward state: the saved pre-activation gradients and
+    the resulting world-model parameter gradients agree to the bf16-mode tolerance."""
+    from sheeprl_prey_b200._lib import CudaOps
+
+    cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=3)
+    od = {"state": obs}
+    params = random_params_like(cfg, od, acts, seed=5)
+    data = _to(harness.synthetic_batch(T, B, od, acts, seed=77, done_p=0.1), DEV)
+    noise = _to(harness.synthetic_noise(T, B, 3, 32, len(acts), seed=78), DEV)
+    ops = CudaOps(DEV, precision="bf16")
+    eng = engine_from_params(cfg, od, acts, _dev_params(params), ops, DEV)
+    eng.load_batch(data)
+    eng.load_noise(noise)
+    eng.world_forward()
+    eng.world_losses()
+    names = ("dpost_raw", "dhidr_pre", "dln_r", "dgates_pre", "dln_gru", "dfeat_pre", "dln_feat")
+    res = []
+    for fused in (False, True):
+        eng.use_fused_bwd = fused
+        ops.bwd_scan_kernel = None
+        eng.wm.grad.zero_()
+        eng.world_backward()
+        torch.cuda.synchronize()
+        assert (ops.bwd_scan_kernel == "cluster") == fused, ops.bwd_scan_kernel
+        res.append(({n: getattr(eng, n).clone() for n in names}, eng.wm.grad.clone()))
+        if fused:   # the bf16 mirrors written by the kernel equal bf16(fp32 output)
+            for n in ("dpost_raw", "dhidr_pre", "dgates_pre", "dfeat_pre"):
+                assert torch.equal(ops._m16_view(getattr(eng, n)), getattr(eng, n).bfloat16()), n
+    worst = {n: rel(res[1][0][n], res[0][0][n]) for n in names}
+    worst["wm_grad"] = rel(res[1][1], res[0][1])
+    assert max(worst.values()) < 3e-2, worst
 
 
 def test_pixel_step_matches_oracle(cuda_ops):

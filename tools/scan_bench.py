@@ -69,9 +69,38 @@ for _ in range(5):
 e1.record()
 torch.cuda.synchronize()
 print("cluster scan kernel", e0.elapsed_time(e1) / 5, "ms")
-st = ops16.scratch[:32].view(torch.int64)[:11].cpu().tolist()
+st = ops16.scratch[:64].view(torch.int64)[:32].cpu().tolist()
 nm = ["P0 masks/saves", "P1 gather+partials", "sync1+LN+allgather", "sync2+gates contraction", "gates partials..sync3..h'..allgather",
       "sync4+hidr contraction+partials", "sync5+LN+allgather", "sync6+logits contraction", "sampling", "sync7"]
 for i in range(10):
     print(f"  {nm[i]:40s} {st[i + 1] - st[i]:8d} clk")
 print("  step total", st[10] - st[0], "clk")
+print("  cluster.sync waits (CTA 0, thread 0):", [st[10 + 2 * n] - st[10 + 2 * n - 1] for n in range(1, 8)])
+
+
+# ---- reverse scan: per-step composition vs cluster kernel
+eng16.world_losses()
+for fused in (False, True):
+    eng16.use_fused_bwd = fused
+    eng16.world_backward()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        eng16.world_backward()
+    e1.record()
+    torch.cuda.synchronize()
+    print("world_backward with", "cluster reverse scan" if fused else "per-step reverse scan (eager)", e0.elapsed_time(e1) / 3, "ms", ops16.bwd_scan_kernel)
+e0.record()
+for _ in range(5):
+    ops16.rssm_observe_bwd(eng16)
+e1.record()
+torch.cuda.synchronize()
+print("cluster reverse scan kernel (+prep)", e0.elapsed_time(e1) / 5, "ms")
+sb = ops16.scratch[:64].view(torch.int64)[:16].cpu().tolist()
+nb = ["B1 unimix bwd + allgather", "sync1", "store + contract Wr1T + LN bwd a + push", "sync2", "combine + LN bwd b + allgather", "sync3",
+      "stores + contract Wr0hT + GRU bwd + push", "sync4", "combine + LN bwd b x3 + allgather x3", "sync5",
+      "stores + contract WgruT + LN bwd a + push", "sync6", "combine + LN bwd b + allgather", "sync7", "stores + contract WmlpzT + carry"]
+for i in range(15):
+    print(f"  {nb[i]:46s} {sb[i + 1] - sb[i]:8d} clk")
+print("  step total", sb[15] - sb[0], "clk")
