@@ -141,16 +141,19 @@ size_t dv3_rssm_observe_fwd_scratch_bytes(void);
 int dv3_rssm_observe_fwd(const Dv3ScanFwdArgs* args, void* stream);
 /* Same scan on ONE thread-block cluster (16 CTAs, else 8): bf16 weight rows streamed from L2 into mma.sync fragments, activations
  * and LayerNorm partials exchanged through distributed shared memory, hardware cluster barriers instead of grid-wide ones.
- * Needs bf16 copies of the three in-loop weight matrices, Wmlp[:, :G*Kc]^T in fp32 (one-hot z = row gather) and the hoisted
+ * Needs the three in-loop weight matrices packed by dv3_pack_mma_a, Wmlp[:, :G*Kc]^T in fp32 (one-hot z = row gather) and the hoisted
  * action projection aW[t] = a_t . Wmlp[:, G*Kc:]^T.  DV3_ERR_UNSUPPORTED when the shape / device cannot run it. */
 typedef struct Dv3ScanClusterExtra {
-  const void* Wgru_bf16; int ld_wgru;   /* [3D, D+U] bf16 */
-  const void* Wr0_bf16; int ld_wr0;     /* [Hh, D+E] bf16 (first D columns used) */
-  const void* Wr1_bf16; int ld_wr1;     /* [G*Kc, Hh] bf16 */
+  const void* Wgru_pk;                  /* dv3_pack_mma_a(3D, D+U, Wgru)        */
+  const void* Wr0_pk;                   /* dv3_pack_mma_a(Hh, D, Wr0[:, :D])    */
+  const void* Wr1_pk;                   /* dv3_pack_mma_a(G*Kc, Hh, Wr1)        */
   const float* WmlpzT;                  /* [G*Kc, U] fp32 */
   const float* aW;                      /* [T*B, U] fp32 */
 } Dv3ScanClusterExtra;
 int dv3_rssm_observe_fwd_cluster(const Dv3ScanFwdArgs* args, const Dv3ScanClusterExtra* extra, void* stream);
+/* Weight matrix -> bf16 in mma.sync.m16n8k16 A-fragment order (the operand layout of the two cluster scan kernels): element
+ * (row, k) is src[row * stride_r + k * stride_k], R % 16 == 0, K % 32 == 0; dst holds R*K bf16. */
+int dv3_pack_mma_a(int R, int K, const float* src, long long stride_r, long long stride_k, void* dst_bf16, void* stream);
 
 /* Reverse scan (backward through time of the same loop) on one thread-block cluster: what autograd does for RSSM.dynamic inside
  * rec_loss.backward() (dreamer_v3.py:177).  Inputs: the tensors saved by the forward scan, dL/d post_logits (KL) and dL/d latent
@@ -169,10 +172,10 @@ typedef struct Dv3ScanBwdArgs {
   const float* x_gru; int ld_xgru;                      /* [T*B, D+U]: h_in in the first D columns */
   const float* feat_pre; const float* feat_mean; const float* feat_rstd;
   const float* g_r; const float* b_r; const float* g_gru; const float* b_gru; const float* g_mlp; const float* b_mlp;
-  const void* Wr1T_bf16; int ld_wr1t;                   /* [Hh, G*Kc]  = Wr1^T            */
-  const void* Wr0hT_bf16; int ld_wr0ht;                 /* [D, Hh]     = Wr0[:, :D]^T     */
-  const void* WgruT_bf16; int ld_wgrut;                 /* [D+U, 3D]   = Wgru^T           */
-  const void* WmlpzT_bf16; int ld_wmlpzt;               /* [G*Kc, U]   = Wmlp[:, :G*Kc]^T */
+  const void* Wr1T_pk;                                  /* dv3_pack_mma_a of Wr1^T [Hh, G*Kc], Wr0[:, :D]^T [D, Hh],       */
+  const void* Wr0hT_pk;                                 /* Wgru^T [D+U, 3D], Wmlp[:, :G*Kc]^T [G*Kc, U] (strides swapped:  */
+  const void* WgruT_pk;                                 /* no transposed copy is materialised)                             */
+  const void* WmlpzT_pk;
   float* dpost_raw; float* dhidr_pre; float* dln_r; float* dgates_pre; float* dln_gru; float* dfeat_pre; float* dln_feat;
   void* dpost_raw_bf16; void* dhidr_pre_bf16; void* dgates_pre_bf16; void* dfeat_pre_bf16;   /* optional mirrors (NULL = none) */
   long long* dbg;                                       /* optional: 16 clock64 stamps of CTA 0 at step T-2 */

@@ -47,6 +47,7 @@ SIGNATURES = {
     "dv3_rssm_observe_fwd": [c_fp, c_fp],
     "dv3_rssm_observe_fwd_cluster": [c_fp, c_fp, c_fp],
     "dv3_rssm_observe_bwd_cluster": [c_fp, c_fp],
+    "dv3_pack_mma_a": [_i, _i, c_fp, _ll, _ll, c_fp, c_fp],
     "dv3_unimix_bwd_prep": [_i, _i, _i, _f, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_unimix_fwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp],
     "dv3_sample_onehot": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
@@ -96,8 +97,7 @@ class ScanFwdArgs(C.Structure):
 
 class ScanClusterExtra(C.Structure):
     """Mirror of `Dv3ScanClusterExtra` (include/dv3_b200.h)."""
-    _fields_ = [("Wgru_bf16", c_fp), ("ld_wgru", _i), ("Wr0_bf16", c_fp), ("ld_wr0", _i), ("Wr1_bf16", c_fp), ("ld_wr1", _i),
-                ("WmlpzT", c_fp), ("aW", c_fp)]
+    _fields_ = [("Wgru_pk", c_fp), ("Wr0_pk", c_fp), ("Wr1_pk", c_fp), ("WmlpzT", c_fp), ("aW", c_fp)]
 
 
 class ScanBwdArgs(C.Structure):
@@ -108,8 +108,7 @@ class ScanBwdArgs(C.Structure):
         ("hidr_pre", c_fp), ("hidr_mean", c_fp), ("hidr_rstd", c_fp), ("gates_pre", c_fp), ("gru_mean", c_fp), ("gru_rstd", c_fp),
         ("x_gru", c_fp), ("ld_xgru", _i), ("feat_pre", c_fp), ("feat_mean", c_fp), ("feat_rstd", c_fp),
         ("g_r", c_fp), ("b_r", c_fp), ("g_gru", c_fp), ("b_gru", c_fp), ("g_mlp", c_fp), ("b_mlp", c_fp),
-        ("Wr1T_bf16", c_fp), ("ld_wr1t", _i), ("Wr0hT_bf16", c_fp), ("ld_wr0ht", _i), ("WgruT_bf16", c_fp), ("ld_wgrut", _i),
-        ("WmlpzT_bf16", c_fp), ("ld_wmlpzt", _i),
+        ("Wr1T_pk", c_fp), ("Wr0hT_pk", c_fp), ("WgruT_pk", c_fp), ("WmlpzT_pk", c_fp),
         ("dpost_raw", c_fp), ("dhidr_pre", c_fp), ("dln_r", c_fp), ("dgates_pre", c_fp), ("dln_gru", c_fp), ("dfeat_pre", c_fp),
         ("dln_feat", c_fp),
         ("dpost_raw_bf16", c_fp), ("dhidr_pre_bf16", c_fp), ("dgates_pre_bf16", c_fp), ("dfeat_pre_bf16", c_fp),
@@ -508,11 +507,12 @@ class CudaOps:
         if self.use_mirrors and self.use_cluster_scan and getattr(eng, "aW", None) is not None:
             # one thread-block cluster, bf16 weights streamed into mma.sync fragments, DSMEM exchange (rssm_scan_cluster.cu)
             x = ScanClusterExtra()
-            x.Wgru_bf16, x.ld_wgru = self._m16(_p(eng.Wgru)), eng.Wgru.stride(0)
-            x.Wr0_bf16, x.ld_wr0 = self._m16(_p(eng.Wr0)), eng.Wr0.stride(0)
-            x.Wr1_bf16, x.ld_wr1 = self._m16(_p(eng.Wr1)), eng.Wr1.stride(0)
+            D, U, Hh, S = eng.D, eng.U, eng.Hh, eng.S
+            x.Wgru_pk = self._pack(eng, "gru", 3 * D, D + U, eng.Wgru, eng.Wgru.stride(0), 1)
+            x.Wr0_pk = self._pack(eng, "r0", Hh, D, eng.Wr0, eng.Wr0.stride(0), 1)
+            x.Wr1_pk = self._pack(eng, "r1", S, Hh, eng.Wr1, eng.Wr1.stride(0), 1)
             x.WmlpzT, x.aW = _p(eng.W_mlpzT), _p(eng.aW)
-            if x.Wgru_bf16 and x.Wr0_bf16 and x.Wr1_bf16:
+            if x.Wgru_pk and x.Wr0_pk and x.Wr1_pk:
                 rc = self.lib.dv3_rssm_observe_fwd_cluster(C.addressof(a), C.addressof(x), self._s())
                 if rc == 0:
                     self.launches += 1
@@ -529,6 +529,19 @@ class CudaOps:
         self.launches += 1
         return True
 
+    def _pack(self, eng, name, R, K, W, stride_r, stride_k):
+        """bf16 copy of a weight matrix (or its transpose: swap the strides) in mma.sync A-fragment order for the cluster scan
+        kernels; the buffer is created on first use (eager warm-up step) and refilled every step.  None if the shape does not tile."""
+        if (R & 15) or (K & 31):
+            return None
+        pk = eng.__dict__.setdefault("_packed", {})
+        buf = pk.get(name)
+        if buf is None:
+            buf = pk[name] = torch.empty(R * K, dtype=torch.bfloat16, device=self.device)
+        self.launches += 1
+        _chk(self.lib.dv3_pack_mma_a(R, K, W.data_ptr(), stride_r, stride_k, buf.data_ptr(), self._s()), "dv3_pack_mma_a")
+        return buf.data_ptr()
+
     def unimix_bwd_prep(self, raw, groups, K, unimix, ps, coef, pn):
         pr, R, _, ldr = _mat(raw)
         assert ps.is_contiguous() and coef.is_contiguous() and pn.is_contiguous()
@@ -540,7 +553,10 @@ class CudaOps:
         the shape / device is outside the kernel's plan (the engine then runs the per-step composition)."""
         if not (self.use_mirrors and self.use_cluster_scan):
             return False
-        w16 = [self._m16(_p(t)) for t in (eng.W_r1T, eng.W_r0hT, eng.W_gruT, eng.W_mlpzT)]
+        D, U, Hh, S = eng.D, eng.U, eng.Hh, eng.S
+        # transposed weights straight from the fp32 parameters (strides swapped), in MMA-fragment order
+        w16 = [self._pack(eng, "r1T", Hh, S, eng.Wr1, 1, eng.Wr1.stride(0)), self._pack(eng, "r0hT", D, Hh, eng.Wr0, 1, eng.Wr0.stride(0)),
+               self._pack(eng, "gruT", D + U, 3 * D, eng.Wgru, 1, eng.Wgru.stride(0)), self._pack(eng, "mlpzT", S, U, eng.Wmlp, 1, eng.Wmlp.stride(0))]
         if any(w is None for w in w16):
             return False
         eng.ops.unimix_bwd_prep(eng.post_raw, eng.G, eng.K, float(eng.cfg.algo.unimix), eng.ub_ps, eng.ub_coef, eng.ub_pn)
@@ -554,10 +570,7 @@ class CudaOps:
         a.x_gru, a.ld_xgru = _p(eng.x_gru), eng.x_gru.stride(0)
         a.feat_pre, a.feat_mean, a.feat_rstd = _p(eng.feat_pre), _p(eng.feat_mean), _p(eng.feat_rstd)
         a.g_r, a.b_r, a.g_gru, a.b_gru, a.g_mlp, a.b_mlp = _p(eng.g_r), _p(eng.b_r), _p(eng.g_gru), _p(eng.b_gru), _p(eng.g_mlp), _p(eng.b_mlp)
-        a.Wr1T_bf16, a.ld_wr1t = w16[0], eng.W_r1T.stride(0)
-        a.Wr0hT_bf16, a.ld_wr0ht = w16[1], eng.W_r0hT.stride(0)
-        a.WgruT_bf16, a.ld_wgrut = w16[2], eng.W_gruT.stride(0)
-        a.WmlpzT_bf16, a.ld_wmlpzt = w16[3], eng.W_mlpzT.stride(0)
+        a.Wr1T_pk, a.Wr0hT_pk, a.WgruT_pk, a.WmlpzT_pk = w16
         a.dpost_raw, a.dhidr_pre, a.dln_r = _p(eng.dpost_raw), _p(eng.dhidr_pre), _p(eng.dln_r)
         a.dgates_pre, a.dln_gru, a.dfeat_pre, a.dln_feat = _p(eng.dgates_pre), _p(eng.dln_gru), _p(eng.dfeat_pre), _p(eng.dln_feat)
         a.dpost_raw_bf16, a.dhidr_pre_bf16 = self._m16(_p(eng.dpost_raw)), self._m16(_p(eng.dhidr_pre))

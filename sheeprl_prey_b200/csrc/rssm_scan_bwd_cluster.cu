@@ -126,10 +126,10 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
   const int npairs = B * gper;
   const int sld = max(max(sper, hper), max(3 * dper, uper));
   typedef __nv_bfloat16 bf;
-  const bf* Wr1T = reinterpret_cast<const bf*>(a.Wr1T_bf16);
-  const bf* Wr0hT = reinterpret_cast<const bf*>(a.Wr0hT_bf16);
-  const bf* WgruT = reinterpret_cast<const bf*>(a.WgruT_bf16);
-  const bf* WmlpzT = reinterpret_cast<const bf*>(a.WmlpzT_bf16);
+  const uint4* Wr1T = reinterpret_cast<const uint4*>(a.Wr1T_pk);      // transposed weights packed by dv3_pack_mma_a
+  const uint4* Wr0hT = reinterpret_cast<const uint4*>(a.Wr0hT_pk);
+  const uint4* WgruT = reinterpret_cast<const uint4*>(a.WgruT_pk);
+  const uint4* WmlpzT = reinterpret_cast<const uint4*>(a.WmlpzT_pk);
   bf* m_pr = reinterpret_cast<bf*>(a.dpost_raw_bf16);
   bf* m_hp = reinterpret_cast<bf*>(a.dhidr_pre_bf16);
   bf* m_gp = reinterpret_cast<bf*>(a.dgates_pre_bf16);
@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     store_saved(a.dpost_raw + row0 * S + s0, m_pr ? m_pr + row0 * S + s0 : nullptr, S, sv_pr, stage, sld, sper, B);
 
     // ================= B2: d hid = d post_raw . Wr1 (own columns), LayerNorm + SiLU backward =================
-    contract(Wr1T, a.ld_wr1t, hper >> 4, h0, hper >> 4, 0, S, x_pr, ld_pr, part, outb);
+    contract(Wr1T, hper >> 4, h0, hper >> 4, 0, S, x_pr, ld_pr, part, outb);
     ln_bwd_a(outb, f_hp, hper, f_st, f_st + MB, p_r, xhb, sv_lr);
     __syncthreads();
     sum2_push(outb, xhb, hper, lnp, c, CL);
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     if (t > 0) fetch_b2(t - 1);
 
     // ================= B3: dh_t += d hidr_pre . Wr0[:, :D] (own units), GRU gate backward =================
-    contract(Wr0hT, a.ld_wr0ht, dper >> 4, d0, dper >> 4, 0, Hh, x_hp, ld_hp, part, outb);
+    contract(Wr0hT, dper >> 4, d0, dper >> 4, 0, Hh, x_hp, ld_hp, part, outb);
 #pragma unroll 1
     for (int e = tid; e < MB * dper; e += CT) {
       const int m = e >> lg_d, dl = e & (dper - 1);
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     if (t > 0) fetch_b3(t - 1);
 
     // ================= B4: [dh_{t-1} part | d feat] = d gates_pre . Wgru (own columns), LayerNorm + SiLU backward =================
-    contract(WgruT, a.ld_wgrut, (dper + uper) >> 4, d0, dper >> 4, D + u0 - d0, D3, x_gp, ld_gp, part, outb);   // dper == uper
+    contract(WgruT, (dper + uper) >> 4, d0, dper >> 4, D + u0 - d0, D3, x_gp, ld_gp, part, outb);   // dper == uper
 #pragma unroll 1
     for (int e = tid; e < MB * dper; e += CT) dhp[e] = outb[(e & (dper - 1)) * OB + (e >> lg_d)];
     ln_bwd_a(outb + dper * OB, f_fp, uper, f_st + 4 * MB, f_st + 5 * MB, p_mlp, xhb, sv_lf);
@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     if (t > 0) fetch_b4(t - 1);
 
     // ================= B5: dz_{t-1} = d feat_pre . Wmlp[:, :S] (own categoricals); carry through the reset mask =================
-    contract(WmlpzT, a.ld_wmlpzt, sper >> 4, s0, sper >> 4, 0, U, x_fp, ld_fp, part, outb);
+    contract(WmlpzT, sper >> 4, s0, sper >> 4, 0, U, x_fp, ld_fp, part, outb);
     const int* rs_t = s_first + t * MB;
 #pragma unroll 1
     for (int e = tid; e < MB * sper; e += CT) { const int m = e >> lg_s; dzc[e] = rs_t[m] ? 0.f : outb[(e & (sper - 1)) * OB + m]; }
@@ -415,10 +415,9 @@ extern "C" int dv3_rssm_observe_bwd_cluster(const Dv3ScanBwdArgs* h, void* strea
   if (!h) return DV3_ERR_ARG;
   if (h->B < 1 || h->B > MB || h->T < 1 || h->G < 1 || h->Kc < 1) return DV3_ERR_UNSUPPORTED;
   const int S = h->G * h->Kc;
-  if (!h->Wr1T_bf16 || !h->Wr0hT_bf16 || !h->WgruT_bf16 || !h->WmlpzT_bf16) return DV3_ERR_UNSUPPORTED;
-  if ((S & 31) || (h->Hh & 31) || (h->D & 31) || (h->U & 31) || (h->ld_wr1t & 7) || (h->ld_wr0ht & 7) || (h->ld_wgrut & 7) || (h->ld_wmlpzt & 7) ||
-      (h->ld_dlat & 3) || (h->ld_xgru & 3) ||
-      (((uintptr_t)h->Wr1T_bf16 | (uintptr_t)h->Wr0hT_bf16 | (uintptr_t)h->WgruT_bf16 | (uintptr_t)h->WmlpzT_bf16 | (uintptr_t)h->ps | (uintptr_t)h->coef |
+  if (!h->Wr1T_pk || !h->Wr0hT_pk || !h->WgruT_pk || !h->WmlpzT_pk) return DV3_ERR_UNSUPPORTED;
+  if ((S & 31) || (h->Hh & 31) || (h->D & 31) || (h->U & 31) || (h->ld_dlat & 3) || (h->ld_xgru & 3) ||
+      (((uintptr_t)h->Wr1T_pk | (uintptr_t)h->Wr0hT_pk | (uintptr_t)h->WgruT_pk | (uintptr_t)h->WmlpzT_pk | (uintptr_t)h->ps | (uintptr_t)h->coef |
         (uintptr_t)h->pn | (uintptr_t)h->dpost_logits | (uintptr_t)h->dlatent | (uintptr_t)h->hidr_pre | (uintptr_t)h->gates_pre | (uintptr_t)h->x_gru |
         (uintptr_t)h->feat_pre | (uintptr_t)h->dpost_raw_bf16 | (uintptr_t)h->dhidr_pre_bf16 | (uintptr_t)h->dgates_pre_bf16 |
         (uintptr_t)h->dfeat_pre_bf16) & 15))

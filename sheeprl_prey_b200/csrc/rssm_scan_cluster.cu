@@ -27,9 +27,9 @@ using namespace sc;
 
 struct KArgs {
   Dv3ScanFwdArgs a;
-  const __nv_bfloat16* Wgru16; int ld_wgru16;
-  const __nv_bfloat16* Wr0_16; int ld_wr0_16;
-  const __nv_bfloat16* Wr1_16; int ld_wr1_16;
+  const uint4* Wgru_pk;         // in-loop weights packed in MMA-fragment order (dv3_pack_mma_a)
+  const uint4* Wr0_pk;
+  const uint4* Wr1_pk;
   const float* WmlpzT;          // [S, U] fp32 = Wmlp[:, :S]^T
   const float* aW;              // [T*B, U] fp32 = masked action . Wmlp[:, S:]^T
   long long* dbg;
@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
     store_rows(a.x_gru + (size_t)row0 * a.ld_xgru + D + u0, a.ld_xgru, dfr, sld, uper, B);
 
     // ================= P2: GRU gates: own rows {d, D+d, 2D+d} of Wgru . [h, feat] =================
-    contract(k.Wgru16, k.ld_wgru16, nt_g, d0, tg, D, KG, xg, ldxg, part, outb);      // outb row = gate * dper + dl
+    contract(k.Wgru_pk, nt_g, d0, tg, D, KG, xg, ldxg, part, outb);      // outb row = gate * dper + dl
     SDBG(4);
     ln_push(outb, 3 * dper, lnp, c, CL);
     SDBG(15);
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
     store_rows(a.x_rep + (size_t)row0 * a.ld_xrep + d0, a.ld_xrep, hown, dper, dper, B);
 
     // ================= P3: posterior hidden: own rows of Wr0[:, :D] . h' + (e_t . Wr0[:, D:]^T + b) =================
-    contract(k.Wr0_16, k.ld_wr0_16, nt_h, h0, nt_h, 0, D, xg, ldxg, part, outb);
+    contract(k.Wr0_pk, nt_h, h0, nt_h, 0, D, xg, ldxg, part, outb);
 #pragma unroll 1
     for (int e = tid; e < B * hper; e += CT) { const int m = e >> lg_h, hl = e & (hper - 1); outb[hl * OB + m] += s_ew[e]; }
     __syncthreads();
@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
     store_rows(a.hidr + (size_t)row0 * Hh + h0, Hh, dfr, sld, hper, B);
 
     // ================= P4: posterior logits of the own categoricals, unimix, inverse-CDF sample =================
-    contract(k.Wr1_16, k.ld_wr1_16, nt_s, s0, nt_s, 0, Hh, hid, ldh, part, outb);
+    contract(k.Wr1_pk, nt_s, s0, nt_s, 0, Hh, hid, ldh, part, outb);
     SDBG(8);
 #pragma unroll 1
     for (int p = warp; p < npairs; p += CW) {                // one warp per (batch row, own categorical); lane = class (Kc <= 32)
@@ -265,22 +265,20 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
         const float pr = (1.f - a.unimix) * (e1 / se) + a.unimix / (float)Kc;
         lu = on ? logf(fminf(fmaxf(pr, DV3_EPS32), 1.f - DV3_EPS32)) : -INFINITY;
       }
-      const float mx2 = warp_max(lu);
-      const float se2 = warp_sum(on ? expf(lu - mx2) : 0.f);
-      const float lse = mx2 + logf(se2);
-      const float x3 = on ? (lu - lse) : -INFINITY;       // probs = softmax(lu - lse), as torch's Categorical(logits=lu).probs
-      const float mx3 = warp_max(x3);
-      const float e3 = on ? expf(x3 - mx3) : 0.f;
-      const float se3 = warp_sum(e3);
-      const float prob = e3 / se3;
-      int choice = 0;
+      // Sampling probabilities: Categorical(logits = lu).probs = softmax(lu) = pm / sum(pm) up to fp32 round-off (the reference
+      // renormalises log(pm) twice); with bf16 contractions upstream that round-off is far below the logits' own error, so the
+      // draw uses pm directly and a warp prefix sum instead of the sequential cumsum of the fp32 kernels.
+      float prob = (a.unimix > 0.f) ? (on ? fminf(fmaxf((1.f - a.unimix) * (e1 / se) + a.unimix / (float)Kc, DV3_EPS32), 1.f - DV3_EPS32) : 0.f)
+                                    : (e1 / se);
+      prob = prob / warp_sum(prob);
+      int choice;
       if (a.forced_idx) {
         choice = __float_as_int(s_uu[p]);
-      } else {                                             // idx = #{k : cumsum_k(p) <= u}: sequential fp32 cumsum (the sampling contract),
-        const float uu = s_uu[p];                          // every lane runs the same chain on shuffled-in probabilities
-        float cs = 0.f;
-#pragma unroll 4
-        for (int kk = 0; kk < Kc; ++kk) { cs += __shfl_sync(0xffffffffu, prob, kk); choice += (cs <= uu) ? 1 : 0; }
+      } else {                                             // idx = #{k : cumsum_k(p) <= u}
+        float cs = prob;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const float v = __shfl_up_sync(0xffffffffu, cs, o); if (lane >= o) cs += v; }
+        choice = __popc(__ballot_sync(0xffffffffu, on && cs <= s_uu[p]));
         if (choice > Kc - 1) choice = Kc - 1;
       }
       if (on) {
@@ -364,10 +362,9 @@ extern "C" int dv3_rssm_observe_fwd_cluster(const Dv3ScanFwdArgs* h, const Dv3Sc
   if (h->B < 1 || h->B > MB || h->T < 1 || h->G < 1 || h->Kc < 1 || h->Kc > 32 || (h->Kc & 3) || (h->ld_xmlp & 3) ||
       ((uintptr_t)h->x_mlp & 15))
     return DV3_ERR_UNSUPPORTED;
-  if (!x->Wgru_bf16 || !x->Wr0_bf16 || !x->Wr1_bf16 || !x->WmlpzT || !x->aW) return DV3_ERR_UNSUPPORTED;
+  if (!x->Wgru_pk || !x->Wr0_pk || !x->Wr1_pk || !x->WmlpzT || !x->aW) return DV3_ERR_UNSUPPORTED;
   const int KG = h->D + h->U;
-  if ((KG & 31) || (h->D & 31) || (h->Hh & 31) || (x->ld_wgru & 7) || (x->ld_wr0 & 7) || (x->ld_wr1 & 7) ||
-      ((uintptr_t)x->Wgru_bf16 & 15) || ((uintptr_t)x->Wr0_bf16 & 15) || ((uintptr_t)x->Wr1_bf16 & 15))
+  if ((KG & 31) || (h->D & 31) || (h->Hh & 31) || ((uintptr_t)x->Wgru_pk & 15) || ((uintptr_t)x->Wr0_pk & 15) || ((uintptr_t)x->Wr1_pk & 15))
     return DV3_ERR_UNSUPPORTED;   // 16 B fragment loads, 32-wide k chunks
   int dev = 0, max_smem = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -375,9 +372,9 @@ extern "C" int dv3_rssm_observe_fwd_cluster(const Dv3ScanFwdArgs* h, const Dv3Sc
   cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   KArgs k;
   k.a = *h;
-  k.Wgru16 = reinterpret_cast<const __nv_bfloat16*>(x->Wgru_bf16); k.ld_wgru16 = x->ld_wgru;
-  k.Wr0_16 = reinterpret_cast<const __nv_bfloat16*>(x->Wr0_bf16); k.ld_wr0_16 = x->ld_wr0;
-  k.Wr1_16 = reinterpret_cast<const __nv_bfloat16*>(x->Wr1_bf16); k.ld_wr1_16 = x->ld_wr1;
+  k.Wgru_pk = reinterpret_cast<const uint4*>(x->Wgru_pk);
+  k.Wr0_pk = reinterpret_cast<const uint4*>(x->Wr0_pk);
+  k.Wr1_pk = reinterpret_cast<const uint4*>(x->Wr1_pk);
   k.WmlpzT = x->WmlpzT;
   k.aW = x->aW;
   k.dbg = (getenv("DV3_SCAN_DEBUG") && h->scratch && h->scratch_bytes >= 64 * sizeof(long long)) ? reinterpret_cast<long long*>(h->scratch) : nullptr;
@@ -391,4 +388,35 @@ extern "C" int dv3_rssm_observe_fwd_cluster(const Dv3ScanFwdArgs* h, const Dv3Sc
     return launch_cluster(k, CL, smem, (cudaStream_t)stream_, false);
   }
   return DV3_ERR_UNSUPPORTED;
+}
+
+// ---- weights in MMA-fragment order -----------------------------------------------------------------------------------------------
+// dst[((tile * (K/32) + chunk) * 32 + lane) * 16 + j] (bf16) with lane = 4 gid + tig, j = 8 mma + 2 reg + half:
+//   row = 16 tile + gid + 8 (reg & 1),   k = 32 chunk + 8 tig + 4 mma + 2 (reg >> 1) + half
+// = the a0..a3 registers of the two mma.sync.m16n8k16 of a 32-wide k chunk (k order inside the chunk permuted as in sc::contract).
+// src element (row, k) is src[row * stride_r + k * stride_k] (fp32), so the same kernel packs W and W^T.
+namespace {
+__global__ void __launch_bounds__(256) pack_mma_a_kernel(int R, int K, const float* __restrict__ src, long long stride_r, long long stride_k,
+                                                         __nv_bfloat16* __restrict__ dst) {
+  const size_t n = (size_t)R * K;
+  const int nch = K >> 5;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int j = (int)(i & 15), lane = (int)((i >> 4) & 31);
+    const size_t tc = i >> 9;
+    const int chunk = (int)(tc % nch), tile = (int)(tc / nch);
+    const int gid = lane >> 2, tig = lane & 3, mma = j >> 3, reg = (j >> 1) & 3, half = j & 1;
+    const int row = 16 * tile + gid + 8 * (reg & 1), kk = 32 * chunk + 8 * tig + 4 * mma + 2 * (reg >> 1) + half;
+    dst[i] = __float2bfloat16_rn(src[(size_t)row * stride_r + (size_t)kk * stride_k]);
+  }
+}
+}  // namespace
+
+extern "C" int dv3_pack_mma_a(int R, int K, const float* src, long long stride_r, long long stride_k, void* dst_bf16, void* stream) {
+  if (R <= 0 || K <= 0 || !src || !dst_bf16) return DV3_ERR_ARG;
+  if ((R & 15) || (K & 31)) return DV3_ERR_UNSUPPORTED;
+  size_t g = ((size_t)R * K + 255) / 256;
+  if (g > 148 * 16) g = 148 * 16;
+  pack_mma_a_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(R, K, src, stride_r, stride_k, reinterpret_cast<__nv_bfloat16*>(dst_bf16));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
 }

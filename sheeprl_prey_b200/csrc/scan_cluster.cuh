@@ -37,12 +37,15 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 
 // Contraction of `ntiles` tiles of 16 weight rows with X[MB][K] (bf16, shared memory, row stride ldx):
 //   outb[(ti * 16 + r) * OB + m] = sum_k W[tile_row(ti) + r, k] * X[m, k],  tile_row(ti) = row_base + (ti / tpb) * blk_stride + (ti % tpb) * 16
-// (W bf16 in global memory, row stride ldw).  Work unit = (tile, k-part): ksplit = 8 / gcd(ntiles, 8) so that the units divide evenly
-// over the CW = 8 warps.  Within a 32-wide k chunk thread (gid, tig) loads the 8 consecutive k of its two weight rows (global, 16 B)
-// and of its two batch rows (shared, 16 B); the contraction index is permuted identically in the A and B fragments, so no shuffles /
-// ldmatrix are needed.  Partial sums go through part[tile][kq][16][MB] and are added in a fixed order (deterministic).
-static __device__ __noinline__ void contract(const __nv_bfloat16* __restrict__ W, int ldw, int ntiles, int row_base, int tpb, int blk_stride, int K,
-                                      const __nv_bfloat16* X, int ldx, float* part, float* outb) {
+// W is PACKED in MMA-fragment order by dv3_pack_mma_a (see rssm_scan_cluster.cu): for every (16-row tile, 32-wide k chunk) the 32
+// lanes' A fragments of the two m16n8k16 MMAs of the chunk are 32 contiguous bytes each -> two coalesced LDG.128 per lane and chunk,
+// no register shuffling, immediate-offset addressing in the unrolled loop.  The k order inside a chunk is permuted (thread tig owns
+// k = 8 tig .. 8 tig + 7); the B fragments read the same 8 consecutive k of the two batch rows from shared memory (LDS.128), so
+// the permutation is consistent and the sum is unchanged.
+// Work unit = (tile, k-part): ksplit = 8 / gcd(ntiles, 8) so that the units divide evenly over the CW = 8 warps.  Partial sums go
+// through part[tile][kq][16][MB] and are added in a fixed order (deterministic).
+static __device__ __noinline__ void contract(const uint4* __restrict__ Wp, int ntiles, int row_base, int tpb, int blk_stride, int K,
+                                             const __nv_bfloat16* X, int ldx, float* part, float* outb) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gid = lane >> 2, tig = lane & 3;
   const int g = (ntiles & 1) ? 1 : ((ntiles & 2) ? 2 : ((ntiles & 4) ? 4 : 8));
   const int ksplit = 8 / g, ks_shift = (ksplit == 8) ? 3 : ((ksplit == 4) ? 2 : ((ksplit == 2) ? 1 : 0));
@@ -54,20 +57,22 @@ static __device__ __noinline__ void contract(const __nv_bfloat16* __restrict__ W
     const int u = warp * upw + j, tile = u >> ks_shift, kq = u & (ksplit - 1);
     const int ch0 = (kq * nch) >> ks_shift, ch1 = ((kq + 1) * nch) >> ks_shift;
     const int blk = tile >> lg_tpb, trow = row_base + blk * blk_stride + (tile & (tpb - 1)) * 16;   // tpb is a power of two
-    const __nv_bfloat16* w0 = W + (size_t)(trow + gid) * ldw + tig * 8;
-    const __nv_bfloat16* w1 = w0 + (size_t)8 * ldw;
+    const uint4* wp = Wp + ((size_t)((trow >> 4) * nch + ch0) * 32 + lane) * 2;
+    const __nv_bfloat16* xa = xa_p + (ch0 << 5);
+    const __nv_bfloat16* xb = xb_p + (ch0 << 5);
     float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll 4
     for (int ch = ch0; ch < ch1; ++ch) {
-      const int k0 = ch << 5;
-      const uint4 wa = __ldg(reinterpret_cast<const uint4*>(w0 + k0));
-      const uint4 wb = __ldg(reinterpret_cast<const uint4*>(w1 + k0));
-      const uint4 xa = *reinterpret_cast<const uint4*>(xa_p + k0);
-      const uint4 xb = *reinterpret_cast<const uint4*>(xb_p + k0);
-      mma_bf16(acc[0], wa.x, wb.x, wa.y, wb.y, xa.x, xa.y);
-      mma_bf16(acc[0], wa.z, wb.z, wa.w, wb.w, xa.z, xa.w);
-      mma_bf16(acc[1], wa.x, wb.x, wa.y, wb.y, xb.x, xb.y);
-      mma_bf16(acc[1], wa.z, wb.z, wa.w, wb.w, xb.z, xb.w);
+      const uint4 w1 = __ldg(wp), w2 = __ldg(wp + 1);
+      const uint4 va = *reinterpret_cast<const uint4*>(xa);
+      const uint4 vb = *reinterpret_cast<const uint4*>(xb);
+      mma_bf16(acc[0], w1.x, w1.y, w1.z, w1.w, va.x, va.y);
+      mma_bf16(acc[0], w2.x, w2.y, w2.z, w2.w, va.z, va.w);
+      mma_bf16(acc[1], w1.x, w1.y, w1.z, w1.w, vb.x, vb.y);
+      mma_bf16(acc[1], w2.x, w2.y, w2.z, w2.w, vb.z, vb.w);
+      wp += 64;
+      xa += 32;
+      xb += 32;
     }
     float* p = part + (size_t)u * 256;
     *reinterpret_cast<float2*>(p + gid * MB + 2 * tig) = make_float2(acc[0][0], acc[0][1]);

@@ -260,7 +260,6 @@ class DV3Engine:
         self.eW = z(N, Hh)                       # e_t . Wr0[:, D:]^T + b_r0 for all t (hoisted out of the scan)
         self.ub_ps, self.ub_coef, self.ub_pn = z(N, S), z(N, S), z(N, S)   # unimix Jacobian factors (cluster reverse scan)
         self.use_fused_bwd = os.environ.get("DV3_FUSED_BWD_SCAN", "1") != "0"
-        _mirror(ops, self.W_r1T, self.W_r0hT, self.W_gruT, self.W_mlpzT)
         self.aW = z(N, U)                        # a_t . Wmlp[:, S:]^T for all t (hoisted out of the scan; cluster kernel)
         self.Wmlp_z = z(U, S)                    # compact copy of Wmlp[:, :S] for the rollout (row stride S+A is not TMA-loadable)
         _mirror(ops, self.x_rep, self.x_gru, self.x_mlp._base, self.latent, self.hidr, self.Wmlp_z, self.dpost_raw, self.dhidr_pre,
@@ -387,11 +386,7 @@ class DV3Engine:
         self.trans0.forward(self.zero_h)
         ops.unimix_fwd(self.trans0.out, G, K, mix, self.zreset_logits)
         ops.sample_onehot(self.zreset_logits, G, K, None, None, 1, self.zreset_idx, self.zreset)
-        # transposed copies of the weights the reverse scan contracts against
-        ops.transpose(self.Wr1, self.W_r1T)
-        ops.transpose(self.Wr0[:, :D], self.W_r0hT)
-        ops.transpose(self.Wgru, self.W_gruT)
-        ops.transpose(self.Wmlp[:, :S], self.W_mlpzT)
+        ops.transpose(self.Wmlp[:, :S], self.W_mlpzT)         # one-hot z input = row gather (cluster scan); reverse scan operand
         # a4: observe scan -- one persistent cooperative kernel when the shape fits, else the per-step composition
         fused = False
         if self.use_fused_scan:
@@ -490,6 +485,10 @@ class DV3Engine:
             fused_bwd = ops.rssm_observe_bwd(self)
             if not fused_bwd:
                 self.use_fused_bwd = False
+        if not fused_bwd:                                     # transposed copies of the weights the per-step reverse scan contracts against
+            ops.transpose(self.Wr1, self.W_r1T)
+            ops.transpose(self.Wr0[:, :D], self.W_r0hT)
+            ops.transpose(self.Wgru, self.W_gruT)
         for t in range(T - 1, -1, -1) if not fused_bwd else ():
             r = slice(t * B, (t + 1) * B)
             rp = slice((t - 1) * B, t * B)
