@@ -189,6 +189,10 @@ int dv3_unimix_bwd_prep(int R, int groups, int K, float mix, const float* raw, i
 int dv3_unimix_fwd(int R, int groups, int K, float mix, const float* raw, int ldr, float* logits, int ldo, void* stream);
 int dv3_sample_onehot(int R, int groups, int K, const float* logits, int ldl, const float* u, int ldu, const int* forced,
                       int ldf, int mode, int* idx, int ldi, float* onehot, int ldo, void* onehot_bf16, void* stream);
+/* dv3_unimix_fwd + dv3_sample_onehot(mode 0) in one launch (imagination rollout, dreamer_v3.py:232-257): `logits` (optional)
+ * receives the unimix logits; fast != 0 draws with a warp prefix sum instead of the sequential fp32 cumsum (bf16 precision mode). */
+int dv3_unimix_sample(int R, int groups, int K, float mix, const float* raw, int ldr, const float* u, int ldu, const int* forced, int ldf,
+                      int* idx, int ldi, float* onehot, int ldo, void* onehot_bf16, float* logits, int ldl, int fast, void* stream);
 int dv3_unimix_bwd(int R, int groups, int K, float mix, const float* raw, int ldr, const float* dlogits, int lddl,
                    const float* dz, int lddz, float* draw, int lddr, void* stream);
 

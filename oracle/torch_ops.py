@@ -187,6 +187,13 @@ class TorchOps:
         p = (1 - unimix) * p + unimix / K
         logits.copy_(torch.log(p.clamp(min=_EPS32, max=1 - _EPS32)).reshape(R, groups * K))
 
+    def unimix_sample(self, raw: Tensor, groups: int, K: int, unimix: float, u: Optional[Tensor], forced: Optional[Tensor],
+                      idx: Tensor, onehot: Tensor, logits: Optional[Tensor] = None) -> None:
+        """unimix_fwd followed by sample_onehot(mode=0) on its output."""
+        lg = torch.empty_like(raw) if logits is None else logits
+        self.unimix_fwd(raw, groups, K, unimix, lg)
+        self.sample_onehot(lg, groups, K, u, forced, 0, idx, onehot)
+
     def sample_onehot(self, logits: Tensor, groups: int, K: int, u: Optional[Tensor], forced: Optional[Tensor],
                       mode: int, idx: Tensor, onehot: Tensor) -> None:
         """probs = softmax(logits - logsumexp(logits)) per group; idx = forced, or argmax (mode=1), or the

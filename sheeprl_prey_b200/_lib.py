@@ -48,6 +48,7 @@ SIGNATURES = {
     "dv3_rssm_observe_fwd_cluster": [c_fp, c_fp, c_fp],
     "dv3_rssm_observe_bwd_cluster": [c_fp, c_fp],
     "dv3_pack_mma_a": [_i, _i, c_fp, _ll, _ll, c_fp, c_fp],
+    "dv3_unimix_sample": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, _i, _i, c_fp],
     "dv3_unimix_bwd_prep": [_i, _i, _i, _f, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_unimix_fwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp],
     "dv3_sample_onehot": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
@@ -405,6 +406,20 @@ class CudaOps:
         self.launches += 1
         _chk(self.lib.dv3_sample_onehot(R, groups, K, pl, ldl, pu, ldu, pf, ldf, mode, pi, ldi, po, ldo, self._m16(po), self._s()),
              "dv3_sample_onehot")
+
+    def unimix_sample(self, raw, groups, K, unimix, u, forced, idx, onehot, logits=None):
+        """unimix_fwd + sample_onehot(mode 0) in one launch; `logits` optionally receives the unimix logits."""
+        pr, R, _, ldr = _mat(raw)
+        pu, ldu = (None, 0) if u is None else (_mat(u)[0], _mat(u)[3])
+        pf, ldf = (None, 0) if forced is None else (_mat(forced)[0], _mat(forced)[3])
+        if forced is not None:
+            assert forced.dtype == torch.int32
+        pi, _, _, ldi = _mat(idx)
+        po, _, _, ldo = _mat(onehot)
+        pl, ldl = (None, 0) if logits is None else (_mat(logits)[0], _mat(logits)[3])
+        self.launches += 1
+        _chk(self.lib.dv3_unimix_sample(R, groups, K, unimix, pr, ldr, pu, ldu, pf, ldf, pi, ldi, po, ldo, self._m16(po), pl, ldl,
+                                        int(self.precision == "bf16"), self._s()), "dv3_unimix_sample")
 
     def unimix_bwd(self, raw, groups, K, unimix, dlogits, dz, draw):
         pr, R, _, ldr = _mat(raw)

@@ -116,6 +116,60 @@ ln_act_fwd_warp_kernel(int M, int U, const float* __restrict__ x, int ldx, const
   if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
 }
 
+// Same, row kept in registers: one 16 B load per lane and 128 columns, a single pass over global memory (U % 4 == 0, U <= 128 * NV,
+// 16 B aligned rows).  The imagination rollout calls this 60+ times per step on 1024 x 512 rows, where the three dependent
+// passes of the generic kernel cost three L2 round trips.
+template <int NV>
+__global__ void __launch_bounds__(LW_WARPS * 32)
+ln_act_fwd_warp_vec_kernel(int M, int U, const float* __restrict__ x, int ldx, const float* __restrict__ gamma,
+                           const float* __restrict__ beta, float eps, int act, float* __restrict__ y, int ldy,
+                           float* __restrict__ mean, float* __restrict__ rstd, __nv_bfloat16* __restrict__ y16) {
+  const int lane = threadIdx.x & 31;
+  const size_t row = (size_t)blockIdx.x * LW_WARPS + (threadIdx.x >> 5);
+  if (row >= (size_t)M) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + row * ldx);
+  const int n4 = U >> 2;
+  float4 v[NV];
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int i = lane + 32 * j;
+    v[j] = (i < n4) ? xr[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+  }
+  const float mu = warp_sum(s) / (float)U;
+  float q = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    if (lane + 32 * j < n4) {
+      const float a = v[j].x - mu, b = v[j].y - mu, c = v[j].z - mu, d = v[j].w - mu;
+      q = fmaf(a, a, q); q = fmaf(b, b, q); q = fmaf(c, c, q); q = fmaf(d, d, q);
+    }
+  }
+  const float rs = rsqrtf(warp_sum(q) / (float)U + eps);
+  float4* yr = reinterpret_cast<float4*>(y + row * ldy);
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int i = lane + 32 * j;
+    if (i < n4) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + i), b = __ldg(reinterpret_cast<const float4*>(beta) + i);
+      float4 o;
+      o.x = (v[j].x - mu) * rs * g.x + b.x; o.y = (v[j].y - mu) * rs * g.y + b.y;
+      o.z = (v[j].z - mu) * rs * g.z + b.z; o.w = (v[j].w - mu) * rs * g.w + b.w;
+      if (act) { o.x = siluf_(o.x); o.y = siluf_(o.y); o.z = siluf_(o.z); o.w = siluf_(o.w); }
+      yr[i] = o;
+      if (y16) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(y16 + row * ldy + 4 * i) = pk;
+      }
+    }
+  }
+  if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+}
+
 __global__ void __launch_bounds__(LW_WARPS * 32)
 ln_act_bwd_warp_kernel(int M, int U, const float* __restrict__ dy, int lddy, const float* __restrict__ x, int ldx,
                        const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
@@ -213,8 +267,18 @@ int dv3_u8_nchw_to_nhwc(int N, int C, int HW, const unsigned char* src, float sc
 int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
                         float* y, int ldy, float* mean, float* rstd, void* y_bf16, void* stream) {
   if (M <= 0 || U <= 0) return DV3_ERR_ARG;
-  ln_act_fwd_warp_kernel<<<(M + LW_WARPS - 1) / LW_WARPS, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(
-      M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
+  const bool vec = (U & 3) == 0 && U <= 1024 && (ldx & 3) == 0 && (ldy & 3) == 0 &&
+                   ((((uintptr_t)x | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0) && (((uintptr_t)y_bf16 & 7) == 0);
+  const dim3 grid((M + LW_WARPS - 1) / LW_WARPS);
+  if (vec && U <= 512)
+    ln_act_fwd_warp_vec_kernel<4><<<grid, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd,
+                                                                                    reinterpret_cast<__nv_bfloat16*>(y_bf16));
+  else if (vec)
+    ln_act_fwd_warp_vec_kernel<8><<<grid, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd,
+                                                                                    reinterpret_cast<__nv_bfloat16*>(y_bf16));
+  else
+    ln_act_fwd_warp_kernel<<<grid, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(
+        M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

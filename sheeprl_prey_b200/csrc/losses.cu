@@ -137,6 +137,62 @@ sample_onehot_kernel(int R, int groups, int K, const float* __restrict__ logits,
   }
 }
 
+// ---------------------------------------------------------------- unimix + sample in one pass (imagination rollout)
+// = unimix_fwd followed by sample_onehot(mode 0) on its output, same arithmetic; the unimix logits are written only if asked for.
+// fast != 0 (bf16 precision mode): the draw uses a warp prefix sum instead of the sequential fp32 cumsum of the sampling contract.
+template <int KRT>
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+unimix_sample_kernel(int R, int groups, int K, float mix, const float* __restrict__ raw, int ldr, const float* __restrict__ u, int ldu,
+                     const int* __restrict__ forced, int ldf, int* __restrict__ idx, int ldi, float* __restrict__ onehot, int ldo,
+                     __nv_bfloat16* __restrict__ onehot16, float* __restrict__ logits, int ldl, int fast) {
+  __shared__ float sp[WARPS_PER_BLOCK][KR * 32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int gid = blockIdx.x * WARPS_PER_BLOCK + w;
+  if (gid >= R * groups) return;
+  const int row = gid / groups, g = gid % groups;
+  Group<KRT> r, ps, pm, lu;
+  int choice;
+  if (forced && !logits) {
+    choice = forced[(size_t)row * ldf + g];
+  } else {
+    load_group(r, raw + (size_t)row * ldr + g * K, K, lane);
+    softmax_group(r, ps, K, lane);
+    if (mix > 0.f) unimix_group(ps, pm, lu, mix, K, lane);
+    else lu = r;
+    if (logits) { float* lo = logits + (size_t)row * ldl + g * K; for_k<KRT>(K, lane, [&](int j, int k) { lo[k] = lu.v[j]; }); }
+    if (forced) {
+      choice = forced[(size_t)row * ldf + g];
+    } else {
+      Group<KRT> ln, p;
+      normalise_group(lu, ln, p, K, lane);
+      const float uu = u[(size_t)row * ldu + g];
+      if (fast && KRT == 1) {
+        float cs = (lane < K) ? p.v[0] : 0.f;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const float v = __shfl_up_sync(0xffffffffu, cs, o); if (lane >= o) cs += v; }
+        choice = __popc(__ballot_sync(0xffffffffu, lane < K && cs <= uu));
+      } else {
+        for_k<KRT>(K, lane, [&](int j, int k) { sp[w][k] = p.v[j]; });
+        __syncwarp();
+        choice = 0;
+        if (lane == 0) {
+          float c = 0.f;
+          for (int k = 0; k < K; ++k) { c += sp[w][k]; choice += (c <= uu) ? 1 : 0; }
+        }
+        choice = __shfl_sync(0xffffffffu, choice, 0);
+      }
+      if (choice > K - 1) choice = K - 1;
+    }
+  }
+  if (lane == 0) idx[(size_t)row * ldi + g] = choice;
+  float* o = onehot + (size_t)row * ldo + g * K;
+  for_k<KRT>(K, lane, [&](int, int k) { o[k] = (k == choice) ? 1.f : 0.f; });
+  if (onehot16) {
+    __nv_bfloat16* o16 = onehot16 + (size_t)row * ldo + g * K;
+    for_k<KRT>(K, lane, [&](int, int k) { o16[k] = __float2bfloat16_rn((k == choice) ? 1.f : 0.f); });
+  }
+}
+
 // ---------------------------------------------------------------- unimix backward (+ straight-through)
 template <int KRT>
 __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
@@ -553,6 +609,16 @@ int dv3_sample_onehot(int R, int groups, int K, const float* logits, int ldl, co
   if (!forced && !mode && !u) return DV3_ERR_ARG;
   DV3_DISPATCH_KR(K, sample_onehot_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
       R, groups, K, logits, ldl, u, ldu, forced, ldf, mode, idx, ldi, onehot, ldo, reinterpret_cast<__nv_bfloat16*>(onehot_bf16)));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_unimix_sample(int R, int groups, int K, float mix, const float* raw, int ldr, const float* u, int ldu, const int* forced, int ldf,
+                      int* idx, int ldi, float* onehot, int ldo, void* onehot_bf16, float* logits, int ldl, int fast, void* stream) {
+  if (R <= 0 || groups <= 0 || K <= 0) return DV3_ERR_ARG;
+  if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
+  if (!forced && !u) return DV3_ERR_ARG;
+  DV3_DISPATCH_KR(K, unimix_sample_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
+      R, groups, K, mix, raw, ldr, u, ldu, forced, ldf, idx, ldi, onehot, ldo, reinterpret_cast<__nv_bfloat16*>(onehot_bf16), logits, ldl, fast));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -551,8 +551,7 @@ class DV3Engine:
             self.act_stack.forward(self.traj[r], i * N, (i + 1) * N)
             col = 0
             for j, k in enumerate(self.actions_dim):
-                ops.unimix_fwd(self.act_stack.out[r, col:col + k], 1, k, mix, self.act_logits[:, col:col + k])
-                ops.sample_onehot(self.act_logits[:, col:col + k], 1, k, u[:, j:j + 1], None if fidx is None else fidx[r, j:j + 1], 0,
+                ops.unimix_sample(self.act_stack.out[r, col:col + k], 1, k, mix, u[:, j:j + 1], None if fidx is None else fidx[r, j:j + 1],
                                   self.act_idx[r, j:j + 1], self.acts[r, col:col + k])
                 col += k
 
@@ -567,9 +566,8 @@ class DV3Engine:
             ops.gemm("NT", self.img_feat, self.Wgru[:, D:], self.img_gates, accumulate=True)
             ops.gru_gate_fwd(self.img_gates, self.g_gru, self.b_gru, self.traj[rp, S:], self.traj[r, S:], self.img_mean, self.img_rstd)
             self.trans.forward(self.traj[r, S:])
-            ops.unimix_fwd(self.trans.out, G, K, mix, self.img_logits)
-            ops.sample_onehot(self.img_logits, G, K, self.u_z[i - 1],
-                              None if forced is None else forced["z_idx"][i - 1], 0, self.z_idx[i - 1], self.traj[r, :S])
+            ops.unimix_sample(self.trans.out, G, K, mix, self.u_z[i - 1], None if forced is None else forced["z_idx"][i - 1],
+                              self.z_idx[i - 1], self.traj[r, :S])
             policy(i, self.u_act[i - 1], fa)
 
     def behaviour(self) -> None:

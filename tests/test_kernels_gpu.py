@@ -59,7 +59,8 @@ def test_transpose_copy(cuda_ops):
     assert torch.equal(d2[:, 20:80], s[:, 5:65]) and float(d2[:, :20].abs().sum()) == 0
 
 
-@pytest.mark.parametrize("M,U,act,eps", [(16, 512, 1, 1e-3), (1024, 640, 1, 1e-5), (3, 40, 0, 1e-5), (16, 1536, 1, 1e-3)])
+@pytest.mark.parametrize("M,U,act,eps", [(16, 512, 1, 1e-3), (1024, 640, 1, 1e-5), (3, 40, 0, 1e-5), (16, 1536, 1, 1e-3), (300, 512, 1, 1e-3),
+                                         (257, 1024, 0, 1e-5), (256, 24, 1, 1e-3)])
 def test_ln_act(cuda_ops, torch_ops, M, U, act, eps):
     x, g, b = rnd(M, U, scale=2.0) + 0.3, rnd(U) * 0.2 + 1, rnd(U) * 0.1
     outs = []
@@ -501,3 +502,26 @@ def test_bf16_side_outputs(cuda_ops_bf16):
     assert ops.gemm_log[0][-1] == "tma"
     ops.gemm_log = None
     assert rel(out.double(), y.bfloat16().double() @ W.bfloat16().double().t()) < 2e-5
+
+
+@pytest.mark.parametrize("R,groups,K", [(1024, 32, 32), (1024, 1, 100), (7, 1, 2), (64, 4, 18)])
+def test_unimix_sample_fused(cuda_ops, cuda_ops_bf16, R, groups, K):
+    """dv3_unimix_sample == dv3_unimix_fwd followed by dv3_sample_onehot (same indices, one-hots and logits); the bf16-mode
+    variant (warp prefix sum instead of the sequential cumsum) may only differ where the uniform sits on a CDF step."""
+    raw = rnd(R, groups * K, scale=3.0)
+    u = torch.rand(R, groups, device=DEV)
+    lg = torch.zeros(R, groups * K, device=DEV)
+    cuda_ops.unimix_fwd(raw, groups, K, 0.01, lg)
+    idx0 = torch.zeros(R, groups, dtype=torch.int32, device=DEV)
+    oh0 = torch.zeros(R, groups * K, device=DEV)
+    cuda_ops.sample_onehot(lg, groups, K, u, None, 0, idx0, oh0)
+    idx1, oh1, lg1 = torch.zeros_like(idx0), torch.zeros_like(oh0), torch.zeros_like(lg)
+    cuda_ops.unimix_sample(raw, groups, K, 0.01, u, None, idx1, oh1, logits=lg1)
+    assert torch.equal(idx1, idx0) and torch.equal(oh1, oh0) and torch.equal(lg1, lg)
+    idx2, oh2 = torch.zeros_like(idx0), torch.zeros_like(oh0)
+    cuda_ops.unimix_sample(raw, groups, K, 0.01, None, idx0, idx2, oh2)          # forced
+    assert torch.equal(idx2, idx0) and torch.equal(oh2, oh0)
+    idx3, oh3 = torch.zeros_like(idx0), torch.zeros_like(oh0)
+    cuda_ops_bf16.unimix_sample(raw, groups, K, 0.01, u, None, idx3, oh3)
+    assert float((idx3 != idx0).float().mean()) < 1e-3
+    assert torch.equal(oh3.reshape(R, groups, K).argmax(-1).int(), idx3) and float(oh3.sum()) == R * groups
