@@ -16,6 +16,41 @@
     if (e__ != cudaSuccess) return (int)e__;                  \
   } while (0)
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------------------------
+// A kernel launched through dv3_launch_pdl may be scheduled while its predecessor on the stream is still draining; it must call
+// pdl_sync() before its first access to global memory (griddepcontrol.wait = predecessor complete and flushed).  The prologue
+// before that point (index math, barrier / TMEM set-up, descriptor prefetch) overlaps the predecessor's tail and the launch
+// latency; inside the step's CUDA graph the attribute becomes a programmatic dependency edge.  Off unless $DV3_PDL=1 (no gain measured).
+// In a kernel launched the ordinary way both instructions are no-ops.
+static __device__ __forceinline__ void pdl_sync() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+#ifndef __CUDA_ARCH__
+#include <stdlib.h>
+static inline int dv3_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DV3_PDL"); v = (e && e[0] == '1') ? 1 : 0; }   // opt-in: measured 120.6 (on) vs 122.2 (off) steps/s
+  return v;
+}
+#endif
+template <typename... KA, typename... A>
+static inline cudaError_t dv3_launch_pdl(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+#ifndef __CUDA_ARCH__
+  at[0].val.programmaticStreamSerializationAllowed = dv3_pdl_enabled();
+#endif
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, KA(args)...);
+}
+
 static __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -124,6 +124,7 @@ __global__ void __launch_bounds__(LW_WARPS * 32)
 ln_act_fwd_warp_vec_kernel(int M, int U, const float* __restrict__ x, int ldx, const float* __restrict__ gamma,
                            const float* __restrict__ beta, float eps, int act, float* __restrict__ y, int ldy,
                            float* __restrict__ mean, float* __restrict__ rstd, __nv_bfloat16* __restrict__ y16) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const size_t row = (size_t)blockIdx.x * LW_WARPS + (threadIdx.x >> 5);
   if (row >= (size_t)M) return;
@@ -175,6 +176,7 @@ ln_act_bwd_warp_kernel(int M, int U, const float* __restrict__ dy, int lddy, con
                        const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
                        const float* __restrict__ rstd, int act, float* __restrict__ dx, int lddx, float* __restrict__ dln,
                        int lddln, __nv_bfloat16* __restrict__ dx16) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const size_t row = (size_t)blockIdx.x * LW_WARPS + (threadIdx.x >> 5);
   if (row >= (size_t)M) return;
@@ -271,11 +273,11 @@ int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamm
                    ((((uintptr_t)x | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta) & 15) == 0) && (((uintptr_t)y_bf16 & 7) == 0);
   const dim3 grid((M + LW_WARPS - 1) / LW_WARPS);
   if (vec && U <= 512)
-    ln_act_fwd_warp_vec_kernel<4><<<grid, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd,
-                                                                                    reinterpret_cast<__nv_bfloat16*>(y_bf16));
+    dv3_launch_pdl(ln_act_fwd_warp_vec_kernel<4>, grid, dim3(LW_WARPS * 32), 0, (cudaStream_t)stream, M, U, x, ldx, gamma, beta, eps, act, y, ldy,
+                   mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
   else if (vec)
-    ln_act_fwd_warp_vec_kernel<8><<<grid, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd,
-                                                                                    reinterpret_cast<__nv_bfloat16*>(y_bf16));
+    dv3_launch_pdl(ln_act_fwd_warp_vec_kernel<8>, grid, dim3(LW_WARPS * 32), 0, (cudaStream_t)stream, M, U, x, ldx, gamma, beta, eps, act, y, ldy,
+                   mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
   else
     ln_act_fwd_warp_kernel<<<grid, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(
         M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
@@ -287,8 +289,8 @@ int dv3_ln_act_bwd_rows(int M, int U, const float* dy, int lddy, const float* x,
                         void* stream) {
   if (M <= 0 || U <= 0) return DV3_ERR_ARG;
   if ((const void*)dx == (const void*)dy) return DV3_ERR_ARG;
-  ln_act_bwd_warp_kernel<<<(M + LW_WARPS - 1) / LW_WARPS, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(
-      M, U, dy, lddy, x, ldx, gamma, beta, mean, rstd, act, dx, lddx, dln, lddln, reinterpret_cast<__nv_bfloat16*>(dx_bf16));
+  dv3_launch_pdl(ln_act_bwd_warp_kernel, dim3((M + LW_WARPS - 1) / LW_WARPS), dim3(LW_WARPS * 32), 0, (cudaStream_t)stream, M, U, dy, lddy, x, ldx,
+                 gamma, beta, mean, rstd, act, dx, lddx, dln, lddln, reinterpret_cast<__nv_bfloat16*>(dx_bf16));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -23,7 +23,7 @@
 
 namespace {
 
-constexpr int TBM = 128, TBN = 128, TBK = 64, STAGES = 6;
+constexpr int TBM = 128, TBN = 128, TBK = 64, STAGES = 3;   // 3 x 32 KB per CTA: two CTAs per SM, one runs its epilogue while the other feeds the tensor core
 constexpr int NUM_THREADS = 192;
 constexpr int STAGE_A_BYTES = TBM * TBK * 2, STAGE_B_BYTES = TBN * TBK * 2;
 constexpr int TMEM_COLS = 128;
@@ -78,13 +78,14 @@ __device__ __forceinline__ uint64_t make_smem_desc_mn(uint32_t smem_addr) {   //
 }
 
 __global__ void zero2d_tma_kernel(int M, int N, float* __restrict__ C, int ldc) {
+  pdl_sync();
   const size_t n = (size_t)M * N;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     C[(i / N) * ldc + (i % N)] = 0.f;
 }
 
 template <bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(NUM_THREADS, 2)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                      float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int kb_per_split) {
   extern __shared__ uint8_t smem_raw[];
@@ -118,6 +119,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_sync();     // everything above (barriers, TMEM, descriptor prefetch) overlaps the tail of the previous kernel on the stream
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -295,10 +297,11 @@ int launch_tma(int M, int N, int K, const void* A, int lda, const void* B, int l
     size_t n = (size_t)M * N;
     int zb = (int)((n + 255) / 256);
     if (zb > 1184) zb = 1184;
-    zero2d_tma_kernel<<<zb, 256, 0, stream>>>(M, N, C, ldc);
+    dv3_launch_pdl(zero2d_tma_kernel, dim3(zb), dim3(256), 0, stream, M, N, C, ldc);
     DV3_LAUNCH_CHECK();
   }
-  gemm_bf16_tma_kernel<A_MN, B_MN><<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(tmA, tmB, M, N, K, C, ldc, bias, accumulate, kb_per_split);
+  dv3_launch_pdl(gemm_bf16_tma_kernel<A_MN, B_MN>, grid, dim3(NUM_THREADS), SMEM_BYTES, stream, tmA, tmB, M, N, K, C, ldc, bias, accumulate,
+                 kb_per_split);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }
@@ -330,6 +333,7 @@ extern "C" int dv3_gemm_bf16_tma(int mode, int M, int N, int K, const void* A, i
 // fused bf16 side output (weight arenas after Adam, scan products, strided copies).
 namespace {
 __global__ void __launch_bounds__(256) f32_to_bf16_vec_kernel(size_t n4, const float4* __restrict__ s, uint2* __restrict__ d) {
+  pdl_sync();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const float4 v = __ldg(s + i);
     __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
@@ -342,6 +346,7 @@ __global__ void __launch_bounds__(256) f32_to_bf16_vec_kernel(size_t n4, const f
 // one row per blockIdx.y step, columns vectorised by 4 when the row starts stay 16 B (source) / 8 B (destination) aligned
 __global__ void __launch_bounds__(256) f32_to_bf16_rows_kernel(int R, int Cc, const float* __restrict__ s, int lds,
                                                                __nv_bfloat16* __restrict__ d, int ldd, int vec) {
+  pdl_sync();
   for (int r = blockIdx.y; r < R; r += gridDim.y) {
     const float* sr = s + (size_t)r * lds;
     __nv_bfloat16* dr = d + (size_t)r * ldd;
@@ -368,14 +373,14 @@ extern "C" int dv3_f32_to_bf16(int R, int Cc, const float* src, int lds, void* d
     const size_t n4 = (size_t)R * Cc / 4;
     size_t g = (n4 + 255) / 256;
     if (g > 148 * 8) g = 148 * 8;
-    f32_to_bf16_vec_kernel<<<(int)g, 256, 0, (cudaStream_t)stream>>>(n4, reinterpret_cast<const float4*>(src),
-                                                                      reinterpret_cast<uint2*>(dst));
+    dv3_launch_pdl(f32_to_bf16_vec_kernel, dim3((int)g), dim3(256), 0, (cudaStream_t)stream, n4, reinterpret_cast<const float4*>(src),
+                   reinterpret_cast<uint2*>(dst));
   } else {
     const int vec = aligned && (Cc & 3) == 0 && (lds & 3) == 0 && (ldd & 3) == 0;
     const int per_row = vec ? Cc / 4 : Cc;
     dim3 grid((per_row + 255) / 256, R > 4096 ? 4096 : R);
     if (grid.x > 64) grid.x = 64;
-    f32_to_bf16_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(R, Cc, src, lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd, vec);
+    dv3_launch_pdl(f32_to_bf16_rows_kernel, grid, dim3(256), 0, (cudaStream_t)stream, R, Cc, src, lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd, vec);
   }
   DV3_LAUNCH_CHECK();
   return DV3_OK;

@@ -146,6 +146,7 @@ unimix_sample_kernel(int R, int groups, int K, float mix, const float* __restric
                      const int* __restrict__ forced, int ldf, int* __restrict__ idx, int ldi, float* __restrict__ onehot, int ldo,
                      __nv_bfloat16* __restrict__ onehot16, float* __restrict__ logits, int ldl, int fast) {
   __shared__ float sp[WARPS_PER_BLOCK][KR * 32];
+  pdl_sync();
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int gid = blockIdx.x * WARPS_PER_BLOCK + w;
   if (gid >= R * groups) return;
@@ -617,8 +618,9 @@ int dv3_unimix_sample(int R, int groups, int K, float mix, const float* raw, int
   if (R <= 0 || groups <= 0 || K <= 0) return DV3_ERR_ARG;
   if (K > KR * 32) return DV3_ERR_UNSUPPORTED;
   if (!forced && !u) return DV3_ERR_ARG;
-  DV3_DISPATCH_KR(K, unimix_sample_kernel<KRT><<<groups_grid((long long)R * groups), WARPS_PER_BLOCK * 32, 0, (cudaStream_t)stream>>>(
-      R, groups, K, mix, raw, ldr, u, ldu, forced, ldf, idx, ldi, onehot, ldo, reinterpret_cast<__nv_bfloat16*>(onehot_bf16), logits, ldl, fast));
+  DV3_DISPATCH_KR(K, dv3_launch_pdl(unimix_sample_kernel<KRT>, dim3(groups_grid((long long)R * groups)), dim3(WARPS_PER_BLOCK * 32), 0,
+                                    (cudaStream_t)stream, R, groups, K, mix, raw, ldr, u, ldu, forced, ldf, idx, ldi, onehot, ldo,
+                                    reinterpret_cast<__nv_bfloat16*>(onehot_bf16), logits, ldl, fast));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

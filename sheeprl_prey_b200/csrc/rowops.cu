@@ -86,6 +86,7 @@ col_reduce_stage1(int M, int U, const float* __restrict__ d, int ldd, const floa
                   const float* __restrict__ mean, const float* __restrict__ rstd, int rows_per_chunk,
                   float* __restrict__ partial) {
   __shared__ float sa[CR_ROWLANES][CR_COLS + 1], sb[CR_ROWLANES][CR_COLS + 1];
+  pdl_sync();
   const int c = threadIdx.x % CR_COLS, rl = threadIdx.x / CR_COLS;
   const int u = blockIdx.x * CR_COLS + c;
   const int r0 = blockIdx.y * rows_per_chunk, r1 = min(M, r0 + rows_per_chunk);
@@ -108,6 +109,7 @@ col_reduce_stage1(int M, int U, const float* __restrict__ d, int ldd, const floa
 }
 __global__ void col_reduce_stage2(int U, int nchunks, const float* __restrict__ partial, float* __restrict__ out_a,
                                   float* __restrict__ out_b) {
+  pdl_sync();
   const int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= U) return;
   float a = 0.f, b = 0.f;
@@ -153,6 +155,7 @@ __global__ void __launch_bounds__(256)
 gru_gate_fwd_warp_kernel(int R, int D, const float* __restrict__ gp, int ldg, const float* __restrict__ lnw,
                          const float* __restrict__ lnb, const float* __restrict__ h_in, int ldhi, float* __restrict__ h_out,
                          int ldho, float* __restrict__ mean, float* __restrict__ rstd, __nv_bfloat16* __restrict__ h16) {
+  pdl_sync();
   const int lane = threadIdx.x & 31;
   const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= (size_t)R) return;
@@ -241,6 +244,7 @@ __global__ void symlog_kernel(size_t n, const float* __restrict__ x, float* __re
     y[i] = symlogf_(x[i]);
 }
 __global__ void copy2d_kernel(int R, int C, const float* __restrict__ s, int lds, float* __restrict__ d, int ldd) {
+  pdl_sync();
   const size_t n = (size_t)R * C;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
     const int r = (int)(i / C), c = (int)(i % C);
@@ -340,10 +344,10 @@ int dv3_col_reduce(int M, int U, const float* d, int ldd, const float* x, int ld
   if (nchunks > 64) nchunks = 64;
   const int rows_per_chunk = (M + nchunks - 1) / nchunks;
   dim3 g1((U + CR_COLS - 1) / CR_COLS, nchunks);
-  col_reduce_stage1<<<g1, CR_COLS * CR_ROWLANES, 0, (cudaStream_t)stream>>>(M, U, d, ldd, x, ldx, mean, rstd,
+  dv3_launch_pdl(col_reduce_stage1, g1, dim3(CR_COLS * CR_ROWLANES), 0, (cudaStream_t)stream, M, U, d, ldd, x, ldx, mean, rstd,
                                                                           rows_per_chunk, scratch);
   DV3_LAUNCH_CHECK();
-  col_reduce_stage2<<<(U + 127) / 128, 128, 0, (cudaStream_t)stream>>>(U, nchunks, scratch, out_a, out_b);
+  dv3_launch_pdl(col_reduce_stage2, dim3((U + 127) / 128), dim3(128), 0, (cudaStream_t)stream, U, nchunks, (const float*)scratch, out_a, out_b);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }
@@ -387,9 +391,9 @@ int dv3_col_reduce_noalloc(int M, int U, const float* d, int ldd, const float* x
   if (nchunks > DV3_COL_REDUCE_MAX_CHUNKS) nchunks = DV3_COL_REDUCE_MAX_CHUNKS;
   const int rows_per_chunk = (M + nchunks - 1) / nchunks;
   dim3 g1((U + CR_COLS - 1) / CR_COLS, nchunks);
-  col_reduce_stage1<<<g1, CR_COLS * CR_ROWLANES, 0, (cudaStream_t)stream>>>(M, U, d, ldd, x, ldx, mean, rstd, rows_per_chunk, partials);
+  dv3_launch_pdl(col_reduce_stage1, g1, dim3(CR_COLS * CR_ROWLANES), 0, (cudaStream_t)stream, M, U, d, ldd, x, ldx, mean, rstd, rows_per_chunk, partials);
   DV3_LAUNCH_CHECK();
-  col_reduce_stage2<<<(U + 127) / 128, 128, 0, (cudaStream_t)stream>>>(U, nchunks, partials, out_a, out_b);
+  dv3_launch_pdl(col_reduce_stage2, dim3((U + 127) / 128), dim3(128), 0, (cudaStream_t)stream, U, nchunks, (const float*)partials, out_a, out_b);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }
@@ -399,8 +403,8 @@ int dv3_gru_gate_fwd(int R, int D, const float* gates_pre, int ldg, const float*
                      void* stream) {
   if (R <= 0 || D <= 0) return DV3_ERR_ARG;
   if (R >= 256 && D <= 512)
-    gru_gate_fwd_warp_kernel<16><<<(R + 7) / 8, 256, 0, (cudaStream_t)stream>>>(R, D, gates_pre, ldg, lnw, lnb, h_in, ldhi, h_out, ldho, mean, rstd,
-                                                                                reinterpret_cast<__nv_bfloat16*>(h_out_bf16));
+    dv3_launch_pdl(gru_gate_fwd_warp_kernel<16>, dim3((R + 7) / 8), dim3(256), 0, (cudaStream_t)stream, R, D, gates_pre, ldg, lnw, lnb, h_in, ldhi,
+                   h_out, ldho, mean, rstd, reinterpret_cast<__nv_bfloat16*>(h_out_bf16));
   else
     gru_gate_fwd_kernel<<<R, ROW_THREADS, 0, (cudaStream_t)stream>>>(D, gates_pre, ldg, lnw, lnb, h_in, ldhi, h_out, ldho,
                                                                     mean, rstd, reinterpret_cast<__nv_bfloat16*>(h_out_bf16));
@@ -426,7 +430,7 @@ int dv3_symlog(size_t n, const float* x, float* y, void* stream) {
 }
 int dv3_copy2d(int R, int C, const float* s, int lds, float* d, int ldd, void* stream) {
   if (R <= 0 || C <= 0) return DV3_ERR_ARG;
-  copy2d_kernel<<<grid_for((size_t)R * C, 256), 256, 0, (cudaStream_t)stream>>>(R, C, s, lds, d, ldd);
+  dv3_launch_pdl(copy2d_kernel, dim3(grid_for((size_t)R * C, 256)), dim3(256), 0, (cudaStream_t)stream, R, C, s, lds, d, ldd);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }
