@@ -95,6 +95,12 @@ int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamm
 int dv3_ln_act_bwd_rows(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
                         const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* dx_bf16,
                         void* stream);
+/* dv3_ln_act_bwd + the two column reductions that follow it in a dense layer's backward, in one pass: dx (+ bf16 mirror),
+ * dgamma[u] = sum_m g xhat, dbeta[u] = sum_m g, dbias[u] = sum_m dx (NULL = not wanted).  U % 4 == 0, U <= 1024, 16 B aligned
+ * rows, else DV3_ERR_UNSUPPORTED; scratch >= 296 * 3 * U floats. */
+int dv3_ln_act_bwd_fused(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
+                         const float* mean, const float* rstd, int act, float* dx, int lddx, void* dx_bf16, float* dgamma, float* dbeta,
+                         float* dbias, float* scratch, size_t scratch_bytes, void* stream);
 /* MSEDistribution.log_prob, utils/distribution.py:212-221: loss[m] = sum_d (mode-x)^2, dmode = scale*2*(mode-x) */
 int dv3_mse_rows(int M, int D, const float* mode, const float* target, float scale, float* loss_rows, float* dmode, void* stream);
 

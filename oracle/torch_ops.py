@@ -93,6 +93,13 @@ class TorchOps:
         gg = g * gamma
         dx.copy_(rstd[:, None] * (gg - gg.mean(-1, keepdim=True) - xhat * (gg * xhat).mean(-1, keepdim=True)))
 
+    def ln_act_bwd_fused(self, dy, x, gamma, beta, mean, rstd, act, dx, dln, dgamma, dbeta, dbias) -> None:
+        """ln_act_bwd, ln_param_grad and (dbias given) colsum(dx) of a dense layer's backward."""
+        self.ln_act_bwd(dy, x, gamma, beta, mean, rstd, act, dx, dln)
+        self.ln_param_grad(dln, x, mean, rstd, dgamma, dbeta)
+        if dbias is not None:
+            self.colsum(dx, dbias)
+
     def ln_param_grad(self, dln: Tensor, x: Tensor, mean: Tensor, rstd: Tensor, dgamma: Tensor, dbeta: Tensor) -> None:
         """dgamma[u] = sum_m dln[m,u] * xhat[m,u];  dbeta[u] = sum_m dln[m,u]  (overwrite)."""
         xhat = (x - mean[:, None]) * rstd[:, None]

@@ -48,6 +48,7 @@ SIGNATURES = {
     "dv3_rssm_observe_fwd_cluster": [c_fp, c_fp, c_fp],
     "dv3_rssm_observe_bwd_cluster": [c_fp, c_fp],
     "dv3_pack_mma_a": [_i, _i, c_fp, _ll, _ll, c_fp, c_fp],
+    "dv3_ln_act_bwd_fused": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
     "dv3_unimix_sample": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, _i, _i, c_fp],
     "dv3_unimix_bwd_prep": [_i, _i, _i, _f, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_unimix_fwd": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp],
@@ -323,6 +324,25 @@ class CudaOps:
         fn = self.lib.dv3_ln_act_bwd_rows if (U <= 1024 and M >= 256) else self.lib.dv3_ln_act_bwd
         _chk(fn(M, U, pdy, lddy, px, ldx, _p(gamma), _p(beta), _p(mean), _p(rstd), act, pdx, lddx, pdl, lddl, self._m16(pdx), self._s()),
              "dv3_ln_act_bwd")
+
+    def ln_act_bwd_fused(self, dy, x, gamma, beta, mean, rstd, act, dx, dln, dgamma, dbeta, dbias):
+        """ln_act_bwd + ln_param_grad + colsum(dx) of a dense layer's backward; one pass when the shape allows (dln then stays
+        unwritten), else the three separate kernels."""
+        pdy, M, U, lddy = _mat(dy)
+        px, _, _, ldx = _mat(x)
+        pdx, _, _, lddx = _mat(dx)
+        if M >= 256:
+            rc = self.lib.dv3_ln_act_bwd_fused(M, U, pdy, lddy, px, ldx, _p(gamma), _p(beta), _p(mean), _p(rstd), act, pdx, lddx, self._m16(pdx),
+                                               _p(dgamma), _p(dbeta), _p(dbias), self.scratch.data_ptr(), self.scratch.numel() * 4, self._s())
+            if rc == 0:
+                self.launches += 2
+                return
+            if rc != -2:
+                _chk(rc, "dv3_ln_act_bwd_fused")
+        self.ln_act_bwd(dy, x, gamma, beta, mean, rstd, act, dx, dln)
+        self.ln_param_grad(dln, x, mean, rstd, dgamma, dbeta)
+        if dbias is not None:
+            self.colsum(dx, dbias)
 
     def ln_param_grad(self, dln, x, mean, rstd, dgamma, dbeta):
         pd, M, U, ldd = _mat(dln)

@@ -213,6 +213,108 @@ ln_act_bwd_warp_kernel(int M, int U, const float* __restrict__ dy, int lddy, con
   }
 }
 
+// LayerNorm(+SiLU) backward with the parameter gradients fused in: one pass over dy / x produces dx (+ its bf16 mirror) AND the
+// column sums dgamma[u] = sum_m g xhat, dbeta[u] = sum_m g, dbias[u] = sum_m dx (the bias gradient of the Linear in front of the
+// LayerNorm), instead of writing g to memory and re-reading it together with x in two more kernels.  Warp per row, rows in
+// registers (U % 4 == 0, U <= 128 * NV), grid-stride over rows with per-lane column accumulators; per-block partials go to
+// scratch[block][3][U] and are summed in block order by the second kernel (deterministic).
+template <int NV>
+__global__ void __launch_bounds__(LW_WARPS * 32)
+ln_act_bwd_colsum_kernel(int M, int U, const float* __restrict__ dy, int lddy, const float* __restrict__ x, int ldx,
+                         const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
+                         const float* __restrict__ rstd, int act, float* __restrict__ dx, int lddx, __nv_bfloat16* __restrict__ dx16,
+                         float* __restrict__ partial) {
+  extern __shared__ float red[];                     // [LW_WARPS][U]
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n4 = U >> 2;
+  float4 ag[NV], ab[NV], ax[NV], gm[NV], bt[NV];
+#pragma unroll
+  for (int j = 0; j < NV; ++j) {
+    const int i = lane + 32 * j;
+    ag[j] = ab[j] = ax[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    gm[j] = (i < n4) ? __ldg(reinterpret_cast<const float4*>(gamma) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    bt[j] = (i < n4) ? __ldg(reinterpret_cast<const float4*>(beta) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (size_t row = (size_t)blockIdx.x * LW_WARPS + warp; row < (size_t)M; row += (size_t)gridDim.x * LW_WARPS) {
+    const float4* xr = reinterpret_cast<const float4*>(x + row * ldx);
+    const float4* dr = reinterpret_cast<const float4*>(dy + row * lddy);
+    const float mu = mean[row], rs = rstd[row];
+    float4 xh[NV], gg[NV];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = lane + 32 * j;
+      if (i < n4) {
+        const float4 xv = xr[i], dv = dr[i];
+        float4 h, g;
+        h.x = (xv.x - mu) * rs; h.y = (xv.y - mu) * rs; h.z = (xv.z - mu) * rs; h.w = (xv.w - mu) * rs;
+        g = dv;
+        if (act) {
+          float ln, sg;
+          ln = h.x * gm[j].x + bt[j].x; sg = sigmoidf_(ln); g.x *= sg * (1.f + ln * (1.f - sg));
+          ln = h.y * gm[j].y + bt[j].y; sg = sigmoidf_(ln); g.y *= sg * (1.f + ln * (1.f - sg));
+          ln = h.z * gm[j].z + bt[j].z; sg = sigmoidf_(ln); g.z *= sg * (1.f + ln * (1.f - sg));
+          ln = h.w * gm[j].w + bt[j].w; sg = sigmoidf_(ln); g.w *= sg * (1.f + ln * (1.f - sg));
+        }
+        ab[j].x += g.x; ab[j].y += g.y; ab[j].z += g.z; ab[j].w += g.w;
+        ag[j].x = fmaf(g.x, h.x, ag[j].x); ag[j].y = fmaf(g.y, h.y, ag[j].y); ag[j].z = fmaf(g.z, h.z, ag[j].z); ag[j].w = fmaf(g.w, h.w, ag[j].w);
+        g.x *= gm[j].x; g.y *= gm[j].y; g.z *= gm[j].z; g.w *= gm[j].w;
+        s1 += (g.x + g.y) + (g.z + g.w);
+        s2 = fmaf(g.x, h.x, s2); s2 = fmaf(g.y, h.y, s2); s2 = fmaf(g.z, h.z, s2); s2 = fmaf(g.w, h.w, s2);
+        xh[j] = h;
+        gg[j] = g;
+      }
+    }
+    s1 = warp_sum(s1) / (float)U;
+    s2 = warp_sum(s2) / (float)U;
+    float4* oxr = reinterpret_cast<float4*>(dx + row * lddx);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = lane + 32 * j;
+      if (i < n4) {
+        float4 o;
+        o.x = rs * (gg[j].x - s1 - xh[j].x * s2); o.y = rs * (gg[j].y - s1 - xh[j].y * s2);
+        o.z = rs * (gg[j].z - s1 - xh[j].z * s2); o.w = rs * (gg[j].w - s1 - xh[j].w * s2);
+        oxr[i] = o;
+        ax[j].x += o.x; ax[j].y += o.y; ax[j].z += o.z; ax[j].w += o.w;
+        if (dx16) {
+          __nv_bfloat162 lo = __floats2bfloat162_rn(o.x, o.y), hi = __floats2bfloat162_rn(o.z, o.w);
+          uint2 pk;
+          pk.x = *reinterpret_cast<uint32_t*>(&lo);
+          pk.y = *reinterpret_cast<uint32_t*>(&hi);
+          *reinterpret_cast<uint2*>(dx16 + row * lddx + 4 * i) = pk;
+        }
+      }
+    }
+  }
+  // block partials: warps -> shared -> one [3][U] record per block
+#pragma unroll 1
+  for (int k = 0; k < 3; ++k) {
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = lane + 32 * j;
+      if (i < n4) reinterpret_cast<float4*>(red + warp * U)[i] = (k == 0) ? ag[j] : ((k == 1) ? ab[j] : ax[j]);
+    }
+    __syncthreads();
+    for (int u = threadIdx.x; u < U; u += LW_WARPS * 32) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < LW_WARPS; ++w) s += red[w * U + u];
+      partial[((size_t)blockIdx.x * 3 + k) * U + u] = s;
+    }
+  }
+}
+__global__ void __launch_bounds__(128) colsum3_stage2_kernel(int U, int nblocks, const float* __restrict__ partial, float* __restrict__ o0,
+                                                             float* __restrict__ o1, float* __restrict__ o2) {
+  const int u = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+  float* o = (k == 0) ? o0 : ((k == 1) ? o1 : o2);
+  if (u >= U || !o) return;
+  float s = 0.f;
+  for (int b = 0; b < nblocks; ++b) s += partial[((size_t)b * 3 + k) * U + u];
+  o[u] = s;
+}
+
 // MSEDistribution.log_prob (sheeprl/utils/distribution.py:212-221): loss[m] = sum_d (mode - x)^2, dmode = scale*2*(mode-x)
 __global__ void __launch_bounds__(256) mse_rows_kernel(int M, int Dd, const float* __restrict__ mode, const float* __restrict__ target,
                                                       float scale, float* __restrict__ loss_rows, float* __restrict__ dmode) {
@@ -291,6 +393,29 @@ int dv3_ln_act_bwd_rows(int M, int U, const float* dy, int lddy, const float* x,
   if ((const void*)dx == (const void*)dy) return DV3_ERR_ARG;
   dv3_launch_pdl(ln_act_bwd_warp_kernel, dim3((M + LW_WARPS - 1) / LW_WARPS), dim3(LW_WARPS * 32), 0, (cudaStream_t)stream, M, U, dy, lddy, x, ldx,
                  gamma, beta, mean, rstd, act, dx, lddx, dln, lddln, reinterpret_cast<__nv_bfloat16*>(dx_bf16));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_ln_act_bwd_fused(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
+                         const float* mean, const float* rstd, int act, float* dx, int lddx, void* dx_bf16, float* dgamma, float* dbeta,
+                         float* dbias, float* scratch, size_t scratch_bytes, void* stream) {
+  if (M <= 0 || U <= 0 || !scratch) return DV3_ERR_ARG;
+  if ((const void*)dx == (const void*)dy) return DV3_ERR_ARG;
+  if ((U & 3) || U > 1024 || (ldx & 3) || (lddy & 3) || (lddx & 3) ||
+      ((((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx | (uintptr_t)gamma | (uintptr_t)beta) & 15) != 0) || (((uintptr_t)dx_bf16 & 7) != 0))
+    return DV3_ERR_UNSUPPORTED;
+  int nblocks = (M + LW_WARPS - 1) / LW_WARPS;
+  if (nblocks > 296) nblocks = 296;
+  if (scratch_bytes < (size_t)nblocks * 3 * U * sizeof(float)) return DV3_ERR_SCRATCH;
+  const size_t smem = (size_t)LW_WARPS * U * sizeof(float);
+  if (U <= 512)
+    ln_act_bwd_colsum_kernel<4><<<nblocks, LW_WARPS * 32, smem, (cudaStream_t)stream>>>(M, U, dy, lddy, x, ldx, gamma, beta, mean, rstd, act, dx, lddx,
+                                                                                      reinterpret_cast<__nv_bfloat16*>(dx_bf16), scratch);
+  else
+    ln_act_bwd_colsum_kernel<8><<<nblocks, LW_WARPS * 32, smem, (cudaStream_t)stream>>>(M, U, dy, lddy, x, ldx, gamma, beta, mean, rstd, act, dx, lddx,
+                                                                                      reinterpret_cast<__nv_bfloat16*>(dx_bf16), scratch);
+  DV3_LAUNCH_CHECK();
+  colsum3_stage2_kernel<<<dim3((U + 127) / 128, 3), 128, 0, (cudaStream_t)stream>>>(U, nblocks, scratch, dgamma, dbeta, dbias);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -159,10 +159,8 @@ class DenseStack:
             U = L["w"].shape[0]
             dpre = self._dpre[: rows * U].view(rows, U)
             dln = self._dln[: rows * U].view(rows, U)
-            ops.ln_act_bwd(dact, self.pre[i][:rows], L["g"], L["beta"], self.mean[i][:rows], self.rstd[i][:rows], 1, dpre, dln)
-            ops.ln_param_grad(dln, self.pre[i][:rows], self.mean[i][:rows], self.rstd[i][:rows], L["dg"], L["dbeta"])
-            if L.get("b") is not None:
-                ops.colsum(dpre, L["db"])
+            ops.ln_act_bwd_fused(dact, self.pre[i][:rows], L["g"], L["beta"], self.mean[i][:rows], self.rstd[i][:rows], 1, dpre, dln,
+                                 L["dg"], L["dbeta"], L["db"] if L.get("b") is not None else None)
             inp = self.act[i - 1][:rows] if i > 0 else x[:rows]
             ops.gemm("TN", dpre, inp, L["dw"])
             if i > 0:

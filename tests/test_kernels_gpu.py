@@ -525,3 +525,21 @@ def test_unimix_sample_fused(cuda_ops, cuda_ops_bf16, R, groups, K):
     cuda_ops_bf16.unimix_sample(raw, groups, K, 0.01, u, None, idx3, oh3)
     assert float((idx3 != idx0).float().mean()) < 1e-3
     assert torch.equal(oh3.reshape(R, groups, K).argmax(-1).int(), idx3) and float(oh3.sum()) == R * groups
+
+
+@pytest.mark.parametrize("M,U,act,bias", [(1024, 512, 1, True), (16384, 512, 1, False), (300, 640, 1, True), (257, 1024, 0, True), (256, 24, 1, True),
+                                          (16, 512, 1, True), (1024, 510, 1, True)])
+def test_ln_act_bwd_fused(cuda_ops, torch_ops, M, U, act, bias):
+    """LayerNorm(+SiLU) backward with fused column sums == the three separate ops (fallback shapes included)."""
+    x, g, b = rnd(M, U, scale=2.0) + 0.3, rnd(U) * 0.2 + 1, rnd(U) * 0.1
+    mean, rstd = x.mean(-1), (x.var(-1, unbiased=False) + 1e-3).rsqrt()
+    dy = rnd(M, U, seed=3)
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        dx, dln = torch.zeros(M, U + 8, device=DEV)[:, :U], torch.zeros(M, U, device=DEV)
+        dg, db, dbias = torch.zeros(U, device=DEV), torch.zeros(U, device=DEV), torch.zeros(U, device=DEV)
+        ops.ln_act_bwd_fused(dy, x, g, b, mean, rstd, act, dx, dln, dg, db, dbias if bias else None)
+        res.append((dx, dg, db, dbias))
+    torch.cuda.synchronize()
+    for i, (a, r) in enumerate(zip(res[1], res[0])):
+        assert rel(a.double(), r.double()) < 3e-5, (i, rel(a.double(), r.double()))
