@@ -92,6 +92,12 @@ int dv3_u8_nchw_to_nhwc(int N, int C, int HW, const unsigned char* src, float sc
 /* warp-per-row variants of dv3_ln_act_fwd / _bwd for narrow rows (channel LayerNorm over N*H*W pixel rows) */
 int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,
                         float* y, int ldy, float* mean, float* rstd, void* y_bf16, void* stream);
+/* dv3_ln_act_fwd_rows on x + sum_h add_table[head_off[h] + add_idx[m, h], :]: the one-hot (discrete action) input block of the Linear
+ * in front of the LayerNorm as a row gather of its transposed weights instead of a K = A contraction (rollout, agent.py:296-309).
+ * n_heads <= 4, head_off is a HOST array; DV3_ERR_UNSUPPORTED for shapes outside the vector kernel (U % 4, U > 1024, alignment). */
+int dv3_ln_act_fwd_rows_gather(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act, float* y, int ldy,
+                               float* mean, float* rstd, void* y_bf16, const float* add_table, int ld_table, const int* add_idx, int ld_idx,
+                               int n_heads, const int* head_off_host, void* stream);
 int dv3_ln_act_bwd_rows(int M, int U, const float* dy, int lddy, const float* x, int ldx, const float* gamma, const float* beta,
                         const float* mean, const float* rstd, int act, float* dx, int lddx, float* dln, int lddln, void* dx_bf16,
                         void* stream);

@@ -93,6 +93,14 @@ class TorchOps:
         gg = g * gamma
         dx.copy_(rstd[:, None] * (gg - gg.mean(-1, keepdim=True) - xhat * (gg * xhat).mean(-1, keepdim=True)))
 
+    def ln_act_fwd_gather(self, x, gamma, beta, eps, act, y, mean, rstd, table, idx, head_offsets) -> bool:
+        """ln_act_fwd on x + sum_h table[head_offsets[h] + idx[:, h]]."""
+        xx = x.clone()
+        for h, off in enumerate(head_offsets):
+            xx += table[idx[:, h].long() + int(off)]
+        self.ln_act_fwd(xx, gamma, beta, eps, act, y, mean, rstd)
+        return True
+
     def ln_act_bwd_fused(self, dy, x, gamma, beta, mean, rstd, act, dx, dln, dgamma, dbeta, dbias) -> None:
         """ln_act_bwd, ln_param_grad and (dbias given) colsum(dx) of a dense layer's backward."""
         self.ln_act_bwd(dy, x, gamma, beta, mean, rstd, act, dx, dln)

@@ -48,6 +48,7 @@ SIGNATURES = {
     "dv3_rssm_observe_fwd_cluster": [c_fp, c_fp, c_fp],
     "dv3_rssm_observe_bwd_cluster": [c_fp, c_fp],
     "dv3_pack_mma_a": [_i, _i, c_fp, _ll, _ll, c_fp, c_fp],
+    "dv3_ln_act_fwd_rows_gather": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, _i, c_fp, c_fp],
     "dv3_ln_act_bwd_fused": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
     "dv3_unimix_sample": [_i, _i, _i, _f, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, _i, _i, c_fp],
     "dv3_unimix_bwd_prep": [_i, _i, _i, _f, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
@@ -314,6 +315,23 @@ class CudaOps:
         self.launches += 1
         fn = self.lib.dv3_ln_act_fwd_rows if (U <= 1024 and M >= 256) else self.lib.dv3_ln_act_fwd
         _chk(fn(M, U, px, ldx, _p(gamma), _p(beta), eps, act, py, ldy, _p(mean), _p(rstd), self._m16(py), self._s()), "dv3_ln_act_fwd")
+
+    def ln_act_fwd_gather(self, x, gamma, beta, eps, act, y, mean, rstd, table, idx, head_offsets) -> bool:
+        """ln_act_fwd on x + sum_h table[head_offsets[h] + idx[:, h]] (one-hot input block as a row gather).  False = shape outside
+        the kernel's plan (caller uses the dense contraction)."""
+        px, M, U, ldx = _mat(x)
+        py, _, _, ldy = _mat(y)
+        pt, _, _, ldt = _mat(table)
+        pi, _, nh, ldi = _mat(idx)
+        assert idx.dtype == torch.int32 and len(head_offsets) == nh
+        ho = (C.c_int * max(nh, 1))(*[int(v) for v in head_offsets])
+        rc = self.lib.dv3_ln_act_fwd_rows_gather(M, U, px, ldx, _p(gamma), _p(beta), eps, act, py, ldy, _p(mean), _p(rstd), self._m16(py), pt, ldt,
+                                                 pi, ldi, nh, C.cast(ho, C.c_void_p), self._s())
+        if rc == -2:
+            return False
+        _chk(rc, "dv3_ln_act_fwd_rows_gather")
+        self.launches += 1
+        return True
 
     def ln_act_bwd(self, dy, x, gamma, beta, mean, rstd, act, dx, dln):
         pdy, M, U, lddy = _mat(dy)

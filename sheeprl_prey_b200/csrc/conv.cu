@@ -123,7 +123,9 @@ template <int NV>
 __global__ void __launch_bounds__(LW_WARPS * 32)
 ln_act_fwd_warp_vec_kernel(int M, int U, const float* __restrict__ x, int ldx, const float* __restrict__ gamma,
                            const float* __restrict__ beta, float eps, int act, float* __restrict__ y, int ldy,
-                           float* __restrict__ mean, float* __restrict__ rstd, __nv_bfloat16* __restrict__ y16) {
+                           float* __restrict__ mean, float* __restrict__ rstd, __nv_bfloat16* __restrict__ y16,
+                           const float* __restrict__ add_table, int ld_table, const int* __restrict__ add_idx, int ld_idx, int n_heads,
+                           int4 head_off) {
   pdl_sync();
   const int lane = threadIdx.x & 31;
   const size_t row = (size_t)blockIdx.x * LW_WARPS + (threadIdx.x >> 5);
@@ -131,13 +133,24 @@ ln_act_fwd_warp_vec_kernel(int M, int U, const float* __restrict__ x, int ldx, c
   const float4* xr = reinterpret_cast<const float4*>(x + row * ldx);
   const int n4 = U >> 2;
   float4 v[NV];
-  float s = 0.f;
 #pragma unroll
   for (int j = 0; j < NV; ++j) {
     const int i = lane + 32 * j;
     v[j] = (i < n4) ? xr[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-    s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
   }
+  // optional: x += sum_h table[head_off[h] + idx[row, h], :]  (a one-hot input block of the Linear in front, as a row gather)
+  for (int h = 0; h < n_heads; ++h) {
+    const int off = (h == 0) ? head_off.x : ((h == 1) ? head_off.y : ((h == 2) ? head_off.z : head_off.w));
+    const float4* tr = reinterpret_cast<const float4*>(add_table + (size_t)(off + add_idx[row * ld_idx + h]) * ld_table);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = lane + 32 * j;
+      if (i < n4) { const float4 t = __ldg(tr + i); v[j].x += t.x; v[j].y += t.y; v[j].z += t.z; v[j].w += t.w; }
+    }
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int j = 0; j < NV; ++j) s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
   const float mu = warp_sum(s) / (float)U;
   float q = 0.f;
 #pragma unroll
@@ -376,13 +389,32 @@ int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamm
   const dim3 grid((M + LW_WARPS - 1) / LW_WARPS);
   if (vec && U <= 512)
     dv3_launch_pdl(ln_act_fwd_warp_vec_kernel<4>, grid, dim3(LW_WARPS * 32), 0, (cudaStream_t)stream, M, U, x, ldx, gamma, beta, eps, act, y, ldy,
-                   mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
+                   mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16), (const float*)nullptr, 0, (const int*)nullptr, 0, 0, make_int4(0, 0, 0, 0));
   else if (vec)
     dv3_launch_pdl(ln_act_fwd_warp_vec_kernel<8>, grid, dim3(LW_WARPS * 32), 0, (cudaStream_t)stream, M, U, x, ldx, gamma, beta, eps, act, y, ldy,
-                   mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
+                   mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16), (const float*)nullptr, 0, (const int*)nullptr, 0, 0, make_int4(0, 0, 0, 0));
   else
     ln_act_fwd_warp_kernel<<<grid, LW_WARPS * 32, 0, (cudaStream_t)stream>>>(
         M, U, x, ldx, gamma, beta, eps, act, y, ldy, mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16));
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+int dv3_ln_act_fwd_rows_gather(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act, float* y, int ldy,
+                               float* mean, float* rstd, void* y_bf16, const float* add_table, int ld_table, const int* add_idx, int ld_idx,
+                               int n_heads, const int* head_off_host, void* stream) {
+  if (M <= 0 || U <= 0 || !add_table || !add_idx || n_heads < 1 || !head_off_host) return DV3_ERR_ARG;
+  const bool vec = (U & 3) == 0 && U <= 1024 && (ldx & 3) == 0 && (ldy & 3) == 0 && (ld_table & 3) == 0 && n_heads <= 4 &&
+                   ((((uintptr_t)x | (uintptr_t)y | (uintptr_t)gamma | (uintptr_t)beta | (uintptr_t)add_table) & 15) == 0) &&
+                   (((uintptr_t)y_bf16 & 7) == 0);
+  if (!vec) return DV3_ERR_UNSUPPORTED;
+  int4 ho = make_int4(head_off_host[0], n_heads > 1 ? head_off_host[1] : 0, n_heads > 2 ? head_off_host[2] : 0, n_heads > 3 ? head_off_host[3] : 0);
+  const dim3 grid((M + LW_WARPS - 1) / LW_WARPS);
+  if (U <= 512)
+    dv3_launch_pdl(ln_act_fwd_warp_vec_kernel<4>, grid, dim3(LW_WARPS * 32), 0, (cudaStream_t)stream, M, U, x, ldx, gamma, beta, eps, act, y, ldy,
+                   mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16), add_table, ld_table, add_idx, ld_idx, n_heads, ho);
+  else
+    dv3_launch_pdl(ln_act_fwd_warp_vec_kernel<8>, grid, dim3(LW_WARPS * 32), 0, (cudaStream_t)stream, M, U, x, ldx, gamma, beta, eps, act, y, ldy,
+                   mean, rstd, reinterpret_cast<__nv_bfloat16*>(y_bf16), add_table, ld_table, add_idx, ld_idx, n_heads, ho);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

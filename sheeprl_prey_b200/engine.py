@@ -259,6 +259,8 @@ class DV3Engine:
         self.ub_ps, self.ub_coef, self.ub_pn = z(N, S), z(N, S), z(N, S)   # unimix Jacobian factors (cluster reverse scan)
         self.use_fused_bwd = os.environ.get("DV3_FUSED_BWD_SCAN", "1") != "0"
         self.aW = z(N, U)                        # a_t . Wmlp[:, S:]^T for all t (hoisted out of the scan; cluster kernel)
+        self.W_mlpaT = z(A, _round_up(U, 4))[:, :U]   # Wmlp[:, S:]^T: discrete actions enter the rollout's first layer as a row gather
+        self.act_head_off = [int(sum(self.actions_dim[:j])) for j in range(len(self.actions_dim))]
         self.Wmlp_z = z(U, S)                    # compact copy of Wmlp[:, :S] for the rollout (row stride S+A is not TMA-loadable)
         _mirror(ops, self.x_rep, self.x_gru, self.x_mlp._base, self.latent, self.hidr, self.Wmlp_z, self.dpost_raw, self.dhidr_pre,
                 self.dgates_pre, self.dfeat_pre, self.dprior_logits, self.d_rec._base, self.d_rew._base)
@@ -542,6 +544,8 @@ class DV3Engine:
         G, K, mix = self.G, self.K, self.cfg.algo.unimix
         _refresh(ops, self.wm.flat, self.actor.flat)               # the world model was just updated (dreamer_v3.py:187)
         ops.copy2d(self.Wmlp[:, :S], self.Wmlp_z)
+        ops.transpose(self.Wmlp[:, S:], self.W_mlpaT)
+        gather_ok = hasattr(ops, "ln_act_fwd_gather") and len(self.actions_dim) <= 4
         ops.copy2d(self.latent, self.traj[:N])
 
         def policy(i, u, fidx):
@@ -558,8 +562,12 @@ class DV3Engine:
         for i in range(1, H + 1):
             r, rp = slice(i * N, (i + 1) * N), slice((i - 1) * N, i * N)
             ops.gemm("NT", self.traj[rp, :S], self.Wmlp_z, self.img_feat_pre)
-            ops.gemm("NT", self.acts[rp], self.Wmlp[:, S:], self.img_feat_pre, accumulate=True)
-            ops.ln_act_fwd(self.img_feat_pre, self.g_mlp, self.b_mlp, 1e-3, 1, self.img_feat, self.img_mean, self.img_rstd)
+            if gather_ok:      # one-hot actions: a . Wmlp[:, S:]^T = rows of the transposed weight, added inside the LayerNorm kernel
+                gather_ok = ops.ln_act_fwd_gather(self.img_feat_pre, self.g_mlp, self.b_mlp, 1e-3, 1, self.img_feat, self.img_mean,
+                                                  self.img_rstd, self.W_mlpaT, self.act_idx[rp], self.act_head_off)
+            if not gather_ok:
+                ops.gemm("NT", self.acts[rp], self.Wmlp[:, S:], self.img_feat_pre, accumulate=True)
+                ops.ln_act_fwd(self.img_feat_pre, self.g_mlp, self.b_mlp, 1e-3, 1, self.img_feat, self.img_mean, self.img_rstd)
             ops.gemm("NT", self.traj[rp, S:], self.Wgru[:, :D], self.img_gates)
             ops.gemm("NT", self.img_feat, self.Wgru[:, D:], self.img_gates, accumulate=True)
             ops.gru_gate_fwd(self.img_gates, self.g_gru, self.b_gru, self.traj[rp, S:], self.traj[r, S:], self.img_mean, self.img_rstd)

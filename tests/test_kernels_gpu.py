@@ -543,3 +543,21 @@ def test_ln_act_bwd_fused(cuda_ops, torch_ops, M, U, act, bias):
     torch.cuda.synchronize()
     for i, (a, r) in enumerate(zip(res[1], res[0])):
         assert rel(a.double(), r.double()) < 3e-5, (i, rel(a.double(), r.double()))
+
+
+@pytest.mark.parametrize("M,U,heads", [(1024, 512, [100]), (300, 640, [7, 3]), (256, 1024, [2, 2, 2, 2]), (257, 24, [18])])
+def test_ln_act_fwd_gather(cuda_ops, torch_ops, M, U, heads):
+    """LayerNorm(+SiLU) forward with the one-hot input block added as a row gather == the plain statement."""
+    A = sum(heads)
+    x, g, b = rnd(M, U, scale=2.0) + 0.3, rnd(U) * 0.2 + 1, rnd(U) * 0.1
+    table = torch.zeros(A, (U + 3) // 4 * 4, device=DEV)[:, :U]
+    table.copy_(rnd(A, U, seed=21))
+    idx = torch.stack([torch.randint(0, k, (M,), device=DEV) for k in heads], 1).int()
+    offs = [sum(heads[:j]) for j in range(len(heads))]
+    outs = []
+    for ops in (torch_ops, cuda_ops):
+        y, mean, rstd = torch.zeros(M, U, device=DEV), torch.zeros(M, device=DEV), torch.zeros(M, device=DEV)
+        assert ops.ln_act_fwd_gather(x, g, b, 1e-3, 1, y, mean, rstd, table, idx, offs)
+        outs.append((y, mean, rstd))
+    for a, r in zip(outs[1], outs[0]):
+        assert rel(a, r) < TOL
