@@ -316,8 +316,16 @@ def run_ours(args, rank, world, local_rank):
         tot_ms, tot_fl = sum(x[0] for x in big), sum(x[1] for x in big)
         all_ms = sum(s.elapsed_time(e) for (s, e, *_r) in log)
         ach = tot_fl / (tot_ms * 1e-3) / 1e12 if tot_ms > 0 else 0.0
+        traffic, traffic_of = None, None
+        try:   # dram__bytes_read + dram__bytes_write of one `ncu --set full` launch of the dominant kernel (largest shape of the step)
+            with open(os.path.join(ROOT, "profiles", "r01_gemm_tma_ncu.json")) as fh:
+                nc = json.load(fh)
+            if args.precision == "bf16" and args.size == "S":
+                traffic, traffic_of = nc["dram_bytes_read"] + nc["dram_bytes_write"], nc["shape"] + "; algorithmic bytes %d" % nc["algorithmic_bytes"]
+        except (OSError, KeyError, ValueError):
+            pass
         roof = {"bound": "tensor", "kernel": eng.ops.gemm_kernel_name, "achieved": ach, "peak": pk["tc_sustained"], "unit": "TFLOP/s",
-                "frac": ach / pk["tc_sustained"], "traffic": None, "launches_per_step": len(big) // 2,
+                "frac": ach / pk["tc_sustained"], "traffic": traffic, "traffic_of": traffic_of, "launches_per_step": len(big) // 2,
                 "avg_launch_ms": tot_ms / max(1, len(big)), "kernel_ms_per_step": tot_ms / 2, "all_gemm_ms_per_step": all_ms / 2,
                 "peak_source": pk["src"] + " bf16_tflops_sustained (of measured)",
                 "whole_step_tc_frac": GFLOP_PER_STEP[args.size] * (value / world) / 1e3 / pk["tc_sustained"]}
