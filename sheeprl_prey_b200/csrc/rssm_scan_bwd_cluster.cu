@@ -14,6 +14,7 @@
 //   B4  [dh_{t-1} part | d feat] = d gates_pre . Wgru (own columns);  LayerNorm+SiLU backward                    -> d feat_pre
 //   B5  dz_{t-1} = d feat_pre . Wmlp[:, :S] (own categoricals);  carry = (1 - first_t) * (dz_{t-1}, dh_{t-1} part + dh_t (1 - u))
 // Seven hardware cluster barriers per step; saved-activation inputs of step t-1 are fetched with cp.async while step t runs.
+#define DV3_SCAN_CT 256   // threads per CTA (8 warps: 1.84 ms; 16 warps spill at the 128-register cap (2.02 ms))
 #include "scan_cluster.cuh"
 #include "dv3_b200.h"
 #include <stdio.h>

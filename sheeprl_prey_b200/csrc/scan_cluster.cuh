@@ -15,15 +15,20 @@ namespace cg = cooperative_groups;
 namespace sc {
 
 constexpr int MB = 16;          // batch rows (B <= 16) = the two n8 tiles of the MMA
-constexpr int CT = 256;         // threads per CTA
+#ifndef DV3_SCAN_CT
+#define DV3_SCAN_CT 512
+#endif
+constexpr int CT = DV3_SCAN_CT; // threads per CTA
 constexpr int CW = CT / 32;     // warps per CTA
 constexpr int OB = MB + 1;      // row stride of the own-output buffers (odd: conflict-free by row and by column)
 constexpr int MAXT = 12;        // at most 12 row tiles (192 rows) per contraction and CTA
 
-__host__ __device__ inline int part_kb(int ntiles) {      // partial-sum slots (1 KB each) of a contraction with `ntiles` tiles
-  const int g = (ntiles & 1) ? 1 : ((ntiles & 2) ? 2 : ((ntiles & 4) ? 4 : 8));
-  return ntiles * (8 / g);
+__host__ __device__ inline int ksplit_of(int ntiles) {    // CW / gcd(ntiles, CW): (tile, k-part) units divide evenly over the warps
+  int g = 1;
+  while (g < CW && (ntiles & g) == 0) g <<= 1;
+  return CW / g;
 }
+__host__ __device__ inline int part_kb(int ntiles) { return ntiles * ksplit_of(ntiles); }   // partial-sum slots (1 KB each)
 
 __device__ __forceinline__ void mma_bf16(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
   asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -42,13 +47,12 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // no register shuffling, immediate-offset addressing in the unrolled loop.  The k order inside a chunk is permuted (thread tig owns
 // k = 8 tig .. 8 tig + 7); the B fragments read the same 8 consecutive k of the two batch rows from shared memory (LDS.128), so
 // the permutation is consistent and the sum is unchanged.
-// Work unit = (tile, k-part): ksplit = 8 / gcd(ntiles, 8) so that the units divide evenly over the CW = 8 warps.  Partial sums go
+// Work unit = (tile, k-part): ksplit = CW / gcd(ntiles, CW) so that the units divide evenly over the CW warps.  Partial sums go
 // through part[tile][kq][16][MB] and are added in a fixed order (deterministic).
 static __device__ __noinline__ void contract(const uint4* __restrict__ Wp, int ntiles, int row_base, int tpb, int blk_stride, int K,
                                              const __nv_bfloat16* X, int ldx, float* part, float* outb) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gid = lane >> 2, tig = lane & 3;
-  const int g = (ntiles & 1) ? 1 : ((ntiles & 2) ? 2 : ((ntiles & 4) ? 4 : 8));
-  const int ksplit = 8 / g, ks_shift = (ksplit == 8) ? 3 : ((ksplit == 4) ? 2 : ((ksplit == 2) ? 1 : 0));
+  const int ksplit = ksplit_of(ntiles), ks_shift = 31 - __clz(ksplit);
   const int upw = (ntiles * ksplit) / CW, nch = K >> 5, lg_tpb = 31 - __clz(tpb);
   const __nv_bfloat16* xa_p = X + gid * ldx + tig * 8;
   const __nv_bfloat16* xb_p = X + (gid + 8) * ldx + tig * 8;
@@ -81,9 +85,9 @@ static __device__ __noinline__ void contract(const uint4* __restrict__ Wp, int n
     *reinterpret_cast<float2*>(p + (gid + 8) * MB + 8 + 2 * tig) = make_float2(acc[1][2], acc[1][3]);
   }
   __syncthreads();
-  const int e = threadIdx.x;                              // CT == 256 == one tile of outputs per pass
 #pragma unroll 1
-  for (int tile = 0; tile < ntiles; ++tile) {
+  for (int i = threadIdx.x; i < ntiles * 256; i += CT) {
+    const int tile = i >> 8, e = i & 255;
     const float* p = part + (size_t)(tile << ks_shift) * 256 + e;
     float s = p[0];
 #pragma unroll 1
