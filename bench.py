@@ -312,7 +312,7 @@ def run_ours(args, rank, world, local_rank):
         if rank == 0 and os.path.isdir(os.path.join(ROOT, "gpurun_out")):
             with open(os.path.join(ROOT, "gpurun_out", f"phases_{args.size}_{args.precision}.json"), "w") as fh:
                 json.dump(phases, fh, indent=1)
-        big = [(s.elapsed_time(e), f) for (s, e, f, M, N, Kk, mode, kern) in log if kern in ("tma", "tc") or (kern == "simt" and M > 32)]
+        big = [(s.elapsed_time(e), f) for (s, e, f, M, N, Kk, mode, kern) in log if kern in ("tma", "tma+ln", "tc") or (kern == "simt" and M > 32)]
         tot_ms, tot_fl = sum(x[0] for x in big), sum(x[1] for x in big)
         all_ms = sum(s.elapsed_time(e) for (s, e, *_r) in log)
         ach = tot_fl / (tot_ms * 1e-3) / 1e12 if tot_ms > 0 else 0.0

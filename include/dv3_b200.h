@@ -59,6 +59,13 @@ int dv3_gemm_bf16_tc(int mode, int M, int N, int K, const float* A, int lda, con
  * written in the same pass, so the next contraction reads half the bytes (NULL = no mirror). */
 int dv3_gemm_bf16_tma(int mode, int M, int N, int K, const void* A_bf16, int lda, const void* B_bf16, int ldb, float* C, int ldc,
                       const float* bias, int accumulate, void* stream);
+/* Linear + LayerNorm + SiLU (the reference's miniblock, utils/model.py:71-87) in ONE kernel: y = act(LN(A . B^T + bias)).  The
+ * N / 128 column tiles of a 128-row block run as a thread-block cluster and exchange per-row (mean, M2) partials through distributed
+ * shared memory; pre (optional) receives the pre-LN values the backward needs, y_bf16 (optional) the bf16 mirror of y.
+ * N % 128 == 0 and N <= 1024, bf16 K-major operands as for dv3_gemm_bf16_tma, else DV3_ERR_UNSUPPORTED. */
+int dv3_gemm_ln_bf16_tma(int M, int N, int K, const void* A_bf16, int lda, const void* B_bf16, int ldb, const float* bias, const float* gamma,
+                         const float* beta, float eps, int act, float* pre, int ldp, float* y, int ldy, void* y_bf16, float* mean, float* rstd,
+                         void* stream);
 int dv3_f32_to_bf16(int R, int C, const float* src, int lds, void* dst_bf16, int ldd, void* stream);
 
 /* ---- LayerNorm(+SiLU) blocks: miniblock order Linear -> LayerNorm -> SiLU, utils/model.py:71-87 ---------- */

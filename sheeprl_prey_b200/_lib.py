@@ -26,6 +26,7 @@ SIGNATURES = {
     "dv3_gemm_bf16_tc": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_gemm_bf16_tma": [_i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp],
     "dv3_f32_to_bf16": [_i, _i, c_fp, _i, c_fp, _i, c_fp],
+    "dv3_gemm_ln_bf16_tma": [_i, _i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_ln_act_fwd": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_ln_act_bwd": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
     "dv3_col_reduce_scratch_bytes": [_i, _i],
@@ -189,6 +190,9 @@ class CudaOps:
         self.use_mirrors = self.precision == "bf16" and os.environ.get("DV3_BF16_RESIDENT", "1") != "0"
         self.mirror_check = os.environ.get("DV3_MIRROR_CHECK", "0") == "1"
         self.use_cluster_scan = os.environ.get("DV3_CLUSTER_SCAN", "1") != "0"
+        # Linear+LayerNorm+SiLU in one clustered kernel (dv3_gemm_ln_bf16_tma): correct (tests) but its epilogue -- one thread per row
+        # for three TMEM sweeps and 128 SiLUs -- is slower than the separate warp-per-row LayerNorm: 117 vs 130 steps/s.  Opt-in.
+        self.use_gemm_ln = os.environ.get("DV3_GEMM_LN", "0") == "1"
         self.scan_kernel = None
         self.bwd_scan_kernel = None
         self._mir_start: List[int] = []
@@ -292,6 +296,37 @@ class CudaOps:
         if self.gemm_log is not None:
             e1.record(torch.cuda.current_stream(self.device))
             self.gemm_log.append((e0, e1, 2.0 * M * N * K, M, N, K, mode, kern))
+
+    def gemm_ln(self, A, W, bias, gamma, beta, eps, act, pre, y, mean, rstd) -> bool:
+        """y = act(LN(A . W^T + bias)) in one kernel (pre receives the pre-LN values); False when the operands have no bf16 mirror
+        or the shape is outside the fused kernel's plan -- the caller then issues the contraction and the LayerNorm separately."""
+        if not (self.use_mirrors and self.use_gemm_ln):
+            return False
+        pa, M, K, lda = _mat(A)
+        pb, N, Kb, ldb = _mat(W)
+        if M < 128 or K < 32 or (N % 128) or N > 1024:
+            return False
+        ma, mb = self._m16(pa), self._m16(pb)
+        if ma is None or mb is None or ((lda | ldb) & 7) or ((ma | mb) & 15):
+            return False
+        if self.mirror_check:
+            self._check_mirror(A, f"A of fused NT M{M} N{N} K{K}")
+            self._check_mirror(W, f"B of fused NT M{M} N{N} K{K}")
+        pp, _, _, ldp = _mat(pre)
+        py, _, _, ldy = _mat(y)
+        if self.gemm_log is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(torch.cuda.current_stream(self.device))
+        rc = self.lib.dv3_gemm_ln_bf16_tma(M, N, K, ma, lda, mb, ldb, _p(bias), _p(gamma), _p(beta), eps, act, pp, ldp, py, ldy, self._m16(py),
+                                           _p(mean), _p(rstd), self._s())
+        if rc == -2:
+            return False
+        _chk(rc, "dv3_gemm_ln_bf16_tma")
+        self.launches += 1
+        if self.gemm_log is not None:
+            e1.record(torch.cuda.current_stream(self.device))
+            self.gemm_log.append((e0, e1, 2.0 * M * N * K, M, N, K, "NT", "tma+ln"))
+        return True
 
     def transpose(self, src, dst):
         ps, R, Cc, lds = _mat(src)

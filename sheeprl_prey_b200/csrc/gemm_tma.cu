@@ -20,6 +20,8 @@
 #include "common.cuh"
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 namespace {
 
@@ -244,7 +246,190 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   }
 }
 
+// ---- Linear + LayerNorm + SiLU in one kernel ------------------------------------------------------------------------------------
+// y = SiLU(LayerNorm(A . B^T + bias)) for a layer whose N (<= 1024, multiple of 128) output features span CL = N / 128 column tiles:
+// the CL CTAs that own the tiles of one 128-row block form a thread-block cluster.  Main loop as above (TMA ring -> tcgen05.mma ->
+// TMEM).  Epilogue: every thread owns one row of its CTA's 128 x 128 tile in TMEM; it reduces (mean, M2) over its 128 columns,
+// pushes the pair into the shared memory of all CTAs of the cluster (DSMEM), and after one cluster barrier merges the CL partials
+// (Chan) into the row statistics, re-reads the accumulator from TMEM and writes the pre-LN value (kept for the backward), the
+// activation and its bf16 mirror.  Saves the separate LayerNorm launch and its re-read of the pre-activation.
+constexpr int LN_MAX_CL = 8;
+__global__ void __launch_bounds__(NUM_THREADS, 2)
+gemm_ln_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
+                   const float* __restrict__ bias, const float* __restrict__ gamma, const float* __restrict__ beta, float eps, int act,
+                   float* __restrict__ pre, int ldp, float* __restrict__ y, int ldy, __nv_bfloat16* __restrict__ y16,
+                   float* __restrict__ mean, float* __restrict__ rstd) {
+  cg::cluster_group cluster = cg::this_cluster();
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * STAGE_A_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (STAGE_A_BYTES + STAGE_B_BYTES));
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  float* prm = reinterpret_cast<float*>(tmem_ptr_smem + 4);            // [3][128]: bias | gamma | beta of this column tile
+  float2* stats = reinterpret_cast<float2*>(prm + 3 * TBN);            // [LN_MAX_CL][128] (mean, M2) pushed by the cluster's CTAs
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * TBN;
+  const int num_kb = (K + TBK - 1) / TBK;
+  const int CL = (int)cluster.num_blocks(), crank = (int)cluster.block_rank();
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(TMEM_COLS));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_sync();
+  for (int i = threadIdx.x; i < TBN; i += NUM_THREADS) {
+    prm[i] = bias ? __ldg(bias + n0 + i) : 0.f;
+    prm[TBN + i] = __ldg(gamma + n0 + i);
+    prm[2 * TBN + i] = __ldg(beta + n0 + i);
+  }
+  cluster.sync();                    // every CTA of the cluster is resident (its `stats` may now be written remotely); prm visible
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % STAGES;
+        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+        mbar_wait(&empty_bar[s], ph ^ 1u);
+        mbar_expect_tx(&full_bar[s], STAGE_A_BYTES + STAGE_B_BYTES);
+        tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], kb * TBK, m0);
+        tma_load_2d(smem_b + s * STAGE_B_BYTES, &tmB, &full_bar[s], kb * TBK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % STAGES;
+      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      mbar_wait(&full_bar[s], ph);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (lane == 0) {
+        const uint32_t a_addr = smem_u32(smem_a + s * STAGE_A_BYTES);
+        const uint32_t b_addr = smem_u32(smem_b + s * STAGE_B_BYTES);
+#pragma unroll
+        for (int k = 0; k < TBK / 16; ++k) {
+          const uint64_t adesc = make_smem_desc(a_addr + k * 32);
+          const uint64_t bdesc = make_smem_desc(b_addr + k * 32);
+          const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+          asm volatile(
+              "{\n"
+              ".reg .pred p;\n"
+              "setp.ne.b32 p, %4, 0;\n"
+              "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+              "}\n" ::"r"(tmem_base),
+              "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+              : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[s])) : "memory");
+        if (kb == num_kb - 1)
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(tmem_full_bar)) : "memory");
+      }
+      __syncwarp();
+    }
+  }
+  const int ew = warp & 3;                                   // epilogue warps 2-5: TMEM lanes [32 ew, 32 ew + 32)
+  const int rl = ew * 32 + lane;                             // row of the tile owned by this thread
+  const uint32_t trow = tmem_base + ((uint32_t)(ew * 32) << 16);
+  auto ld32 = [&](int c0, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(trow + (uint32_t)c0));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+  };
+  if (warp >= 2) {
+    // ---- pass 1: (mean, M2) of the own 128 columns of the row
+    mbar_wait(tmem_full_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    uint32_t r[32];
+    float s = 0.f;
+#pragma unroll 1
+    for (int c0 = 0; c0 < TBN; c0 += 32) {
+      ld32(c0, r);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) s += __uint_as_float(r[j]) + prm[c0 + j];
+    }
+    const float mu_c = s * (1.f / (float)TBN);
+    float q = 0.f;
+#pragma unroll 1
+    for (int c0 = 0; c0 < TBN; c0 += 32) {
+      ld32(c0, r);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) { const float d = __uint_as_float(r[j]) + prm[c0 + j] - mu_c; q = fmaf(d, d, q); }
+    }
+    for (int peer = 0; peer < CL; ++peer) cluster.map_shared_rank(stats, peer)[crank * TBM + rl] = make_float2(mu_c, q);
+  }
+  cluster.sync();                    // all partials of the row block have arrived
+  if (warp >= 2) {
+    // ---- pass 2: row statistics, normalise, activation, stores (32 x 32 chunks transposed through shared memory: coalesced rows)
+    float mu = 0.f;
+    for (int cc = 0; cc < CL; ++cc) mu += stats[cc * TBM + rl].x;
+    mu /= (float)CL;
+    float m2 = 0.f;
+    for (int cc = 0; cc < CL; ++cc) { const float2 p = stats[cc * TBM + rl]; const float d = p.x - mu; m2 += p.y + (float)TBN * d * d; }
+    const float rs = rsqrtf(m2 / (float)N + eps);
+    const int grow = m0 + rl;
+    if (crank == 0 && grow < M) { mean[grow] = mu; rstd[grow] = rs; }
+    float* stg = reinterpret_cast<float*>(smem) + ew * (32 * 33);      // operand ring is idle now
+    const int rows_here = min(32, M - (m0 + ew * 32));
+    uint32_t r[32];
+#pragma unroll 1
+    for (int c0 = 0; c0 < TBN; c0 += 32) {
+      ld32(c0, r);
+      const int gn = n0 + c0 + lane;
+      // pre-LN values
+#pragma unroll
+      for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = __uint_as_float(r[j]) + prm[c0 + j];
+      __syncwarp();
+      if (pre) {
+        for (int rr = 0; rr < rows_here; ++rr) pre[(size_t)(m0 + ew * 32 + rr) * ldp + gn] = stg[rr * 33 + lane];
+      }
+      __syncwarp();
+      // activations
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const float ln = (__uint_as_float(r[j]) + prm[c0 + j] - mu) * rs * prm[TBN + c0 + j] + prm[2 * TBN + c0 + j];
+        stg[lane * 33 + j] = act ? siluf_(ln) : ln;
+      }
+      __syncwarp();
+      for (int rr = 0; rr < rows_here; ++rr) {
+        const float o = stg[rr * 33 + lane];
+        const size_t off = (size_t)(m0 + ew * 32 + rr) * ldy + gn;
+        y[off] = o;
+        if (y16) y16[off] = __float2bfloat16_rn(o);
+      }
+      __syncwarp();
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+  }
+}
+
 constexpr int SMEM_BYTES = STAGES * (STAGE_A_BYTES + STAGE_B_BYTES) + (2 * STAGES + 1) * 8 + 16 + 1024;
+constexpr int SMEM_BYTES_LN = SMEM_BYTES + 64 + 3 * TBN * 4 + LN_MAX_CL * TBM * 8;
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -307,6 +492,50 @@ int launch_tma(int M, int N, int K, const void* A, int lda, const void* B, int l
 }
 
 }  // namespace
+
+extern "C" int dv3_gemm_ln_bf16_tma(int M, int N, int K, const void* A, int lda, const void* B, int ldb, const float* bias, const float* gamma,
+                                    const float* beta, float eps, int act, float* pre, int ldp, float* y, int ldy, void* y_bf16, float* mean,
+                                    float* rstd, void* stream_) {
+  if (M <= 0 || N <= 0 || K <= 0 || !A || !B || !gamma || !beta || !y || !mean || !rstd) return DV3_ERR_ARG;
+  if ((N % TBN) || N / TBN > LN_MAX_CL) return DV3_ERR_UNSUPPORTED;       // one cluster = all column tiles of a row block
+  if (((uintptr_t)A & 15) || ((uintptr_t)B & 15) || (lda & 7) || (ldb & 7)) return DV3_ERR_UNSUPPORTED;
+  if (!g_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return DV3_ERR_UNSUPPORTED;
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_ln_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES_LN);
+    if (e != cudaSuccess) return (int)e;
+    configured = true;
+  }
+  CUtensorMap tmA, tmB;
+  int rc = make_map(&tmA, A, M, K, lda, false);
+  if (rc) return rc;
+  rc = make_map(&tmB, B, N, K, ldb, false);
+  if (rc) return rc;
+  const int CL = N / TBN;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(CL, (M + TBM - 1) / TBM, 1);
+  if (cfg.gridDim.y > 65535) return DV3_ERR_UNSUPPORTED;
+  cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = SMEM_BYTES_LN;
+  cfg.stream = (cudaStream_t)stream_;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_ln_tma_kernel, tmA, tmB, M, N, K, bias, gamma, beta, eps, act, pre, ldp, y, ldy,
+                                     reinterpret_cast<__nv_bfloat16*>(y_bf16), mean, rstd);
+  if (e != cudaSuccess) return (int)e;
+  return DV3_OK;
+}
 
 extern "C" int dv3_gemm_bf16_tma(int mode, int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc,
                                  const float* bias, int accumulate, void* stream_) {

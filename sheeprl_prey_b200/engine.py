@@ -125,10 +125,13 @@ class DenseStack:
         ops = self.ops
         r1 = self.rows if r1 is None else r1
         inp = x
+        fuse = getattr(ops, "gemm_ln", None)
         for i, L in enumerate(self.layers):
-            ops.gemm("NT", inp, L["w"], self.pre[i][r0:r1], bias=L.get("b"))
-            ops.ln_act_fwd(self.pre[i][r0:r1], L["g"], L["beta"], L["eps"], 1, self.act[i][r0:r1],
-                           self.mean[i][r0:r1], self.rstd[i][r0:r1])
+            if fuse is None or not fuse(inp, L["w"], L.get("b"), L["g"], L["beta"], L["eps"], 1, self.pre[i][r0:r1], self.act[i][r0:r1],
+                                        self.mean[i][r0:r1], self.rstd[i][r0:r1]):
+                ops.gemm("NT", inp, L["w"], self.pre[i][r0:r1], bias=L.get("b"))
+                ops.ln_act_fwd(self.pre[i][r0:r1], L["g"], L["beta"], L["eps"], 1, self.act[i][r0:r1],
+                               self.mean[i][r0:r1], self.rstd[i][r0:r1])
             inp = self.act[i][r0:r1]
         col = 0
         for h in self.heads:

@@ -561,3 +561,30 @@ def test_ln_act_fwd_gather(cuda_ops, torch_ops, M, U, heads):
         outs.append((y, mean, rstd))
     for a, r in zip(outs[1], outs[0]):
         assert rel(a, r) < TOL
+
+
+@pytest.mark.parametrize("M,N,K,bias", [(1024, 512, 512, True), (16384, 512, 1536, True), (1000, 640, 520, False), (130, 1024, 64, True),
+                                        (1024, 128, 256, True)])
+def test_gemm_ln_fused(cuda_ops_bf16, M, N, K, bias):
+    """Linear + LayerNorm + SiLU in one clustered tcgen05 kernel == TMA GEMM followed by the LayerNorm kernel (same bf16 operands)."""
+    ops = cuda_ops_bf16
+    ops.use_gemm_ln = True          # opt-in path (see CudaOps.__init__)
+    pad = (K + 7) // 8 * 8
+    A = torch.zeros(M, pad, device=DEV)[:, :K]
+    W = torch.zeros(N, pad, device=DEV)[:, :K]
+    A.copy_(rnd(M, K))
+    W.copy_(rnd(N, K, seed=3) * 0.1)
+    b = rnd(N, seed=4) if bias else None
+    g, be = rnd(N, seed=5) * 0.2 + 1, rnd(N, seed=6) * 0.1
+    for t in (A._base, W._base):
+        ops.mirror(t)
+        ops.refresh(t)
+    pre0, y0, mean0, rstd0 = torch.zeros(M, N, device=DEV), torch.zeros(M, N, device=DEV), torch.zeros(M, device=DEV), torch.zeros(M, device=DEV)
+    ops.gemm("NT", A, W, pre0, bias=b)
+    ops.ln_act_fwd(pre0, g, be, 1e-3, 1, y0, mean0, rstd0)
+    pre1, y1, mean1, rstd1 = torch.zeros_like(pre0), torch.zeros_like(y0), torch.zeros_like(mean0), torch.zeros_like(rstd0)
+    ops.mirror(y1)
+    assert ops.gemm_ln(A, W, b, g, be, 1e-3, 1, pre1, y1, mean1, rstd1)
+    torch.cuda.synchronize()
+    assert rel(pre1, pre0) < 2e-5 and rel(y1, y0) < 5e-5 and rel(mean1, mean0) < 2e-5 and rel(rstd1, rstd0) < 2e-5
+    assert torch.equal(ops._m16_view(y1), y1.bfloat16())
