@@ -14,7 +14,7 @@
 //   B4  [dh_{t-1} part | d feat] = d gates_pre . Wgru (own columns);  LayerNorm+SiLU backward                    -> d feat_pre
 //   B5  dz_{t-1} = d feat_pre . Wmlp[:, :S] (own categoricals);  carry = (1 - first_t) * (dz_{t-1}, dh_{t-1} part + dh_t (1 - u))
 // Seven hardware cluster barriers per step; saved-activation inputs of step t-1 are fetched with cp.async while step t runs.
-#define DV3_SCAN_CT 256   // threads per CTA (8 warps: 1.84 ms; 16 warps spill at the 128-register cap (2.02 ms))
+#define DV3_SCAN_CT 256   // threads per CTA (8 warps: 1.84 ms; 16 warps at the 128-register cap: 1.93 ms)
 #include "scan_cluster.cuh"
 #include "dv3_b200.h"
 #include <stdio.h>
@@ -154,29 +154,33 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
   float* p_r = takef(2 * hper);
   float* p_gru = takef(6 * dper);
   float* p_mlp = takef(2 * uper);
-  float* dzc = takef((size_t)MB * sper);                  // carried dL/dz (own categoricals), dL/dh (own units)
-  float* dhc = takef((size_t)MB * dper);
-  float* dhd = takef((size_t)MB * dper);                  // dh_t * (1 - u): direct path to h_{t-1}
-  float* dhp = takef((size_t)MB * dper);                  // h_{t-1} part of d gates_pre . Wgru
-  // saved gradients whose global store is deferred by one barrier
-  float* sv_pr = takef((size_t)MB * sper);
-  float* sv_hp = takef((size_t)MB * hper);
-  float* sv_lr = takef((size_t)MB * hper);
-  float* sv_gp = takef((size_t)MB * 3 * dper);            // [gate][m][dl]
-  float* sv_lg = takef((size_t)MB * 3 * dper);
-  float* sv_fp = takef((size_t)MB * uper);
-  float* sv_lf = takef((size_t)MB * uper);
-  // cp.async landing zones: the saved forward tensors of the next step to process
-  float* f_ps = takef((size_t)MB * sper);
-  float* f_cf = takef((size_t)MB * sper);
-  float* f_pn = takef((size_t)MB * sper);
-  float* f_dl = takef((size_t)MB * sper);
-  float* f_dz = takef((size_t)MB * sper);
-  float* f_dh = takef((size_t)MB * dper);
-  float* f_hp = takef((size_t)MB * hper);
-  float* f_gp = takef((size_t)MB * 3 * dper);             // [gate][m][dl]
-  float* f_hi = takef((size_t)MB * dper);
-  float* f_fp = takef((size_t)MB * uper);
+  // Own-slice buffers, grouped by size so that each one is `group base + index * size` (cheap to rematerialise: keeping ~25 separate
+  // pointers live across the time loop is what pushes the 16-warp build over its 128-register cap).
+  float* gS = takef((size_t)7 * MB * sper);
+  float* gD = takef((size_t)14 * MB * dper);
+  float* gH = takef((size_t)3 * MB * hper);
+  float* gU = takef((size_t)3 * MB * uper);
+#define dzc (gS)                               /* carried dL/dz (own categoricals) */
+#define sv_pr (gS + 1 * MB * sper)             /* saved gradients whose global store is deferred by one barrier: sv_* */
+#define f_ps (gS + 2 * MB * sper)              /* cp.async landing zones (saved forward tensors of the next step to process): f_* */
+#define f_cf (gS + 3 * MB * sper)
+#define f_pn (gS + 4 * MB * sper)
+#define f_dl (gS + 5 * MB * sper)
+#define f_dz (gS + 6 * MB * sper)
+#define dhc (gD)                               /* carried dL/dh (own units) */
+#define dhd (gD + 1 * MB * dper)               /* dh_t * (1 - u): direct path to h_{t-1} */
+#define dhp (gD + 2 * MB * dper)               /* h_{t-1} part of d gates_pre . Wgru */
+#define f_dh (gD + 3 * MB * dper)
+#define f_hi (gD + 4 * MB * dper)
+#define sv_gp (gD + 5 * MB * dper)             /* [gate][m][dl] */
+#define sv_lg (gD + 8 * MB * dper)
+#define f_gp (gD + 11 * MB * dper)
+#define sv_hp (gH)
+#define sv_lr (gH + 1 * MB * hper)
+#define f_hp (gH + 2 * MB * hper)
+#define sv_fp (gU)
+#define sv_lf (gU + 1 * MB * uper)
+#define f_fp (gU + 2 * MB * uper)
   float* f_st = takef(6 * MB);                            // hidr mean|rstd, gru mean|rstd, feat mean|rstd
 
   for (int i = tid; i < MB * ld_pr / 2; i += CT) reinterpret_cast<uint32_t*>(x_pr)[i] = 0u;
@@ -356,6 +360,28 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     BDBG(15);
   }
 }
+
+#undef dzc
+#undef sv_pr
+#undef f_ps
+#undef f_cf
+#undef f_pn
+#undef f_dl
+#undef f_dz
+#undef dhc
+#undef dhd
+#undef dhp
+#undef f_dh
+#undef f_hi
+#undef sv_gp
+#undef sv_lg
+#undef f_gp
+#undef sv_hp
+#undef sv_lr
+#undef f_hp
+#undef sv_fp
+#undef sv_lf
+#undef f_fp
 
 bool shape_ok(const Dv3ScanBwdArgs* h, int CL, size_t* smem_bytes, int max_smem) {
   if (h->U % (16 * CL) || h->D % (16 * CL) || h->Hh % (16 * CL) || h->G % CL || ((h->G / CL) * h->Kc) % 16) return false;
