@@ -3,18 +3,18 @@
 //   C[M,N] (+)= op(A) * op(B) (+ bias)      NT / NN / TN, fp32 operands in HBM, arbitrary leading dimensions, ragged edges.
 //
 // Design (sm_100a only):
-//   * one CTA per 128 x 128 output tile, 256 threads, warp-specialised:
-//       warps 0-3  producers : read the fp32 operand tiles from global memory (coalesced for either majorness), round to
-//                              bf16 in registers and write them into shared memory directly in the canonical K-major
-//                              SWIZZLE_128B UMMA layout (so the fp32->bf16 conversion and any transposition are fused
-//                              into the load path: no staging copies of activations / weights / gradients in HBM);
-//       warp  4    issuer    : allocates TMEM, one elected lane issues tcgen05.mma (M128 x N128 x K16, kind::f16) per
+//   * one CTA per 128 x 128 output tile, 384 threads, warp-specialised:
+//       warps 0-3  producers A, warps 4-7 producers B : read the fp32 operand tiles from global memory (coalesced for either
+//                              majorness), round to bf16 in registers and write them into shared memory directly in the canonical
+//                              SWIZZLE_128B UMMA layout -- K-major, or MN-major for operands whose contiguous dimension is M / N
+//                              (no transposition) -- so the fp32->bf16 conversion is fused into the load path;
+//       warp  8    issuer    : allocates TMEM, one elected lane issues tcgen05.mma (M128 x N128 x K16, kind::f16) per
 //                              16-wide k slice, and tcgen05.commit's the stage's "empty" mbarrier;
-//       warps 4-7  epilogue  : tcgen05.ld the 128x128 fp32 accumulator (one TMEM lane = one output row), add bias /
-//                              accumulate, store to global.
+//       warps 8-11 epilogue  : tcgen05.ld the 128x128 fp32 accumulator (one TMEM lane = one output row), transpose 32 x 32
+//                              chunks through shared memory, add bias / accumulate / split-K atomics, coalesced stores.
 //   * 4-stage shared-memory ring (32 KB / stage) with full / empty mbarriers; generic-proxy writes are made visible to
 //     the tensor core's async proxy with fence.proxy.async before the "full" arrive.
-// Replaces torch addmm/mm (cuBLAS) on the large-M contractions of the step (a3, a5, a8, a9, a12, a13 and
+// Used for operands that have no bf16 mirror (gemm_tma.cu takes the mirrored ones).  Replaces torch addmm/mm (cuBLAS) on the large-M contractions of the step (a3, a5, a8, a9, a12, a13 and
 // the batched weight-gradient contractions of a7).  Numerics: bf16 operands, fp32 accumulate -> the north-star's
 // "2e-2 for bf16 tensor-core GEMMs" mode.
 #include "common.cuh"

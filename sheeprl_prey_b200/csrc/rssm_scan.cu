@@ -7,7 +7,7 @@
 //
 // Design: grid = one CTA per SM (cooperative launch); each CTA owns a fixed slice of the output rows of every in-loop
 // weight matrix and keeps that slice in shared memory for the whole scan (XS/S/M sizes: the in-loop weights fit in the
-// 148 x 227 KB of aggregate shared memory; slices that do not fit are streamed from L2).  Per step there are five
+// 148 x 227 KB of aggregate shared memory; slices that do not fit are streamed from L2).  Per step there are six
 // grid-wide barriers (one per dependent contraction / normalisation), and the activation vectors (B <= 16 rows) are
 // exchanged through L2.  All LayerNorms, the GRU gates, unimix, and the inverse-CDF sampling are fused into the stages:
 //   P1  feat_pre slice  = gather-sum of W_mlp columns selected by the one-hot z  +  W_mlp[:, S:] . a_t
@@ -15,8 +15,10 @@
 //       per-CTA (mean, M2) of the own gate values (Chan's parallel variance)
 //   P3  LayerNorm statistics of the 3D gate vector from the per-CTA partials; gates -> h'[own d]
 //   P4  hidr_pre slice  = W_r0[:, :D] . h' + (e_t . W_r0[:, D:]^T + b)   (the embedding part is hoisted out of the scan)
-//   P5  CTAs 0..G-1 own one categorical each: hid = SiLU(LN(hidr_pre)); 32 logits = W_r1 rows . hid + b; unimix;
-//       sample z_t by inverse CDF of the injected uniform; write raw / unimix logits, index, one-hot.
+//   P5a hid = SiLU(LN(hidr_pre)) (every CTA, redundantly); own posterior logit rows = W_r1 rows . hid + b  (balanced over all CTAs)
+//   P5b CTAs 0..G-1 own one categorical each: unimix; sample z_t by inverse CDF of the injected uniform; write unimix logits,
+//       index, one-hot.   (six grid-wide barriers per step in total)
+// This is the fp32-precision kernel; in bf16 precision the step uses the cluster kernel of rssm_scan_cluster.cu instead.
 // Everything the hand-written backward needs (pre-LN values, LN statistics, inputs of every contraction) is written to the
 // same buffers the per-op path fills.
 #include "common.cuh"
