@@ -92,7 +92,7 @@ int dv3_col_reduce_noalloc(int M, int U, const float* d, int ldd, const float* x
 /* ---- pixel encoder / decoder: CNNEncoder agent.py:28-80, CNNDecoder agent.py:136-206, LayerNormChannelLast
  * utils/model.py:225-235.  Activations are channel-last; k = tap*C + c with tap = kh*4 + kw; the contractions run on
  * dv3_gemm_*: Conv2d(k4,s2,p1) = im2col + GEMM, ConvTranspose2d(k4,s2,p1) = GEMM + col2im (and vice versa backward). */
-int dv3_im2col_k4s2p1(int N, int H, int W, int C, const float* x, float* col, void* stream);
+int dv3_im2col_k4s2p1(int N, int H, int W, int C, const float* x, float* col, void* col_bf16, void* stream);
 int dv3_col2im_k4s2p1(int N, int Hi, int Wi, int C, const float* col, const float* bias, float add, float* y, void* stream);
 int dv3_permute_last2(int A, int B, int C, const float* src, long long lds, float* dst, long long ldd, void* stream);
 int dv3_u8_nchw_to_nhwc(int N, int C, int HW, const unsigned char* src, float scale, float* dst, int Ctot, int c_off, void* stream);

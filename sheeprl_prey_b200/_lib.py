@@ -32,7 +32,7 @@ SIGNATURES = {
     "dv3_col_reduce_scratch_bytes": [_i, _i],
     "dv3_col_reduce": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
     "dv3_col_reduce_noalloc": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp],
-    "dv3_im2col_k4s2p1": [_i, _i, _i, _i, c_fp, c_fp, c_fp],
+    "dv3_im2col_k4s2p1": [_i, _i, _i, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_col2im_k4s2p1": [_i, _i, _i, _i, c_fp, c_fp, _f, c_fp, c_fp],
     "dv3_permute_last2": [_i, _i, _i, c_fp, _ll, c_fp, _ll, c_fp],
     "dv3_u8_nchw_to_nhwc": [_i, _i, _i, c_fp, _f, c_fp, _i, _i, c_fp],
@@ -418,7 +418,7 @@ class CudaOps:
     def im2col(self, x, N, H, W, Cc, col):
         assert x.is_contiguous() and col.is_contiguous() and col.numel() == N * (H // 2) * (W // 2) * 16 * Cc
         self.launches += 1
-        _chk(self.lib.dv3_im2col_k4s2p1(N, H, W, Cc, _p(x), _p(col), self._s()), "dv3_im2col_k4s2p1")
+        _chk(self.lib.dv3_im2col_k4s2p1(N, H, W, Cc, _p(x), _p(col), self._m16(_p(col)), self._s()), "dv3_im2col_k4s2p1")
 
     def col2im(self, col, N, Hi, Wi, Cc, bias, add, y):
         assert col.is_contiguous() and y.is_contiguous() and y.numel() == N * Hi * Wi * 4 * Cc
@@ -429,6 +429,8 @@ class CudaOps:
         """dst[a][c][b] = src[a][b][c]; lds / ldd = element stride between consecutive a (default B*C)."""
         self.launches += 1
         _chk(self.lib.dv3_permute_last2(A, Bn, Cn, _p(src), lds or Bn * Cn, _p(dst), ldd or Bn * Cn, self._s()), "dv3_permute_last2")
+        if ldd is None and dst.dim() <= 2:
+            self.refresh(dst.reshape(1, -1) if dst.dim() == 1 else dst)      # contiguous destinations with a bf16 mirror
 
     def u8_to_nhwc(self, src, N, Cc, HW, scale, dst, Ctot, c_off):
         assert src.dtype == torch.uint8 and src.is_contiguous()
@@ -440,6 +442,7 @@ class CudaOps:
         assert mode.is_contiguous() and target.is_contiguous() and dmode.is_contiguous()
         self.launches += 1
         _chk(self.lib.dv3_mse_rows(M, Dd, _p(mode), _p(target), float(scale), _p(loss_rows), _p(dmode), self._s()), "dv3_mse_rows")
+        self.refresh(dmode)
 
     # ---------------------------------------------------------------- GRU
     def gru_gate_fwd(self, gates_pre, lnw, lnb, h_in, h_out, mean, rstd):

@@ -18,6 +18,15 @@ import torch
 Tensor = torch.Tensor
 
 
+def _mirror(ops, *tensors) -> None:
+    """bf16 mirrors for the contraction operands (CudaOps in bf16 precision; see engine._mirror)."""
+    fn = getattr(ops, "mirror", None)
+    if fn is not None:
+        for t in tensors:
+            if t is not None:
+                fn(t)
+
+
 class ConvEncoder:
     def __init__(self, ops, device, N: int, in_channels: Sequence[int], image_hw: int, layers: List[dict], out_view: Tensor, ld_out: int):
         """layers[l]: dict(w [Cout,Cin,4,4], g, beta, dw, dg, dbeta).  out_view: [N, 16*C_last] view (row stride ld_out) that
@@ -50,6 +59,7 @@ class ConvEncoder:
         self._dpre = torch.empty(rmax, **f32)
         self._dln = torch.empty(rmax, **f32)
         self._dact = torch.empty(max(max(d[3] * d[2] for d in self.dims), N * image_hw * image_hw * self.C0), **f32)
+        _mirror(ops, *self.col, *self.wt, *self.act, self._dpre)
 
     def load_images(self, images: Sequence[Tensor]) -> None:
         """images[k]: uint8 [T,B,C_k,H,W] (or [N,C_k,H,W]); -> x0 (channel-last, /255; dreamer_v3.py:102)."""
@@ -85,8 +95,7 @@ class ConvEncoder:
             H, Cin, Cout, rows = self.dims[l]
             dpre = self._dpre[: rows * Cout].view(rows, Cout)
             dln = self._dln[: rows * Cout].view(rows, Cout)
-            ops.ln_act_bwd(dact, self.pre[l], L["g"], L["beta"], self.mean[l], self.rstd[l], 1, dpre, dln)
-            ops.ln_param_grad(dln, self.pre[l], self.mean[l], self.rstd[l], L["dg"], L["dbeta"])
+            ops.ln_act_bwd_fused(dact, self.pre[l], L["g"], L["beta"], self.mean[l], self.rstd[l], 1, dpre, dln, L["dg"], L["dbeta"], None)
             ops.gemm("TN", dpre, self.col[l], self.dwt[l])
             ops.permute_last2(self.dwt[l], Cout, 16, Cin, L["dw"])                     # back to [Cout][Cin][16]
             if l > 0:
@@ -129,6 +138,7 @@ class ConvDecoder:
         self._dx = torch.empty(max(d[3] * d[1] for d in self.dims), **f32)
         self.d_rec = torch.empty(N, self.out_hw * self.out_hw * self.out_c, **f32)
         self.loss_rows = torch.empty(N, **f32)
+        _mirror(ops, self.x0, *self.colT, *self.wr, *[a for a in self.act if a is not None], self._dpre, self.d_rec, self.dlin_out)
 
     def forward(self, latent: Tensor) -> None:
         ops = self.ops
@@ -162,8 +172,7 @@ class ConvDecoder:
             if L.get("g") is not None:
                 dpre = self._dpre[: rows_out * Cout].view(rows_out, Cout)
                 dln = self._dln[: rows_out * Cout].view(rows_out, Cout)
-                ops.ln_act_bwd(dout, self.pre[l], L["g"], L["beta"], self.mean[l], self.rstd[l], 1, dpre, dln)
-                ops.ln_param_grad(dln, self.pre[l], self.mean[l], self.rstd[l], L["dg"], L["dbeta"])
+                ops.ln_act_bwd_fused(dout, self.pre[l], L["g"], L["beta"], self.mean[l], self.rstd[l], 1, dpre, dln, L["dg"], L["dbeta"], None)
             else:
                 dpre = dout
             if L.get("b") is not None:

@@ -15,7 +15,7 @@ namespace {
 
 // col[(n*Ho + oh)*Wo + ow][tap*C + c] = x[n][2*oh-1+kh][2*ow-1+kw][c]  (0 outside), tap = kh*4 + kw, Ho = H/2, Wo = W/2
 __global__ void __launch_bounds__(256) im2col_k4s2p1_kernel(int N, int H, int W, int C, const float* __restrict__ x,
-                                                           float* __restrict__ col) {
+                                                           float* __restrict__ col, __nv_bfloat16* __restrict__ col16) {
   const int Ho = H >> 1, Wo = W >> 1;
   const size_t total = (size_t)N * Ho * Wo * 16 * C;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(256) im2col_k4s2p1_kernel(int N, int H, int W,
     float v = 0.f;
     if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = __ldg(x + (((size_t)n * H + ih) * W + iw) * C + c);
     col[i] = v;
+    if (col16) col16[i] = __float2bfloat16_rn(v);
   }
 }
 
@@ -357,9 +358,10 @@ static inline int grid_for(size_t n) {
 
 extern "C" {
 
-int dv3_im2col_k4s2p1(int N, int H, int W, int C, const float* x, float* col, void* stream) {
+int dv3_im2col_k4s2p1(int N, int H, int W, int C, const float* x, float* col, void* col_bf16, void* stream) {
   if (N <= 0 || H < 2 || W < 2 || (H & 1) || (W & 1) || C <= 0) return DV3_ERR_ARG;
-  im2col_k4s2p1_kernel<<<grid_for((size_t)N * (H / 2) * (W / 2) * 16 * C), 256, 0, (cudaStream_t)stream>>>(N, H, W, C, x, col);
+  im2col_k4s2p1_kernel<<<grid_for((size_t)N * (H / 2) * (W / 2) * 16 * C), 256, 0, (cudaStream_t)stream>>>(
+      N, H, W, C, x, col, reinterpret_cast<__nv_bfloat16*>(col_bf16));
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -369,3 +369,38 @@ def test_pixel_step_matches_oracle(cuda_ops):
     coef = min(1.0, 1000.0 / (float(out["Grads/world_model"]) + 1e-6))
     worst = max((rel(eng.wm.g[k] * coef, out["world_grads"][k]), k) for k in eng.wm.g)
     assert worst[0] < 5e-5, worst
+
+
+def test_pixel_step_bf16_resident_within_2e2():
+    """Pixel + vector observations in bf16 mode: the convolution contractions read bf16 mirrors (im2col / weight re-order / LayerNorm
+    kernels write them) through the TMA kernel; every contraction checks its mirrors; losses and gradients within the bf16 tolerance."""
+    from sheeprl_prey_b200._lib import CudaOps
+
+    B, T, H = 4, 8, 3
+    cfg = make_cfg("XS", batch_size=B, sequence_length=T, horizon=H, deter=64, hidden=48, units=64, layers=2, cnn_mult=8,
+                   cnn_keys=("rgb",), mlp_keys=("state",))
+    od, acts = {"rgb": (3, 64, 64), "state": 9}, [6]
+    params = random_params_like(cfg, od, acts, seed=3)
+    tr = O.OracleTrainer(cfg, od, acts, params["wm"], params["actor"], params["critic"], params["target"])
+    data = harness.synthetic_batch(T, B, od, acts, seed=21, done_p=0.1)
+    noise = harness.synthetic_noise(T, B, H, 32, len(acts), seed=22)
+    out = tr.step({k: v.clone() for k, v in data.items()}, noise)
+    ops = CudaOps(DEV, precision="bf16")
+    ops.mirror_check = True
+    eng = engine_from_params(cfg, od, acts, _dev_params(params), ops, DEV)
+    eng.load_batch(_to(data, DEV))
+    eng.load_noise(_to(noise, DEV))
+    forced = dict(post_idx=out["post_idx"].reshape(T * B, -1).int().to(DEV),
+                  imagine=dict(z_idx=out["z_idx"].int().to(DEV), act_idx=out["act_idx"].int().to(DEV)))
+    ops.gemm_log = []
+    eng.step(forced)
+    torch.cuda.synchronize()
+    kernels = [g[-1] for g in ops.gemm_log]
+    ops.gemm_log = None
+    assert kernels.count("tma") > 20, {k: kernels.count(k) for k in set(kernels)}
+    md = eng.metrics_dict()
+    for k in ("Loss/world_model_loss", "Loss/observation_loss", "Loss/reward_loss", "Loss/state_loss", "Loss/continue_loss", "State/kl"):
+        assert abs(md[k] - float(out[k])) <= 2e-2 * max(1.0, abs(float(out[k]))), (k, md[k], float(out[k]))
+    coef = min(1.0, 1000.0 / (float(out["Grads/world_model"]) + 1e-6))
+    worst = max((rel(eng.wm.g[k] * coef, out["world_grads"][k]), k) for k in eng.wm.g)
+    assert worst[0] < 5e-2, worst
