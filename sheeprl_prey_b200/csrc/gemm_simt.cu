@@ -321,9 +321,10 @@ gemm_skinny_splitk_kernel(int M, int N, int K, const float* __restrict__ A, int 
 
 
 // ---- narrow outputs ---------------------------------------------------------------------------------------------------
-// NT with N <= 16 (scalar / few-column heads: continue logit, low-dimensional observation decoder): one warp per row of A,
+// NT with N <= 32 (scalar / few-column heads: continue logit, low-dimensional observation decoder, small action spaces): one warp per row of A,
 // memory-bound on A (read once, coalesced 16 B per lane); the N weight rows stay in L1.
 constexpr int NARROW = 16;
+constexpr int NT_NARROW = 32;   // NT: up to 32 output columns per row (one accumulator each)
 __global__ void __launch_bounds__(256)
 gemm_nt_narrow_kernel(int M, int N, int K, const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
                       float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int vec) {
@@ -331,14 +332,14 @@ gemm_nt_narrow_kernel(int M, int N, int K, const float* __restrict__ A, int lda,
   const size_t row = (size_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= (size_t)M) return;
   const float* a = A + row * lda;
-  float acc[NARROW];
+  float acc[NT_NARROW];
 #pragma unroll
-  for (int n = 0; n < NARROW; ++n) acc[n] = 0.f;
+  for (int n = 0; n < NT_NARROW; ++n) acc[n] = 0.f;
   if (vec) {
     for (int k = lane * 4; k < K; k += 128) {
       const float4 av = __ldg(reinterpret_cast<const float4*>(a + k));
 #pragma unroll
-      for (int n = 0; n < NARROW; ++n) {
+      for (int n = 0; n < NT_NARROW; ++n) {
         if (n < N) {
           const float4 w = __ldg(reinterpret_cast<const float4*>(B + (size_t)n * ldb + k));
           acc[n] = fmaf(av.x, w.x, fmaf(av.y, w.y, fmaf(av.z, w.z, fmaf(av.w, w.w, acc[n]))));
@@ -349,12 +350,12 @@ gemm_nt_narrow_kernel(int M, int N, int K, const float* __restrict__ A, int lda,
     for (int k = lane; k < K; k += 32) {
       const float av = __ldg(a + k);
 #pragma unroll
-      for (int n = 0; n < NARROW; ++n)
+      for (int n = 0; n < NT_NARROW; ++n)
         if (n < N) acc[n] = fmaf(av, __ldg(B + (size_t)n * ldb + k), acc[n]);
     }
   }
 #pragma unroll
-  for (int n = 0; n < NARROW; ++n) {
+  for (int n = 0; n < NT_NARROW; ++n) {
     if (n < N) {
       float v = warp_sum(acc[n]);
       if (lane == 0) {
@@ -436,7 +437,7 @@ extern "C" int dv3_gemm_f32(int mode, int M, int N, int K, const float* A, int l
     DV3_LAUNCH_CHECK();
     return DV3_OK;
   }
-  if (mode == MODE_NT && N <= NARROW && M > 32) {
+  if (mode == MODE_NT && N <= NT_NARROW && M > 32) {
     const int vec = (K & 3) == 0 && (lda & 3) == 0 && (ldb & 3) == 0 && (((uintptr_t)A | (uintptr_t)B) & 15) == 0;
     gemm_nt_narrow_kernel<<<(M + 7) / 8, 256, 0, stream>>>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, vec);
     DV3_LAUNCH_CHECK();

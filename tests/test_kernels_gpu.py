@@ -24,7 +24,7 @@ def rnd(*shape, scale=1.0, seed=None):
 @pytest.mark.parametrize("M,N,K", [(16, 512, 1124), (1, 1024, 256), (8, 100, 40), (32, 1536, 1024), (33, 77, 19),
                                    (1024, 512, 1536), (1024, 255, 512), (1024, 1, 512), (257, 130, 14), (128, 128, 16),
                                    (14, 512, 1024), (512, 14, 1024), (1, 512, 4096), (300, 3, 77), (16384, 1, 512), (1000, 14, 510),
-                                   (16, 16, 15360)])
+                                   (16, 16, 15360), (1024, 18, 640), (1000, 31, 130)])
 def test_gemm(cuda_ops, torch_ops, mode, M, N, K):
     A = rnd(M, K) if mode != "TN" else rnd(K, M)
     B = rnd(N, K) if mode == "NT" else rnd(K, N)
