@@ -86,7 +86,8 @@ __global__ void zero2d_tma_kernel(int M, int N, float* __restrict__ C, int ldc) 
     C[(i / N) * ldc + (i % N)] = 0.f;
 }
 
-template <bool A_MN, bool B_MN>
+// BN = 128, or 64 for contractions with few output tiles (twice as many CTAs share the L2->SM traffic, half the epilogue each)
+template <bool A_MN, bool B_MN, int BN>
 __global__ void __launch_bounds__(NUM_THREADS, 2)
 gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                      float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int kb_per_split) {
@@ -94,13 +95,14 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * STAGE_A_BYTES;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (STAGE_A_BYTES + STAGE_B_BYTES));
+  constexpr int SB_BYTES = BN * TBK * 2;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (STAGE_A_BYTES + SB_BYTES));
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * TBN;
+  const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * BN;
   const int total_kb = (K + TBK - 1) / TBK;
   const int kb0 = blockIdx.z * kb_per_split;
   const int num_kb = min(kb_per_split, total_kb - kb0);
@@ -114,7 +116,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(TMEM_COLS));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(BN));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -130,7 +132,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         const int s = kb % STAGES;
         const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
         mbar_wait(&empty_bar[s], ph ^ 1u);
-        mbar_expect_tx(&full_bar[s], STAGE_A_BYTES + STAGE_B_BYTES);
+        mbar_expect_tx(&full_bar[s], STAGE_A_BYTES + SB_BYTES);
         const int k0 = (kb0 + kb) * TBK;
         if (A_MN) {
           tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], m0, k0);
@@ -139,17 +141,17 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], k0, m0);
         }
         if (B_MN) {
-          tma_load_2d(smem_b + s * STAGE_B_BYTES, &tmB, &full_bar[s], n0, k0);
-          tma_load_2d(smem_b + s * STAGE_B_BYTES + 8192, &tmB, &full_bar[s], n0 + 64, k0);
+          tma_load_2d(smem_b + s * SB_BYTES, &tmB, &full_bar[s], n0, k0);
+          if (BN == 128) tma_load_2d(smem_b + s * SB_BYTES + 8192, &tmB, &full_bar[s], n0 + 64, k0);
         } else {
-          tma_load_2d(smem_b + s * STAGE_B_BYTES, &tmB, &full_bar[s], k0, n0);
+          tma_load_2d(smem_b + s * SB_BYTES, &tmB, &full_bar[s], k0, n0);
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
-                           ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % STAGES;
       const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
@@ -157,7 +159,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       if (lane == 0) {
         const uint32_t a_addr = smem_u32(smem_a + s * STAGE_A_BYTES);
-        const uint32_t b_addr = smem_u32(smem_b + s * STAGE_B_BYTES);
+        const uint32_t b_addr = smem_u32(smem_b + s * SB_BYTES);
 #pragma unroll
         for (int k = 0; k < TBK / 16; ++k) {
           // K-major: 16 bf16 = 32 B along K inside the swizzle atom.  MN-major: 16 k = two 1 KB k-groups.
@@ -186,7 +188,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     const int ew = warp & 3;
     float* stg = reinterpret_cast<float*>(smem) + ew * (32 * 33);
 #pragma unroll 1
-    for (int c0 = 0; c0 < TBN; c0 += 32) {
+    for (int c0 = 0; c0 < BN; c0 += 32) {
       if (n0 + c0 >= N) break;
       uint32_t r[32];
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)c0;
@@ -242,7 +244,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(BN));
   }
 }
 
@@ -438,10 +440,10 @@ EncodeTiledFn g_encode = nullptr;
 
 // K-major operand: [rows, K] bf16, K contiguous, row stride ld -> box 64 (k) x 128 (rows).
 // MN-major operand: [K, rows] bf16, rows contiguous, row stride ld -> box 64 (rows) x 64 (k); two boxes per tile.
-int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld, bool mn_major) {
+int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld, bool mn_major, int box_rows = TBM) {
   const cuuint64_t dims[2] = {(cuuint64_t)(mn_major ? rows : K), (cuuint64_t)(mn_major ? K : rows)};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  const cuuint32_t box[2] = {64, (cuuint32_t)(mn_major ? TBK : TBM)};
+  const cuuint32_t box[2] = {64, (cuuint32_t)(mn_major ? TBK : box_rows)};
   const cuuint32_t estr[2] = {1, 1};
   CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -449,21 +451,21 @@ int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld, bool mn
   return r == CUDA_SUCCESS ? 0 : 1000 + (int)r;
 }
 
-template <bool A_MN, bool B_MN>
-int launch_tma(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc, const float* bias,
+template <bool A_MN, bool B_MN, int BN>
+int launch_tma_bn(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc, const float* bias,
                int accumulate, cudaStream_t stream) {
   static bool configured = false;
   if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<A_MN, B_MN, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
     configured = true;
   }
   CUtensorMap tmA, tmB;
   int rc = make_map(&tmA, A, M, K, lda, A_MN);
   if (rc) return rc;
-  rc = make_map(&tmB, B, N, K, ldb, B_MN);
+  rc = make_map(&tmB, B, N, K, ldb, B_MN, BN);
   if (rc) return rc;
-  dim3 grid((N + TBN - 1) / TBN, (M + TBM - 1) / TBM, 1);
+  dim3 grid((N + BN - 1) / BN, (M + TBM - 1) / TBM, 1);
   if (grid.y > 65535) return DV3_ERR_UNSUPPORTED;
   // split-K when the output has too few tiles to fill the 148 SMs (weight gradients: K = T*B*H rows; small-batch forwards)
   const int total_kb = (K + TBK - 1) / TBK;
@@ -485,10 +487,19 @@ int launch_tma(int M, int N, int K, const void* A, int lda, const void* B, int l
     dv3_launch_pdl(zero2d_tma_kernel, dim3(zb), dim3(256), 0, stream, M, N, C, ldc);
     DV3_LAUNCH_CHECK();
   }
-  dv3_launch_pdl(gemm_bf16_tma_kernel<A_MN, B_MN>, grid, dim3(NUM_THREADS), SMEM_BYTES, stream, tmA, tmB, M, N, K, C, ldc, bias, accumulate,
+  dv3_launch_pdl(gemm_bf16_tma_kernel<A_MN, B_MN, BN>, grid, dim3(NUM_THREADS), SMEM_BYTES, stream, tmA, tmB, M, N, K, C, ldc, bias, accumulate,
                  kb_per_split);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
+}
+
+template <bool A_MN, bool B_MN>
+int launch_tma(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc, const float* bias,
+               int accumulate, cudaStream_t stream) {
+  const int tiles128 = ((N + TBN - 1) / TBN) * ((M + TBM - 1) / TBM);
+  if (tiles128 < 74 && N > 64)      // fewer 128-wide tiles than half the SMs: 64-wide tiles double the CTAs
+    return launch_tma_bn<A_MN, B_MN, 64>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
+  return launch_tma_bn<A_MN, B_MN, 128>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
 }
 
 }  // namespace
