@@ -319,14 +319,25 @@ ln_act_bwd_colsum_kernel(int M, int U, const float* __restrict__ dy, int lddy, c
     }
   }
 }
-__global__ void __launch_bounds__(128) colsum3_stage2_kernel(int U, int nblocks, const float* __restrict__ partial, float* __restrict__ o0,
+// 32 columns x 8 row lanes per block: each lane sums every 8th block partial, then a fixed-order reduction in shared memory
+__global__ void __launch_bounds__(256) colsum3_stage2_kernel(int U, int nblocks, const float* __restrict__ partial, float* __restrict__ o0,
                                                              float* __restrict__ o1, float* __restrict__ o2) {
-  const int u = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+  __shared__ float red[8][33];
+  const int c = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int u = blockIdx.x * 32 + c, k = blockIdx.y;
   float* o = (k == 0) ? o0 : ((k == 1) ? o1 : o2);
-  if (u >= U || !o) return;
+  if (!o) return;
   float s = 0.f;
-  for (int b = 0; b < nblocks; ++b) s += partial[((size_t)b * 3 + k) * U + u];
-  o[u] = s;
+  if (u < U)
+    for (int b = rl; b < nblocks; b += 8) s += partial[((size_t)b * 3 + k) * U + u];
+  red[rl][c] = s;
+  __syncthreads();
+  if (rl == 0 && u < U) {
+    float t = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) t += red[r][c];
+    o[u] = t;
+  }
 }
 
 // MSEDistribution.log_prob (sheeprl/utils/distribution.py:212-221): loss[m] = sum_d (mode - x)^2, dmode = scale*2*(mode-x)
@@ -449,7 +460,7 @@ int dv3_ln_act_bwd_fused(int M, int U, const float* dy, int lddy, const float* x
     ln_act_bwd_colsum_kernel<8><<<nblocks, LW_WARPS * 32, smem, (cudaStream_t)stream>>>(M, U, dy, lddy, x, ldx, gamma, beta, mean, rstd, act, dx, lddx,
                                                                                       reinterpret_cast<__nv_bfloat16*>(dx_bf16), scratch);
   DV3_LAUNCH_CHECK();
-  colsum3_stage2_kernel<<<dim3((U + 127) / 128, 3), 128, 0, (cudaStream_t)stream>>>(U, nblocks, scratch, dgamma, dbeta, dbias);
+  colsum3_stage2_kernel<<<dim3((U + 31) / 32, 3), 256, 0, (cudaStream_t)stream>>>(U, nblocks, scratch, dgamma, dbeta, dbias);
   DV3_LAUNCH_CHECK();
   return DV3_OK;
 }

@@ -497,7 +497,7 @@ template <bool A_MN, bool B_MN>
 int launch_tma(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc, const float* bias,
                int accumulate, cudaStream_t stream) {
   const int tiles128 = ((N + TBN - 1) / TBN) * ((M + TBM - 1) / TBM);
-  if (tiles128 < 74 && N > 64)      // fewer 128-wide tiles than half the SMs: 64-wide tiles double the CTAs
+  if (tiles128 < 74 && N > 64)      // fewer 128-wide tiles than half the SMs: 64-wide tiles double the CTAs (threshold 148: no gain)
     return launch_tma_bn<A_MN, B_MN, 64>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
   return launch_tma_bn<A_MN, B_MN, 128>(M, N, K, A, lda, B, ldb, C, ldc, bias, accumulate, stream);
 }

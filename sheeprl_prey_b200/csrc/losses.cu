@@ -165,14 +165,23 @@ unimix_sample_kernel(int R, int groups, int K, float mix, const float* __restric
       choice = forced[(size_t)row * ldf + g];
     } else {
       Group<KRT> ln, p;
-      normalise_group(lu, ln, p, K, lane);
       const float uu = u[(size_t)row * ldu + g];
-      if (fast && KRT == 1) {
+      if (fast && KRT == 1 && mix > 0.f) {
+        // bf16 precision mode: Categorical(logits = log pm).probs = pm / sum(pm) up to fp32 round-off (the reference renormalises
+        // log(pm) twice) -- far below the bf16 error of the logits -- and a warp prefix sum replaces the sequential cumsum
+        float pc = (lane < K) ? fminf(fmaxf(pm.v[0], DV3_EPS32), 1.f - DV3_EPS32) : 0.f;
+        float cs = pc / warp_sum(pc);
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const float v = __shfl_up_sync(0xffffffffu, cs, o); if (lane >= o) cs += v; }
+        choice = __popc(__ballot_sync(0xffffffffu, lane < K && cs <= uu));
+      } else if (fast && KRT == 1) {
+        normalise_group(lu, ln, p, K, lane);
         float cs = (lane < K) ? p.v[0] : 0.f;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { const float v = __shfl_up_sync(0xffffffffu, cs, o); if (lane >= o) cs += v; }
         choice = __popc(__ballot_sync(0xffffffffu, lane < K && cs <= uu));
       } else {
+        normalise_group(lu, ln, p, K, lane);
         for_k<KRT>(K, lane, [&](int j, int k) { sp[w][k] = p.v[j]; });
         __syncwarp();
         choice = 0;
