@@ -184,6 +184,7 @@ class CudaOps:
             raise RuntimeError("CudaOps needs a CUDA device; sheeprl_prey_b200 has no CPU path")
         self.scratch = torch.empty(scratch_bytes // 4, dtype=torch.float32, device=self.device)
         self.launches = 0   # kernels of ours enqueued so far
+        self.gemm_replay = None   # when a list: (re-issue closure, flops) of every tensor-core contraction (bench roofline)
         self.gemm_log = None   # when a list: (start_event, end_event, flops, M, N, K, mode, kernel) per gemm call (bench / profiling)
         # bf16 mirrors (bf16 precision only): for a registered fp32 buffer, a bf16 buffer with the same element layout.  Producer
         # kernels write both in one pass; contractions whose two operands are mirrored run the TMA-fed kernel on the mirrors.
@@ -287,10 +288,16 @@ class CudaOps:
                 kern = "tma"
                 _chk(self.lib.dv3_gemm_bf16_tma(_MODE[mode], M, N, K, ma, lda, mb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()),
                      "dv3_gemm_bf16_tma")
+                if self.gemm_replay is not None:   # (bench) re-issue exactly this launch later, inside a graph of contractions only
+                    fn, args = self.lib.dv3_gemm_bf16_tma, (_MODE[mode], M, N, K, ma, lda, mb, ldb, pc, ldc, _p(bias), int(accumulate))
+                    self.gemm_replay.append((lambda fn=fn, args=args: fn(*args, self._s()), 2.0 * M * N * K))
             else:
                 kern = "tc"
                 _chk(self.lib.dv3_gemm_bf16_tc(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()),
                      "dv3_gemm_bf16_tc")
+                if self.gemm_replay is not None:
+                    fn, args = self.lib.dv3_gemm_bf16_tc, (_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate))
+                    self.gemm_replay.append((lambda fn=fn, args=args: fn(*args, self._s()), 2.0 * M * N * K))
         else:
             _chk(self.lib.dv3_gemm_f32(_MODE[mode], M, N, K, pa, lda, pb, ldb, pc, ldc, _p(bias), int(accumulate), self._s()), "dv3_gemm_f32")
         if self.gemm_log is not None:
