@@ -262,11 +262,12 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     }
     __syncthreads();
     allgather(x_pr, ld_pr, s0, sper, stage, sld, CL);
-    if (t > 0) fetch_b1(t - 1);
     BDBG(1);
-    cluster.sync();                                                                   // #1
-    BDBG(2);
+    cluster_arrive();                                                                 // #1 (stores / prefetches hide in the barrier)
+    if (t > 0) fetch_b1(t - 1);
     store_saved(a.dpost_raw + row0 * S + s0, m_pr ? m_pr + row0 * S + s0 : nullptr, S, sv_pr, stage, sld, sper, B);
+    cluster_wait();
+    BDBG(2);
 
     // ================= B2: d hid = d post_raw . Wr1 (own columns), LayerNorm + SiLU backward =================
     contract(Wr1T, hper >> 4, h0, hper >> 4, 0, S, x_pr, ld_pr, part, outb);
@@ -281,11 +282,12 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     __syncthreads();
     allgather(x_hp, ld_hp, h0, hper, stage, sld, CL);
     BDBG(5);
-    cluster.sync();                                                                   // #3
-    BDBG(6);
+    cluster_arrive();                                                                 // #3
     store_saved(a.dhidr_pre + row0 * Hh + h0, m_hp ? m_hp + row0 * Hh + h0 : nullptr, Hh, sv_hp, stage, sld, hper, B);
     store_saved(a.dln_r + row0 * Hh + h0, nullptr, Hh, sv_lr, nullptr, 0, hper, B);
     if (t > 0) fetch_b2(t - 1);
+    cluster_wait();
+    BDBG(6);
 
     // ================= B3: dh_t += d hidr_pre . Wr0[:, :D] (own units), GRU gate backward =================
     contract(Wr0hT, dper >> 4, d0, dper >> 4, 0, Hh, x_hp, ld_hp, part, outb);
@@ -320,14 +322,15 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     __syncthreads();
     for (int gate = 0; gate < 3; ++gate) allgather(x_gp, ld_gp, gate * D + d0, dper, stage + gate * dper, sld, CL);
     BDBG(9);
-    cluster.sync();                                                                   // #5
-    BDBG(10);
+    cluster_arrive();                                                                 // #5
     for (int gate = 0; gate < 3; ++gate) {
       store_saved(a.dgates_pre + row0 * D3 + gate * D + d0, m_gp ? m_gp + row0 * D3 + gate * D + d0 : nullptr, D3,
                   sv_gp + gate * MB * dper, stage + gate * dper, sld, dper, B);
       store_saved(a.dln_gru + row0 * D3 + gate * D + d0, nullptr, D3, sv_lg + gate * MB * dper, nullptr, 0, dper, B);
     }
     if (t > 0) fetch_b3(t - 1);
+    cluster_wait();
+    BDBG(10);
 
     // ================= B4: [dh_{t-1} part | d feat] = d gates_pre . Wgru (own columns), LayerNorm + SiLU backward =================
     contract(WgruT, (dper + uper) >> 4, d0, dper >> 4, D + u0 - d0, D3, x_gp, ld_gp, part, outb);   // dper == uper
@@ -344,11 +347,12 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_bwd_cluster_kernel(const _
     __syncthreads();
     allgather(x_fp, ld_fp, u0, uper, stage, sld, CL);
     BDBG(13);
-    cluster.sync();                                                                   // #7
-    BDBG(14);
+    cluster_arrive();                                                                 // #7
     store_saved(a.dfeat_pre + row0 * U + u0, m_fp ? m_fp + row0 * U + u0 : nullptr, U, sv_fp, stage, sld, uper, B);
     store_saved(a.dln_feat + row0 * U + u0, nullptr, U, sv_lf, nullptr, 0, uper, B);
     if (t > 0) fetch_b4(t - 1);
+    cluster_wait();
+    BDBG(14);
 
     // ================= B5: dz_{t-1} = d feat_pre . Wmlp[:, :S] (own categoricals); carry through the reset mask =================
     contract(WmlpzT, sper >> 4, s0, sper >> 4, 0, U, x_fp, ld_fp, part, outb);

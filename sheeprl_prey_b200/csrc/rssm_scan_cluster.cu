@@ -138,7 +138,6 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
   for (int t = 0; t < a.T; ++t) {
     const int row0 = t * B;
     SDBG(0);
-    if (t > 0) flush_posterior(row0 - B);
     // ================= P0: reset masking (agent.py:379-384), saved inputs of the step =================
     const int* rs_t = s_first + t * MB;
     cp_async_wait_all();
@@ -181,26 +180,35 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
     ln_push(outb, uper, lnp, c, CL);
     SDBG(2);
     SDBG(11);
-    cluster.sync();                                                                   // #1
+    cluster_arrive();                                                                 // #1
+    store_cols(a.feat_pre + (size_t)row0 * U + u0, U, outb, uper, B);
+    cluster_wait();
     SDBG(12);
     ln_combine(lnp, CL, uper, 1e-3f, s_stat, a.feat_mean + row0, a.feat_rstd + row0, c == 0, B);
-    store_cols(a.feat_pre + (size_t)row0 * U + u0, U, outb, uper, B);
     ln_silu_slice(outb, uper, s_stat, p_mlp, dfr, stage, sld);
     __syncthreads();
     allgather(xg, ldxg, D + u0, uper, stage, sld, CL);
-    if (t + 1 < a.T) fetch_aw(t + 1);
     SDBG(3);
     SDBG(13);
-    cluster.sync();                                                                   // #2
-    SDBG(14);
+    cluster_arrive();                                                                 // #2
+    if (t + 1 < a.T) fetch_aw(t + 1);
     store_rows(a.x_gru + (size_t)row0 * a.ld_xgru + D + u0, a.ld_xgru, dfr, sld, uper, B);
+    cluster_wait();
+    SDBG(14);
 
     // ================= P2: GRU gates: own rows {d, D+d, 2D+d} of Wgru . [h, feat] =================
     contract(k.Wgru_pk, nt_g, d0, tg, D, KG, xg, ldxg, part, outb);      // outb row = gate * dper + dl
     SDBG(4);
     ln_push(outb, 3 * dper, lnp, c, CL);
     SDBG(15);
-    cluster.sync();                                                                   // #3
+    cluster_arrive();                                                                 // #3
+#pragma unroll 1
+    for (int e = tid; e < B * dper; e += CT) {                // saved pre-LN gates (own rows of the three gates)
+      const int m = e >> lg_d, dl = e & (dper - 1);
+      float* gp = a.gates_pre + (size_t)(row0 + m) * 3 * D + d0 + dl;
+      gp[0] = outb[dl * OB + m]; gp[D] = outb[(dper + dl) * OB + m]; gp[2 * D] = outb[(2 * dper + dl) * OB + m];
+    }
+    cluster_wait();
     SDBG(16);
     ln_combine(lnp, CL, 3 * dper, 1e-5f, s_stat, a.gru_mean + row0, a.gru_rstd + row0, c == 0, B);
 #pragma unroll 1
@@ -208,10 +216,6 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
       const int m = e >> lg_d, dl = e & (dper - 1);
       const float mu = s_stat[m], rs = s_stat[MB + m];
       const float g0v = outb[dl * OB + m], g1v = outb[(dper + dl) * OB + m], g2v = outb[(2 * dper + dl) * OB + m];
-      if (m < B) {
-        float* gp = a.gates_pre + (size_t)(row0 + m) * 3 * D + d0 + dl;
-        gp[0] = g0v; gp[D] = g1v; gp[2 * D] = g2v;
-      }
       const float r = sigmoidf_((g0v - mu) * rs * p_gru[dl] + p_gru[3 * dper + dl]);
       const float cp = (g1v - mu) * rs * p_gru[dper + dl] + p_gru[4 * dper + dl];
       const float cd = tanhf(r * cp);
@@ -224,9 +228,10 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
     allgather(xg, ldxg, d0, dper, stage, sld, CL);
     SDBG(5);
     SDBG(17);
-    cluster.sync();                                                                   // #4
-    SDBG(18);
+    cluster_arrive();                                                                 // #4
     store_rows(a.x_rep + (size_t)row0 * a.ld_xrep + d0, a.ld_xrep, hown, dper, dper, B);
+    cluster_wait();
+    SDBG(18);
 
     // ================= P3: posterior hidden: own rows of Wr0[:, :D] . h' + (e_t . Wr0[:, D:]^T + b) =================
     contract(k.Wr0_pk, nt_h, h0, nt_h, 0, D, xg, ldxg, part, outb);
@@ -234,21 +239,23 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
     for (int e = tid; e < B * hper; e += CT) { const int m = e >> lg_h, hl = e & (hper - 1); outb[hl * OB + m] += s_ew[e]; }
     __syncthreads();
     ln_push(outb, hper, lnp, c, CL);
-    if (t + 1 < a.T) fetch_ew(t + 1);
     SDBG(6);
     SDBG(19);
-    cluster.sync();                                                                   // #5
+    cluster_arrive();                                                                 // #5
+    if (t + 1 < a.T) fetch_ew(t + 1);
+    store_cols(a.hidr_pre + (size_t)row0 * Hh + h0, Hh, outb, hper, B);
+    cluster_wait();
     SDBG(20);
     ln_combine(lnp, CL, hper, 1e-5f, s_stat, a.hidr_mean + row0, a.hidr_rstd + row0, c == 0, B);
-    store_cols(a.hidr_pre + (size_t)row0 * Hh + h0, Hh, outb, hper, B);
     ln_silu_slice(outb, hper, s_stat, p_r, dfr, stage, sld);
     __syncthreads();
     allgather(hid, ldh, h0, hper, stage, sld, CL);
     SDBG(7);
     SDBG(21);
-    cluster.sync();                                                                   // #6
-    SDBG(22);
+    cluster_arrive();                                                                 // #6
     store_rows(a.hidr + (size_t)row0 * Hh + h0, Hh, dfr, sld, hper, B);
+    cluster_wait();
+    SDBG(22);
 
     // ================= P4: posterior logits of the own categoricals, unimix, inverse-CDF sample =================
     contract(k.Wr1_pk, nt_s, s0, nt_s, 0, Hh, hid, ldh, part, outb);
@@ -290,14 +297,15 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
       if (lane < CL) cluster.map_shared_rank(idxf, lane)[m * G + g] = choice;
     }
     __syncthreads();
-    if (t + 1 < a.T) fetch_uu(t + 1);
     SDBG(9);
     SDBG(23);
-    cluster.sync();                                                                   // #7
+    cluster_arrive();                                                                 // #7
+    if (t + 1 < a.T) fetch_uu(t + 1);
+    flush_posterior(row0);
+    cluster_wait();
     SDBG(24);
     SDBG(10);
   }
-  flush_posterior((a.T - 1) * B);
 }
 
 int launch_cluster(KArgs& k, int CL, size_t smem_bytes, cudaStream_t stream, bool probe_only) {

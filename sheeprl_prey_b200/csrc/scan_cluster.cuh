@@ -40,6 +40,12 @@ __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// Cluster barrier in two halves: between the arrive (release: own DSMEM pushes are ordered before it) and the wait (acquire) a CTA
+// does work that needs nothing from its peers -- the global stores of activations it already holds, cp.async prefetches -- so that
+// this work hides in the barrier's latency (~1.4 k clk here) instead of following it.
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
 // Contraction of `ntiles` tiles of 16 weight rows with X[MB][K] (bf16, shared memory, row stride ldx):
 //   outb[(ti * 16 + r) * OB + m] = sum_k W[tile_row(ti) + r, k] * X[m, k],  tile_row(ti) = row_base + (ti / tpb) * blk_stride + (ti % tpb) * 16
 // W is PACKED in MMA-fragment order by dv3_pack_mma_a (see rssm_scan_cluster.cu): for every (16-row tile, 32-wide k chunk) the 32
