@@ -35,6 +35,7 @@ struct KArgs {
   const float* aW;              // [T*B, U] fp32 = masked action . Wmlp[:, S:]^T
   long long* dbg;
   int CL;
+  int w_resident;               // Wr0 / Wr1 tiles of the CTA fit in shared memory next to the working set
 };
 
 #define SDBG(p) do { if (k.dbg && c == 0 && tid == 0 && t == 1) k.dbg[p] = clock64(); } while (0)
@@ -82,6 +83,15 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
   float* s_aw = reinterpret_cast<float*>(take((size_t)MB * uper * 4));                 // cp.async landing zones (next step's inputs)
   float* s_ew = reinterpret_cast<float*>(take((size_t)MB * hper * 4));
   float* s_uu = reinterpret_cast<float*>(take((size_t)MB * gper * 4));                 // uniforms (or forced indices, as int bits)
+  // resident weights (k.w_resident): this CTA's packed tiles of Wr0[:, :D] and Wr1 stay in shared memory for all T steps
+  uint4* w_r0_s = k.w_resident ? reinterpret_cast<uint4*>(take((size_t)nt_h * (D >> 5) * 1024)) : nullptr;
+  uint4* w_r1_s = k.w_resident ? reinterpret_cast<uint4*>(take((size_t)nt_s * (Hh >> 5) * 1024)) : nullptr;
+  if (k.w_resident) {
+    const uint4* g0p = k.Wr0_pk + (size_t)(h0 >> 4) * (D >> 5) * 64;
+    for (int i = tid; i < nt_h * (D >> 5) * 64; i += CT) w_r0_s[i] = __ldg(g0p + i);
+    const uint4* g1p = k.Wr1_pk + (size_t)(s0 >> 4) * (Hh >> 5) * 64;
+    for (int i = tid; i < nt_s * (Hh >> 5) * 64; i += CT) w_r1_s[i] = __ldg(g1p + i);
+  }
 
   for (int i = tid; i < MB * ldxg / 2; i += CT) reinterpret_cast<uint32_t*>(xg)[i] = 0u;
   for (int i = tid; i < MB * ldh / 2; i += CT) reinterpret_cast<uint32_t*>(hid)[i] = 0u;
@@ -234,7 +244,8 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
     SDBG(18);
 
     // ================= P3: posterior hidden: own rows of Wr0[:, :D] . h' + (e_t . Wr0[:, D:]^T + b) =================
-    contract(k.Wr0_pk, nt_h, h0, nt_h, 0, D, xg, ldxg, part, outb);
+    if (k.w_resident) contract_t<true>(w_r0_s, nt_h, 0, nt_h, 0, D, xg, ldxg, part, outb);
+    else contract(k.Wr0_pk, nt_h, h0, nt_h, 0, D, xg, ldxg, part, outb);
 #pragma unroll 1
     for (int e = tid; e < B * hper; e += CT) { const int m = e >> lg_h, hl = e & (hper - 1); outb[hl * OB + m] += s_ew[e]; }
     __syncthreads();
@@ -258,7 +269,8 @@ __global__ void __launch_bounds__(CT, 1) rssm_observe_fwd_cluster_kernel(const _
     SDBG(22);
 
     // ================= P4: posterior logits of the own categoricals, unimix, inverse-CDF sample =================
-    contract(k.Wr1_pk, nt_s, s0, nt_s, 0, Hh, hid, ldh, part, outb);
+    if (k.w_resident) contract_t<true>(w_r1_s, nt_s, 0, nt_s, 0, Hh, hid, ldh, part, outb);
+    else contract(k.Wr1_pk, nt_s, s0, nt_s, 0, Hh, hid, ldh, part, outb);
     SDBG(8);
 #pragma unroll 1
     for (int p = warp; p < npairs; p += CW) {                // one warp per (batch row, own categorical); lane = class (Kc <= 32)
@@ -363,6 +375,11 @@ bool shape_ok(const Dv3ScanFwdArgs* h, int CL, size_t* smem_bytes, int max_smem)
   *smem_bytes = b + 16;
   return (long long)*smem_bytes <= (long long)max_smem;
 }
+// extra shared memory for the resident Wr0 / Wr1 tiles of one CTA
+size_t resident_bytes(const Dv3ScanFwdArgs* h, int CL) {
+  const int hper = h->Hh / CL, sper = (h->G / CL) * h->Kc;
+  return (size_t)(hper >> 4) * (h->D >> 5) * 1024 + (size_t)(sper >> 4) * (h->Hh >> 5) * 1024 + 32;
+}
 
 }  // namespace
 
@@ -393,6 +410,9 @@ extern "C" int dv3_rssm_observe_fwd_cluster(const Dv3ScanFwdArgs* h, const Dv3Sc
   size_t smem = 0;
   for (int CL = 16; CL >= 8; CL >>= 1) {
     if (CL > want || !shape_ok(h, CL, &smem, max_smem)) continue;
+    k.w_resident = 0;
+    if (!getenv("DV3_SCAN_NO_RESIDENT") && smem + resident_bytes(h, CL) <= (size_t)max_smem) { k.w_resident = 1; smem += resident_bytes(h, CL); }
+    if (getenv("DV3_SCAN_DEBUG")) fprintf(stderr, "[dv3 cluster scan] CL=%d smem=%zu KB resident=%d (max %d KB)\n", CL, smem / 1024, k.w_resident, max_smem / 1024);
     if (launch_cluster(k, CL, smem, (cudaStream_t)stream_, true) != DV3_OK) continue;
     return launch_cluster(k, CL, smem, (cudaStream_t)stream_, false);
   }

@@ -55,8 +55,10 @@ __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.w
 // the permutation is consistent and the sum is unchanged.
 // Work unit = (tile, k-part): ksplit = CW / gcd(ntiles, CW) so that the units divide evenly over the CW warps.  Partial sums go
 // through part[tile][kq][16][MB] and are added in a fixed order (deterministic).
-static __device__ __noinline__ void contract(const uint4* __restrict__ Wp, int ntiles, int row_base, int tpb, int blk_stride, int K,
-                                             const __nv_bfloat16* X, int ldx, float* part, float* outb) {
+// WSMEM: the packed tiles were copied into shared memory once (weights resident for the whole scan): plain loads instead of LDG.
+template <bool WSMEM>
+static __device__ __noinline__ void contract_t(const uint4* __restrict__ Wp, int ntiles, int row_base, int tpb, int blk_stride, int K,
+                                               const __nv_bfloat16* X, int ldx, float* part, float* outb) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, gid = lane >> 2, tig = lane & 3;
   const int ksplit = ksplit_of(ntiles), ks_shift = 31 - __clz(ksplit);
   const int upw = (ntiles * ksplit) / CW, nch = K >> 5, lg_tpb = 31 - __clz(tpb);
@@ -73,7 +75,7 @@ static __device__ __noinline__ void contract(const uint4* __restrict__ Wp, int n
     float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll 4
     for (int ch = ch0; ch < ch1; ++ch) {
-      const uint4 w1 = __ldg(wp), w2 = __ldg(wp + 1);
+      const uint4 w1 = WSMEM ? wp[0] : __ldg(wp), w2 = WSMEM ? wp[1] : __ldg(wp + 1);
       const uint4 va = *reinterpret_cast<const uint4*>(xa);
       const uint4 vb = *reinterpret_cast<const uint4*>(xb);
       mma_bf16(acc[0], w1.x, w1.y, w1.z, w1.w, va.x, va.y);
@@ -101,6 +103,11 @@ static __device__ __noinline__ void contract(const uint4* __restrict__ Wp, int n
     outb[(size_t)(tile * 16 + (e >> 4)) * OB + (e & 15)] = s;
   }
   __syncthreads();
+}
+
+static __device__ __forceinline__ void contract(const uint4* Wp, int ntiles, int row_base, int tpb, int blk_stride, int K,
+                                                const __nv_bfloat16* X, int ldx, float* part, float* outb) {
+  contract_t<false>(Wp, ntiles, row_base, tpb, blk_stride, K, X, ldx, part, outb);
 }
 
 // LayerNorm statistics of a vector spread over the cluster.  Own values of batch row m: vals[j * OB + m], j < n.  Every CTA pushes
