@@ -199,6 +199,11 @@ class DV3Engine:
         a, w = cfg.algo, cfg.algo.world_model
         self.cfg, self.ops, self.device, self.dist = cfg, ops, device, dist
         self.wm, self.actor, self.critic, self.target = wm, actor, critic, target
+        # first offset of the parameters whose gradients are complete before the reverse scan (heads at the tail of the arena)
+        tail = [o for k, (o, n, shp) in wm.offsets.items() if k.startswith(("observation_model.", "reward_model.", "continue_model."))]
+        head_max = max([o + n for k, (o, n, shp) in wm.offsets.items()
+                        if not k.startswith(("observation_model.", "reward_model.", "continue_model."))] or [0])
+        self.wm_tail_from = min(tail) if tail and min(tail) >= head_max else 0
         self.keys = list(cfg.mlp_keys.encoder)
         self.cnn_keys = list(cfg.cnn_keys.encoder)
         if list(cfg.cnn_keys.decoder) != self.cnn_keys or list(cfg.mlp_keys.decoder) != self.keys:
@@ -482,6 +487,13 @@ class DV3Engine:
         ops.unimix_bwd(self.trans.out, G, K, mix, self.dprior_logits, None, self.dprior_logits)
         _refresh(ops, self.dprior_logits)
         self.trans.backward(self.x_rep[:, :D], N, self.dprior_logits, dx=self.dlatent[:, S:], dx_accumulate=True)
+        # a15: the gradients of the decoder / reward / continue heads (the tail of the flat arena) are final here: their all-reduce
+        # runs on the communication stream while the reverse scan (16 SMs) and the remaining weight gradients are computed
+        self._wm_pending, self._wm_done_from = None, -1
+        if self.dist is not None and self.wm_tail_from > 0:
+            h = self._start_reduce(self.wm.grad[self.wm_tail_from:])
+            if h is not None:
+                self._wm_pending, self._wm_done_from = [h], self.wm_tail_from
         # reverse scan: only dh / dz propagate sequentially -- one cluster kernel when available, else the per-step composition
         fused_bwd = False
         if self.use_fused_bwd and hasattr(ops, "rssm_observe_bwd"):
@@ -531,10 +543,24 @@ class DV3Engine:
         if self.enc is not None:
             self.enc.backward(self.obs_sym, N, self.de[:, self.cnn_out:])
 
-    def _optimize(self, arena: Arena, tag: str, max_norm: float, slot: str) -> None:
-        """a7 / a15: gradient all-reduce (data parallel), global-norm clip, Adam."""
+    def _start_reduce(self, grad: Tensor):
+        """a15: launch the data-parallel mean of a (slice of a) flat gradient arena; None when there is nothing to do."""
+        if self.dist is None or not hasattr(self.dist, "start_reduce_mean"):
+            return None
+        return self.dist.start_reduce_mean(grad)
+
+    def _optimize(self, arena: Arena, tag: str, max_norm: float, slot: str, pending=None, done_from: int = -1) -> None:
+        """a7 / a15: gradient all-reduce (data parallel), global-norm clip, Adam.  `pending`: handles of reductions started earlier
+        (overlapped with independent kernels); `done_from` >= 0: arena.grad[done_from:] is covered by them, only the head is
+        reduced here."""
         if self.dist is not None:
-            self.dist.all_reduce_mean(arena.grad)
+            if pending is None:
+                self.dist.all_reduce_mean(arena.grad)
+            else:
+                if done_from > 0:
+                    self.dist.all_reduce_mean(arena.grad[:done_from])
+                for h in pending:
+                    self.dist.finish_reduce(h)
         hp = self.opt_hparams[tag]
         self.ops.adam_clip(arena.flat, arena.grad, arena.m, arena.v, arena.step, hp["lr"], hp["beta1"], hp["beta2"], hp["eps"],
                            max_norm, self.metrics, _SLOT[slot])
@@ -606,7 +632,9 @@ class DV3Engine:
         ops.reduce_mean(self.pl_rows, 0, self.metrics, _SLOT["Loss/policy_loss"], 1.0 / M0, False)
         _refresh(ops, self.d_actor_raw)
         self.act_stack.backward(self.traj, M0, self.d_actor_raw)
-        self._optimize(self.actor, "actor", a.actor.clip_gradients, "Grads/actor")
+        h_actor = self._start_reduce(self.actor.grad)          # overlaps the critic's loss / backward below (independent of the actor update)
+        if h_actor is None:
+            self._optimize(self.actor, "actor", a.actor.clip_gradients, "Grads/actor")
         # a13: critic loss (activations of the value pass above; target critic forward)
         self.tcrit_stack.forward(self.traj[:M0])
         ops.twohot_mean(self.tcrit_stack.out, self.tvalues)
@@ -615,7 +643,12 @@ class DV3Engine:
         ops.reduce_mean(self.vl_rows, 0, self.metrics, _SLOT["Loss/value_loss"], 1.0 / M0, False)
         _refresh(ops, self.d_crit)
         self.crit_stack.backward(self.traj, M0, self.d_crit)
-        self._optimize(self.critic, "critic", a.critic.clip_gradients, "Grads/critic")
+        if h_actor is not None:
+            h_critic = self._start_reduce(self.critic.grad)
+            self._optimize(self.actor, "actor", a.actor.clip_gradients, "Grads/actor", pending=[h_actor])
+            self._optimize(self.critic, "critic", a.critic.clip_gradients, "Grads/critic", pending=[h_critic])
+        else:
+            self._optimize(self.critic, "critic", a.critic.clip_gradients, "Grads/critic")
 
     # ------------------------------------------------------------------ whole step
     def step(self, forced: Optional[dict] = None) -> None:
@@ -625,7 +658,8 @@ class DV3Engine:
         self.world_forward(None if forced is None else forced.get("post_idx"))
         self.world_losses()
         self.world_backward()
-        self._optimize(self.wm, "world", w.clip_gradients, "Grads/world_model")
+        self._optimize(self.wm, "world", w.clip_gradients, "Grads/world_model", pending=getattr(self, "_wm_pending", None),
+                       done_from=getattr(self, "_wm_done_from", -1))
         self.imagine(None if forced is None else forced.get("imagine"))
         self.behaviour()
 
@@ -646,7 +680,8 @@ class DV3Engine:
         mark("world_losses")
         self.world_backward()
         mark("world_backward (heads, prior head, reverse scan, weight grads, encoder)")
-        self._optimize(self.wm, "world", w.clip_gradients, "Grads/world_model")
+        self._optimize(self.wm, "world", w.clip_gradients, "Grads/world_model", pending=getattr(self, "_wm_pending", None),
+                       done_from=getattr(self, "_wm_done_from", -1))
         mark("world clip+Adam")
         self.imagine()
         mark("imagination rollout (H steps x [GRU, prior, sample, actor])")

@@ -21,5 +21,19 @@ class TorchDist:
             dist.all_reduce(t, op=dist.ReduceOp.SUM)
             t.div_(self.world_size)
 
+    def start_reduce_mean(self, t: torch.Tensor):
+        """Asynchronous all_reduce_mean: the collective runs on the process group's stream while the caller keeps enqueueing
+        independent work; finish_reduce(handle) orders the caller's stream after it (inside a CUDA graph capture this becomes a
+        fork / join of the graph)."""
+        if dist.get_backend() == "nccl":
+            return (dist.all_reduce(t, op=dist.ReduceOp.AVG, async_op=True), None)
+        return (dist.all_reduce(t, op=dist.ReduceOp.SUM, async_op=True), t)
+
+    def finish_reduce(self, handle) -> None:
+        work, t = handle
+        work.wait()
+        if t is not None:
+            t.div_(self.world_size)
+
     def all_gather(self, src: torch.Tensor, dst: torch.Tensor) -> None:
         dist.all_gather_into_tensor(dst, src)
