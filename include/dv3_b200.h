@@ -170,6 +170,22 @@ typedef struct Dv3ScanClusterExtra {
   const float* aW;                      /* [T*B, U] fp32 */
 } Dv3ScanClusterExtra;
 int dv3_rssm_observe_fwd_cluster(const Dv3ScanFwdArgs* args, const Dv3ScanClusterExtra* extra, void* stream);
+/* The same scan with tcgen05 tensor cores (rssm_scan_tc.cu): per 16 batch rows one thread-block cluster (16 CTAs, else 8) whose
+ * CTAs each own 1/CL of every feature dimension.  Weight rows are the M = 128 operand of tcgen05.mma (batch rows = N = 16, fp32
+ * accumulate in TMEM), streamed by cp.async.bulk through an mbarrier ring from a per-CTA, per-step bf16 stream that
+ * dv3_scan_tc_fwd_pack lays out in consumption order; activations, LayerNorm partials and sampled indices cross the cluster as
+ * bulk copies / st.async that complete on the receiver's mbarrier (no cluster barriers).  Any B (one cluster per 16 rows), per-CTA
+ * slices need not be powers of two.  dv3_scan_tc_fwd_config: cluster size and stream size (bytes) for a shape, DV3_ERR_UNSUPPORTED
+ * when the shape does not divide.  Replaces the same reference loop as dv3_rssm_observe_fwd (dreamer_v3.py:122-129). */
+typedef struct Dv3ScanTcExtra {
+  const void* stream;                   /* dv3_scan_tc_fwd_pack output */
+  const float* WmlpzT;                  /* [G*Kc, U] fp32 = Wmlp[:, :G*Kc]^T */
+  const float* aW;                      /* [T*B, U] fp32 = masked action . Wmlp[:, G*Kc:]^T */
+} Dv3ScanTcExtra;
+int dv3_scan_tc_fwd_config(int D, int U, int Hh, int G, int Kc, int* cluster_size, size_t* stream_bytes);
+int dv3_scan_tc_fwd_pack(int D, int U, int Hh, int G, int Kc, const float* Wgru, int ld_wgru, const float* Wr0, int ld_wr0,
+                         const float* Wr1, int ld_wr1, void* dst, void* stream);
+int dv3_rssm_observe_fwd_tc(const Dv3ScanFwdArgs* args, const Dv3ScanTcExtra* extra, void* stream);
 /* Weight matrix -> bf16 in mma.sync.m16n8k16 A-fragment order (the operand layout of the two cluster scan kernels): element
  * (row, k) is src[row * stride_r + k * stride_k], R % 16 == 0, K % 32 == 0; dst holds R*K bf16. */
 int dv3_pack_mma_a(int R, int K, const float* src, long long stride_r, long long stride_k, void* dst_bf16, void* stream);

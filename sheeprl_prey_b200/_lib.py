@@ -48,6 +48,9 @@ SIGNATURES = {
     "dv3_rssm_observe_fwd": [c_fp, c_fp],
     "dv3_rssm_observe_fwd_cluster": [c_fp, c_fp, c_fp],
     "dv3_rssm_observe_bwd_cluster": [c_fp, c_fp],
+    "dv3_scan_tc_fwd_config": [_i, _i, _i, _i, _i, c_fp, c_fp],
+    "dv3_scan_tc_fwd_pack": [_i, _i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
+    "dv3_rssm_observe_fwd_tc": [c_fp, c_fp, c_fp],
     "dv3_pack_mma_a": [_i, _i, c_fp, _ll, _ll, c_fp, c_fp],
     "dv3_ln_act_fwd_rows_gather": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, _i, c_fp, c_fp],
     "dv3_ln_act_bwd_fused": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
@@ -102,6 +105,11 @@ class ScanFwdArgs(C.Structure):
 class ScanClusterExtra(C.Structure):
     """Mirror of `Dv3ScanClusterExtra` (include/dv3_b200.h)."""
     _fields_ = [("Wgru_pk", c_fp), ("Wr0_pk", c_fp), ("Wr1_pk", c_fp), ("WmlpzT", c_fp), ("aW", c_fp)]
+
+
+class ScanTcExtra(C.Structure):
+    """Mirror of `Dv3ScanTcExtra` (include/dv3_b200.h)."""
+    _fields_ = [("stream", c_fp), ("WmlpzT", c_fp), ("aW", c_fp)]
 
 
 class ScanBwdArgs(C.Structure):
@@ -191,6 +199,7 @@ class CudaOps:
         self.use_mirrors = self.precision == "bf16" and os.environ.get("DV3_BF16_RESIDENT", "1") != "0"
         self.mirror_check = os.environ.get("DV3_MIRROR_CHECK", "0") == "1"
         self.use_cluster_scan = os.environ.get("DV3_CLUSTER_SCAN", "1") != "0"
+        self.use_tc_scan = os.environ.get("DV3_TC_SCAN", "1") != "0"      # tcgen05 scan kernels (rssm_scan_tc.cu), tried first
         # Linear+LayerNorm+SiLU in one clustered kernel (dv3_gemm_ln_bf16_tma): correct (tests) but its epilogue -- one thread per row
         # for three TMEM sweeps and 128 SiLUs -- is slower than the separate warp-per-row LayerNorm: 117 vs 130 steps/s.  Opt-in.
         self.use_gemm_ln = os.environ.get("DV3_GEMM_LN", "0") == "1"
@@ -602,6 +611,22 @@ class CudaOps:
         a.post_raw, a.post_logits, a.post_idx = _p(eng.post_raw), _p(eng.post_logits), _p(eng.post_idx)
         a.latent, a.ld_lat = _p(eng.latent), eng.latent.stride(0)
         a.scratch, a.scratch_bytes = self.scratch.data_ptr(), self.scratch.numel() * 4
+        if self.use_mirrors and self.use_tc_scan and getattr(eng, "aW", None) is not None:
+            # tcgen05 swap-AB contractions, bulk-copy weight ring, mbarrier exchange across one cluster per 16 batch rows
+            stream = self._tc_stream(eng, "fwd")
+            if stream is not None:
+                x = ScanTcExtra()
+                x.stream, x.WmlpzT, x.aW = stream, _p(eng.W_mlpzT), _p(eng.aW)
+                rc = self.lib.dv3_rssm_observe_fwd_tc(C.addressof(a), C.addressof(x), self._s())
+                if rc == 0:
+                    self.launches += 1
+                    self.scan_kernel = "tcgen05"
+                    return True
+                if rc != -2:
+                    _chk(rc, "dv3_rssm_observe_fwd_tc")
+            self.use_tc_scan = False
+        if eng.B > 16:
+            return False
         if self.use_mirrors and self.use_cluster_scan and getattr(eng, "aW", None) is not None:
             # one thread-block cluster, bf16 weights streamed into mma.sync fragments, DSMEM exchange (rssm_scan_cluster.cu)
             x = ScanClusterExtra()
@@ -626,6 +651,23 @@ class CudaOps:
         _chk(rc, "dv3_rssm_observe_fwd")
         self.launches += 1
         return True
+
+    def _tc_stream(self, eng, which):
+        """Per-CTA, per-step bf16 weight stream of the tcgen05 scan (created on first use, refilled every step: the weights change
+        with every Adam step).  None when the shape is outside the kernel's plan."""
+        pk = eng.__dict__.setdefault("_packed", {})
+        key = "tc_" + which
+        if key not in pk:
+            cl, nbytes = C.c_int(0), C.c_size_t(0)
+            rc = self.lib.dv3_scan_tc_fwd_config(eng.D, eng.U, eng.Hh, eng.G, eng.K, C.addressof(cl), C.addressof(nbytes))
+            pk[key] = None if rc != 0 else torch.empty(nbytes.value, dtype=torch.uint8, device=self.device)
+        buf = pk[key]
+        if buf is None:
+            return None
+        self.launches += 1
+        _chk(self.lib.dv3_scan_tc_fwd_pack(eng.D, eng.U, eng.Hh, eng.G, eng.K, _p(eng.Wgru), eng.Wgru.stride(0), _p(eng.Wr0), eng.Wr0.stride(0),
+                                           _p(eng.Wr1), eng.Wr1.stride(0), buf.data_ptr(), self._s()), "dv3_scan_tc_fwd_pack")
+        return buf.data_ptr()
 
     def _pack(self, eng, name, R, K, W, stride_r, stride_k):
         """bf16 copy of a weight matrix (or its transpose: swap the strides) in mma.sync A-fragment order for the cluster scan

@@ -1,0 +1,598 @@
+// RSSM observe scan (forward) with tcgen05 tensor cores: the whole loop dreamer_v3.py:122-129 over RSSM.dynamic (agent.py:350-388)
+// -- RecurrentModel (agent.py:296-309), LayerNormGRUCell (models/models.py:388-395), _representation (agent.py:404-420), unimix +
+// straight-through one-hot sampling -- as ONE kernel for all T steps.  Machinery: scan_tc.cuh.
+//
+// Per step (own = this CTA's 1/CL slice of every feature dimension), contractions in the order the MMA warp issues them:
+//   gh(t)  gates  += Wgru[own rows, :D]  . h_{t-1}      issued as soon as h_{t-1} has arrived (overlaps the posterior of step t-1)
+//   P1     feat    = SiLU(LN(gather of Wmlp[:, :S]^T rows by the one-hot z_{t-1} + hoisted action projection))      (epilogue only)
+//   gf(t)  gates  += Wgru[own rows, D:]  . feat         -> LN over 3D (stats exchange) -> GRU gates -> h_t  (exchange)
+//   r0(t)  hid     = Wr0[own rows, :D]   . h_t + (e_t . Wr0[:, D:]^T + b)  -> LN (stats exchange) -> SiLU   (exchange)
+//   r1(t)  logits  = Wr1[own rows]       . hid + b      -> unimix, inverse-CDF sample of the own categoricals (index exchange)
+// Everything the hand-written backward needs is written to the same fp32 buffers as by the per-op path.
+#include "scan_tc.cuh"
+#include "dv3_b200.h"
+#include <stdio.h>
+#include <stdlib.h>
+
+namespace {
+using namespace tcs;
+
+enum { SEG_GH = 0, SEG_GF = 1, SEG_R0 = 2, SEG_R1 = 3 };
+enum { X_FEAT = 0, X_H = 1, X_HID = 2 };            // activation exchanges (consumed by the MMA warp)
+enum { ST_FEAT = 0, ST_GRU = 1, ST_HID = 2 };        // LayerNorm-partial exchanges (consumed by the epilogue)
+
+struct FwdK {
+  Dv3ScanFwdArgs a;
+  Plan plan;
+  const uint8_t* stream;        // packed weights: [CL][step_bytes]
+  const float* WmlpzT;          // [S, U] fp32 = Wmlp[:, :S]^T
+  const float* aW;              // [T*B, U] fp32 = masked action . Wmlp[:, S:]^T
+  long long* dbg;
+  int CL, nslots;
+};
+
+#define SDBG(p) do { if (k.dbg && c == 0 && blockIdx.x == 0 && et == 0 && t == 2) k.dbg[p] = clock64(); } while (0)
+
+__global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid_constant__ FwdK k) {
+  const Dv3ScanFwdArgs& a = k.a;
+  const Plan& pl = k.plan;
+  extern __shared__ __align__(128) uint8_t smraw[];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int CL = k.CL;
+  uint32_t crank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+  const int c = (int)crank;
+  const int b0 = ((int)blockIdx.x / CL) * NB;                 // first batch row of this cluster
+  const int Bv = min(NB, a.B - b0);                           // valid batch rows
+  const int B = a.B, G = a.G, Kc = a.Kc, D = a.D, U = a.U, Hh = a.Hh;
+  const int S = G * Kc;
+  const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc;
+  const int u0 = c * uper, d0 = c * dper, h0 = c * hper, s0 = c * sper;
+  const int npairs = NB * gper;
+
+  // ---- shared memory carve-up
+  uint8_t* sp = smraw;
+  auto take = [&](size_t bytes) { uint8_t* p = sp; sp += (bytes + 127) & ~(size_t)127; return p; };
+  uint8_t* ring_p = take((size_t)k.nslots * pl.slot_bytes + 2048);          // + slack: M = 128 reads past a packed tile's rows
+  uint8_t* xh = take((size_t)(D >> 3) * BROW);                              // activation operands [k8][NB rows][8 k] bf16
+  uint8_t* xf = take((size_t)(U >> 3) * BROW);
+  uint8_t* xhid = take((size_t)(Hh >> 3) * BROW);
+  const int fmax = max(max(uper, dper), hper);
+  uint8_t* stage = take((size_t)(fmax >> 3) * BROW);                         // own slice in operand layout (source of the pushes)
+  const int rows_max = max(max(3 * dper, uper), max(hper, sper));
+  float* outb = reinterpret_cast<float*>(take((size_t)rows_max * OB * 4));   // own pre-activations [row][OB]
+  float* outl = reinterpret_cast<float*>(take((size_t)sper * OB * 4));       // own unimix logits
+  float* hown = reinterpret_cast<float*>(take((size_t)NB * dper * 4));       // own fp32 slice of h  [m][dl]
+  float* lnp = reinterpret_cast<float*>(take((size_t)3 * CL * NB * 8));      // [3 exchanges][CL][NB] (mean, M2)
+  float* s_stat = reinterpret_cast<float*>(take(2 * NB * 4));
+  int* idxf = reinterpret_cast<int*>(take((size_t)G * NB * 4));              // sampled z indices of all groups [g][m] (peers write)
+  int* idxe = reinterpret_cast<int*>(take((size_t)G * NB * 4));              // effective (reset-masked) indices of this step
+  int* idxo = reinterpret_cast<int*>(take((size_t)npairs * 4));              // own sampled indices [m][gl]
+  int* s_zreset = reinterpret_cast<int*>(take((size_t)G * 4));
+  uint32_t* s_rmask = reinterpret_cast<uint32_t*>(take((size_t)a.T * 4));    // bit m: batch row m is reset at step t (or padding)
+  float* p_mlp = reinterpret_cast<float*>(take((size_t)2 * uper * 4));
+  float* p_gru = reinterpret_cast<float*>(take((size_t)6 * dper * 4));
+  float* p_r = reinterpret_cast<float*>(take((size_t)2 * hper * 4));
+  float* p_br1 = reinterpret_cast<float*>(take((size_t)sper * 4));
+  float* s_aw = reinterpret_cast<float*>(take((size_t)NB * uper * 4));       // cp.async landing zones (next step's inputs)
+  float* s_ew = reinterpret_cast<float*>(take((size_t)NB * hper * 4));
+  float* s_uu = reinterpret_cast<float*>(take((size_t)npairs * 4));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(take((size_t)(2 * k.nslots + 16) * 8));
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + k.nslots;
+  uint64_t* acc_bar = bars + 2 * k.nslots;        // [3]: gates, r0, r1 accumulators complete
+  uint64_t* act_bar = acc_bar + 3;                // [3]: feat, h, hid slices of all peers landed
+  uint64_t* stat_bar = act_bar + 3;               // [3]
+  uint64_t* idx_bar = stat_bar + 3;               // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(idx_bar + 2);
+
+  // ---- one-time set-up (all threads)
+  for (int i = tid; i < ((D + U + Hh) >> 3) * BROW / 16; i += NT) reinterpret_cast<uint4*>(xh)[i] = make_uint4(0u, 0u, 0u, 0u);   // xh|xf|xhid contiguous
+  for (int i = tid; i < (int)((k.nslots * pl.slot_bytes + 2048) / 16); i += NT) reinterpret_cast<uint4*>(ring_p)[i] = make_uint4(0u, 0u, 0u, 0u);
+  for (int i = tid; i < (fmax >> 3) * BROW / 16; i += NT) reinterpret_cast<uint4*>(stage)[i] = make_uint4(0u, 0u, 0u, 0u);
+  for (int i = tid; i < NB * dper; i += NT) hown[i] = 0.f;
+  for (int i = tid; i < G * NB; i += NT) { idxf[i] = 0; idxe[i] = 0; }
+  for (int i = tid; i < NB * uper; i += NT) s_aw[i] = 0.f;
+  for (int i = tid; i < NB * hper; i += NT) s_ew[i] = 0.f;
+  for (int i = tid; i < npairs; i += NT) s_uu[i] = 0.f;
+  for (int i = tid; i < G; i += NT) s_zreset[i] = __ldg(a.zreset_idx + i);
+  for (int t = tid; t < a.T; t += NT) {
+    uint32_t msk = 0;
+    for (int m = 0; m < NB; ++m) if (m >= Bv || t == 0 || __ldg(a.first + (size_t)t * B + b0 + m) != 0.f) msk |= 1u << m;
+    s_rmask[t] = msk;
+  }
+  for (int i = tid; i < uper; i += NT) { p_mlp[i] = __ldg(a.g_mlp + u0 + i); p_mlp[uper + i] = __ldg(a.b_mlp + u0 + i); }
+  for (int i = tid; i < 3 * dper; i += NT) {
+    const int gate = i / dper, dl = i - gate * dper;
+    p_gru[i] = __ldg(a.g_gru + gate * D + d0 + dl);
+    p_gru[3 * dper + i] = __ldg(a.b_gru + gate * D + d0 + dl);
+  }
+  for (int i = tid; i < hper; i += NT) { p_r[i] = __ldg(a.g_r + h0 + i); p_r[hper + i] = __ldg(a.b_r + h0 + i); }
+  for (int i = tid; i < sper; i += NT) p_br1[i] = __ldg(a.br1 + s0 + i);
+  if (tid == 0) {
+    for (int s = 0; s < k.nslots; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int i = 0; i < 10; ++i) mbar_init(&acc_bar[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(128));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  cluster_sync_all();          // every CTA's barriers and buffers exist before any peer writes into them
+
+  Ring rg;
+  rg.base = smem_u32(ring_p); rg.slot_bytes = pl.slot_bytes; rg.nslots = k.nslots; rg.full = full_bar; rg.empty = empty_bar;
+  const uint8_t* stream_cta = k.stream + (size_t)c * pl.step_bytes;
+
+  if (warp == 0) {
+    // ===================================================== producer =====================================================
+    RingPos pos = {0u, 0u};
+    produce_seg(pl, SEG_GH, stream_cta, rg, pos);
+#pragma unroll 1
+    for (int t = 0; t < a.T; ++t) {
+      produce_seg(pl, SEG_GF, stream_cta, rg, pos);
+      produce_seg(pl, SEG_R0, stream_cta, rg, pos);
+      if (t + 1 < a.T) produce_seg(pl, SEG_GH, stream_cta, rg, pos);
+      produce_seg(pl, SEG_R1, stream_cta, rg, pos);
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer =====================================================
+    RingPos pos = {0u, 0u};
+    const uint32_t xh_a = smem_u32(xh), xf_a = smem_u32(xf), xhid_a = smem_u32(xhid);
+    const uint32_t feat_bytes = (uint32_t)CL * (uper >> 3) * BROW, h_bytes = (uint32_t)CL * (dper >> 3) * BROW,
+                   hid_bytes = (uint32_t)CL * (hper >> 3) * BROW;
+    mma_seg(pl, SEG_GH, xh_a, tmem_base, rg, pos);                       // h_{-1} = 0
+#pragma unroll 1
+    for (int t = 0; t < a.T; ++t) {
+      const uint32_t par = (uint32_t)t & 1u;
+      if (elect_one()) mbar_expect_tx(&act_bar[X_FEAT], feat_bytes);
+      __syncwarp();
+      mbar_wait(&act_bar[X_FEAT], par);
+      mma_seg(pl, SEG_GF, xf_a, tmem_base, rg, pos);
+      if (elect_one()) umma_commit(&acc_bar[0]);
+      __syncwarp();
+      if (elect_one()) mbar_expect_tx(&act_bar[X_H], h_bytes);
+      __syncwarp();
+      mbar_wait(&act_bar[X_H], par);
+      mma_seg(pl, SEG_R0, xh_a, tmem_base, rg, pos);
+      if (elect_one()) umma_commit(&acc_bar[1]);
+      __syncwarp();
+      if (t + 1 < a.T) {
+        // reset rows of step t+1 see h = 0 (agent.py:379-381); the posterior of step t above needed the unmasked h_t
+        const uint32_t rm = s_rmask[t + 1] & ((1u << Bv) - 1u);
+        if (rm) {
+          mbar_wait(&acc_bar[1], par);                                   // r0(t) has finished reading xh
+#pragma unroll 1
+          for (int m = 0; m < NB; ++m)
+            if ((rm >> m) & 1u)
+              for (int k8 = lane; k8 < (D >> 3); k8 += 32) *reinterpret_cast<uint4*>(xh + b_off(m, k8 * 8)) = make_uint4(0u, 0u, 0u, 0u);
+          fence_proxy_async();
+          __syncwarp();
+        }
+        mma_seg(pl, SEG_GH, xh_a, tmem_base, rg, pos);
+      }
+      if (elect_one()) mbar_expect_tx(&act_bar[X_HID], hid_bytes);
+      __syncwarp();
+      mbar_wait(&act_bar[X_HID], par);
+      mma_seg(pl, SEG_R1, xhid_a, tmem_base, rg, pos);
+      if (elect_one()) umma_commit(&acc_bar[2]);
+      __syncwarp();
+    }
+  } else {
+    // ===================================================== epilogue =====================================================
+    const int et = tid - 64, ew = et >> 5;
+    const uint32_t stage_a = smem_u32(stage);
+    const int col_g = pl.seg[SEG_GH].tmem_col, col_r0 = pl.seg[SEG_R0].tmem_col, col_r1 = pl.seg[SEG_R1].tmem_col;
+    float* lnp0 = lnp;
+    float* lnp1 = lnp + (size_t)CL * NB * 2;
+    float* lnp2 = lnp + (size_t)2 * CL * NB * 2;
+
+    auto fetch_aw = [&](int t) {
+      for (int e = et; e < Bv * uper; e += NT_EPI) { const int m = e / uper, ul = e - m * uper; cp_async4(s_aw + m * uper + ul, k.aW + ((size_t)t * B + b0 + m) * U + u0 + ul); }
+    };
+    auto fetch_ew = [&](int t) {
+      for (int e = et; e < Bv * hper; e += NT_EPI) { const int m = e / hper, hl = e - m * hper; cp_async4(s_ew + m * hper + hl, a.eW + ((size_t)t * B + b0 + m) * Hh + h0 + hl); }
+    };
+    auto fetch_uu = [&](int t) {
+      for (int e = et; e < Bv * gper; e += NT_EPI) {
+        const int m = e / gper, gl = e - m * gper;
+        const size_t src = ((size_t)t * B + b0 + m) * G + c * gper + gl;
+        if (a.forced_idx) cp_async4(s_uu + m * gper + gl, a.forced_idx + src);
+        else cp_async4(s_uu + m * gper + gl, a.u_post + src);
+      }
+    };
+    fetch_aw(0);
+    fetch_ew(0);
+    fetch_uu(0);
+
+#pragma unroll 1
+    for (int t = 0; t < a.T; ++t) {
+      const uint32_t par = (uint32_t)t & 1u;
+      const size_t row0 = (size_t)t * B + b0;
+      const uint32_t rmask = s_rmask[t];
+      SDBG(0);
+      // ================= P0: arm this step's receive barriers; reset masking (agent.py:379-384) =================
+      if (et == 0) {
+        mbar_expect_tx(&stat_bar[ST_FEAT], (uint32_t)CL * NB * 8);
+        mbar_expect_tx(&stat_bar[ST_GRU], (uint32_t)CL * NB * 8);
+        mbar_expect_tx(&stat_bar[ST_HID], (uint32_t)CL * NB * 8);
+      }
+      if (t > 0) mbar_wait(&idx_bar[0], par ^ 1u);                         // z_{t-1} of every group has arrived
+      if (et == 0) mbar_expect_tx(&idx_bar[0], (uint32_t)G * NB * 4);      // (armed only once the previous phase has completed)
+      cp_async_wait_all();
+#pragma unroll 1
+      for (int i = et; i < G * NB; i += NT_EPI) { const int g = i >> 4, m = i & 15; idxe[i] = ((rmask >> m) & 1u) ? s_zreset[g] : idxf[i]; }
+#pragma unroll 1
+      for (int e = et; e < NB * dper; e += NT_EPI) { const int m = e / dper; if ((rmask >> m) & 1u) hown[e] = 0.f; }
+      epi_bar();
+      // saved inputs of the step: one-hot z_in (own categoricals) and h_in (own units)
+#pragma unroll 1
+      for (int i = et; i < Bv * (sper >> 2); i += NT_EPI) {
+        const int m = i / (sper >> 2), sl = (i - m * (sper >> 2)) << 2, s = s0 + sl, g = s / Kc, kk = s - g * Kc, ch = idxe[g * NB + m];
+        *reinterpret_cast<float4*>(a.x_mlp + (row0 + m) * a.ld_xmlp + s) =
+            make_float4(ch == kk ? 1.f : 0.f, ch == kk + 1 ? 1.f : 0.f, ch == kk + 2 ? 1.f : 0.f, ch == kk + 3 ? 1.f : 0.f);
+      }
+#pragma unroll 1
+      for (int e = et; e < Bv * dper; e += NT_EPI) { const int m = e / dper, dl = e - m * dper; a.x_gru[(row0 + m) * a.ld_xgru + d0 + dl] = hown[e]; }
+      SDBG(1);
+
+      // ================= P1: feat = SiLU(LN(Wmlp . [z, a])) -- one-hot gather + hoisted action projection =================
+#pragma unroll 1
+      for (int e = et; e < NB * uper; e += NT_EPI) {
+        const int m = e / uper, ul = e - m * uper;
+        float acc = s_aw[e];
+        const float* wcol = k.WmlpzT + u0 + ul;
+#pragma unroll 1
+        for (int g0 = 0; g0 < G; g0 += 16) {                    // 16 independent row gathers in flight
+          float v[16];
+#pragma unroll
+          for (int q = 0; q < 16; ++q) v[q] = (g0 + q < G) ? __ldg(wcol + (size_t)((g0 + q) * Kc + idxe[(g0 + q) * NB + m]) * U) : 0.f;
+#pragma unroll
+          for (int q = 0; q < 16; ++q) acc += v[q];
+        }
+        outb[ul * OB + m] = acc;
+      }
+      epi_bar();
+      stats_push(outb, uper, lnp0, &stat_bar[ST_FEAT], c, CL, ew, lane);
+      SDBG(2);
+#pragma unroll 1
+      for (int e = et; e < Bv * uper; e += NT_EPI) { const int m = e / uper, ul = e - m * uper; a.feat_pre[(row0 + m) * U + u0 + ul] = outb[ul * OB + m]; }
+      if (t + 1 < a.T) fetch_aw(t + 1);
+      mbar_wait(&stat_bar[ST_FEAT], par);
+      stats_combine(lnp0, CL, uper, 1e-3f, s_stat, a.feat_mean + row0, a.feat_rstd + row0, c == 0 ? Bv : 0, ew, lane);
+      epi_bar();
+      SDBG(3);
+#pragma unroll 1
+      for (int i = et; i < NB * (uper >> 1); i += NT_EPI) {     // two features per thread -> one 4 B store into the operand layout
+        const int m = i / (uper >> 1), ul = (i - m * (uper >> 1)) << 1;
+        const float mu = s_stat[m], rs = s_stat[NB + m];
+        float f0 = siluf_((outb[ul * OB + m] - mu) * rs * p_mlp[ul] + p_mlp[uper + ul]);
+        float f1 = siluf_((outb[(ul + 1) * OB + m] - mu) * rs * p_mlp[ul + 1] + p_mlp[uper + ul + 1]);
+        if (m < Bv) *reinterpret_cast<float2*>(a.x_gru + (row0 + m) * a.ld_xgru + D + u0 + ul) = make_float2(f0, f1);
+        else { f0 = 0.f; f1 = 0.f; }
+        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, ul)) = __floats2bfloat162_rn(f0, f1);
+      }
+      fence_proxy_async();
+      epi_bar();
+      push_act(stage_a, (uint32_t)(uper >> 3) * BROW, smem_u32(xf), &act_bar[X_FEAT], c, CL, ew);
+      SDBG(4);
+
+      // ================= P2: GRU gates: own rows {d, D+d, 2D+d} of Wgru . [h, feat] =================
+      mbar_wait(&acc_bar[0], par);
+      tc_fence_after();
+      SDBG(5);
+      tmem_to_outb(tmem_base, col_g, 3 * dper, outb, ew, lane);          // outb row = gate * dper + dl
+      epi_bar();
+      stats_push(outb, 3 * dper, lnp1, &stat_bar[ST_GRU], c, CL, ew, lane);
+#pragma unroll 1
+      for (int e = et; e < Bv * dper; e += NT_EPI) {            // saved pre-LN gates (own rows of the three gates)
+        const int m = e / dper, dl = e - m * dper;
+        float* gp = a.gates_pre + (row0 + m) * 3 * D + d0 + dl;
+        gp[0] = outb[dl * OB + m]; gp[D] = outb[(dper + dl) * OB + m]; gp[2 * D] = outb[(2 * dper + dl) * OB + m];
+      }
+      mbar_wait(&stat_bar[ST_GRU], par);
+      stats_combine(lnp1, CL, 3 * dper, 1e-5f, s_stat, a.gru_mean + row0, a.gru_rstd + row0, c == 0 ? Bv : 0, ew, lane);
+      epi_bar();
+      SDBG(6);
+#pragma unroll 1
+      for (int i = et; i < NB * (dper >> 1); i += NT_EPI) {
+        const int m = i / (dper >> 1), dl = (i - m * (dper >> 1)) << 1;
+        const float mu = s_stat[m], rs = s_stat[NB + m];
+        float hn[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int d = dl + j;
+          const float r = sigmoidf_((outb[d * OB + m] - mu) * rs * p_gru[d] + p_gru[3 * dper + d]);
+          const float cp = (outb[(dper + d) * OB + m] - mu) * rs * p_gru[dper + d] + p_gru[4 * dper + d];
+          const float cd = tanhf(r * cp);
+          const float u = sigmoidf_((outb[(2 * dper + d) * OB + m] - mu) * rs * p_gru[2 * dper + d] + p_gru[5 * dper + d] - 1.f);
+          hn[j] = u * cd + (1.f - u) * hown[m * dper + d];
+          if (m >= Bv) hn[j] = 0.f;
+          hown[m * dper + d] = hn[j];
+        }
+        if (m < Bv) *reinterpret_cast<float2*>(a.x_rep + (row0 + m) * a.ld_xrep + d0 + dl) = make_float2(hn[0], hn[1]);
+        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, dl)) = __floats2bfloat162_rn(hn[0], hn[1]);
+      }
+      fence_proxy_async();
+      epi_bar();
+      push_act(stage_a, (uint32_t)(dper >> 3) * BROW, smem_u32(xh), &act_bar[X_H], c, CL, ew);
+      SDBG(7);
+
+      // ================= P3: posterior hidden: own rows of Wr0[:, :D] . h' + (e_t . Wr0[:, D:]^T + b) =================
+      mbar_wait(&acc_bar[1], par);
+      tc_fence_after();
+      SDBG(8);
+      tmem_to_outb(tmem_base, col_r0, hper, outb, ew, lane);
+      epi_bar();
+#pragma unroll 1
+      for (int e = et; e < NB * hper; e += NT_EPI) { const int m = e / hper, hl = e - m * hper; outb[hl * OB + m] += s_ew[e]; }
+      epi_bar();
+      stats_push(outb, hper, lnp2, &stat_bar[ST_HID], c, CL, ew, lane);
+#pragma unroll 1
+      for (int e = et; e < Bv * hper; e += NT_EPI) { const int m = e / hper, hl = e - m * hper; a.hidr_pre[(row0 + m) * Hh + h0 + hl] = outb[hl * OB + m]; }
+      if (t + 1 < a.T) fetch_ew(t + 1);
+      mbar_wait(&stat_bar[ST_HID], par);
+      stats_combine(lnp2, CL, hper, 1e-5f, s_stat, a.hidr_mean + row0, a.hidr_rstd + row0, c == 0 ? Bv : 0, ew, lane);
+      epi_bar();
+      SDBG(9);
+#pragma unroll 1
+      for (int i = et; i < NB * (hper >> 1); i += NT_EPI) {
+        const int m = i / (hper >> 1), hl = (i - m * (hper >> 1)) << 1;
+        const float mu = s_stat[m], rs = s_stat[NB + m];
+        float f0 = siluf_((outb[hl * OB + m] - mu) * rs * p_r[hl] + p_r[hper + hl]);
+        float f1 = siluf_((outb[(hl + 1) * OB + m] - mu) * rs * p_r[hl + 1] + p_r[hper + hl + 1]);
+        if (m < Bv) *reinterpret_cast<float2*>(a.hidr + (row0 + m) * Hh + h0 + hl) = make_float2(f0, f1);
+        else { f0 = 0.f; f1 = 0.f; }
+        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, hl)) = __floats2bfloat162_rn(f0, f1);
+      }
+      fence_proxy_async();
+      epi_bar();
+      push_act(stage_a, (uint32_t)(hper >> 3) * BROW, smem_u32(xhid), &act_bar[X_HID], c, CL, ew);
+      SDBG(10);
+
+      // ================= P4: posterior logits of the own categoricals, unimix, inverse-CDF sample =================
+      mbar_wait(&acc_bar[2], par);
+      tc_fence_after();
+      SDBG(11);
+      tmem_to_outb(tmem_base, col_r1, sper, outb, ew, lane);
+      epi_bar();
+#pragma unroll 1
+      for (int p = ew; p < npairs; p += EW) {                  // one warp per (batch row, own categorical); lane = class (Kc <= 32)
+        const int m = p / gper, gl = p - m * gper, g = c * gper + gl;
+        const bool on = lane < Kc;
+        const float raw = on ? (outb[(size_t)(gl * Kc + lane) * OB + m] + p_br1[gl * Kc + lane]) : -INFINITY;
+        const float mx = warp_max(raw);
+        const float e1 = on ? expf(raw - mx) : 0.f;
+        const float se = warp_sum(e1);
+        float lu = raw;
+        if (a.unimix > 0.f) {
+          const float pr = (1.f - a.unimix) * (e1 / se) + a.unimix / (float)Kc;
+          lu = on ? logf(fminf(fmaxf(pr, DV3_EPS32), 1.f - DV3_EPS32)) : -INFINITY;
+        }
+        // Sampling probabilities: Categorical(logits = lu).probs = softmax(lu) = pm / sum(pm) up to fp32 round-off (the reference
+        // renormalises log(pm) twice); with bf16 contractions upstream that round-off is far below the logits' own error, so the
+        // draw uses pm directly and a warp prefix sum instead of the sequential cumsum of the fp32 kernels.
+        float prob = (a.unimix > 0.f) ? (on ? fminf(fmaxf((1.f - a.unimix) * (e1 / se) + a.unimix / (float)Kc, DV3_EPS32), 1.f - DV3_EPS32) : 0.f)
+                                      : (e1 / se);
+        prob = prob / warp_sum(prob);
+        int choice;
+        if (a.forced_idx) {
+          choice = __float_as_int(s_uu[p]);
+        } else {                                             // idx = #{k : cumsum_k(p) <= u}
+          float cs = prob;
+#pragma unroll
+          for (int o = 1; o < 32; o <<= 1) { const float v = __shfl_up_sync(0xffffffffu, cs, o); if (lane >= o) cs += v; }
+          choice = __popc(__ballot_sync(0xffffffffu, on && cs <= s_uu[p]));
+          if (choice > Kc - 1) choice = Kc - 1;
+        }
+        if (on) {
+          outb[(size_t)(gl * Kc + lane) * OB + m] = raw;
+          outl[(size_t)(gl * Kc + lane) * OB + m] = lu;
+        }
+        if (lane == 0) idxo[p] = choice;
+        if (lane < CL) st_async_b32(mapa(smem_u32(idxf + g * NB + m), (uint32_t)lane), (uint32_t)choice, mapa(smem_u32(&idx_bar[0]), (uint32_t)lane));
+      }
+      epi_bar();
+      SDBG(12);
+      if (t + 1 < a.T) fetch_uu(t + 1);
+      // global stores of the posterior of this step
+#pragma unroll 1
+      for (int e = et; e < Bv * sper; e += NT_EPI) {
+        const int m = e / sper, sl = e - m * sper, gl = sl / Kc;
+        a.post_raw[(row0 + m) * S + s0 + sl] = outb[sl * OB + m];
+        a.post_logits[(row0 + m) * S + s0 + sl] = outl[sl * OB + m];
+        a.latent[(row0 + m) * a.ld_lat + s0 + sl] = (idxo[m * gper + gl] == (sl - gl * Kc)) ? 1.f : 0.f;
+      }
+      for (int e = et; e < Bv * gper; e += NT_EPI) { const int m = e / gper, gl = e - m * gper; a.post_idx[(row0 + m) * G + c * gper + gl] = idxo[e]; }
+      SDBG(13);
+      epi_bar();                                               // idxo / outb / outl are rewritten by the next step
+    }
+    tc_fence_before();
+  }
+
+  // ---- teardown: nobody may still be writing into a peer that has left
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128));
+  }
+}
+
+// ---- host ------------------------------------------------------------------------------------------------------------------------
+bool build_plan(int D, int U, int Hh, int G, int Kc, int CL, Plan* pl) {
+  if (CL < 1 || D % CL || U % CL || Hh % CL || G % CL) return false;
+  const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc;
+  if ((uper & 7) || (dper & 7) || (hper & 7) || (sper & 3) || Kc > 32 || (D & 15) || (U & 15) || (Hh & 15)) return false;
+  if (hper > 128 || sper > 128 || 3 * dper > 128 * 6) return false;
+  memset(pl, 0, sizeof(Plan));
+  uint32_t off16 = 0;
+  const int gt = (3 * dper + 127) / 128;                      // gate tiles: TMEM columns [0, gt * NB)
+  RowBlk gb[3] = {{0, dper}, {D, dper}, {2 * D, dper}};
+  RowBlk hb[1] = {{0, hper}};
+  RowBlk sb[1] = {{0, sper}};
+  if (plan_add_seg(*pl, 3 * dper, D, 0, 1, 0, 3, gb, 0, off16) != SEG_GH) return false;
+  if (plan_add_seg(*pl, 3 * dper, U, 0, 0, 0, 3, gb, D, off16) != SEG_GF) return false;
+  if (plan_add_seg(*pl, hper, D, gt * NB, 1, 0, 1, hb, 0, off16) != SEG_R0) return false;
+  if (plan_add_seg(*pl, sper, Hh, gt * NB + NB, 1, 0, 1, sb, 0, off16) != SEG_R1) return false;
+  if (gt * NB + 2 * NB > 128) return false;
+  pl->step_bytes = off16 * 16;
+  return true;
+}
+
+size_t fixed_smem(const Dv3ScanFwdArgs* h, int CL) {
+  const int D = h->D, U = h->U, Hh = h->Hh, G = h->G, Kc = h->Kc;
+  const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc;
+  auto r = [](size_t b) { return (b + 127) & ~(size_t)127; };
+  auto mx = [](int x, int y) { return x > y ? x : y; };
+  const int fmax = mx(mx(uper, dper), hper), rows_max = mx(mx(3 * dper, uper), mx(hper, sper)), npairs = NB * gper;
+  return r((size_t)(D >> 3) * BROW) + r((size_t)(U >> 3) * BROW) + r((size_t)(Hh >> 3) * BROW) + r((size_t)(fmax >> 3) * BROW) +
+         r((size_t)rows_max * OB * 4) + r((size_t)sper * OB * 4) + r((size_t)NB * dper * 4) + r((size_t)3 * CL * NB * 8) + r(2 * NB * 4) +
+         2 * r((size_t)G * NB * 4) + r((size_t)npairs * 4) + r((size_t)G * 4) + r((size_t)h->T * 4) + r((size_t)2 * uper * 4) +
+         r((size_t)6 * dper * 4) + r((size_t)2 * hper * 4) + r((size_t)sper * 4) + r((size_t)NB * uper * 4) + r((size_t)NB * hper * 4) +
+         r((size_t)npairs * 4) + 128 /* alignment of the dynamic segment */;
+}
+
+// xh | xf | xhid must be contiguous for the set-up loop that zeroes them: true when every size is a multiple of 128 B (BROW = 256)
+int launch_tc(FwdK& k, int nclusters, size_t smem_bytes, cudaStream_t stream, bool probe_only) {
+  auto kern = rssm_observe_fwd_tc_kernel;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  if (e != cudaSuccess) { cudaGetLastError(); return DV3_ERR_UNSUPPORTED; }
+  if (k.CL > 8) {
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) { cudaGetLastError(); return DV3_ERR_UNSUPPORTED; }
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(k.CL * nclusters, 1, 1);
+  cfg.blockDim = dim3(NT, 1, 1);
+  cfg.dynamicSmemBytes = smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = k.CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  int nmax = 0;
+  e = cudaOccupancyMaxActiveClusters(&nmax, kern, &cfg);
+  if (e != cudaSuccess || nmax < nclusters) { cudaGetLastError(); return DV3_ERR_UNSUPPORTED; }   // all clusters must be co-resident? no: independent
+  if (probe_only) return DV3_OK;
+  e = cudaLaunchKernelEx(&cfg, kern, k);
+  if (e != cudaSuccess) return (int)e;
+  return DV3_OK;
+}
+
+}  // namespace
+
+// Plan of the forward scan's weight stream for a shape (the same function sizes the buffer, drives the packing kernel and the scan).
+extern "C" int dv3_scan_tc_fwd_config(int D, int U, int Hh, int G, int Kc, int* cluster_size, size_t* stream_bytes) {
+  Plan pl;
+  for (int CL = 16; CL >= 8; CL >>= 1) {
+    if (!build_plan(D, U, Hh, G, Kc, CL, &pl)) continue;
+    if (cluster_size) *cluster_size = CL;
+    if (stream_bytes) *stream_bytes = (size_t)CL * pl.step_bytes;
+    return DV3_OK;
+  }
+  return DV3_ERR_UNSUPPORTED;
+}
+
+// ---- packing: fp32 weights -> per-CTA, per-step bf16 stream in the MMA's shared-memory image -----------------------------------
+namespace {
+struct PackSrc { const float* W; long long sr, sc; };
+struct PackK { Plan plan; PackSrc src[MAX_SEG]; uint8_t* dst; int CL; };
+// one block per (cta, chunk); unit = 8 consecutive k of one row (16 B in the stream)
+__global__ void __launch_bounds__(256) scan_tc_pack_kernel(const __grid_constant__ PackK p) {
+  const int cta = blockIdx.x / p.plan.nchunks, ci = blockIdx.x - cta * p.plan.nchunks;
+  const Chunk ch = p.plan.c[ci];
+  const Seg& sg = p.plan.seg[ch.seg];
+  const PackSrc src = p.src[ch.seg];
+  const int rp = ch.lbo16, nunits = (int)ch.bytes16;
+  uint4* dst = reinterpret_cast<uint4*>(p.dst + (size_t)cta * p.plan.step_bytes) + ch.off16;
+  for (int u = threadIdx.x; u < nunits; u += blockDim.x) {
+    const int k8 = u / rp, r = u - k8 * rp;
+    const int j = ch.tile * 128 + r;                         // local row of the segment
+    uint4 out = make_uint4(0u, 0u, 0u, 0u);
+    if (j < sg.rows) {
+      int start = 0, grow = -1;
+      for (int b = 0; b < sg.nblk; ++b) {
+        if (j < start + sg.blk[b].size) { grow = sg.blk[b].base + cta * sg.blk[b].size + (j - start); break; }
+        start += sg.blk[b].size;
+      }
+      const int kk = ch.k0 + k8 * 8;
+      const float* s = src.W + (size_t)grow * src.sr + (size_t)(sg.col0 + kk) * src.sc;
+      float v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = (kk + q < sg.K) ? __ldg(s + (size_t)q * src.sc) : 0.f;
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(v[0], v[1]), h1 = __floats2bfloat162_rn(v[2], v[3]), h2 = __floats2bfloat162_rn(v[4], v[5]),
+                     h3 = __floats2bfloat162_rn(v[6], v[7]);
+      out.x = *reinterpret_cast<uint32_t*>(&h0); out.y = *reinterpret_cast<uint32_t*>(&h1);
+      out.z = *reinterpret_cast<uint32_t*>(&h2); out.w = *reinterpret_cast<uint32_t*>(&h3);
+    }
+    // stream order inside a chunk: [k8][row group][8 rows] x 16 B  ==  unit index u
+    dst[u] = out;
+  }
+}
+}  // namespace
+
+extern "C" int dv3_scan_tc_fwd_pack(int D, int U, int Hh, int G, int Kc, const float* Wgru, int ld_wgru, const float* Wr0, int ld_wr0,
+                                    const float* Wr1, int ld_wr1, void* dst, void* stream) {
+  if (!Wgru || !Wr0 || !Wr1 || !dst) return DV3_ERR_ARG;
+  PackK p;
+  int CL = 0;
+  for (CL = 16; CL >= 8; CL >>= 1) if (build_plan(D, U, Hh, G, Kc, CL, &p.plan)) break;
+  if (CL < 8) return DV3_ERR_UNSUPPORTED;
+  p.CL = CL;
+  p.dst = reinterpret_cast<uint8_t*>(dst);
+  p.src[SEG_GH] = {Wgru, ld_wgru, 1};
+  p.src[SEG_GF] = {Wgru, ld_wgru, 1};
+  p.src[SEG_R0] = {Wr0, ld_wr0, 1};
+  p.src[SEG_R1] = {Wr1, ld_wr1, 1};
+  scan_tc_pack_kernel<<<CL * p.plan.nchunks, 256, 0, (cudaStream_t)stream>>>(p);
+  DV3_LAUNCH_CHECK();
+  return DV3_OK;
+}
+
+extern "C" int dv3_rssm_observe_fwd_tc(const Dv3ScanFwdArgs* h, const Dv3ScanTcExtra* x, void* stream_) {
+  if (!h || !x) return DV3_ERR_ARG;
+  if (h->B < 1 || h->T < 1 || h->G < 1 || h->Kc < 1 || h->Kc > 32 || (h->Kc & 3) || (h->ld_xmlp & 3) || ((uintptr_t)h->x_mlp & 15) ||
+      (h->ld_xgru & 1) || (h->ld_xrep & 1) || ((uintptr_t)h->x_gru & 7) || ((uintptr_t)h->x_rep & 7) || ((uintptr_t)h->hidr & 7) || (h->D & 1))
+    return DV3_ERR_UNSUPPORTED;
+  if (!x->stream || !x->WmlpzT || !x->aW || ((uintptr_t)x->stream & 15)) return DV3_ERR_UNSUPPORTED;
+  int dev = 0, max_smem = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  FwdK* k = new FwdK;
+  int rc = DV3_ERR_UNSUPPORTED;
+  for (int CL = 16; CL >= 8; CL >>= 1) {
+    if (!build_plan(h->D, h->U, h->Hh, h->G, h->Kc, CL, &k->plan)) continue;
+    k->a = *h;
+    k->stream = reinterpret_cast<const uint8_t*>(x->stream);
+    k->WmlpzT = x->WmlpzT;
+    k->aW = x->aW;
+    k->CL = CL;
+    k->dbg = (getenv("DV3_SCAN_DEBUG") && h->scratch && h->scratch_bytes >= 64 * sizeof(long long)) ? reinterpret_cast<long long*>(h->scratch) : nullptr;
+    const size_t fixed = fixed_smem(h, CL) + 2048 + 128 /* ring slack + alignment */;
+    int nslots = ((long long)max_smem - (long long)fixed - 512) / (long long)k->plan.slot_bytes;
+    if (nslots > 12) nslots = 12;
+    if (nslots < 2) continue;
+    const size_t smem = fixed + (size_t)nslots * k->plan.slot_bytes + (size_t)(2 * nslots + 16) * 8 + 128;
+    k->nslots = nslots;
+    const int nclusters = (h->B + NB - 1) / NB;
+    if (getenv("DV3_SCAN_DEBUG"))
+      fprintf(stderr, "[dv3 tc scan] CL=%d clusters=%d slots=%d x %u B, step stream %u B/CTA, %d chunks, smem %zu KB (max %d KB)\n", CL, nclusters, nslots,
+              k->plan.slot_bytes, k->plan.step_bytes, k->plan.nchunks, smem / 1024, max_smem / 1024);
+    if (launch_tc(*k, nclusters, smem, (cudaStream_t)stream_, true) != DV3_OK) continue;
+    rc = launch_tc(*k, nclusters, smem, (cudaStream_t)stream_, false);
+    break;
+  }
+  delete k;
+  return rc;
+}

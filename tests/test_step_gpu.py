@@ -263,11 +263,18 @@ def test_persistent_scan_matches_per_step_composition(cuda_ops, size, B, T, obs,
         assert rel(getattr(b, name), getattr(a, name)) < 1e-5, (name, rel(getattr(b, name), getattr(a, name)))
 
 
-@pytest.mark.parametrize("size,B,T,obs,acts", [("S", 16, 64, 14, [100]), ("XS", 16, 20, 4, [2]), ("S", 5, 9, 14, [7, 3]), ("M", 16, 12, 20, [18])])
-def test_cluster_scan_matches_cooperative_scan(cuda_ops, size, B, T, obs, acts):
-    """dv3_rssm_observe_fwd_cluster (one 16-CTA cluster, bf16 weights in mma.sync fragments, DSMEM exchange) against the fp32
-    cooperative scan kernel.  The contractions round their operands to bf16, so tensors agree to the bf16-mode tolerance (2e-2 of
-    the tensor's max) under teacher-forced draws; free-running draws flip only where a uniform lands next to a CDF step."""
+@pytest.mark.parametrize("size,B,T,obs,acts,kernel", [
+    ("S", 16, 64, 14, [100], "tcgen05"), ("XS", 16, 20, 4, [2], "tcgen05"), ("S", 5, 9, 14, [7, 3], "tcgen05"),
+    ("M", 16, 12, 20, [18], "tcgen05"),          # 640 / 16 = 40 columns per CTA: not a power of two
+    ("L", 32, 6, 20, [18], "tcgen05"),           # B = 32: two clusters of 16 rows; D 2048, three 128-row gate tiles per CTA
+    ("prey", 16, 8, 14, [100], "tcgen05"),       # as-shipped prey size: D = Hh = 256, U = 1024
+    ("S", 16, 16, 14, [100], "cluster"), ("XS", 7, 10, 4, [2], "cluster")])
+def test_fused_bf16_scan_matches_fp32_scan(cuda_ops, size, B, T, obs, acts, kernel):
+    """The bf16 forward scans -- dv3_rssm_observe_fwd_tc (tcgen05 swap-AB contractions, bulk-copy weight ring, mbarrier exchange
+    over one cluster per 16 batch rows) and its predecessor dv3_rssm_observe_fwd_cluster (mma.sync) -- against the fp32 scan
+    (cooperative kernel, or the per-step composition for B > 16).  The contractions round their operands to bf16, so tensors agree
+    to the bf16-mode tolerance (2e-2 of the tensor's max) under teacher-forced draws; free-running draws flip only where a uniform
+    lands next to a CDF step."""
     from sheeprl_prey_b200._lib import CudaOps
 
     cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=3)
@@ -280,17 +287,14 @@ def test_cluster_scan_matches_cooperative_scan(cuda_ops, size, B, T, obs, acts):
     ref.load_noise(noise)
     ref.world_forward()
     torch.cuda.synchronize()
-    assert ref.use_fused_scan
     ops = CudaOps(DEV, precision="bf16")
+    ops.use_tc_scan = kernel == "tcgen05"
     eng = engine_from_params(cfg, od, acts, _dev_params(params), ops, DEV)
     eng.load_batch(data)
     eng.load_noise(noise)
     eng.world_forward()
     torch.cuda.synchronize()
-    if size == "M":       # 640 / 16 columns per CTA is not a power of two: outside the cluster kernel's plan, cooperative kernel runs
-        assert ops.scan_kernel == "cooperative", ops.scan_kernel
-        return
-    assert ops.scan_kernel == "cluster", ops.scan_kernel
+    assert ops.scan_kernel == kernel, ops.scan_kernel
     # free-running draws: a flip (uniform next to a CDF step) changes the state and everything after it, so only the first step
     # measures the flip rate itself
     flips0 = float((eng.post_idx[:B] != ref.post_idx[:B]).float().mean())

@@ -1,0 +1,63 @@
+#!/usr/bin/env python
+"""Times the tcgen05 scan kernels alone (CUDA events around repeated launches, weights re-packed outside the timed region) and prints the
+clock64 stamps the epilogue of CTA 0 records during step 2 (DV3_SCAN_DEBUG=1).  usage: scan_bench_tc.py [size] [B] [T] [--old]"""
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+os.environ.setdefault("DV3_SCAN_DEBUG", "1")
+from oracle import harness  # noqa: E402
+from sheeprl_prey_b200._lib import CudaOps  # noqa: E402
+from sheeprl_prey_b200.configs import make_cfg  # noqa: E402
+from util import engine_from_params, random_params_like  # noqa: E402
+
+args = [a for a in sys.argv[1:] if not a.startswith("--")]
+size = args[0] if len(args) > 0 else "S"
+B = int(args[1]) if len(args) > 1 else 16
+T = int(args[2]) if len(args) > 2 else 64
+old = "--old" in sys.argv
+dev = "cuda:0"
+cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=15)
+od, acts = {"state": 14}, [100]
+params = random_params_like(cfg, od, acts, seed=5)
+ops = CudaOps(dev, precision="bf16")
+ops.use_tc_scan = not old
+eng = engine_from_params(cfg, od, acts, {n: {k: v.to(dev) for k, v in d.items()} for n, d in params.items()}, ops, dev)
+eng.load_batch({k: v.to(dev) for k, v in harness.synthetic_batch(T, B, od, acts, seed=1).items()})
+eng.load_noise(None)
+eng.world_forward()
+eng.world_losses()
+eng.world_backward()
+torch.cuda.synchronize()
+out = {"size": size, "B": B, "T": T, "fwd_kernel": ops.scan_kernel, "bwd_kernel": ops.bwd_scan_kernel}
+
+
+def timed(fn, n=10):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+out["fwd_ms_incl_pack"] = timed(lambda: ops.rssm_observe_fwd(eng, None))
+st = ops.scratch[:64].view(torch.int64)[:32].cpu().tolist()
+names = ["P0 arm/idx wait/mask", "P0 saves", "P1 gather+stats push", "P1 stats wait+combine", "P1 LN+push", "wait gates acc", "P2 tmem->outb.. stats",
+         "P2 gates+push", "wait r0 acc", "P3 stats", "P3 LN+push", "wait r1 acc", "P4 sample", "P4 stores"]
+if ops.scan_kernel == "tcgen05":
+    out["fwd_phases_clk"] = {names[i]: st[i + 1] - st[i] for i in range(13)}
+    out["fwd_step_clk"] = st[13] - st[0]
+out["bwd_ms_incl_prep_pack"] = timed(lambda: ops.rssm_observe_bwd(eng))
+print(json.dumps(out, indent=1))
+os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+with open(os.path.join(ROOT, "gpurun_out", f"scan_bench_tc_{size}_B{B}{'_old' if old else ''}.json"), "w") as f:
+    json.dump(out, f, indent=1)
