@@ -29,6 +29,7 @@ struct FwdK {
   const float* aW;              // [T*B, U] fp32 = masked action . Wmlp[:, S:]^T
   long long* dbg;
   int CL, nslots;
+  int tab_smem;                  // this CTA's columns of Wmlp[:, :S]^T live in shared memory as bf16 (one-hot gather without L2 latency)
 };
 
 #define SDBG(p) do { if (k.dbg && c == 0 && blockIdx.x == 0 && et == 0 && t == 2) k.dbg[p] = clock64(); } while (0)
@@ -56,18 +57,21 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
   auto take = [&](size_t bytes) { uint8_t* p = sp; sp += (bytes + 127) & ~(size_t)127; return p; };
   uint8_t* ring_p = take((size_t)k.nslots * pl.slot_bytes + 2048);          // + slack: M = 128 reads past a packed tile's rows
   uint8_t* xh = take((size_t)(D >> 3) * BROW);                              // activation operands [k8][NB rows][8 k] bf16
-  uint8_t* xf = take((size_t)(U >> 3) * BROW);
-  uint8_t* xhid = take((size_t)(Hh >> 3) * BROW);
+  // feat_t and the posterior hidden share one buffer: feat_{t+1} cannot arrive before every CTA has sampled z_t (after r1(t) read the
+  // hidden), the hidden of step t not before every CTA's r0(t) has completed (issued after gf(t), which read feat_t)
+  uint8_t* xf = take((size_t)(max(U, Hh) >> 3) * BROW);
+  uint8_t* xhid = xf;
   const int fmax = max(max(uper, dper), hper);
   uint8_t* stage = take((size_t)(fmax >> 3) * BROW);                         // own slice in operand layout (source of the pushes)
   const int rows_max = max(max(3 * dper, uper), max(hper, sper));
   float* outb = reinterpret_cast<float*>(take((size_t)rows_max * OB * 4));   // own pre-activations [row][OB]
-  float* outl = reinterpret_cast<float*>(take((size_t)sper * OB * 4));       // own unimix logits
-  float* hown = reinterpret_cast<float*>(take((size_t)NB * dper * 4));       // own fp32 slice of h  [m][dl]
+  float* outp = reinterpret_cast<float*>(take((size_t)sper * OB * 4));       // own posterior raw logits  } kept until the next step
+  float* outl = reinterpret_cast<float*>(take((size_t)sper * OB * 4));       // own unimix logits         } stores them to global
+  float* hown = reinterpret_cast<float*>(take((size_t)NB * dper * 4));       // own fp32 slice of h  [m][dl] (double-buffered: the saved
+  float* hnew = reinterpret_cast<float*>(take((size_t)NB * dper * 4));       // h_in of a step is stored to global after its gates ran)
   float* lnp = reinterpret_cast<float*>(take((size_t)3 * CL * NB * 8));      // [3 exchanges][CL][NB] (mean, M2)
   float* s_stat = reinterpret_cast<float*>(take(2 * NB * 4));
   int* idxf = reinterpret_cast<int*>(take((size_t)G * NB * 4));              // sampled z indices of all groups [g][m] (peers write)
-  int* idxe = reinterpret_cast<int*>(take((size_t)G * NB * 4));              // effective (reset-masked) indices of this step
   int* idxo = reinterpret_cast<int*>(take((size_t)npairs * 4));              // own sampled indices [m][gl]
   int* s_zreset = reinterpret_cast<int*>(take((size_t)G * 4));
   uint32_t* s_rmask = reinterpret_cast<uint32_t*>(take((size_t)a.T * 4));    // bit m: batch row m is reset at step t (or padding)
@@ -78,6 +82,7 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
   float* s_aw = reinterpret_cast<float*>(take((size_t)NB * uper * 4));       // cp.async landing zones (next step's inputs)
   float* s_ew = reinterpret_cast<float*>(take((size_t)NB * hper * 4));
   float* s_uu = reinterpret_cast<float*>(take((size_t)npairs * 4));
+  __nv_bfloat16* tab = k.tab_smem ? reinterpret_cast<__nv_bfloat16*>(take((size_t)S * uper * 2)) : nullptr;   // [S][uper]
   uint64_t* bars = reinterpret_cast<uint64_t*>(take((size_t)(2 * k.nslots + 16) * 8));
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + k.nslots;
@@ -88,11 +93,11 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(idx_bar + 2);
 
   // ---- one-time set-up (all threads)
-  for (int i = tid; i < ((D + U + Hh) >> 3) * BROW / 16; i += NT) reinterpret_cast<uint4*>(xh)[i] = make_uint4(0u, 0u, 0u, 0u);   // xh|xf|xhid contiguous
+  for (int i = tid; i < ((D + max(U, Hh)) >> 3) * BROW / 16; i += NT) reinterpret_cast<uint4*>(xh)[i] = make_uint4(0u, 0u, 0u, 0u);   // xh | xf contiguous
   for (int i = tid; i < (int)((k.nslots * pl.slot_bytes + 2048) / 16); i += NT) reinterpret_cast<uint4*>(ring_p)[i] = make_uint4(0u, 0u, 0u, 0u);
   for (int i = tid; i < (fmax >> 3) * BROW / 16; i += NT) reinterpret_cast<uint4*>(stage)[i] = make_uint4(0u, 0u, 0u, 0u);
-  for (int i = tid; i < NB * dper; i += NT) hown[i] = 0.f;
-  for (int i = tid; i < G * NB; i += NT) { idxf[i] = 0; idxe[i] = 0; }
+  for (int i = tid; i < NB * dper; i += NT) { hown[i] = 0.f; hnew[i] = 0.f; }
+  for (int i = tid; i < G * NB; i += NT) idxf[i] = 0;
   for (int i = tid; i < NB * uper; i += NT) s_aw[i] = 0.f;
   for (int i = tid; i < NB * hper; i += NT) s_ew[i] = 0.f;
   for (int i = tid; i < npairs; i += NT) s_uu[i] = 0.f;
@@ -110,6 +115,13 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
   }
   for (int i = tid; i < hper; i += NT) { p_r[i] = __ldg(a.g_r + h0 + i); p_r[hper + i] = __ldg(a.b_r + h0 + i); }
   for (int i = tid; i < sper; i += NT) p_br1[i] = __ldg(a.br1 + s0 + i);
+  if (tab) {
+    for (int i = tid; i < S * (uper >> 1); i += NT) {
+      const int srow = i / (uper >> 1), ul = (i - srow * (uper >> 1)) << 1;
+      const float2 w = *reinterpret_cast<const float2*>(k.WmlpzT + (size_t)srow * U + u0 + ul);
+      *reinterpret_cast<__nv_bfloat162*>(tab + srow * uper + ul) = __floats2bfloat162_rn(w.x, w.y);
+    }
+  }
   if (tid == 0) {
     for (int s = 0; s < k.nslots; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int i = 0; i < 10; ++i) mbar_init(&acc_bar[i], 1);
@@ -207,6 +219,17 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
         else cp_async4(s_uu + m * gper + gl, a.u_post + src);
       }
     };
+    // global stores of the posterior sampled in the step whose first row is prow0 (outp / outl / idxo live until the next P4)
+    auto flush_posterior = [&](size_t prow0) {
+#pragma unroll 1
+      for (int e = et; e < Bv * sper; e += NT_EPI) {
+        const int m = e / sper, sl = e - m * sper, gl = sl / Kc;
+        a.post_raw[(prow0 + m) * S + s0 + sl] = outp[sl * OB + m];
+        a.post_logits[(prow0 + m) * S + s0 + sl] = outl[sl * OB + m];
+        a.latent[(prow0 + m) * a.ld_lat + s0 + sl] = (idxo[m * gper + gl] == (sl - gl * Kc)) ? 1.f : 0.f;
+      }
+      for (int e = et; e < Bv * gper; e += NT_EPI) { const int m = e / gper, gl = e - m * gper; a.post_idx[(prow0 + m) * G + c * gper + gl] = idxo[e]; }
+    };
     fetch_aw(0);
     fetch_ew(0);
     fetch_uu(0);
@@ -217,7 +240,7 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
       const size_t row0 = (size_t)t * B + b0;
       const uint32_t rmask = s_rmask[t];
       SDBG(0);
-      // ================= P0: arm this step's receive barriers; reset masking (agent.py:379-384) =================
+      // ================= P0: arm this step's receive barriers; wait for z_{t-1} =================
       if (et == 0) {
         mbar_expect_tx(&stat_bar[ST_FEAT], (uint32_t)CL * NB * 8);
         mbar_expect_tx(&stat_bar[ST_GRU], (uint32_t)CL * NB * 8);
@@ -226,48 +249,51 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
       if (t > 0) mbar_wait(&idx_bar[0], par ^ 1u);                         // z_{t-1} of every group has arrived
       if (et == 0) mbar_expect_tx(&idx_bar[0], (uint32_t)G * NB * 4);      // (armed only once the previous phase has completed)
       cp_async_wait_all();
-#pragma unroll 1
-      for (int i = et; i < G * NB; i += NT_EPI) { const int g = i >> 4, m = i & 15; idxe[i] = ((rmask >> m) & 1u) ? s_zreset[g] : idxf[i]; }
-#pragma unroll 1
-      for (int e = et; e < NB * dper; e += NT_EPI) { const int m = e / dper; if ((rmask >> m) & 1u) hown[e] = 0.f; }
-      epi_bar();
-      // saved inputs of the step: one-hot z_in (own categoricals) and h_in (own units)
-#pragma unroll 1
-      for (int i = et; i < Bv * (sper >> 2); i += NT_EPI) {
-        const int m = i / (sper >> 2), sl = (i - m * (sper >> 2)) << 2, s = s0 + sl, g = s / Kc, kk = s - g * Kc, ch = idxe[g * NB + m];
-        *reinterpret_cast<float4*>(a.x_mlp + (row0 + m) * a.ld_xmlp + s) =
-            make_float4(ch == kk ? 1.f : 0.f, ch == kk + 1 ? 1.f : 0.f, ch == kk + 2 ? 1.f : 0.f, ch == kk + 3 ? 1.f : 0.f);
-      }
-#pragma unroll 1
-      for (int e = et; e < Bv * dper; e += NT_EPI) { const int m = e / dper, dl = e - m * dper; a.x_gru[(row0 + m) * a.ld_xgru + d0 + dl] = hown[e]; }
+      epi_bar();                                                           // s_aw / s_ew / s_uu landed (other threads' cp.async)
       SDBG(1);
-
+      // reset rows (agent.py:379-384) use z = mode(transition(0)) and h = 0: applied where idxf / hown are read
+#define ZIDX(g, m) ((((rmask) >> (m)) & 1u) ? s_zreset[(g)] : idxf[(g) * NB + (m)])
       // ================= P1: feat = SiLU(LN(Wmlp . [z, a])) -- one-hot gather + hoisted action projection =================
+      if (tab) {
 #pragma unroll 1
-      for (int e = et; e < NB * uper; e += NT_EPI) {
-        const int m = e / uper, ul = e - m * uper;
-        float acc = s_aw[e];
-        const float* wcol = k.WmlpzT + u0 + ul;
-#pragma unroll 1
-        for (int g0 = 0; g0 < G; g0 += 16) {                    // 16 independent row gathers in flight
-          float v[16];
-#pragma unroll
-          for (int q = 0; q < 16; ++q) v[q] = (g0 + q < G) ? __ldg(wcol + (size_t)((g0 + q) * Kc + idxe[(g0 + q) * NB + m]) * U) : 0.f;
-#pragma unroll
-          for (int q = 0; q < 16; ++q) acc += v[q];
+        for (int i = et; i < NB * (uper >> 1); i += NT_EPI) {     // two adjacent features per thread, G independent 4 B loads
+          const int m = i / (uper >> 1), ul = (i - m * (uper >> 1)) << 1;
+          float a0 = s_aw[m * uper + ul], a1 = s_aw[m * uper + ul + 1];
+          const __nv_bfloat16* tcol = tab + ul;
+#pragma unroll 8
+          for (int g = 0; g < G; ++g) {
+            const float2 w = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(tcol + (g * Kc + ZIDX(g, m)) * uper));
+            a0 += w.x; a1 += w.y;
+          }
+          outb[ul * OB + m] = a0;
+          outb[(ul + 1) * OB + m] = a1;
         }
-        outb[ul * OB + m] = acc;
+      } else {
+#pragma unroll 1
+        for (int e = et; e < NB * uper; e += NT_EPI) {
+          const int m = e / uper, ul = e - m * uper;
+          float acc = s_aw[e];
+          const float* wcol = k.WmlpzT + u0 + ul;
+#pragma unroll 1
+          for (int g0 = 0; g0 < G; g0 += 16) {                    // 16 independent row gathers in flight
+            float v[16];
+#pragma unroll
+            for (int q = 0; q < 16; ++q) v[q] = (g0 + q < G) ? __ldg(wcol + (size_t)((g0 + q) * Kc + ZIDX(g0 + q, m)) * U) : 0.f;
+#pragma unroll
+            for (int q = 0; q < 16; ++q) acc += v[q];
+          }
+          outb[ul * OB + m] = acc;
+        }
       }
       epi_bar();
-      stats_push(outb, uper, lnp0, &stat_bar[ST_FEAT], c, CL, ew, lane);
       SDBG(2);
-#pragma unroll 1
-      for (int e = et; e < Bv * uper; e += NT_EPI) { const int m = e / uper, ul = e - m * uper; a.feat_pre[(row0 + m) * U + u0 + ul] = outb[ul * OB + m]; }
-      if (t + 1 < a.T) fetch_aw(t + 1);
+      stats_push(outb, uper, lnp0, &stat_bar[ST_FEAT], c, CL, ew, lane);
+      SDBG(3);
       mbar_wait(&stat_bar[ST_FEAT], par);
+      SDBG(4);
       stats_combine(lnp0, CL, uper, 1e-3f, s_stat, a.feat_mean + row0, a.feat_rstd + row0, c == 0 ? Bv : 0, ew, lane);
       epi_bar();
-      SDBG(3);
+      SDBG(5);
 #pragma unroll 1
       for (int i = et; i < NB * (uper >> 1); i += NT_EPI) {     // two features per thread -> one 4 B store into the operand layout
         const int m = i / (uper >> 1), ul = (i - m * (uper >> 1)) << 1;
@@ -278,32 +304,50 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
         else { f0 = 0.f; f1 = 0.f; }
         *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, ul)) = __floats2bfloat162_rn(f0, f1);
       }
+      SDBG(6);
       fence_proxy_async();
       epi_bar();
+      SDBG(7);
       push_act(stage_a, (uint32_t)(uper >> 3) * BROW, smem_u32(xf), &act_bar[X_FEAT], c, CL, ew);
-      SDBG(4);
+      SDBG(8);
+      // while the slices travel and the MMA warp contracts: saved inputs of the step (one-hot z_in of the own categoricals, h_in of
+      // the own units), the pre-LN feature, the posterior of the PREVIOUS step, next step's action projection
+#pragma unroll 1
+      for (int i = et; i < Bv * (sper >> 2); i += NT_EPI) {
+        const int m = i / (sper >> 2), sl = (i - m * (sper >> 2)) << 2, sc_ = s0 + sl, g = sc_ / Kc, kk = sc_ - g * Kc, ch = ZIDX(g, m);
+        *reinterpret_cast<float4*>(a.x_mlp + (row0 + m) * a.ld_xmlp + sc_) =
+            make_float4(ch == kk ? 1.f : 0.f, ch == kk + 1 ? 1.f : 0.f, ch == kk + 2 ? 1.f : 0.f, ch == kk + 3 ? 1.f : 0.f);
+      }
+#pragma unroll 1
+      for (int e = et; e < Bv * dper; e += NT_EPI) {
+        const int m = e / dper, dl = e - m * dper;
+        a.x_gru[(row0 + m) * a.ld_xgru + d0 + dl] = ((rmask >> m) & 1u) ? 0.f : hown[e];
+      }
+#pragma unroll 1
+      for (int e = et; e < Bv * uper; e += NT_EPI) { const int m = e / uper, ul = e - m * uper; a.feat_pre[(row0 + m) * U + u0 + ul] = outb[ul * OB + m]; }
+      if (t > 0) flush_posterior(row0 - B);
+      if (t + 1 < a.T) fetch_aw(t + 1);
+      SDBG(9);
 
       // ================= P2: GRU gates: own rows {d, D+d, 2D+d} of Wgru . [h, feat] =================
       mbar_wait(&acc_bar[0], par);
       tc_fence_after();
-      SDBG(5);
-      tmem_to_outb(tmem_base, col_g, 3 * dper, outb, ew, lane);          // outb row = gate * dper + dl
+      SDBG(10);
+      tmem_to_outb(tmem_base, col_g, 3 * dper, pl.seg[SEG_GH].m64, outb, nullptr, 0, ew, lane);          // outb row = gate * dper + dl
       epi_bar();
+      SDBG(11);
       stats_push(outb, 3 * dper, lnp1, &stat_bar[ST_GRU], c, CL, ew, lane);
-#pragma unroll 1
-      for (int e = et; e < Bv * dper; e += NT_EPI) {            // saved pre-LN gates (own rows of the three gates)
-        const int m = e / dper, dl = e - m * dper;
-        float* gp = a.gates_pre + (row0 + m) * 3 * D + d0 + dl;
-        gp[0] = outb[dl * OB + m]; gp[D] = outb[(dper + dl) * OB + m]; gp[2 * D] = outb[(2 * dper + dl) * OB + m];
-      }
+      SDBG(12);
       mbar_wait(&stat_bar[ST_GRU], par);
+      SDBG(13);
       stats_combine(lnp1, CL, 3 * dper, 1e-5f, s_stat, a.gru_mean + row0, a.gru_rstd + row0, c == 0 ? Bv : 0, ew, lane);
       epi_bar();
-      SDBG(6);
+      SDBG(14);
 #pragma unroll 1
       for (int i = et; i < NB * (dper >> 1); i += NT_EPI) {
         const int m = i / (dper >> 1), dl = (i - m * (dper >> 1)) << 1;
         const float mu = s_stat[m], rs = s_stat[NB + m];
+        const bool rst = (rmask >> m) & 1u;
         float hn[2];
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
@@ -312,35 +356,43 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
           const float cp = (outb[(dper + d) * OB + m] - mu) * rs * p_gru[dper + d] + p_gru[4 * dper + d];
           const float cd = tanhf(r * cp);
           const float u = sigmoidf_((outb[(2 * dper + d) * OB + m] - mu) * rs * p_gru[2 * dper + d] + p_gru[5 * dper + d] - 1.f);
-          hn[j] = u * cd + (1.f - u) * hown[m * dper + d];
+          hn[j] = u * cd + (1.f - u) * (rst ? 0.f : hown[m * dper + d]);
           if (m >= Bv) hn[j] = 0.f;
-          hown[m * dper + d] = hn[j];
         }
         if (m < Bv) *reinterpret_cast<float2*>(a.x_rep + (row0 + m) * a.ld_xrep + d0 + dl) = make_float2(hn[0], hn[1]);
         *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, dl)) = __floats2bfloat162_rn(hn[0], hn[1]);
+        hnew[m * dper + dl] = hn[0];
+        hnew[m * dper + dl + 1] = hn[1];
       }
+      SDBG(15);
       fence_proxy_async();
       epi_bar();
+      SDBG(16);
       push_act(stage_a, (uint32_t)(dper >> 3) * BROW, smem_u32(xh), &act_bar[X_H], c, CL, ew);
-      SDBG(7);
+      SDBG(17);
+#pragma unroll 1
+      for (int e = et; e < Bv * dper; e += NT_EPI) {            // saved pre-LN gates (own rows of the three gates)
+        const int m = e / dper, dl = e - m * dper;
+        float* gp = a.gates_pre + (row0 + m) * 3 * D + d0 + dl;
+        gp[0] = outb[dl * OB + m]; gp[D] = outb[(dper + dl) * OB + m]; gp[2 * D] = outb[(2 * dper + dl) * OB + m];
+      }
+      { float* tmp = hown; hown = hnew; hnew = tmp; }          // (the x_gru store of this step, above, read the old buffer before the gates)
+      SDBG(18);
 
       // ================= P3: posterior hidden: own rows of Wr0[:, :D] . h' + (e_t . Wr0[:, D:]^T + b) =================
       mbar_wait(&acc_bar[1], par);
       tc_fence_after();
-      SDBG(8);
-      tmem_to_outb(tmem_base, col_r0, hper, outb, ew, lane);
+      SDBG(19);
+      tmem_to_outb(tmem_base, col_r0, hper, pl.seg[SEG_R0].m64, outb, s_ew, hper, ew, lane);
       epi_bar();
-#pragma unroll 1
-      for (int e = et; e < NB * hper; e += NT_EPI) { const int m = e / hper, hl = e - m * hper; outb[hl * OB + m] += s_ew[e]; }
-      epi_bar();
+      SDBG(20);
       stats_push(outb, hper, lnp2, &stat_bar[ST_HID], c, CL, ew, lane);
-#pragma unroll 1
-      for (int e = et; e < Bv * hper; e += NT_EPI) { const int m = e / hper, hl = e - m * hper; a.hidr_pre[(row0 + m) * Hh + h0 + hl] = outb[hl * OB + m]; }
-      if (t + 1 < a.T) fetch_ew(t + 1);
+      SDBG(21);
       mbar_wait(&stat_bar[ST_HID], par);
+      SDBG(22);
       stats_combine(lnp2, CL, hper, 1e-5f, s_stat, a.hidr_mean + row0, a.hidr_rstd + row0, c == 0 ? Bv : 0, ew, lane);
       epi_bar();
-      SDBG(9);
+      SDBG(23);
 #pragma unroll 1
       for (int i = et; i < NB * (hper >> 1); i += NT_EPI) {
         const int m = i / (hper >> 1), hl = (i - m * (hper >> 1)) << 1;
@@ -351,68 +403,104 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
         else { f0 = 0.f; f1 = 0.f; }
         *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, hl)) = __floats2bfloat162_rn(f0, f1);
       }
+      SDBG(24);
       fence_proxy_async();
       epi_bar();
+      SDBG(25);
       push_act(stage_a, (uint32_t)(hper >> 3) * BROW, smem_u32(xhid), &act_bar[X_HID], c, CL, ew);
-      SDBG(10);
+      SDBG(26);
+#pragma unroll 1
+      for (int e = et; e < Bv * hper; e += NT_EPI) { const int m = e / hper, hl = e - m * hper; a.hidr_pre[(row0 + m) * Hh + h0 + hl] = outb[hl * OB + m]; }
+      if (t + 1 < a.T) fetch_ew(t + 1);
+      SDBG(27);
 
       // ================= P4: posterior logits of the own categoricals, unimix, inverse-CDF sample =================
       mbar_wait(&acc_bar[2], par);
       tc_fence_after();
-      SDBG(11);
-      tmem_to_outb(tmem_base, col_r1, sper, outb, ew, lane);
+      SDBG(28);
+      tmem_to_outb(tmem_base, col_r1, sper, pl.seg[SEG_R1].m64, outp, nullptr, 0, ew, lane);
       epi_bar();
+      SDBG(29);
+      // one warp per (batch row, own categorical), lane = class (Kc <= 32); four pairs at a time so that their shuffle chains overlap
 #pragma unroll 1
-      for (int p = ew; p < npairs; p += EW) {                  // one warp per (batch row, own categorical); lane = class (Kc <= 32)
-        const int m = p / gper, gl = p - m * gper, g = c * gper + gl;
+      for (int pb = ew; pb < npairs; pb += 4 * EW) {
+        float raw[4], e1[4], lu[4], prob[4], mx[4], se[4];
+        int pm[4], pg[4];
         const bool on = lane < Kc;
-        const float raw = on ? (outb[(size_t)(gl * Kc + lane) * OB + m] + p_br1[gl * Kc + lane]) : -INFINITY;
-        const float mx = warp_max(raw);
-        const float e1 = on ? expf(raw - mx) : 0.f;
-        const float se = warp_sum(e1);
-        float lu = raw;
-        if (a.unimix > 0.f) {
-          const float pr = (1.f - a.unimix) * (e1 / se) + a.unimix / (float)Kc;
-          lu = on ? logf(fminf(fmaxf(pr, DV3_EPS32), 1.f - DV3_EPS32)) : -INFINITY;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int p = min(pb + j * EW, npairs - 1);
+          pm[j] = p / gper; pg[j] = p - pm[j] * gper;
+          raw[j] = on ? (outp[(size_t)(pg[j] * Kc + lane) * OB + pm[j]] + p_br1[pg[j] * Kc + lane]) : -INFINITY;
+          mx[j] = raw[j];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], o));
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { e1[j] = on ? expf(raw[j] - mx[j]) : 0.f; se[j] = e1[j]; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) se[j] += __shfl_xor_sync(0xffffffffu, se[j], o);
         }
         // Sampling probabilities: Categorical(logits = lu).probs = softmax(lu) = pm / sum(pm) up to fp32 round-off (the reference
         // renormalises log(pm) twice); with bf16 contractions upstream that round-off is far below the logits' own error, so the
         // draw uses pm directly and a warp prefix sum instead of the sequential cumsum of the fp32 kernels.
-        float prob = (a.unimix > 0.f) ? (on ? fminf(fmaxf((1.f - a.unimix) * (e1 / se) + a.unimix / (float)Kc, DV3_EPS32), 1.f - DV3_EPS32) : 0.f)
-                                      : (e1 / se);
-        prob = prob / warp_sum(prob);
-        int choice;
-        if (a.forced_idx) {
-          choice = __float_as_int(s_uu[p]);
-        } else {                                             // idx = #{k : cumsum_k(p) <= u}
-          float cs = prob;
+        float ps[4];
 #pragma unroll
-          for (int o = 1; o < 32; o <<= 1) { const float v = __shfl_up_sync(0xffffffffu, cs, o); if (lane >= o) cs += v; }
-          choice = __popc(__ballot_sync(0xffffffffu, on && cs <= s_uu[p]));
-          if (choice > Kc - 1) choice = Kc - 1;
+        for (int j = 0; j < 4; ++j) {
+          lu[j] = raw[j];
+          prob[j] = e1[j] / se[j];
+          if (a.unimix > 0.f) {
+            const float pr = fminf(fmaxf((1.f - a.unimix) * prob[j] + a.unimix / (float)Kc, DV3_EPS32), 1.f - DV3_EPS32);
+            lu[j] = on ? logf(pr) : -INFINITY;
+            prob[j] = on ? pr : 0.f;
+          }
+          ps[j] = prob[j];
         }
-        if (on) {
-          outb[(size_t)(gl * Kc + lane) * OB + m] = raw;
-          outl[(size_t)(gl * Kc + lane) * OB + m] = lu;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) ps[j] += __shfl_xor_sync(0xffffffffu, ps[j], o);
         }
-        if (lane == 0) idxo[p] = choice;
-        if (lane < CL) st_async_b32(mapa(smem_u32(idxf + g * NB + m), (uint32_t)lane), (uint32_t)choice, mapa(smem_u32(&idx_bar[0]), (uint32_t)lane));
+        float cs[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { prob[j] = prob[j] / ps[j]; cs[j] = prob[j]; }
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { const float v = __shfl_up_sync(0xffffffffu, cs[j], o); if (lane >= o) cs[j] += v; }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int p = pb + j * EW;
+          int choice;
+          if (a.forced_idx) {
+            choice = __float_as_int(s_uu[min(p, npairs - 1)]);
+          } else {                                           // idx = #{k : cumsum_k(p) <= u}
+            choice = __popc(__ballot_sync(0xffffffffu, on && cs[j] <= s_uu[min(p, npairs - 1)]));
+            if (choice > Kc - 1) choice = Kc - 1;
+          }
+          if (p < npairs) {
+            if (on) {
+              outp[(size_t)(pg[j] * Kc + lane) * OB + pm[j]] = raw[j];
+              outl[(size_t)(pg[j] * Kc + lane) * OB + pm[j]] = lu[j];
+            }
+            if (lane == 0) idxo[p] = choice;
+            if (lane < CL)
+              st_async_b32(mapa(smem_u32(idxf + (c * gper + pg[j]) * NB + pm[j]), (uint32_t)lane), (uint32_t)choice, mapa(smem_u32(&idx_bar[0]), (uint32_t)lane));
+          }
+        }
       }
-      epi_bar();
-      SDBG(12);
+      SDBG(30);
       if (t + 1 < a.T) fetch_uu(t + 1);
-      // global stores of the posterior of this step
-#pragma unroll 1
-      for (int e = et; e < Bv * sper; e += NT_EPI) {
-        const int m = e / sper, sl = e - m * sper, gl = sl / Kc;
-        a.post_raw[(row0 + m) * S + s0 + sl] = outb[sl * OB + m];
-        a.post_logits[(row0 + m) * S + s0 + sl] = outl[sl * OB + m];
-        a.latent[(row0 + m) * a.ld_lat + s0 + sl] = (idxo[m * gper + gl] == (sl - gl * Kc)) ? 1.f : 0.f;
-      }
-      for (int e = et; e < Bv * gper; e += NT_EPI) { const int m = e / gper, gl = e - m * gper; a.post_idx[(row0 + m) * G + c * gper + gl] = idxo[e]; }
-      SDBG(13);
-      epi_bar();                                               // idxo / outb / outl are rewritten by the next step
+      epi_bar();                                               // idxo / outp / outl complete before the next step reads / flushes them
+      SDBG(31);
     }
+    flush_posterior((size_t)(a.T - 1) * B + b0);
     tc_fence_before();
   }
 
@@ -426,7 +514,7 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------------
-bool build_plan(int D, int U, int Hh, int G, int Kc, int CL, Plan* pl) {
+bool build_plan(int D, int U, int Hh, int G, int Kc, int CL, int slot_max, Plan* pl) {
   if (CL < 1 || D % CL || U % CL || Hh % CL || G % CL) return false;
   const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc;
   if ((uper & 7) || (dper & 7) || (hper & 7) || (sper & 3) || Kc > 32 || (D & 15) || (U & 15) || (Hh & 15)) return false;
@@ -437,30 +525,65 @@ bool build_plan(int D, int U, int Hh, int G, int Kc, int CL, Plan* pl) {
   RowBlk gb[3] = {{0, dper}, {D, dper}, {2 * D, dper}};
   RowBlk hb[1] = {{0, hper}};
   RowBlk sb[1] = {{0, sper}};
-  if (plan_add_seg(*pl, 3 * dper, D, 0, 1, 0, 3, gb, 0, off16) != SEG_GH) return false;
-  if (plan_add_seg(*pl, 3 * dper, U, 0, 0, 0, 3, gb, D, off16) != SEG_GF) return false;
-  if (plan_add_seg(*pl, hper, D, gt * NB, 1, 0, 1, hb, 0, off16) != SEG_R0) return false;
-  if (plan_add_seg(*pl, sper, Hh, gt * NB + NB, 1, 0, 1, sb, 0, off16) != SEG_R1) return false;
+  if (plan_add_seg(*pl, slot_max, 3 * dper, D, 0, 1, 0, 3, gb, 0, off16) != SEG_GH) return false;
+  if (plan_add_seg(*pl, slot_max, 3 * dper, U, 0, 0, 0, 3, gb, D, off16) != SEG_GF) return false;
+  if (plan_add_seg(*pl, slot_max, hper, D, gt * NB, 1, 0, 1, hb, 0, off16) != SEG_R0) return false;
+  if (plan_add_seg(*pl, slot_max, sper, Hh, gt * NB + NB, 1, 0, 1, sb, 0, off16) != SEG_R1) return false;
+  pl->seg[SEG_GF].m64 = pl->seg[SEG_GH].m64;
   if (gt * NB + 2 * NB > 128) return false;
   pl->step_bytes = off16 * 16;
   return true;
 }
 
-size_t fixed_smem(const Dv3ScanFwdArgs* h, int CL) {
-  const int D = h->D, U = h->U, Hh = h->Hh, G = h->G, Kc = h->Kc;
+constexpr int T_MAX = 1024;      // s_rmask is sized for the launch's T; the plan selection reserves room for this many steps
+
+size_t fixed_smem(int D, int U, int Hh, int G, int Kc, int CL, int T) {
   const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc;
   auto r = [](size_t b) { return (b + 127) & ~(size_t)127; };
   auto mx = [](int x, int y) { return x > y ? x : y; };
   const int fmax = mx(mx(uper, dper), hper), rows_max = mx(mx(3 * dper, uper), mx(hper, sper)), npairs = NB * gper;
-  return r((size_t)(D >> 3) * BROW) + r((size_t)(U >> 3) * BROW) + r((size_t)(Hh >> 3) * BROW) + r((size_t)(fmax >> 3) * BROW) +
-         r((size_t)rows_max * OB * 4) + r((size_t)sper * OB * 4) + r((size_t)NB * dper * 4) + r((size_t)3 * CL * NB * 8) + r(2 * NB * 4) +
-         2 * r((size_t)G * NB * 4) + r((size_t)npairs * 4) + r((size_t)G * 4) + r((size_t)h->T * 4) + r((size_t)2 * uper * 4) +
+  return r((size_t)(D >> 3) * BROW) + r((size_t)(mx(U, Hh) >> 3) * BROW) + r((size_t)(fmax >> 3) * BROW) +
+         r((size_t)rows_max * OB * 4) + 2 * r((size_t)sper * OB * 4) + 2 * r((size_t)NB * dper * 4) + r((size_t)3 * CL * NB * 8) + r(2 * NB * 4) +
+         r((size_t)G * NB * 4) + r((size_t)npairs * 4) + r((size_t)G * 4) + r((size_t)T * 4) + r((size_t)2 * uper * 4) +
          r((size_t)6 * dper * 4) + r((size_t)2 * hper * 4) + r((size_t)sper * 4) + r((size_t)NB * uper * 4) + r((size_t)NB * hper * 4) +
-         r((size_t)npairs * 4) + 128 /* alignment of the dynamic segment */;
+         r((size_t)npairs * 4) + 2048 + 128 /* ring slack */ + 128 /* alignment of the dynamic segment */;
 }
 
-// xh | xf | xhid must be contiguous for the set-up loop that zeroes them: true when every size is a multiple of 128 B (BROW = 256)
-int launch_tc(FwdK& k, int nclusters, size_t smem_bytes, cudaStream_t stream, bool probe_only) {
+struct Choice { int CL, nslots, tab_smem; size_t smem; };
+// The one place that decides cluster size, ring slot size / depth and whether the gather table is resident: the stream size query,
+// the packing kernel and the launch must all see the same plan.  Preference: 16 CTAs over 8; the largest slots that still leave a
+// ring of >= 4 of them (then >= 3); the resident table if at least 64 KB of ring remain next to it.
+bool select_plan(int D, int U, int Hh, int G, int Kc, int max_smem, Plan* pl, Choice* ch) {
+  const bool table_ok = !getenv("DV3_SCAN_NO_TABLE");
+  for (int CL = 16; CL >= 8; CL >>= 1) {
+    const size_t tab_bytes = ((size_t)G * Kc * (U / CL) * 2 + 127) & ~(size_t)127;
+    for (int tab = table_ok ? 1 : 0; tab >= 0; --tab) {
+      for (int want = 4; want >= (tab ? 4 : 2); --want) {
+        for (int slot_max = 32768; slot_max >= 4096; slot_max >>= 1) {
+          if (!build_plan(D, U, Hh, G, Kc, CL, slot_max, pl)) continue;
+          const size_t fixed = fixed_smem(D, U, Hh, G, Kc, CL, T_MAX);
+          const long long room = (long long)max_smem - (long long)fixed - 512 - (tab ? (long long)tab_bytes : 0);
+          if (room < (tab ? 49152 : 0)) break;
+          int nslots = (int)(room / (long long)pl->slot_bytes);
+          if (nslots < want) continue;
+          if (nslots > 12) nslots = 12;
+          ch->CL = CL; ch->nslots = nslots; ch->tab_smem = tab;
+          ch->smem = fixed + (tab ? tab_bytes : 0) + (size_t)nslots * pl->slot_bytes + (((size_t)(2 * nslots + 16) * 8 + 127) & ~(size_t)127);
+          return true;
+        }
+      }
+    }
+  }
+  return false;
+}
+int device_max_smem() {
+  int dev = 0, max_smem = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  return max_smem;
+}
+
+int launch_tc(FwdK& k, int nclusters, size_t smem_bytes, cudaStream_t stream) {
   auto kern = rssm_observe_fwd_tc_kernel;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) { cudaGetLastError(); return DV3_ERR_UNSUPPORTED; }
@@ -482,8 +605,7 @@ int launch_tc(FwdK& k, int nclusters, size_t smem_bytes, cudaStream_t stream, bo
   cfg.numAttrs = 1;
   int nmax = 0;
   e = cudaOccupancyMaxActiveClusters(&nmax, kern, &cfg);
-  if (e != cudaSuccess || nmax < nclusters) { cudaGetLastError(); return DV3_ERR_UNSUPPORTED; }   // all clusters must be co-resident? no: independent
-  if (probe_only) return DV3_OK;
+  if (e != cudaSuccess || nmax < 1) { cudaGetLastError(); return DV3_ERR_UNSUPPORTED; }   // clusters are independent: they need not be co-resident
   e = cudaLaunchKernelEx(&cfg, kern, k);
   if (e != cudaSuccess) return (int)e;
   return DV3_OK;
@@ -494,13 +616,11 @@ int launch_tc(FwdK& k, int nclusters, size_t smem_bytes, cudaStream_t stream, bo
 // Plan of the forward scan's weight stream for a shape (the same function sizes the buffer, drives the packing kernel and the scan).
 extern "C" int dv3_scan_tc_fwd_config(int D, int U, int Hh, int G, int Kc, int* cluster_size, size_t* stream_bytes) {
   Plan pl;
-  for (int CL = 16; CL >= 8; CL >>= 1) {
-    if (!build_plan(D, U, Hh, G, Kc, CL, &pl)) continue;
-    if (cluster_size) *cluster_size = CL;
-    if (stream_bytes) *stream_bytes = (size_t)CL * pl.step_bytes;
-    return DV3_OK;
-  }
-  return DV3_ERR_UNSUPPORTED;
+  Choice ch;
+  if (!select_plan(D, U, Hh, G, Kc, device_max_smem(), &pl, &ch)) return DV3_ERR_UNSUPPORTED;
+  if (cluster_size) *cluster_size = ch.CL;
+  if (stream_bytes) *stream_bytes = (size_t)ch.CL * pl.step_bytes;
+  return DV3_OK;
 }
 
 // ---- packing: fp32 weights -> per-CTA, per-step bf16 stream in the MMA's shared-memory image -----------------------------------
@@ -545,9 +665,9 @@ extern "C" int dv3_scan_tc_fwd_pack(int D, int U, int Hh, int G, int Kc, const f
                                     const float* Wr1, int ld_wr1, void* dst, void* stream) {
   if (!Wgru || !Wr0 || !Wr1 || !dst) return DV3_ERR_ARG;
   PackK p;
-  int CL = 0;
-  for (CL = 16; CL >= 8; CL >>= 1) if (build_plan(D, U, Hh, G, Kc, CL, &p.plan)) break;
-  if (CL < 8) return DV3_ERR_UNSUPPORTED;
+  Choice ch;
+  if (!select_plan(D, U, Hh, G, Kc, device_max_smem(), &p.plan, &ch)) return DV3_ERR_UNSUPPORTED;
+  const int CL = ch.CL;
   p.CL = CL;
   p.dst = reinterpret_cast<uint8_t*>(dst);
   p.src[SEG_GH] = {Wgru, ld_wgru, 1};
@@ -565,33 +685,25 @@ extern "C" int dv3_rssm_observe_fwd_tc(const Dv3ScanFwdArgs* h, const Dv3ScanTcE
       (h->ld_xgru & 1) || (h->ld_xrep & 1) || ((uintptr_t)h->x_gru & 7) || ((uintptr_t)h->x_rep & 7) || ((uintptr_t)h->hidr & 7) || (h->D & 1))
     return DV3_ERR_UNSUPPORTED;
   if (!x->stream || !x->WmlpzT || !x->aW || ((uintptr_t)x->stream & 15)) return DV3_ERR_UNSUPPORTED;
-  int dev = 0, max_smem = 0;
-  cudaError_t e = cudaGetDevice(&dev);
-  if (e != cudaSuccess) return (int)e;
-  cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (h->T > T_MAX) return DV3_ERR_UNSUPPORTED;
+  const int max_smem = device_max_smem();
   FwdK* k = new FwdK;
+  Choice ch;
   int rc = DV3_ERR_UNSUPPORTED;
-  for (int CL = 16; CL >= 8; CL >>= 1) {
-    if (!build_plan(h->D, h->U, h->Hh, h->G, h->Kc, CL, &k->plan)) continue;
+  if (select_plan(h->D, h->U, h->Hh, h->G, h->Kc, max_smem, &k->plan, &ch)) {
     k->a = *h;
     k->stream = reinterpret_cast<const uint8_t*>(x->stream);
     k->WmlpzT = x->WmlpzT;
     k->aW = x->aW;
-    k->CL = CL;
+    k->CL = ch.CL;
+    k->nslots = ch.nslots;
+    k->tab_smem = (ch.tab_smem && !((uintptr_t)x->WmlpzT & 7) && !(h->U & 1)) ? 1 : 0;
     k->dbg = (getenv("DV3_SCAN_DEBUG") && h->scratch && h->scratch_bytes >= 64 * sizeof(long long)) ? reinterpret_cast<long long*>(h->scratch) : nullptr;
-    const size_t fixed = fixed_smem(h, CL) + 2048 + 128 /* ring slack + alignment */;
-    int nslots = ((long long)max_smem - (long long)fixed - 512) / (long long)k->plan.slot_bytes;
-    if (nslots > 12) nslots = 12;
-    if (nslots < 2) continue;
-    const size_t smem = fixed + (size_t)nslots * k->plan.slot_bytes + (size_t)(2 * nslots + 16) * 8 + 128;
-    k->nslots = nslots;
     const int nclusters = (h->B + NB - 1) / NB;
     if (getenv("DV3_SCAN_DEBUG"))
-      fprintf(stderr, "[dv3 tc scan] CL=%d clusters=%d slots=%d x %u B, step stream %u B/CTA, %d chunks, smem %zu KB (max %d KB)\n", CL, nclusters, nslots,
-              k->plan.slot_bytes, k->plan.step_bytes, k->plan.nchunks, smem / 1024, max_smem / 1024);
-    if (launch_tc(*k, nclusters, smem, (cudaStream_t)stream_, true) != DV3_OK) continue;
-    rc = launch_tc(*k, nclusters, smem, (cudaStream_t)stream_, false);
-    break;
+      fprintf(stderr, "[dv3 tc scan] CL=%d clusters=%d slots=%d x %u B, table %d, step stream %u B/CTA, %d chunks, smem %zu KB (max %d KB)\n", ch.CL,
+              nclusters, ch.nslots, k->plan.slot_bytes, k->tab_smem, k->plan.step_bytes, k->plan.nchunks, ch.smem / 1024, max_smem / 1024);
+    rc = launch_tc(*k, nclusters, ch.smem, (cudaStream_t)stream_);
   }
   delete k;
   return rc;

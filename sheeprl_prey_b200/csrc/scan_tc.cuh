@@ -28,9 +28,8 @@ constexpr int OB = NB + 1;             // row stride of the [feature][batch] sta
 constexpr int EW = 8;                  // epilogue warps
 constexpr int NT_EPI = EW * 32;
 constexpr int NT = 64 + NT_EPI;        // warp 0 producer, warp 1 MMA issuer, warps 2..9 epilogue
-constexpr int MAX_CHUNKS = 160;
+constexpr int MAX_CHUNKS = 200;
 constexpr int MAX_SEG = 6;
-constexpr int SLOT_MAX_BYTES = 32 * 1024;
 constexpr int BROW = NB * 16;          // bytes of one 8-wide k chunk of an activation operand (NB rows x 16 B)
 
 // One bulk copy of the weight stream = `nmma` MMAs of one 128-row tile.
@@ -46,7 +45,7 @@ struct Chunk {
 };
 struct RowBlk { int base, size; };     // local rows [start, start + size) -> weight rows base + cta * size + (j - start)
 struct Seg {
-  int rows, ntiles, K, chunk_begin, chunk_end, tmem_col, fresh;
+  int rows, ntiles, K, chunk_begin, chunk_end, tmem_col, fresh, m64;   // m64: one tile of <= 64 rows, issued as M = 64 MMAs
   int nblk; RowBlk blk[3]; int col0;   // packing: which rows / columns of the source matrix
 };
 struct Plan {
@@ -136,8 +135,11 @@ __device__ __forceinline__ uint64_t desc_ns(uint32_t addr, uint32_t lbo_bytes) {
   d |= (uint64_t)1 << 46;
   return d;
 }
-__device__ __forceinline__ void umma_n16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accum) {
-  constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NB >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+// instruction descriptor: fp32 accumulate, bf16 x bf16, both K-major, N = NB, M = 128 or 64
+__device__ __forceinline__ uint32_t idesc_n16(int M) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NB >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_n16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
   asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_d), "l"(adesc),
                "l"(bdesc), "r"(idesc), "r"(accum) : "memory");
 }
@@ -183,6 +185,7 @@ __device__ __forceinline__ void produce_seg(const Plan& pl, int si, const uint8_
 __device__ __forceinline__ void mma_seg(const Plan& pl, int si, uint32_t bbuf, uint32_t tmem_base, const Ring& rg, RingPos& pos) {
   const int cb = pl.seg[si].chunk_begin, ce = pl.seg[si].chunk_end;
   const uint32_t col = (uint32_t)pl.seg[si].tmem_col, fresh = (uint32_t)pl.seg[si].fresh;
+  const uint32_t idesc = idesc_n16(pl.seg[si].m64 ? 64 : 128);
 #pragma unroll 1
   for (int ci = cb; ci < ce; ++ci) {
     const uint32_t nmma = pl.c[ci].nmma, lbo16 = pl.c[ci].lbo16, bk8 = pl.c[ci].b_k8, tile = pl.c[ci].tile, k0 = pl.c[ci].k0;
@@ -195,7 +198,7 @@ __device__ __forceinline__ void mma_seg(const Plan& pl, int si, uint32_t bbuf, u
     uint32_t acc = (fresh && k0 == 0) ? 0u : 1u;
 #pragma unroll 2
     for (uint32_t j = 0; j < nmma; ++j) {
-      if (elect_one()) umma_n16(dcol, ad0 + (uint64_t)(j * astep), bd0 + (uint64_t)(j * bstep), acc);
+      if (elect_one()) umma_n16(dcol, ad0 + (uint64_t)(j * astep), bd0 + (uint64_t)(j * bstep), idesc, acc);
       acc = 1u;
     }
     if (elect_one()) umma_commit(&rg.empty[pos.slot]);
@@ -205,8 +208,23 @@ __device__ __forceinline__ void mma_seg(const Plan& pl, int si, uint32_t bbuf, u
 }
 // epilogue warps: accumulator of a segment (rows x NB) -> outb[row * OB + m].  ew = epilogue warp 0..7 (hardware warp ew + 2: TMEM
 // lane quadrant (ew + 2) % 4, column half ew / 4).
-__device__ __forceinline__ void tmem_to_outb(uint32_t tmem_base, int col, int rows, float* outb, int ew, int lane) {
+// An M = 64 accumulator keeps row r in TMEM lane 32 (r / 16) + r % 16 (profiles/r02a_probe_umma.md).
+// `add` (optional): add[m * add_ld + row] is added on the way (a hoisted, batched part of the same pre-activation).
+__device__ __forceinline__ void tmem_to_outb(uint32_t tmem_base, int col, int rows, int m64, float* outb, const float* add, int add_ld, int ew, int lane) {
   const int q = (ew + 2) & 3, half = ew >> 2;
+  if (m64) {
+    if (16 * q < rows) {
+      float v[8];
+      tmem_ld8(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(col + 8 * half), v);
+      const int r = 16 * q + lane;
+      if (lane < 16 && r < rows) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) outb[r * OB + 8 * half + j] = v[j] + (add ? add[(8 * half + j) * add_ld + r] : 0.f);
+      }
+    }
+    tc_fence_before();
+    return;
+  }
 #pragma unroll 1
   for (int r0 = 32 * q; r0 < rows; r0 += 128) {
     float v[8];
@@ -214,7 +232,7 @@ __device__ __forceinline__ void tmem_to_outb(uint32_t tmem_base, int col, int ro
     const int r = r0 + lane;
     if (r < rows) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) outb[r * OB + 8 * half + j] = v[j];
+      for (int j = 0; j < 8; ++j) outb[r * OB + 8 * half + j] = v[j] + (add ? add[(8 * half + j) * add_ld + r] : 0.f);
     }
   }
   tc_fence_before();
@@ -285,17 +303,18 @@ __device__ __forceinline__ uint32_t b_off(int m, int k) { return (uint32_t)((k >
 #endif  // __CUDACC__
 
 // ---- host: plan of the weight stream ----------------------------------------------------------------------------------------------
-inline int plan_add_seg(Plan& pl, int rows, int K, int tmem_col, int fresh, int b_k8_base, int nblk, const RowBlk* blk, int col0, uint32_t& off16) {
+inline int plan_add_seg(Plan& pl, int slot_max_bytes, int rows, int K, int tmem_col, int fresh, int b_k8_base, int nblk, const RowBlk* blk, int col0,
+                        uint32_t& off16) {
   if (pl.nseg >= MAX_SEG || rows <= 0 || (K & 15)) return -1;
   Seg& s = pl.seg[pl.nseg];
-  s.rows = rows; s.K = K; s.ntiles = (rows + 127) / 128; s.tmem_col = tmem_col; s.fresh = fresh;
+  s.rows = rows; s.K = K; s.ntiles = (rows + 127) / 128; s.tmem_col = tmem_col; s.fresh = fresh; s.m64 = rows <= 64 ? 1 : 0;
   s.nblk = nblk; for (int i = 0; i < nblk; ++i) s.blk[i] = blk[i];
   s.col0 = col0;
   s.chunk_begin = pl.nchunks;
   // chunk depth: as deep as a slot allows for the widest tile (fewer, larger copies: ~160 clk of producer time per copy)
   const int rows_pad_max = ((rows < 128 ? rows : 128) + 7) & ~7;
   int KC = 256;
-  while (KC > 16 && rows_pad_max * KC * 2 > SLOT_MAX_BYTES) KC >>= 1;
+  while (KC > 16 && rows_pad_max * KC * 2 > slot_max_bytes) KC >>= 1;
   for (int k0 = 0; k0 < K; k0 += KC) {
     const int kc = (K - k0 < KC) ? (K - k0) : KC;
     for (int t = 0; t < s.ntiles; ++t) {

@@ -309,7 +309,9 @@ def test_fused_bf16_scan_matches_fp32_scan(cuda_ops, size, B, T, obs, acts, kern
                  "hidr_mean", "hidr_rstd", "post_raw", "post_logits", "latent", "prior_logits"):
         worst[name] = rel(getattr(eng, name), getattr(ref, name))
     assert max(worst.values()) < 2e-2, worst
-    assert worst["feat_pre"] < 2e-3, worst                # fp32 row gather; only the hoisted action projection is a bf16 contraction
+    # feat_pre = one-hot row gather + hoisted action projection: the tcgen05 kernel gathers from a bf16 table (a contraction with bf16
+    # operands like every other one in this mode), the mma.sync kernel from the fp32 weights
+    assert worst["feat_pre"] < (1e-2 if kernel == "tcgen05" else 2e-3), worst
 
 
 @pytest.mark.parametrize("size,B,T,obs,acts", [("S", 16, 64, 14, [100]), ("XS", 16, 20, 4, [2]), ("S", 5, 9, 14, [7, 3])])
