@@ -70,7 +70,6 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
   float* hown = reinterpret_cast<float*>(take((size_t)NB * dper * 4));       // own fp32 slice of h  [m][dl] (double-buffered: the saved
   float* hnew = reinterpret_cast<float*>(take((size_t)NB * dper * 4));       // h_in of a step is stored to global after its gates ran)
   float* lnp = reinterpret_cast<float*>(take((size_t)3 * CL * NB * 8));      // [3 exchanges][CL][NB] (mean, M2)
-  float* s_stat = reinterpret_cast<float*>(take(2 * NB * 4));
   int* idxf = reinterpret_cast<int*>(take((size_t)G * NB * 4));              // sampled z indices of all groups [g][m] (peers write)
   int* idxo = reinterpret_cast<int*>(take((size_t)npairs * 4));              // own sampled indices [m][gl]
   int* s_zreset = reinterpret_cast<int*>(take((size_t)G * 4));
@@ -222,23 +221,66 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
     // global stores of the posterior sampled in the step whose first row is prow0 (outp / outl / idxo live until the next P4)
     auto flush_posterior = [&](size_t prow0) {
 #pragma unroll 1
-      for (int e = et; e < Bv * sper; e += NT_EPI) {
-        const int m = e / sper, sl = e - m * sper, gl = sl / Kc;
-        a.post_raw[(prow0 + m) * S + s0 + sl] = outp[sl * OB + m];
-        a.post_logits[(prow0 + m) * S + s0 + sl] = outl[sl * OB + m];
-        a.latent[(prow0 + m) * a.ld_lat + s0 + sl] = (idxo[m * gper + gl] == (sl - gl * Kc)) ? 1.f : 0.f;
+      for (int m = ew; m < Bv; m += EW) {
+        for (int sl = lane; sl < sper; sl += 32) {
+          const int gl = (int)__umulhi((uint32_t)sl, 0xFFFFFFFFu / (uint32_t)Kc + 1u);
+          a.post_raw[(prow0 + m) * S + s0 + sl] = outp[sl * OB + m];
+          a.post_logits[(prow0 + m) * S + s0 + sl] = outl[sl * OB + m];
+          a.latent[(prow0 + m) * a.ld_lat + s0 + sl] = (idxo[m * gper + gl] == (sl - gl * Kc)) ? 1.f : 0.f;
+        }
+        if (lane < gper) a.post_idx[(prow0 + m) * G + c * gper + lane] = idxo[m * gper + lane];
       }
-      for (int e = et; e < Bv * gper; e += NT_EPI) { const int m = e / gper, gl = e - m * gper; a.post_idx[(prow0 + m) * G + c * gper + gl] = idxo[e]; }
     };
     fetch_aw(0);
     fetch_ew(0);
     fetch_uu(0);
+
+    // Thread <-> data mapping of the element-wise work: epilogue warp ew owns batch rows 2 ew and 2 ew + 1, one half-warp each
+    // (hl = half, l16 = lane in the half); the 16 lanes stride over the features of the row.  The LayerNorm partials, their
+    // cluster-wide combination and the normalisation of a row then live in the registers of one half-warp: no shared-memory round
+    // trip and no block barrier between them.  Global stores use one warp per row (128 B segments).
+    const int hl = lane >> 4, l16 = lane & 15, mrow = 2 * ew + hl;
+    const uint32_t fd_kc = 0xFFFFFFFFu / (uint32_t)Kc + 1u;      // n / Kc = __umulhi(n, fd_kc) for n * Kc < 2^32
+
+    // mean / rstd of batch row mrow over a vector spread over the cluster: own values vals[j * OB + mrow], j < n.
+    // Partials (mean, M2) go to lnp[c][m] of every peer (st.async, completes on the peer's barrier); after the wait the CL partials
+    // are merged with Chan's formula (equal counts).  Returns the statistics in every lane of the half-warp.
+    auto row_stats = [&](const float* vals, int n, float* lnp_x, uint64_t* bar, uint32_t parity, float eps, float* gmean, float* grstd,
+                         float& mean_out, float& rstd_out) {
+      float sx = 0.f;
+      for (int j = l16; j < n; j += 16) sx += vals[j * OB + mrow];
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) sx += __shfl_xor_sync(0xffffffffu, sx, o);
+      const float mu_c = sx / (float)n;
+      float q = 0.f;
+      for (int j = l16; j < n; j += 16) { const float d = vals[j * OB + mrow] - mu_c; q = fmaf(d, d, q); }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+      if (l16 < CL) st_async_f2(mapa(smem_u32(lnp_x + (c * NB + mrow) * 2), (uint32_t)l16), mu_c, q, mapa(smem_u32(bar), (uint32_t)l16));
+      mbar_wait(bar, parity);
+      const float2 pc = (l16 < CL) ? reinterpret_cast<const float2*>(lnp_x)[l16 * NB + mrow] : make_float2(0.f, 0.f);
+      float sm = pc.x;
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) sm += __shfl_xor_sync(0xffffffffu, sm, o);
+      const float mu = sm / (float)CL;
+      const float dm = pc.x - mu;
+      float m2 = (l16 < CL) ? (pc.y + (float)n * dm * dm) : 0.f;
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) m2 += __shfl_xor_sync(0xffffffffu, m2, o);
+      const float rs = rsqrtf(m2 / (float)(n * CL) + eps);
+      if (c == 0 && l16 == 0 && mrow < Bv) { gmean[mrow] = mu; grstd[mrow] = rs; }
+      mean_out = mu; rstd_out = rs;
+    };
+    // bf16-mode activations: exp / divide through the fast paths (error ~1e-6, far below the bf16 rounding of the contractions)
+    auto fsigmoid = [](float x) { return __fdividef(1.f, 1.f + __expf(-x)); };
+    auto ftanh = [](float x) { const float e = __expf(-2.f * fabsf(x)); return copysignf(__fdividef(1.f - e, 1.f + e), x); };
 
 #pragma unroll 1
     for (int t = 0; t < a.T; ++t) {
       const uint32_t par = (uint32_t)t & 1u;
       const size_t row0 = (size_t)t * B + b0;
       const uint32_t rmask = s_rmask[t];
+      const bool rst = (rmask >> mrow) & 1u;                     // reset rows (agent.py:379-384): z = mode(transition(0)), h = 0
       SDBG(0);
       // ================= P0: arm this step's receive barriers; wait for z_{t-1} =================
       if (et == 0) {
@@ -251,231 +293,198 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
       cp_async_wait_all();
       epi_bar();                                                           // s_aw / s_ew / s_uu landed (other threads' cp.async)
       SDBG(1);
-      // reset rows (agent.py:379-384) use z = mode(transition(0)) and h = 0: applied where idxf / hown are read
 #define ZIDX(g, m) ((((rmask) >> (m)) & 1u) ? s_zreset[(g)] : idxf[(g) * NB + (m)])
       // ================= P1: feat = SiLU(LN(Wmlp . [z, a])) -- one-hot gather + hoisted action projection =================
       if (tab) {
 #pragma unroll 1
-        for (int i = et; i < NB * (uper >> 1); i += NT_EPI) {     // two adjacent features per thread, G independent 4 B loads
-          const int m = i / (uper >> 1), ul = (i - m * (uper >> 1)) << 1;
-          float a0 = s_aw[m * uper + ul], a1 = s_aw[m * uper + ul + 1];
+        for (int ul = 2 * l16; ul < uper; ul += 32) {             // two adjacent features per lane, G independent 4 B loads
+          float a0 = s_aw[mrow * uper + ul], a1 = s_aw[mrow * uper + ul + 1];
           const __nv_bfloat16* tcol = tab + ul;
 #pragma unroll 8
           for (int g = 0; g < G; ++g) {
-            const float2 w = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(tcol + (g * Kc + ZIDX(g, m)) * uper));
+            const int zi = rst ? s_zreset[g] : idxf[g * NB + mrow];
+            const float2 w = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(tcol + (g * Kc + zi) * uper));
             a0 += w.x; a1 += w.y;
           }
-          outb[ul * OB + m] = a0;
-          outb[(ul + 1) * OB + m] = a1;
+          outb[ul * OB + mrow] = a0;
+          outb[(ul + 1) * OB + mrow] = a1;
         }
       } else {
 #pragma unroll 1
-        for (int e = et; e < NB * uper; e += NT_EPI) {
-          const int m = e / uper, ul = e - m * uper;
-          float acc = s_aw[e];
+        for (int ul = l16; ul < uper; ul += 16) {
+          float acc = s_aw[mrow * uper + ul];
           const float* wcol = k.WmlpzT + u0 + ul;
 #pragma unroll 1
           for (int g0 = 0; g0 < G; g0 += 16) {                    // 16 independent row gathers in flight
             float v[16];
 #pragma unroll
-            for (int q = 0; q < 16; ++q) v[q] = (g0 + q < G) ? __ldg(wcol + (size_t)((g0 + q) * Kc + ZIDX(g0 + q, m)) * U) : 0.f;
+            for (int q = 0; q < 16; ++q) v[q] = (g0 + q < G) ? __ldg(wcol + (size_t)((g0 + q) * Kc + (rst ? s_zreset[g0 + q] : idxf[(g0 + q) * NB + mrow])) * U) : 0.f;
 #pragma unroll
             for (int q = 0; q < 16; ++q) acc += v[q];
           }
-          outb[ul * OB + m] = acc;
+          outb[ul * OB + mrow] = acc;
         }
       }
-      epi_bar();
+      __syncwarp();
       SDBG(2);
-      stats_push(outb, uper, lnp0, &stat_bar[ST_FEAT], c, CL, ew, lane);
+      float mu, rs;
+      row_stats(outb, uper, lnp0, &stat_bar[ST_FEAT], par, 1e-3f, a.feat_mean + row0, a.feat_rstd + row0, mu, rs);
       SDBG(3);
-      mbar_wait(&stat_bar[ST_FEAT], par);
-      SDBG(4);
-      stats_combine(lnp0, CL, uper, 1e-3f, s_stat, a.feat_mean + row0, a.feat_rstd + row0, c == 0 ? Bv : 0, ew, lane);
-      epi_bar();
-      SDBG(5);
 #pragma unroll 1
-      for (int i = et; i < NB * (uper >> 1); i += NT_EPI) {     // two features per thread -> one 4 B store into the operand layout
-        const int m = i / (uper >> 1), ul = (i - m * (uper >> 1)) << 1;
-        const float mu = s_stat[m], rs = s_stat[NB + m];
-        float f0 = siluf_((outb[ul * OB + m] - mu) * rs * p_mlp[ul] + p_mlp[uper + ul]);
-        float f1 = siluf_((outb[(ul + 1) * OB + m] - mu) * rs * p_mlp[ul + 1] + p_mlp[uper + ul + 1]);
-        if (m < Bv) *reinterpret_cast<float2*>(a.x_gru + (row0 + m) * a.ld_xgru + D + u0 + ul) = make_float2(f0, f1);
+      for (int ul = 2 * l16; ul < uper; ul += 32) {              // -> one 4 B store into the operand layout
+        float f0 = (outb[ul * OB + mrow] - mu) * rs * p_mlp[ul] + p_mlp[uper + ul];
+        float f1 = (outb[(ul + 1) * OB + mrow] - mu) * rs * p_mlp[ul + 1] + p_mlp[uper + ul + 1];
+        f0 *= fsigmoid(f0); f1 *= fsigmoid(f1);
+        if (mrow < Bv) *reinterpret_cast<float2*>(a.x_gru + (row0 + mrow) * a.ld_xgru + D + u0 + ul) = make_float2(f0, f1);
         else { f0 = 0.f; f1 = 0.f; }
-        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, ul)) = __floats2bfloat162_rn(f0, f1);
+        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(mrow, ul)) = __floats2bfloat162_rn(f0, f1);
       }
-      SDBG(6);
       fence_proxy_async();
       epi_bar();
-      SDBG(7);
+      SDBG(4);
       push_act(stage_a, (uint32_t)(uper >> 3) * BROW, smem_u32(xf), &act_bar[X_FEAT], c, CL, ew);
-      SDBG(8);
+      SDBG(5);
       // while the slices travel and the MMA warp contracts: saved inputs of the step (one-hot z_in of the own categoricals, h_in of
       // the own units), the pre-LN feature, the posterior of the PREVIOUS step, next step's action projection
 #pragma unroll 1
-      for (int i = et; i < Bv * (sper >> 2); i += NT_EPI) {
-        const int m = i / (sper >> 2), sl = (i - m * (sper >> 2)) << 2, sc_ = s0 + sl, g = sc_ / Kc, kk = sc_ - g * Kc, ch = ZIDX(g, m);
-        *reinterpret_cast<float4*>(a.x_mlp + (row0 + m) * a.ld_xmlp + sc_) =
-            make_float4(ch == kk ? 1.f : 0.f, ch == kk + 1 ? 1.f : 0.f, ch == kk + 2 ? 1.f : 0.f, ch == kk + 3 ? 1.f : 0.f);
+      for (int m = ew; m < Bv; m += EW) {
+        const bool rm = (rmask >> m) & 1u;
+        for (int q = lane; q < (sper >> 2); q += 32) {
+          const int sc_ = s0 + 4 * q, g = (int)__umulhi((uint32_t)sc_, fd_kc), kk = sc_ - g * Kc, ch = rm ? s_zreset[g] : idxf[g * NB + m];
+          *reinterpret_cast<float4*>(a.x_mlp + (row0 + m) * a.ld_xmlp + sc_) =
+              make_float4(ch == kk ? 1.f : 0.f, ch == kk + 1 ? 1.f : 0.f, ch == kk + 2 ? 1.f : 0.f, ch == kk + 3 ? 1.f : 0.f);
+        }
+        for (int dl = lane; dl < dper; dl += 32) a.x_gru[(row0 + m) * a.ld_xgru + d0 + dl] = rm ? 0.f : hown[m * dper + dl];
+        for (int ul = lane; ul < uper; ul += 32) a.feat_pre[(row0 + m) * U + u0 + ul] = outb[ul * OB + m];
       }
-#pragma unroll 1
-      for (int e = et; e < Bv * dper; e += NT_EPI) {
-        const int m = e / dper, dl = e - m * dper;
-        a.x_gru[(row0 + m) * a.ld_xgru + d0 + dl] = ((rmask >> m) & 1u) ? 0.f : hown[e];
-      }
-#pragma unroll 1
-      for (int e = et; e < Bv * uper; e += NT_EPI) { const int m = e / uper, ul = e - m * uper; a.feat_pre[(row0 + m) * U + u0 + ul] = outb[ul * OB + m]; }
       if (t > 0) flush_posterior(row0 - B);
       if (t + 1 < a.T) fetch_aw(t + 1);
-      SDBG(9);
+      SDBG(6);
 
       // ================= P2: GRU gates: own rows {d, D+d, 2D+d} of Wgru . [h, feat] =================
       mbar_wait(&acc_bar[0], par);
       tc_fence_after();
-      SDBG(10);
+      SDBG(7);
       tmem_to_outb(tmem_base, col_g, 3 * dper, pl.seg[SEG_GH].m64, outb, nullptr, 0, ew, lane);          // outb row = gate * dper + dl
       epi_bar();
-      SDBG(11);
-      stats_push(outb, 3 * dper, lnp1, &stat_bar[ST_GRU], c, CL, ew, lane);
-      SDBG(12);
-      mbar_wait(&stat_bar[ST_GRU], par);
-      SDBG(13);
-      stats_combine(lnp1, CL, 3 * dper, 1e-5f, s_stat, a.gru_mean + row0, a.gru_rstd + row0, c == 0 ? Bv : 0, ew, lane);
-      epi_bar();
-      SDBG(14);
+      SDBG(8);
+      row_stats(outb, 3 * dper, lnp1, &stat_bar[ST_GRU], par, 1e-5f, a.gru_mean + row0, a.gru_rstd + row0, mu, rs);
+      SDBG(9);
 #pragma unroll 1
-      for (int i = et; i < NB * (dper >> 1); i += NT_EPI) {
-        const int m = i / (dper >> 1), dl = (i - m * (dper >> 1)) << 1;
-        const float mu = s_stat[m], rs = s_stat[NB + m];
-        const bool rst = (rmask >> m) & 1u;
+      for (int dl = 2 * l16; dl < dper; dl += 32) {
         float hn[2];
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
           const int d = dl + j;
-          const float r = sigmoidf_((outb[d * OB + m] - mu) * rs * p_gru[d] + p_gru[3 * dper + d]);
-          const float cp = (outb[(dper + d) * OB + m] - mu) * rs * p_gru[dper + d] + p_gru[4 * dper + d];
-          const float cd = tanhf(r * cp);
-          const float u = sigmoidf_((outb[(2 * dper + d) * OB + m] - mu) * rs * p_gru[2 * dper + d] + p_gru[5 * dper + d] - 1.f);
-          hn[j] = u * cd + (1.f - u) * (rst ? 0.f : hown[m * dper + d]);
-          if (m >= Bv) hn[j] = 0.f;
+          const float r = fsigmoid((outb[d * OB + mrow] - mu) * rs * p_gru[d] + p_gru[3 * dper + d]);
+          const float cp = (outb[(dper + d) * OB + mrow] - mu) * rs * p_gru[dper + d] + p_gru[4 * dper + d];
+          const float cd = ftanh(r * cp);
+          const float u = fsigmoid((outb[(2 * dper + d) * OB + mrow] - mu) * rs * p_gru[2 * dper + d] + p_gru[5 * dper + d] - 1.f);
+          hn[j] = u * cd + (1.f - u) * (rst ? 0.f : hown[mrow * dper + d]);
+          if (mrow >= Bv) hn[j] = 0.f;
         }
-        if (m < Bv) *reinterpret_cast<float2*>(a.x_rep + (row0 + m) * a.ld_xrep + d0 + dl) = make_float2(hn[0], hn[1]);
-        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, dl)) = __floats2bfloat162_rn(hn[0], hn[1]);
-        hnew[m * dper + dl] = hn[0];
-        hnew[m * dper + dl + 1] = hn[1];
+        if (mrow < Bv) *reinterpret_cast<float2*>(a.x_rep + (row0 + mrow) * a.ld_xrep + d0 + dl) = make_float2(hn[0], hn[1]);
+        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(mrow, dl)) = __floats2bfloat162_rn(hn[0], hn[1]);
+        hnew[mrow * dper + dl] = hn[0];
+        hnew[mrow * dper + dl + 1] = hn[1];
       }
-      SDBG(15);
       fence_proxy_async();
       epi_bar();
-      SDBG(16);
+      SDBG(10);
       push_act(stage_a, (uint32_t)(dper >> 3) * BROW, smem_u32(xh), &act_bar[X_H], c, CL, ew);
-      SDBG(17);
+      SDBG(11);
 #pragma unroll 1
-      for (int e = et; e < Bv * dper; e += NT_EPI) {            // saved pre-LN gates (own rows of the three gates)
-        const int m = e / dper, dl = e - m * dper;
-        float* gp = a.gates_pre + (row0 + m) * 3 * D + d0 + dl;
-        gp[0] = outb[dl * OB + m]; gp[D] = outb[(dper + dl) * OB + m]; gp[2 * D] = outb[(2 * dper + dl) * OB + m];
-      }
+      for (int m = ew; m < Bv; m += EW)                         // saved pre-LN gates (own rows of the three gates)
+        for (int j = lane; j < 3 * dper; j += 32) {
+          const int gate = (j >= 2 * dper) ? 2 : (j >= dper ? 1 : 0);
+          a.gates_pre[(row0 + m) * 3 * D + gate * D + d0 + (j - gate * dper)] = outb[j * OB + m];
+        }
       { float* tmp = hown; hown = hnew; hnew = tmp; }          // (the x_gru store of this step, above, read the old buffer before the gates)
-      SDBG(18);
+      SDBG(12);
 
       // ================= P3: posterior hidden: own rows of Wr0[:, :D] . h' + (e_t . Wr0[:, D:]^T + b) =================
       mbar_wait(&acc_bar[1], par);
       tc_fence_after();
-      SDBG(19);
+      SDBG(13);
       tmem_to_outb(tmem_base, col_r0, hper, pl.seg[SEG_R0].m64, outb, s_ew, hper, ew, lane);
       epi_bar();
-      SDBG(20);
-      stats_push(outb, hper, lnp2, &stat_bar[ST_HID], c, CL, ew, lane);
-      SDBG(21);
-      mbar_wait(&stat_bar[ST_HID], par);
-      SDBG(22);
-      stats_combine(lnp2, CL, hper, 1e-5f, s_stat, a.hidr_mean + row0, a.hidr_rstd + row0, c == 0 ? Bv : 0, ew, lane);
-      epi_bar();
-      SDBG(23);
+      SDBG(14);
+      row_stats(outb, hper, lnp2, &stat_bar[ST_HID], par, 1e-5f, a.hidr_mean + row0, a.hidr_rstd + row0, mu, rs);
+      SDBG(15);
 #pragma unroll 1
-      for (int i = et; i < NB * (hper >> 1); i += NT_EPI) {
-        const int m = i / (hper >> 1), hl = (i - m * (hper >> 1)) << 1;
-        const float mu = s_stat[m], rs = s_stat[NB + m];
-        float f0 = siluf_((outb[hl * OB + m] - mu) * rs * p_r[hl] + p_r[hper + hl]);
-        float f1 = siluf_((outb[(hl + 1) * OB + m] - mu) * rs * p_r[hl + 1] + p_r[hper + hl + 1]);
-        if (m < Bv) *reinterpret_cast<float2*>(a.hidr + (row0 + m) * Hh + h0 + hl) = make_float2(f0, f1);
+      for (int hl_ = 2 * l16; hl_ < hper; hl_ += 32) {
+        float f0 = (outb[hl_ * OB + mrow] - mu) * rs * p_r[hl_] + p_r[hper + hl_];
+        float f1 = (outb[(hl_ + 1) * OB + mrow] - mu) * rs * p_r[hl_ + 1] + p_r[hper + hl_ + 1];
+        f0 *= fsigmoid(f0); f1 *= fsigmoid(f1);
+        if (mrow < Bv) *reinterpret_cast<float2*>(a.hidr + (row0 + mrow) * Hh + h0 + hl_) = make_float2(f0, f1);
         else { f0 = 0.f; f1 = 0.f; }
-        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(m, hl)) = __floats2bfloat162_rn(f0, f1);
+        *reinterpret_cast<__nv_bfloat162*>(stage + b_off(mrow, hl_)) = __floats2bfloat162_rn(f0, f1);
       }
-      SDBG(24);
       fence_proxy_async();
       epi_bar();
-      SDBG(25);
+      SDBG(16);
       push_act(stage_a, (uint32_t)(hper >> 3) * BROW, smem_u32(xhid), &act_bar[X_HID], c, CL, ew);
-      SDBG(26);
+      SDBG(17);
 #pragma unroll 1
-      for (int e = et; e < Bv * hper; e += NT_EPI) { const int m = e / hper, hl = e - m * hper; a.hidr_pre[(row0 + m) * Hh + h0 + hl] = outb[hl * OB + m]; }
+      for (int m = ew; m < Bv; m += EW)
+        for (int j = lane; j < hper; j += 32) a.hidr_pre[(row0 + m) * Hh + h0 + j] = outb[j * OB + m];
       if (t + 1 < a.T) fetch_ew(t + 1);
-      SDBG(27);
+      SDBG(18);
 
       // ================= P4: posterior logits of the own categoricals, unimix, inverse-CDF sample =================
       mbar_wait(&acc_bar[2], par);
       tc_fence_after();
-      SDBG(28);
+      SDBG(19);
       tmem_to_outb(tmem_base, col_r1, sper, pl.seg[SEG_R1].m64, outp, nullptr, 0, ew, lane);
       epi_bar();
-      SDBG(29);
-      // one warp per (batch row, own categorical), lane = class (Kc <= 32); four pairs at a time so that their shuffle chains overlap
+      SDBG(20);
+      // One warp per (batch row, own categorical), lane = class (Kc <= 32); the warp's pairs two at a time so that their shuffle
+      // chains overlap.  Sampling probabilities: the unimix probabilities themselves (they sum to 1 up to fp32 round-off; the
+      // reference renormalises log(p) twice, a difference far below the bf16 error of the logits) and a warp prefix sum instead of
+      // the sequential cumsum of the fp32 kernels.
+      const float um = a.unimix, um_k = um / (float)Kc;
 #pragma unroll 1
-      for (int pb = ew; pb < npairs; pb += 4 * EW) {
-        float raw[4], e1[4], lu[4], prob[4], mx[4], se[4];
-        int pm[4], pg[4];
+      for (int pb = ew; pb < npairs; pb += 2 * EW) {
+        float raw[2], e1[2], lu[2], prob[2], mx[2], se[2], cs[2];
+        int pm[2], pg[2];
         const bool on = lane < Kc;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < 2; ++j) {
           const int p = min(pb + j * EW, npairs - 1);
-          pm[j] = p / gper; pg[j] = p - pm[j] * gper;
+          pg[j] = p % gper; pm[j] = p / gper;
           raw[j] = on ? (outp[(size_t)(pg[j] * Kc + lane) * OB + pm[j]] + p_br1[pg[j] * Kc + lane]) : -INFINITY;
           mx[j] = raw[j];
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], o));
+          for (int j = 0; j < 2; ++j) mx[j] = fmaxf(mx[j], __shfl_xor_sync(0xffffffffu, mx[j], o));
         }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { e1[j] = on ? expf(raw[j] - mx[j]) : 0.f; se[j] = e1[j]; }
+        for (int j = 0; j < 2; ++j) { e1[j] = on ? __expf(raw[j] - mx[j]) : 0.f; se[j] = e1[j]; }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) se[j] += __shfl_xor_sync(0xffffffffu, se[j], o);
+          for (int j = 0; j < 2; ++j) se[j] += __shfl_xor_sync(0xffffffffu, se[j], o);
         }
-        // Sampling probabilities: Categorical(logits = lu).probs = softmax(lu) = pm / sum(pm) up to fp32 round-off (the reference
-        // renormalises log(pm) twice); with bf16 contractions upstream that round-off is far below the logits' own error, so the
-        // draw uses pm directly and a warp prefix sum instead of the sequential cumsum of the fp32 kernels.
-        float ps[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < 2; ++j) {
           lu[j] = raw[j];
-          prob[j] = e1[j] / se[j];
-          if (a.unimix > 0.f) {
-            const float pr = fminf(fmaxf((1.f - a.unimix) * prob[j] + a.unimix / (float)Kc, DV3_EPS32), 1.f - DV3_EPS32);
-            lu[j] = on ? logf(pr) : -INFINITY;
+          prob[j] = __fdividef(e1[j], se[j]);
+          if (um > 0.f) {
+            const float pr = fminf(fmaxf((1.f - um) * prob[j] + um_k, DV3_EPS32), 1.f - DV3_EPS32);
+            lu[j] = on ? __logf(pr) : -INFINITY;
             prob[j] = on ? pr : 0.f;
           }
-          ps[j] = prob[j];
+          cs[j] = prob[j];
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) ps[j] += __shfl_xor_sync(0xffffffffu, ps[j], o);
-        }
-        float cs[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { prob[j] = prob[j] / ps[j]; cs[j] = prob[j]; }
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) { const float v = __shfl_up_sync(0xffffffffu, cs[j], o); if (lane >= o) cs[j] += v; }
+          for (int j = 0; j < 2; ++j) { const float v = __shfl_up_sync(0xffffffffu, cs[j], o); if (lane >= o) cs[j] += v; }
         }
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < 2; ++j) {
           const int p = pb + j * EW;
           int choice;
           if (a.forced_idx) {
@@ -495,10 +504,10 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
           }
         }
       }
-      SDBG(30);
+      SDBG(21);
       if (t + 1 < a.T) fetch_uu(t + 1);
       epi_bar();                                               // idxo / outp / outl complete before the next step reads / flushes them
-      SDBG(31);
+      SDBG(22);
     }
     flush_posterior((size_t)(a.T - 1) * B + b0);
     tc_fence_before();

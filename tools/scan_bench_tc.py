@@ -51,14 +51,13 @@ def timed(fn, n=10):
 
 out["fwd_ms_incl_pack"] = timed(lambda: ops.rssm_observe_fwd(eng, None))
 st = ops.scratch[:64].view(torch.int64)[:32].cpu().tolist()
-names = ["P0 arm + wait idx + cp.async wait + bar", "P1 gather + bar", "P1 stats push", "P1 stats wait", "P1 combine + bar", "P1 LN/SiLU -> stage",
-         "P1 proxy fence + bar", "P1 push feat", "P1 deferred stores", "wait gates acc", "P2 tmem->outb + bar", "P2 stats push", "P2 stats wait",
-         "P2 combine + bar", "P2 gates -> stage", "P2 proxy fence + bar", "P2 push h", "P2 deferred stores", "wait r0 acc", "P3 tmem->outb + bar",
-         "P3 stats push", "P3 stats wait", "P3 combine + bar", "P3 LN/SiLU -> stage", "P3 proxy fence + bar", "P3 push hid", "P3 deferred stores",
-         "wait r1 acc", "P4 tmem->outp + bar", "P4 sample + idx push", "P4 fetch + bar"]
+names = ["P0 arm + wait idx + cp.async wait + bar", "P1 gather", "P1 stats exchange", "P1 LN/SiLU -> stage + fence + bar", "P1 push feat", "P1 deferred stores",
+         "wait gates acc", "P2 tmem->outb + bar", "P2 stats exchange", "P2 gates -> stage + fence + bar", "P2 push h", "P2 deferred stores", "wait r0 acc",
+         "P3 tmem->outb + bar", "P3 stats exchange", "P3 LN/SiLU -> stage + fence + bar", "P3 push hid", "P3 deferred stores", "wait r1 acc",
+         "P4 tmem->outp + bar", "P4 sample + idx push", "P4 fetch + bar"]
 if ops.scan_kernel == "tcgen05":
-    out["fwd_phases_clk"] = {names[i]: st[i + 1] - st[i] for i in range(31)}
-    out["fwd_step_clk"] = st[31] - st[0]
+    out["fwd_phases_clk"] = {names[i]: st[i + 1] - st[i] for i in range(22)}
+    out["fwd_step_clk"] = st[22] - st[0]
 out["bwd_ms_incl_prep_pack"] = timed(lambda: ops.rssm_observe_bwd(eng))
 print(json.dumps(out, indent=1))
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
