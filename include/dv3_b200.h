@@ -216,6 +216,14 @@ typedef struct Dv3ScanBwdArgs {
   long long* dbg;                                       /* optional: 16 clock64 stamps of CTA 0 at step T-2 */
 } Dv3ScanBwdArgs;
 int dv3_rssm_observe_bwd_cluster(const Dv3ScanBwdArgs* args, void* stream);
+/* The same reverse scan with tcgen05 tensor cores (rssm_scan_bwd_tc.cu; machinery as dv3_rssm_observe_fwd_tc): the four transposed
+ * in-loop weight matrices come as one per-CTA, per-step bf16 stream (dv3_scan_tc_bwd_pack reads the fp32 parameters with swapped
+ * strides); the *_pk fields of the argument block are ignored.  Any B (one cluster per 16 rows); DV3_ERR_UNSUPPORTED when the shape
+ * does not fit (e.g. the [16, 3D] gradient operand of very large D does not fit next to a weight ring in shared memory). */
+int dv3_scan_tc_bwd_config(int D, int U, int Hh, int G, int Kc, int* cluster_size, size_t* stream_bytes);
+int dv3_scan_tc_bwd_pack(int D, int U, int Hh, int G, int Kc, const float* Wr1, int ld_wr1, const float* Wr0, int ld_wr0,
+                         const float* Wgru, int ld_wgru, const float* Wmlp, int ld_wmlp, void* dst, void* stream);
+int dv3_rssm_observe_bwd_tc(const Dv3ScanBwdArgs* args, const void* weight_stream, void* stream);
 /* ps = softmax(raw), pn = Categorical(logits = unimix(raw)).probs, coef = (1-mix)/pm inside the clamp else 0 (mix = 0: ps = pn,
  * coef = 1): the step-independent factors of the unimix + straight-through Jacobian (see dv3_unimix_bwd). */
 int dv3_unimix_bwd_prep(int R, int groups, int K, float mix, const float* raw, int ldr, float* ps, float* coef, float* pn, void* stream);

@@ -51,6 +51,9 @@ SIGNATURES = {
     "dv3_scan_tc_fwd_config": [_i, _i, _i, _i, _i, c_fp, c_fp],
     "dv3_scan_tc_fwd_pack": [_i, _i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
     "dv3_rssm_observe_fwd_tc": [c_fp, c_fp, c_fp],
+    "dv3_scan_tc_bwd_config": [_i, _i, _i, _i, _i, c_fp, c_fp],
+    "dv3_scan_tc_bwd_pack": [_i, _i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
+    "dv3_rssm_observe_bwd_tc": [c_fp, c_fp, c_fp],
     "dv3_pack_mma_a": [_i, _i, c_fp, _ll, _ll, c_fp, c_fp],
     "dv3_ln_act_fwd_rows_gather": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, _i, c_fp, c_fp],
     "dv3_ln_act_bwd_fused": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
@@ -200,6 +203,7 @@ class CudaOps:
         self.mirror_check = os.environ.get("DV3_MIRROR_CHECK", "0") == "1"
         self.use_cluster_scan = os.environ.get("DV3_CLUSTER_SCAN", "1") != "0"
         self.use_tc_scan = os.environ.get("DV3_TC_SCAN", "1") != "0"      # tcgen05 scan kernels (rssm_scan_tc.cu), tried first
+        self.use_tc_scan_bwd = self.use_tc_scan
         # Linear+LayerNorm+SiLU in one clustered kernel (dv3_gemm_ln_bf16_tma): correct (tests) but its epilogue -- one thread per row
         # for three TMEM sweeps and 128 SiLUs -- is slower than the separate warp-per-row LayerNorm: 117 vs 130 steps/s.  Opt-in.
         self.use_gemm_ln = os.environ.get("DV3_GEMM_LN", "0") == "1"
@@ -659,14 +663,20 @@ class CudaOps:
         key = "tc_" + which
         if key not in pk:
             cl, nbytes = C.c_int(0), C.c_size_t(0)
-            rc = self.lib.dv3_scan_tc_fwd_config(eng.D, eng.U, eng.Hh, eng.G, eng.K, C.addressof(cl), C.addressof(nbytes))
+            cfg = self.lib.dv3_scan_tc_fwd_config if which == "fwd" else self.lib.dv3_scan_tc_bwd_config
+            rc = cfg(eng.D, eng.U, eng.Hh, eng.G, eng.K, C.addressof(cl), C.addressof(nbytes))
             pk[key] = None if rc != 0 else torch.empty(nbytes.value, dtype=torch.uint8, device=self.device)
         buf = pk[key]
         if buf is None:
             return None
         self.launches += 1
-        _chk(self.lib.dv3_scan_tc_fwd_pack(eng.D, eng.U, eng.Hh, eng.G, eng.K, _p(eng.Wgru), eng.Wgru.stride(0), _p(eng.Wr0), eng.Wr0.stride(0),
-                                           _p(eng.Wr1), eng.Wr1.stride(0), buf.data_ptr(), self._s()), "dv3_scan_tc_fwd_pack")
+        if which == "fwd":
+            _chk(self.lib.dv3_scan_tc_fwd_pack(eng.D, eng.U, eng.Hh, eng.G, eng.K, _p(eng.Wgru), eng.Wgru.stride(0), _p(eng.Wr0), eng.Wr0.stride(0),
+                                               _p(eng.Wr1), eng.Wr1.stride(0), buf.data_ptr(), self._s()), "dv3_scan_tc_fwd_pack")
+        else:
+            _chk(self.lib.dv3_scan_tc_bwd_pack(eng.D, eng.U, eng.Hh, eng.G, eng.K, _p(eng.Wr1), eng.Wr1.stride(0), _p(eng.Wr0), eng.Wr0.stride(0),
+                                               _p(eng.Wgru), eng.Wgru.stride(0), _p(eng.Wmlp), eng.Wmlp.stride(0), buf.data_ptr(), self._s()),
+                 "dv3_scan_tc_bwd_pack")
         return buf.data_ptr()
 
     def _pack(self, eng, name, R, K, W, stride_r, stride_k):
@@ -689,16 +699,22 @@ class CudaOps:
         _chk(self.lib.dv3_unimix_bwd_prep(R, groups, K, unimix, pr, ldr, _p(ps), _p(coef), _p(pn), self._s()), "dv3_unimix_bwd_prep")
 
     def rssm_observe_bwd(self, eng) -> bool:
-        """Whole reverse scan in one cluster launch (rssm_scan_bwd_cluster.cu; bf16 precision with mirrors only).  Returns False when
-        the shape / device is outside the kernel's plan (the engine then runs the per-step composition)."""
-        if not (self.use_mirrors and self.use_cluster_scan):
+        """Whole reverse scan in one launch: the tcgen05 kernel (rssm_scan_bwd_tc.cu) when the shape fits, else the mma.sync cluster kernel
+        (rssm_scan_bwd_cluster.cu); bf16 precision with mirrors only.  Returns False when neither can run the shape (the engine then
+        runs the per-step composition)."""
+        if not self.use_mirrors:
+            return False
+        tc_stream = self._tc_stream(eng, "bwd") if self.use_tc_scan_bwd else None
+        if tc_stream is None and not (self.use_cluster_scan and eng.B <= 16):
             return False
         D, U, Hh, S = eng.D, eng.U, eng.Hh, eng.S
-        # transposed weights straight from the fp32 parameters (strides swapped), in MMA-fragment order
-        w16 = [self._pack(eng, "r1T", Hh, S, eng.Wr1, 1, eng.Wr1.stride(0)), self._pack(eng, "r0hT", D, Hh, eng.Wr0, 1, eng.Wr0.stride(0)),
-               self._pack(eng, "gruT", D + U, 3 * D, eng.Wgru, 1, eng.Wgru.stride(0)), self._pack(eng, "mlpzT", S, U, eng.Wmlp, 1, eng.Wmlp.stride(0))]
-        if any(w is None for w in w16):
-            return False
+        w16 = [None] * 4
+        if tc_stream is None:
+            # transposed weights straight from the fp32 parameters (strides swapped), in MMA-fragment order
+            w16 = [self._pack(eng, "r1T", Hh, S, eng.Wr1, 1, eng.Wr1.stride(0)), self._pack(eng, "r0hT", D, Hh, eng.Wr0, 1, eng.Wr0.stride(0)),
+                   self._pack(eng, "gruT", D + U, 3 * D, eng.Wgru, 1, eng.Wgru.stride(0)), self._pack(eng, "mlpzT", S, U, eng.Wmlp, 1, eng.Wmlp.stride(0))]
+            if any(w is None for w in w16):
+                return False
         eng.ops.unimix_bwd_prep(eng.post_raw, eng.G, eng.K, float(eng.cfg.algo.unimix), eng.ub_ps, eng.ub_coef, eng.ub_pn)
         a = ScanBwdArgs()
         a.T, a.B, a.G, a.Kc, a.D, a.U, a.Hh = eng.T, eng.B, eng.G, eng.K, eng.D, eng.U, eng.Hh
@@ -716,6 +732,16 @@ class CudaOps:
         a.dpost_raw_bf16, a.dhidr_pre_bf16 = self._m16(_p(eng.dpost_raw)), self._m16(_p(eng.dhidr_pre))
         a.dgates_pre_bf16, a.dfeat_pre_bf16 = self._m16(_p(eng.dgates_pre)), self._m16(_p(eng.dfeat_pre))
         a.dbg = self.scratch.data_ptr() if os.environ.get("DV3_SCAN_DEBUG") else None
+        if tc_stream is not None:
+            rc = self.lib.dv3_rssm_observe_bwd_tc(C.addressof(a), tc_stream, self._s())
+            if rc == 0:
+                self.launches += 1
+                self.bwd_scan_kernel = "tcgen05"
+                return True
+            if rc != -2:
+                _chk(rc, "dv3_rssm_observe_bwd_tc")
+            self.use_tc_scan_bwd = False
+            return self.rssm_observe_bwd(eng)
         rc = self.lib.dv3_rssm_observe_bwd_cluster(C.addressof(a), self._s())
         if rc == -2:
             self.use_cluster_bwd_ok = False

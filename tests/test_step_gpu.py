@@ -314,11 +314,16 @@ def test_fused_bf16_scan_matches_fp32_scan(cuda_ops, size, B, T, obs, acts, kern
     assert worst["feat_pre"] < (1e-2 if kernel == "tcgen05" else 2e-3), worst
 
 
-@pytest.mark.parametrize("size,B,T,obs,acts", [("S", 16, 64, 14, [100]), ("XS", 16, 20, 4, [2]), ("S", 5, 9, 14, [7, 3])])
-def test_cluster_reverse_scan_matches_per_step_composition(size, B, T, obs, acts):
-    """dv3_rssm_observe_bwd_cluster (the whole reverse scan on one cluster, bf16 transposed weights in mma.sync fragments) against
-    the per-step kernels (fp32 contractions for the B-row steps) on the same forward state: the saved pre-activation gradients and
-    the resulting world-model parameter gradients agree to the bf16-mode tolerance."""
+@pytest.mark.parametrize("size,B,T,obs,acts,kernel", [
+    ("S", 16, 64, 14, [100], "tcgen05"), ("XS", 16, 20, 4, [2], "tcgen05"), ("S", 5, 9, 14, [7, 3], "tcgen05"),
+    ("S", 32, 6, 14, [100], "tcgen05"),          # B = 32: two clusters of 16 rows
+    ("prey", 16, 8, 14, [100], "tcgen05"),       # D = Hh = 256, U = 1024: unequal slices in the Wgru^T contraction
+    ("S", 16, 16, 14, [100], "cluster"), ("XS", 7, 10, 4, [2], "cluster")])
+def test_fused_reverse_scan_matches_per_step_composition(size, B, T, obs, acts, kernel):
+    """The one-launch reverse scans -- dv3_rssm_observe_bwd_tc (tcgen05, transposed weights through the bulk-copy ring) and its
+    predecessor dv3_rssm_observe_bwd_cluster (mma.sync) -- against the per-step kernels (fp32 contractions for the B-row steps) on the
+    same forward state: the saved pre-activation gradients and the resulting world-model parameter gradients agree to the bf16-mode
+    tolerance."""
     from sheeprl_prey_b200._lib import CudaOps
 
     cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=3)
@@ -327,6 +332,7 @@ def test_cluster_reverse_scan_matches_per_step_composition(size, B, T, obs, acts
     data = _to(harness.synthetic_batch(T, B, od, acts, seed=77, done_p=0.1), DEV)
     noise = _to(harness.synthetic_noise(T, B, 3, 32, len(acts), seed=78), DEV)
     ops = CudaOps(DEV, precision="bf16")
+    ops.use_tc_scan_bwd = kernel == "tcgen05"
     eng = engine_from_params(cfg, od, acts, _dev_params(params), ops, DEV)
     eng.load_batch(data)
     eng.load_noise(noise)
@@ -340,7 +346,7 @@ def test_cluster_reverse_scan_matches_per_step_composition(size, B, T, obs, acts
         eng.wm.grad.zero_()
         eng.world_backward()
         torch.cuda.synchronize()
-        assert (ops.bwd_scan_kernel == "cluster") == fused, ops.bwd_scan_kernel
+        assert ops.bwd_scan_kernel == (kernel if fused else None), ops.bwd_scan_kernel
         res.append(({n: getattr(eng, n).clone() for n in names}, eng.wm.grad.clone()))
         if fused:   # the bf16 mirrors written by the kernel equal bf16(fp32 output)
             for n in ("dpost_raw", "dhidr_pre", "dgates_pre", "dfeat_pre"):
