@@ -7,7 +7,7 @@ Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl refere
 import this file.  The product package (sheeprl_prey_b200/) never does; it raises if its CUDA
 extension is missing.
 
-Parity status: PINNED.  tests/test_oracle_vs_reference.py runs the unmodified reference
+Parity status: PINNED.  tests/test_oracle.py runs the unmodified reference
 (`/root/reference/sheeprl/algos/dreamer_v3/*.py`, imported through oracle/ref_shim.py) and this
 restatement on the same weights, batch and injected sampling noise and requires agreement to
 fp32 round-off; oracle/make_golden.py stores reference outputs in tests/golden/ so that the
@@ -386,7 +386,9 @@ class DV3Oracle:
         with torch.no_grad():
             values = twohot_mean(self.critic_logits(traj))
             rewards = twohot_mean(self.reward_logits(traj))
-            cont_p = torch.sigmoid(self.continue_logits(traj))
+            cont_logit = self.continue_logits(traj)
+            self.last_continue_logits_img = cont_logit    # pre-threshold value, kept for the parity tests
+            cont_p = torch.sigmoid(cont_logit)
             continues = (cont_p >= 0.5).to(traj.dtype)  # Bernoulli.mode (NaN at exactly 0.5 is not reproduced)
             true_done = (1 - dones).flatten().reshape(1, -1, 1)
             continues = torch.cat((true_done, continues[1:]))
@@ -514,6 +516,6 @@ class OracleTrainer:
                       "obs_loss_tb", "reward_loss_tb", "continue_loss_tb", "kl_tb", "reward_logits", "continue_logits"):
                 out[k] = W[k].detach()
             out.update(traj=traj, imagined_actions=acts, act_idx=act_idx, z_idx=z_idx, values=values, rewards=rewards,
-                       continues=continues, lambda_values=lam, discount=discount,
+                       continues=continues, continue_logits_img=m.last_continue_logits_img, lambda_values=lam, discount=discount,
                        moments_low=self.low.clone(), moments_high=self.high.clone(), invscale=invscale)
         return out

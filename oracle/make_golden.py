@@ -6,6 +6,10 @@
 dv3_step.pt : reference build_models() weights (perturbed so no head is degenerate), a synthetic batch, the injected
               sampling noise, and the reference train() outputs for two consecutive gradient steps (the 13 aggregator
               metrics, drawn indices, Moments buffers, parameters after step 2).
+dv3_xs_b16t64.npz : BASELINE.json config 1 at its real shape (DreamerV3-XS, obs 4 / Discrete(2), B16 x T64, H15): the reference train()
+              run for two gradient steps on seeded parameters / batch / noise that the tests regenerate from the seeds
+              (tests/util.py::random_params_like, oracle/harness.py), so the file holds only results: the 13 metrics, Moments,
+              every drawn index (uint8) and per-tensor parameter norms before and after.
 buffers.pt  : a scripted add/sample session on the reference AsyncReplayBuffer(sequential=True) under a fixed
               torch seed (everything added, every sampled batch).
 """
@@ -90,6 +94,70 @@ def make_step_golden(STEP_CFG=STEP_CFG, STEP_OBS=STEP_OBS, STEP_ACTIONS=STEP_ACT
                     params2=params2, torch_version=torch.__version__), os.path.join(GOLDEN_DIR, fname))
 
 
+BASE_KW = dict(size="XS", batch_size=16, sequence_length=64, horizon=15)
+BASE_OBS = {"state": 4}
+BASE_ACTIONS = [2]
+BASE_SEEDS = dict(params=11, data=1234, noise=99)
+
+
+def make_baseline_golden(fname="dv3_xs_b16t64.npz"):
+    """BASELINE config 1 at full size through the UNMODIFIED reference; inputs are regenerated from seeds by the tests."""
+    import json
+    import sys
+
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(os.path.dirname(GOLDEN_DIR)))
+    from util import random_params_like
+
+    dv3, agent, loss, utils, buffers, dist = ref_shim.ref_modules()
+    from sheeprl.utils.utils import dotdict as ref_dotdict
+
+    cfg = ref_dotdict(make_cfg(**BASE_KW))
+    T, B, H = cfg.per_rank_sequence_length, cfg.per_rank_batch_size, cfg.algo.horizon
+    G, nh = cfg.algo.world_model.stochastic_size, len(BASE_ACTIONS)
+    params = random_params_like(make_cfg(**BASE_KW), BASE_OBS, BASE_ACTIONS, seed=BASE_SEEDS["params"])
+    fab = ref_shim.FakeFabric()
+    wm, actor, critic, tcritic = agent.build_models(fab, BASE_ACTIONS, False, cfg, ObsSpace({k: (d,) for k, d in BASE_OBS.items()}),
+                                                    params["wm"], params["actor"], params["critic"], params["target"])
+    data = harness.synthetic_batch(T, B, BASE_OBS, BASE_ACTIONS, seed=BASE_SEEDS["data"], done_p=1 / 50)
+    noise = harness.synthetic_noise(T, B, H, G, nh, seed=BASE_SEEDS["noise"])
+    a = cfg.algo
+    wo = torch.optim.Adam(wm.parameters(), lr=a.world_model.optimizer.lr, eps=a.world_model.optimizer.eps)
+    ao = torch.optim.Adam(actor.parameters(), lr=a.actor.optimizer.lr, eps=a.actor.optimizer.eps)
+    co = torch.optim.Adam(critic.parameters(), lr=a.critic.optimizer.lr, eps=a.critic.optimizer.eps)
+    mom = utils.Moments(fab, a.actor.moments.decay, a.actor.moments.max, a.actor.moments.percentile.low, a.actor.moments.percentile.high)
+    S = harness.strip_wrapper_keys
+    arrays, meta = {}, dict(kw=BASE_KW, obs=BASE_OBS, actions_dim=BASE_ACTIONS, seeds=BASE_SEEDS, torch_version=torch.__version__, steps=[])
+    meta["norms0"] = {n: {k: float(v.double().norm()) for k, v in params[n].items()} for n in ("wm", "actor", "critic", "target")}
+    for it in range(2):
+        agg = ref_shim.Aggregator()
+        tape = ref_shim.NoiseTape(harness.noise_tape_order(noise, T, H, nh, T * B))
+        tape.install(dist)
+        try:
+            dv3.train(fab, wm, actor, critic, tcritic, wo, ao, co, {k: v.clone() for k, v in data.items()}, agg, cfg, False, BASE_ACTIONS, mom)
+        finally:
+            tape.uninstall()
+        ix = tape.indices
+        post_idx = torch.stack([ix[2 * t + 1] for t in range(T)]).reshape(T, B, G)
+        o = 2 * T
+        act_idx = [torch.stack([ix[o + i].reshape(-1) for i in range(nh)], -1)]
+        o += nh
+        z_idx = []
+        for h in range(H):
+            z_idx.append(ix[o].reshape(T * B, G))
+            o += 1
+            act_idx.append(torch.stack([ix[o + i].reshape(-1) for i in range(nh)], -1))
+            o += nh
+        arrays[f"post_idx{it}"] = post_idx.to(torch.uint8).numpy()
+        arrays[f"z_idx{it}"] = torch.stack(z_idx).to(torch.uint8).numpy()
+        arrays[f"act_idx{it}"] = torch.stack(act_idx).to(torch.uint8).numpy()
+        meta["steps"].append(dict(metrics={k: float(v) for k, v in agg.values.items()}, moments_low=float(mom.low), moments_high=float(mom.high)))
+    meta["norms2"] = {n: {k: float(v.double().norm()) for k, v in S(m.state_dict()).items()} for n, m in (("wm", wm), ("actor", actor), ("critic", critic))}
+    arrays["meta"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, fname), **arrays)
+
+
 def make_buffer_golden():
     dv3, agent, loss, utils, buffers, dist = ref_shim.ref_modules()
     torch.manual_seed(1234)
@@ -146,5 +214,6 @@ if __name__ == "__main__":
     make_step_golden()
     make_step_golden(PIX_CFG, PIX_OBS, PIX_ACTIONS, "dv3_step_pixels.pt")
     make_buffer_golden()
+    make_baseline_golden()
     for f in sorted(os.listdir(GOLDEN_DIR)):
         print(f, os.path.getsize(os.path.join(GOLDEN_DIR, f)))

@@ -37,6 +37,42 @@ def test_oracle_matches_reference_golden(fixture):
             assert rel(mine[k], v) < 2e-5, (name, k)
 
 
+def test_oracle_matches_reference_golden_at_baseline_size():
+    """BASELINE.json config 1 at its real shape (XS, B16 x T64, H15): the reference's train() outputs for two gradient steps
+    (tests/golden/dv3_xs_b16t64.npz, oracle/make_golden.py::make_baseline_golden) against the oracle on inputs regenerated from the
+    recorded seeds."""
+    from oracle import harness
+    from util import load_baseline_golden, random_params_like
+
+    meta, ix = load_baseline_golden()
+    cfg = make_cfg(**meta["kw"])
+    od, acts, seeds = meta["obs"], meta["actions_dim"], meta["seeds"]
+    T, B, H = cfg.per_rank_sequence_length, cfg.per_rank_batch_size, cfg.algo.horizon
+    params = random_params_like(cfg, od, acts, seed=seeds["params"])
+    for n, d in meta["norms0"].items():           # the regenerated parameters are the ones the reference ran on
+        for k, v in d.items():
+            assert abs(float(params[n][k].double().norm()) - v) <= 1e-6 * max(1.0, v), (n, k)
+    tr = O.OracleTrainer(cfg, od, acts, params["wm"], params["actor"], params["critic"], params["target"])
+    data = harness.synthetic_batch(T, B, od, acts, seed=seeds["data"], done_p=1 / 50)
+    noise = harness.synthetic_noise(T, B, H, 32, len(acts), seed=seeds["noise"])
+    for it in range(2):
+        # step 0 free-running: the 500 k draws of the step must come out as the reference's; step 1 teacher-forced with the reference's
+        # draws (after one Adam step the two sides differ by fp32 round-off, enough to flip a draw that sits on a CDF step: SURVEY H2)
+        forced = None if it == 0 else dict(post_idx=ix["post_idx1"], imagine=dict(z_idx=ix["z_idx1"], act_idx=ix["act_idx1"].reshape(H + 1, T * B, -1)))
+        out = tr.step({k: v.clone() for k, v in data.items()}, noise, forced=forced)
+        ref = meta["steps"][it]
+        for k in KEYS:
+            tol = 1e-4 if k.startswith("Grads/") else 2e-5
+            assert abs(float(out[k]) - ref["metrics"][k]) <= tol * max(1.0, abs(ref["metrics"][k])), (it, k, float(out[k]), ref["metrics"][k])
+        assert torch.equal(out["post_idx"].long(), ix[f"post_idx{it}"])
+        assert torch.equal(out["z_idx"].long(), ix[f"z_idx{it}"])
+        assert torch.equal(out["act_idx"].long().reshape(ix[f"act_idx{it}"].shape), ix[f"act_idx{it}"])
+        assert abs(float(tr.low) - ref["moments_low"]) < 1e-6 and abs(float(tr.high) - ref["moments_high"]) < 1e-6
+    for name, mine in (("wm", tr.wm), ("actor", tr.actor), ("critic", tr.critic)):
+        for k, v in meta["norms2"][name].items():
+            assert abs(float(mine[k].double().norm()) - v) <= 2e-5 * max(1e-3, v), (name, k)
+
+
 @pytest.mark.skipif(not ref_shim.reference_available(), reason="reference tree only exists in the build container")
 def test_oracle_matches_reference_live():
     from oracle import harness

@@ -11,6 +11,17 @@ def load_golden(name):
     return torch.load(os.path.join(GOLDEN, name), weights_only=False)
 
 
+def load_baseline_golden(name="dv3_xs_b16t64.npz"):
+    """The BASELINE-size golden (oracle/make_golden.py::make_baseline_golden): (meta dict, dict of index arrays)."""
+    import json
+
+    import numpy as np
+
+    z = np.load(os.path.join(GOLDEN, name))
+    meta = json.loads(bytes(z["meta"]).decode())
+    return meta, {k: torch.from_numpy(z[k].astype("int64")) for k in z.files if k != "meta"}
+
+
 def rel(a, b):
     a, b = a.detach().double().cpu(), b.detach().double().cpu()
     return float((a - b).abs().max() / (b.abs().max() + 1e-20))
