@@ -355,6 +355,14 @@ def _arena_from(module: nn.Module, device) -> Arena:
     return arena
 
 
+def _mix_seed(seed: int, rank: int) -> int:
+    """splitmix64(seed) ^ rank: decorrelates nearby seeds, keeps ranks of one run on distinct streams."""
+    z = (seed + 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+    return (z ^ (z >> 31)) ^ rank
+
+
 def build_models(
     fabric: Any,
     actions_dim: Sequence[int],
@@ -365,10 +373,8 @@ def build_models(
     actor_state: Optional[Dict[str, Tensor]] = None,
     critic_state: Optional[Dict[str, Tensor]] = None,
     target_critic_state: Optional[Dict[str, Tensor]] = None,
-    ops=None,
 ) -> Tuple[WorldModel, nn.Module, nn.Module, nn.Module]:
-    """Same positional contract as the reference's build_models.  `ops` is a test seam (the CPU statement of the
-    kernels for host-logic tests); by default the CUDA library is required."""
+    """Same positional contract as the reference's build_models.  The CUDA library is required (there is no CPU path)."""
     w, a = cfg.algo.world_model, cfg.algo
     device = torch.device(fabric.device)
     keys = list(cfg.mlp_keys.encoder or [])
@@ -425,16 +431,18 @@ def build_models(
     for m in (world_model, actor, critic, target_critic):
         m.to(device)
     arenas = [_arena_from(m, device) for m in (world_model, actor, critic, target_critic)]
-    if ops is None:
-        from ..._lib import CudaOps
+    from ... import _lib
 
-        ops = CudaOps(device)
+    ops = _lib.CudaOps(device)
     dist = None
     if getattr(fabric, "world_size", 1) > 1:
         from ...parallel import TorchDist
 
         dist = TorchDist(fabric.world_size)
-    engine = DV3Engine(cfg, obs_shapes, list(actions_dim), *arenas, ops, device, dist=dist, seed=int(getattr(fabric, "global_rank", 0)))
+    # sampling noise: counter-based generator keyed by (cfg.seed, rank) -- the reference seeds every rank through
+    # fabric.seed_everything(cfg.seed) (sheeprl/cli.py); runs with different seeds must not share their training-step noise
+    engine = DV3Engine(cfg, obs_shapes, list(actions_dim), *arenas, ops, device, dist=dist,
+                       seed=_mix_seed(int(cfg.get("seed", 42) or 0), int(getattr(fabric, "global_rank", 0))))
     object.__setattr__(world_model, "_dv3_engine", engine)   # not a submodule / not in state_dict
 
     # Fabric wrapping, same call sites as agent.py:1054-1063 (DDP hooks are inert: the engine all-reduces its own grads)

@@ -52,12 +52,23 @@ def _graphed_step(eng: DV3Engine) -> None:
 def _adopt_optimizer(eng: DV3Engine, arena, optimizer, tag: str) -> None:
     """Make a caller-created torch.optim.Adam the owner of the engine's flat Adam state: its per-parameter
     exp_avg / exp_avg_sq become views into the arena buffers, so optimizer.state_dict() (checkpoints,
-    dreamer_v3.py:781-795) stays valid while the fused kernel does the update."""
-    if optimizer is None or getattr(optimizer, "_dv3_adopted", None) is arena:
+    dreamer_v3.py:781-795) stays valid while the fused kernel does the update.
+    Checked on every call: `optimizer.load_state_dict()` replaces the state tensors, so when they no longer alias the arena (a
+    resume after the first train() call) the loaded moments are imported again; a changed lr / betas / eps is picked up and the
+    captured CUDA graph, which froze the old values, is dropped."""
+    if optimizer is None:
         return
     group = optimizer.param_groups[0]
     b1, b2 = group.get("betas", (0.9, 0.999))
-    eng.opt_hparams[tag] = dict(lr=float(group["lr"]), eps=float(group["eps"]), beta1=float(b1), beta2=float(b2))
+    hp = dict(lr=float(group["lr"]), eps=float(group["eps"]), beta1=float(b1), beta2=float(b2))
+    if eng.opt_hparams.get(tag) != hp:
+        eng.opt_hparams[tag] = hp
+        eng._graph = None                    # hyper-parameters are baked into the captured launches
+    probe = getattr(optimizer, "_dv3_probe", None)       # (first parameter, address its exp_avg must have while adopted)
+    if getattr(optimizer, "_dv3_adopted", None) is arena and probe is not None:
+        st0 = optimizer.state.get(probe[0])
+        if st0 and "exp_avg" in st0 and st0["exp_avg"].data_ptr() == probe[1]:
+            return                           # still aliased: nothing to do
     if group.get("weight_decay", 0) not in (0, 0.0):
         raise NotImplementedError("weight decay is not part of the reference's DreamerV3 config (optim/adam.yaml)")
     by_ptr = {v.data_ptr(): k for k, v in arena.p.items()}
@@ -67,7 +78,7 @@ def _adopt_optimizer(eng: DV3Engine, arena, optimizer, tag: str) -> None:
             raise RuntimeError("optimizer parameter is not an arena view; build the models with sheeprl_prey_b200.build_models")
         off, n, shape = arena.offsets[name]
         st = optimizer.state[p]
-        if "exp_avg" in st:   # resumed optimizer: import its moments
+        if "exp_avg" in st and st["exp_avg"].data_ptr() != arena.m[off:].data_ptr():   # resumed optimizer: import its moments
             arena.m[off:off + n].view(shape).copy_(st["exp_avg"])
             arena.v[off:off + n].view(shape).copy_(st["exp_avg_sq"])
             arena.step.fill_(float(st["step"]))
@@ -75,6 +86,26 @@ def _adopt_optimizer(eng: DV3Engine, arena, optimizer, tag: str) -> None:
         st["exp_avg_sq"] = arena.v[off:off + n].view(shape)
         st["step"] = arena.step.view(())
     optimizer._dv3_adopted = arena
+    p0 = group["params"][0]
+    optimizer._dv3_probe = (p0, optimizer.state[p0]["exp_avg"].data_ptr())
+
+
+def _bind_moments(eng: DV3Engine, moments) -> None:
+    """`moments.low / high` (and our `rng_counter`) become VIEWS of the engine's device state: the step updates them in place, and
+    `moments.load_state_dict()` -- which copies into the existing buffers -- writes straight into the engine, whenever it is called.
+    Works for the reference's own Moments module too (same buffer names, algos/dreamer_v3/utils.py:28-29)."""
+    if moments is None:
+        return
+    low = getattr(moments, "low", None)
+    if low is not None and low.data_ptr() == eng.mom_state.data_ptr():
+        return
+    eng.mom_state[0:1].copy_(moments.low.reshape(1).to(eng.mom_state.device))
+    eng.mom_state[1:2].copy_(moments.high.reshape(1).to(eng.mom_state.device))
+    moments.low = eng.mom_state[0]
+    moments.high = eng.mom_state[1]
+    if hasattr(moments, "rng_counter"):      # resume continues the noise stream instead of replaying steps 0..k
+        eng.rng_counter.copy_(moments.rng_counter.reshape(1).to(eng.rng_counter.device))
+        moments.rng_counter = eng.rng_counter
 
 
 def train(
@@ -104,19 +135,13 @@ def train(
     _adopt_optimizer(eng, eng.wm, world_optimizer, "world")
     _adopt_optimizer(eng, eng.actor, actor_optimizer, "actor")
     _adopt_optimizer(eng, eng.critic, critic_optimizer, "critic")
-    if moments is not None and not getattr(moments, "_dv3_bound", False):
-        eng.mom_state[0:1].copy_(moments.low.reshape(1))
-        eng.mom_state[1:2].copy_(moments.high.reshape(1))
-        moments._dv3_bound = True
+    _bind_moments(eng, moments)
     eng.load_batch(data)
     if noise is not None or not _graphs_enabled(eng):
         eng.load_noise(noise)
         eng.step()
     else:
         _graphed_step(eng)
-    if moments is not None:
-        moments.low = eng.mom_state[0].clone()
-        moments.high = eng.mom_state[1].clone()
     if aggregator is not None:
         m = eng.metrics
         for i, k in enumerate(METRIC_KEYS):
@@ -124,11 +149,36 @@ def train(
 
 
 class Moments(torch.nn.Module):
-    """State holder with the reference's buffers (algos/dreamer_v3/utils.py:16-41); the percentile / EMA arithmetic runs
-    in dv3_moments inside the step."""
+    """The reference's return-normalisation state (algos/dreamer_v3/utils.py:16-41) with the same buffers, constructor and
+    `forward`.  Inside train() the percentile / EMA arithmetic runs in dv3_moments on the engine's copy of the state, which
+    `low` / `high` alias after the first call; `forward` is the same arithmetic for any other caller.  `rng_counter` (ours) is the
+    position of the step's counter-based noise generator, saved with the module so that a resumed run continues the stream."""
 
     def __init__(self, fabric=None, decay: float = 0.99, max_: float = 1e8, percentile_low: float = 0.05, percentile_high: float = 0.95):
         super().__init__()
+        self._fabric = fabric
         self._decay, self._max, self._percentile_low, self._percentile_high = decay, max_, percentile_low, percentile_high
         self.register_buffer("low", torch.zeros((), dtype=torch.float32))
         self.register_buffer("high", torch.zeros((), dtype=torch.float32))
+        self.register_buffer("rng_counter", torch.zeros(1, dtype=torch.int64))
+
+    def forward(self, x: torch.Tensor, fabric=None):
+        """utils.py:34-41: EMA of the 5 % / 95 % quantiles over all ranks' values; returns (offset, invscale)."""
+        fabric = fabric if fabric is not None else self._fabric
+        gathered = fabric.all_gather(x).detach() if fabric is not None and hasattr(fabric, "all_gather") else x.detach()
+        gathered = gathered.float().reshape(-1)
+        n = gathered.numel()
+        if gathered.is_cuda:
+            # exact torch.quantile (linear interpolation) through the library's radix select, EMA included
+            from ..._lib import load_library
+
+            state = torch.stack((self.low.reshape(()), self.high.reshape(()))).contiguous()
+            out = torch.empty(2, dtype=torch.float32, device=gathered.device)
+            rc = load_library().dv3_moments(n, gathered.contiguous().data_ptr(), state.data_ptr(), out.data_ptr(), self._decay, self._max,
+                                            self._percentile_low, self._percentile_high, torch.cuda.current_stream(gathered.device).cuda_stream)
+            if rc != 0:
+                raise RuntimeError(f"dv3_moments failed ({rc})")
+            self.low.copy_(state[0])
+            self.high.copy_(state[1])
+            return out[0], out[1]
+        raise RuntimeError("Moments.forward needs CUDA tensors: sheeprl_prey_b200 has no CPU path")

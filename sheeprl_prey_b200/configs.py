@@ -73,6 +73,7 @@ def make_cfg(
         return {"_target_": "torch.optim.Adam", "lr": lr, "eps": eps, "weight_decay": 0, "betas": [0.9, 0.999]}
 
     cfg: Dict[str, Any] = {
+        "seed": 42,                                           # sheeprl/configs/config.yaml
         "per_rank_batch_size": batch_size,
         "per_rank_sequence_length": sequence_length,
         "distribution": {"validate_args": False, "type": "auto"},

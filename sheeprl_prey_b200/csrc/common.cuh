@@ -34,6 +34,16 @@ static inline int dv3_pdl_enabled() {
   return v;
 }
 #endif
+// One-time per-DEVICE set-up (cudaFuncSetAttribute applies to the current device only): true the first time it is called with a given
+// device current.  `mask` is a function-local static, one bit per device ordinal.
+static inline bool dv3_first_call_on_device(unsigned long long* mask) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+  const unsigned long long bit = 1ull << dev;
+  if (*mask & bit) return false;
+  *mask |= bit;
+  return true;
+}
 template <typename... KA, typename... A>
 static inline cudaError_t dv3_launch_pdl(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, A... args) {
   cudaLaunchConfig_t cfg = {};

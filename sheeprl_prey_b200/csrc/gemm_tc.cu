@@ -360,11 +360,10 @@ constexpr int SMEM_BYTES = STAGES * (STAGE_A_BYTES + STAGE_B_BYTES) + (2 * STAGE
 template <int MODE, bool MNMAJ>
 int launch_tc(int M, int N, int K, const float* A, int lda, const float* B, int ldb, float* C, int ldc, const float* bias,
               int accumulate, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;      // per device: the attribute does not carry over to other GPUs of the process
+  if (dv3_first_call_on_device(&configured)) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<MODE, MNMAJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
-    configured = true;
   }
   dim3 grid((N + TBN - 1) / TBN, (M + TBM - 1) / TBM, 1);
   if (grid.y > 65535) return DV3_ERR_UNSUPPORTED;

@@ -454,11 +454,10 @@ int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld, bool mn
 template <bool A_MN, bool B_MN, int BN>
 int launch_tma_bn(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc, const float* bias,
                int accumulate, cudaStream_t stream) {
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;      // per device: the attribute does not carry over to other GPUs of the process
+  if (dv3_first_call_on_device(&configured)) {
     cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tma_kernel<A_MN, B_MN, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) return (int)e;
-    configured = true;
   }
   CUtensorMap tmA, tmB;
   int rc = make_map(&tmA, A, M, K, lda, A_MN);
@@ -517,11 +516,10 @@ extern "C" int dv3_gemm_ln_bf16_tma(int M, int N, int K, const void* A, int lda,
     if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return DV3_ERR_UNSUPPORTED;
     g_encode = reinterpret_cast<EncodeTiledFn>(fn);
   }
-  static bool configured = false;
-  if (!configured) {
+  static unsigned long long configured = 0;      // per device: the attribute does not carry over to other GPUs of the process
+  if (dv3_first_call_on_device(&configured)) {
     cudaError_t e = cudaFuncSetAttribute(gemm_ln_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES_LN);
     if (e != cudaSuccess) return (int)e;
-    configured = true;
   }
   CUtensorMap tmA, tmB;
   int rc = make_map(&tmA, A, M, K, lda, false);

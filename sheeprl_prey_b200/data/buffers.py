@@ -101,7 +101,7 @@ class _EnvView:
 
 class AsyncReplayBuffer:
     def __init__(self, buffer_size: int, n_envs: int = 1, device: Union[torch.device, str] = "cuda", memmap: bool = False,
-                 memmap_dir=None, sequential: bool = False, ops=None):
+                 memmap_dir=None, sequential: bool = False):
         if buffer_size <= 0:
             raise ValueError(f"The buffer size must be greater than zero, got: {buffer_size}")
         if n_envs <= 0:
@@ -113,9 +113,22 @@ class AsyncReplayBuffer:
         self._store: Optional[Dict[str, Tensor]] = None
         self._pos: List[int] = [0] * n_envs
         self._full: List[bool] = [False] * n_envs
-        self._ops = ops
         self._lib = None
         self._draw_env_counts = True
+
+    # ------------------------------------------------------------------ checkpoints (utils/callback.py:23-64 pickles `rb`)
+    def __getstate__(self):
+        """Picklable state: the rings as CPU tensors, no library handle (a ctypes.CDLL cannot be pickled)."""
+        st = {k: v for k, v in self.__dict__.items() if k not in ("_lib", "_keepalive", "_store")}
+        st["_store"] = None if self._store is None else {k: v.cpu() for k, v in self._store.items()}
+        return st
+
+    def __setstate__(self, st):
+        self.__dict__.update(st)
+        self._lib = None
+        if self._store is not None:
+            dev = self._device if (self._device.type != "cuda" or torch.cuda.is_available()) else torch.device("cpu")
+            self._store = {k: v.to(dev) for k, v in self._store.items()}
 
     # ------------------------------------------------------------------ properties of the reference API
     @property
@@ -179,10 +192,6 @@ class AsyncReplayBuffer:
             self._pos[env] = (pos + L) % size
 
     def _ring_write(self, src: Tensor, ring: Tensor, env: int, pos: int, L: int, row_bytes: int) -> None:
-        if self._ops is not None:                       # test seam: CPU statement of the kernel
-            idx = (pos + torch.arange(L)) % self._buffer_size
-            ring[env, idx.to(ring.device)] = src
-            return
         rc = self._library().dv3_buffer_add(src.data_ptr(), ring.data_ptr(), env, pos, L, self._buffer_size, row_bytes, self._stream())
         if rc != 0:
             raise RuntimeError(f"dv3_buffer_add failed ({rc})")
@@ -243,40 +252,48 @@ class AsyncReplayBuffer:
             out = TensorBatch({k: v.reshape(n_samples * batch_size, 1, *v.shape[3:]) for k, v in out.items()}, (n_samples * batch_size, 1))
         return out
 
+    MAX_KEYS_PER_LAUNCH = 8      # dv3_seq_gather takes up to 8 keys per launch (kernel argument block); more keys = more launches
+
     def gather(self, env_id: Tensor, start: Tensor, col: Tensor, samp: Tensor, batch_size: int, T: int, n_samples: int) -> TensorBatch:
         keys = list(self._store.keys())
         out = {k: torch.empty(n_samples, T, batch_size, *self._store[k].shape[2:], dtype=self._store[k].dtype, device=self._device)
                for k in keys}
-        if self._ops is not None:                       # test seam (CPU): plain indexing statement of the kernel
-            t = torch.arange(T)
-            for j in range(env_id.numel()):
-                rows = (int(start[j]) + t) % self._buffer_size
-                for k in keys:
-                    out[k][int(samp[j]), :, int(col[j])] = self._store[k][int(env_id[j]), rows]
-            return TensorBatch(out, (n_samples, T, batch_size))
-        dev = self._device
-        idx = [x.to(dev, non_blocking=True) for x in (env_id, start, col, samp)]
-        n = len(keys)
-        src = (C.c_void_p * n)(*[self._store[k].data_ptr() for k in keys])
-        dst = (C.c_void_p * n)(*[out[k].data_ptr() for k in keys])
-        rb = (C.c_longlong * n)(*[self._store[k][0, 0].numel() * self._store[k].element_size() for k in keys])
-        rc = self._library().dv3_seq_gather(n, C.cast(src, C.c_void_p), C.cast(dst, C.c_void_p), C.cast(rb, C.c_void_p),
-                                            self._buffer_size, T, batch_size, n_samples, idx[0].data_ptr(), idx[1].data_ptr(),
-                                            idx[2].data_ptr(), idx[3].data_ptr(), self._stream())
-        if rc != 0:
-            raise RuntimeError(f"dv3_seq_gather failed ({rc})")
-        self._keepalive = idx
+        self._gather_rows(keys, out, env_id, start, col, samp, batch_size, T, n_samples)
         return TensorBatch(out, (n_samples, T, batch_size))
+
+    def _gather_rows(self, keys, out, env_id, start, col, samp, batch_size, T, n_samples) -> None:
+        dev = self._device
+        # the four index vectors travel in ONE pinned staging buffer and one async copy (they are a few hundred bytes)
+        n_seq = env_id.numel()
+        host = torch.empty(5 * n_seq, dtype=torch.int32).pin_memory() if dev.type == "cuda" else torch.empty(5 * n_seq, dtype=torch.int32)
+        host[:2 * n_seq].view(torch.int64).copy_(start)         # (int64 first: keeps its 8-byte alignment)
+        host[2 * n_seq:3 * n_seq] = env_id
+        host[3 * n_seq:4 * n_seq] = col
+        host[4 * n_seq:] = samp
+        didx = host.to(dev, non_blocking=True)
+        p_start, p_env = didx.data_ptr(), didx.data_ptr() + 8 * n_seq
+        p_col, p_samp = didx.data_ptr() + 12 * n_seq, didx.data_ptr() + 16 * n_seq
+        for k0 in range(0, len(keys), self.MAX_KEYS_PER_LAUNCH):
+            kk = keys[k0:k0 + self.MAX_KEYS_PER_LAUNCH]
+            n = len(kk)
+            src = (C.c_void_p * n)(*[self._store[k].data_ptr() for k in kk])
+            dst = (C.c_void_p * n)(*[out[k].data_ptr() for k in kk])
+            rb = (C.c_longlong * n)(*[self._store[k][0, 0].numel() * self._store[k].element_size() for k in kk])
+            rc = self._library().dv3_seq_gather(n, C.cast(src, C.c_void_p), C.cast(dst, C.c_void_p), C.cast(rb, C.c_void_p),
+                                                self._buffer_size, T, batch_size, n_samples, p_env, p_start, p_col, p_samp, self._stream())
+            if rc != 0:
+                raise RuntimeError(f"dv3_seq_gather failed ({rc}) for keys {kk}")
+        self._keepalive = (host, didx)
 
 
 class SequentialReplayBuffer(AsyncReplayBuffer):
     """Single-ring sequential buffer (buffers.py:219-339).  DreamerV3 only ever instantiates it with n_envs=1 (one per
     environment inside AsyncReplayBuffer, buffers.py:630-640), which is what is supported here."""
 
-    def __init__(self, buffer_size: int, n_envs: int = 1, device="cuda", memmap: bool = False, memmap_dir=None, ops=None):
+    def __init__(self, buffer_size: int, n_envs: int = 1, device="cuda", memmap: bool = False, memmap_dir=None):
         if n_envs != 1:
             raise NotImplementedError("SequentialReplayBuffer with n_envs > 1 is not on the DreamerV3 path; use AsyncReplayBuffer")
-        super().__init__(buffer_size, n_envs, device, memmap, memmap_dir, sequential=True, ops=ops)
+        super().__init__(buffer_size, n_envs, device, memmap, memmap_dir, sequential=True)
         self._draw_env_counts = False
 
     @property

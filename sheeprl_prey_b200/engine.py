@@ -562,6 +562,8 @@ class DV3Engine:
                 for h in pending:
                     self.dist.finish_reduce(h)
         hp = self.opt_hparams[tag]
+        if max_norm is None or max_norm <= 0:      # the reference skips clipping then (dreamer_v3.py:180-186); inf makes the coefficient clamp to 1
+            max_norm = float("inf")
         self.ops.adam_clip(arena.flat, arena.grad, arena.m, arena.v, arena.step, hp["lr"], hp["beta1"], hp["beta2"], hp["eps"],
                            max_norm, self.metrics, _SLOT[slot])
 

@@ -5,12 +5,14 @@ import pytest
 import torch
 
 from sheeprl_prey_b200.data.buffers import AsyncReplayBuffer, SequentialReplayBuffer, plan_sequential_starts
-from util import load_golden
+from util import cpu_replay_buffer, load_golden
+
+CpuAsync, CpuSequential = cpu_replay_buffer("AsyncReplayBuffer"), cpu_replay_buffer("SequentialReplayBuffer")
 
 
-def _replay_session(sess, device, ops):
+def _replay_session(sess, device, cls):
     torch.manual_seed(sess["seed"])
-    rb = AsyncReplayBuffer(sess["size"], sess["n_envs"], device=device, sequential=True, ops=ops)
+    rb = cls(sess["size"], sess["n_envs"], device=device, sequential=True)
     it = iter(sess["samples"])
     for ev in sess["script"]:
         if ev[0] == "add":
@@ -26,21 +28,21 @@ def _replay_session(sess, device, ops):
 
 def test_golden_sessions_host_logic():
     for sess in load_golden("buffers.pt"):
-        _replay_session(sess, "cpu", "cpu")
+        _replay_session(sess, "cpu", CpuAsync)
 
 
 @pytest.mark.gpu
 def test_golden_sessions_gpu():
     for sess in load_golden("buffers.pt"):
-        _replay_session(sess, "cuda:0", None)
+        _replay_session(sess, "cuda:0", AsyncReplayBuffer)
 
 
 def test_constructor_guards_and_errors():
     with pytest.raises(ValueError):
-        AsyncReplayBuffer(-1, ops="cpu")
+        AsyncReplayBuffer(-1)
     with pytest.raises(ValueError):
-        AsyncReplayBuffer(1, -1, ops="cpu")
-    rb = SequentialReplayBuffer(10, 1, device="cpu", ops="cpu")
+        AsyncReplayBuffer(1, -1)
+    rb = CpuSequential(10, 1, device="cpu")
     with pytest.raises(RuntimeError):
         rb.sample(2, sequence_length=2)
     rb.add({"t": torch.rand(5, 1, 1)})
@@ -53,13 +55,13 @@ def test_constructor_guards_and_errors():
 
 def test_sequences_never_straddle_the_write_head():
     size, T = 20, 6
-    rb = SequentialReplayBuffer(size, 1, device="cpu", ops="cpu")
+    rb = CpuSequential(size, 1, device="cpu")
     rb.add({"t": torch.arange(27, dtype=torch.float32).view(27, 1, 1)})   # full, pos = 7
     assert rb.full == (True,) and rb._pos[0] == 7
     s = rb.sample(256, sequence_length=T)["t"][0, :, :, 0]                 # [T, 256]
     assert bool((s[1:] - s[:-1] == 1).all())                               # consecutive in time => never crosses pos
     # not full: stays below pos
-    rb2 = SequentialReplayBuffer(size, 1, device="cpu", ops="cpu")
+    rb2 = CpuSequential(size, 1, device="cpu")
     rb2.add({"t": torch.arange(9, dtype=torch.float32).view(9, 1, 1)})
     s2 = rb2.sample(128, sequence_length=4)["t"]
     assert float(s2.max()) <= 8
@@ -79,7 +81,7 @@ def test_start_distribution_matches_reference_list_semantics():
 
 
 def test_env_view_pokes_storage():
-    rb = AsyncReplayBuffer(6, 2, device="cpu", sequential=True, ops="cpu")
+    rb = CpuAsync(6, 2, device="cpu", sequential=True)
     rb.add({"dones": torch.zeros(3, 2, 1)})
     rb.buffer[1]["dones"][(rb.buffer[1]._pos - 1) % rb.buffer_size] = 1.0     # dreamer_v3.py:636-640
     assert float(rb._store["dones"][1, 2, 0]) == 1.0 and float(rb._store["dones"][0].sum()) == 0.0
@@ -112,3 +114,40 @@ def test_gather_large_bit_exact():
     idx = torch.arange(L - size, L)
     expect[idx % size] = chunk["state"][idx, 2]
     assert torch.equal(rb._store["state"][2].cpu(), expect)
+
+
+def test_buffer_pickles_without_the_library_handle():
+    """The checkpoint callback pickles the buffer (utils/callback.py:23-64): state survives, the ctypes handle does not travel."""
+    import pickle
+
+    rb = CpuAsync(9, 2, device="cpu", sequential=True)
+    rb.add({"state": torch.randn(5, 2, 3), "dones": torch.zeros(5, 2, 1)})
+    rb._lib = object()                       # stands for the loaded CDLL
+    rb2 = pickle.loads(pickle.dumps(rb))
+    assert rb2._lib is None and rb2._pos == rb._pos and rb2._full == rb._full
+    assert all(torch.equal(rb2._store[k], rb._store[k]) for k in rb._store)
+    torch.manual_seed(1)
+    a = rb.sample(4, sequence_length=3)
+    torch.manual_seed(1)
+    b = rb2.sample(4, sequence_length=3)
+    assert all(torch.equal(a[k], b[k]) for k in a)
+
+
+@pytest.mark.gpu
+def test_gather_with_more_keys_than_one_launch_takes():
+    """More than 8 keys (4 bookkeeping keys + many observation keys): the gather is issued in chunks of 8 keys."""
+    dev = "cuda:0"
+    rb = AsyncReplayBuffer(64, 2, device=dev, sequential=True)
+    g = torch.Generator().manual_seed(3)
+    data = {f"obs{i}": torch.randn(80, 2, 3 + i, generator=g) for i in range(9)}
+    data.update(actions=torch.randn(80, 2, 4, generator=g), rewards=torch.randn(80, 2, 1, generator=g), dones=torch.zeros(80, 2, 1),
+                is_first=torch.zeros(80, 2, 1))
+    rb.add(data)
+    torch.manual_seed(5)
+    env_id, start, col, samp = rb.plan(6, 7, 2)
+    out = rb.gather(env_id, start, col, samp, 6, 7, 2)
+    t = torch.arange(7)
+    for j in range(env_id.numel()):
+        rows = (int(start[j]) + t) % 64
+        for k in data:
+            assert torch.equal(out[k][int(samp[j]), :, int(col[j])].cpu(), rb._store[k][int(env_id[j])].cpu()[rows]), k
