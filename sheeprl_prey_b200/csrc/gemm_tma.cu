@@ -60,6 +60,11 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* t
       "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer)
       : "memory");
 }
+__device__ __forceinline__ uint32_t elect_one_sync() {
+  uint32_t pred = 0;
+  asm volatile("{\n.reg .b32 rx;\n.reg .pred px;\nelect.sync rx|px, %1;\n@px mov.s32 %0, 1;\n}\n" : "+r"(pred) : "r"(0xFFFFFFFFu));
+  return pred;
+}
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {   // K-major SWIZZLE_128B (see gemm_tc.cu)
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
@@ -101,7 +106,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;   // provably warp-uniform
   const int m0 = blockIdx.y * TBM, n0 = blockIdx.x * BN;
   const int total_kb = (K + TBK - 1) / TBK;
   const int kb0 = blockIdx.z * kb_per_split;
@@ -125,13 +130,16 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   const uint32_t tmem_base = *tmem_ptr_smem;
   pdl_sync();     // everything above (barriers, TMEM, descriptor prefetch) overlaps the tail of the previous kernel on the stream
 
+  // Both single-thread roles run WARP-UNIFORM code with elect.sync around the asynchronous instruction: issued from a divergent
+  // branch (`if (lane == 0)`) every tcgen05.mma / TMA instruction costs an ELECT + R2UR emulation loop in SASS (84 vs 44-68 clk per
+  // MMA, profiles/r02a_probe_umma.md), which made the main loop issue-bound.
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % STAGES;
-        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
-        mbar_wait(&empty_bar[s], ph ^ 1u);
+    for (int kb = 0; kb < num_kb; ++kb) {
+      const int s = kb % STAGES;
+      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      mbar_wait(&empty_bar[s], ph ^ 1u);
+      if (elect_one_sync()) {
         mbar_expect_tx(&full_bar[s], STAGE_A_BYTES + SB_BYTES);
         const int k0 = (kb0 + kb) * TBK;
         if (A_MN) {
@@ -147,34 +155,37 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           tma_load_2d(smem_b + s * SB_BYTES, &tmB, &full_bar[s], k0, n0);
         }
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
                            ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+    // descriptor of k-step 0 of stage 0; later k-steps / stages only add a constant to the 14-bit address field (units of 16 B).
+    // K-major: 16 bf16 = 32 B along K inside the swizzle atom.  MN-major: 16 k = two 1 KB k-groups.
+    const uint64_t adesc0 = A_MN ? make_smem_desc_mn(smem_u32(smem_a)) : make_smem_desc(smem_u32(smem_a));
+    const uint64_t bdesc0 = B_MN ? make_smem_desc_mn(smem_u32(smem_b)) : make_smem_desc(smem_u32(smem_b));
+    constexpr uint32_t A_KSTEP = (A_MN ? 2048 : 32) >> 4, B_KSTEP = (B_MN ? 2048 : 32) >> 4;
     for (int kb = 0; kb < num_kb; ++kb) {
       const int s = kb % STAGES;
       const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
       mbar_wait(&full_bar[s], ph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      if (lane == 0) {
-        const uint32_t a_addr = smem_u32(smem_a + s * STAGE_A_BYTES);
-        const uint32_t b_addr = smem_u32(smem_b + s * SB_BYTES);
+      const uint64_t ad = adesc0 + (uint64_t)((uint32_t)(s * STAGE_A_BYTES) >> 4), bd = bdesc0 + (uint64_t)((uint32_t)(s * SB_BYTES) >> 4);
 #pragma unroll
-        for (int k = 0; k < TBK / 16; ++k) {
-          // K-major: 16 bf16 = 32 B along K inside the swizzle atom.  MN-major: 16 k = two 1 KB k-groups.
-          const uint64_t adesc = A_MN ? make_smem_desc_mn(a_addr + k * 2048) : make_smem_desc(a_addr + k * 32);
-          const uint64_t bdesc = B_MN ? make_smem_desc_mn(b_addr + k * 2048) : make_smem_desc(b_addr + k * 32);
-          const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+      for (int k = 0; k < TBK / 16; ++k) {
+        const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+        if (elect_one_sync())
           asm volatile(
               "{\n"
               ".reg .pred p;\n"
               "setp.ne.b32 p, %4, 0;\n"
               "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
               "}\n" ::"r"(tmem_base),
-              "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+              "l"(ad + (uint64_t)(k * A_KSTEP)), "l"(bd + (uint64_t)(k * B_KSTEP)), "r"(idesc), "r"(accum)
               : "memory");
-        }
+      }
+      if (elect_one_sync()) {
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[s])) : "memory");
         if (kb == num_kb - 1)
           asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(tmem_full_bar)) : "memory");
