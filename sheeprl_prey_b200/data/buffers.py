@@ -119,7 +119,7 @@ class AsyncReplayBuffer:
     # ------------------------------------------------------------------ checkpoints (utils/callback.py:23-64 pickles `rb`)
     def __getstate__(self):
         """Picklable state: the rings as CPU tensors, no library handle (a ctypes.CDLL cannot be pickled)."""
-        st = {k: v for k, v in self.__dict__.items() if k not in ("_lib", "_keepalive", "_store")}
+        st = {k: v for k, v in self.__dict__.items() if k not in ("_lib", "_keepalive", "_store", "_stage", "_stage_ev", "_stage_i")}
         st["_store"] = None if self._store is None else {k: v.cpu() for k, v in self._store.items()}
         return st
 
@@ -265,7 +265,7 @@ class AsyncReplayBuffer:
         dev = self._device
         # the four index vectors travel in ONE pinned staging buffer and one async copy (they are a few hundred bytes)
         n_seq = env_id.numel()
-        host = torch.empty(5 * n_seq, dtype=torch.int32).pin_memory() if dev.type == "cuda" else torch.empty(5 * n_seq, dtype=torch.int32)
+        host = self._index_staging(5 * n_seq)
         host[:2 * n_seq].view(torch.int64).copy_(start)         # (int64 first: keeps its 8-byte alignment)
         host[2 * n_seq:3 * n_seq] = env_id
         host[3 * n_seq:4 * n_seq] = col
@@ -283,7 +283,23 @@ class AsyncReplayBuffer:
                                                 self._buffer_size, T, batch_size, n_samples, p_env, p_start, p_col, p_samp, self._stream())
             if rc != 0:
                 raise RuntimeError(f"dv3_seq_gather failed ({rc}) for keys {kk}")
-        self._keepalive = (host, didx)
+        self._keepalive = didx
+        if dev.type == "cuda":
+            self._stage_ev[self._stage_i].record(torch.cuda.current_stream(dev))
+
+    def _index_staging(self, n: int) -> Tensor:
+        """Pinned host staging for the index upload: a small ring of reusable buffers (allocating pinned memory per call costs more
+        than the gather itself); a buffer is reused only after the copy that read it has completed."""
+        if self._device.type != "cuda":
+            return torch.empty(n, dtype=torch.int32)
+        ring = self.__dict__.setdefault("_stage", [])
+        if not ring or ring[0].numel() < n:
+            ring[:] = [torch.empty(max(n, 1024), dtype=torch.int32).pin_memory() for _ in range(8)]
+            self._stage_ev = [torch.cuda.Event() for _ in range(8)]
+            self._stage_i = -1
+        self._stage_i = (self._stage_i + 1) % len(ring)
+        self._stage_ev[self._stage_i].synchronize()
+        return ring[self._stage_i][:n]
 
 
 class SequentialReplayBuffer(AsyncReplayBuffer):
