@@ -630,6 +630,7 @@ class CudaOps:
                     _chk(rc, "dv3_rssm_observe_fwd_tc")
             self.use_tc_scan = False
         if eng.B > 16:
+            self.scan_kernel = None
             return False
         if self.use_mirrors and self.use_cluster_scan and getattr(eng, "aW", None) is not None:
             # one thread-block cluster, bf16 weights streamed into mma.sync fragments, DSMEM exchange (rssm_scan_cluster.cu)
@@ -651,6 +652,7 @@ class CudaOps:
         self.scan_kernel = "cooperative"
         rc = self.lib.dv3_rssm_observe_fwd(C.addressof(a), self._s())
         if rc == -2:
+            self.scan_kernel = None
             return False
         _chk(rc, "dv3_rssm_observe_fwd")
         self.launches += 1

@@ -162,18 +162,24 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
 #pragma unroll 1
     for (int t = 0; t < a.T; ++t) {
       const uint32_t par = (uint32_t)t & 1u;
+#define MDBG(p) do { if (k.dbg && c == 0 && blockIdx.x == 0 && lane == 0 && t == 2) k.dbg[p] = clock64(); } while (0)
+      MDBG(40);
       if (elect_one()) mbar_expect_tx(&act_bar[X_FEAT], feat_bytes);
       __syncwarp();
       mbar_wait(&act_bar[X_FEAT], par);
+      MDBG(41);
       mma_seg(pl, SEG_GF, xf_a, tmem_base, rg, pos);
       if (elect_one()) umma_commit(&acc_bar[0]);
       __syncwarp();
+      MDBG(42);
       if (elect_one()) mbar_expect_tx(&act_bar[X_H], h_bytes);
       __syncwarp();
       mbar_wait(&act_bar[X_H], par);
+      MDBG(43);
       mma_seg(pl, SEG_R0, xh_a, tmem_base, rg, pos);
       if (elect_one()) umma_commit(&acc_bar[1]);
       __syncwarp();
+      MDBG(44);
       if (t + 1 < a.T) {
         // reset rows of step t+1 see h = 0 (agent.py:379-381); the posterior of step t above needed the unmasked h_t
         const uint32_t rm = s_rmask[t + 1] & ((1u << Bv) - 1u);
@@ -188,12 +194,15 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
         }
         mma_seg(pl, SEG_GH, xh_a, tmem_base, rg, pos);
       }
+      MDBG(45);
       if (elect_one()) mbar_expect_tx(&act_bar[X_HID], hid_bytes);
       __syncwarp();
       mbar_wait(&act_bar[X_HID], par);
+      MDBG(46);
       mma_seg(pl, SEG_R1, xhid_a, tmem_base, rg, pos);
       if (elect_one()) umma_commit(&acc_bar[2]);
       __syncwarp();
+      MDBG(47);
     }
   } else {
     // ===================================================== epilogue =====================================================
@@ -246,7 +255,7 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
     // Partials (mean, M2) go to lnp[c][m] of every peer (st.async, completes on the peer's barrier); after the wait the CL partials
     // are merged with Chan's formula (equal counts).  Returns the statistics in every lane of the half-warp.
     auto row_stats = [&](const float* vals, int n, float* lnp_x, uint64_t* bar, uint32_t parity, float eps, float* gmean, float* grstd,
-                         float& mean_out, float& rstd_out) {
+                         float& mean_out, float& rstd_out, long long* dbg4) {
       float sx = 0.f;
       for (int j = l16; j < n; j += 16) sx += vals[j * OB + mrow];
 #pragma unroll
@@ -256,8 +265,11 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
       for (int j = l16; j < n; j += 16) { const float d = vals[j * OB + mrow] - mu_c; q = fmaf(d, d, q); }
 #pragma unroll
       for (int o = 8; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+      if (dbg4) dbg4[0] = clock64();
       if (l16 < CL) st_async_f2(mapa(smem_u32(lnp_x + (c * NB + mrow) * 2), (uint32_t)l16), mu_c, q, mapa(smem_u32(bar), (uint32_t)l16));
+      if (dbg4) dbg4[1] = clock64();
       mbar_wait(bar, parity);
+      if (dbg4) dbg4[2] = clock64();
       const float2 pc = (l16 < CL) ? reinterpret_cast<const float2*>(lnp_x)[l16 * NB + mrow] : make_float2(0.f, 0.f);
       float sm = pc.x;
 #pragma unroll
@@ -328,7 +340,7 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
       __syncwarp();
       SDBG(2);
       float mu, rs;
-      row_stats(outb, uper, lnp0, &stat_bar[ST_FEAT], par, 1e-3f, a.feat_mean + row0, a.feat_rstd + row0, mu, rs);
+      row_stats(outb, uper, lnp0, &stat_bar[ST_FEAT], par, 1e-3f, a.feat_mean + row0, a.feat_rstd + row0, mu, rs, nullptr);
       SDBG(3);
 #pragma unroll 1
       for (int ul = 2 * l16; ul < uper; ul += 32) {              // -> one 4 B store into the operand layout
@@ -368,7 +380,8 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
       tmem_to_outb(tmem_base, col_g, 3 * dper, pl.seg[SEG_GH].m64, outb, nullptr, 0, ew, lane);          // outb row = gate * dper + dl
       epi_bar();
       SDBG(8);
-      row_stats(outb, 3 * dper, lnp1, &stat_bar[ST_GRU], par, 1e-5f, a.gru_mean + row0, a.gru_rstd + row0, mu, rs);
+      row_stats(outb, 3 * dper, lnp1, &stat_bar[ST_GRU], par, 1e-5f, a.gru_mean + row0, a.gru_rstd + row0, mu, rs,
+                (k.dbg && c == 0 && blockIdx.x == 0 && et == 0 && t == 2) ? k.dbg + 32 : nullptr);
       SDBG(9);
 #pragma unroll 1
       for (int dl = 2 * l16; dl < dper; dl += 32) {
@@ -409,7 +422,7 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_fwd_tc_kernel(const __grid
       tmem_to_outb(tmem_base, col_r0, hper, pl.seg[SEG_R0].m64, outb, s_ew, hper, ew, lane);
       epi_bar();
       SDBG(14);
-      row_stats(outb, hper, lnp2, &stat_bar[ST_HID], par, 1e-5f, a.hidr_mean + row0, a.hidr_rstd + row0, mu, rs);
+      row_stats(outb, hper, lnp2, &stat_bar[ST_HID], par, 1e-5f, a.hidr_mean + row0, a.hidr_rstd + row0, mu, rs, nullptr);
       SDBG(15);
 #pragma unroll 1
       for (int hl_ = 2 * l16; hl_ < hper; hl_ += 32) {

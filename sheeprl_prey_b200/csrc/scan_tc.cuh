@@ -87,6 +87,14 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   if (mbar_try(bar, parity)) return;
   mbar_wait_slow(bar, parity);
 }
+// the same wait without a function call: used by the single-role warps, whose loops must stay free of calls so that ptxas keeps their
+// descriptor arithmetic in uniform registers (a call inside the loop pushed it into vector registers + R2UR: ~90 clk per MMA issued)
+__device__ __forceinline__ void mbar_wait_inline(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try(bar, parity)) {
+    if (++spins > (1u << 24)) __trap();
+  }
+}
 __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
   uint32_t r;
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
@@ -172,7 +180,7 @@ __device__ __forceinline__ void produce_seg(const Plan& pl, int si, const uint8_
 #pragma unroll 1
   for (int ci = cb; ci < ce; ++ci) {
     const uint32_t off = pl.c[ci].off16, bytes = (uint32_t)pl.c[ci].bytes16 << 4;
-    mbar_wait(&rg.empty[pos.slot], pos.phase ^ 1u);
+    mbar_wait_inline(&rg.empty[pos.slot], pos.phase ^ 1u);
     if (elect_one()) {
       mbar_expect_tx(&rg.full[pos.slot], bytes);
       bulk_g2s(rg.base + pos.slot * rg.slot_bytes, stream_cta + ((size_t)off << 4), bytes, &rg.full[pos.slot]);
@@ -189,14 +197,14 @@ __device__ __forceinline__ void mma_seg(const Plan& pl, int si, uint32_t bbuf, u
 #pragma unroll 1
   for (int ci = cb; ci < ce; ++ci) {
     const uint32_t nmma = pl.c[ci].nmma, lbo16 = pl.c[ci].lbo16, bk8 = pl.c[ci].b_k8, tile = pl.c[ci].tile, k0 = pl.c[ci].k0;
-    mbar_wait(&rg.full[pos.slot], pos.phase);
+    mbar_wait_inline(&rg.full[pos.slot], pos.phase);
     tc_fence_after();
     const uint64_t ad0 = desc_ns(rg.base + pos.slot * rg.slot_bytes, lbo16 << 4);
     const uint64_t bd0 = desc_ns(bbuf + bk8 * BROW, BROW);
     const uint32_t dcol = tmem_base + col + tile * NB;
     const uint32_t astep = lbo16 * 2, bstep = (2 * BROW) >> 4;       // one MMA = K 16 = two 8-wide k chunks
     uint32_t acc = (fresh && k0 == 0) ? 0u : 1u;
-#pragma unroll 2
+#pragma unroll 4
     for (uint32_t j = 0; j < nmma; ++j) {
       if (elect_one()) umma_n16(dcol, ad0 + (uint64_t)(j * astep), bd0 + (uint64_t)(j * bstep), idesc, acc);
       acc = 1u;
