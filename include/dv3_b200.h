@@ -262,6 +262,42 @@ int dv3_actor_loss(int M, int n_heads, const int* head_dims_host, const float* r
                    const float* lam, const float* values, const float* discount, const float* mom, float mix, float ent_coef,
                    float scale, float* loss_rows, float* draw, int ldd, void* stream);
 
+/* ---- imagination rollout as one persistent kernel (rollout_tc.cu): RSSM.imagination (agent.py:439-455) + Actor.forward
+ * (agent.py:682-739) for H steps from N start states, dreamer_v3.py:219-257, bf16 tensor-core mode.  Rows are split into 128-row
+ * blocks, each run by a thread-block cluster whose CTAs own 1/CL of every layer's output features; every layer is a TMA-fed
+ * tcgen05 GEMM with its LayerNorm / GRU / unimix-sampling epilogue, layer outputs meet in the global trajectory / activation buffers.
+ * All operands with a 16 suffix are bf16 copies with the layout of their fp32 originals.  Inputs: rows [0, N) of traj / traj16 hold
+ * the start states [z one-hot | h].  DV3_ERR_UNSUPPORTED when the shape is outside the plan (N % 128, several action heads,
+ * per-CTA slices that are not multiples of 16, ...): the caller then composes the rollout from the per-op entry points. */
+#define DV3_ROLLOUT_MAX_LAYERS 6
+typedef struct Dv3RolloutArgs {
+  int N, H, G, Kc, S, D, U, Hh, A, lat, L, Ua, nh;
+  int head_dim[4], head_off[4];
+  float unimix;
+  /* weights (bf16, K contiguous) and their row strides in elements */
+  const void* Wz16; int ld_wz;            /* Wmlp[:, :S]        [U, S]     */
+  const void* Wgru16; int ld_wgru;        /* rnn.linear.weight  [3D, D+U]  */
+  const void* Wt016; int ld_wt0;          /* transition layer 0 [Hh, D]    */
+  const void* Wt116; int ld_wt1;          /* transition head    [S, Hh]    */
+  const void* Wa16[DV3_ROLLOUT_MAX_LAYERS]; int ld_wa[DV3_ROLLOUT_MAX_LAYERS];   /* actor layers [Ua, lat] / [Ua, Ua] */
+  const void* Wh16; int ld_wh;            /* actor head         [A, Ua]    */
+  /* fp32 parameters */
+  const float* W_mlpaT; int ld_mlpaT;     /* Wmlp[:, S:]^T [A, U]: one-hot actions enter as a row gather */
+  const float* g_mlp; const float* b_mlp; const float* g_gru; const float* b_gru;
+  const float* bt0; const float* g_t; const float* b_t; const float* bt1;
+  const float* ga[DV3_ROLLOUT_MAX_LAYERS]; const float* ba[DV3_ROLLOUT_MAX_LAYERS]; const float* bh;
+  /* sampling noise / teacher forcing */
+  const float* u_z; const float* u_act0; const float* u_act;      /* [H, N, G], [N, nh], [H, N, nh] */
+  const int* f_z; const int* f_act;                               /* forced draws [H, N, G] / [(H+1) N, nh], or NULL */
+  /* state and outputs */
+  float* traj; void* traj16;              /* [(H+1) N, lat] */
+  void* feat16; void* thid16;             /* scratch [N, U], [N, Hh] bf16 */
+  float* apre[DV3_ROLLOUT_MAX_LAYERS]; float* aact[DV3_ROLLOUT_MAX_LAYERS]; void* aact16[DV3_ROLLOUT_MAX_LAYERS];   /* [(H+1) N, Ua] */
+  float* amean[DV3_ROLLOUT_MAX_LAYERS]; float* arstd[DV3_ROLLOUT_MAX_LAYERS];                                       /* [(H+1) N]     */
+  float* aout; int* act_idx; float* acts; int* z_idx;             /* [(H+1) N, A], [(H+1) N, nh], [(H+1) N, A] or NULL, [H, N, G] */
+} Dv3RolloutArgs;
+int dv3_rollout_tc(const Dv3RolloutArgs* args, void* stream);
+
 /* ---- optimizer: clip_grad_norm_ + torch.optim.Adam.step, dreamer_v3.py:179-187,:318-323,:339-344 ---------- */
 size_t dv3_adam_clip_scratch_bytes(void);
 int dv3_adam_clip(size_t n, float* p, const float* g, float* m, float* v, float* step, double lr, double beta1, double beta2,

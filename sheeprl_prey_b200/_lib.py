@@ -54,6 +54,7 @@ SIGNATURES = {
     "dv3_scan_tc_bwd_config": [_i, _i, _i, _i, _i, c_fp, c_fp],
     "dv3_scan_tc_bwd_pack": [_i, _i, _i, _i, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
     "dv3_rssm_observe_bwd_tc": [c_fp, c_fp, c_fp],
+    "dv3_rollout_tc": [c_fp, c_fp],
     "dv3_pack_mma_a": [_i, _i, c_fp, _ll, _ll, c_fp, c_fp],
     "dv3_ln_act_fwd_rows_gather": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, _i, c_fp, c_fp],
     "dv3_ln_act_bwd_fused": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, c_fp, _sz, c_fp],
@@ -113,6 +114,26 @@ class ScanClusterExtra(C.Structure):
 class ScanTcExtra(C.Structure):
     """Mirror of `Dv3ScanTcExtra` (include/dv3_b200.h)."""
     _fields_ = [("stream", c_fp), ("WmlpzT", c_fp), ("aW", c_fp)]
+
+
+ROLLOUT_MAX_LAYERS = 6
+
+
+class RolloutArgs(C.Structure):
+    """Mirror of `Dv3RolloutArgs` (include/dv3_b200.h)."""
+    _L = ROLLOUT_MAX_LAYERS
+    _fields_ = [
+        ("N", _i), ("H", _i), ("G", _i), ("Kc", _i), ("S", _i), ("D", _i), ("U", _i), ("Hh", _i), ("A", _i), ("lat", _i), ("L", _i), ("Ua", _i),
+        ("nh", _i), ("head_dim", _i * 4), ("head_off", _i * 4), ("unimix", _f),
+        ("Wz16", c_fp), ("ld_wz", _i), ("Wgru16", c_fp), ("ld_wgru", _i), ("Wt016", c_fp), ("ld_wt0", _i), ("Wt116", c_fp), ("ld_wt1", _i),
+        ("Wa16", c_fp * _L), ("ld_wa", _i * _L), ("Wh16", c_fp), ("ld_wh", _i),
+        ("W_mlpaT", c_fp), ("ld_mlpaT", _i), ("g_mlp", c_fp), ("b_mlp", c_fp), ("g_gru", c_fp), ("b_gru", c_fp),
+        ("bt0", c_fp), ("g_t", c_fp), ("b_t", c_fp), ("bt1", c_fp), ("ga", c_fp * _L), ("ba", c_fp * _L), ("bh", c_fp),
+        ("u_z", c_fp), ("u_act0", c_fp), ("u_act", c_fp), ("f_z", c_fp), ("f_act", c_fp),
+        ("traj", c_fp), ("traj16", c_fp), ("feat16", c_fp), ("thid16", c_fp),
+        ("apre", c_fp * _L), ("aact", c_fp * _L), ("aact16", c_fp * _L), ("amean", c_fp * _L), ("arstd", c_fp * _L),
+        ("aout", c_fp), ("act_idx", c_fp), ("acts", c_fp), ("z_idx", c_fp),
+    ]
 
 
 class ScanBwdArgs(C.Structure):
@@ -204,6 +225,8 @@ class CudaOps:
         self.use_cluster_scan = os.environ.get("DV3_CLUSTER_SCAN", "1") != "0"
         self.use_tc_scan = os.environ.get("DV3_TC_SCAN", "1") != "0"      # tcgen05 scan kernels (rssm_scan_tc.cu), tried first
         self.use_tc_scan_bwd = self.use_tc_scan
+        self.use_rollout_tc = os.environ.get("DV3_ROLLOUT_TC", "1") != "0"   # persistent imagination kernel (rollout_tc.cu), tried first
+        self.rollout_kernel = None
         # Linear+LayerNorm+SiLU in one clustered kernel (dv3_gemm_ln_bf16_tma): correct (tests) but its epilogue -- one thread per row
         # for three TMEM sweeps and 128 SiLUs -- is slower than the separate warp-per-row LayerNorm: 117 vs 130 steps/s.  Opt-in.
         self.use_gemm_ln = os.environ.get("DV3_GEMM_LN", "0") == "1"
@@ -696,6 +719,68 @@ class CudaOps:
         self.launches += 1
         _chk(self.lib.dv3_pack_mma_a(R, K, W.data_ptr(), stride_r, stride_k, buf.data_ptr(), self._s()), "dv3_pack_mma_a")
         return buf.data_ptr()
+
+    def rollout_tc(self, eng, forced) -> bool:
+        """The whole imagination rollout (H steps of GRU + prior + sampling + actor on N rows) in one persistent kernel.  Expects rows
+        [0, N) of eng.traj (and its mirror) to hold the start states and the weight mirrors to be fresh.  False = shape outside the
+        kernel's plan; the engine then composes the rollout from the per-op entry points."""
+        if not (self.use_mirrors and self.use_rollout_tc):
+            return False
+        st, tr = eng.act_stack, eng.trans
+        L = len(st.layers)
+        if L > ROLLOUT_MAX_LAYERS or len(st.heads) != 1 or len(tr.layers) != 1 or len(eng.actions_dim) != 1:
+            return False
+        m16 = self._m16
+        sc = eng.__dict__.setdefault("_rollout_scratch", {})
+        if "feat16" not in sc:
+            sc["feat16"] = torch.zeros(eng.N, eng.U, dtype=torch.bfloat16, device=self.device)
+            sc["thid16"] = torch.zeros(eng.N, eng.Hh, dtype=torch.bfloat16, device=self.device)
+        a = RolloutArgs()
+        a.N, a.H, a.G, a.Kc, a.S, a.D, a.U, a.Hh, a.A, a.lat = eng.N, eng.H, eng.G, eng.K, eng.S, eng.D, eng.U, eng.Hh, eng.A, eng.lat
+        a.L, a.Ua, a.nh = L, st.layers[0]["w"].shape[0], 1
+        a.head_dim[0], a.head_off[0] = eng.actions_dim[0], 0
+        a.unimix = float(eng.cfg.algo.unimix)
+        wl = [eng.Wmlp_z, eng.Wgru, tr.layers[0]["w"], tr.heads[0]["w"], st.heads[0]["w"]] + [Lr["w"] for Lr in st.layers]
+        ptrs = [m16(_p(w)) for w in wl]
+        acts16 = [m16(_p(x)) for x in st.act]
+        t16 = m16(_p(eng.traj))
+        if any(x is None for x in ptrs + acts16) or t16 is None:
+            return False
+        a.Wz16, a.ld_wz = ptrs[0], eng.Wmlp_z.stride(0)
+        a.Wgru16, a.ld_wgru = ptrs[1], eng.Wgru.stride(0)
+        a.Wt016, a.ld_wt0 = ptrs[2], tr.layers[0]["w"].stride(0)
+        a.Wt116, a.ld_wt1 = ptrs[3], tr.heads[0]["w"].stride(0)
+        a.Wh16, a.ld_wh = ptrs[4], st.heads[0]["w"].stride(0)
+        for l, Lr in enumerate(st.layers):
+            a.Wa16[l], a.ld_wa[l] = ptrs[5 + l], Lr["w"].stride(0)
+            a.ga[l], a.ba[l] = _p(Lr["g"]), _p(Lr["beta"])
+            a.apre[l], a.aact[l], a.aact16[l] = _p(st.pre[l]), _p(st.act[l]), acts16[l]
+            a.amean[l], a.arstd[l] = _p(st.mean[l]), _p(st.rstd[l])
+            if Lr.get("b") is not None or st.pre[l].stride(0) != a.Ua or st.act[l].stride(0) != a.Ua:
+                return False
+        a.W_mlpaT, a.ld_mlpaT = _p(eng.W_mlpaT), eng.W_mlpaT.stride(0)
+        a.g_mlp, a.b_mlp, a.g_gru, a.b_gru = _p(eng.g_mlp), _p(eng.b_mlp), _p(eng.g_gru), _p(eng.b_gru)
+        a.bt0, a.g_t, a.b_t = _p(tr.layers[0]["b"]), _p(tr.layers[0]["g"]), _p(tr.layers[0]["beta"])
+        a.bt1, a.bh = _p(tr.heads[0]["b"]), _p(st.heads[0]["b"])
+        a.u_z, a.u_act0, a.u_act = _p(eng.u_z), _p(eng.u_act0), _p(eng.u_act)
+        if forced is not None:
+            fz, fa = forced["z_idx"], forced["act_idx"].reshape(eng.M1, -1)
+            assert fz.dtype == torch.int32 and fa.dtype == torch.int32 and fz.is_contiguous() and fa.is_contiguous()
+            sc["forced"] = (fz, fa)
+            a.f_z, a.f_act = _p(fz), _p(fa)
+        a.traj, a.traj16 = _p(eng.traj), t16
+        a.feat16, a.thid16 = _p(sc["feat16"]), _p(sc["thid16"])
+        a.aout, a.act_idx, a.acts, a.z_idx = _p(st.out), _p(eng.act_idx), _p(eng.acts), _p(eng.z_idx)
+        if st.out.stride(0) != eng.A or eng.traj.stride(0) != eng.lat:
+            return False
+        rc = self.lib.dv3_rollout_tc(C.addressof(a), self._s())
+        if rc == -2:
+            self.use_rollout_tc = False
+            return False
+        _chk(rc, "dv3_rollout_tc")
+        self.launches += 1
+        self.rollout_kernel = "tcgen05"
+        return True
 
     def unimix_bwd_prep(self, raw, groups, K, unimix, ps, coef, pn):
         pr, R, _, ldr = _mat(raw)

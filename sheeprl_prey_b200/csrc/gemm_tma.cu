@@ -462,6 +462,17 @@ int make_map(CUtensorMap* tm, const void* base, int rows, int K, int ld, bool mn
   return r == CUDA_SUCCESS ? 0 : 1000 + (int)r;
 }
 
+bool ensure_encode() {
+  if (!g_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return false;
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  return true;
+}
+
 template <bool A_MN, bool B_MN, int BN>
 int launch_tma_bn(int M, int N, int K, const void* A, int lda, const void* B, int ldb, float* C, int ldc, const float* bias,
                int accumulate, cudaStream_t stream) {
@@ -513,6 +524,21 @@ int launch_tma(int M, int N, int K, const void* A, int lda, const void* B, int l
 }
 
 }  // namespace
+
+// K-major bf16 [rows, cols] operand with row stride ld_elems -> SWIZZLE_128B boxes of box_rows x box_cols (box_cols * 2 B = 128 B).
+// Shared with rollout_tc.cu.
+int dv3_internal_make_map_2d(CUtensorMap* tm, const void* base, unsigned long long rows, unsigned long long cols, unsigned long long ld_elems,
+                             unsigned box_rows, unsigned box_cols) {
+  if (!ensure_encode()) return DV3_ERR_UNSUPPORTED;
+  if (((uintptr_t)base & 15) || (ld_elems & 7) || box_rows == 0 || box_rows > 256 || box_cols != 64) return DV3_ERR_UNSUPPORTED;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld_elems * 2};
+  const cuuint32_t box[2] = {box_cols, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? DV3_OK : DV3_ERR_UNSUPPORTED;
+}
 
 extern "C" int dv3_gemm_ln_bf16_tma(int M, int N, int K, const void* A, int lda, const void* B, int ldb, const float* bias, const float* gamma,
                                     const float* beta, float eps, int act, float* pre, int ldp, float* y, int ldy, void* y_bf16, float* mean,

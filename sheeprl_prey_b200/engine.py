@@ -578,6 +578,9 @@ class DV3Engine:
         ops.transpose(self.Wmlp[:, S:], self.W_mlpaT)
         gather_ok = hasattr(ops, "ln_act_fwd_gather") and len(self.actions_dim) <= 4
         ops.copy2d(self.latent, self.traj[:N])
+        fused = getattr(ops, "rollout_tc", None)
+        if fused is not None and fused(self, forced):       # one persistent kernel for all H steps (rollout_tc.cu)
+            return
 
         def policy(i, u, fidx):
             r = slice(i * N, (i + 1) * N)

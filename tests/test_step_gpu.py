@@ -519,6 +519,56 @@ def test_fused_reverse_scan_matches_per_step_composition(size, B, T, obs, acts, 
     assert max(worst.values()) < 3e-2, worst
 
 
+@pytest.mark.parametrize("size,B,T,H,obs,acts", [("S", 16, 64, 15, 14, [100]), ("XS", 16, 64, 15, 4, [2]), ("S", 8, 16, 4, 14, [7])])
+def test_fused_rollout_matches_per_op_rollout(size, B, T, H, obs, acts):
+    """dv3_rollout_tc (the whole imagination rollout as one persistent kernel: TMA-fed tcgen05 layers, LayerNorm / GRU / sampling
+    epilogues, cluster-wide feature split) against the per-op rollout on the same weights and start states, teacher-forced with the
+    per-op rollout's own draws: both run bf16 contractions, so they agree to the bf16-mode tolerance; free-running, the draws differ
+    only where a uniform sits next to a CDF step."""
+    from sheeprl_prey_b200._lib import CudaOps
+
+    cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=H)
+    od = {"state": obs}
+    params = random_params_like(cfg, od, acts, seed=5)
+    data = _to(harness.synthetic_batch(T, B, od, acts, seed=77, done_p=0.05), DEV)
+    noise = _to(harness.synthetic_noise(T, B, H, 32, len(acts), seed=78), DEV)
+    ops = CudaOps(DEV, precision="bf16")
+    eng = engine_from_params(cfg, od, acts, _dev_params(params), ops, DEV)
+    eng.load_batch(data)
+    eng.load_noise(noise)
+    eng.world_forward()
+    names = ["traj", "z_idx", "act_idx"]
+    stack = lambda: {f"pre{i}": t.clone() for i, t in enumerate(eng.act_stack.pre)} | {f"act{i}": t.clone() for i, t in enumerate(eng.act_stack.act)} | \
+        {f"mean{i}": t.clone() for i, t in enumerate(eng.act_stack.mean)} | {f"rstd{i}": t.clone() for i, t in enumerate(eng.act_stack.rstd)} | \
+        {"out": eng.act_stack.out.clone()}   # noqa: E731
+    ops.use_rollout_tc = False
+    eng.imagine()
+    torch.cuda.synchronize()
+    assert ops.rollout_kernel is None
+    ref = {n: getattr(eng, n).clone() for n in names} | stack()
+    forced = dict(z_idx=ref["z_idx"].clone(), act_idx=ref["act_idx"].reshape(H + 1, T * B, -1).clone())
+    ops.use_rollout_tc = True
+    # free-running: same uniforms, own draws
+    eng.imagine()
+    torch.cuda.synchronize()
+    assert ops.rollout_kernel == "tcgen05", ops.rollout_kernel
+    flips_first = float((eng.z_idx[0] != ref["z_idx"][0]).float().mean())
+    assert flips_first < 0.02, flips_first
+    assert float((eng.act_idx[:T * B] != ref["act_idx"][:T * B]).float().mean()) < 0.02
+    # teacher-forced: identical draws -> continuous tensors to the bf16-mode tolerance
+    eng.imagine(forced)
+    torch.cuda.synchronize()
+    got = {n: getattr(eng, n).clone() for n in names} | stack()
+    assert torch.equal(got["z_idx"], ref["z_idx"]) and torch.equal(got["act_idx"], ref["act_idx"])
+    assert torch.equal(got["traj"][:, :eng.S], ref["traj"][:, :eng.S])           # one-hot stochastic states
+    worst = {n: rel(got[n], ref[n]) for n in got if n not in ("z_idx", "act_idx")}
+    assert max(worst.values()) < 2e-2, worst
+    # the bf16 mirrors the behaviour phase reads equal bf16(fp32 buffer)
+    assert torch.equal(ops._m16_view(eng.traj), eng.traj.bfloat16())
+    for t in eng.act_stack.act:
+        assert torch.equal(ops._m16_view(t), t.bfloat16())
+
+
 def test_pixel_step_matches_oracle(cuda_ops):
     """Pixel + vector observations (multi-encoder / multi-decoder, BASELINE config-4 structure at a small size) vs the oracle."""
     B, T, H = 4, 8, 3
