@@ -295,6 +295,7 @@ typedef struct Dv3RolloutArgs {
   float* apre[DV3_ROLLOUT_MAX_LAYERS]; float* aact[DV3_ROLLOUT_MAX_LAYERS]; void* aact16[DV3_ROLLOUT_MAX_LAYERS];   /* [(H+1) N, Ua] */
   float* amean[DV3_ROLLOUT_MAX_LAYERS]; float* arstd[DV3_ROLLOUT_MAX_LAYERS];                                       /* [(H+1) N]     */
   float* aout; int* act_idx; float* acts; int* z_idx;             /* [(H+1) N, A], [(H+1) N, nh], [(H+1) N, A] or NULL, [H, N, G] */
+  long long* dbg;                         /* optional: 60 clock64 stamps of one epilogue thread during step 2 ($DV3_SCAN_DEBUG) */
 } Dv3RolloutArgs;
 int dv3_rollout_tc(const Dv3RolloutArgs* args, void* stream);
 

@@ -132,7 +132,7 @@ class RolloutArgs(C.Structure):
         ("u_z", c_fp), ("u_act0", c_fp), ("u_act", c_fp), ("f_z", c_fp), ("f_act", c_fp),
         ("traj", c_fp), ("traj16", c_fp), ("feat16", c_fp), ("thid16", c_fp),
         ("apre", c_fp * _L), ("aact", c_fp * _L), ("aact16", c_fp * _L), ("amean", c_fp * _L), ("arstd", c_fp * _L),
-        ("aout", c_fp), ("act_idx", c_fp), ("acts", c_fp), ("z_idx", c_fp),
+        ("aout", c_fp), ("act_idx", c_fp), ("acts", c_fp), ("z_idx", c_fp), ("dbg", c_fp),
     ]
 
 
@@ -225,7 +225,8 @@ class CudaOps:
         self.use_cluster_scan = os.environ.get("DV3_CLUSTER_SCAN", "1") != "0"
         self.use_tc_scan = os.environ.get("DV3_TC_SCAN", "1") != "0"      # tcgen05 scan kernels (rssm_scan_tc.cu), tried first
         self.use_tc_scan_bwd = self.use_tc_scan
-        self.use_rollout_tc = os.environ.get("DV3_ROLLOUT_TC", "1") != "0"   # persistent imagination kernel (rollout_tc.cu), tried first
+        # persistent imagination kernel (rollout_tc.cu): on when it beats the per-op rollout inside the step's CUDA graph
+        self.use_rollout_tc = os.environ.get("DV3_ROLLOUT_TC", "0") == "1"
         self.rollout_kernel = None
         # Linear+LayerNorm+SiLU in one clustered kernel (dv3_gemm_ln_bf16_tma): correct (tests) but its epilogue -- one thread per row
         # for three TMEM sweeps and 128 SiLUs -- is slower than the separate warp-per-row LayerNorm: 117 vs 130 steps/s.  Opt-in.
@@ -773,6 +774,7 @@ class CudaOps:
         a.aout, a.act_idx, a.acts, a.z_idx = _p(st.out), _p(eng.act_idx), _p(eng.acts), _p(eng.z_idx)
         if st.out.stride(0) != eng.A or eng.traj.stride(0) != eng.lat:
             return False
+        a.dbg = self.scratch.data_ptr() if os.environ.get("DV3_SCAN_DEBUG") else None
         rc = self.lib.dv3_rollout_tc(C.addressof(a), self._s())
         if rc == -2:
             self.use_rollout_tc = False

