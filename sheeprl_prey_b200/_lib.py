@@ -225,8 +225,8 @@ class CudaOps:
         self.use_cluster_scan = os.environ.get("DV3_CLUSTER_SCAN", "1") != "0"
         self.use_tc_scan = os.environ.get("DV3_TC_SCAN", "1") != "0"      # tcgen05 scan kernels (rssm_scan_tc.cu), tried first
         self.use_tc_scan_bwd = self.use_tc_scan
-        # persistent imagination kernel (rollout_tc.cu): on when it beats the per-op rollout inside the step's CUDA graph
-        self.use_rollout_tc = os.environ.get("DV3_ROLLOUT_TC", "0") == "1"
+        # persistent imagination kernel (rollout_tc.cu), tried first (1.34 ms vs 1.60 ms for the per-op rollout inside a CUDA graph at config S)
+        self.use_rollout_tc = os.environ.get("DV3_ROLLOUT_TC", "1") != "0"
         self.rollout_kernel = None
         # Linear+LayerNorm+SiLU in one clustered kernel (dv3_gemm_ln_bf16_tma): correct (tests) but its epilogue -- one thread per row
         # for three TMEM sweeps and 128 SiLUs -- is slower than the separate warp-per-row LayerNorm: 117 vs 130 steps/s.  Opt-in.

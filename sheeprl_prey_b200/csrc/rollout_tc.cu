@@ -11,9 +11,11 @@
 //     producer warp : TMA (SWIZZLE_128B boxes) of the 128-row activation tile [128 x 64 k] and of this CTA's weight rows [n_own x 64 k]
 //                     into an mbarrier ring;
 //     MMA warp      : tcgen05.mma M128 x N n_own x K16, fp32 accumulator in TMEM;
-//     epilogue warps: thread = row; TMEM -> registers; bias / one-hot action gather; LayerNorm statistics over the CTA's columns,
-//                     exchanged with the peers by st.async on the receiver's mbarrier; normalise, SiLU / GRU gates / unimix +
-//                     inverse-CDF sampling; results to global memory (fp32 for the losses, bf16 as the next layer's operand).
+//     epilogue warps: 16 warps, thread = (row, quarter of the CTA's columns); ONE TMEM -> register pass per stage; bias / one-hot
+//                     action gather; LayerNorm statistics over the CTA's columns (partials of the four quarters through shared
+//                     memory), exchanged with the peers by st.async on the receiver's mbarrier; normalise, SiLU / GRU gates /
+//                     unimix + inverse-CDF sampling; results to global memory (fp32 for the losses, bf16 as the next operand).
+//                     (A first version with one thread per row and 4 epilogue warps was latency-starved: 57-75 k clk per stage.)
 // The layer outputs of all CTAs of a cluster form the next layer's input: they meet in L2-resident global buffers (the trajectory
 // and actor-activation buffers that the behaviour phase needs anyway) and are re-read by TMA after a cluster barrier; generic-proxy
 // stores are ordered before the async-proxy reads with fence.proxy.async.  All TMA loads read this GPU's memory only.
@@ -35,7 +37,8 @@ constexpr int NSTG = 4;
 constexpr int A_BYTES = RM * KB * 2;    // 16 KB
 constexpr int NMAX = 192;               // most output features per CTA and stage
 constexpr int B_BYTES = NMAX * KB * 2;  // 24 KB
-constexpr int NTHR = 192;               // warp 0 producer, warp 1 MMA, warps 2-5 epilogue (thread = row)
+constexpr int NEPI = 512;               // 16 epilogue warps: 4 per TMEM lane quadrant, each taking a quarter of the stage's columns
+constexpr int NTHR = 64 + NEPI;         // warp 0 producer, warp 1 MMA, warps 2-17 epilogue
 constexpr int MAXL = DV3_ROLLOUT_MAX_LAYERS;
 constexpr int MAXCL = 16;
 
@@ -97,29 +100,8 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-  uint32_t r[16];
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
-                 "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-               : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-}
 __device__ __forceinline__ float fsigmoid(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 __device__ __forceinline__ float ftanh(float x) { const float e = __expf(-2.f * fabsf(x)); return copysignf(__fdividef(1.f - e, 1.f + e), x); }
-__device__ __forceinline__ void store16_f32(float* dst, const float* v) {
-#pragma unroll
-  for (int j = 0; j < 16; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-}
-__device__ __forceinline__ void store16_bf16(__nv_bfloat16* dst, const float* v) {
-  uint32_t w[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) { __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]); w[j] = *reinterpret_cast<uint32_t*>(&h); }
-  *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
-  *reinterpret_cast<uint4*>(dst + 8) = make_uint4(w[4], w[5], w[6], w[7]);
-}
 
 // One dense layer of the chain for this CTA: which activation tile(s) to stream, which weight rows, how many output columns.
 struct Stage {
@@ -139,7 +121,8 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   uint8_t* ring_a = smem;
   uint8_t* ring_b = smem + NSTG * A_BYTES;
   float2* lnp = reinterpret_cast<float2*>(smem + NSTG * (A_BYTES + B_BYTES));       // [MAXCL][RM] (mean, M2) pushed by the peers
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(lnp + MAXCL * RM);
+  float2* red = lnp + MAXCL * RM;                                                   // [4][RM] partials of the four column quarters
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(red + 4 * RM);
   uint64_t* empty_bar = full_bar + NSTG;
   uint64_t* acc_bar = empty_bar + NSTG;
   uint64_t* stat_bar = acc_bar + 1;
@@ -223,16 +206,44 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       if (++pp.slot == NSTG) { pp.slot = 0; pp.phase ^= 1u; }
     }
   };
-  // epilogue helpers (thread = row rl of the block)
-  const int ew = warp & 3, rl = 32 * ew + lane;
-  const uint32_t t_lane = tmem_base + ((uint32_t)(32 * ew) << 16);
-  // LayerNorm statistics of a row whose columns are spread over the cluster: (mean, M2) of the own n columns go to every peer's
-  // lnp[c][rl] (st.async, completes on the peer's barrier), then the CL partials are merged (Chan, equal counts).
+  // ---- epilogue: thread = (row rl, column quarter cq).  Hardware warp w reaches TMEM lanes 32 (w % 4) ..: the four warps of one cq
+  // cover the four lane quadrants.
+  const int ewarp = warp - 2, cq = ewarp >> 2, rl = 32 * (warp & 3) + lane;
+  const uint32_t t_lane = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16);
+  auto epi_bar = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(NEPI) : "memory"); };
+  auto ld8 = [&](int col, float* v) {
+    uint32_t r[8];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(t_lane + (uint32_t)col));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]);
+  };
+  auto st8_f32 = [](float* dst, const float* v) {
+    *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  };
+  auto st8_bf16 = [](__nv_bfloat16* dst, const float* v) {
+    uint32_t w[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]); w[j] = *reinterpret_cast<uint32_t*>(&h); }
+    *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+  };
+  // LayerNorm statistics of row rl over columns spread over the 4 quarters of this CTA and the CL CTAs of the cluster: quarter partials
+  // (sum, sum of squares) meet in shared memory; the cq == 0 thread of the row sends the CTA's (mean, M2) to every peer's lnp[c][rl]
+  // (st.async, completes on the peer's barrier); then every thread merges the CL partials (Chan, equal counts).
   auto ln_exchange = [&](float s, float q, int n, float eps, float& mu, float& rs) {
-    const float mu_c = s / (float)n, m2_c = fmaxf(q - s * mu_c, 0.f);
+    red[cq * RM + rl] = make_float2(s, q);
     if (tid == 64) mbar_expect_tx(stat_bar, (uint32_t)CL * RM * 8);
-    const uint32_t my = smem_u32(&lnp[c * RM + rl]), bar = smem_u32(stat_bar);
-    for (int p = 0; p < CL; ++p) st_async_f2(mapa(my, (uint32_t)p), mu_c, m2_c, mapa(bar, (uint32_t)p));
+    epi_bar();
+    if (cq == 0) {
+      float ss = 0.f, qq = 0.f;
+#pragma unroll
+      for (int x = 0; x < 4; ++x) { const float2 p = red[x * RM + rl]; ss += p.x; qq += p.y; }
+      const float mu_c = ss / (float)n, m2_c = fmaxf(qq - ss * mu_c, 0.f);
+      const uint32_t my = smem_u32(&lnp[c * RM + rl]), bar = smem_u32(stat_bar);
+      for (int p = 0; p < CL; ++p) st_async_f2(mapa(my, (uint32_t)p), mu_c, m2_c, mapa(bar, (uint32_t)p));
+    }
     mbar_wait(stat_bar, stat_par);
     stat_par ^= 1u;
     float sm = 0.f;
@@ -242,85 +253,52 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     for (int p = 0; p < CL; ++p) { const float2 pc = lnp[p * RM + rl]; const float d = pc.x - mu; m2 += pc.y + (float)n * d * d; }
     rs = rsqrtf(m2 / (float)(n * CL) + eps);
   };
-  // dense layer + LayerNorm + SiLU: acc (+ bias) (+ gathered action rows) -> [pre] -> act (fp32) / act16 (bf16) at columns col0 + [0, n)
+  // dense layer + LayerNorm + SiLU on the thread's n / 4 columns, streamed from TMEM twice in 8-column chunks (statistics, then
+  // normalisation: keeping the columns in registers across the exchange spilled at 576 threads per CTA):
+  // acc (+ bias) (+ gathered action rows) -> [pre] -> act (fp32) / act16 (bf16) at columns col0 + [0, n)
+  auto chunk = [&](int tcol, int gcol, const float* bias, const float* add_tab, int add_ld, const int* add_idx, float* x) {
+    ld8(tcol, x);
+    if (bias) {
+      const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + gcol)), b1 = __ldg(reinterpret_cast<const float4*>(bias + gcol + 4));
+      x[0] += b0.x; x[1] += b0.y; x[2] += b0.z; x[3] += b0.w; x[4] += b1.x; x[5] += b1.y; x[6] += b1.z; x[7] += b1.w;
+    }
+    if (add_tab) {
+      for (int h = 0; h < a.nh; ++h) {
+        const float* tr = add_tab + (size_t)(a.head_off[h] + add_idx[h]) * add_ld + gcol;
+        const float4 t0 = __ldg(reinterpret_cast<const float4*>(tr)), t1 = __ldg(reinterpret_cast<const float4*>(tr + 4));
+        x[0] += t0.x; x[1] += t0.y; x[2] += t0.z; x[3] += t0.w; x[4] += t1.x; x[5] += t1.y; x[6] += t1.z; x[7] += t1.w;
+      }
+    }
+  };
   auto ln_silu_epilogue = [&](int n, const float* bias, const float* gamma, const float* beta, float eps, const float* add_tab, int add_ld,
                               const int* add_idx, float* pre, float* act, __nv_bfloat16* act16, int ld_out, size_t grow, int col0, float* gmean,
                               float* grstd) {
+    const int nq = n >> 2, cb = cq * nq;                 // this thread's columns [cb, cb + nq) of the CTA's n
     float s = 0.f, q = 0.f;
-    float v[16];
 #pragma unroll 1
-    for (int c0 = 0; c0 < n; c0 += 16) {
-      tmem_ld16(t_lane + (uint32_t)c0, v);
+    for (int c0 = 0; c0 < nq; c0 += 8) {
+      float x[8];
+      chunk(cb + c0, col0 + cb + c0, bias, add_tab, add_ld, add_idx, x);
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        float x = v[j] + (bias ? __ldg(bias + col0 + c0 + j) : 0.f);
-        if (add_tab) for (int h = 0; h < a.nh; ++h) x += __ldg(add_tab + (size_t)(a.head_off[h] + add_idx[h]) * add_ld + col0 + c0 + j);
-        if (c0 + j < n) { s += x; q = fmaf(x, x, q); }
-        v[j] = x;
-      }
-      if (pre) store16_f32(pre + grow * ld_out + col0 + c0, v);
+      for (int j = 0; j < 8; ++j) { s += x[j]; q = fmaf(x[j], x[j], q); }
+      if (pre) st8_f32(pre + grow * ld_out + col0 + cb + c0, x);
     }
     float mu, rs;
     ln_exchange(s, q, n, eps, mu, rs);
-    if (gmean && c == 0) { gmean[grow] = mu; grstd[grow] = rs; }
+    if (gmean && c == 0 && cq == 0) { gmean[grow] = mu; grstd[grow] = rs; }
 #pragma unroll 1
-    for (int c0 = 0; c0 < n; c0 += 16) {
-      tmem_ld16(t_lane + (uint32_t)c0, v);
+    for (int c0 = 0; c0 < nq; c0 += 8) {
+      float x[8];
+      const int gcol = col0 + cb + c0;
+      chunk(cb + c0, gcol, bias, add_tab, add_ld, add_idx, x);
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + gcol)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + gcol + 4));
+      const float4 e0 = __ldg(reinterpret_cast<const float4*>(beta + gcol)), e1 = __ldg(reinterpret_cast<const float4*>(beta + gcol + 4));
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w}, bb[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        float x = v[j] + (bias ? __ldg(bias + col0 + c0 + j) : 0.f);
-        if (add_tab) for (int h = 0; h < a.nh; ++h) x += __ldg(add_tab + (size_t)(a.head_off[h] + add_idx[h]) * add_ld + col0 + c0 + j);
-        x = (x - mu) * rs * __ldg(gamma + col0 + c0 + j) + __ldg(beta + col0 + c0 + j);
-        v[j] = x * fsigmoid(x);
-      }
-      if (act) store16_f32(act + grow * ld_out + col0 + c0, v);
-      store16_bf16(act16 + grow * ld_out + col0 + c0, v);
+      for (int j = 0; j < 8; ++j) { const float t = (x[j] - mu) * rs * gg[j] + bb[j]; x[j] = t * fsigmoid(t); }
+      if (act) st8_f32(act + grow * ld_out + gcol, x);
+      st8_bf16(act16 + grow * ld_out + gcol, x);
     }
-  };
-  // unimix + inverse-CDF draw of one categorical whose Kn raw logits sit in TMEM columns [tc0, tc0 + Kn) (+ bias): the sampling
-  // probabilities are the unimix probabilities themselves, renormalised (bf16-mode contract, see dv3_unimix_sample)
-  auto sample_cat = [&](int tc0, int Kn, const float* bias, float u, int forced, float* raw_out) -> int {
-    float v[16];
-    float mx = -INFINITY;
-    for (int c0 = 0; c0 < Kn; c0 += 16) {
-      tmem_ld16(t_lane + (uint32_t)(tc0 + c0), v);
-#pragma unroll
-      for (int j = 0; j < 16; ++j)
-        if (c0 + j < Kn) { const float x = v[j] + __ldg(bias + c0 + j); mx = fmaxf(mx, x); if (raw_out) raw_out[c0 + j] = x; }
-    }
-    if (forced >= 0) return forced;
-    float se = 0.f;
-    for (int c0 = 0; c0 < Kn; c0 += 16) {
-      tmem_ld16(t_lane + (uint32_t)(tc0 + c0), v);
-#pragma unroll
-      for (int j = 0; j < 16; ++j)
-        if (c0 + j < Kn) se += __expf(v[j] + __ldg(bias + c0 + j) - mx);
-    }
-    const float mixk = a.unimix / (float)Kn;
-    float tot = 0.f;
-    for (int c0 = 0; c0 < Kn; c0 += 16) {
-      tmem_ld16(t_lane + (uint32_t)(tc0 + c0), v);
-#pragma unroll
-      for (int j = 0; j < 16; ++j)
-        if (c0 + j < Kn) {
-          const float p = __fdividef(__expf(v[j] + __ldg(bias + c0 + j) - mx), se);
-          tot += (a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p;
-        }
-    }
-    const float thr = u * tot;      // idx = #{k : cumsum_k(p) / tot <= u}
-    float cs = 0.f;
-    int idx = 0;
-    for (int c0 = 0; c0 < Kn; c0 += 16) {
-      tmem_ld16(t_lane + (uint32_t)(tc0 + c0), v);
-#pragma unroll
-      for (int j = 0; j < 16; ++j)
-        if (c0 + j < Kn) {
-          const float p = __fdividef(__expf(v[j] + __ldg(bias + c0 + j) - mx), se);
-          cs += (a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p;
-          idx += (cs <= thr) ? 1 : 0;
-        }
-    }
-    return min(idx, Kn - 1);
   };
   auto wait_acc = [&]() {
     RDBG();
@@ -351,7 +329,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       if (l == 0) { st.a0 = &k.m_traj; st.a0_col = 0; st.a0_row = arow; st.K0 = lat; }
       else { st.a0 = &k.m_act[l - 1]; st.a0_col = 0; st.a0_row = arow; st.K0 = Ua; }
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wa[l]; st.nb = 1; st.b_row[0] = au0; st.b_rows = aper; st.n_pad = (aper + 15) & ~15;
+      st.b = &k.m_wa[l]; st.nb = 1; st.b_row[0] = au0; st.b_rows = aper; st.n_pad = aper;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
@@ -361,7 +339,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       }
       end_stage();
     }
-    {   // head(s): all action logits of a row live in CTA 0 of the cluster
+    {   // head: all action logits of a row live in CTA 0 of the cluster; the four column quarters are 32 logits wide (the last one shorter)
       Stage st;
       st.a0 = &k.m_act[L - 1]; st.a0_col = 0; st.a0_row = arow; st.K0 = Ua;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
@@ -371,15 +349,81 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
         else if (warp == 1) issue(st);
         else {
           wait_acc();
-          int col = 0;
-          for (int h = 0; h < a.nh; ++h) {
-            const int dim = a.head_dim[h];
-            const float u = (i == 0) ? a.u_act0[(size_t)(row_blk + rl) * a.nh + h] : a.u_act[((size_t)(i - 1) * N + row_blk + rl) * a.nh + h];
-            const int forced = a.f_act ? a.f_act[grow * a.nh + h] : -1;
-            const int idx = sample_cat(col, dim, a.bh + col, u, forced, a.aout + grow * A + col);
-            a.act_idx[grow * a.nh + h] = idx;
-            if (a.acts) for (int j = 0; j < dim; ++j) a.acts[grow * A + col + j] = (j == idx) ? 1.f : 0.f;
-            col += dim;
+          // this thread: logits [32 cq, 32 cq + 32) of the row, streamed from TMEM in 8-column chunks for each of the four passes
+          // (row maximum, softmax denominator, total unimix mass, the draw); the four quarters meet in shared memory each time
+          const int dim = a.head_dim[0], cb = 32 * cq, npad = st.n_pad;
+          auto logits8 = [&](int c0, float* x) {
+            if (cb + c0 < npad) {
+              ld8(cb + c0, x);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) { const int col = cb + c0 + j; x[j] = (col < dim) ? x[j] + __ldg(a.bh + col) : -INFINITY; }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) x[j] = -INFINITY;
+            }
+          };
+          float mx = -INFINITY;
+#pragma unroll 1
+          for (int c0 = 0; c0 < 32; c0 += 8) {
+            float x[8];
+            logits8(c0, x);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { mx = fmaxf(mx, x[j]); if (cb + c0 + j < dim) a.aout[grow * A + cb + c0 + j] = x[j]; }
+          }
+          red[cq * RM + rl].x = mx;
+          epi_bar();
+          mx = fmaxf(fmaxf(red[rl].x, red[RM + rl].x), fmaxf(red[2 * RM + rl].x, red[3 * RM + rl].x));
+          float se = 0.f;
+#pragma unroll 1
+          for (int c0 = 0; c0 < 32; c0 += 8) {
+            float x[8];
+            logits8(c0, x);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) se += __expf(x[j] - mx);
+          }
+          red[cq * RM + rl].y = se;
+          epi_bar();
+          se = red[rl].y + red[RM + rl].y + red[2 * RM + rl].y + red[3 * RM + rl].y;
+          const float mixk = a.unimix / (float)dim, inv = __fdividef(1.f, se);
+          auto pm8 = [&](int c0, float* x) {     // unimix probabilities of 8 logits
+            logits8(c0, x);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float p = __expf(x[j] - mx) * inv;
+              x[j] = (cb + c0 + j < dim) ? ((a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p) : 0.f;
+            }
+          };
+          float mass = 0.f;
+#pragma unroll 1
+          for (int c0 = 0; c0 < 32; c0 += 8) {
+            float x[8];
+            pm8(c0, x);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) mass += x[j];
+          }
+          epi_bar();                                   // (everyone has read red[].x / .y)
+          red[cq * RM + rl].x = mass;
+          epi_bar();
+          float before = 0.f, tot = 0.f;
+#pragma unroll
+          for (int qq = 0; qq < 4; ++qq) { const float mq = red[qq * RM + rl].x; tot += mq; if (qq < cq) before += mq; }
+          const float u = (i == 0) ? a.u_act0[(size_t)(row_blk + rl)] : a.u_act[(size_t)(i - 1) * N + row_blk + rl];
+          const float thr = u * tot;                   // idx = #{k : cumsum_k(p) / tot <= u}
+          float cs = before;
+          int cnt = 0;
+#pragma unroll 1
+          for (int c0 = 0; c0 < 32; c0 += 8) {
+            float x[8];
+            pm8(c0, x);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { cs += x[j]; cnt += (cb + c0 + j < dim && cs <= thr) ? 1 : 0; }
+          }
+          red[cq * RM + rl].y = __int_as_float(cnt);
+          epi_bar();
+          if (cq == 0) {
+            int idx = __float_as_int(red[rl].y) + __float_as_int(red[RM + rl].y) + __float_as_int(red[2 * RM + rl].y) + __float_as_int(red[3 * RM + rl].y);
+            idx = min(idx, dim - 1);
+            a.act_idx[grow] = a.f_act ? a.f_act[grow] : idx;
           }
         }
       }
@@ -399,54 +443,64 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       Stage st;
       st.a0 = &k.m_traj; st.a0_col = 0; st.a0_row = prow; st.K0 = S;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wz; st.nb = 1; st.b_row[0] = u0; st.b_rows = uper; st.n_pad = (uper + 15) & ~15;
+      st.b = &k.m_wz; st.nb = 1; st.b_row[0] = u0; st.b_rows = uper; st.n_pad = uper;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
-        int aidx[4];
-        for (int h = 0; h < a.nh; ++h) aidx[h] = a.act_idx[gp * a.nh + h];
+        int aidx[1];
+        aidx[0] = a.act_idx[gp];
         ln_silu_epilogue(uper, nullptr, a.g_mlp, a.b_mlp, 1e-3f, a.W_mlpaT, a.ld_mlpaT, aidx, nullptr, nullptr, feat16, U, (size_t)lrow, u0, nullptr, nullptr);
       }
       end_stage();
     }
-    // ---- S2: GRU: gates = LN(Wgru . [h_{i-1}, feat]) -> h_i   (own units d0.. of the three gates)
+    // ---- S2: GRU: gates = LN(Wgru . [h_{i-1}, feat]) -> h_i   (own units d0.. of the three gates; this thread: dper / 4 of them)
     {
       Stage st;
       st.a0 = &k.m_traj; st.a0_col = S; st.a0_row = prow; st.K0 = D;
       st.a1 = &k.m_feat; st.a1_col = 0; st.a1_row = row_blk; st.K1 = U;
-      st.b = &k.m_wgru; st.nb = 3; st.b_row[0] = d0; st.b_row[1] = D + d0; st.b_row[2] = 2 * D + d0; st.b_rows = dper; st.n_pad = (3 * dper + 15) & ~15;
+      st.b = &k.m_wgru; st.nb = 3; st.b_row[0] = d0; st.b_row[1] = D + d0; st.b_row[2] = 2 * D + d0; st.b_rows = dper; st.n_pad = 3 * dper;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
-        float s = 0.f, q = 0.f, v[16];
+        const int dq = dper >> 2, db = cq * dq;            // this thread: units [db, db + dq) of the CTA's dper, 8 at a time
+        float s = 0.f, q = 0.f;
 #pragma unroll 1
-        for (int c0 = 0; c0 < 3 * dper; c0 += 16) {
-          tmem_ld16(t_lane + (uint32_t)c0, v);
+        for (int c0 = 0; c0 < dq; c0 += 8) {
+          float vr[8], vc[8], vu[8];
+          ld8(db + c0, vr);
+          ld8(dper + db + c0, vc);
+          ld8(2 * dper + db + c0, vu);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) { s += v[j]; q = fmaf(v[j], v[j], q); }
+          for (int j = 0; j < 8; ++j) {
+            s += vr[j] + vc[j] + vu[j];
+            q = fmaf(vr[j], vr[j], fmaf(vc[j], vc[j], fmaf(vu[j], vu[j], q)));
+          }
         }
         float mu, rs;
         ln_exchange(s, q, 3 * dper, 1e-5f, mu, rs);
-        float vr[16], vc[16], vu[16], hn[16];
 #pragma unroll 1
-        for (int c0 = 0; c0 < dper; c0 += 16) {
-          tmem_ld16(t_lane + (uint32_t)c0, vr);
-          tmem_ld16(t_lane + (uint32_t)(dper + c0), vc);
-          tmem_ld16(t_lane + (uint32_t)(2 * dper + c0), vu);
-          const float* hp = a.traj + gp * lat + S + d0 + c0;
+        for (int c0 = 0; c0 < dq; c0 += 8) {
+          float vr[8], vc[8], vu[8];
+          ld8(db + c0, vr);
+          ld8(dper + db + c0, vc);
+          ld8(2 * dper + db + c0, vu);
+          const int d = d0 + db + c0;
+          const float* hp = a.traj + gp * lat + S + d;
+          const float4 h0_ = *reinterpret_cast<const float4*>(hp), h1_ = *reinterpret_cast<const float4*>(hp + 4);
+          const float hv[8] = {h0_.x, h0_.y, h0_.z, h0_.w, h1_.x, h1_.y, h1_.z, h1_.w};
+          float hn[8];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int d = d0 + c0 + j;
-            const float r = fsigmoid((vr[j] - mu) * rs * __ldg(a.g_gru + d) + __ldg(a.b_gru + d));
-            const float cp = (vc[j] - mu) * rs * __ldg(a.g_gru + D + d) + __ldg(a.b_gru + D + d);
+          for (int j = 0; j < 8; ++j) {
+            const float r = fsigmoid((vr[j] - mu) * rs * __ldg(a.g_gru + d + j) + __ldg(a.b_gru + d + j));
+            const float cp = (vc[j] - mu) * rs * __ldg(a.g_gru + D + d + j) + __ldg(a.b_gru + D + d + j);
             const float cd = ftanh(r * cp);
-            const float u = fsigmoid((vu[j] - mu) * rs * __ldg(a.g_gru + 2 * D + d) + __ldg(a.b_gru + 2 * D + d) - 1.f);
-            hn[j] = u * cd + (1.f - u) * hp[j];
+            const float u = fsigmoid((vu[j] - mu) * rs * __ldg(a.g_gru + 2 * D + d + j) + __ldg(a.b_gru + 2 * D + d + j) - 1.f);
+            hn[j] = u * cd + (1.f - u) * hv[j];
           }
-          store16_f32(a.traj + gc * lat + S + d0 + c0, hn);
-          store16_bf16(traj16 + gc * lat + S + d0 + c0, hn);
+          st8_f32(a.traj + gc * lat + S + d, hn);
+          st8_bf16(traj16 + gc * lat + S + d, hn);
         }
       }
       end_stage();
@@ -456,7 +510,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       Stage st;
       st.a0 = &k.m_traj; st.a0_col = S; st.a0_row = crow; st.K0 = D;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wt0; st.nb = 1; st.b_row[0] = h0; st.b_rows = hper; st.n_pad = (hper + 15) & ~15;
+      st.b = &k.m_wt0; st.nb = 1; st.b_row[0] = h0; st.b_rows = hper; st.n_pad = hper;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
@@ -465,28 +519,83 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       }
       end_stage();
     }
-    // ---- S4: prior logits of the own categoricals -> unimix -> sample z_i (one-hot into the trajectory)
+    // ---- S4: prior logits of the own categoricals -> unimix -> sample z_i (one-hot into the trajectory); this thread: groups cq, cq + 4, ..
     {
       Stage st;
       st.a0 = &k.m_thid; st.a0_col = 0; st.a0_row = row_blk; st.K0 = Hh;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wt1; st.nb = 1; st.b_row[0] = s0; st.b_rows = sper; st.n_pad = (sper + 15) & ~15;
+      st.b = &k.m_wt1; st.nb = 1; st.b_row[0] = s0; st.b_rows = sper; st.n_pad = sper;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
 #pragma unroll 1
-        for (int gl = 0; gl < gper; ++gl) {
+        for (int gl = cq; gl < gper; gl += 4) {
           const int g = c * gper + gl;
           const size_t zi = ((size_t)(i - 1) * N + row_blk + rl) * G + g;
-          const int idx = sample_cat(gl * Kc, Kc, a.bt1 + s0 + gl * Kc, a.u_z[zi], a.f_z ? a.f_z[zi] : -1, nullptr);
+          auto lg8 = [&](int c0, float* x) {
+            ld8(gl * Kc + c0, x);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) x[j] += __ldg(a.bt1 + s0 + gl * Kc + c0 + j);
+          };
+          int idx;
+          if (a.f_z) {
+            idx = a.f_z[zi];
+          } else {
+            float mx = -INFINITY;
+#pragma unroll 1
+            for (int c0 = 0; c0 < Kc; c0 += 8) {
+              float x[8];
+              lg8(c0, x);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) mx = fmaxf(mx, x[j]);
+            }
+            float se = 0.f;
+#pragma unroll 1
+            for (int c0 = 0; c0 < Kc; c0 += 8) {
+              float x[8];
+              lg8(c0, x);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) se += __expf(x[j] - mx);
+            }
+            const float mixk = a.unimix / (float)Kc, inv = __fdividef(1.f, se);
+            // unimix probabilities sum to 1 up to round-off unless the clamp bites: one pass for the total, one for the draw
+            float tot = 0.f;
+#pragma unroll 1
+            for (int c0 = 0; c0 < Kc; c0 += 8) {
+              float x[8];
+              lg8(c0, x);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float p = __expf(x[j] - mx) * inv;
+                tot += (a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p;
+              }
+            }
+            const float thr = a.u_z[zi] * tot;         // idx = #{k : cumsum_k(p) / tot <= u}
+            float cs = 0.f;
+            idx = 0;
+#pragma unroll 1
+            for (int c0 = 0; c0 < Kc; c0 += 8) {
+              float x[8];
+              lg8(c0, x);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float p = __expf(x[j] - mx) * inv;
+                cs += (a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p;
+                idx += (cs <= thr) ? 1 : 0;
+              }
+            }
+            idx = min(idx, Kc - 1);
+          }
           a.z_idx[zi] = idx;
           float* zo = a.traj + gc * lat + s0 + gl * Kc;
           __nv_bfloat16* zo16 = traj16 + gc * lat + s0 + gl * Kc;
-          for (int j = 0; j < Kc; j += 4) {
-            *reinterpret_cast<float4*>(zo + j) = make_float4(j == idx ? 1.f : 0.f, j + 1 == idx ? 1.f : 0.f, j + 2 == idx ? 1.f : 0.f, j + 3 == idx ? 1.f : 0.f);
-            __nv_bfloat162 h0_ = __floats2bfloat162_rn(j == idx ? 1.f : 0.f, j + 1 == idx ? 1.f : 0.f), h1_ = __floats2bfloat162_rn(j + 2 == idx ? 1.f : 0.f, j + 3 == idx ? 1.f : 0.f);
-            *reinterpret_cast<uint2*>(zo16 + j) = make_uint2(*reinterpret_cast<uint32_t*>(&h0_), *reinterpret_cast<uint32_t*>(&h1_));
+          for (int j = 0; j < Kc; j += 8) {
+            float oh[8];
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj) oh[jj] = (j + jj == idx) ? 1.f : 0.f;
+            st8_f32(zo + j, oh);
+            st8_bf16(zo16 + j, oh);
           }
         }
       }
@@ -502,15 +611,15 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   }
 }
 
-constexpr size_t SMEM_BYTES = NSTG * (A_BYTES + B_BYTES) + MAXCL * RM * 8 + (2 * NSTG + 2) * 8 + 16 + 1024;
+constexpr size_t SMEM_BYTES = NSTG * (A_BYTES + B_BYTES) + MAXCL * RM * 8 + 4 * RM * 8 + (2 * NSTG + 2) * 8 + 16 + 1024;
 
 int pick_cluster(const Dv3RolloutArgs* a) {
   for (int CL = 8; CL <= 16; CL <<= 1) {
     if (a->U % CL || a->D % CL || a->Hh % CL || a->G % CL || a->Ua % CL) continue;
     const int uper = a->U / CL, dper = a->D / CL, hper = a->Hh / CL, sper = (a->G / CL) * a->Kc, aper = a->Ua / CL;
-    // 16-column TMEM chunks and 16-element vector stores per thread: every per-CTA slice must be a multiple of 16
-    if ((uper & 15) || (dper & 15) || (hper & 15) || (sper & 15) || (aper & 15)) continue;
-    if (3 * dper > NMAX || uper > NMAX || hper > NMAX || sper > NMAX || aper > NMAX) continue;
+    // a thread owns a quarter of the CTA's columns of a layer, in 8-column TMEM chunks kept in registers (<= 32 per layer, <= 16 per gate)
+    if ((uper & 31) || (dper & 31) || (hper & 31) || (aper & 31) || (sper & 15) || (a->Kc & 7)) continue;
+    if (uper > 128 || hper > 128 || aper > 128 || dper > 64 || sper > NMAX) continue;
     return CL;
   }
   return 0;
@@ -523,7 +632,7 @@ extern "C" int dv3_rollout_tc(const Dv3RolloutArgs* a, void* stream_) {
   if (a->N <= 0 || a->N % RM || a->H < 1 || a->L < 1 || a->L > MAXL || a->nh < 1 || a->nh > 4 || a->Kc > 32 || (a->Kc & 3)) return DV3_ERR_UNSUPPORTED;
   if (a->S != a->G * a->Kc || a->lat != a->S + a->D || (a->S % KB) || (a->D % KB) || (a->U % KB) || (a->Hh % KB) || (a->Ua % KB) || (a->lat % KB))
     return DV3_ERR_UNSUPPORTED;
-  if (a->A > NMAX || a->nh != 1) return DV3_ERR_UNSUPPORTED;          // one action head (its logits live in one CTA); several heads: per-op path
+  if (a->A > 128 || a->nh != 1) return DV3_ERR_UNSUPPORTED;           // one action head of <= 128 logits (they live in one CTA, 32 per column quarter)
   if ((a->ld_mlpaT & 3)) return DV3_ERR_UNSUPPORTED;
   const int CL = pick_cluster(a);
   if (!CL) return DV3_ERR_UNSUPPORTED;
