@@ -32,6 +32,7 @@ struct BwdK {
   Plan plan;
   const uint8_t* stream;        // packed transposed weights: [CL][step_bytes]
   int CL, nslots;
+  int nb;                       // batch rows per cluster (N of the MMA): 16, or 8 when the [nb, 3D] gradient operand would not fit
 };
 
 #define BDBG(p) do { if (a.dbg && c == 0 && blockIdx.x == 0 && et == 0 && t == a.T - 3) a.dbg[p] = clock64(); } while (0)
@@ -46,8 +47,9 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
   uint32_t crank;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
   const int c = (int)crank;
-  const int b0 = ((int)blockIdx.x / CL) * NB;
-  const int Bv = min(NB, a.B - b0);
+  const int nb = k.nb, ob = nb + 1, brow = nb * 16;          // batch tile of this launch (the namespace constants NB / OB / BROW are the 16-row case)
+  const int b0 = ((int)blockIdx.x / CL) * nb;
+  const int Bv = min(nb, a.B - b0);
   const int B = a.B, G = a.G, Kc = a.Kc, D = a.D, U = a.U, Hh = a.Hh;
   const int S = G * Kc, D3 = 3 * D, lat = a.ld_dlat;
   const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc;
@@ -66,30 +68,30 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
   // operand buffers (gradient vectors of all CL slices, bf16, MMA layout).  d post_raw / d gates_pre share one buffer and
   // d hidr_pre / d feat_pre the other: a slice of the later vector can only arrive after every CTA's contraction with the earlier
   // one has completed (its result is needed, cluster-wide, before the later vector exists).
-  uint8_t* xa = take((size_t)(max(S, D3) >> 3) * BROW);
-  uint8_t* xb = take((size_t)(max(Hh, U) >> 3) * BROW);
+  uint8_t* xa = take((size_t)(max(S, D3) >> 3) * brow);
+  uint8_t* xb = take((size_t)(max(Hh, U) >> 3) * brow);
   const int fmax = max(max(sper, hper), max(3 * dper, uper));
-  uint8_t* stage = take((size_t)(fmax >> 3) * BROW);
+  uint8_t* stage = take((size_t)(fmax >> 3) * brow);
   const int rows_max = max(max(hper, 3 * dper), max(dper + uper, sper));
-  float* outb = takef((size_t)rows_max * OB);          // accumulator [row][m]
-  float* wg = takef((size_t)rows_max * OB);            // gg = g * gamma  [row][m]
-  float* wx = takef((size_t)rows_max * OB);            // xhat            [row][m]
-  float* lnp = takef((size_t)3 * CL * NB * 2);
-  float* dzc = takef((size_t)NB * sper);               // carried dL/dz (own categoricals) [m][sl]
-  float* dhc = takef((size_t)NB * dper);               // carried dL/dh (own units) [m][dl]
-  float* dhd = takef((size_t)NB * dper);               // dh_t * (1 - u): direct path to h_{t-1}
-  float* dhp = takef((size_t)NB * dper);               // h_{t-1} part of Wgru^T . d gates_pre
-  float* f_ps = takef((size_t)NB * sper);              // cp.async landing zones (saved forward tensors of the next step to process)
-  float* f_cf = takef((size_t)NB * sper);
-  float* f_pn = takef((size_t)NB * sper);
-  float* f_dl = takef((size_t)NB * sper);
-  float* f_dz = takef((size_t)NB * sper);
-  float* f_hp = takef((size_t)NB * hper);
-  float* f_dh = takef((size_t)NB * dper);
-  float* f_hi = takef((size_t)NB * dper);
-  float* f_gp = takef((size_t)3 * NB * dper);          // [gate][m][dl]
-  float* f_fp = takef((size_t)NB * uper);
-  float* f_st = takef(6 * NB);                         // hidr mean|rstd, gru mean|rstd, feat mean|rstd
+  float* outb = takef((size_t)rows_max * ob);          // accumulator [row][m]
+  float* wg = takef((size_t)rows_max * ob);            // gg = g * gamma  [row][m]
+  float* wx = takef((size_t)rows_max * ob);            // xhat            [row][m]
+  float* lnp = takef((size_t)3 * CL * nb * 2);
+  float* dzc = takef((size_t)nb * sper);               // carried dL/dz (own categoricals) [m][sl]
+  float* dhc = takef((size_t)nb * dper);               // carried dL/dh (own units) [m][dl]
+  float* dhd = takef((size_t)nb * dper);               // dh_t * (1 - u): direct path to h_{t-1}
+  float* dhp = takef((size_t)nb * dper);               // h_{t-1} part of Wgru^T . d gates_pre
+  float* f_ps = takef((size_t)nb * sper);              // cp.async landing zones (saved forward tensors of the next step to process)
+  float* f_cf = takef((size_t)nb * sper);
+  float* f_pn = takef((size_t)nb * sper);
+  float* f_dl = takef((size_t)nb * sper);
+  float* f_dz = takef((size_t)nb * sper);
+  float* f_hp = takef((size_t)nb * hper);
+  float* f_dh = takef((size_t)nb * dper);
+  float* f_hi = takef((size_t)nb * dper);
+  float* f_gp = takef((size_t)3 * nb * dper);          // [gate][m][dl]
+  float* f_fp = takef((size_t)nb * uper);
+  float* f_st = takef(6 * nb);                         // hidr mean|rstd, gru mean|rstd, feat mean|rstd
   uint32_t* s_rmask = reinterpret_cast<uint32_t*>(take((size_t)a.T * 4));
   float* p_r = takef(2 * hper);
   float* p_gru = takef(6 * dper);
@@ -103,18 +105,18 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(sum_bar + 4);
 
   // ---- one-time set-up
-  for (int i = tid; i < ((max(S, D3) + max(Hh, U)) >> 3) * BROW / 16; i += NT) reinterpret_cast<uint4*>(xa)[i] = make_uint4(0u, 0u, 0u, 0u);   // xa | xb contiguous
+  for (int i = tid; i < ((max(S, D3) + max(Hh, U)) >> 3) * brow / 16; i += NT) reinterpret_cast<uint4*>(xa)[i] = make_uint4(0u, 0u, 0u, 0u);   // xa | xb contiguous
   for (int i = tid; i < (int)((k.nslots * pl.slot_bytes + 2048) / 16); i += NT) reinterpret_cast<uint4*>(ring_p)[i] = make_uint4(0u, 0u, 0u, 0u);
-  for (int i = tid; i < (fmax >> 3) * BROW / 16; i += NT) reinterpret_cast<uint4*>(stage)[i] = make_uint4(0u, 0u, 0u, 0u);
-  for (int i = tid; i < NB * sper; i += NT) { dzc[i] = 0.f; f_ps[i] = f_cf[i] = f_pn[i] = f_dl[i] = f_dz[i] = 0.f; }
-  for (int i = tid; i < NB * dper; i += NT) { dhc[i] = dhd[i] = dhp[i] = 0.f; f_dh[i] = f_hi[i] = 0.f; }
-  for (int i = tid; i < 3 * NB * dper; i += NT) f_gp[i] = 0.f;
-  for (int i = tid; i < NB * hper; i += NT) f_hp[i] = 0.f;
-  for (int i = tid; i < NB * uper; i += NT) f_fp[i] = 0.f;
-  for (int i = tid; i < 6 * NB; i += NT) f_st[i] = (i / NB) & 1 ? 1.f : 0.f;
+  for (int i = tid; i < (fmax >> 3) * brow / 16; i += NT) reinterpret_cast<uint4*>(stage)[i] = make_uint4(0u, 0u, 0u, 0u);
+  for (int i = tid; i < nb * sper; i += NT) { dzc[i] = 0.f; f_ps[i] = f_cf[i] = f_pn[i] = f_dl[i] = f_dz[i] = 0.f; }
+  for (int i = tid; i < nb * dper; i += NT) { dhc[i] = dhd[i] = dhp[i] = 0.f; f_dh[i] = f_hi[i] = 0.f; }
+  for (int i = tid; i < 3 * nb * dper; i += NT) f_gp[i] = 0.f;
+  for (int i = tid; i < nb * hper; i += NT) f_hp[i] = 0.f;
+  for (int i = tid; i < nb * uper; i += NT) f_fp[i] = 0.f;
+  for (int i = tid; i < 6 * nb; i += NT) f_st[i] = (i / nb) & 1 ? 1.f : 0.f;
   for (int t = tid; t < a.T; t += NT) {
     uint32_t msk = 0;
-    for (int m = 0; m < NB; ++m) if (m >= Bv || t == 0 || __ldg(a.first + (size_t)t * B + b0 + m) != 0.f) msk |= 1u << m;
+    for (int m = 0; m < nb; ++m) if (m >= Bv || t == 0 || __ldg(a.first + (size_t)t * B + b0 + m) != 0.f) msk |= 1u << m;
     s_rmask[t] = msk;
   }
   for (int i = tid; i < hper; i += NT) { p_r[i] = __ldg(a.g_r + h0 + i); p_r[hper + i] = __ldg(a.b_r + h0 + i); }
@@ -154,8 +156,8 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
     // ===================================================== MMA issuer =====================================================
     RingPos pos = {0u, 0u};
     const uint32_t xa_a = smem_u32(xa), xb_a = smem_u32(xb);
-    const uint32_t nbytes[4] = {(uint32_t)CL * (sper >> 3) * BROW, (uint32_t)CL * (hper >> 3) * BROW, (uint32_t)CL * 3 * (dper >> 3) * BROW,
-                                (uint32_t)CL * (uper >> 3) * BROW};
+    const uint32_t nbytes[4] = {(uint32_t)CL * (sper >> 3) * brow, (uint32_t)CL * (hper >> 3) * brow, (uint32_t)CL * 3 * (dper >> 3) * brow,
+                                (uint32_t)CL * (uper >> 3) * brow};
 #pragma unroll 1
     for (int it = 0; it < a.T; ++it) {
       const uint32_t par = (uint32_t)it & 1u;
@@ -164,7 +166,7 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
         if (elect_one()) mbar_expect_tx(&act_bar[si], nbytes[si]);
         __syncwarp();
         mbar_wait(&act_bar[si], par);
-        mma_seg(pl, si, (si == SEG_R1T || si == SEG_GRUT) ? xa_a : xb_a, tmem_base, rg, pos);
+        mma_seg(pl, si, (si == SEG_R1T || si == SEG_GRUT) ? xa_a : xb_a, tmem_base, rg, pos, nb);
         if (elect_one()) umma_commit(&acc_bar[si]);
         __syncwarp();
       }
@@ -172,11 +174,14 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
   } else {
     // ===================================================== epilogue =====================================================
     const int et = tid - 64, ew = et >> 5;
-    const int hl = lane >> 4, l16 = lane & 15, mrow = 2 * ew + hl;       // one half-warp per batch row (see rssm_scan_tc.cu)
+    // nb = 16: one half-warp per batch row (see rssm_scan_tc.cu); nb = 8: warps 0-3 take two rows each, warps 4-7 only keep the barriers
+    const int hl = lane >> 4, l16 = lane & 15, mrow_raw = 2 * ew + hl;
+    const bool has_row = mrow_raw < nb;
+    const int mrow = has_row ? mrow_raw : 0;        // (row-less warps skip the per-row work: they only keep the barriers and do their share of the pushes)
     const uint32_t stage_a = smem_u32(stage);
     float* lnp0 = lnp;
-    float* lnp1 = lnp + (size_t)CL * NB * 2;
-    float* lnp2 = lnp + (size_t)2 * CL * NB * 2;
+    float* lnp1 = lnp + (size_t)CL * nb * 2;
+    float* lnp2 = lnp + (size_t)2 * CL * nb * 2;
 
     // asynchronous fetch of rows m < Bv of a global [.., ld] slice (cols floats, 16 B aligned) into smem [m][cols]
     auto fetch_rows = [&](float* dst, const float* src, int ld, int cols) {
@@ -196,30 +201,30 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
     auto fetch_b2 = [&](int t) {
       const size_t r = (size_t)t * B + b0;
       fetch_rows(f_hp, a.hidr_pre + r * Hh + h0, Hh, hper);
-      if (et < Bv) { cp_async4(f_st + et, a.hidr_mean + r + et); cp_async4(f_st + NB + et, a.hidr_rstd + r + et); }
+      if (et < Bv) { cp_async4(f_st + et, a.hidr_mean + r + et); cp_async4(f_st + nb + et, a.hidr_rstd + r + et); }
     };
     auto fetch_b3 = [&](int t) {
       const size_t r = (size_t)t * B + b0;
       fetch_rows(f_dh, a.dlatent + r * lat + S + d0, lat, dper);
       fetch_rows(f_hi, a.x_gru + r * a.ld_xgru + d0, a.ld_xgru, dper);
-      for (int gate = 0; gate < 3; ++gate) fetch_rows(f_gp + gate * NB * dper, a.gates_pre + r * D3 + gate * D + d0, D3, dper);
-      if (et < Bv) { cp_async4(f_st + 2 * NB + et, a.gru_mean + r + et); cp_async4(f_st + 3 * NB + et, a.gru_rstd + r + et); }
+      for (int gate = 0; gate < 3; ++gate) fetch_rows(f_gp + gate * nb * dper, a.gates_pre + r * D3 + gate * D + d0, D3, dper);
+      if (et < Bv) { cp_async4(f_st + 2 * nb + et, a.gru_mean + r + et); cp_async4(f_st + 3 * nb + et, a.gru_rstd + r + et); }
     };
     auto fetch_b4 = [&](int t) {
       const size_t r = (size_t)t * B + b0;
       fetch_rows(f_fp, a.feat_pre + r * U + u0, U, uper);
-      if (et < Bv) { cp_async4(f_st + 4 * NB + et, a.feat_mean + r + et); cp_async4(f_st + 5 * NB + et, a.feat_rstd + r + et); }
+      if (et < Bv) { cp_async4(f_st + 4 * nb + et, a.feat_mean + r + et); cp_async4(f_st + 5 * nb + et, a.feat_rstd + r + et); }
     };
     // row sums over a vector spread over the cluster (LayerNorm backward): s1 = sum gg, s2 = sum gg * xh over this CTA's n values of
     // batch row mrow -> every peer (st.async on its barrier) -> after the wait the CL partials are added.  Returns s1 / n_total, s2 / n_total.
     auto row_sums = [&](const float* gg, const float* xh, int n, int n_total, float* lnp_x, uint64_t* bar, uint32_t parity, float& m1, float& m2) {
       float s1 = 0.f, s2 = 0.f;
-      for (int j = l16; j < n; j += 16) { const float g = gg[j * OB + mrow]; s1 += g; s2 = fmaf(g, xh[j * OB + mrow], s2); }
+      for (int j = l16; j < n; j += 16) { const float g = gg[j * ob + mrow]; s1 += g; s2 = fmaf(g, xh[j * ob + mrow], s2); }
 #pragma unroll
       for (int o = 8; o > 0; o >>= 1) { s1 += __shfl_xor_sync(0xffffffffu, s1, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
-      if (l16 < CL) st_async_f2(mapa(smem_u32(lnp_x + (c * NB + mrow) * 2), (uint32_t)l16), s1, s2, mapa(smem_u32(bar), (uint32_t)l16));
+      if (l16 < CL && has_row) st_async_f2(mapa(smem_u32(lnp_x + (c * nb + mrow) * 2), (uint32_t)l16), s1, s2, mapa(smem_u32(bar), (uint32_t)l16));
       mbar_wait(bar, parity);
-      const float2 pc = (l16 < CL) ? reinterpret_cast<const float2*>(lnp_x)[l16 * NB + mrow] : make_float2(0.f, 0.f);
+      const float2 pc = (l16 < CL) ? reinterpret_cast<const float2*>(lnp_x)[l16 * nb + mrow] : make_float2(0.f, 0.f);
       s1 = pc.x; s2 = pc.y;
 #pragma unroll
       for (int o = 8; o > 0; o >>= 1) { s1 += __shfl_xor_sync(0xffffffffu, s1, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
@@ -238,18 +243,18 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
       const uint32_t par = (uint32_t)(a.T - 1 - t) & 1u;
       const size_t row0 = (size_t)t * B + b0;
       const bool rst = (s_rmask[t] >> mrow) & 1u;
-      const bool live = mrow < Bv;
+      const bool live = has_row && mrow < Bv;
       BDBG(0);
       if (et == 0) {
-        mbar_expect_tx(&sum_bar[SM_HID], (uint32_t)CL * NB * 8);
-        mbar_expect_tx(&sum_bar[SM_GRU], (uint32_t)CL * NB * 8);
-        mbar_expect_tx(&sum_bar[SM_FEAT], (uint32_t)CL * NB * 8);
+        mbar_expect_tx(&sum_bar[SM_HID], (uint32_t)CL * nb * 8);
+        mbar_expect_tx(&sum_bar[SM_GRU], (uint32_t)CL * nb * 8);
+        mbar_expect_tx(&sum_bar[SM_FEAT], (uint32_t)CL * nb * 8);
       }
       cp_async_wait_all();
       epi_bar();                                                 // this step's saved tensors landed (other threads' cp.async)
       // ================= B1: dz_t -> d post_raw (own categoricals of batch row mrow; two classes per lane) =================
 #pragma unroll 1
-      for (int gl = 0; gl < gper; ++gl) {
+      for (int gl = 0; gl < (has_row ? gper : 0); ++gl) {     // (row-less warps only keep the barriers and the pushes)
         float o[2];
         float dz[2], pk[2], dot = 0.f;
 #pragma unroll
@@ -287,13 +292,13 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
               a.dpost_raw[(row0 + mrow) * S + s0 + sl] = ov;
               if (m_pr) m_pr[(row0 + mrow) * S + s0 + sl] = __float2bfloat16_rn(ov);
             }
-            *reinterpret_cast<bf*>(stage + b_off(mrow, sl)) = __float2bfloat16_rn(ov);
+            *reinterpret_cast<bf*>(stage + b_off(mrow, sl, brow)) = __float2bfloat16_rn(ov);
           }
         }
       }
       fence_proxy_async();
       epi_bar();
-      push_act(stage_a, (uint32_t)(sper >> 3) * BROW, smem_u32(xa), &act_bar[X_PR], c, CL, ew);
+      push_act(stage_a, (uint32_t)(sper >> 3) * brow, smem_u32(xa), &act_bar[X_PR], c, CL, ew);
       BDBG(1);
       if (t > 0) fetch_b1(t - 1);
 
@@ -301,38 +306,38 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
       mbar_wait(&acc_bar[SEG_R1T], par);
       tc_fence_after();
       BDBG(2);
-      tmem_to_outb(tmem_base, pl.seg[SEG_R1T].tmem_col, hper, pl.seg[SEG_R1T].m64, outb, nullptr, 0, ew, lane);
+      tmem_to_outb(tmem_base, pl.seg[SEG_R1T].tmem_col, hper, pl.seg[SEG_R1T].m64, outb, nullptr, 0, ew, lane, nb);
       epi_bar();
-      {
-        const float mean = f_st[mrow], rstd = f_st[NB + mrow];
+      if (has_row) {
+        const float mean = f_st[mrow], rstd = f_st[nb + mrow];
         for (int j = l16; j < hper; j += 16) {
           const float xh = (f_hp[mrow * hper + j] - mean) * rstd;
           const float ln = xh * p_r[j] + p_r[hper + j];
           const float sg = fsigmoid(ln);
-          const float g = outb[j * OB + mrow] * sg * (1.f + ln * (1.f - sg));
+          const float g = outb[j * ob + mrow] * sg * (1.f + ln * (1.f - sg));
           if (live) a.dln_r[(row0 + mrow) * Hh + h0 + j] = g;
-          wg[j * OB + mrow] = g * p_r[j];
-          wx[j * OB + mrow] = xh;
+          wg[j * ob + mrow] = g * p_r[j];
+          wx[j * ob + mrow] = xh;
         }
         __syncwarp();
         float m1, m2;
         row_sums(wg, wx, hper, Hh, lnp0, &sum_bar[SM_HID], par, m1, m2);
         BDBG(3);
         for (int j = 2 * l16; j < hper; j += 32) {
-          float o0 = rstd * (wg[j * OB + mrow] - m1 - wx[j * OB + mrow] * m2);
-          float o1 = rstd * (wg[(j + 1) * OB + mrow] - m1 - wx[(j + 1) * OB + mrow] * m2);
+          float o0 = rstd * (wg[j * ob + mrow] - m1 - wx[j * ob + mrow] * m2);
+          float o1 = rstd * (wg[(j + 1) * ob + mrow] - m1 - wx[(j + 1) * ob + mrow] * m2);
           if (!live) { o0 = 0.f; o1 = 0.f; }
-          const __nv_bfloat162 ob = __floats2bfloat162_rn(o0, o1);
+          const __nv_bfloat162 o16 = __floats2bfloat162_rn(o0, o1);
           if (live) {
             *reinterpret_cast<float2*>(a.dhidr_pre + (row0 + mrow) * Hh + h0 + j) = make_float2(o0, o1);
-            if (m_hp) *reinterpret_cast<__nv_bfloat162*>(m_hp + (row0 + mrow) * Hh + h0 + j) = ob;
+            if (m_hp) *reinterpret_cast<__nv_bfloat162*>(m_hp + (row0 + mrow) * Hh + h0 + j) = o16;
           }
-          *reinterpret_cast<__nv_bfloat162*>(stage + b_off(mrow, j)) = ob;
+          *reinterpret_cast<__nv_bfloat162*>(stage + b_off(mrow, j, brow)) = o16;
         }
       }
       fence_proxy_async();
       epi_bar();
-      push_act(stage_a, (uint32_t)(hper >> 3) * BROW, smem_u32(xb), &act_bar[X_HP], c, CL, ew);
+      push_act(stage_a, (uint32_t)(hper >> 3) * brow, smem_u32(xb), &act_bar[X_HP], c, CL, ew);
       BDBG(4);
       if (t > 0) fetch_b2(t - 1);
 
@@ -340,14 +345,14 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
       mbar_wait(&acc_bar[SEG_R0T], par);
       tc_fence_after();
       BDBG(5);
-      tmem_to_outb(tmem_base, pl.seg[SEG_R0T].tmem_col, dper, pl.seg[SEG_R0T].m64, outb, nullptr, 0, ew, lane);
+      tmem_to_outb(tmem_base, pl.seg[SEG_R0T].tmem_col, dper, pl.seg[SEG_R0T].m64, outb, nullptr, 0, ew, lane, nb);
       epi_bar();
-      {
-        const float mu = f_st[2 * NB + mrow], rs = f_st[3 * NB + mrow];
+      if (has_row) {
+        const float mu = f_st[2 * nb + mrow], rs = f_st[3 * nb + mrow];
         for (int dl = l16; dl < dper; dl += 16) {
           const int e = mrow * dper + dl;
-          const float dho = outb[dl * OB + mrow] + f_dh[e] + dhc[e];
-          const float xr = (f_gp[e] - mu) * rs, xc = (f_gp[NB * dper + e] - mu) * rs, xu = (f_gp[2 * NB * dper + e] - mu) * rs;
+          const float dho = outb[dl * ob + mrow] + f_dh[e] + dhc[e];
+          const float xr = (f_gp[e] - mu) * rs, xc = (f_gp[nb * dper + e] - mu) * rs, xu = (f_gp[2 * nb * dper + e] - mu) * rs;
           const float r = fsigmoid(xr * p_gru[dl] + p_gru[3 * dper + dl]);
           const float cp = xc * p_gru[dper + dl] + p_gru[4 * dper + dl];
           const float cc = ftanh(r * cp);
@@ -360,10 +365,10 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
             float* dl_ = a.dln_gru + (row0 + mrow) * D3 + d0 + dl;
             dl_[0] = g_r; dl_[D] = g_c; dl_[2 * D] = g_u;
           }
-          wx[dl * OB + mrow] = xr; wx[(dper + dl) * OB + mrow] = xc; wx[(2 * dper + dl) * OB + mrow] = xu;
-          wg[dl * OB + mrow] = g_r * p_gru[dl];
-          wg[(dper + dl) * OB + mrow] = g_c * p_gru[dper + dl];
-          wg[(2 * dper + dl) * OB + mrow] = g_u * p_gru[2 * dper + dl];
+          wx[dl * ob + mrow] = xr; wx[(dper + dl) * ob + mrow] = xc; wx[(2 * dper + dl) * ob + mrow] = xu;
+          wg[dl * ob + mrow] = g_r * p_gru[dl];
+          wg[(dper + dl) * ob + mrow] = g_c * p_gru[dper + dl];
+          wg[(2 * dper + dl) * ob + mrow] = g_u * p_gru[2 * dper + dl];
         }
         __syncwarp();
         float m1, m2;
@@ -372,15 +377,15 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
         for (int gate = 0; gate < 3; ++gate)
           for (int dl = 2 * l16; dl < dper; dl += 32) {
             const int j = gate * dper + dl;
-            float o0 = rs * (wg[j * OB + mrow] - m1 - wx[j * OB + mrow] * m2);
-            float o1 = rs * (wg[(j + 1) * OB + mrow] - m1 - wx[(j + 1) * OB + mrow] * m2);
+            float o0 = rs * (wg[j * ob + mrow] - m1 - wx[j * ob + mrow] * m2);
+            float o1 = rs * (wg[(j + 1) * ob + mrow] - m1 - wx[(j + 1) * ob + mrow] * m2);
             if (!live) { o0 = 0.f; o1 = 0.f; }
-            const __nv_bfloat162 ob = __floats2bfloat162_rn(o0, o1);
+            const __nv_bfloat162 o16 = __floats2bfloat162_rn(o0, o1);
             if (live) {
               *reinterpret_cast<float2*>(a.dgates_pre + (row0 + mrow) * D3 + gate * D + d0 + dl) = make_float2(o0, o1);
-              if (m_gp) *reinterpret_cast<__nv_bfloat162*>(m_gp + (row0 + mrow) * D3 + gate * D + d0 + dl) = ob;
+              if (m_gp) *reinterpret_cast<__nv_bfloat162*>(m_gp + (row0 + mrow) * D3 + gate * D + d0 + dl) = o16;
             }
-            *reinterpret_cast<__nv_bfloat162*>(stage + (size_t)gate * (dper >> 3) * BROW + b_off(mrow, dl)) = ob;
+            *reinterpret_cast<__nv_bfloat162*>(stage + (size_t)gate * (dper >> 3) * brow + b_off(mrow, dl, brow)) = o16;
           }
       }
       fence_proxy_async();
@@ -389,9 +394,9 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
 #pragma unroll 1
       for (int p = ew; p < 3 * CL; p += EW) {
         const int peer = p % CL, gate = p / CL;
-        const uint32_t bytes = (uint32_t)(dper >> 3) * BROW;
+        const uint32_t bytes = (uint32_t)(dper >> 3) * brow;
         if (elect_one())
-          bulk_s2peer(mapa(smem_u32(xa) + (uint32_t)(gate * (D >> 3)) * BROW + (uint32_t)c * bytes, (uint32_t)peer), stage_a + (uint32_t)gate * bytes, bytes,
+          bulk_s2peer(mapa(smem_u32(xa) + (uint32_t)(gate * (D >> 3)) * brow + (uint32_t)c * bytes, (uint32_t)peer), stage_a + (uint32_t)gate * bytes, bytes,
                       mapa(smem_u32(&act_bar[X_GP]), (uint32_t)peer));
         __syncwarp();
       }
@@ -402,39 +407,39 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
       mbar_wait(&acc_bar[SEG_GRUT], par);
       tc_fence_after();
       BDBG(8);
-      tmem_to_outb(tmem_base, pl.seg[SEG_GRUT].tmem_col, dper + uper, pl.seg[SEG_GRUT].m64, outb, nullptr, 0, ew, lane);
+      tmem_to_outb(tmem_base, pl.seg[SEG_GRUT].tmem_col, dper + uper, pl.seg[SEG_GRUT].m64, outb, nullptr, 0, ew, lane, nb);
       epi_bar();
-      {
-        for (int dl = l16; dl < dper; dl += 16) dhp[mrow * dper + dl] = outb[dl * OB + mrow];
-        const float mean = f_st[4 * NB + mrow], rstd = f_st[5 * NB + mrow];
+      if (has_row) {
+        for (int dl = l16; dl < dper; dl += 16) dhp[mrow * dper + dl] = outb[dl * ob + mrow];
+        const float mean = f_st[4 * nb + mrow], rstd = f_st[5 * nb + mrow];
         for (int j = l16; j < uper; j += 16) {
           const float xh = (f_fp[mrow * uper + j] - mean) * rstd;
           const float ln = xh * p_mlp[j] + p_mlp[uper + j];
           const float sg = fsigmoid(ln);
-          const float g = outb[(dper + j) * OB + mrow] * sg * (1.f + ln * (1.f - sg));
+          const float g = outb[(dper + j) * ob + mrow] * sg * (1.f + ln * (1.f - sg));
           if (live) a.dln_feat[(row0 + mrow) * U + u0 + j] = g;
-          wg[j * OB + mrow] = g * p_mlp[j];
-          wx[j * OB + mrow] = xh;
+          wg[j * ob + mrow] = g * p_mlp[j];
+          wx[j * ob + mrow] = xh;
         }
         __syncwarp();
         float m1, m2;
         row_sums(wg, wx, uper, U, lnp2, &sum_bar[SM_FEAT], par, m1, m2);
         BDBG(9);
         for (int j = 2 * l16; j < uper; j += 32) {
-          float o0 = rstd * (wg[j * OB + mrow] - m1 - wx[j * OB + mrow] * m2);
-          float o1 = rstd * (wg[(j + 1) * OB + mrow] - m1 - wx[(j + 1) * OB + mrow] * m2);
+          float o0 = rstd * (wg[j * ob + mrow] - m1 - wx[j * ob + mrow] * m2);
+          float o1 = rstd * (wg[(j + 1) * ob + mrow] - m1 - wx[(j + 1) * ob + mrow] * m2);
           if (!live) { o0 = 0.f; o1 = 0.f; }
-          const __nv_bfloat162 ob = __floats2bfloat162_rn(o0, o1);
+          const __nv_bfloat162 o16 = __floats2bfloat162_rn(o0, o1);
           if (live) {
             *reinterpret_cast<float2*>(a.dfeat_pre + (row0 + mrow) * U + u0 + j) = make_float2(o0, o1);
-            if (m_fp) *reinterpret_cast<__nv_bfloat162*>(m_fp + (row0 + mrow) * U + u0 + j) = ob;
+            if (m_fp) *reinterpret_cast<__nv_bfloat162*>(m_fp + (row0 + mrow) * U + u0 + j) = o16;
           }
-          *reinterpret_cast<__nv_bfloat162*>(stage + b_off(mrow, j)) = ob;
+          *reinterpret_cast<__nv_bfloat162*>(stage + b_off(mrow, j, brow)) = o16;
         }
       }
       fence_proxy_async();
       epi_bar();
-      push_act(stage_a, (uint32_t)(uper >> 3) * BROW, smem_u32(xb), &act_bar[X_FP], c, CL, ew);
+      push_act(stage_a, (uint32_t)(uper >> 3) * brow, smem_u32(xb), &act_bar[X_FP], c, CL, ew);
       BDBG(10);
       if (t > 0) fetch_b4(t - 1);
 
@@ -442,10 +447,12 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
       mbar_wait(&acc_bar[SEG_MLPT], par);
       tc_fence_after();
       BDBG(11);
-      tmem_to_outb(tmem_base, pl.seg[SEG_MLPT].tmem_col, sper, pl.seg[SEG_MLPT].m64, outb, nullptr, 0, ew, lane);
+      tmem_to_outb(tmem_base, pl.seg[SEG_MLPT].tmem_col, sper, pl.seg[SEG_MLPT].m64, outb, nullptr, 0, ew, lane, nb);
       epi_bar();
-      for (int sl = l16; sl < sper; sl += 16) dzc[mrow * sper + sl] = rst ? 0.f : outb[sl * OB + mrow];
-      for (int dl = l16; dl < dper; dl += 16) { const int e = mrow * dper + dl; dhc[e] = rst ? 0.f : (dhp[e] + dhd[e]); }
+      if (has_row) {
+        for (int sl = l16; sl < sper; sl += 16) dzc[mrow * sper + sl] = rst ? 0.f : outb[sl * ob + mrow];
+        for (int dl = l16; dl < dper; dl += 16) { const int e = mrow * dper + dl; dhc[e] = rst ? 0.f : (dhp[e] + dhd[e]); }
+      }
       BDBG(12);
     }
     tc_fence_before();
@@ -461,30 +468,33 @@ __global__ void __launch_bounds__(NT, 1) rssm_observe_bwd_tc_kernel(const __grid
 }
 
 // ---- host ------------------------------------------------------------------------------------------------------------------------
-bool build_plan_bwd(int D, int U, int Hh, int G, int Kc, int CL, int slot_max, Plan* pl) {
+bool build_plan_bwd(int D, int U, int Hh, int G, int Kc, int CL, int slot_max, int nb, Plan* pl) {
   if (CL < 1 || D % CL || U % CL || Hh % CL || G % CL) return false;
   const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc, S = G * Kc;
   if ((uper & 7) || (dper & 7) || (hper & 7) || (sper & 7) || Kc > 32 || (D & 15) || (U & 15) || (Hh & 15) || (S & 15)) return false;
-  if (hper > 128 || sper > 128 || dper > 128 || dper + uper > 128 * 4) return false;
+  if (hper > 128 || sper > 128 || dper > 128 || dper + uper > 128 * 3) return false;
   memset(pl, 0, sizeof(Plan));
   uint32_t off16 = 0;
-  const int gt = (dper + uper + 127) / 128;
+  const int tr = nb >= 16 ? 128 : 64;                         // N = 8 is only legal with M = 64 tiles
+  const int gt = (dper + uper + tr - 1) / tr;
   RowBlk hb[1] = {{0, hper}};
   RowBlk db[1] = {{0, dper}};
   RowBlk gb[2] = {{0, dper}, {D, uper}};
   RowBlk sb[1] = {{0, sper}};
-  if (plan_add_seg(*pl, slot_max, hper, S, 0, 1, 0, 1, hb, 0, off16) != SEG_R1T) return false;
-  if (plan_add_seg(*pl, slot_max, dper, Hh, NB, 1, 0, 1, db, 0, off16) != SEG_R0T) return false;
-  if (plan_add_seg(*pl, slot_max, dper + uper, 3 * D, 2 * NB, 1, 0, 2, gb, 0, off16) != SEG_GRUT) return false;
-  if (plan_add_seg(*pl, slot_max, sper, U, (2 + gt) * NB, 1, 0, 1, sb, 0, off16) != SEG_MLPT) return false;
-  if ((3 + gt) * NB > 128) return false;
+  const int t1 = (hper + tr - 1) / tr, t2 = (dper + tr - 1) / tr, t4 = (sper + tr - 1) / tr;
+  if (plan_add_seg(*pl, slot_max, hper, S, 0, 1, 0, 1, hb, 0, off16, tr) != SEG_R1T) return false;
+  if (plan_add_seg(*pl, slot_max, dper, Hh, t1 * NB, 1, 0, 1, db, 0, off16, tr) != SEG_R0T) return false;
+  if (plan_add_seg(*pl, slot_max, dper + uper, 3 * D, (t1 + t2) * NB, 1, 0, 2, gb, 0, off16, tr) != SEG_GRUT) return false;
+  if (plan_add_seg(*pl, slot_max, sper, U, (t1 + t2 + gt) * NB, 1, 0, 1, sb, 0, off16, tr) != SEG_MLPT) return false;
+  if ((t1 + t2 + gt + t4) * NB > 128) return false;
   pl->step_bytes = off16 * 16;
   return true;
 }
 
 constexpr int T_MAX_B = 1024;
 
-size_t fixed_smem_bwd(int D, int U, int Hh, int G, int Kc, int CL, int T) {
+size_t fixed_smem_bwd(int D, int U, int Hh, int G, int Kc, int CL, int T, int nb) {
+  const int NB = nb, OB = nb + 1, BROW = nb * 16;      // shadow the 16-row namespace constants
   const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc, S = G * Kc;
   auto r = [](size_t b) { return (b + 127) & ~(size_t)127; };
   auto mx = [](int x, int y) { return x > y ? x : y; };
@@ -495,18 +505,20 @@ size_t fixed_smem_bwd(int D, int U, int Hh, int G, int Kc, int CL, int T) {
          2048 + 128 + 128;
 }
 
-struct ChoiceB { int CL, nslots; size_t smem; };
+struct ChoiceB { int CL, nslots, nb; size_t smem; };
+// Preference: 16 batch rows per cluster over 8 (half the clusters, same per-cluster time); 16 CTAs over 8; a ring of >= 4 slots of >= 8 KB.
 bool select_plan_bwd(int D, int U, int Hh, int G, int Kc, int max_smem, Plan* pl, ChoiceB* ch) {
+  for (int nb = 16; nb >= 8; nb >>= 1)
   for (int CL = 16; CL >= 8; CL >>= 1) {
-    for (int want = 4; want >= 2; --want) {
-      for (int slot_max = 32768; slot_max >= 4096; slot_max >>= 1) {
-        if (!build_plan_bwd(D, U, Hh, G, Kc, CL, slot_max, pl)) continue;
-        const size_t fixed = fixed_smem_bwd(D, U, Hh, G, Kc, CL, T_MAX_B);
+    for (int want = 4; want >= 3; --want) {
+      for (int slot_max = 32768; slot_max >= 8192; slot_max >>= 1) {
+        if (!build_plan_bwd(D, U, Hh, G, Kc, CL, slot_max, nb, pl)) continue;
+        const size_t fixed = fixed_smem_bwd(D, U, Hh, G, Kc, CL, T_MAX_B, nb);
         const long long room = (long long)max_smem - (long long)fixed - 512;
         int nslots = (int)(room / (long long)pl->slot_bytes);
         if (nslots < want) continue;
         if (nslots > 12) nslots = 12;
-        ch->CL = CL; ch->nslots = nslots;
+        ch->CL = CL; ch->nslots = nslots; ch->nb = nb;
         ch->smem = fixed + (size_t)nslots * pl->slot_bytes + (((size_t)(2 * nslots + 16) * 8 + 127) & ~(size_t)127);
         return true;
       }
@@ -533,7 +545,7 @@ __global__ void __launch_bounds__(256) scan_tc_pack_bwd_kernel(const __grid_cons
   uint4* dst = reinterpret_cast<uint4*>(p.dst + (size_t)cta * p.plan.step_bytes) + ch.off16;
   for (int u = threadIdx.x; u < nunits; u += blockDim.x) {
     const int k8 = u / rp, r = u - k8 * rp;
-    const int j = ch.tile * 128 + r;
+    const int j = ch.tile * sg.tile_rows + r;
     uint4 out = make_uint4(0u, 0u, 0u, 0u);
     if (j < sg.rows) {
       int start = 0, grow = -1;
@@ -604,9 +616,10 @@ extern "C" int dv3_rssm_observe_bwd_tc(const Dv3ScanBwdArgs* h, const void* stre
     k->stream = reinterpret_cast<const uint8_t*>(stream_pk);
     k->CL = ch.CL;
     k->nslots = ch.nslots;
-    const int nclusters = (h->B + NB - 1) / NB;
+    k->nb = ch.nb;
+    const int nclusters = (h->B + ch.nb - 1) / ch.nb;
     if (getenv("DV3_SCAN_DEBUG"))
-      fprintf(stderr, "[dv3 tc reverse scan] CL=%d clusters=%d slots=%d x %u B, step stream %u B/CTA, %d chunks, smem %zu KB (max %d KB)\n", ch.CL, nclusters,
+      fprintf(stderr, "[dv3 tc reverse scan] rows/cluster=%d CL=%d clusters=%d slots=%d x %u B, step stream %u B/CTA, %d chunks, smem %zu KB (max %d KB)\n", ch.nb, ch.CL, nclusters,
               ch.nslots, k->plan.slot_bytes, k->plan.step_bytes, k->plan.nchunks, ch.smem / 1024, max_smem / 1024);
     auto kern = rssm_observe_bwd_tc_kernel;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ch.smem);

@@ -659,7 +659,7 @@ __global__ void __launch_bounds__(256) scan_tc_pack_kernel(const __grid_constant
   uint4* dst = reinterpret_cast<uint4*>(p.dst + (size_t)cta * p.plan.step_bytes) + ch.off16;
   for (int u = threadIdx.x; u < nunits; u += blockDim.x) {
     const int k8 = u / rp, r = u - k8 * rp;
-    const int j = ch.tile * 128 + r;                         // local row of the segment
+    const int j = ch.tile * sg.tile_rows + r;                         // local row of the segment
     uint4 out = make_uint4(0u, 0u, 0u, 0u);
     if (j < sg.rows) {
       int start = 0, grow = -1;

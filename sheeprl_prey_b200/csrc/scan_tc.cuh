@@ -45,7 +45,8 @@ struct Chunk {
 };
 struct RowBlk { int base, size; };     // local rows [start, start + size) -> weight rows base + cta * size + (j - start)
 struct Seg {
-  int rows, ntiles, K, chunk_begin, chunk_end, tmem_col, fresh, m64;   // m64: one tile of <= 64 rows, issued as M = 64 MMAs
+  int rows, ntiles, K, chunk_begin, chunk_end, tmem_col, fresh, m64;   // m64: tiles of <= 64 rows, issued as M = 64 MMAs
+  int tile_rows;                       // 128, or 64 (an 8-row batch tile needs M = 64: M = 128 requires N % 16 == 0)
   int nblk; RowBlk blk[3]; int col0;   // packing: which rows / columns of the source matrix
 };
 struct Plan {
@@ -144,8 +145,8 @@ __device__ __forceinline__ uint64_t desc_ns(uint32_t addr, uint32_t lbo_bytes) {
   return d;
 }
 // instruction descriptor: fp32 accumulate, bf16 x bf16, both K-major, N = NB, M = 128 or 64
-__device__ __forceinline__ uint32_t idesc_n16(int M) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(NB >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+__device__ __forceinline__ uint32_t idesc_n16(int M, int nb = NB) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(nb >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 __device__ __forceinline__ void umma_n16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
   asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_d), "l"(adesc),
@@ -190,19 +191,21 @@ __device__ __forceinline__ void produce_seg(const Plan& pl, int si, const uint8_
   }
 }
 // MMA warp: all chunks of one segment against the activation operand at shared address `bbuf`
-__device__ __forceinline__ void mma_seg(const Plan& pl, int si, uint32_t bbuf, uint32_t tmem_base, const Ring& rg, RingPos& pos) {
+// nb: batch rows per cluster (N of the MMA): 16, or 8 for shapes whose operand buffers do not fit otherwise (reverse scan of large D)
+__device__ __forceinline__ void mma_seg(const Plan& pl, int si, uint32_t bbuf, uint32_t tmem_base, const Ring& rg, RingPos& pos, int nb = NB) {
   const int cb = pl.seg[si].chunk_begin, ce = pl.seg[si].chunk_end;
   const uint32_t col = (uint32_t)pl.seg[si].tmem_col, fresh = (uint32_t)pl.seg[si].fresh;
-  const uint32_t idesc = idesc_n16(pl.seg[si].m64 ? 64 : 128);
+  const uint32_t idesc = idesc_n16(pl.seg[si].m64 ? 64 : 128, nb);
+  const uint32_t brow = (uint32_t)nb * 16;
 #pragma unroll 1
   for (int ci = cb; ci < ce; ++ci) {
     const uint32_t nmma = pl.c[ci].nmma, lbo16 = pl.c[ci].lbo16, bk8 = pl.c[ci].b_k8, tile = pl.c[ci].tile, k0 = pl.c[ci].k0;
     mbar_wait_inline(&rg.full[pos.slot], pos.phase);
     tc_fence_after();
     const uint64_t ad0 = desc_ns(rg.base + pos.slot * rg.slot_bytes, lbo16 << 4);
-    const uint64_t bd0 = desc_ns(bbuf + bk8 * BROW, BROW);
+    const uint64_t bd0 = desc_ns(bbuf + bk8 * brow, brow);
     const uint32_t dcol = tmem_base + col + tile * NB;
-    const uint32_t astep = lbo16 * 2, bstep = (2 * BROW) >> 4;       // one MMA = K 16 = two 8-wide k chunks
+    const uint32_t astep = lbo16 * 2, bstep = (2 * brow) >> 4;       // one MMA = K 16 = two 8-wide k chunks
     uint32_t acc = (fresh && k0 == 0) ? 0u : 1u;
 #pragma unroll 4
     for (uint32_t j = 0; j < nmma; ++j) {
@@ -218,16 +221,20 @@ __device__ __forceinline__ void mma_seg(const Plan& pl, int si, uint32_t bbuf, u
 // lane quadrant (ew + 2) % 4, column half ew / 4).
 // An M = 64 accumulator keeps row r in TMEM lane 32 (r / 16) + r % 16 (profiles/r02a_probe_umma.md).
 // `add` (optional): add[m * add_ld + row] is added on the way (a hoisted, batched part of the same pre-activation).
-__device__ __forceinline__ void tmem_to_outb(uint32_t tmem_base, int col, int rows, int m64, float* outb, const float* add, int add_ld, int ew, int lane) {
-  const int q = (ew + 2) & 3, half = ew >> 2;
-  if (m64) {
-    if (16 * q < rows) {
+// nb = 8: only the first column half exists; ob = row stride of outb (nb + 1).
+__device__ __forceinline__ void tmem_to_outb(uint32_t tmem_base, int col, int rows, int m64, float* outb, const float* add, int add_ld, int ew, int lane,
+                                             int nb = NB) {
+  const int q = (ew + 2) & 3, half = ew >> 2, ob = nb + 1;
+  if (8 * half >= nb) { tc_fence_before(); return; }
+  if (m64) {                                   // tiles of 64 rows: row 64 t + 16 q + lane (lane < 16) sits in TMEM lane 32 q + lane
+#pragma unroll 1
+    for (int t0 = 16 * q; t0 < rows; t0 += 64) {
       float v[8];
-      tmem_ld8(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(col + 8 * half), v);
-      const int r = 16 * q + lane;
+      tmem_ld8(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(col + (t0 >> 6) * NB + 8 * half), v);
+      const int r = t0 + lane;
       if (lane < 16 && r < rows) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) outb[r * OB + 8 * half + j] = v[j] + (add ? add[(8 * half + j) * add_ld + r] : 0.f);
+        for (int j = 0; j < 8; ++j) outb[r * ob + 8 * half + j] = v[j] + (add ? add[(8 * half + j) * add_ld + r] : 0.f);
       }
     }
     tc_fence_before();
@@ -240,7 +247,7 @@ __device__ __forceinline__ void tmem_to_outb(uint32_t tmem_base, int col, int ro
     const int r = r0 + lane;
     if (r < rows) {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) outb[r * OB + 8 * half + j] = v[j] + (add ? add[(8 * half + j) * add_ld + r] : 0.f);
+      for (int j = 0; j < 8; ++j) outb[r * ob + 8 * half + j] = v[j] + (add ? add[(8 * half + j) * add_ld + r] : 0.f);
     }
   }
   tc_fence_before();
@@ -299,7 +306,7 @@ __device__ __forceinline__ void sum2_combine(const float* lnp, int CL, int n_tot
   if (l16 == 0) { s_stat[m] = s1 / (float)n_total; s_stat[NB + m] = s2 / (float)n_total; }
 }
 // push this CTA's activation slice (already in operand layout in `stage`, `bytes` long) into slot c of every peer's operand buffer
-__device__ __forceinline__ void push_act(uint32_t stage_addr, uint32_t bytes, uint32_t buf_addr, uint64_t* bar, int c, int CL, int ew) {
+__device__ __forceinline__ void push_act(uint32_t stage_addr, uint32_t bytes, uint32_t buf_addr, uint64_t* bar, int c, int CL, int ew) {   // (bytes already reflect the batch tile)
 #pragma unroll 1
   for (int p = ew; p < CL; p += EW) {
     if (elect_one()) bulk_s2peer(mapa(buf_addr + (uint32_t)c * bytes, (uint32_t)p), stage_addr, bytes, mapa(smem_u32(bar), (uint32_t)p));
@@ -307,27 +314,28 @@ __device__ __forceinline__ void push_act(uint32_t stage_addr, uint32_t bytes, ui
   }
 }
 // offset (bytes) of element (m, k) inside an activation operand / slice that starts at k = 0
-__device__ __forceinline__ uint32_t b_off(int m, int k) { return (uint32_t)((k >> 3) * BROW + (m >> 3) * 128 + (m & 7) * 16 + (k & 7) * 2); }
+__device__ __forceinline__ uint32_t b_off(int m, int k, int brow = BROW) { return (uint32_t)((k >> 3) * brow + (m >> 3) * 128 + (m & 7) * 16 + (k & 7) * 2); }
 #endif  // __CUDACC__
 
 // ---- host: plan of the weight stream ----------------------------------------------------------------------------------------------
 inline int plan_add_seg(Plan& pl, int slot_max_bytes, int rows, int K, int tmem_col, int fresh, int b_k8_base, int nblk, const RowBlk* blk, int col0,
-                        uint32_t& off16) {
+                        uint32_t& off16, int tile_rows = 128) {
   if (pl.nseg >= MAX_SEG || rows <= 0 || (K & 15)) return -1;
   Seg& s = pl.seg[pl.nseg];
-  s.rows = rows; s.K = K; s.ntiles = (rows + 127) / 128; s.tmem_col = tmem_col; s.fresh = fresh; s.m64 = rows <= 64 ? 1 : 0;
+  s.rows = rows; s.K = K; s.tile_rows = tile_rows; s.ntiles = (rows + tile_rows - 1) / tile_rows; s.tmem_col = tmem_col; s.fresh = fresh;
+  s.m64 = (rows <= 64 || tile_rows == 64) ? 1 : 0;
   s.nblk = nblk; for (int i = 0; i < nblk; ++i) s.blk[i] = blk[i];
   s.col0 = col0;
   s.chunk_begin = pl.nchunks;
   // chunk depth: as deep as a slot allows for the widest tile (fewer, larger copies: ~160 clk of producer time per copy)
-  const int rows_pad_max = ((rows < 128 ? rows : 128) + 7) & ~7;
+  const int rows_pad_max = ((rows < tile_rows ? rows : tile_rows) + 7) & ~7;
   int KC = 256;
   while (KC > 16 && rows_pad_max * KC * 2 > slot_max_bytes) KC >>= 1;
   for (int k0 = 0; k0 < K; k0 += KC) {
     const int kc = (K - k0 < KC) ? (K - k0) : KC;
     for (int t = 0; t < s.ntiles; ++t) {
       if (pl.nchunks >= MAX_CHUNKS) return -1;
-      const int trows = (rows - t * 128 < 128) ? rows - t * 128 : 128;
+      const int trows = (rows - t * tile_rows < tile_rows) ? rows - t * tile_rows : tile_rows;
       const int rp = (trows + 7) & ~7;
       Chunk& c = pl.c[pl.nchunks++];
       c.off16 = off16; c.bytes16 = (uint16_t)(rp * kc * 2 / 16); c.nmma = (uint16_t)(kc / 16); c.lbo16 = (uint16_t)rp;

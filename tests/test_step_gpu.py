@@ -481,6 +481,8 @@ def test_fused_bf16_scan_matches_fp32_scan(cuda_ops, size, B, T, obs, acts, kern
     ("S", 16, 64, 14, [100], "tcgen05"), ("XS", 16, 20, 4, [2], "tcgen05"), ("S", 5, 9, 14, [7, 3], "tcgen05"),
     ("S", 32, 6, 14, [100], "tcgen05"),          # B = 32: two clusters of 16 rows
     ("prey", 16, 8, 14, [100], "tcgen05"),       # D = Hh = 256, U = 1024: unequal slices in the Wgru^T contraction
+    ("M", 16, 12, 20, [18], "tcgen05"),          # D = 1024: the [16, 3D] operand does not fit -> two clusters of 8 batch rows
+    ("M", 5, 7, 20, [18], "tcgen05"),
     ("S", 16, 16, 14, [100], "cluster"), ("XS", 7, 10, 4, [2], "cluster")])
 def test_fused_reverse_scan_matches_per_step_composition(size, B, T, obs, acts, kernel):
     """The one-launch reverse scans -- dv3_rssm_observe_bwd_tc (tcgen05, transposed weights through the bulk-copy ring) and its
