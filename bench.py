@@ -398,6 +398,27 @@ def kernel_rooflines(run, value):
                                        f"the kernel's own MMAs execute {mult * executed * rows_tb / 1e9:.2f} GFLOP of it (prior head and hoisted projections run batched outside)",
                         "method": "5 launches back to back with the packed weights reused, CUDA events"})
         ops.reuse_packed_weights = False
+    # ---- imagination rollout (one persistent launch: H steps of prior RSSM + actor on N = T*B rows)
+    if getattr(ops, "use_rollout_tc", False) and ops.rollout_kernel is not None:
+        S, U, D, Hh, A, lat, H, N = eng.S, eng.U, eng.D, eng.Hh, eng.A, eng.lat, eng.H, eng.N
+        st = eng.act_stack
+        Ua, La = st.layers[0]["w"].shape[0], len(st.layers)
+        f_actor = 2.0 * (lat * Ua + (La - 1) * Ua * Ua + Ua * A)
+        f_img = 2.0 * (S * U + (U + D) * 3 * D + D * Hh + Hh * S)       # the action part of the first layer is a row gather (one-hot actions)
+        fl = N * (H * (f_img + f_actor) + f_actor)
+        fn = lambda: eng.imagine()  # noqa: E731
+        ms = event_time(torch, fn, 5)
+        tc = fl / (ms * 1e-3) / 1e12
+        traffic, traffic_of, _ = ncu_traffic("rollout")
+        saved_bytes = N * (H + 1) * (lat * 6 + La * Ua * 10 + A * 4) + N * H * (3 * D + Hh + S) * 4.0
+        out.append({"class": "imagination rollout", "kernel": "rollout_tc_kernel", "bound": "tensor", "achieved": tc, "peak": pk["tc_sustained"],
+                    "unit": "TFLOP/s", "frac": tc / pk["tc_sustained"],
+                    "hbm_form": {"achieved": saved_bytes / (ms * 1e-3) / 1e9, "peak": pk["hbm"], "unit": "GB/s",
+                                 "frac": saved_bytes / (ms * 1e-3) / 1e9 / pk["hbm"], "algorithmic_bytes": saved_bytes},
+                    "traffic": traffic, "traffic_of": traffic_of, "launches_per_step": 1, "avg_launch_ms": ms, "kernel_ms_per_step": ms,
+                    "algorithmic": f"N x (H x (prior-RSSM step + actor) + actor) = {N} rows x {(H * (f_img + f_actor) + f_actor) / 1e6:.1f} MFLOP = {fl / 1e9:.1f} GFLOP; "
+                                   "bytes form = trajectory (fp32 + bf16 mirror) and the activations kept for the behaviour backward",
+                    "method": "5 x Engine.imagine() (start-state copy + weight-mirror refresh + the persistent kernel), CUDA events"})
     # ---- fused clip + Adam on the world-model arena (32 B / parameter)
     a = eng.wm
     hp = eng.opt_hparams["world"]
