@@ -462,7 +462,10 @@ class CudaOps:
     def im2col(self, x, N, H, W, Cc, col):
         assert x.is_contiguous() and col.is_contiguous() and col.numel() == N * (H // 2) * (W // 2) * 16 * Cc
         self.launches += 1
-        _chk(self.lib.dv3_im2col_k4s2p1(N, H, W, Cc, _p(x), _p(col), self._m16(_p(col)), self._s()), "dv3_im2col_k4s2p1")
+        m16 = self._m16(_p(col))
+        # bf16 precision: only the contractions read `col`, and they read its bf16 mirror, so the fp32 copy (2/3 of the bytes) is not written
+        p32 = None if (m16 is not None and not self.mirror_check) else _p(col)
+        _chk(self.lib.dv3_im2col_k4s2p1(N, H, W, Cc, _p(x), p32, m16, self._s()), "dv3_im2col_k4s2p1")
 
     def col2im(self, col, N, Hi, Wi, Cc, bias, add, y):
         assert col.is_contiguous() and y.is_contiguous() and y.numel() == N * Hi * Wi * 4 * Cc

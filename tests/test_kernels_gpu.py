@@ -60,7 +60,8 @@ def test_transpose_copy(cuda_ops):
 
 
 @pytest.mark.parametrize("M,U,act,eps", [(16, 512, 1, 1e-3), (1024, 640, 1, 1e-5), (3, 40, 0, 1e-5), (16, 1536, 1, 1e-3), (300, 512, 1, 1e-3),
-                                         (257, 1024, 0, 1e-5), (256, 24, 1, 1e-3)])
+                                         (257, 1024, 0, 1e-5), (256, 24, 1, 1e-3), (4099, 32, 1, 1e-3), (1031, 64, 1, 1e-3), (517, 100, 0, 1e-3),
+                                         (300, 128, 1, 1e-3), (259, 8, 1, 1e-3)])
 def test_ln_act(cuda_ops, torch_ops, M, U, act, eps):
     x, g, b = rnd(M, U, scale=2.0) + 0.3, rnd(U) * 0.2 + 1, rnd(U) * 0.1
     outs = []
@@ -349,6 +350,37 @@ def test_gemm_bf16_strided_views():
     assert torch.equal(C1[:, :101], big_c[:, :101]) and torch.equal(C1[:, 357:], big_c[:, 357:])
 
 
+def test_colsum_narrow(cuda_ops, torch_ops):
+    """Column sums / LayerNorm parameter sums of a tall, 3-column matrix (the image-channel bias gradient): the row-per-thread kernel."""
+    M, U = 70001, 3
+    d, x = rnd(M, U, seed=1), rnd(M, U, seed=2)
+    mean, rstd = x.mean(-1), (x.var(-1, unbiased=False) + 1e-3).rsqrt()
+    res = []
+    for ops in (torch_ops, cuda_ops):
+        db, dg, db2 = torch.zeros(U, device=DEV), torch.zeros(U, device=DEV), torch.zeros(U, device=DEV)
+        ops.colsum(d, db)
+        ops.ln_param_grad(d, x, mean, rstd, dg, db2)
+        res.append((db, dg, db2))
+    for a, r in zip(res[1], res[0]):
+        assert rel(a.double(), r.double()) < 2e-5
+    assert torch.allclose(res[1][0].double(), d.double().sum(0), rtol=1e-4, atol=1e-3)
+
+
+def test_im2col_bf16_only(cuda_ops_bf16):
+    """bf16 precision: im2col writes only the bf16 mirror of `col` (vector and scalar kernels) == bf16(unfold)."""
+    from oracle.torch_ops import TorchOps
+
+    for N, H, C in [(3, 16, 32), (2, 64, 3), (5, 8, 24)]:
+        x = rnd(N * H * H, C)
+        col = torch.full((N * (H // 2) ** 2, 16 * C), 7.0, device=DEV)
+        cuda_ops_bf16.mirror(col)
+        cuda_ops_bf16.im2col(x, N, H, H, C, col)
+        ref = torch.zeros_like(col)
+        TorchOps().im2col(x, N, H, H, C, ref)
+        assert torch.equal(cuda_ops_bf16._m16_view(col).view_as(col), ref.bfloat16())
+        assert torch.all(col == 7.0)       # the fp32 copy is left alone
+
+
 @pytest.mark.parametrize("N,H,C", [(3, 64, 3), (5, 16, 24), (2, 8, 96), (7, 4, 40)])
 def test_conv_data_movement(cuda_ops, torch_ops, N, H, C):
     x = rnd(N * H * H, C)
@@ -528,7 +560,8 @@ def test_unimix_sample_fused(cuda_ops, cuda_ops_bf16, R, groups, K):
 
 
 @pytest.mark.parametrize("M,U,act,bias", [(1024, 512, 1, True), (16384, 512, 1, False), (300, 640, 1, True), (257, 1024, 0, True), (256, 24, 1, True),
-                                          (16, 512, 1, True), (1024, 510, 1, True)])
+                                          (16, 512, 1, True), (1024, 510, 1, True), (40003, 32, 1, True), (9001, 64, 1, False), (517, 100, 0, True),
+                                          (300, 128, 1, True), (2000, 256, 1, True), (259, 8, 1, True)])
 def test_ln_act_bwd_fused(cuda_ops, torch_ops, M, U, act, bias):
     """LayerNorm(+SiLU) backward with fused column sums == the three separate ops (fallback shapes included)."""
     x, g, b = rnd(M, U, scale=2.0) + 0.3, rnd(U) * 0.2 + 1, rnd(U) * 0.1
