@@ -306,8 +306,9 @@ class Actor(nn.Module):
 
 class PlayerDV3(nn.Module):
     """Environment-interaction side of the agent (agent.py:458-599): shares the trained modules' weights and steps
-    encoder -> GRU -> posterior -> actor once per env step, in plain torch.  It is the caller of the hot path, not part of it
-    (SURVEY.md section 8f-2); provided so that `main()` runs against these modules without the reference's class."""
+    encoder -> GRU -> posterior -> actor once per env step.  With modules from `build_models` on a CUDA device the step runs on the
+    library's kernels (`sheeprl_prey_b200/player.py`, state on the device, one CUDA graph per step); otherwise (CPU modules) it is the
+    same arithmetic in plain torch.  It is the caller of the hot path, not part of it."""
 
     def __init__(self, encoder, rssm: RSSM, actor, actions_dim: Sequence[int], num_envs: int, stochastic_size: int,
                  recurrent_state_size: int, device="cpu", discrete_size: int = 32):
@@ -319,9 +320,22 @@ class PlayerDV3(nn.Module):
         self.actions_dim, self.num_envs = list(actions_dim), num_envs
         self.stochastic_size, self.discrete_size, self.recurrent_state_size = stochastic_size, discrete_size, recurrent_state_size
         self.device = torch.device(device)
+        eng = getattr(unwrap(rssm), "_dv3_engine", None)
+        self._cuda = None
+        if eng is not None and eng.device.type == "cuda" and self.device.type == "cuda":
+            from ...player import PlayerStep
+
+            object.__setattr__(self, "_cuda", PlayerStep(eng, num_envs, seed=eng.seed + 0x5DEECE66D))
+
+    def _sync_views(self) -> None:
+        self.actions, self.recurrent_state, self.stochastic_state = self._cuda.actions, self._cuda.recurrent_state, self._cuda.stochastic_state
 
     @torch.no_grad()
     def init_states(self, reset_envs: Optional[Sequence[int]] = None) -> None:
+        if self._cuda is not None:
+            self._cuda.init_states(reset_envs)
+            self._sync_views()
+            return
         if reset_envs is None or len(reset_envs) == 0:
             self.actions = torch.zeros(1, self.num_envs, sum(self.actions_dim), device=self.device)
             self.recurrent_state = torch.zeros(1, self.num_envs, self.recurrent_state_size, device=self.device)
@@ -334,6 +348,10 @@ class PlayerDV3(nn.Module):
 
     @torch.no_grad()
     def get_greedy_action(self, obs: Dict[str, Tensor], is_training: bool = True, mask=None) -> Sequence[Tensor]:
+        if self._cuda is not None:
+            actions = self._cuda.step(obs, is_training, mask)
+            self._sync_views()
+            return actions
         embedded = self.encoder(obs)
         self.recurrent_state = self.rssm.recurrent_model(torch.cat((self.stochastic_state, self.actions), -1), self.recurrent_state)
         _, stoch = self.rssm._representation(self.recurrent_state, embedded)
@@ -444,6 +462,7 @@ def build_models(
     engine = DV3Engine(cfg, obs_shapes, list(actions_dim), *arenas, ops, device, dist=dist,
                        seed=_mix_seed(int(cfg.get("seed", 42) or 0), int(getattr(fabric, "global_rank", 0))))
     object.__setattr__(world_model, "_dv3_engine", engine)   # not a submodule / not in state_dict
+    object.__setattr__(world_model.rssm, "_dv3_engine", engine)   # PlayerDV3 is handed (encoder, rssm, actor), not the world model
 
     # Fabric wrapping, same call sites as agent.py:1054-1063 (DDP hooks are inert: the engine all-reduces its own grads)
     wm = world_model

@@ -45,7 +45,7 @@ constexpr int MAXCL = 16;
 struct RollK {
   CUtensorMap m_traj, m_feat, m_thid, m_act[MAXL], m_wz, m_wgru, m_wt0, m_wt1, m_wa[MAXL], m_wh;
   Dv3RolloutArgs a;
-  int CL;
+  int CL, tmem_cols;
   long long* dbg;
 };
 
@@ -109,6 +109,8 @@ struct Stage {
   const CUtensorMap* a1; int a1_col, a1_row, K1;      // optional second source (concatenated along K)
   const CUtensorMap* b; int nb, b_row[3], b_rows;     // nb boxes of b_rows weight rows each (GRU: the three gates)
   int n_pad;                                          // N of the MMA (multiple of 16, >= nb * b_rows)
+  int npass, pass_row_step, pass_tmem_step;           // the stage's N split into npass sweeps over K (pass p: weight rows + p * pass_row_step,
+                                                      // accumulator columns + p * pass_tmem_step); 1 except for a GRU with D / CL > 64
 };
 struct Pipe {            // ring position, advanced identically by the producer and the MMA warp
   uint32_t slot, phase;
@@ -138,6 +140,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   const int N = a.N, H = a.H, S = a.S, G = a.G, Kc = a.Kc, D = a.D, U = a.U, Hh = a.Hh, A = a.A, lat = a.lat, L = a.L, Ua = a.Ua;
   const int uper = U / CL, dper = D / CL, hper = Hh / CL, gper = G / CL, sper = gper * Kc, aper = Ua / CL;
   const int u0 = c * uper, d0 = c * dper, h0 = c * hper, s0 = c * sper, au0 = c * aper;
+  const int dpp = dper < 64 ? dper : 64;                    // GRU units per pass (accumulator: [pass][gate][dpp] columns)
   const int row_blk = blk * RM;                             // first row of the block inside a step's N rows
 
   for (int i = tid; i < NSTG * (A_BYTES + B_BYTES) / 16; i += NTHR) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -148,7 +151,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(k.tmem_cols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -169,17 +172,21 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     const int nk0 = st.K0 / KB, nk = nk0 + st.K1 / KB;
     const uint32_t bytes = A_BYTES + (uint32_t)st.nb * st.b_rows * KB * 2;
 #pragma unroll 1
-    for (int kb = 0; kb < nk; ++kb) {
-      mbar_wait(&empty_bar[pp.slot], pp.phase ^ 1u);
-      if (elect_one()) {
-        mbar_expect_tx(&full_bar[pp.slot], bytes);
-        const uint32_t da = smem_u32(ring_a + pp.slot * A_BYTES), db = smem_u32(ring_b + pp.slot * B_BYTES);
-        if (kb < nk0) tma_load_2d(da, st.a0, &full_bar[pp.slot], st.a0_col + kb * KB, st.a0_row);
-        else tma_load_2d(da, st.a1, &full_bar[pp.slot], st.a1_col + (kb - nk0) * KB, st.a1_row);
-        for (int j = 0; j < st.nb; ++j) tma_load_2d(db + (uint32_t)j * st.b_rows * KB * 2, st.b, &full_bar[pp.slot], kb * KB, st.b_row[j]);
+    for (int ps = 0; ps < st.npass; ++ps) {
+      const int roff = ps * st.pass_row_step;
+#pragma unroll 1
+      for (int kb = 0; kb < nk; ++kb) {
+        mbar_wait(&empty_bar[pp.slot], pp.phase ^ 1u);
+        if (elect_one()) {
+          mbar_expect_tx(&full_bar[pp.slot], bytes);
+          const uint32_t da = smem_u32(ring_a + pp.slot * A_BYTES), db = smem_u32(ring_b + pp.slot * B_BYTES);
+          if (kb < nk0) tma_load_2d(da, st.a0, &full_bar[pp.slot], st.a0_col + kb * KB, st.a0_row);
+          else tma_load_2d(da, st.a1, &full_bar[pp.slot], st.a1_col + (kb - nk0) * KB, st.a1_row);
+          for (int j = 0; j < st.nb; ++j) tma_load_2d(db + (uint32_t)j * st.b_rows * KB * 2, st.b, &full_bar[pp.slot], kb * KB, st.b_row[j] + roff);
+        }
+        __syncwarp();
+        if (++pp.slot == NSTG) { pp.slot = 0; pp.phase ^= 1u; }
       }
-      __syncwarp();
-      if (++pp.slot == NSTG) { pp.slot = 0; pp.phase ^= 1u; }
     }
   };
   auto issue = [&](const Stage& st) {
@@ -187,23 +194,29 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(st.n_pad >> 3) << 17) | ((uint32_t)(RM >> 4) << 24);
     const uint64_t ad0 = make_desc_sw128(smem_u32(ring_a)), bd0 = make_desc_sw128(smem_u32(ring_b));
 #pragma unroll 1
-    for (int kb = 0; kb < nk; ++kb) {
-      mbar_wait(&full_bar[pp.slot], pp.phase);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint64_t ad = ad0 + (uint64_t)((pp.slot * A_BYTES) >> 4), bd = bd0 + (uint64_t)((pp.slot * B_BYTES) >> 4);
+    for (int ps = 0; ps < st.npass; ++ps) {
+      const uint32_t dcol = tmem_base + (uint32_t)(ps * st.pass_tmem_step);
+      const bool last_pass = (ps == st.npass - 1);
+#pragma unroll 1
+      for (int kb = 0; kb < nk; ++kb) {
+        mbar_wait(&full_bar[pp.slot], pp.phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint64_t ad = ad0 + (uint64_t)((pp.slot * A_BYTES) >> 4), bd = bd0 + (uint64_t)((pp.slot * B_BYTES) >> 4);
 #pragma unroll
-      for (int kk = 0; kk < KB / 16; ++kk) {
-        const uint32_t accum = (kb > 0 || kk > 0) ? 1u : 0u;
-        if (elect_one())
-          asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_base),
-                       "l"(ad + (uint64_t)(kk * 2)), "l"(bd + (uint64_t)(kk * 2)), "r"(idesc), "r"(accum) : "memory");
+        for (int kk = 0; kk < KB / 16; ++kk) {
+          const uint32_t accum = (kb > 0 || kk > 0) ? 1u : 0u;
+          if (elect_one())
+            asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(dcol),
+                         "l"(ad + (uint64_t)(kk * 2)), "l"(bd + (uint64_t)(kk * 2)), "r"(idesc), "r"(accum) : "memory");
+        }
+        if (elect_one()) {
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[pp.slot])) : "memory");
+          if (last_pass && kb == nk - 1)
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(acc_bar)) : "memory");
+        }
+        __syncwarp();
+        if (++pp.slot == NSTG) { pp.slot = 0; pp.phase ^= 1u; }
       }
-      if (elect_one()) {
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[pp.slot])) : "memory");
-        if (kb == nk - 1) asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(acc_bar)) : "memory");
-      }
-      __syncwarp();
-      if (++pp.slot == NSTG) { pp.slot = 0; pp.phase ^= 1u; }
     }
   };
   // ---- epilogue: thread = (row rl, column quarter cq).  Hardware warp w reaches TMEM lanes 32 (w % 4) ..: the four warps of one cq
@@ -218,6 +231,26 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]);
+  };
+  // four 8-column loads in flight, one wait: x[0..32) = accumulator columns [col, col + 32) of this thread's row (chunks at or past
+  // `ncols` columns are skipped and left untouched).  The registers pass through the wait statement so that no use is scheduled above it.
+  auto ld32 = [&](int col, int ncols, float* v) {
+    uint32_t r[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) r[j] = 0u;
+#pragma unroll
+    for (int c0 = 0; c0 < 32; c0 += 8)
+      if (c0 < ncols)
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+                     : "=r"(r[c0]), "=r"(r[c0 + 1]), "=r"(r[c0 + 2]), "=r"(r[c0 + 3]), "=r"(r[c0 + 4]), "=r"(r[c0 + 5]), "=r"(r[c0 + 6]), "=r"(r[c0 + 7])
+                     : "r"(t_lane + (uint32_t)(col + c0)));
+#pragma unroll
+    for (int c0 = 0; c0 < 32; c0 += 8)
+      asm volatile("tcgen05.wait::ld.sync.aligned;"
+                   : "+r"(r[c0]), "+r"(r[c0 + 1]), "+r"(r[c0 + 2]), "+r"(r[c0 + 3]), "+r"(r[c0 + 4]), "+r"(r[c0 + 5]), "+r"(r[c0 + 6]), "+r"(r[c0 + 7])
+                   :: "memory");
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
   };
   auto st8_f32 = [](float* dst, const float* v) {
     *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
@@ -273,10 +306,10 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   auto ln_silu_epilogue = [&](int n, const float* bias, const float* gamma, const float* beta, float eps, const float* add_tab, int add_ld,
                               const int* add_idx, float* pre, float* act, __nv_bfloat16* act16, int ld_out, size_t grow, int col0, float* gmean,
                               float* grstd) {
-    const int nq = n >> 2, cb = cq * nq;                 // this thread's columns [cb, cb + nq) of the CTA's n
+    const int nq = (((n + 3) >> 2) + 7) & ~7, cb = cq * nq;   // this thread's columns [cb, min(cb + nq, n)) of the CTA's n (n % 8 == 0)
     float s = 0.f, q = 0.f;
 #pragma unroll 1
-    for (int c0 = 0; c0 < nq; c0 += 8) {
+    for (int c0 = 0; c0 < nq && cb + c0 < n; c0 += 8) {
       float x[8];
       chunk(cb + c0, col0 + cb + c0, bias, add_tab, add_ld, add_idx, x);
 #pragma unroll
@@ -287,7 +320,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     ln_exchange(s, q, n, eps, mu, rs);
     if (gmean && c == 0 && cq == 0) { gmean[grow] = mu; grstd[grow] = rs; }
 #pragma unroll 1
-    for (int c0 = 0; c0 < nq; c0 += 8) {
+    for (int c0 = 0; c0 < nq && cb + c0 < n; c0 += 8) {
       float x[8];
       const int gcol = col0 + cb + c0;
       chunk(cb + c0, gcol, bias, add_tab, add_ld, add_idx, x);
@@ -329,7 +362,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       if (l == 0) { st.a0 = &k.m_traj; st.a0_col = 0; st.a0_row = arow; st.K0 = lat; }
       else { st.a0 = &k.m_act[l - 1]; st.a0_col = 0; st.a0_row = arow; st.K0 = Ua; }
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wa[l]; st.nb = 1; st.b_row[0] = au0; st.b_rows = aper; st.n_pad = aper;
+      st.b = &k.m_wa[l]; st.nb = 1; st.b_row[0] = au0; st.b_rows = aper; st.n_pad = aper; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
@@ -343,63 +376,44 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       Stage st;
       st.a0 = &k.m_act[L - 1]; st.a0_col = 0; st.a0_row = arow; st.K0 = Ua;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wh; st.nb = 1; st.b_row[0] = 0; st.b_rows = A; st.n_pad = (A + 15) & ~15;
+      st.b = &k.m_wh; st.nb = 1; st.b_row[0] = 0; st.b_rows = A; st.n_pad = (A + 15) & ~15; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
       if (c == 0) {
         if (warp == 0) produce(st);
         else if (warp == 1) issue(st);
         else {
           wait_acc();
-          // this thread: logits [32 cq, 32 cq + 32) of the row, streamed from TMEM in 8-column chunks for each of the four passes
-          // (row maximum, softmax denominator, total unimix mass, the draw); the four quarters meet in shared memory each time
+          // this thread: logits [32 cq, 32 cq + 32) of the row, in registers (one TMEM pass, one exponential per logit); the four
+          // quarters meet in shared memory for the row maximum, the softmax denominator, the total unimix mass and the draw
           const int dim = a.head_dim[0], cb = 32 * cq, npad = st.n_pad;
-          auto logits8 = [&](int c0, float* x) {
-            if (cb + c0 < npad) {
-              ld8(cb + c0, x);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) { const int col = cb + c0 + j; x[j] = (col < dim) ? x[j] + __ldg(a.bh + col) : -INFINITY; }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) x[j] = -INFINITY;
-            }
-          };
+          float x[32];
+          ld32(cb, npad - cb, x);
           float mx = -INFINITY;
-#pragma unroll 1
-          for (int c0 = 0; c0 < 32; c0 += 8) {
-            float x[8];
-            logits8(c0, x);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { mx = fmaxf(mx, x[j]); if (cb + c0 + j < dim) a.aout[grow * A + cb + c0 + j] = x[j]; }
+          for (int j = 0; j < 32; ++j) {
+            const int col = cb + j;
+            x[j] = (col < dim) ? x[j] + __ldg(a.bh + col) : -INFINITY;
+            mx = fmaxf(mx, x[j]);
+            if (col < dim) a.aout[grow * A + col] = x[j];
           }
           red[cq * RM + rl].x = mx;
           epi_bar();
           mx = fmaxf(fmaxf(red[rl].x, red[RM + rl].x), fmaxf(red[2 * RM + rl].x, red[3 * RM + rl].x));
           float se = 0.f;
-#pragma unroll 1
-          for (int c0 = 0; c0 < 32; c0 += 8) {
-            float x[8];
-            logits8(c0, x);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) se += __expf(x[j] - mx);
+          for (int j = 0; j < 32; ++j) {
+            x[j] = __expf(x[j] - mx);           // exp(-inf) = 0 for the columns past the head
+            se += x[j];
           }
           red[cq * RM + rl].y = se;
           epi_bar();
           se = red[rl].y + red[RM + rl].y + red[2 * RM + rl].y + red[3 * RM + rl].y;
           const float mixk = a.unimix / (float)dim, inv = __fdividef(1.f, se);
-          auto pm8 = [&](int c0, float* x) {     // unimix probabilities of 8 logits
-            logits8(c0, x);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float p = __expf(x[j] - mx) * inv;
-              x[j] = (cb + c0 + j < dim) ? ((a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p) : 0.f;
-            }
-          };
           float mass = 0.f;
-#pragma unroll 1
-          for (int c0 = 0; c0 < 32; c0 += 8) {
-            float x[8];
-            pm8(c0, x);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) mass += x[j];
+          for (int j = 0; j < 32; ++j) {
+            const float p = x[j] * inv;
+            x[j] = (cb + j < dim) ? ((a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p) : 0.f;
+            mass += x[j];
           }
           epi_bar();                                   // (everyone has read red[].x / .y)
           red[cq * RM + rl].x = mass;
@@ -411,13 +425,8 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
           const float thr = u * tot;                   // idx = #{k : cumsum_k(p) / tot <= u}
           float cs = before;
           int cnt = 0;
-#pragma unroll 1
-          for (int c0 = 0; c0 < 32; c0 += 8) {
-            float x[8];
-            pm8(c0, x);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { cs += x[j]; cnt += (cb + c0 + j < dim && cs <= thr) ? 1 : 0; }
-          }
+          for (int j = 0; j < 32; ++j) { cs += x[j]; cnt += (cb + j < dim && cs <= thr) ? 1 : 0; }
           red[cq * RM + rl].y = __int_as_float(cnt);
           epi_bar();
           if (cq == 0) {
@@ -443,7 +452,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       Stage st;
       st.a0 = &k.m_traj; st.a0_col = 0; st.a0_row = prow; st.K0 = S;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wz; st.nb = 1; st.b_row[0] = u0; st.b_rows = uper; st.n_pad = uper;
+      st.b = &k.m_wz; st.nb = 1; st.b_row[0] = u0; st.b_rows = uper; st.n_pad = uper; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
@@ -459,19 +468,21 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       Stage st;
       st.a0 = &k.m_traj; st.a0_col = S; st.a0_row = prow; st.K0 = D;
       st.a1 = &k.m_feat; st.a1_col = 0; st.a1_row = row_blk; st.K1 = U;
-      st.b = &k.m_wgru; st.nb = 3; st.b_row[0] = d0; st.b_row[1] = D + d0; st.b_row[2] = 2 * D + d0; st.b_rows = dper; st.n_pad = 3 * dper;
+      st.b = &k.m_wgru; st.nb = 3; st.b_row[0] = d0; st.b_row[1] = D + d0; st.b_row[2] = 2 * D + d0; st.b_rows = dpp; st.n_pad = 3 * dpp;
+      st.npass = dper / dpp; st.pass_row_step = dpp; st.pass_tmem_step = 3 * dpp;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
         const int dq = dper >> 2, db = cq * dq;            // this thread: units [db, db + dq) of the CTA's dper, 8 at a time
+        auto gate_col = [&](int ul, int g) { const int ps = ul / dpp; return ps * 3 * dpp + g * dpp + (ul - ps * dpp); };
         float s = 0.f, q = 0.f;
 #pragma unroll 1
         for (int c0 = 0; c0 < dq; c0 += 8) {
           float vr[8], vc[8], vu[8];
-          ld8(db + c0, vr);
-          ld8(dper + db + c0, vc);
-          ld8(2 * dper + db + c0, vu);
+          ld8(gate_col(db + c0, 0), vr);
+          ld8(gate_col(db + c0, 1), vc);
+          ld8(gate_col(db + c0, 2), vu);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             s += vr[j] + vc[j] + vu[j];
@@ -483,9 +494,9 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
 #pragma unroll 1
         for (int c0 = 0; c0 < dq; c0 += 8) {
           float vr[8], vc[8], vu[8];
-          ld8(db + c0, vr);
-          ld8(dper + db + c0, vc);
-          ld8(2 * dper + db + c0, vu);
+          ld8(gate_col(db + c0, 0), vr);
+          ld8(gate_col(db + c0, 1), vc);
+          ld8(gate_col(db + c0, 2), vu);
           const int d = d0 + db + c0;
           const float* hp = a.traj + gp * lat + S + d;
           const float4 h0_ = *reinterpret_cast<const float4*>(hp), h1_ = *reinterpret_cast<const float4*>(hp + 4);
@@ -510,7 +521,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       Stage st;
       st.a0 = &k.m_traj; st.a0_col = S; st.a0_row = crow; st.K0 = D;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wt0; st.nb = 1; st.b_row[0] = h0; st.b_rows = hper; st.n_pad = hper;
+      st.b = &k.m_wt0; st.nb = 1; st.b_row[0] = h0; st.b_rows = hper; st.n_pad = hper; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
@@ -524,7 +535,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       Stage st;
       st.a0 = &k.m_thid; st.a0_col = 0; st.a0_row = row_blk; st.K0 = Hh;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
-      st.b = &k.m_wt1; st.nb = 1; st.b_row[0] = s0; st.b_rows = sper; st.n_pad = sper;
+      st.b = &k.m_wt1; st.nb = 1; st.b_row[0] = s0; st.b_rows = sper; st.n_pad = sper; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
       if (warp == 0) produce(st);
       else if (warp == 1) issue(st);
       else {
@@ -533,57 +544,45 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
         for (int gl = cq; gl < gper; gl += 4) {
           const int g = c * gper + gl;
           const size_t zi = ((size_t)(i - 1) * N + row_blk + rl) * G + g;
-          auto lg8 = [&](int c0, float* x) {
-            ld8(gl * Kc + c0, x);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) x[j] += __ldg(a.bt1 + s0 + gl * Kc + c0 + j);
-          };
           int idx;
           if (a.f_z) {
             idx = a.f_z[zi];
           } else {
+            // the group's Kc <= 32 logits in registers: one TMEM pass, one exponential per class
+            float x[32];
+            ld32(gl * Kc, Kc, x);
+            const float* bp = a.bt1 + s0 + gl * Kc;
             float mx = -INFINITY;
-#pragma unroll 1
-            for (int c0 = 0; c0 < Kc; c0 += 8) {
-              float x[8];
-              lg8(c0, x);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) mx = fmaxf(mx, x[j]);
+            for (int j = 0; j < 32; j += 4) {
+              if (j < Kc) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bp + j));
+                x[j] += b4.x; x[j + 1] += b4.y; x[j + 2] += b4.z; x[j + 3] += b4.w;
+                mx = fmaxf(fmaxf(mx, fmaxf(x[j], x[j + 1])), fmaxf(x[j + 2], x[j + 3]));
+              }
             }
             float se = 0.f;
-#pragma unroll 1
-            for (int c0 = 0; c0 < Kc; c0 += 8) {
-              float x[8];
-              lg8(c0, x);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) se += __expf(x[j] - mx);
+            for (int j = 0; j < 32; ++j) {
+              x[j] = (j < Kc) ? __expf(x[j] - mx) : 0.f;
+              se += x[j];
             }
             const float mixk = a.unimix / (float)Kc, inv = __fdividef(1.f, se);
-            // unimix probabilities sum to 1 up to round-off unless the clamp bites: one pass for the total, one for the draw
+            // unimix probabilities sum to 1 up to round-off unless the clamp bites: the draw is against their actual total
             float tot = 0.f;
-#pragma unroll 1
-            for (int c0 = 0; c0 < Kc; c0 += 8) {
-              float x[8];
-              lg8(c0, x);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float p = __expf(x[j] - mx) * inv;
-                tot += (a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p;
-              }
+            for (int j = 0; j < 32; ++j) {
+              const float p = x[j] * inv;
+              x[j] = (j < Kc) ? ((a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p) : 0.f;
+              tot += x[j];
             }
             const float thr = a.u_z[zi] * tot;         // idx = #{k : cumsum_k(p) / tot <= u}
             float cs = 0.f;
             idx = 0;
-#pragma unroll 1
-            for (int c0 = 0; c0 < Kc; c0 += 8) {
-              float x[8];
-              lg8(c0, x);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const float p = __expf(x[j] - mx) * inv;
-                cs += (a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p;
-                idx += (cs <= thr) ? 1 : 0;
-              }
+            for (int j = 0; j < 32; ++j) {
+              cs += x[j];
+              idx += (j < Kc && cs <= thr) ? 1 : 0;
             }
             idx = min(idx, Kc - 1);
           }
@@ -607,7 +606,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(k.tmem_cols));
   }
 }
 
@@ -617,9 +616,11 @@ int pick_cluster(const Dv3RolloutArgs* a) {
   for (int CL = 8; CL <= 16; CL <<= 1) {
     if (a->U % CL || a->D % CL || a->Hh % CL || a->G % CL || a->Ua % CL) continue;
     const int uper = a->U / CL, dper = a->D / CL, hper = a->Hh / CL, sper = (a->G / CL) * a->Kc, aper = a->Ua / CL;
-    // a thread owns a quarter of the CTA's columns of a layer, in 8-column TMEM chunks kept in registers (<= 32 per layer, <= 16 per gate)
-    if ((uper & 31) || (dper & 31) || (hper & 31) || (aper & 31) || (sper & 15) || (a->Kc & 7)) continue;
-    if (uper > 128 || hper > 128 || aper > 128 || dper > 64 || sper > NMAX) continue;
+    // MMA N: multiples of 16; a thread owns a quarter of the CTA's columns in 8-column TMEM chunks (GRU: dper / 4 units per thread);
+    // a GRU with more than 64 own units runs as passes of 64 (3 x 64 accumulator columns each)
+    if ((uper & 15) || (hper & 15) || (aper & 15) || (dper & 31) || (sper & 15) || (a->Kc & 7)) continue;
+    if (uper > NMAX || hper > NMAX || aper > NMAX || sper > NMAX) continue;
+    if (dper > 64 && ((dper & 63) || dper > 128)) continue;
     return CL;
   }
   return 0;
@@ -640,6 +641,10 @@ extern "C" int dv3_rollout_tc(const Dv3RolloutArgs* a, void* stream_) {
   RollK* k = new RollK;
   k->a = *a;
   k->CL = CL;
+  {
+    const int dper_ = a->D / CL, need = dper_ > 64 ? 3 * dper_ : 256;
+    k->tmem_cols = need > 256 ? 512 : 256;
+  }
   k->dbg = getenv("DV3_SCAN_DEBUG") ? reinterpret_cast<long long*>(a->dbg) : nullptr;
   int rc = 0;
   auto mk = [&](CUtensorMap* tm, const void* base, int rows, int cols, int ld, int box_rows) {

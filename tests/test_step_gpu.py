@@ -172,6 +172,148 @@ def test_train_api_on_gpu():
     assert float(mom.low) != 0.0 or float(mom.high) != 0.0
 
 
+@pytest.mark.parametrize("pixels", [False, True])
+def test_player_step_on_gpu_matches_module_forward(pixels):
+    """PlayerDV3 on CUDA runs the library's step body (sheeprl_prey_b200/player.py; reference agent.py:512-599).  Every env step is
+    replayed with the eager modules (same weights: the parameters are views of the engine's arenas) under the draws' contract
+    idx = #{k : cumsum_k(probs) <= u} with the uniforms the kernels used; states, logits and actions must agree, across resets and a
+    gradient step in between (the player sees updated weights without a copy)."""
+    from oracle import dv3_oracle as O
+    from sheeprl_prey_b200.algos.dreamer_v3 import build_models, train
+    from sheeprl_prey_b200.algos.dreamer_v3.agent import PlayerDV3
+    from sheeprl_prey_b200.algos.dreamer_v3.dreamer_v3 import Moments
+    from sheeprl_prey_b200.configs import ObsSpace
+    from util import Aggregator, FakeFabric
+
+    torch.backends.cudnn.allow_tf32 = False          # the eager replay below is the fp32 statement of the step
+    kw = dict(cnn_keys=["rgb"], cnn_mult=4) if pixels else {}
+    cfg = make_cfg("XS", batch_size=4, sequence_length=8, horizon=3, **kw)
+    acts, n = [5, 3], 4
+    od = {"state": 9, "rgb": (3, 64, 64)} if pixels else {"state": 9}
+    fab = FakeFabric(DEV)
+    torch.manual_seed(1)
+    wm, actor, critic, target = build_models(fab, acts, False, cfg, ObsSpace({k: ((v,) if isinstance(v, int) else v) for k, v in od.items()}))
+    w = cfg.algo.world_model
+    player = PlayerDV3(wm.encoder, wm.rssm, actor, acts, n, w.stochastic_size, w.recurrent_model.recurrent_state_size, DEV, w.discrete_size)
+    assert player._cuda is not None
+    G, K, S, mix = w.stochastic_size, w.discrete_size, w.stochastic_size * w.discrete_size, cfg.algo.unimix
+    player.init_states()
+    z0 = wm.rssm._transition(torch.zeros(1, n, w.recurrent_model.recurrent_state_size, device=DEV), sample_state=False)[1].reshape(1, n, -1)
+    assert torch.equal(player.stochastic_state, z0) and float(player.recurrent_state.abs().sum()) == 0.0
+
+    def ref_step(obs, h, z, a, u_z, u_a, is_training):
+        with torch.no_grad():
+            emb = wm.encoder(obs)
+            h2 = wm.rssm.recurrent_model(torch.cat((z, a), -1), h)
+            raw = wm.rssm.representation_model(torch.cat((h2, emb), -1)).view(n, G, K)
+            idx = O.inverse_cdf(O.categorical_probs(O.unimix_logits(raw, mix)), u_z)
+            z2 = torch.nn.functional.one_hot(idx, K).float().view(1, n, S)
+            x = actor.model(torch.cat((z2, h2), -1))
+            outs, idxs = [], []
+            for j, head in enumerate(actor.mlp_heads):
+                lg = head(x).view(n, -1)
+                ai = O.inverse_cdf(O.categorical_probs(O.unimix_logits(lg, mix)), u_a[:, j]) if is_training else lg.argmax(-1)
+                outs.append(torch.nn.functional.one_hot(ai, lg.shape[-1]).float().view(1, n, -1))
+                idxs.append(ai)
+        return h2, z2, torch.cat(outs, -1), raw, idxs
+
+    gen = torch.Generator().manual_seed(5)
+    for t in range(7):
+        obs = {"state": torch.randn(1, n, 9, generator=gen).to(DEV)}
+        if pixels:
+            obs["rgb"] = (torch.randint(0, 256, (1, n, 3, 64, 64), generator=gen).float() / 255.0).to(DEV)
+        h, z, a = player.recurrent_state.clone(), player.stochastic_state.clone(), player.actions.clone()
+        is_training = t != 5
+        got = player.get_greedy_action(obs, is_training) if not is_training else player.get_exploration_action(obs)
+        torch.cuda.synchronize()
+        h2, z2, a2, raw, idxs = ref_step(obs, h, z, a, player._cuda.u_z.clone(), player._cuda.u_a.clone(), is_training)
+        assert rel(player.recurrent_state, h2) < 2e-5, t
+        assert rel(player._cuda.post_raw.view(n, G, K), raw) < 5e-5, t
+        # a draw may differ only where the uniform sits within round-off of a CDF step; at these sizes it does not happen
+        assert torch.equal(player._cuda.z_idx.long(), (z2.view(n, G, K).argmax(-1))), t
+        assert torch.equal(player.stochastic_state, z2) and torch.equal(player.actions, a2), t
+        assert len(got) == 2 and got[0].shape == (1, n, 5) and got[1].shape == (1, n, 3)
+        assert torch.equal(torch.cat(got, -1), a2)
+        if t == 2:
+            player.init_states([1, 3])
+            assert float(player.recurrent_state[:, [1, 3]].abs().sum()) == 0.0 and torch.equal(player.stochastic_state[:, [1, 3]], z0[:, [1, 3]])
+            assert float(player.actions[:, [1, 3]].abs().sum()) == 0.0 and float(player.recurrent_state[:, [0, 2]].abs().sum()) > 0.0
+        if t == 3:      # a gradient step between env steps: the player's next step uses the new weights
+            a_ = cfg.algo
+            wo = torch.optim.Adam(wm.parameters(), lr=a_.world_model.optimizer.lr, eps=a_.world_model.optimizer.eps)
+            ao = torch.optim.Adam(actor.parameters(), lr=a_.actor.optimizer.lr, eps=a_.actor.optimizer.eps)
+            co = torch.optim.Adam(critic.parameters(), lr=a_.critic.optimizer.lr, eps=a_.critic.optimizer.eps)
+            mom = Moments(fab, 0.99, 1.0, 0.05, 0.95).to(DEV)
+            data = _to(harness.synthetic_batch(8, 4, od, acts, seed=3), DEV)
+            before = wm.state_dict()["rssm.recurrent_model.rnn.linear.weight"].clone()
+            train(fab, wm, actor, critic, target, wo, ao, co, data, Aggregator(), cfg, False, acts, mom)
+            assert not torch.equal(before, wm.state_dict()["rssm.recurrent_model.rnn.linear.weight"])
+
+
+def test_checkpoint_round_trip_on_gpu(tmp_path):
+    """Save -> file -> fresh process state -> resume, in the reference's checkpoint layout (dreamer_v3.py:781-791 writes it,
+    :452-455 / :475-477 / :489 read it): training continued from the file equals uninterrupted training, weights, optimizer moments,
+    return-normalisation state and noise stream included."""
+    from sheeprl_prey_b200.algos.dreamer_v3 import build_models, train
+    from sheeprl_prey_b200.algos.dreamer_v3.dreamer_v3 import Moments
+    from sheeprl_prey_b200.configs import ObsSpace
+    from util import Aggregator, FakeFabric
+
+    cfg = make_cfg("XS", batch_size=8, sequence_length=16, horizon=5)
+    acts, od = [6], {"state": 9}
+    fab = FakeFabric(DEV)
+    a = cfg.algo
+    batches = [_to(harness.synthetic_batch(16, 8, od, acts, seed=30 + i), DEV) for i in range(4)]
+
+    def make(seed, state=None):
+        torch.manual_seed(seed)
+        st = state or {}
+        wm, actor, critic, target = build_models(fab, acts, False, cfg, ObsSpace({"state": (9,)}), st.get("world_model"), st.get("actor"),
+                                                 st.get("critic"), st.get("target_critic"))
+        wo = torch.optim.Adam(wm.parameters(), lr=a.world_model.optimizer.lr, eps=a.world_model.optimizer.eps)
+        ao = torch.optim.Adam(actor.parameters(), lr=a.actor.optimizer.lr, eps=a.actor.optimizer.eps)
+        co = torch.optim.Adam(critic.parameters(), lr=a.critic.optimizer.lr, eps=a.critic.optimizer.eps)
+        mom = Moments(fab, 0.99, 1.0, 0.05, 0.95).to(DEV)
+        if state:
+            wo.load_state_dict(state["world_optimizer"])
+            ao.load_state_dict(state["actor_optimizer"])
+            co.load_state_dict(state["critic_optimizer"])
+            mom.load_state_dict(state["moments"])
+        return wm, actor, critic, target, wo, ao, co, mom
+
+    def steps(run, which):
+        wm, actor, critic, target, wo, ao, co, mom = run
+        out = []
+        for i in which:
+            agg = Aggregator()
+            train(fab, wm, actor, critic, target, wo, ao, co, {k: v.clone() for k, v in batches[i].items()}, agg, cfg, False, acts, mom)
+            out.append(dict(agg.values))
+        return out
+
+    run_a = make(0)
+    steps(run_a, [0, 1])
+    wm, actor, critic, target, wo, ao, co, mom = run_a
+    torch.save({"world_model": wm.state_dict(), "actor": actor.state_dict(), "critic": critic.state_dict(), "target_critic": target.state_dict(),
+                "world_optimizer": wo.state_dict(), "actor_optimizer": ao.state_dict(), "critic_optimizer": co.state_dict(),
+                "moments": mom.state_dict()}, tmp_path / "ckpt.ckpt")
+    metrics_a = steps(run_a, [2, 3])
+    state = torch.load(tmp_path / "ckpt.ckpt", map_location=DEV, weights_only=False)
+    run_b = make(123, state)                      # different initial weights: everything must come from the file
+    metrics_b = steps(run_b, [2, 3])
+    for ma, mb in zip(metrics_a, metrics_b):
+        for k in METRIC_KEYS:
+            assert abs(ma[k] - mb[k]) <= 1e-6 * max(1.0, abs(ma[k])), (k, ma[k], mb[k])
+    for mod_a, mod_b in zip(run_a[:4], run_b[:4]):
+        sa, sb = mod_a.state_dict(), mod_b.state_dict()
+        for k in sa:
+            assert torch.equal(sa[k], sb[k]), k
+    for oa, ob in ((run_a[4], run_b[4]), (run_a[5], run_b[5]), (run_a[6], run_b[6])):
+        for ia, ib in zip(oa.state_dict()["state"].values(), ob.state_dict()["state"].values()):
+            assert torch.equal(ia["exp_avg"], ib["exp_avg"]) and torch.equal(ia["exp_avg_sq"], ib["exp_avg_sq"]) and float(ia["step"]) == float(ib["step"])
+    assert torch.equal(run_a[7].low, run_b[7].low) and torch.equal(run_a[7].high, run_b[7].high)
+    assert int(run_a[7].rng_counter) == int(run_b[7].rng_counter) > 0
+
+
 def test_step_reproduces_reference_golden_at_baseline_size(cuda_ops):
     """BASELINE.json config 1 at its real shape (XS, obs 4 / Discrete(2), B16 x T64, H15) against the reference's own train() outputs
     (tests/golden/dv3_xs_b16t64.npz: inputs regenerated from the recorded seeds, fp32 mode)."""
@@ -521,7 +663,8 @@ def test_fused_reverse_scan_matches_per_step_composition(size, B, T, obs, acts, 
     assert max(worst.values()) < 3e-2, worst
 
 
-@pytest.mark.parametrize("size,B,T,H,obs,acts", [("S", 16, 64, 15, 14, [100]), ("XS", 16, 64, 15, 4, [2]), ("S", 8, 16, 4, 14, [7])])
+@pytest.mark.parametrize("size,B,T,H,obs,acts", [("S", 16, 64, 15, 14, [100]), ("XS", 16, 64, 15, 4, [2]), ("S", 8, 16, 4, 14, [7]),
+                                                    ("M", 8, 32, 3, 14, [18])])      # M: 80-wide slices, GRU as two 64-unit passes
 def test_fused_rollout_matches_per_op_rollout(size, B, T, H, obs, acts):
     """dv3_rollout_tc (the whole imagination rollout as one persistent kernel: TMA-fed tcgen05 layers, LayerNorm / GRU / sampling
     epilogues, cluster-wide feature split) against the per-op rollout on the same weights and start states, teacher-forced with the

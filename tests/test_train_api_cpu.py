@@ -117,3 +117,13 @@ def test_state_loaded_after_the_first_step_reaches_the_engine():
     wo.param_groups[0]["lr"] = 3e-5
     step()
     assert eng.opt_hparams["world"]["lr"] == 3e-5
+
+
+def test_checkpoint_round_trip_host_logic(tmp_path, monkeypatch):
+    """The save -> file -> resume test of the GPU suite (tests/test_step_gpu.py) run through the CPU seam: state_dict layout, optimizer
+    adoption and the noise counter carried by `moments.state_dict()` are host logic."""
+    import test_step_gpu as gpu_tests
+
+    monkeypatch.setattr(gpu_tests, "DEV", "cpu")
+    with cpu_ops():
+        gpu_tests.test_checkpoint_round_trip_on_gpu(tmp_path)
