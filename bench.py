@@ -464,6 +464,8 @@ def run_ours(args, rank, world, local_rank):
     dev = torch.device(f"cuda:{local_rank}")
     torch.cuda.set_device(dev)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"          # NCCL prints its version banner on stdout: keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     run = Run(args.size, args.precision, dev, world, rank, args.buffer)
     eng, wl = run.eng, run.wl

@@ -656,7 +656,7 @@ extern "C" int dv3_rollout_tc(const Dv3RolloutArgs* a, void* stream_) {
   mk(&k->m_thid, a->thid16, a->N, a->Hh, a->Hh, RM);
   for (int l = 0; l < a->L; ++l) mk(&k->m_act[l], a->aact16[l], M1, a->Ua, a->Ua, RM);
   mk(&k->m_wz, a->Wz16, a->U, a->S, a->ld_wz, uper);
-  mk(&k->m_wgru, a->Wgru16, 3 * a->D, a->D + a->U, a->ld_wgru, dper);
+  mk(&k->m_wgru, a->Wgru16, 3 * a->D, a->D + a->U, a->ld_wgru, dper < 64 ? dper : 64);      // one gate of one pass per box
   mk(&k->m_wt0, a->Wt016, a->Hh, a->D, a->ld_wt0, hper);
   mk(&k->m_wt1, a->Wt116, a->S, a->Hh, a->ld_wt1, sper);
   for (int l = 0; l < a->L; ++l) mk(&k->m_wa[l], a->Wa16[l], a->Ua, l == 0 ? a->lat : a->Ua, a->ld_wa[l], aper);

@@ -303,14 +303,16 @@ def test_checkpoint_round_trip_on_gpu(tmp_path):
     for ma, mb in zip(metrics_a, metrics_b):
         for k in METRIC_KEYS:
             assert abs(ma[k] - mb[k]) <= 1e-6 * max(1.0, abs(ma[k])), (k, ma[k], mb[k])
+    # not bit-exact: the split-K weight-gradient contractions accumulate with fp32 atomics, whose order varies from run to run
+    close = lambda x, y: float((x - y).abs().max()) <= 1e-5 * float(x.abs().max()) + 1e-12  # noqa: E731
     for mod_a, mod_b in zip(run_a[:4], run_b[:4]):
         sa, sb = mod_a.state_dict(), mod_b.state_dict()
         for k in sa:
-            assert torch.equal(sa[k], sb[k]), k
+            assert close(sa[k], sb[k]), k
     for oa, ob in ((run_a[4], run_b[4]), (run_a[5], run_b[5]), (run_a[6], run_b[6])):
         for ia, ib in zip(oa.state_dict()["state"].values(), ob.state_dict()["state"].values()):
-            assert torch.equal(ia["exp_avg"], ib["exp_avg"]) and torch.equal(ia["exp_avg_sq"], ib["exp_avg_sq"]) and float(ia["step"]) == float(ib["step"])
-    assert torch.equal(run_a[7].low, run_b[7].low) and torch.equal(run_a[7].high, run_b[7].high)
+            assert close(ia["exp_avg"], ib["exp_avg"]) and close(ia["exp_avg_sq"], ib["exp_avg_sq"]) and float(ia["step"]) == float(ib["step"]) == 4.0
+    assert close(run_a[7].low, run_b[7].low) and close(run_a[7].high, run_b[7].high)
     assert int(run_a[7].rng_counter) == int(run_b[7].rng_counter) > 0
 
 
