@@ -303,18 +303,52 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       }
     }
   };
+  // ---- staged stores.  With thread = row every global store of the epilogue would touch 32 different cache lines (16 B used of each
+  // 32 B sector): measured, the LSU then bounds the stage (8-22 k clk per epilogue).  The TMA ring is idle between the stage's last
+  // MMA (acc_bar) and the cluster barrier that ends the stage, so results are parked there as fp32 [RM][n + 4] tiles (pitch = 16 mod
+  // 64 B: conflict-free 16 B accesses for thread = row) and written out row-contiguously by all 16 warps; the proxy fence of
+  // end_stage orders these generic-proxy writes before the next stage's TMA writes to the same bytes.
+  float* stg0 = reinterpret_cast<float*>(ring_a);
+  float* stg1 = reinterpret_cast<float*>(ring_a + 72 * 1024);
+  const int etid = tid - 64;
+  auto sts8 = [](float* dst, const float* v) {
+    *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  };
+  auto lds8 = [](const float* src, float* v) {
+    const float4 a0 = *reinterpret_cast<const float4*>(src), a1 = *reinterpret_cast<const float4*>(src + 4);
+    v[0] = a0.x; v[1] = a0.y; v[2] = a0.z; v[3] = a0.w; v[4] = a1.x; v[5] = a1.y; v[6] = a1.z; v[7] = a1.w;
+  };
+  // tile [RM][n] (pitch floats) -> rows grow0.. of a global fp32 matrix (and / or its bf16 mirror) at column col0; all epilogue threads
+  auto write_tile = [&](const float* tile, int pitch, int n, float* g32, __nv_bfloat16* g16, size_t grow0, int ld, int col0) {
+    const int n4 = n >> 2, total = RM * n4;
+    for (int i = etid; i < total; i += NEPI) {
+      const int r = i / n4, c4 = i - r * n4;
+      const float4 v = *reinterpret_cast<const float4*>(tile + r * pitch + 4 * c4);
+      const size_t o = (grow0 + r) * (size_t)ld + col0 + 4 * c4;
+      if (g32) *reinterpret_cast<float4*>(g32 + o) = v;
+      if (g16) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(g16 + o) = pk;
+      }
+    }
+  };
   auto ln_silu_epilogue = [&](int n, const float* bias, const float* gamma, const float* beta, float eps, const float* add_tab, int add_ld,
                               const int* add_idx, float* pre, float* act, __nv_bfloat16* act16, int ld_out, size_t grow, int col0, float* gmean,
                               float* grstd) {
     const int nq = (((n + 3) >> 2) + 7) & ~7, cb = cq * nq;   // this thread's columns [cb, min(cb + nq, n)) of the CTA's n (n % 8 == 0)
+    const int pitch = n + 4;
     float s = 0.f, q = 0.f;
 #pragma unroll 1
-    for (int c0 = 0; c0 < nq && cb + c0 < n; c0 += 8) {
+    for (int c0 = 0; c0 < nq && cb + c0 < n; c0 += 8) {       // one TMEM pass: statistics; the pre-LayerNorm values wait in stg1
       float x[8];
       chunk(cb + c0, col0 + cb + c0, bias, add_tab, add_ld, add_idx, x);
 #pragma unroll
       for (int j = 0; j < 8; ++j) { s += x[j]; q = fmaf(x[j], x[j], q); }
-      if (pre) st8_f32(pre + grow * ld_out + col0 + cb + c0, x);
+      sts8(stg1 + rl * pitch + cb + c0, x);
     }
     float mu, rs;
     ln_exchange(s, q, n, eps, mu, rs);
@@ -323,15 +357,18 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     for (int c0 = 0; c0 < nq && cb + c0 < n; c0 += 8) {
       float x[8];
       const int gcol = col0 + cb + c0;
-      chunk(cb + c0, gcol, bias, add_tab, add_ld, add_idx, x);
+      lds8(stg1 + rl * pitch + cb + c0, x);                   // (own values)
       const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + gcol)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + gcol + 4));
       const float4 e0 = __ldg(reinterpret_cast<const float4*>(beta + gcol)), e1 = __ldg(reinterpret_cast<const float4*>(beta + gcol + 4));
       const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w}, bb[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
 #pragma unroll
       for (int j = 0; j < 8; ++j) { const float t = (x[j] - mu) * rs * gg[j] + bb[j]; x[j] = t * fsigmoid(t); }
-      if (act) st8_f32(act + grow * ld_out + gcol, x);
-      st8_bf16(act16 + grow * ld_out + gcol, x);
+      sts8(stg0 + rl * pitch + cb + c0, x);
     }
+    epi_bar();
+    const size_t grow0 = grow - (size_t)rl;
+    if (pre) write_tile(stg1, pitch, n, pre, nullptr, grow0, ld_out, col0);
+    write_tile(stg0, pitch, n, act, act16, grow0, ld_out, col0);
   };
   auto wait_acc = [&]() {
     RDBG();
@@ -393,7 +430,12 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
             const int col = cb + j;
             x[j] = (col < dim) ? x[j] + __ldg(a.bh + col) : -INFINITY;
             mx = fmaxf(mx, x[j]);
-            if (col < dim) a.aout[grow * A + col] = x[j];
+          }
+          const int hpitch = npad + 4;
+          if (cb < npad) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8)
+              if (cb + j < npad) sts8(stg0 + rl * hpitch + cb + j, x + j);
           }
           red[cq * RM + rl].x = mx;
           epi_bar();
@@ -433,6 +475,11 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
             int idx = __float_as_int(red[rl].y) + __float_as_int(red[RM + rl].y) + __float_as_int(red[2 * RM + rl].y) + __float_as_int(red[3 * RM + rl].y);
             idx = min(idx, dim - 1);
             a.act_idx[grow] = a.f_act ? a.f_act[grow] : idx;
+          }
+          // the block's logits are one contiguous piece of the [M1][A] output: coalesced copy from the staged tile
+          for (int e = etid; e < RM * A; e += NEPI) {
+            const int r = e / A, col = e - r * A;
+            a.aout[((size_t)arow) * A + e] = stg0[r * hpitch + col];
           }
         }
       }
@@ -475,7 +522,16 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       else {
         wait_acc();
         const int dq = dper >> 2, db = cq * dq;            // this thread: units [db, db + dq) of the CTA's dper, 8 at a time
+        const int hpitch = dper + 4;
         auto gate_col = [&](int ul, int g) { const int ps = ul / dpp; return ps * 3 * dpp + g * dpp + (ul - ps * dpp); };
+        {   // h_{i-1}[:, d0 .. d0 + dper) of the block's rows -> stg1, row-contiguous cp.async in the shadow of the statistics pass
+          const int n4 = dper >> 2, total = RM * n4;
+          for (int e = etid; e < total; e += NEPI) {
+            const int r = e / n4, c4 = e - r * n4;
+            const float* src = a.traj + ((size_t)prow + r) * lat + S + d0 + 4 * c4;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stg1 + r * hpitch + 4 * c4)), "l"(src) : "memory");
+          }
+        }
         float s = 0.f, q = 0.f;
 #pragma unroll 1
         for (int c0 = 0; c0 < dq; c0 += 8) {
@@ -489,19 +545,17 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
             q = fmaf(vr[j], vr[j], fmaf(vc[j], vc[j], fmaf(vu[j], vu[j], q)));
           }
         }
+        asm volatile("cp.async.wait_all;" ::: "memory");   // (own copies; the barrier inside ln_exchange publishes everyone's)
         float mu, rs;
         ln_exchange(s, q, 3 * dper, 1e-5f, mu, rs);
 #pragma unroll 1
         for (int c0 = 0; c0 < dq; c0 += 8) {
-          float vr[8], vc[8], vu[8];
+          float vr[8], vc[8], vu[8], hv[8], hn[8];
           ld8(gate_col(db + c0, 0), vr);
           ld8(gate_col(db + c0, 1), vc);
           ld8(gate_col(db + c0, 2), vu);
+          lds8(stg1 + rl * hpitch + db + c0, hv);
           const int d = d0 + db + c0;
-          const float* hp = a.traj + gp * lat + S + d;
-          const float4 h0_ = *reinterpret_cast<const float4*>(hp), h1_ = *reinterpret_cast<const float4*>(hp + 4);
-          const float hv[8] = {h0_.x, h0_.y, h0_.z, h0_.w, h1_.x, h1_.y, h1_.z, h1_.w};
-          float hn[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float r = fsigmoid((vr[j] - mu) * rs * __ldg(a.g_gru + d + j) + __ldg(a.b_gru + d + j));
@@ -510,9 +564,10 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
             const float u = fsigmoid((vu[j] - mu) * rs * __ldg(a.g_gru + 2 * D + d + j) + __ldg(a.b_gru + 2 * D + d + j) - 1.f);
             hn[j] = u * cd + (1.f - u) * hv[j];
           }
-          st8_f32(a.traj + gc * lat + S + d, hn);
-          st8_bf16(traj16 + gc * lat + S + d, hn);
+          sts8(stg0 + rl * hpitch + db + c0, hn);
         }
+        epi_bar();
+        write_tile(stg0, hpitch, dper, a.traj, traj16, (size_t)crow, lat, S + d0);
       }
       end_stage();
     }
@@ -586,15 +641,27 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
             }
             idx = min(idx, Kc - 1);
           }
-          a.z_idx[zi] = idx;
-          float* zo = a.traj + gc * lat + s0 + gl * Kc;
-          __nv_bfloat16* zo16 = traj16 + gc * lat + s0 + gl * Kc;
-          for (int j = 0; j < Kc; j += 8) {
-            float oh[8];
-#pragma unroll
-            for (int jj = 0; jj < 8; ++jj) oh[jj] = (j + jj == idx) ? 1.f : 0.f;
-            st8_f32(zo + j, oh);
-            st8_bf16(zo16 + j, oh);
+          reinterpret_cast<int*>(stg0)[rl * gper + gl] = idx;
+        }
+        epi_bar();
+        {   // write-out, row-contiguous: the sampled indices and their one-hot rows (fp32 trajectory + bf16 mirror)
+          const int* zs = reinterpret_cast<const int*>(stg0);
+          for (int e = etid; e < RM * gper; e += NEPI) {
+            const int r = e / gper, gl = e - r * gper;
+            a.z_idx[((size_t)(i - 1) * N + row_blk + r) * G + c * gper + gl] = zs[e];
+          }
+          const int n4 = sper >> 2, total = RM * n4;
+          for (int e = etid; e < total; e += NEPI) {
+            const int r = e / n4, col = (e - r * n4) << 2;
+            const int gl = col / Kc, k0 = col - gl * Kc, idx = zs[r * gper + gl];
+            const float4 v = make_float4(k0 == idx ? 1.f : 0.f, k0 + 1 == idx ? 1.f : 0.f, k0 + 2 == idx ? 1.f : 0.f, k0 + 3 == idx ? 1.f : 0.f);
+            const size_t o = ((size_t)crow + r) * lat + s0 + col;
+            *reinterpret_cast<float4*>(a.traj + o) = v;
+            __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t*>(&lo);
+            pk.y = *reinterpret_cast<uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(traj16 + o) = pk;
           }
         }
       }
