@@ -18,7 +18,12 @@
 //                     (A first version with one thread per row and 4 epilogue warps was latency-starved: 57-75 k clk per stage.)
 // The layer outputs of all CTAs of a cluster form the next layer's input: they meet in L2-resident global buffers (the trajectory
 // and actor-activation buffers that the behaviour phase needs anyway) and are re-read by TMA after a cluster barrier; generic-proxy
-// stores are ordered before the async-proxy reads with fence.proxy.async.  All TMA loads read this GPU's memory only.
+// stores are ordered before the async-proxy reads with fence.proxy.async.
+// The 128-row activation tile of a k-block is the same for all CL CTAs of a cluster: each CTA loads RM / CL of its rows and multicasts
+// them into every CTA's ring slot (cp.async.bulk.tensor ... .multicast::cluster), so the tile crosses L2 -> SM once per cluster
+// instead of CL times; ring slots are therefore recycled cluster-wide (every MMA warp commits to every CTA's empty barrier).  TMA
+// multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU: the
+// host entry point refuses buffers that are not allocations of the launching device.
 #include "common.cuh"
 #include "dv3_b200.h"
 #include <cuda.h>
@@ -77,6 +82,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void tma_load_2d(uint32_t smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c_inner, int c_outer) {
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_dst),
                "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c_inner, int c_outer, uint16_t mask) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+               ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer), "h"(mask) : "memory");
 }
 __device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr) {   // K-major SWIZZLE_128B: SBO 1024, version 1, layout 2
   uint64_t d = 0;
@@ -145,7 +154,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
 
   for (int i = tid; i < NSTG * (A_BYTES + B_BYTES) / 16; i += NTHR) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
   if (tid == 0) {
-    for (int s = 0; s < NSTG; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < NSTG; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], (uint32_t)k.CL); }   // a slot is free when ALL CTAs' MMAs left it
     mbar_init(acc_bar, 1);
     mbar_init(stat_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -168,6 +177,9 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   uint32_t acc_par = 0, stat_par = 0;
 
   // ---- the three roles of one stage -------------------------------------------------------------------------------------------------
+  const int a_slice_row = c * (RM / CL);
+  const uint32_t a_slice_off = (uint32_t)a_slice_row * KB * 2;
+  const uint16_t mc_mask = (uint16_t)((1u << CL) - 1u);
   auto produce = [&](const Stage& st) {
     const int nk0 = st.K0 / KB, nk = nk0 + st.K1 / KB;
     const uint32_t bytes = A_BYTES + (uint32_t)st.nb * st.b_rows * KB * 2;
@@ -180,8 +192,9 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
         if (elect_one()) {
           mbar_expect_tx(&full_bar[pp.slot], bytes);
           const uint32_t da = smem_u32(ring_a + pp.slot * A_BYTES), db = smem_u32(ring_b + pp.slot * B_BYTES);
-          if (kb < nk0) tma_load_2d(da, st.a0, &full_bar[pp.slot], st.a0_col + kb * KB, st.a0_row);
-          else tma_load_2d(da, st.a1, &full_bar[pp.slot], st.a1_col + (kb - nk0) * KB, st.a1_row);
+          // own RM / CL rows of the activation tile, multicast into the same slot of every CTA of the cluster (this GPU's memory only)
+          if (kb < nk0) tma_load_2d_mc(da + a_slice_off, st.a0, &full_bar[pp.slot], st.a0_col + kb * KB, st.a0_row + a_slice_row, mc_mask);
+          else tma_load_2d_mc(da + a_slice_off, st.a1, &full_bar[pp.slot], st.a1_col + (kb - nk0) * KB, st.a1_row + a_slice_row, mc_mask);
           for (int j = 0; j < st.nb; ++j) tma_load_2d(db + (uint32_t)j * st.b_rows * KB * 2, st.b, &full_bar[pp.slot], kb * KB, st.b_row[j] + roff);
         }
         __syncwarp();
@@ -210,7 +223,8 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
                          "l"(ad + (uint64_t)(kk * 2)), "l"(bd + (uint64_t)(kk * 2)), "r"(idesc), "r"(accum) : "memory");
         }
         if (elect_one()) {
-          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[pp.slot])) : "memory");
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(&empty_bar[pp.slot])),
+                       "h"(mc_mask) : "memory");
           if (last_pass && kb == nk - 1)
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(acc_bar)) : "memory");
         }
@@ -414,11 +428,13 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       st.a0 = &k.m_act[L - 1]; st.a0_col = 0; st.a0_row = arow; st.K0 = Ua;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
       st.b = &k.m_wh; st.nb = 1; st.b_row[0] = 0; st.b_rows = A; st.n_pad = (A + 15) & ~15; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
-      if (c == 0) {
-        if (warp == 0) produce(st);
-        else if (warp == 1) issue(st);
-        else {
-          wait_acc();
+      // every CTA runs the head's loads and MMAs (the ring positions and the cluster-wide slot barriers stay in lockstep); only CTA 0
+      // has an epilogue: all action logits of a row live there
+      if (warp == 0) produce(st);
+      else if (warp == 1) issue(st);
+      else {
+        wait_acc();
+        if (c == 0) {
           // this thread: logits [32 cq, 32 cq + 32) of the row, in registers (one TMEM pass, one exponential per logit); the four
           // quarters meet in shared memory for the row maximum, the softmax denominator, the total unimix mass and the draw
           const int dim = a.head_dim[0], cb = 32 * cq, npad = st.n_pad;
@@ -705,6 +721,21 @@ extern "C" int dv3_rollout_tc(const Dv3RolloutArgs* a, void* stream_) {
   const int CL = pick_cluster(a);
   if (!CL) return DV3_ERR_UNSUPPORTED;
   const int M1 = (a->H + 1) * a->N;
+  {   // the multicast loads must read allocations of the launching device only (first and last byte of every activation buffer)
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return DV3_ERR_UNSUPPORTED;
+    auto local = [&](const void* p, size_t bytes) {
+      for (const char* q : {static_cast<const char*>(p), static_cast<const char*>(p) + bytes - 1}) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, q) != cudaSuccess) { cudaGetLastError(); return false; }
+        if (at.type != cudaMemoryTypeDevice || at.device != dev) return false;
+      }
+      return true;
+    };
+    bool ok = local(a->traj16, (size_t)M1 * a->lat * 2) && local(a->feat16, (size_t)a->N * a->U * 2) && local(a->thid16, (size_t)a->N * a->Hh * 2);
+    for (int l = 0; l < a->L && ok; ++l) ok = local(a->aact16[l], (size_t)M1 * a->Ua * 2);
+    if (!ok) return DV3_ERR_UNSUPPORTED;
+  }
   RollK* k = new RollK;
   k->a = *a;
   k->CL = CL;
@@ -718,10 +749,11 @@ extern "C" int dv3_rollout_tc(const Dv3RolloutArgs* a, void* stream_) {
     if (!rc) rc = dv3_internal_make_map_2d(tm, base, (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld, (unsigned)box_rows, KB);
   };
   const int uper = a->U / CL, dper = a->D / CL, hper = a->Hh / CL, sper = (a->G / CL) * a->Kc, aper = a->Ua / CL;
-  mk(&k->m_traj, a->traj16, M1, a->lat, a->lat, RM);
-  mk(&k->m_feat, a->feat16, a->N, a->U, a->U, RM);
-  mk(&k->m_thid, a->thid16, a->N, a->Hh, a->Hh, RM);
-  for (int l = 0; l < a->L; ++l) mk(&k->m_act[l], a->aact16[l], M1, a->Ua, a->Ua, RM);
+  // activation maps: one box = the RM / CL rows a CTA multicasts to its cluster
+  mk(&k->m_traj, a->traj16, M1, a->lat, a->lat, RM / CL);
+  mk(&k->m_feat, a->feat16, a->N, a->U, a->U, RM / CL);
+  mk(&k->m_thid, a->thid16, a->N, a->Hh, a->Hh, RM / CL);
+  for (int l = 0; l < a->L; ++l) mk(&k->m_act[l], a->aact16[l], M1, a->Ua, a->Ua, RM / CL);
   mk(&k->m_wz, a->Wz16, a->U, a->S, a->ld_wz, uper);
   mk(&k->m_wgru, a->Wgru16, 3 * a->D, a->D + a->U, a->ld_wgru, dper < 64 ? dper : 64);      // one gate of one pass per box
   mk(&k->m_wt0, a->Wt016, a->Hh, a->D, a->ld_wt0, hper);
