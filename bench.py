@@ -164,13 +164,16 @@ def run_reference(args, rank):
     wl = WORKLOADS[args.size]
     v, cores, sample = cpu_reference(args.size, steps, warmup, n_ranks=args.gpus)
     gb = wl["B"] * args.gpus
-    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "steps/s", "n_gpus": args.gpus,
+    # the GPU arm's `value` counts per-rank B16 x T64 steps summed over ranks; one CPU step at the global batch is worth n_gpus of them
+    v_job = v * args.gpus
+    line = {"impl": "reference", "metric": METRIC, "value": v_job, "unit": "steps/s", "n_gpus": args.gpus,
             "steps": steps, "warmup": warmup, "ms_per_step": 1000.0 / v, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"] + f", B{wl['B']}xT{T_SEQ}, H{HORIZON}", "global_batch": gb, "seq_len": T_SEQ,
-                       "sequences_per_s": v * gb, "note": "one CPU process at the GPU arm's global batch (per-rank batch x n_gpus): equal work per step"},
-            "cpu_baseline": {"value": v, "unit": "steps/s", "cores": cores, "kind": "port", "sample": sample},
-            "e2e": {"value": v, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+                       "sequences_per_s": v * gb, "global_steps_per_s": v,
+                       "note": "one CPU process at the GPU arm's global batch (per-rank batch x n_gpus): equal work per step; value = global steps/s x n_gpus"},
+            "cpu_baseline": {"value": v_job, "unit": "steps/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": v_job, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
@@ -531,7 +534,7 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            v, cores, sample = cpu_reference(args.size, 2, 1)
+            v, cores, sample = cpu_reference(args.size, 16 if args.size in ("S", "XS") else 2, 2)      # ~10 s of host work at config S
             cpu = {"value": v, "unit": "steps/s", "cores": cores, "kind": "port", "sample": sample}
         ws_gb = torch.cuda.max_memory_allocated(dev) / 1e9
         B, T, H = wl["B"], T_SEQ, HORIZON
@@ -637,7 +640,7 @@ def run_microbench(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--size", default="S", choices=sorted(WORKLOADS))
