@@ -95,6 +95,20 @@ int dv3_col_reduce_noalloc(int M, int U, const float* d, int ldd, const float* x
 int dv3_im2col_k4s2p1(int N, int H, int W, int C, const float* x, float* col, void* col_bf16, void* stream);
 int dv3_col2im_k4s2p1(int N, int Hi, int Wi, int C, const float* col, const float* bias, float add, float* y, void* stream);
 int dv3_permute_last2(int A, int B, int C, const float* src, long long lds, float* dst, long long ldd, void* stream);
+/* The two narrow-channel layers (image channels C = 1, 3 or 4) without im2col / col2im and without a GEMM (csrc/conv_direct.cu):
+ *  - first encoder layer (agent.py:28-80): y[(n,oh,ow)][o] = sum_k col(x)[.][k] * w[o][k], w = [O][16*C] tap-major (ldw), O <= 96;
+ *    with gamma != NULL also act = SiLU(LayerNormChannelLast(y)) (+ bf16 copy), mean, rstd.  The same call with the image-shaped
+ *    output gradient as x and the re-ordered transposed-convolution weight [C_in][16*C] as w is the data gradient of the last
+ *    decoder layer (agent.py:136-206).
+ *  - weight gradient of either layer: dw[a][k] = sum_rows g[row][a] * col(x)[row][k], A <= 64 (two-stage, deterministic).
+ *  - last decoder layer: y[n][oh][ow][c] = bias[c] + add + sum_{taps,ci} x[(n,ih,iw)][ci] * w[ci][(kh*4+kw)*C + c], w = [Ci][16*C]. */
+int dv3_conv_k4s2p1_narrow_fwd(int N, int H, int W, int C, int O, const float* x, const float* w, int ldw, float* y, const float* gamma,
+                               const float* beta, float eps, float* act, void* act_bf16, float* mean, float* rstd, void* stream);
+size_t dv3_conv_k4s2p1_narrow_wgrad_scratch_bytes(int N, int H, int W, int C, int A);
+int dv3_conv_k4s2p1_narrow_wgrad(int N, int H, int W, int C, int A, const float* x, const float* g, float* dw, int lddw, float* scratch,
+                                 size_t scratch_bytes, void* stream);
+int dv3_deconv_k4s2p1_narrow_fwd(int N, int Hi, int Wi, int Ci, int C, const float* x, const float* w, int ldw, const float* bias, float add,
+                                 float* y, void* stream);
 int dv3_u8_nchw_to_nhwc(int N, int C, int HW, const unsigned char* src, float scale, float* dst, int Ctot, int c_off, void* stream);
 /* warp-per-row variants of dv3_ln_act_fwd / _bwd for narrow rows (channel LayerNorm over N*H*W pixel rows) */
 int dv3_ln_act_fwd_rows(int M, int U, const float* x, int ldx, const float* gamma, const float* beta, float eps, int act,

@@ -35,6 +35,10 @@ SIGNATURES = {
     "dv3_im2col_k4s2p1": [_i, _i, _i, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_col2im_k4s2p1": [_i, _i, _i, _i, c_fp, c_fp, _f, c_fp, c_fp],
     "dv3_permute_last2": [_i, _i, _i, c_fp, _ll, c_fp, _ll, c_fp],
+    "dv3_conv_k4s2p1_narrow_fwd": [_i, _i, _i, _i, _i, c_fp, c_fp, _i, c_fp, c_fp, c_fp, _f, c_fp, c_fp, c_fp, c_fp, c_fp],
+    "dv3_conv_k4s2p1_narrow_wgrad_scratch_bytes": [_i, _i, _i, _i, _i],
+    "dv3_conv_k4s2p1_narrow_wgrad": [_i, _i, _i, _i, _i, c_fp, c_fp, c_fp, _i, c_fp, _sz, c_fp],
+    "dv3_deconv_k4s2p1_narrow_fwd": [_i, _i, _i, _i, _i, c_fp, c_fp, _i, c_fp, _f, c_fp, c_fp],
     "dv3_u8_nchw_to_nhwc": [_i, _i, _i, c_fp, _f, c_fp, _i, _i, c_fp],
     "dv3_ln_act_fwd_rows": [_i, _i, c_fp, _i, c_fp, c_fp, _f, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp],
     "dv3_ln_act_bwd_rows": [_i, _i, c_fp, _i, c_fp, _i, c_fp, c_fp, c_fp, c_fp, _i, c_fp, _i, c_fp, _i, c_fp, c_fp],
@@ -82,7 +86,7 @@ SIGNATURES = {
     "dv3_fill": [_sz, c_fp, _f, c_fp],
     "dv3_uniform_fill": [_sz, c_fp, _ull, c_fp, c_fp],
 }
-_RESTYPE = {"dv3_col_reduce_scratch_bytes": _sz, "dv3_adam_clip_scratch_bytes": _sz, "dv3_rssm_observe_fwd_scratch_bytes": _sz}
+_RESTYPE = {"dv3_conv_k4s2p1_narrow_wgrad_scratch_bytes": _sz, "dv3_col_reduce_scratch_bytes": _sz, "dv3_adam_clip_scratch_bytes": _sz, "dv3_rssm_observe_fwd_scratch_bytes": _sz}
 
 
 class ScanFwdArgs(C.Structure):
@@ -471,6 +475,44 @@ class CudaOps:
         assert col.is_contiguous() and y.is_contiguous() and y.numel() == N * Hi * Wi * 4 * Cc
         self.launches += 1
         _chk(self.lib.dv3_col2im_k4s2p1(N, Hi, Wi, Cc, _p(col), _p(bias), float(add), _p(y), self._s()), "dv3_col2im_k4s2p1")
+
+    def conv_narrow_fwd(self, x, N, H, W, Cc, w, y, gamma=None, beta=None, eps=1e-3, act=None, mean=None, rstd=None) -> bool:
+        """Direct k4-s2-p1 convolution of a narrow-channel image (first encoder layer / data gradient of the last decoder layer), with the
+        channel LayerNorm + SiLU fused when gamma is given.  False = shape outside the kernel's plan (caller: im2col + contraction)."""
+        pw, O, K, ldw = _mat(w)
+        assert x.is_contiguous() and y.is_contiguous() and K == 16 * Cc and y.numel() == N * (H // 2) * (W // 2) * O
+        rc = self.lib.dv3_conv_k4s2p1_narrow_fwd(N, H, W, Cc, O, _p(x), pw, ldw, _p(y), _p(gamma), _p(beta), float(eps), _p(act),
+                                                 None if act is None else self._m16(_p(act)), _p(mean), _p(rstd), self._s())
+        if rc == -2:
+            return False
+        _chk(rc, "dv3_conv_k4s2p1_narrow_fwd")
+        self.launches += 1
+        return True
+
+    def conv_narrow_wgrad(self, x, N, H, W, Cc, g, dw) -> bool:
+        """dw[a][k] = sum_rows g[row][a] * col(x)[row][k] for a narrow-channel image x (no im2col buffer)."""
+        pg, rows, A, ldg = _mat(g)
+        pd, A2, K, lddw = _mat(dw)
+        assert x.is_contiguous() and ldg == A and A2 == A and K == 16 * Cc and rows == N * (H // 2) * (W // 2)
+        rc = self.lib.dv3_conv_k4s2p1_narrow_wgrad(N, H, W, Cc, A, _p(x), pg, pd, lddw, self.scratch.data_ptr(), self.scratch.numel() * 4, self._s())
+        if rc == -2:
+            return False
+        _chk(rc, "dv3_conv_k4s2p1_narrow_wgrad")
+        self.launches += 2
+        self.refresh(dw)
+        return True
+
+    def deconv_narrow_fwd(self, x, N, Hi, Wi, w, Cc, bias, add, y) -> bool:
+        """Transposed k4-s2-p1 convolution to a narrow-channel image (last decoder layer): GEMM + col2im in one kernel."""
+        px, rows, Ci, ldx = _mat(x)
+        pw, Ci2, K, ldw = _mat(w)
+        assert ldx == Ci and Ci2 == Ci and K == 16 * Cc and rows == N * Hi * Wi and y.is_contiguous() and y.numel() == rows * 4 * Cc
+        rc = self.lib.dv3_deconv_k4s2p1_narrow_fwd(N, Hi, Wi, Ci, Cc, px, pw, ldw, _p(bias), float(add), _p(y), self._s())
+        if rc == -2:
+            return False
+        _chk(rc, "dv3_deconv_k4s2p1_narrow_fwd")
+        self.launches += 1
+        return True
 
     def permute_last2(self, src, A, Bn, Cn, dst, lds=None, ldd=None):
         """dst[a][c][b] = src[a][b][c]; lds / ldd = element stride between consecutive a (default B*C)."""

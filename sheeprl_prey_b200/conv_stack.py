@@ -11,11 +11,20 @@ gradients are re-ordered back into the flat gradient arena.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, List, Optional, Sequence
 
 import torch
 
 Tensor = torch.Tensor
+
+
+def _direct(ops) -> bool:
+    """The narrow-channel layers (image <-> first / last feature map) as direct kernels (csrc/conv_direct.cu) instead of
+    im2col / col2im + contraction.  Opt-in ($DV3_CONV_DIRECT=1): at config M the CUDA-core kernels are correct but not faster than the
+    contractions they replace (tools/conv_direct_bench.py: first layer forward 0.34 vs 0.58 ms, but weight gradient 0.40 vs 0.11 ms and
+    last layer forward 0.53 vs 0.39 ms), so the step rate does not move (64.8 vs 64.9 steps/s)."""
+    return hasattr(ops, "conv_narrow_fwd") and os.environ.get("DV3_CONV_DIRECT", "0") == "1"
 
 
 def _mirror(ops, *tensors) -> None:
@@ -75,9 +84,12 @@ class ConvEncoder:
         for l, L in enumerate(self.layers):
             H, Cin, Cout, rows = self.dims[l]
             ops.permute_last2(L["w"], Cout, Cin, 16, self.wt[l])                       # [Cout][Cin][16] -> [Cout][16][Cin]
-            ops.im2col(x, self.N, H, H, Cin, self.col[l])
-            ops.gemm("NT", self.col[l], self.wt[l], self.pre[l])
-            ops.ln_act_fwd(self.pre[l], L["g"], L["beta"], 1e-3, 1, self.act[l], self.mean[l], self.rstd[l])
+            self.direct0 = l == 0 and _direct(ops) and ops.conv_narrow_fwd(x, self.N, H, H, Cin, self.wt[l], self.pre[l], L["g"], L["beta"], 1e-3,
+                                                                           self.act[l], self.mean[l], self.rstd[l])
+            if not (l == 0 and self.direct0):
+                ops.im2col(x, self.N, H, H, Cin, self.col[l])
+                ops.gemm("NT", self.col[l], self.wt[l], self.pre[l])
+                ops.ln_act_fwd(self.pre[l], L["g"], L["beta"], 1e-3, 1, self.act[l], self.mean[l], self.rstd[l])
             x = self.act[l]
         # [N][HW][C] -> [N][C][HW]: the reference flattens NCHW (nn.Flatten(-3,-1), agent.py:73)
         HW = self.H_last * self.H_last
@@ -96,7 +108,10 @@ class ConvEncoder:
             dpre = self._dpre[: rows * Cout].view(rows, Cout)
             dln = self._dln[: rows * Cout].view(rows, Cout)
             ops.ln_act_bwd_fused(dact, self.pre[l], L["g"], L["beta"], self.mean[l], self.rstd[l], 1, dpre, dln, L["dg"], L["dbeta"], None)
-            ops.gemm("TN", dpre, self.col[l], self.dwt[l])
+            if not (l == 0 and getattr(self, "direct0", False) and ops.conv_narrow_wgrad(self.x0, self.N, H, H, Cin, dpre, self.dwt[l])):
+                if l == 0 and getattr(self, "direct0", False):
+                    ops.im2col(self.x0, self.N, H, H, Cin, self.col[l])                 # (the direct forward did not build it)
+                ops.gemm("TN", dpre, self.col[l], self.dwt[l])
             ops.permute_last2(self.dwt[l], Cout, 16, Cin, L["dw"])                     # back to [Cout][Cin][16]
             if l > 0:
                 dcol = self.col[l]                                                     # its forward content is no longer needed
@@ -149,8 +164,9 @@ class ConvDecoder:
         for l, L in enumerate(self.layers):
             H, Cin, Cout, rows_in, rows_out = self.dims[l]
             ops.permute_last2(L["w"], Cin, Cout, 16, self.wr[l])                    # [Cin][Cout][16] -> [Cin][16][Cout]
-            ops.gemm("NN", x, self.wr[l], self.colT[l])
-            ops.col2im(self.colT[l], self.N, H, H, Cout, L.get("b"), 0.5 if l == last else 0.0, self.pre[l])
+            if not (l == last and _direct(ops) and ops.deconv_narrow_fwd(x, self.N, H, H, self.wr[l], Cout, L.get("b"), 0.5, self.pre[l])):
+                ops.gemm("NN", x, self.wr[l], self.colT[l])
+                ops.col2im(self.colT[l], self.N, H, H, Cout, L.get("b"), 0.5 if l == last else 0.0, self.pre[l])
             if L.get("g") is not None:
                 ops.ln_act_fwd(self.pre[l], L["g"], L["beta"], 1e-3, 1, self.act[l], self.mean[l], self.rstd[l])
                 x = self.act[l]
@@ -177,13 +193,17 @@ class ConvDecoder:
                 dpre = dout
             if L.get("b") is not None:
                 ops.colsum(dpre, L["db"])
-            dcolT = self.colT[l]                                                     # forward content no longer needed
-            ops.im2col(dpre, self.N, 2 * H, 2 * H, Cout, dcolT)
             x_in = self.x0 if l == 0 else self.act[l - 1]
-            ops.gemm("TN", x_in, dcolT, self.dwr[l])
-            ops.permute_last2(self.dwr[l], Cin, 16, Cout, L["dw"])                  # back to [Cin][Cout][16]
             dx = self._dx[: rows_in * Cin].view(rows_in, Cin)
-            ops.gemm("NT", dcolT, self.wr[l], dx)
+            if (l == last and _direct(ops) and dpre.is_contiguous() and ops.conv_narrow_wgrad(dpre, self.N, 2 * H, 2 * H, Cout, x_in, self.dwr[l])
+                    and ops.conv_narrow_fwd(dpre, self.N, 2 * H, 2 * H, Cout, self.wr[l], dx)):
+                pass                                                                 # weight and data gradient straight from the image-shaped dpre
+            else:
+                dcolT = self.colT[l]                                                 # forward content no longer needed
+                ops.im2col(dpre, self.N, 2 * H, 2 * H, Cout, dcolT)
+                ops.gemm("TN", x_in, dcolT, self.dwr[l])
+                ops.gemm("NT", dcolT, self.wr[l], dx)
+            ops.permute_last2(self.dwr[l], Cin, 16, Cout, L["dw"])                  # back to [Cin][Cout][16]
             dout = dx
         ops.permute_last2(dout, self.N, 16, self.C0, self.dlin_out)                 # -> [N][C][16]
         ops.gemm("TN", self.dlin_out, latent, self.lin["dw"])

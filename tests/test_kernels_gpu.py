@@ -399,6 +399,47 @@ def test_conv_data_movement(cuda_ops, torch_ops, N, H, C):
     assert rel(res[1][1], res[0][1]) < 1e-6 and rel(res[1][2], res[0][2]) < 1e-6
 
 
+@pytest.mark.parametrize("N,H,C,O", [(3, 64, 3, 48), (2, 16, 3, 32), (5, 8, 4, 24), (1, 64, 1, 96), (130, 4, 3, 48), (2, 32, 3, 64)])
+def test_conv_narrow_direct_kernels(cuda_ops, torch_ops, N, H, C, O):
+    """csrc/conv_direct.cu against im2col / col2im + matmul: forward (+ fused channel LayerNorm + SiLU), weight gradient, and the
+    transposed convolution to a narrow-channel image."""
+    rows = N * (H // 2) ** 2
+    x, w = rnd(N * H * H, C), rnd(O, 16 * C, seed=2) * 0.2
+    g, b = rnd(O, seed=3) * 0.2 + 1, rnd(O, seed=4) * 0.1
+    col = torch.zeros(rows, 16 * C, device=DEV)
+    torch_ops.im2col(x, N, H, H, C, col)
+    y_ref = col.double() @ w.double().t()
+    # plain convolution (the decoder's data gradient uses it like this)
+    y = torch.zeros(rows, O, device=DEV)
+    assert cuda_ops.conv_narrow_fwd(x, N, H, H, C, w, y)
+    assert rel(y.double(), y_ref) < 1e-6
+    # with LayerNorm + SiLU
+    y2, act, mean, rstd = torch.zeros(rows, O, device=DEV), torch.zeros(rows, O, device=DEV), torch.zeros(rows, device=DEV), torch.zeros(rows, device=DEV)
+    assert cuda_ops.conv_narrow_fwd(x, N, H, H, C, w, y2, g, b, 1e-3, act, mean, rstd)
+    ln = torch.nn.functional.layer_norm(y_ref, (O,), g.double(), b.double(), 1e-3)
+    assert torch.equal(y2, y)
+    assert rel(act.double(), torch.nn.functional.silu(ln)) < 5e-6
+    assert rel(mean.double(), y_ref.mean(-1)) < 2e-6 and rel(rstd.double(), (y_ref.var(-1, unbiased=False) + 1e-3).rsqrt()) < 5e-6
+    # weight gradient
+    if O <= 64:
+        gy = rnd(rows, O, seed=5)
+        dw = torch.zeros(O, 16 * C, device=DEV)
+        assert cuda_ops.conv_narrow_wgrad(x, N, H, H, C, gy, dw)
+        assert rel(dw.double(), gy.double().t() @ col.double()) < 1e-5
+        dw2 = torch.zeros(O, 16 * C, device=DEV)
+        cuda_ops.conv_narrow_wgrad(x, N, H, H, C, gy, dw2)
+        assert torch.equal(dw, dw2)                       # two-stage reduction in a fixed order
+    # transposed convolution Ci -> C image channels
+    Ci, Hi = (O + 3) // 4 * 4, H // 2
+    xin, wr, bias = rnd(N * Hi * Hi, Ci, seed=6), rnd(Ci, 16 * C, seed=7) * 0.2, rnd(C, seed=8)
+    colT = (xin.double() @ wr.double()).float()
+    ref = torch.zeros(N * H * H, C, device=DEV)
+    torch_ops.col2im(colT, N, Hi, Hi, C, bias, 0.5, ref)
+    out = torch.zeros(N * H * H, C, device=DEV)
+    assert cuda_ops.deconv_narrow_fwd(xin, N, Hi, Hi, wr, C, bias, 0.5, out)
+    assert rel(out, ref) < 5e-6
+
+
 def test_conv_equals_torch_conv(cuda_ops):
     """im2col + GEMM == F.conv2d(k4,s2,p1);  GEMM + col2im == F.conv_transpose2d(k4,s2,p1)  (fp32 mode)."""
     N, H, Cin, Cout = 4, 16, 12, 20
