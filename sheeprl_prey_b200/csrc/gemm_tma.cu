@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <stdlib.h>
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
@@ -259,6 +260,186 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   }
 }
 
+// ---- persistent variant for contractions with more output tiles than resident CTAs (2 per SM) ------------------------------------
+// One CTA walks the tiles w = blockIdx.x, blockIdx.x + gridDim.x, .. (column tile fastest, so the CTAs running together share A
+// rows in L2).  The TMA ring keeps flowing across tile boundaries, and the accumulator is double-buffered in TMEM (2 x BN columns):
+// the MMA warp starts tile j + 1 in the other buffer while the four epilogue warps drain tile j, so neither the epilogue nor the
+// pipeline fill / CTA set-up of the one-tile-per-CTA kernel sits between two main loops.  No split-K here (few-tile shapes stay on
+// the kernel above).
+template <bool A_MN, bool B_MN, int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 2)
+gemm_bf16_tma_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
+                             float* __restrict__ C, int ldc, const float* __restrict__ bias, int accumulate, int tiles_n, int tiles) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * STAGE_A_BYTES;
+  constexpr int SB_BYTES = BN * TBK * 2;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * (STAGE_A_BYTES + SB_BYTES));
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* acc_full = empty_bar + STAGES;          // [2]
+  uint64_t* acc_empty = acc_full + 2;               // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+  const int num_kb = (K + TBK - 1) / TBK;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 4); }     // one arrival per epilogue warp
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr_smem)), "r"(2 * BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  pdl_sync();
+
+  if (warp == 0) {
+    // ===================== TMA producer: one continuous stream of k-blocks over all of this CTA's tiles =====================
+    uint32_t it = 0;
+    for (int w = blockIdx.x; w < tiles; w += gridDim.x) {
+      const int m0 = (w / tiles_n) * TBM, n0 = (w % tiles_n) * BN;
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
+        mbar_wait(&empty_bar[s], ph ^ 1u);
+        if (elect_one_sync()) {
+          mbar_expect_tx(&full_bar[s], STAGE_A_BYTES + SB_BYTES);
+          const int k0 = kb * TBK;
+          if (A_MN) {
+            tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], m0, k0);
+            tma_load_2d(smem_a + s * STAGE_A_BYTES + 8192, &tmA, &full_bar[s], m0 + 64, k0);
+          } else {
+            tma_load_2d(smem_a + s * STAGE_A_BYTES, &tmA, &full_bar[s], k0, m0);
+          }
+          if (B_MN) {
+            tma_load_2d(smem_b + s * SB_BYTES, &tmB, &full_bar[s], n0, k0);
+            if (BN == 128) tma_load_2d(smem_b + s * SB_BYTES + 8192, &tmB, &full_bar[s], n0 + 64, k0);
+          } else {
+            tma_load_2d(smem_b + s * SB_BYTES, &tmB, &full_bar[s], k0, n0);
+          }
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+                           ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+    const uint64_t adesc0 = A_MN ? make_smem_desc_mn(smem_u32(smem_a)) : make_smem_desc(smem_u32(smem_a));
+    const uint64_t bdesc0 = B_MN ? make_smem_desc_mn(smem_u32(smem_b)) : make_smem_desc(smem_u32(smem_b));
+    constexpr uint32_t A_KSTEP = (A_MN ? 2048 : 32) >> 4, B_KSTEP = (B_MN ? 2048 : 32) >> 4;
+    uint32_t it = 0, j = 0;
+    for (int w = blockIdx.x; w < tiles; w += gridDim.x, ++j) {
+      const uint32_t buf = j & 1u;
+      mbar_wait(&acc_empty[buf], ((j >> 1) & 1u) ^ 1u);             // the epilogue has drained this buffer (first use passes)
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t dcol = tmem_base + buf * BN;
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const uint32_t s = it % STAGES, ph = (it / STAGES) & 1u;
+        mbar_wait(&full_bar[s], ph);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint64_t ad = adesc0 + (uint64_t)((uint32_t)(s * STAGE_A_BYTES) >> 4), bd = bdesc0 + (uint64_t)((uint32_t)(s * SB_BYTES) >> 4);
+#pragma unroll
+        for (int k = 0; k < TBK / 16; ++k) {
+          const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+          if (elect_one_sync())
+            asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(dcol),
+                         "l"(ad + (uint64_t)(k * A_KSTEP)), "l"(bd + (uint64_t)(k * B_KSTEP)), "r"(idesc), "r"(accum) : "memory");
+        }
+        if (elect_one_sync()) {
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[s])) : "memory");
+          if (kb == num_kb - 1)
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&acc_full[buf])) : "memory");
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2-5; warp w owns TMEM lanes [32*(w&3), +32)) =====================
+    // tcgen05.ld gives thread = row; stores want lane = column (row-contiguous 128 B per instruction: with thread = row a 192-byte
+    // row stride made every store instruction touch 32 half-used sectors, 4x the output bytes on the L1 -> L2 path, ncu).  The
+    // 32 x 32 block is transposed through a 16-row staging buffer of the warp, two halves (the ring next to it is live).
+    const int ew = warp & 3;
+    float* stg = reinterpret_cast<float*>(tmem_ptr_smem + 4) + ew * (16 * 33);
+    uint32_t j = 0;
+    for (int w = blockIdx.x; w < tiles; w += gridDim.x, ++j) {
+      const uint32_t buf = j & 1u;
+      const int m0 = (w / tiles_n) * TBM, n0 = (w % tiles_n) * BN;
+      mbar_wait(&acc_full[buf], (j >> 1) & 1u);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        if (n0 + c0 >= N) break;
+        uint32_t r[32];
+        const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(ew * 32) << 16) + (uint32_t)c0;
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+              "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+              "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+              "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+            : "r"(taddr));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const int gn = n0 + c0 + lane;
+        const bool col_ok = gn < N;
+        const float bv = (bias && col_ok) ? __ldg(bias + gn) : 0.f;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          if ((lane >> 4) == half) {
+#pragma unroll
+            for (int q = 0; q < 32; ++q) stg[(lane & 15) * 33 + q] = __uint_as_float(r[q]);
+          }
+          __syncwarp();
+          const int rbase = m0 + ew * 32 + half * 16;
+          const int rows_here = col_ok ? min(16, M - rbase) : 0;
+          float* dst0 = C + (size_t)rbase * ldc + gn;
+          const size_t ld = (size_t)ldc;
+          if (__all_sync(0xffffffffu, rows_here == 16)) {
+            float o[16];
+#pragma unroll
+            for (int rr = 0; rr < 16; ++rr) o[rr] = stg[rr * 33 + lane] + bv;
+            if (accumulate) {
+              float old[16];
+#pragma unroll
+              for (int rr = 0; rr < 16; ++rr) old[rr] = dst0[rr * ld];
+#pragma unroll
+              for (int rr = 0; rr < 16; ++rr) dst0[rr * ld] = old[rr] + o[rr];
+            } else {
+#pragma unroll
+              for (int rr = 0; rr < 16; ++rr) dst0[rr * ld] = o[rr];
+            }
+          } else {
+#pragma unroll 1
+            for (int rr = 0; rr < rows_here; ++rr) {
+              const float o = stg[rr * 33 + lane] + bv;
+              float* d = dst0 + rr * ld;
+              *d = accumulate ? (*d + o) : o;
+            }
+          }
+          __syncwarp();
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&acc_empty[buf])) : "memory");
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+  }
+}
+
 // ---- Linear + LayerNorm + SiLU in one kernel ------------------------------------------------------------------------------------
 // y = SiLU(LayerNorm(A . B^T + bias)) for a layer whose N (<= 1024, multiple of 128) output features span CL = N / 128 column tiles:
 // the CL CTAs that own the tiles of one 128-row block form a thread-block cluster.  Main loop as above (TMA ring -> tcgen05.mma ->
@@ -442,12 +623,14 @@ gemm_ln_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 }
 
 constexpr int SMEM_BYTES = STAGES * (STAGE_A_BYTES + STAGE_B_BYTES) + (2 * STAGES + 1) * 8 + 16 + 1024;
+constexpr int SMEM_BYTES_P = SMEM_BYTES + 64 + 4 * 16 * 33 * 4;     // persistent kernel: 4 more barriers + the epilogue's staging
 constexpr int SMEM_BYTES_LN = SMEM_BYTES + 64 + 3 * TBN * 4 + LN_MAX_CL * TBM * 8;
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode = nullptr;
+const bool g_persistent = []() { const char* e = getenv("DV3_GEMM_PERSISTENT"); return !(e && e[0] == '0'); }();
 
 // K-major operand: [rows, K] bf16, K contiguous, row stride ld -> box 64 (k) x 128 (rows).
 // MN-major operand: [K, rows] bf16, rows contiguous, row stride ld -> box 64 (rows) x 64 (k); two boxes per tile.
@@ -501,6 +684,23 @@ int launch_tma_bn(int M, int N, int K, const void* A, int lda, const void* B, in
   int kb_per_split = (total_kb + splits - 1) / splits;
   splits = (total_kb + kb_per_split - 1) / kb_per_split;
   grid.z = splits;
+  if (splits == 1 && g_persistent) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int slots = 2 * sms;
+    if (tiles > slots && (!bias || ((uintptr_t)bias & 15) == 0)) {
+      static unsigned long long configured_p = 0;
+      if (dv3_first_call_on_device(&configured_p)) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_bf16_tma_persist_kernel<A_MN, B_MN, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES_P);
+        if (e != cudaSuccess) return (int)e;
+      }
+      dv3_launch_pdl(gemm_bf16_tma_persist_kernel<A_MN, B_MN, BN>, dim3(slots), dim3(NUM_THREADS), SMEM_BYTES_P, stream, tmA, tmB, M, N, K, C, ldc, bias,
+                     accumulate, (int)grid.x, tiles);
+      DV3_LAUNCH_CHECK();
+      return DV3_OK;
+    }
+  }
   if (splits > 1 && !accumulate) {
     size_t n = (size_t)M * N;
     int zb = (int)((n + 255) / 256);

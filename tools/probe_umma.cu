@@ -224,7 +224,7 @@ __device__ __forceinline__ uint32_t elect_one() {
   return pred;
 }
 template <int VAR, int NACC>
-__global__ void __launch_bounds__(128) t3a_kernel(int N, int nmma, int a_rows_bytes, long long* out) {
+__global__ void __launch_bounds__(128) t3a_kernel(int N, int nmma, int a_rows_bytes, long long* out, int Mrows = 128) {
   extern __shared__ __align__(1024) uint8_t sm[];
   __shared__ uint64_t bar;
   __shared__ uint32_t tmem_slot;
@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(128) t3a_kernel(int N, int nmma, int a_rows_by
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem = tmem_slot;
-  const uint32_t idesc = make_idesc(128, N);
+  const uint32_t idesc = make_idesc(Mrows, N);
   const uint32_t a0 = smem_u32(sm), b0 = smem_u32(sm) + 128 * 1024;
   if (VAR == 0) {
     if (tid == 0) {
@@ -423,7 +423,7 @@ int main(int argc, char** argv) {
     long long* dout; CK(cudaMalloc(&dout, 256 * 8));
     auto run3a = [&](auto kern, const char* name, int N, int rows_bytes) {
       CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      kern<<<1, 128, 200 * 1024>>>(N, 64, rows_bytes, dout);
+      kern<<<1, 128, 200 * 1024>>>(N, 64, rows_bytes, dout, 128);
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("[T3a] failed: %s\n", cudaGetErrorString(e)); exit(4); }
       long long h[6]; CK(cudaMemcpy(h, dout, 48, cudaMemcpyDeviceToHost));
@@ -438,6 +438,19 @@ int main(int argc, char** argv) {
       if (N <= 64) run3a(t3a_kernel<0, 4>, "divergent,4acc", N, 2048);
     }
     run3a(t3a_kernel<1, 4>, "uniform,4acc,packed32", 16, 512);
+    // M = 64 tiles (A k-chunk = 8 row groups x 128 B): does the per-instruction cost follow the A-operand bytes?
+    auto run3m = [&](const char* name, int M, int N, int rows_bytes) {
+      auto kern = t3a_kernel<1, 1>;
+      CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      kern<<<1, 128, 200 * 1024>>>(N, 64, rows_bytes, dout, M);
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { printf("[T3m] failed: %s\n", cudaGetErrorString(e)); exit(4); }
+      long long h[6]; CK(cudaMemcpy(h, dout, 48, cudaMemcpyDeviceToHost));
+      printf("[T3m %s] 64 MMAs M=%d N=%d K=16, A k-chunk stride %d B: issue %lld clk, issue+complete %lld clk (%.1f clk/MMA)\n", name, M, N, rows_bytes,
+             h[4], h[5], h[5] / 64.0);
+    };
+    for (int N : {8, 16, 32, 64}) run3m("uniform,1acc", 64, N, 1024);
+    for (int N : {16, 64}) run3m("uniform,1acc", 128, N, 2048);
     size_t src_bytes = 148ull * (4u << 20);
     uint8_t* src; CK(cudaMalloc(&src, src_bytes)); CK(cudaMemset(src, 1, src_bytes));
     CK(cudaFuncSetAttribute(t3b_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
