@@ -522,7 +522,7 @@ def run_ours(args, rank, world, local_rank):
                 ms2 = r2.timed(lambda i: r2.step_device(), k2)
                 also[tag] = {"workload": WORKLOADS[size]["desc"] + f", B{WORKLOADS[size]['B']}xT{T_SEQ}, H{HORIZON}", "precision": prec,
                              "value": k2 / (ms2 / 1000.0), "unit": "steps/s", "ms_per_step": ms2 / k2, "steps": k2, "warmup": 3,
-                             "scan_kernels": [r2.eng.ops.scan_kernel, r2.eng.ops.bwd_scan_kernel]}
+                             "scan_kernels": [r2.eng.ops.scan_kernel, r2.eng.ops.bwd_scan_kernel], "rollout_kernel": r2.eng.ops.rollout_kernel}
                 del r2
                 torch.cuda.empty_cache()
             except Exception as ex:      # the headline line must survive a failure of the extras
@@ -543,7 +543,7 @@ def run_ours(args, rank, world, local_rank):
                 "dtype": eng.ops.dtype_name, "data": "synthetic",
                 "config": {"workload": wl["desc"] + f", B{B}xT{T}, H{H}", "global_batch": B * world, "seq_len": T,
                            "parallelism": f"dp{world}", "sequences_per_s": value * B, "cuda_graph": graphed,
-                           "scan_kernels": [eng.ops.scan_kernel, eng.ops.bwd_scan_kernel],
+                           "scan_kernels": [eng.ops.scan_kernel, eng.ops.bwd_scan_kernel], "rollout_kernel": eng.ops.rollout_kernel,
                            "replay": f"4 envs x {args.buffer if 'rgb' not in wl['obs'] else min(args.buffer, 16384)} steps per rank, device resident",
                            "l2": f"no explicit flush: the step streams ~{ws_gb:.1f} GB of resident activations/weights/optimizer state, >> 126 MB L2"},
                 "clocks": clocks,
