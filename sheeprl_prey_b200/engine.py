@@ -204,6 +204,12 @@ class DV3Engine:
         head_max = max([o + n for k, (o, n, shp) in wm.offsets.items()
                         if not k.startswith(("observation_model.", "reward_model.", "continue_model."))] or [0])
         self.wm_tail_from = min(tail) if tail and min(tail) >= head_max else 0
+        # first offset of the RSSM parameters (recurrent / representation / transition model): their gradients are complete after the
+        # scan's weight-gradient contractions, before the encoder's backward -- the second early reduction (everything in front of
+        # it must be encoder parameters)
+        rssm = [o for k, (o, n, shp) in wm.offsets.items() if k.startswith("rssm.")]
+        enc_max = max([o + n for k, (o, n, shp) in wm.offsets.items() if k.startswith("encoder.")] or [0])
+        self.wm_mid_from = min(rssm) if rssm and self.wm_tail_from > 0 and min(rssm) >= enc_max and min(rssm) > 0 else 0
         self.keys = list(cfg.mlp_keys.encoder)
         self.cnn_keys = list(cfg.cnn_keys.encoder)
         if list(cfg.cnn_keys.decoder) != self.cnn_keys or list(cfg.mlp_keys.decoder) != self.keys:
@@ -536,6 +542,12 @@ class DV3Engine:
         ops.gemm("TN", self.dfeat_pre, self.x_mlp, Gd["rssm.recurrent_model.mlp._model.0.weight"])
         ops.ln_param_grad(self.dln_feat, self.feat_pre, self.feat_mean, self.feat_rstd,
                           Gd["rssm.recurrent_model.mlp._model.1.weight"], Gd["rssm.recurrent_model.mlp._model.1.bias"])
+        # a15: the RSSM gradients are final: reduce them while the encoder's backward runs; only the encoder's bucket stays exposed
+        if self._wm_pending is not None and 0 < self.wm_mid_from < self.wm_tail_from:
+            h = self._start_reduce(self.wm.grad[self.wm_mid_from:self.wm_tail_from])
+            if h is not None:
+                self._wm_pending.append(h)
+                self._wm_done_from = self.wm_mid_from
         # encoder
         ops.gemm("NN", self.dhidr_pre, self.Wr0[:, D:], self.de)
         if self.cnn_enc is not None:
@@ -623,13 +635,32 @@ class DV3Engine:
         # a10: lambda-returns + discount
         ops.lambda_returns(self.values, self.rewards_img, self.cont_img.out.view(M1), self.dones, H, N, a.gamma, a.lmbda,
                            self.lam, self.discount)
-        # a11: return normalisation
+        # a11 / a15: the other ranks' lambda-values (Moments) travel while the critic's loss and backward run: neither needs them
         mo = a.actor.moments
+        h_lam = None
         if self.dist is not None:
-            self.dist.all_gather(self.lam, self.lam_all)
-            src = self.lam_all
-        else:
-            src = self.lam
+            if hasattr(self.dist, "start_all_gather") and hasattr(self.dist, "start_reduce_mean"):
+                h_lam = self.dist.start_all_gather(self.lam, self.lam_all)
+            else:
+                self.dist.all_gather(self.lam, self.lam_all)
+        overlap = h_lam is not None
+
+        def critic_part():
+            # a13: critic loss (activations of the value pass above; target critic forward)
+            self.tcrit_stack.forward(self.traj[:M0])
+            ops.twohot_mean(self.tcrit_stack.out, self.tvalues)
+            ops.twohot_loss(self.crit_stack.out[:M0], self.lam, self.discount[:M0], 1.0 / M0, self.vl_rows.view(M0), self.d_crit, False)
+            ops.twohot_loss(self.crit_stack.out[:M0], self.tvalues, self.discount[:M0], 1.0 / M0, self.vl_rows.view(M0), self.d_crit, True)
+            ops.reduce_mean(self.vl_rows, 0, self.metrics, _SLOT["Loss/value_loss"], 1.0 / M0, False)
+            _refresh(ops, self.d_crit)
+            self.crit_stack.backward(self.traj, M0, self.d_crit)
+
+        h_critic = None
+        if overlap:        # data parallel: critic first, its reduction then overlaps the actor's loss and backward
+            critic_part()
+            h_critic = self._start_reduce(self.critic.grad)
+            self.dist.finish_reduce(h_lam)
+        src = self.lam_all if self.dist is not None else self.lam
         ops.moments(src, self.mom_state, self.mom_out, mo.decay, mo.max, mo.percentile.low, mo.percentile.high)
         # a12: actor loss on steps 0..H-1 (activations come from the rollout)
         ops.actor_loss(self.act_stack.out[:M0], self.actions_dim, self.act_idx[:M0], self.lam, self.values[:M0], self.discount[:M0],
@@ -637,22 +668,13 @@ class DV3Engine:
         ops.reduce_mean(self.pl_rows, 0, self.metrics, _SLOT["Loss/policy_loss"], 1.0 / M0, False)
         _refresh(ops, self.d_actor_raw)
         self.act_stack.backward(self.traj, M0, self.d_actor_raw)
-        h_actor = self._start_reduce(self.actor.grad)          # overlaps the critic's loss / backward below (independent of the actor update)
-        if h_actor is None:
-            self._optimize(self.actor, "actor", a.actor.clip_gradients, "Grads/actor")
-        # a13: critic loss (activations of the value pass above; target critic forward)
-        self.tcrit_stack.forward(self.traj[:M0])
-        ops.twohot_mean(self.tcrit_stack.out, self.tvalues)
-        ops.twohot_loss(self.crit_stack.out[:M0], self.lam, self.discount[:M0], 1.0 / M0, self.vl_rows.view(M0), self.d_crit, False)
-        ops.twohot_loss(self.crit_stack.out[:M0], self.tvalues, self.discount[:M0], 1.0 / M0, self.vl_rows.view(M0), self.d_crit, True)
-        ops.reduce_mean(self.vl_rows, 0, self.metrics, _SLOT["Loss/value_loss"], 1.0 / M0, False)
-        _refresh(ops, self.d_crit)
-        self.crit_stack.backward(self.traj, M0, self.d_crit)
-        if h_actor is not None:
-            h_critic = self._start_reduce(self.critic.grad)
+        if overlap:
+            h_actor = self._start_reduce(self.actor.grad)
+            self._optimize(self.critic, "critic", a.critic.clip_gradients, "Grads/critic", pending=[h_critic])   # (runs while the actor's bucket travels)
             self._optimize(self.actor, "actor", a.actor.clip_gradients, "Grads/actor", pending=[h_actor])
-            self._optimize(self.critic, "critic", a.critic.clip_gradients, "Grads/critic", pending=[h_critic])
         else:
+            self._optimize(self.actor, "actor", a.actor.clip_gradients, "Grads/actor")
+            critic_part()
             self._optimize(self.critic, "critic", a.critic.clip_gradients, "Grads/critic")
 
     # ------------------------------------------------------------------ whole step

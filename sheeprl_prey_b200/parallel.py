@@ -37,3 +37,8 @@ class TorchDist:
 
     def all_gather(self, src: torch.Tensor, dst: torch.Tensor) -> None:
         dist.all_gather_into_tensor(dst, src)
+
+    def start_all_gather(self, src: torch.Tensor, dst: torch.Tensor):
+        """Asynchronous all_gather (handle for finish_reduce): the lambda-values of Moments travel while the critic's own loss and
+        backward, which do not need the other ranks' values, are computed."""
+        return (dist.all_gather_into_tensor(dst, src, async_op=True), None)

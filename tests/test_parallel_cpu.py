@@ -52,6 +52,7 @@ def _worker(rank, world, port, tmp):
         locals_.append(e.wm.grad.clone())
     mean_grad = sum(locals_) / world
     ok_grad = float((eng.wm.grad - mean_grad).abs().max()) <= 1e-6 * float(mean_grad.abs().max())
+    ok_grad = ok_grad and 0 < eng.wm_mid_from < eng.wm_tail_from and len(eng._wm_pending) == 2     # both early buckets were used
     torch.save(dict(wm=eng.wm.flat.clone(), actor=eng.actor.flat.clone(), critic=eng.critic.flat.clone(), mom=eng.mom_state.clone(),
                     ok_grad=ok_grad, lam_all=eng.lam_all.clone(), lam=eng.lam.clone()), os.path.join(tmp, f"rank{rank}.pt"))
     dist.destroy_process_group()
