@@ -543,7 +543,7 @@ class DV3Engine:
         ops.ln_param_grad(self.dln_feat, self.feat_pre, self.feat_mean, self.feat_rstd,
                           Gd["rssm.recurrent_model.mlp._model.1.weight"], Gd["rssm.recurrent_model.mlp._model.1.bias"])
         # a15: the RSSM gradients are final: reduce them while the encoder's backward runs; only the encoder's bucket stays exposed
-        if self._wm_pending is not None and 0 < self.wm_mid_from < self.wm_tail_from:
+        if self._wm_pending is not None and 0 < self.wm_mid_from < self.wm_tail_from and os.environ.get("DV3_DP_MID_BUCKET", "1") != "0":
             h = self._start_reduce(self.wm.grad[self.wm_mid_from:self.wm_tail_from])
             if h is not None:
                 self._wm_pending.append(h)

@@ -489,7 +489,9 @@ def test_pixel_small_kernels(cuda_ops, torch_ops):
 @pytest.mark.gpu
 @pytest.mark.parametrize("mode", ["NT", "NN", "TN"])
 @pytest.mark.parametrize("M,N,K", [(128, 128, 64), (1024, 512, 512), (1024, 512, 1536), (16384, 512, 1536), (1000, 255, 520),
-                                   (130, 40, 72), (512, 1536, 16384), (4, 512, 15360), (255, 512, 4096)])
+                                   (130, 40, 72), (512, 1536, 16384), (4, 512, 15360), (255, 512, 4096),
+                                   # more tiles than 2 x 148 CTAs: the persistent kernel, with ragged M / N / K, one k-block, 64-wide N
+                                   (40001, 200, 100), (65536, 48, 48), (20000, 130, 72), (9000, 640, 200)])
 def test_gemm_bf16_tma(mode, M, N, K):
     """TMA-fed tcgen05 GEMM on bf16-resident operands: K-major and MN-major operands, ragged sizes (zero-filled by the TMA
     unit), split-K (long K with few output tiles) and accumulate."""
