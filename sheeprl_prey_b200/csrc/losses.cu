@@ -10,6 +10,7 @@
 //   REINFORCE + entropy actor objective        : sheeprl/algos/dreamer_v3/dreamer_v3.py:292-317
 // One warp owns one categorical group / one row; reductions are warp shuffles.
 #include "common.cuh"
+#include <stddef.h>
 #include <cuda_bf16.h>
 
 namespace {
@@ -462,16 +463,26 @@ static __device__ __forceinline__ float key2f(unsigned k) {
   const unsigned u = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
   return __uint_as_float(u);
 }
-// k-th smallest (0-based) of x[0..n): MSB-first 8-bit radix select; all threads of the block participate.
-static __device__ float select_kth(const float* __restrict__ x, int n, int kth, unsigned* hist, unsigned* bcast) {
+// k-th smallest (0-based) of x[0..n): MSB-first 8-bit radix select; all threads of the block participate.  The histogram update is
+// aggregated per warp (match.any on the bin, one atomic per distinct bin): lambda-values share their exponent, so in the first
+// passes nearly every element hits the same bin and plain shared-memory atomics serialise (with the values of 8 ranks gathered, the
+// one-block kernel took several hundred microseconds on the critical path of the data-parallel step).
+static __device__ unsigned select_kth_key(const float* __restrict__ x, int n, int kth, unsigned* hist, unsigned* bcast) {
   unsigned prefix = 0, mask = 0;
   int rank = kth;
+  const int lane = threadIdx.x & 31;
+  const int n_pad = (n + 31) & ~31;                          // whole warps iterate together (match.any needs the full mask)
   for (int shift = 24; shift >= 0; shift -= 8) {
     for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
     __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-      const unsigned key = f2key(x[i]);
-      if ((key & mask) == prefix) atomicAdd(&hist[(key >> shift) & 255u], 1u);
+    for (int i = threadIdx.x; i < n_pad; i += blockDim.x) {
+      unsigned bin = 0xffffffffu;                            // "no contribution"
+      if (i < n) {
+        const unsigned key = f2key(x[i]);
+        if ((key & mask) == prefix) bin = (key >> shift) & 255u;
+      }
+      const unsigned peers = __match_any_sync(0xffffffffu, bin);
+      if (bin != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&hist[bin], (unsigned)__popc(peers));
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -490,14 +501,37 @@ static __device__ float select_kth(const float* __restrict__ x, int n, int kth, 
     rank -= (int)bcast[1];
     __syncthreads();
   }
-  return key2f(prefix);
+  return prefix;
+}
+// the next order statistic after the kth (whose key is `akey`): the same value if at least kth + 2 elements are <= it, else the
+// smallest larger element -- one counting pass instead of a second radix select
+static __device__ unsigned next_after_key(const float* __restrict__ x, int n, int kth, unsigned akey, unsigned* hist, unsigned* bcast) {
+  if (threadIdx.x == 0) { hist[0] = 0u; hist[1] = 0xffffffffu; }
+  __syncthreads();
+  unsigned cnt = 0, mn = 0xffffffffu;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const unsigned key = f2key(x[i]);
+    if (key <= akey) ++cnt;
+    else mn = min(mn, key);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if ((threadIdx.x & 31) == 0) { atomicAdd(&hist[0], cnt); atomicMin(&hist[1], mn); }
+  __syncthreads();
+  const unsigned res = (hist[0] >= (unsigned)(kth + 2)) ? akey : hist[1];
+  __syncthreads();
+  return res;
 }
 static __device__ float quantile_linear(const float* x, int n, float q, unsigned* hist, unsigned* bcast) {
   const float rank = q * (float)(n - 1);       // fp32, like torch.quantile
   const float fl = floorf(rank), ce = ceilf(rank);
   const float w = rank - fl;
-  const float a = select_kth(x, n, (int)fl, hist, bcast);
-  const float b = ((int)ce == (int)fl) ? a : select_kth(x, n, (int)ce, hist, bcast);
+  const unsigned ak = select_kth_key(x, n, (int)fl, hist, bcast);
+  const float a = key2f(ak);
+  const float b = ((int)ce == (int)fl) ? a : key2f(next_after_key(x, n, (int)fl, ak, hist, bcast));
   return (w < 0.5f) ? (a + w * (b - a)) : (b - (b - a) * (1.f - w));  // at::lerp
 }
 __global__ void __launch_bounds__(1024)
@@ -515,6 +549,152 @@ moments_kernel(int n, const float* __restrict__ x, float* __restrict__ state, fl
     out[0] = nl;
     out[1] = fmaxf(1.f / max_, nh - nl);
   }
+}
+
+// ---- Moments, multi-block (n >= 8192: every data-parallel step gathers the lambda-values of all ranks) -----------------------------
+// The one-block kernel above is bound by its dependent global loads (one per thread and iteration, 10 passes): 66 us at 15 360 values,
+// 474 us at the 122 880 values of 8 ranks -- on the critical path of the step.  Here the radix select runs as three grid-wide
+// histogram passes (11 + 11 + 10 key bits; both quantiles share the launches, each block keeps its slice of x in registers), one
+// counting pass for the upper neighbours of the two order statistics, and a one-block finish; the pass-to-pass decisions (which bin
+// holds the rank) are recomputed by every block from the global histograms, so there is no grid barrier.  State lives in a fixed
+// device array of the library (80 KB): calls on one GPU must not overlap; the finishing kernel leaves it zeroed for the next call (it loads as zeros, so the first call needs no set-up).
+constexpr int MQ_BINS = 2048, MQ_THREADS = 256, MQ_PER_THREAD = 16, MQ_MAX_BLOCKS = 148;
+struct MomScratch {
+  unsigned hist[3][2][MQ_BINS];        // [pass][quantile][bin]  (pass 0 is shared: only [0][0] is used)
+  unsigned cnt[2];                     // #{key <= a_q}
+  unsigned mn[2];                      // max{~key : key > a_q}  (0 = no such element; so the zero-initialised array needs no priming)
+};
+static __device__ MomScratch g_mom;
+
+// bin of `hist` (nbins) that holds 0-based rank `rank`; returns the bin, `below` = elements in lower bins.  All threads of the block.
+static __device__ unsigned mq_find_bin(const unsigned* __restrict__ hist, int nbins, unsigned rank, unsigned* below, unsigned* sh) {
+  // sh: [MQ_THREADS + 2] words of shared memory.  Thread t owns `per` consecutive bins; a block-wide prefix sum of the per-thread
+  // totals names the one thread whose bins straddle the rank, and only that thread walks its bins.
+  const int per = nbins / MQ_THREADS;                       // 8 or 4
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned v[8];
+  unsigned local = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { v[j] = (j < per) ? hist[threadIdx.x * per + j] : 0u; local += v[j]; }
+  unsigned incl = local;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const unsigned t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+  if (lane == 31) sh[warp] = incl;
+  __syncthreads();
+  unsigned woff = 0;
+  for (int w2 = 0; w2 < warp; ++w2) woff += sh[w2];
+  const unsigned excl = woff + incl - local;
+  if (rank >= excl && rank < excl + local) {                // exactly one thread (the total exceeds the rank by construction)
+    unsigned acc = excl;
+    int b = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (j < per - 1 && acc + v[j] <= rank && b == j) { acc += v[j]; b = j + 1; }
+    }
+    sh[MQ_THREADS] = (unsigned)(threadIdx.x * per + b);
+    sh[MQ_THREADS + 1] = acc;
+  }
+  __syncthreads();
+  const unsigned bsel = sh[MQ_THREADS];
+  *below = sh[MQ_THREADS + 1];
+  __syncthreads();
+  return bsel;
+}
+// resolves, for quantile q with 0-based rank `rank`, the key prefix after `npass` passes (bits 31..21, 20..10, 9..0)
+static __device__ unsigned mq_prefix(int q, unsigned rank, int npass, unsigned* sh) {
+  unsigned prefix = 0, below;
+  if (npass >= 1) { const unsigned b = mq_find_bin(g_mom.hist[0][0], MQ_BINS, rank, &below, sh); prefix = b << 21; rank -= below; }
+  if (npass >= 2) { const unsigned b = mq_find_bin(g_mom.hist[1][q], MQ_BINS, rank, &below, sh); prefix |= b << 10; rank -= below; }
+  if (npass >= 3) { const unsigned b = mq_find_bin(g_mom.hist[2][q], 1024, rank, &below, sh); prefix |= b; }
+  return prefix;
+}
+// PASS 0..2: histogram pass; PASS 3: counting pass for the upper neighbours
+template <int PASS>
+__global__ void __launch_bounds__(MQ_THREADS) moments_pass_kernel(int n, const float* __restrict__ x, unsigned rank_lo, unsigned rank_hi) {
+  __shared__ unsigned sh[MQ_THREADS + 2];
+  __shared__ unsigned lh[(PASS == 1 || PASS == 2) ? 2 * MQ_BINS : (PASS == 0 ? MQ_BINS : 4)];
+  // this block's slice of x, loaded before anything that depends on earlier passes: all loads are in flight together
+  unsigned key[MQ_PER_THREAD];
+  const int per_block = MQ_THREADS * MQ_PER_THREAD;
+  for (int base = blockIdx.x * per_block; base < n; base += gridDim.x * per_block) {
+#pragma unroll
+    for (int j = 0; j < MQ_PER_THREAD; ++j) {
+      const int i = base + j * MQ_THREADS + threadIdx.x;
+      key[j] = (i < n) ? f2key(x[i]) : 0u;
+    }
+    unsigned p_lo = 0, p_hi = 0;
+    if (PASS > 0) { p_lo = mq_prefix(0, rank_lo, PASS, sh); p_hi = mq_prefix(1, rank_hi, PASS, sh); }
+    if (PASS < 3) {
+      const int nb = (PASS == 0) ? MQ_BINS : 2 * MQ_BINS;
+      for (int i = threadIdx.x; i < nb; i += MQ_THREADS) lh[i] = 0;
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < MQ_PER_THREAD; ++j) {
+        const int i = base + j * MQ_THREADS + threadIdx.x;
+        if (i < n) {
+          const unsigned kk = key[j];
+          if (PASS == 0) atomicAdd(&lh[kk >> 21], 1u);
+          if (PASS == 1) {
+            if ((kk >> 21) == (p_lo >> 21)) atomicAdd(&lh[(kk >> 10) & 2047u], 1u);
+            if ((kk >> 21) == (p_hi >> 21)) atomicAdd(&lh[MQ_BINS + ((kk >> 10) & 2047u)], 1u);
+          }
+          if (PASS == 2) {
+            if ((kk >> 10) == (p_lo >> 10)) atomicAdd(&lh[kk & 1023u], 1u);
+            if ((kk >> 10) == (p_hi >> 10)) atomicAdd(&lh[MQ_BINS + (kk & 1023u)], 1u);
+          }
+        }
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < nb; i += MQ_THREADS) {
+        const unsigned v = lh[i];
+        if (v) atomicAdd(PASS == 0 ? &g_mom.hist[0][0][i] : &g_mom.hist[PASS][i / MQ_BINS][i % MQ_BINS], v);
+      }
+      __syncthreads();
+    } else {
+      unsigned c0 = 0, c1 = 0, m0 = 0u, m1 = 0u;
+#pragma unroll
+      for (int j = 0; j < MQ_PER_THREAD; ++j) {
+        const int i = base + j * MQ_THREADS + threadIdx.x;
+        if (i < n) {
+          const unsigned kk = key[j];
+          if (kk <= p_lo) ++c0; else m0 = max(m0, ~kk);
+          if (kk <= p_hi) ++c1; else m1 = max(m1, ~kk);
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        c0 += __shfl_xor_sync(0xffffffffu, c0, o); c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+        m0 = max(m0, __shfl_xor_sync(0xffffffffu, m0, o)); m1 = max(m1, __shfl_xor_sync(0xffffffffu, m1, o));
+      }
+      if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&g_mom.cnt[0], c0); atomicAdd(&g_mom.cnt[1], c1);
+        atomicMax(&g_mom.mn[0], m0); atomicMax(&g_mom.mn[1], m1);
+      }
+    }
+  }
+}
+__global__ void __launch_bounds__(MQ_THREADS) moments_finish_kernel(int n, unsigned rank_lo, unsigned rank_hi, float w_lo, float w_hi,
+                                                                    float* __restrict__ state, float* __restrict__ out, float decay, float max_) {
+  __shared__ unsigned sh[MQ_THREADS + 2];
+  const unsigned a_lo = mq_prefix(0, rank_lo, 3, sh), a_hi = mq_prefix(1, rank_hi, 3, sh);
+  if (threadIdx.x == 0) {
+    const unsigned b_lo = (g_mom.cnt[0] >= rank_lo + 2u || g_mom.mn[0] == 0u) ? a_lo : ~g_mom.mn[0];
+    const unsigned b_hi = (g_mom.cnt[1] >= rank_hi + 2u || g_mom.mn[1] == 0u) ? a_hi : ~g_mom.mn[1];
+    auto lerp = [](float a, float b, float w) { return (w < 0.5f) ? (a + w * (b - a)) : (b - (b - a) * (1.f - w)); };   // at::lerp
+    const float lo = (w_lo == 0.f) ? key2f(a_lo) : lerp(key2f(a_lo), key2f(b_lo), w_lo);
+    const float hi = (w_hi == 0.f) ? key2f(a_hi) : lerp(key2f(a_hi), key2f(b_hi), w_hi);
+    const float nl = decay * state[0] + (1.f - decay) * lo;
+    const float nh = decay * state[1] + (1.f - decay) * hi;
+    state[0] = nl;
+    state[1] = nh;
+    out[0] = nl;
+    out[1] = fmaxf(1.f / max_, nh - nl);
+  }
+  __syncthreads();
+  // leave the scratch zeroed (min slots at +inf) for the next call
+  unsigned* h = &g_mom.hist[0][0][0];
+  for (int i = threadIdx.x; i < 3 * 2 * MQ_BINS; i += MQ_THREADS) h[i] = 0u;
+  if (threadIdx.x < 2) { g_mom.cnt[threadIdx.x] = 0u; g_mom.mn[threadIdx.x] = 0u; }
 }
 
 // ---------------------------------------------------------------- actor objective (warp = one imagined state)
@@ -705,6 +885,23 @@ int dv3_lambda_returns(int H, int N, const float* values, const float* rewards, 
 }
 int dv3_moments(int n, const float* x, float* state, float* out, float decay, float max_, float plow, float phigh, void* stream) {
   if (n <= 0) return DV3_ERR_ARG;
+  if (n >= 8192) {
+    // ranks and interpolation weights as torch.quantile computes them (fp32)
+    const float r_lo = plow * (float)(n - 1), r_hi = phigh * (float)(n - 1);
+    const float f_lo = floorf(r_lo), f_hi = floorf(r_hi);
+    const float w_lo = (ceilf(r_lo) == f_lo) ? 0.f : r_lo - f_lo, w_hi = (ceilf(r_hi) == f_hi) ? 0.f : r_hi - f_hi;
+    const unsigned k_lo = (unsigned)f_lo, k_hi = (unsigned)f_hi;
+    cudaStream_t st = (cudaStream_t)stream;
+    int blocks = (n + MQ_THREADS * MQ_PER_THREAD - 1) / (MQ_THREADS * MQ_PER_THREAD);
+    if (blocks > MQ_MAX_BLOCKS) blocks = MQ_MAX_BLOCKS;
+    moments_pass_kernel<0><<<blocks, MQ_THREADS, 0, st>>>(n, x, k_lo, k_hi);
+    moments_pass_kernel<1><<<blocks, MQ_THREADS, 0, st>>>(n, x, k_lo, k_hi);
+    moments_pass_kernel<2><<<blocks, MQ_THREADS, 0, st>>>(n, x, k_lo, k_hi);
+    moments_pass_kernel<3><<<blocks, MQ_THREADS, 0, st>>>(n, x, k_lo, k_hi);
+    moments_finish_kernel<<<1, MQ_THREADS, 0, st>>>(n, k_lo, k_hi, w_lo, w_hi, state, out, decay, max_);
+    DV3_LAUNCH_CHECK();
+    return DV3_OK;
+  }
   moments_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(n, x, state, out, decay, max_, plow, phigh);
   DV3_LAUNCH_CHECK();
   return DV3_OK;

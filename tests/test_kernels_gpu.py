@@ -225,6 +225,16 @@ def test_lambda_moments(cuda_ops, torch_ops):
         st, out = torch.zeros(2, device=DEV), torch.zeros(2, device=DEV)
         cuda_ops.moments(x, st, out, 0.0, 1e8, q, q)
         assert float(st[0]) == float(torch.quantile(x, q)), q
+    # ties, sizes that are not multiples of the warp, the all-gathered size of 8 ranks, narrow value ranges (shared exponent bytes)
+    g = torch.Generator().manual_seed(9)
+    cases = [torch.randint(0, 7, (1001,), generator=g).float(), torch.full((333,), 2.5), torch.randn(122880, generator=g) * 0.01 + 3.0,
+             torch.cat((torch.zeros(50), -torch.zeros(50), torch.randn(31, generator=g))), torch.randn(2, generator=g), torch.randn(1, generator=g)]
+    for xc in cases:
+        xc = xc.to(DEV)
+        for ql, qh in ((0.05, 0.95), (0.0, 1.0), (0.5, 0.123)):
+            st, out = torch.zeros(2, device=DEV), torch.zeros(2, device=DEV)
+            cuda_ops.moments(xc, st, out, 0.0, 1e8, ql, qh)
+            assert float(st[0]) == float(torch.quantile(xc, ql)) and float(st[1]) == float(torch.quantile(xc, qh)), (xc.numel(), ql, qh)
 
 
 @pytest.mark.parametrize("heads", [[100], [3, 5], [18], [200, 2]])
