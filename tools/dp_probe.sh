@@ -1,6 +1,6 @@
 #!/bin/bash
 # Reads the cost of the data-parallel collectives off the step time: bench.py at N ranks with collectives dropped (DV3_DP_SKIP, results
-# are wrong then) or NCCL steered differently.  usage: tools/dp_probe.sh N [size]
+# are wrong then) or NCCL steered differently.  usage: tools/dp_probe.sh N [size] [short]
 N=${1:-8}; SZ=${2:-S}
 run() {
   echo -n "$1: "
@@ -12,6 +12,7 @@ b=json.loads(l[-1]) if l else None
 print(round(b['value'],1), round(b['ms_per_step'],3)) if b else print('failed')"
 }
 run "base" "A=1"
+if [ "$3" = "short" ]; then run "no collectives" "DV3_DP_SKIP=reduce,gather"; exit 0; fi
 run "no collectives" "DV3_DP_SKIP=reduce,gather"
 run "no all-reduce" "DV3_DP_SKIP=reduce"
 run "no all-gather" "DV3_DP_SKIP=gather"
