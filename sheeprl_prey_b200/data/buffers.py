@@ -109,7 +109,7 @@ class AsyncReplayBuffer:
         self._buffer_size, self._n_envs = buffer_size, n_envs
         self._device = torch.device(device)
         self._sequential = sequential
-        self._memmap, self._memmap_dir = memmap, memmap_dir   # accepted for signature compatibility; storage is HBM
+        self._memmap, self._memmap_dir = memmap, memmap_dir   # storage is HBM; the directory is used by flush_memmap / load_memmap
         self._store: Optional[Dict[str, Tensor]] = None
         self._pos: List[int] = [0] * n_envs
         self._full: List[bool] = [False] * n_envs
@@ -129,6 +129,56 @@ class AsyncReplayBuffer:
         if self._store is not None:
             dev = self._device if (self._device.type != "cuda" or torch.cuda.is_available()) else torch.device("cpu")
             self._store = {k: v.to(dev) for k, v in self._store.items()}
+
+    # ------------------------------------------------------------------ on-disk copy in the reference's layout
+    # Reference (memmap=True): `memmap_dir/env_{i}/{key}.memmap`, one raw array [buffer_size, 1, *feature] per key and environment
+    # (buffers.py:134-147, :637), plus tensordict's `meta.pt`.  Here the rings live in HBM and sampling never touches the host, so the
+    # files are not the working storage: `flush_memmap()` writes them (a checkpoint of the replay data another process can mmap),
+    # `load_memmap()` reads them back.  `meta.pt` holds what is needed to reopen the raw files: shapes, dtypes, write positions.
+    def flush_memmap(self, memmap_dir=None) -> None:
+        import os
+
+        import numpy as np
+
+        root = memmap_dir if memmap_dir is not None else self._memmap_dir
+        if root is None:
+            raise ValueError("no memmap_dir: pass one here or to the constructor")
+        if self._store is None:
+            raise RuntimeError("the buffer is empty")
+        meta = {"buffer_size": self._buffer_size, "n_envs": self._n_envs, "pos": list(self._pos), "full": list(self._full), "keys": {}}
+        for k, ring in self._store.items():
+            host = ring.cpu()
+            meta["keys"][k] = {"shape": tuple(host.shape[2:]), "dtype": str(host.dtype).replace("torch.", "")}
+            for i in range(self._n_envs):
+                d = os.path.join(str(root), f"env_{i}")
+                os.makedirs(d, exist_ok=True)
+                arr = host[i].unsqueeze(1).contiguous().numpy()                  # [buffer_size, 1, *feature]
+                mm = np.memmap(os.path.join(d, f"{k}.memmap"), dtype=arr.dtype, mode="w+", shape=arr.shape)
+                mm[...] = arr
+                mm.flush()
+                del mm
+        torch.save(meta, os.path.join(str(root), "meta.pt"))
+
+    def load_memmap(self, memmap_dir=None) -> None:
+        import os
+
+        import numpy as np
+
+        root = memmap_dir if memmap_dir is not None else self._memmap_dir
+        meta = torch.load(os.path.join(str(root), "meta.pt"), weights_only=False)
+        if meta["buffer_size"] != self._buffer_size or meta["n_envs"] != self._n_envs:
+            raise ValueError(f"files hold a {meta['buffer_size']} x {meta['n_envs']} buffer, this one is {self._buffer_size} x {self._n_envs}")
+        store = {}
+        for k, info in meta["keys"].items():
+            dt = getattr(torch, info["dtype"])
+            ring = torch.zeros(self._n_envs, self._buffer_size, *info["shape"], dtype=dt, device=self._device)
+            for i in range(self._n_envs):
+                shape = (self._buffer_size, 1, *info["shape"])
+                mm = np.memmap(os.path.join(str(root), f"env_{i}", f"{k}.memmap"), dtype=np.dtype(info["dtype"]), mode="r", shape=shape)
+                ring[i].copy_(torch.from_numpy(np.ascontiguousarray(mm)).squeeze(1))
+                del mm
+            store[k] = ring
+        self._store, self._pos, self._full = store, list(meta["pos"]), list(meta["full"])
 
     # ------------------------------------------------------------------ properties of the reference API
     @property

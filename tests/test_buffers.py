@@ -133,6 +133,31 @@ def test_buffer_pickles_without_the_library_handle():
     assert all(torch.equal(a[k], b[k]) for k in a)
 
 
+def test_memmap_directory_round_trip(tmp_path):
+    """flush_memmap / load_memmap: `memmap_dir/env_{i}/{key}.memmap` raw arrays [buffer_size, 1, *feature] as the reference lays them
+    out (buffers.py:134-147, :637) + meta.pt; a fresh buffer loaded from the directory samples the same sequences."""
+    import numpy as np
+
+    rb = CpuAsync(7, 2, device="cpu", memmap=True, memmap_dir=tmp_path, sequential=True)
+    rb.add({"state": torch.randn(10, 2, 3), "rgb": torch.randint(0, 256, (10, 2, 3, 4, 4), dtype=torch.uint8), "dones": torch.zeros(10, 2, 1)})
+    rb.add({"state": torch.randn(2, 1, 3), "rgb": torch.zeros(2, 1, 3, 4, 4, dtype=torch.uint8), "dones": torch.ones(2, 1, 1)}, [1])
+    rb.flush_memmap()
+    raw = np.memmap(tmp_path / "env_1" / "state.memmap", dtype=np.float32, mode="r", shape=(7, 1, 3))
+    assert np.array_equal(np.asarray(raw)[:, 0], rb._store["state"][1].numpy())
+    assert (tmp_path / "env_0" / "rgb.memmap").stat().st_size == 7 * 3 * 4 * 4
+    rb2 = CpuAsync(7, 2, device="cpu", memmap=True, memmap_dir=tmp_path, sequential=True)
+    rb2.load_memmap()
+    assert rb2._pos == rb._pos and rb2._full == rb._full
+    assert all(torch.equal(rb2._store[k], rb._store[k]) and rb2._store[k].dtype == rb._store[k].dtype for k in rb._store)
+    torch.manual_seed(3)
+    a = rb.sample(4, sequence_length=3)
+    torch.manual_seed(3)
+    b = rb2.sample(4, sequence_length=3)
+    assert all(torch.equal(a[k], b[k]) for k in a)
+    with pytest.raises(ValueError):
+        CpuAsync(8, 2, device="cpu").load_memmap(tmp_path)
+
+
 @pytest.mark.gpu
 def test_gather_with_more_keys_than_one_launch_takes():
     """More than 8 keys (4 bookkeeping keys + many observation keys): the gather is issued in chunks of 8 keys."""
