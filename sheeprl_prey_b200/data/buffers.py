@@ -175,7 +175,7 @@ class AsyncReplayBuffer:
             for i in range(self._n_envs):
                 shape = (self._buffer_size, 1, *info["shape"])
                 mm = np.memmap(os.path.join(str(root), f"env_{i}", f"{k}.memmap"), dtype=np.dtype(info["dtype"]), mode="r", shape=shape)
-                ring[i].copy_(torch.from_numpy(np.ascontiguousarray(mm)).squeeze(1))
+                ring[i].copy_(torch.from_numpy(np.array(mm)).squeeze(1))
                 del mm
             store[k] = ring
         self._store, self._pos, self._full = store, list(meta["pos"]), list(meta["full"])
@@ -253,6 +253,8 @@ class AsyncReplayBuffer:
         if batch_size <= 0 or n_samples <= 0:
             raise ValueError(f"`batch_size` ({batch_size}) and `n_samples` ({n_samples}) must be both greater than 0")
         if self._store is None:
+            if not self._draw_env_counts:      # SequentialReplayBuffer checks "nothing added" first (buffers.py:271-276)
+                raise ValueError("No sample has been added to the buffer. Please add at least one sample calling `self.add()`")
             raise RuntimeError("The buffer has not been initialized. Try to add some data first.")
         if self._draw_env_counts:
             bs_per_buf = torch.bincount(torch.randint(0, self._n_envs, (batch_size,)))      # buffers.py:678
@@ -365,6 +367,18 @@ class SequentialReplayBuffer(AsyncReplayBuffer):
     @property
     def _pos1(self) -> int:
         return self._pos[0]
+
+    @property
+    def full(self) -> bool:                     # a single ring: a bool, as ReplayBuffer.full (buffers.py:71-73)
+        return self._full[0]
+
+    def __getitem__(self, key: str) -> Tensor:
+        """rb[key]: the ring as [buffer_size, 1, *feature] (ReplayBuffer.__getitem__, buffers.py:205-211)."""
+        if not isinstance(key, str):
+            raise TypeError("`key` must be a string")
+        if self._store is None:
+            raise RuntimeError("The buffer has not been initialized. Try to add some data first.")
+        return self._store[key][0].unsqueeze(1)
 
 
 EnvIndependentReplayBuffer = AsyncReplayBuffer

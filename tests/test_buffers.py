@@ -43,8 +43,10 @@ def test_constructor_guards_and_errors():
     with pytest.raises(ValueError):
         AsyncReplayBuffer(1, -1)
     rb = CpuSequential(10, 1, device="cpu")
-    with pytest.raises(RuntimeError):
+    with pytest.raises(ValueError, match="No sample has been added"):        # reference: test_seq_replay_buffer_sample_no_add
         rb.sample(2, sequence_length=2)
+    with pytest.raises(RuntimeError):                                         # the per-environment container reports it as uninitialised
+        CpuAsync(10, 2, device="cpu", sequential=True).sample(2, sequence_length=2)
     rb.add({"t": torch.rand(5, 1, 1)})
     with pytest.raises(ValueError):
         rb.sample(0, sequence_length=2)
@@ -53,11 +55,51 @@ def test_constructor_guards_and_errors():
     assert rb.sample(3, sequence_length=5, n_samples=2)["t"].shape == (2, 5, 3, 1)
 
 
+def test_reference_sequential_buffer_cases():
+    """The reference's tests/test_data/test_sequential_buffer.py cases, on the same class names and calls."""
+    rb = CpuSequential(5, 1, device="cpu")
+    td1, td2, td3 = {"t": torch.rand(2, 1, 1)}, {"t": torch.rand(2, 1, 1)}, {"t": torch.rand(3, 1, 1)}
+    rb.add(td1)
+    rb.add(td2)
+    rb.add(td3)                                                    # test_seq_replay_buffer_add_tds: wraps around
+    assert rb.full
+    assert rb["t"][0] == td3["t"][-2] and rb["t"][1] == td3["t"][-1]
+    torch.testing.assert_close(rb["t"][2:4], td2["t"])
+    rb = CpuSequential(5, 1, device="cpu")
+    td = {"t": torch.rand(6, 1, 1)}
+    rb.add(td)                                                     # test_seq_replay_buffer_add_single_td: oversize add
+    assert rb.full and rb["t"][0] == td["t"][-1]
+    rb = CpuSequential(10, 1, device="cpu")
+    rb.add({"t": torch.rand(11, 1, 1)})
+    assert rb.sample(4, sequence_length=2)["t"].shape == (1, 2, 4, 1)     # test_seq_replay_buffer_sample
+    rb = CpuSequential(1, 1, device="cpu")
+    one = {"t": torch.rand(1, 1, 1)}
+    rb.add(one)                                                    # test_seq_replay_buffer_sample_one_element
+    assert rb.full and rb.sample(1, sequence_length=1)["t"].view(-1) == one["t"].view(-1)
+    with pytest.raises(ValueError):
+        rb.sample(1, sequence_length=2)
+    for seq_len in (50, 1000):                                     # test_seq_replay_buffer_sample_full(_large_sl)
+        size = 10000
+        rb = CpuSequential(size, 1, device="cpu")
+        rb.add({"t": (torch.arange(10500) % size).view(-1, 1, 1)})
+        s = rb.sample(1000, sequence_length=seq_len, n_samples=5)["t"][..., 0]
+        pos = rb._pos[0]
+        assert not torch.logical_and(s[:, 0, :] < pos, s[:, -1, :] >= pos).any()
+        assert not torch.logical_and(s[:, 0, :] >= size + pos - seq_len + 1, s[:, -1, :] < pos).any()
+    rb = CpuSequential(10, 1, device="cpu")
+    rb.add({"t": torch.arange(5).view(-1, 1, 1)})
+    with pytest.raises(ValueError, match="too long sequence length"):     # test_seq_replay_buffer_sample_fail_not_full
+        rb.sample(5, sequence_length=8, n_samples=1)
+    rb = CpuSequential(10, 1, device="cpu")
+    rb.add({"t": torch.arange(7).view(-1, 1, 1) * 1.0})
+    assert (rb.sample(2, sequence_length=5, n_samples=2)["t"] < 7).all()  # test_seq_replay_buffer_sample_not_full
+
+
 def test_sequences_never_straddle_the_write_head():
     size, T = 20, 6
     rb = CpuSequential(size, 1, device="cpu")
     rb.add({"t": torch.arange(27, dtype=torch.float32).view(27, 1, 1)})   # full, pos = 7
-    assert rb.full == (True,) and rb._pos[0] == 7
+    assert rb.full is True and rb._pos[0] == 7
     s = rb.sample(256, sequence_length=T)["t"][0, :, :, 0]                 # [T, 256]
     assert bool((s[1:] - s[:-1] == 1).all())                               # consecutive in time => never crosses pos
     # not full: stays below pos
