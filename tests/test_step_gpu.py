@@ -364,6 +364,9 @@ _CASES = {
     "XS": ("XS", 16, 64, 15, {"state": 4}, [2]),              # BASELINE config 1
     "M-pixels": ("M", 16, 64, 15, {"rgb": (3, 64, 64)}, [18]),  # BASELINE config 3 at its real shape (m = 48, 64x64x3)
     "S-B32": ("S", 32, 16, 15, {"state": 14}, [100]),         # per-rank batch 32 (config 4's batch): two 16-row scan clusters
+    # the shape of the reference's own end-to-end test (tests/test_algos/test_algos.py:561-600: batch 1, sequence 1, horizon 8, 8-wide
+    # layers, cnn multiplier 2, pixels, multi-discrete actions): every fused kernel refuses it, the per-op composition must carry it
+    "ref-e2e-tiny": ("XS", 1, 1, 8, {"rgb": (3, 64, 64)}, [2, 3], dict(deter=8, hidden=8, units=8, layers=1, cnn_mult=2)),
 }
 _ORACLE_CACHE = {}
 
@@ -375,10 +378,10 @@ def _oracle_case(name, doctored):
     actor / critic losses) is incomparable."""
     key = (name, doctored)
     if key not in _ORACLE_CACHE:
-        size, B, T, H, od, acts = _CASES[name]
+        size, B, T, H, od, acts, *extra = _CASES[name]
         cnn = tuple(k for k, d in od.items() if not isinstance(d, int))
         mlp = tuple(k for k, d in od.items() if isinstance(d, int))
-        cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=H, cnn_keys=cnn, mlp_keys=mlp)
+        cfg = make_cfg(size, batch_size=B, sequence_length=T, horizon=H, cnn_keys=cnn, mlp_keys=mlp, **(extra[0] if extra else {}))
         params = random_params_like(cfg, od, acts, seed=11)
         if doctored:
             params["wm"][f"continue_model._model.{3 * cfg.algo.world_model.discount_model.mlp_layers}.bias"] += 4.0
@@ -391,7 +394,7 @@ def _oracle_case(name, doctored):
 
 
 def _run_forced(ops, name, doctored):
-    size, B, T, H, od, acts = _CASES[name]
+    size, B, T, H, od, acts = _CASES[name][:6]
     cfg, params, data, noise, out = _oracle_case(name, doctored)
     eng = engine_from_params(cfg, od, acts, _dev_params(params), ops, DEV)
     eng.load_batch(_to(data, DEV))
@@ -419,7 +422,7 @@ def test_step_bf16_tensor_core_mode_within_2e2(name, resident):
     read through TMA (gemm_tma.cu), tcgen05 scan kernels; every contraction first checks that its mirrors equal bf16(fp32 operand)."""
     from sheeprl_prey_b200._lib import CudaOps
 
-    size, B, T, H, od, acts = _CASES[name]
+    size, B, T, H, od, acts = _CASES[name][:6]
     N = T * B
     ops = CudaOps(DEV, precision="bf16", scratch_bytes=(64 << 20) if "pixels" in name else (32 << 20))
     ops.use_mirrors = resident
@@ -477,7 +480,7 @@ def test_step_bf16_on_undoctored_weights(name):
     around the threshold."""
     from sheeprl_prey_b200._lib import CudaOps
 
-    size, B, T, H, od, acts = _CASES[name]
+    size, B, T, H, od, acts = _CASES[name][:6]
     N = T * B
     ops = CudaOps(DEV, precision="bf16")
     eng, out = _run_forced(ops, name, doctored=False)
@@ -508,10 +511,10 @@ def test_step_bf16_on_undoctored_weights(name):
             assert v < 2e-2, (k, rep)
 
 
-@pytest.mark.parametrize("name", ["M-pixels", "S-B32"])
+@pytest.mark.parametrize("name", ["M-pixels", "S-B32", "ref-e2e-tiny"])
 def test_step_fp32_matches_oracle_at_config_shapes(cuda_ops, name):
     """fp32 mode at BASELINE config 3's real shape (M, 64x64x3 pixels, m = 48, B16 x T64) and at per-rank batch 32."""
-    size, B, T, H, od, acts = _CASES[name]
+    size, B, T, H, od, acts = _CASES[name][:6]
     N = T * B
     eng, out = _run_forced(cuda_ops, name, doctored=True)
     md = eng.metrics_dict()
