@@ -43,7 +43,8 @@ constexpr int A_BYTES = RM * KB * 2;    // 16 KB
 constexpr int NMAX = 192;               // most output features per CTA and stage
 constexpr int B_BYTES = NMAX * KB * 2;  // 24 KB
 constexpr int NEPI = 512;               // 16 epilogue warps: 4 per TMEM lane quadrant, each taking a quarter of the stage's columns
-constexpr int NTHR = 64 + NEPI;         // warp 0 producer, warp 1 MMA, warps 2-17 epilogue
+constexpr int NTHR = 96 + NEPI;         // warp 0 activation producer, warp 1 MMA, warps 2-17 epilogue, warp 18 weight producer
+constexpr int PB_WARP = 18;             // (a TMA issue costs ~160 clk: one warp feeding both operands bounded the short-K stages)
 constexpr int MAXL = DV3_ROLLOUT_MAX_LAYERS;
 constexpr int MAXCL = 16;
 
@@ -180,7 +181,9 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
   const int a_slice_row = c * (RM / CL);
   const uint32_t a_slice_off = (uint32_t)a_slice_row * KB * 2;
   const uint16_t mc_mask = (uint16_t)((1u << CL) - 1u);
-  auto produce = [&](const Stage& st) {
+  // two producer warps share the ring: warp 0 arms the slot's barrier and loads (multicasts) the activation rows, warp PB_WARP loads
+  // the weight boxes; both wait for the slot on the same empty barrier and advance the same ring position
+  auto produce = [&](const Stage& st, bool weights) {
     const int nk0 = st.K0 / KB, nk = nk0 + st.K1 / KB;
     const uint32_t bytes = A_BYTES + (uint32_t)st.nb * st.b_rows * KB * 2;
 #pragma unroll 1
@@ -190,12 +193,16 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       for (int kb = 0; kb < nk; ++kb) {
         mbar_wait(&empty_bar[pp.slot], pp.phase ^ 1u);
         if (elect_one()) {
-          mbar_expect_tx(&full_bar[pp.slot], bytes);
-          const uint32_t da = smem_u32(ring_a + pp.slot * A_BYTES), db = smem_u32(ring_b + pp.slot * B_BYTES);
-          // own RM / CL rows of the activation tile, multicast into the same slot of every CTA of the cluster (this GPU's memory only)
-          if (kb < nk0) tma_load_2d_mc(da + a_slice_off, st.a0, &full_bar[pp.slot], st.a0_col + kb * KB, st.a0_row + a_slice_row, mc_mask);
-          else tma_load_2d_mc(da + a_slice_off, st.a1, &full_bar[pp.slot], st.a1_col + (kb - nk0) * KB, st.a1_row + a_slice_row, mc_mask);
-          for (int j = 0; j < st.nb; ++j) tma_load_2d(db + (uint32_t)j * st.b_rows * KB * 2, st.b, &full_bar[pp.slot], kb * KB, st.b_row[j] + roff);
+          if (!weights) {
+            mbar_expect_tx(&full_bar[pp.slot], bytes);
+            const uint32_t da = smem_u32(ring_a + pp.slot * A_BYTES);
+            // own RM / CL rows of the activation tile, multicast into the same slot of every CTA of the cluster (this GPU's memory only)
+            if (kb < nk0) tma_load_2d_mc(da + a_slice_off, st.a0, &full_bar[pp.slot], st.a0_col + kb * KB, st.a0_row + a_slice_row, mc_mask);
+            else tma_load_2d_mc(da + a_slice_off, st.a1, &full_bar[pp.slot], st.a1_col + (kb - nk0) * KB, st.a1_row + a_slice_row, mc_mask);
+          } else {
+            const uint32_t db = smem_u32(ring_b + pp.slot * B_BYTES);
+            for (int j = 0; j < st.nb; ++j) tma_load_2d(db + (uint32_t)j * st.b_rows * KB * 2, st.b, &full_bar[pp.slot], kb * KB, st.b_row[j] + roff);
+          }
         }
         __syncwarp();
         if (++pp.slot == NSTG) { pp.slot = 0; pp.phase ^= 1u; }
@@ -414,7 +421,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       else { st.a0 = &k.m_act[l - 1]; st.a0_col = 0; st.a0_row = arow; st.K0 = Ua; }
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
       st.b = &k.m_wa[l]; st.nb = 1; st.b_row[0] = au0; st.b_rows = aper; st.n_pad = aper; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
-      if (warp == 0) produce(st);
+      if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
@@ -430,7 +437,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       st.b = &k.m_wh; st.nb = 1; st.b_row[0] = 0; st.b_rows = A; st.n_pad = (A + 15) & ~15; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
       // every CTA runs the head's loads and MMAs (the ring positions and the cluster-wide slot barriers stay in lockstep); only CTA 0
       // has an epilogue: all action logits of a row live there
-      if (warp == 0) produce(st);
+      if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
@@ -516,7 +523,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       st.a0 = &k.m_traj; st.a0_col = 0; st.a0_row = prow; st.K0 = S;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
       st.b = &k.m_wz; st.nb = 1; st.b_row[0] = u0; st.b_rows = uper; st.n_pad = uper; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
-      if (warp == 0) produce(st);
+      if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
@@ -533,7 +540,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       st.a1 = &k.m_feat; st.a1_col = 0; st.a1_row = row_blk; st.K1 = U;
       st.b = &k.m_wgru; st.nb = 3; st.b_row[0] = d0; st.b_row[1] = D + d0; st.b_row[2] = 2 * D + d0; st.b_rows = dpp; st.n_pad = 3 * dpp;
       st.npass = dper / dpp; st.pass_row_step = dpp; st.pass_tmem_step = 3 * dpp;
-      if (warp == 0) produce(st);
+      if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
@@ -593,7 +600,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       st.a0 = &k.m_traj; st.a0_col = S; st.a0_row = crow; st.K0 = D;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
       st.b = &k.m_wt0; st.nb = 1; st.b_row[0] = h0; st.b_rows = hper; st.n_pad = hper; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
-      if (warp == 0) produce(st);
+      if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
@@ -607,7 +614,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       st.a0 = &k.m_thid; st.a0_col = 0; st.a0_row = row_blk; st.K0 = Hh;
       st.a1 = nullptr; st.a1_col = st.a1_row = st.K1 = 0;
       st.b = &k.m_wt1; st.nb = 1; st.b_row[0] = s0; st.b_rows = sper; st.n_pad = sper; st.npass = 1; st.pass_row_step = st.pass_tmem_step = 0;
-      if (warp == 0) produce(st);
+      if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
         wait_acc();
