@@ -38,7 +38,7 @@ namespace {
 
 constexpr int RM = 128;                 // rows per block = M of the MMA
 constexpr int KB = 64;                  // k per ring stage (one 128 B swizzle row of bf16)
-constexpr int NSTG = 4;
+constexpr int NSTG = 4;                 // (5 stages fit and were measured: no change, the stages are not bound by the load round trip)
 constexpr int A_BYTES = RM * KB * 2;    // 16 KB
 constexpr int NMAX = 192;               // most output features per CTA and stage
 constexpr int B_BYTES = NMAX * KB * 2;  // 24 KB
@@ -222,14 +222,13 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
         mbar_wait(&full_bar[pp.slot], pp.phase);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint64_t ad = ad0 + (uint64_t)((pp.slot * A_BYTES) >> 4), bd = bd0 + (uint64_t)((pp.slot * B_BYTES) >> 4);
+        if (elect_one()) {              // one election per k-block: the four MMAs and the commits are issued by the same lane
 #pragma unroll
-        for (int kk = 0; kk < KB / 16; ++kk) {
-          const uint32_t accum = (kb > 0 || kk > 0) ? 1u : 0u;
-          if (elect_one())
+          for (int kk = 0; kk < KB / 16; ++kk) {
+            const uint32_t accum = (kb > 0 || kk > 0) ? 1u : 0u;
             asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(dcol),
                          "l"(ad + (uint64_t)(kk * 2)), "l"(bd + (uint64_t)(kk * 2)), "r"(idesc), "r"(accum) : "memory");
-        }
-        if (elect_one()) {
+          }
           asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(&empty_bar[pp.slot])),
                        "h"(mc_mask) : "memory");
           if (last_pass && kb == nk - 1)
