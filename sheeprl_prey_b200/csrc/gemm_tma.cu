@@ -173,10 +173,10 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       mbar_wait(&full_bar[s], ph);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint64_t ad = adesc0 + (uint64_t)((uint32_t)(s * STAGE_A_BYTES) >> 4), bd = bdesc0 + (uint64_t)((uint32_t)(s * SB_BYTES) >> 4);
+      if (elect_one_sync()) {          // one election per k-block (measured in rollout_tc.cu: per-instruction elections cost ~25 % of the loop)
 #pragma unroll
-      for (int k = 0; k < TBK / 16; ++k) {
-        const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
-        if (elect_one_sync())
+        for (int k = 0; k < TBK / 16; ++k) {
+          const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
           asm volatile(
               "{\n"
               ".reg .pred p;\n"
@@ -185,8 +185,7 @@ gemm_bf16_tma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
               "}\n" ::"r"(tmem_base),
               "l"(ad + (uint64_t)(k * A_KSTEP)), "l"(bd + (uint64_t)(k * B_KSTEP)), "r"(idesc), "r"(accum)
               : "memory");
-      }
-      if (elect_one_sync()) {
+        }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[s])) : "memory");
         if (kb == num_kb - 1)
           asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(tmem_full_bar)) : "memory");
@@ -346,14 +345,13 @@ gemm_bf16_tma_persist_kernel(const __grid_constant__ CUtensorMap tmA, const __gr
         mbar_wait(&full_bar[s], ph);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint64_t ad = adesc0 + (uint64_t)((uint32_t)(s * STAGE_A_BYTES) >> 4), bd = bdesc0 + (uint64_t)((uint32_t)(s * SB_BYTES) >> 4);
+        if (elect_one_sync()) {
 #pragma unroll
-        for (int k = 0; k < TBK / 16; ++k) {
-          const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
-          if (elect_one_sync())
+          for (int k = 0; k < TBK / 16; ++k) {
+            const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
             asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}\n" ::"r"(dcol),
                          "l"(ad + (uint64_t)(k * A_KSTEP)), "l"(bd + (uint64_t)(k * B_KSTEP)), "r"(idesc), "r"(accum) : "memory");
-        }
-        if (elect_one_sync()) {
+          }
           asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&empty_bar[s])) : "memory");
           if (kb == num_kb - 1)
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&acc_full[buf])) : "memory");

@@ -206,13 +206,12 @@ __device__ __forceinline__ void mma_seg(const Plan& pl, int si, uint32_t bbuf, u
     const uint64_t bd0 = desc_ns(bbuf + bk8 * brow, brow);
     const uint32_t dcol = tmem_base + col + tile * NB;
     const uint32_t astep = lbo16 * 2, bstep = (2 * brow) >> 4;       // one MMA = K 16 = two 8-wide k chunks
-    uint32_t acc = (fresh && k0 == 0) ? 0u : 1u;
+    const uint32_t acc0 = (fresh && k0 == 0) ? 0u : 1u;
+    if (elect_one()) {                 // one election per chunk: its MMAs and the slot's commit are issued by the same lane
 #pragma unroll 4
-    for (uint32_t j = 0; j < nmma; ++j) {
-      if (elect_one()) umma_n16(dcol, ad0 + (uint64_t)(j * astep), bd0 + (uint64_t)(j * bstep), idesc, acc);
-      acc = 1u;
+      for (uint32_t j = 0; j < nmma; ++j) umma_n16(dcol, ad0 + (uint64_t)(j * astep), bd0 + (uint64_t)(j * bstep), idesc, j == 0 ? acc0 : 1u);
+      umma_commit(&rg.empty[pos.slot]);
     }
-    if (elect_one()) umma_commit(&rg.empty[pos.slot]);
     __syncwarp();
     ring_advance(pos, rg.nslots);
   }
