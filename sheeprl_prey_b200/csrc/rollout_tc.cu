@@ -272,6 +272,25 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
 #pragma unroll
     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
   };
+  // three 8-column loads (the GRU's three gates) in flight, one wait
+  auto ld8x3 = [&](int c0, int c1, int c2, float* v0, float* v1, float* v2) {
+    uint32_t r[24];
+    const int cols[3] = {c0, c1, c2};
+#pragma unroll
+    for (int g = 0; g < 3; ++g)
+      asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+                   : "=r"(r[8 * g]), "=r"(r[8 * g + 1]), "=r"(r[8 * g + 2]), "=r"(r[8 * g + 3]), "=r"(r[8 * g + 4]), "=r"(r[8 * g + 5]),
+                     "=r"(r[8 * g + 6]), "=r"(r[8 * g + 7])
+                   : "r"(t_lane + (uint32_t)cols[g]));
+#pragma unroll
+    for (int g = 0; g < 3; ++g)
+      asm volatile("tcgen05.wait::ld.sync.aligned;"
+                   : "+r"(r[8 * g]), "+r"(r[8 * g + 1]), "+r"(r[8 * g + 2]), "+r"(r[8 * g + 3]), "+r"(r[8 * g + 4]), "+r"(r[8 * g + 5]),
+                     "+r"(r[8 * g + 6]), "+r"(r[8 * g + 7])
+                   :: "memory");
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { v0[j] = __uint_as_float(r[j]); v1[j] = __uint_as_float(r[8 + j]); v2[j] = __uint_as_float(r[16 + j]); }
+  };
   auto st8_f32 = [](float* dst, const float* v) {
     *reinterpret_cast<float4*>(dst) = make_float4(v[0], v[1], v[2], v[3]);
     *reinterpret_cast<float4*>(dst + 4) = make_float4(v[4], v[5], v[6], v[7]);
@@ -439,6 +458,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
+        const float u_head = (c != 0) ? 0.f : ((i == 0) ? a.u_act0[(size_t)(row_blk + rl)] : a.u_act[(size_t)(i - 1) * N + row_blk + rl]);
         wait_acc();
         if (c == 0) {
           // this thread: logits [32 cq, 32 cq + 32) of the row, in registers (one TMEM pass, one exponential per logit); the four
@@ -485,8 +505,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
           float before = 0.f, tot = 0.f;
 #pragma unroll
           for (int qq = 0; qq < 4; ++qq) { const float mq = red[qq * RM + rl].x; tot += mq; if (qq < cq) before += mq; }
-          const float u = (i == 0) ? a.u_act0[(size_t)(row_blk + rl)] : a.u_act[(size_t)(i - 1) * N + row_blk + rl];
-          const float thr = u * tot;                   // idx = #{k : cumsum_k(p) / tot <= u}
+          const float thr = u_head * tot;                   // idx = #{k : cumsum_k(p) / tot <= u}
           float cs = before;
           int cnt = 0;
 #pragma unroll
@@ -525,9 +544,9 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
-        wait_acc();
         int aidx[1];
-        aidx[0] = a.act_idx[gp];
+        aidx[0] = a.act_idx[gp];                          // (loaded in the shadow of the MMAs)
+        wait_acc();
         ln_silu_epilogue(uper, nullptr, a.g_mlp, a.b_mlp, 1e-3f, a.W_mlpaT, a.ld_mlpaT, aidx, nullptr, nullptr, feat16, U, (size_t)lrow, u0, nullptr, nullptr);
       }
       end_stage();
@@ -558,9 +577,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
 #pragma unroll 1
         for (int c0 = 0; c0 < dq; c0 += 8) {
           float vr[8], vc[8], vu[8];
-          ld8(gate_col(db + c0, 0), vr);
-          ld8(gate_col(db + c0, 1), vc);
-          ld8(gate_col(db + c0, 2), vu);
+          ld8x3(gate_col(db + c0, 0), gate_col(db + c0, 1), gate_col(db + c0, 2), vr, vc, vu);
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             s += vr[j] + vc[j] + vu[j];
@@ -573,9 +590,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
 #pragma unroll 1
         for (int c0 = 0; c0 < dq; c0 += 8) {
           float vr[8], vc[8], vu[8], hv[8], hn[8];
-          ld8(gate_col(db + c0, 0), vr);
-          ld8(gate_col(db + c0, 1), vc);
-          ld8(gate_col(db + c0, 2), vu);
+          ld8x3(gate_col(db + c0, 0), gate_col(db + c0, 1), gate_col(db + c0, 2), vr, vc, vu);
           lds8(stg1 + rl * hpitch + db + c0, hv);
           const int d = d0 + db + c0;
 #pragma unroll
@@ -616,6 +631,8 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
       if (warp == 0 || warp == PB_WARP) produce(st, warp == PB_WARP);
       else if (warp == 1) issue(st);
       else {
+        // the first group's uniform is fetched in the shadow of the MMAs (one uncoalesced L2 round trip per thread)
+        const float uz_first = (!a.f_z && cq < gper) ? a.u_z[((size_t)(i - 1) * N + row_blk + rl) * G + c * gper + cq] : 0.f;
         wait_acc();
 #pragma unroll 1
         for (int gl = cq; gl < gper; gl += 4) {
@@ -653,7 +670,7 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
               x[j] = (j < Kc) ? ((a.unimix > 0.f) ? fminf(fmaxf((1.f - a.unimix) * p + mixk, DV3_EPS32), 1.f - DV3_EPS32) : p) : 0.f;
               tot += x[j];
             }
-            const float thr = a.u_z[zi] * tot;         // idx = #{k : cumsum_k(p) / tot <= u}
+            const float thr = ((gl == cq) ? uz_first : a.u_z[zi]) * tot;         // idx = #{k : cumsum_k(p) / tot <= u}
             float cs = 0.f;
             idx = 0;
 #pragma unroll
