@@ -420,7 +420,10 @@ __global__ void __launch_bounds__(NTHR, 1) rollout_tc_kernel(const __grid_consta
     // this CTA's global stores (generic proxy) must be visible to the peers' TMA loads (async proxy) of the next stage
     RDBG();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    asm volatile("fence.proxy.async;" ::: "memory");
+    if (warp >= 2 && warp != PB_WARP) {          // only the epilogue warps wrote anything (global results, staging tiles in the ring)
+      asm volatile("fence.proxy.async.global;" ::: "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
     cluster_sync_all();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   };
