@@ -8,9 +8,10 @@
 // The N rows are independent, so the kernel splits them into blocks of 128 rows (the M of tcgen05.mma) and gives each block to one
 // thread-block cluster of CL CTAs; CTA c owns 1/CL of the output features of every layer.  A rollout step is a chain of 7 dense
 // layers; each is run as a "stage":
-//     producer warp : TMA (SWIZZLE_128B boxes) of the 128-row activation tile [128 x 64 k] and of this CTA's weight rows [n_own x 64 k]
-//                     into an mbarrier ring;
-//     MMA warp      : tcgen05.mma M128 x N n_own x K16, fp32 accumulator in TMEM;
+//     producer warps: TMA (SWIZZLE_128B boxes) of the 128-row activation tile [128 x 64 k] (warp 0) and of this CTA's weight rows
+//                     [n_own x 64 k] (warp 18) into one mbarrier ring;
+//     MMA warp      : tcgen05.mma M128 x N n_own x K16, fp32 accumulator in TMEM; the four MMAs of a k-block and its commits are
+//                     issued under one elect.sync (an election per instruction cost a quarter of the issue loop);
 //     epilogue warps: 16 warps, thread = (row, quarter of the CTA's columns); ONE TMEM -> register pass per stage; bias / one-hot
 //                     action gather; LayerNorm statistics over the CTA's columns (partials of the four quarters through shared
 //                     memory), exchanged with the peers by st.async on the receiver's mbarrier; normalise, SiLU / GRU gates /
