@@ -10,6 +10,7 @@ dv3_xs_b16t64.npz : BASELINE.json config 1 at its real shape (DreamerV3-XS, obs 
               run for two gradient steps on seeded parameters / batch / noise that the tests regenerate from the seeds
               (tests/util.py::random_params_like, oracle/harness.py), so the file holds only results: the 13 metrics, Moments,
               every drawn index (uint8) and per-tensor parameter norms before and after.
+episode_buffer.pt : a scripted add / evict / sample session on the reference EpisodeBuffer (buffers.py:342-525)
 buffers.pt  : a scripted add/sample session on the reference AsyncReplayBuffer(sequential=True) under a fixed
               torch seed (everything added, every sampled batch).
 """
@@ -209,11 +210,56 @@ def make_buffer_golden():
     torch.save(sessions, os.path.join(GOLDEN_DIR, "buffers.pt"))
 
 
+def episode_session(make_buffer, make_episode=lambda d, L: d):
+    """The scripted EpisodeBuffer session behind tests/golden/episode_buffer.pt: adds with eviction, plain and end-prioritised samples.
+    `make_buffer(size, sl)` builds the buffer under test, `make_episode(dict, L)` wraps an episode in the container it expects."""
+    torch.manual_seed(4321)
+    g = torch.Generator().manual_seed(8)
+    size, sl = 60, 7
+    rb = make_buffer(size, sl)
+    samples = []
+
+    def add(L):
+        d = {"state": torch.randn(L, 3, generator=g), "rgb": torch.randint(0, 256, (L, 2, 3, 3), generator=g, dtype=torch.uint8),
+             "dones": torch.zeros(L, 1)}
+        d["dones"][-1] = 1
+        rb.add(make_episode(d, L))
+
+    def sample(bs, n, ends=False):
+        s = rb.sample(bs, n_samples=n, prioritize_ends=ends)
+        samples.append({k: s[k].clone() for k in s.keys()})
+
+    for L in (9, 14, 7):
+        add(L)
+    sample(5, 2)
+    add(22)
+    sample(4, 1, ends=True)
+    add(19)                  # 9 + 14 + 7 + 22 + 19 > 60: the two oldest episodes go
+    sample(6, 3)
+    add(60)                  # an episode as long as the buffer evicts everything else
+    sample(3, 2, ends=True)
+    add(8)
+    sample(7, 1)
+    return dict(size=size, sl=sl, samples=samples, lengths=[int(e.shape[0]) for e in rb.buffer], total=len(rb), full=bool(rb.full))
+
+
+def make_episode_golden():
+    dv3, agent, loss, utils, buffers, dist = ref_shim.ref_modules()
+    import warnings
+
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        sess = episode_session(lambda size, sl: buffers.EpisodeBuffer(size, sl, device="cpu", memmap=False),
+                               lambda d, L: ref_shim.TD(d, batch_size=[L]))
+    torch.save(sess, os.path.join(GOLDEN_DIR, "episode_buffer.pt"))
+
+
 if __name__ == "__main__":
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     make_step_golden()
     make_step_golden(PIX_CFG, PIX_OBS, PIX_ACTIONS, "dv3_step_pixels.pt")
     make_buffer_golden()
+    make_episode_golden()
     make_baseline_golden()
     for f in sorted(os.listdir(GOLDEN_DIR)):
         print(f, os.path.getsize(os.path.join(GOLDEN_DIR, f)))
